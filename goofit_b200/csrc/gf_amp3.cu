@@ -1,0 +1,267 @@
+// gf_amp3.cu — Amp3Body caches: per-event resonance waves and the normalisation-grid integrals.
+//   k_amp3_waves  all flagged resonances in ONE pass over the events, SoA out   (Amp3Body.cu:288-310,
+//                 detail/SpecialResonanceCalculator.cu:12-46 launched once per resonance in the reference)
+//   k_amp3_grid   every flagged B_i and the efficiency at each grid bin, once   (detail/SpecialResonanceIntegrator.cu:52-121
+//   k_amp3_gram   I_ij = sum_bins B_i conj(B_j) eff, one block per pair          evaluates both amplitudes per pair per bin)
+#include "gf_internal.cuh"
+#include "gf_res.cuh"
+
+struct gf_amp3_state {
+    int node = -1, n_res = 0, slot = -1;
+    long ld = 0, n_events = 0;
+    double2 *d_waves = nullptr;
+    // normalisation grid cache
+    long n_bins = 0;
+    double spec[6] = {0, 0, 0, 0, 0, 0};
+    double2 *d_gridB = nullptr; // [n_res][n_bins]
+    double *d_gridEff = nullptr;
+    double *d_I = nullptr;      // [n_res*n_res*2]
+    bool grid_valid = false;
+};
+
+static gf_amp3_state *find_amp3(gf_ctx *c, int node, bool create) {
+    for(auto *s : c->amp3)
+        if(s->node == node) return s;
+    if(!create) return nullptr;
+    auto *s = new gf_amp3_state();
+    s->node = node;
+    c->amp3.push_back(s);
+    return s;
+}
+
+void gf_amp3_free(gf_ctx *c) {
+    for(auto *s : c->amp3) {
+        cudaFree(s->d_waves); cudaFree(s->d_gridB); cudaFree(s->d_gridEff); cudaFree(s->d_I);
+        delete s;
+    }
+    c->amp3.clear();
+}
+
+__device__ inline gf_decay3 gf_load_decay3(const double *c) {
+    gf_decay3 D;
+    D.M = c[0]; D.d1 = c[1]; D.d2 = c[2]; D.d3 = c[3]; D.rad = c[4]; D.mrad = c[5];
+    return D;
+}
+
+__global__ void __launch_bounds__(GF_THREADS, 2)
+    k_amp3_waves(const gf_dev_view V, int node, unsigned long long mask, double2 *waves, long ld) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    gf_sprog P = gf_stage_program(V, smem);
+    __syncthreads();
+    const gf_node &nd = P.nodes[node];
+    const int32_t *in = P.ints + nd.int_off;
+    const int32_t *ob = P.ints + nd.obs_off;
+    const int nres = in[1];
+    const gf_decay3 D = gf_load_decay3(P.consts + nd.con_off);
+    const double *c12 = P.cols[ob[0]], *c13 = P.cols[ob[1]];
+    const long stride = (long)gridDim.x * blockDim.x;
+    for(long e = (long)blockIdx.x * blockDim.x + threadIdx.x; e < V.n_events; e += stride) {
+        double m12 = __ldg(c12 + e), m13 = __ldg(c13 + e);
+        bool inside = gf_in_dalitz(m12, m13, D.M, D.d1, D.d2, D.d3);
+        double m23 = D.M * D.M + D.d1 * D.d1 + D.d2 * D.d2 + D.d3 * D.d3 - m12 - m13;
+        for(int i = 0; i < nres; ++i) {
+            if(!((mask >> i) & 1ull)) continue;
+            double2 w = make_double2(0.0, 0.0);
+            if(inside) w = gf_resonance(P.nodes[in[2 + i]], P.params, P.consts, D, m12, m13, m23);
+            waves[(size_t)i * ld + e] = w;
+        }
+    }
+}
+
+// Bin centres as SpecialResonanceIntegrator.cu:60-77, including its use of the m12 bin count for the
+// m13 step (slot [2] read twice) — identical for square grids.
+__global__ void __launch_bounds__(GF_THREADS, 2)
+    k_amp3_grid(const gf_dev_view V, int node, int eff_first, int eff_root, unsigned long long mask, double lo12,
+                double hi12, int n12, double lo13, double hi13, long n_bins, double2 *gridB, double *gridEff) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    gf_sprog P = gf_stage_program(V, smem);
+    __syncthreads();
+    const gf_node &nd = P.nodes[node];
+    const int32_t *in = P.ints + nd.int_off;
+    const int32_t *ob = P.ints + nd.obs_off;
+    const int nres = in[1];
+    const gf_decay3 D = gf_load_decay3(P.consts + nd.con_off);
+    const long stride = (long)gridDim.x * blockDim.x;
+    for(long b = (long)blockIdx.x * blockDim.x + threadIdx.x; b < n_bins; b += stride) {
+        int b12 = (int)(b % n12);
+        long b13 = b / n12;
+        double m12 = hi12 - lo12;
+        m12 /= n12;
+        m12 *= (b12 + 0.5);
+        m12 += lo12;
+        double m13 = hi13 - lo13;
+        m13 /= n12;
+        m13 *= (b13 + 0.5);
+        m13 += lo13;
+        bool inside = gf_in_dalitz(m12, m13, D.M, D.d1, D.d2, D.d3);
+        double m23 = D.M * D.M + D.d1 * D.d1 + D.d2 * D.d2 + D.d3 * D.d3 - m12 - m13;
+        for(int i = 0; i < nres; ++i) {
+            if(!((mask >> i) & 1ull)) continue;
+            double2 w = make_double2(0.0, 0.0);
+            if(inside) w = gf_resonance(P.nodes[in[2 + i]], P.params, P.consts, D, m12, m13, m23);
+            gridB[(size_t)i * n_bins + b] = w;
+        }
+        gf_evt_vals evt;
+#pragma unroll
+        for(int k = 0; k < GF_MAX_OBS; k++) evt.v[k] = 0;
+        evt.i = b;
+        evt.v[ob[0]] = m12;
+        evt.v[ob[1]] = m13;
+        gridEff[b] = gf_eval_tree(P, V, eff_first, eff_root, evt);
+    }
+}
+
+// One block per (i,j), i<=j: sum over bins of B_i * conj(B_j) * eff in a fixed order.
+__global__ void __launch_bounds__(GF_THREADS)
+    k_amp3_gram(const double2 *gridB, const double *gridEff, long n_bins, int nres, const int *pairs, double *I) {
+    __shared__ double red[32];
+    const int i = pairs[2 * blockIdx.x], j = pairs[2 * blockIdx.x + 1];
+    const double2 *Bi = gridB + (size_t)i * n_bins, *Bj = gridB + (size_t)j * n_bins;
+    double sr = 0, si = 0;
+    for(long b = threadIdx.x; b < n_bins; b += blockDim.x) {
+        double2 a = Bi[b], c = Bj[b];
+        double e = gridEff[b];
+        double pr = a.x * c.x + a.y * c.y; // a * conj(c)
+        double pi = a.y * c.x - a.x * c.y;
+        sr += pr * e;
+        si += pi * e;
+    }
+    double r = gf_block_sum(sr, red);
+    double q = gf_block_sum(si, red);
+    if(threadIdx.x == 0) {
+        I[2 * (i * nres + j)] = r;
+        I[2 * (i * nres + j) + 1] = q;
+        if(i != j) { // Hermitian: I_ji = conj(I_ij)
+            I[2 * (j * nres + i)] = r;
+            I[2 * (j * nres + i) + 1] = -q;
+        }
+    }
+}
+
+static int amp3_check(gf_ctx *c, int node, gf_amp3_state **out, bool create) {
+    if(!c) return gf_fail("null ctx");
+    if(node < 0 || node >= (int)c->h_nodes.size() || c->h_nodes[node].op != GF_OP_AMP3)
+        return gf_fail("gf_amp3: node is not an Amp3Body record");
+    const gf_node &nd = c->h_nodes[node];
+    if(nd.nint < 2 || nd.ncon < 6 || nd.nobs < 3) return gf_fail("gf_amp3: malformed Amp3Body record");
+    int nres = c->h_ints[nd.int_off + 1];
+    if(nres < 1 || nres > 64 || nd.nint < 2 + nres) return gf_fail("gf_amp3: 1..64 resonances");
+    int slot = c->h_ints[nd.int_off];
+    if(slot < 0 || slot >= GF_MAX_AUX) return gf_fail("gf_amp3: bad aux slot");
+    gf_amp3_state *s = find_amp3(c, node, create);
+    if(!s) return gf_fail("gf_amp3: gf_amp3_alloc not called for this node");
+    s->n_res = nres;
+    s->slot = slot;
+    *out = s;
+    return 0;
+}
+
+extern "C" int gf_amp3_alloc(gf_ctx *c, int node, size_t n_events) {
+    gf_amp3_state *s;
+    if(amp3_check(c, node, &s, true)) return 1;
+    cudaSetDevice(c->device);
+    GF_CUDA(cudaStreamSynchronize(c->stream));
+    cudaFree(s->d_waves);
+    s->d_waves = nullptr;
+    s->n_events = (long)n_events;
+    s->ld = (long)((n_events + 15) & ~size_t(15));
+    if(s->ld == 0) s->ld = 16;
+    GF_CUDA(cudaMalloc(&s->d_waves, sizeof(double2) * (size_t)s->ld * s->n_res));
+    GF_CUDA(cudaMemsetAsync(s->d_waves, 0, sizeof(double2) * (size_t)s->ld * s->n_res, c->stream));
+    if(!s->d_I) GF_CUDA(cudaMalloc(&s->d_I, sizeof(double) * 2 * s->n_res * s->n_res));
+    c->view.aux[s->slot] = s->d_waves;
+    c->view.aux_ld[s->slot] = s->ld;
+    return 0;
+}
+
+static unsigned long long mask_of(const uint8_t *redo, int n) {
+    unsigned long long m = 0;
+    for(int i = 0; i < n; i++)
+        if(!redo || redo[i]) m |= (1ull << i);
+    return m;
+}
+
+extern "C" int gf_amp3_cache_waves(gf_ctx *c, int node, const uint8_t *redo_mask) {
+    gf_amp3_state *s;
+    if(amp3_check(c, node, &s, false)) return 1;
+    if(s->n_events != c->view.n_events) return gf_fail("gf_amp3_cache_waves: cache size != uploaded events");
+    unsigned long long mask = mask_of(redo_mask, s->n_res);
+    if(!mask || s->n_events == 0) return 0;
+    cudaSetDevice(c->device);
+    size_t sm = gf_prog_smem(c);
+    if(sm > 48 * 1024) cudaFuncSetAttribute(k_amp3_waves, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    int blocks = gf_grid_blocks(c, s->n_events, 2);
+    k_amp3_waves<<<blocks, GF_THREADS, sm, c->stream>>>(c->view, node, mask, s->d_waves, s->ld);
+    c->launches++;
+    GF_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int gf_amp3_integrals(gf_ctx *c, int node, const uint8_t *redo_mask, const double *lo_hi_n6, int eff_root,
+                                 double *I_re_im) {
+    gf_amp3_state *s;
+    if(amp3_check(c, node, &s, false)) return 1;
+    if(eff_root < 0 || eff_root >= (int)c->h_nodes.size()) return gf_fail("gf_amp3_integrals: bad efficiency root");
+    cudaSetDevice(c->device);
+    int n12 = (int)std::floor(lo_hi_n6[2] + 0.5), n13 = (int)std::floor(lo_hi_n6[5] + 0.5);
+    if(n12 < 1 || n13 < 1) return gf_fail("gf_amp3_integrals: bins < 1");
+    long n_bins = (long)n12 * n13;
+    bool same = s->grid_valid && s->n_bins == n_bins;
+    for(int k = 0; k < 6 && same; k++) same = (s->spec[k] == lo_hi_n6[k]);
+    unsigned long long mask = mask_of(redo_mask, s->n_res);
+    if(!same) {
+        GF_CUDA(cudaStreamSynchronize(c->stream));
+        cudaFree(s->d_gridB); cudaFree(s->d_gridEff);
+        s->d_gridB = nullptr; s->d_gridEff = nullptr;
+        GF_CUDA(cudaMalloc(&s->d_gridB, sizeof(double2) * (size_t)n_bins * s->n_res));
+        GF_CUDA(cudaMalloc(&s->d_gridEff, sizeof(double) * (size_t)n_bins));
+        s->n_bins = n_bins;
+        for(int k = 0; k < 6; k++) s->spec[k] = lo_hi_n6[k];
+        mask = mask_of(nullptr, s->n_res); // new grid: everything
+        s->grid_valid = true;
+    }
+    size_t sm = gf_prog_smem(c);
+    if(sm > 48 * 1024) cudaFuncSetAttribute(k_amp3_grid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    int eff_first = eff_root - c->h_nodes[eff_root].size + 1;
+    // As in the reference, integrals (and the efficiency they fold in) are refreshed only for flagged
+    // resonances; with nothing flagged the cached I_ij are returned (Amp3Body.cu:266-275,313-316).
+    if(mask) {
+        int blocks = gf_grid_blocks(c, n_bins, 2);
+        k_amp3_grid<<<blocks, GF_THREADS, sm, c->stream>>>(c->view, node, eff_first, eff_root, mask, lo_hi_n6[0],
+                                                          lo_hi_n6[1], n12, lo_hi_n6[3], lo_hi_n6[4], n_bins,
+                                                          s->d_gridB, s->d_gridEff);
+        c->launches++;
+        GF_CUDA(cudaGetLastError());
+    }
+    // pairs whose integral must be refreshed: either member flagged (Amp3Body.cu:313-316)
+    std::vector<int> pairs;
+    for(int i = 0; i < s->n_res; i++)
+        for(int j = i; j < s->n_res; j++)
+            if(((mask >> i) & 1ull) || ((mask >> j) & 1ull)) { pairs.push_back(i); pairs.push_back(j); }
+    if(!pairs.empty()) {
+        int *d_pairs = nullptr;
+        GF_CUDA(cudaMalloc(&d_pairs, sizeof(int) * pairs.size()));
+        GF_CUDA(cudaMemcpyAsync(d_pairs, pairs.data(), sizeof(int) * pairs.size(), cudaMemcpyHostToDevice, c->stream));
+        k_amp3_gram<<<(int)(pairs.size() / 2), GF_THREADS, 0, c->stream>>>(s->d_gridB, s->d_gridEff, n_bins, s->n_res,
+                                                                         d_pairs, s->d_I);
+        c->launches++;
+        GF_CUDA(cudaGetLastError());
+        GF_CUDA(cudaStreamSynchronize(c->stream));
+        cudaFree(d_pairs);
+    }
+    GF_CUDA(cudaMemcpyAsync(I_re_im, s->d_I, sizeof(double) * 2 * s->n_res * s->n_res, cudaMemcpyDeviceToHost, c->stream));
+    GF_CUDA(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+extern "C" int gf_amp3_get_wave(gf_ctx *c, int node, int res, double *out_re_im, size_t n_events) {
+    gf_amp3_state *s;
+    if(amp3_check(c, node, &s, false)) return 1;
+    if(res < 0 || res >= s->n_res) return gf_fail("gf_amp3_get_wave: bad resonance index");
+    if((long)n_events != s->n_events) return gf_fail("gf_amp3_get_wave: size mismatch");
+    cudaSetDevice(c->device);
+    GF_CUDA(cudaMemcpyAsync(out_re_im, s->d_waves + (size_t)res * s->ld, sizeof(double2) * n_events,
+                            cudaMemcpyDeviceToHost, c->stream));
+    GF_CUDA(cudaStreamSynchronize(c->stream));
+    return 0;
+}

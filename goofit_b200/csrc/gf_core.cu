@@ -1,0 +1,448 @@
+// gf_core.cu — context, program/param upload, SoA dataset upload, and the three generic kernels:
+//   k_eval_sum    fused evaluate -> metric -> deterministic grid reduction   (GooPdf.cu:45-78, MetricTaker.cu:17-44)
+//   k_eval_events per-event metric values                                    (GooPdf.cu:112-173)
+//   k_grid_sum    mid-point grid integral of a subtree                       (GooPdf.cu:83-108, MetricTaker.cu:48-96)
+// No Thrust, no function pointers, no CPU fallback: every entry point fails loudly without a device.
+#include "gf_internal.cuh"
+#include <algorithm>
+#include <cmath>
+
+static thread_local std::string g_err;
+void gf_set_error(const std::string &s) { g_err = s; }
+int gf_fail(const std::string &s) {
+    g_err = s;
+    return 1;
+}
+extern "C" const char *gf_last_error(void) { return g_err.c_str(); }
+extern "C" int gf_version(void) { return 100; }
+
+size_t gf_prog_smem(const gf_ctx *c) {
+    return gf_sprog_bytes((int)c->h_nodes.size(), c->n_params, (int)c->h_consts.size(), c->n_norms, (int)c->h_ints.size());
+}
+int gf_grid_blocks(const gf_ctx *c, long n_items, int per_sm) {
+    long need = (n_items + GF_THREADS - 1) / GF_THREADS;
+    long cap = (long)c->sm_count * per_sm;
+    long b = std::min(need, cap);
+    if(b < 1) b = 1;
+    return (int)b;
+}
+int gf_alloc_aux_slot(gf_ctx *c) {
+    for(int i = 0; i < GF_MAX_AUX; i++)
+        if(c->view.aux[i] == nullptr && c->view.aux_ld[i] == 0) {
+            c->view.aux_ld[i] = -1; // reserved
+            return i;
+        }
+    return -1;
+}
+
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(GF_THREADS, 4)
+    k_eval_sum(const gf_dev_view V, int first, int root, int metric, int n_cols, double *partials, unsigned *ticket,
+               double *out) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ double red[32];
+    gf_sprog P = gf_stage_program(V, smem);
+    __syncthreads();
+    const double norm = P.norms[P.nodes[root].norm_slot];
+    double acc = 0;
+    gf_evt_soa evt{P.cols, V.identity_mask, 0};
+    const long stride = (long)gridDim.x * blockDim.x;
+    for(long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < V.n_events; i += stride) {
+        evt.i = i;
+        double raw = gf_eval_tree(P, V, first, root, evt);
+        acc += gf_metric(metric, raw, norm, evt, V, n_cols);
+    }
+    gf_grid_finish(&acc, 1, partials, ticket, out, red);
+}
+
+__global__ void __launch_bounds__(GF_THREADS, 4)
+    k_eval_events(const gf_dev_view V, int first, int root, int metric, int n_cols, double *out) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    gf_sprog P = gf_stage_program(V, smem);
+    __syncthreads();
+    const double norm = P.norms[P.nodes[root].norm_slot];
+    gf_evt_soa evt{P.cols, V.identity_mask, 0};
+    const long stride = (long)gridDim.x * blockDim.x;
+    for(long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < V.n_events; i += stride) {
+        evt.i = i;
+        double raw = gf_eval_tree(P, V, first, root, evt);
+        out[i] = gf_metric(metric, raw, norm, evt, V, n_cols);
+    }
+}
+
+struct gf_grid_spec {
+    double lo[GF_MAX_OBS], hi[GF_MAX_OBS];
+    int nb[GF_MAX_OBS];
+    int col[GF_MAX_OBS];
+    int nobs;
+    long total;
+};
+
+// Bin-centre arithmetic exactly as MetricTaker.cu:75-88: x = (hi-lo)/n * (bin+0.5) + lo, x fastest.
+// Reference quirk kept: every dimension's centre is written to the slot of the subtree root's FIRST
+// observable (`events[id] = x` with id fixed, MetricTaker.cu:73,85) — exact for 1-D integrals,
+// which is all the reference's own configs use.
+__global__ void __launch_bounds__(GF_THREADS, 4)
+    k_grid_sum(const gf_dev_view V, int first, int root, gf_grid_spec G, double *partials, unsigned *ticket,
+               double *out) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ double red[32];
+    gf_sprog P = gf_stage_program(V, smem);
+    __syncthreads();
+    double acc = 0;
+    const long stride = (long)gridDim.x * blockDim.x;
+    for(long b = (long)blockIdx.x * blockDim.x + threadIdx.x; b < G.total; b += stride) {
+        gf_evt_vals evt;
+#pragma unroll
+        for(int k = 0; k < GF_MAX_OBS; k++) evt.v[k] = 0;
+        evt.i = b;
+        long bin = b;
+        for(int d = 0; d < G.nobs; ++d) {
+            int local = (int)(bin % G.nb[d]);
+            double x = G.hi[d] - G.lo[d];
+            x /= G.nb[d];
+            x *= (local + 0.5);
+            x += G.lo[d];
+            evt.v[G.col[0]] = x;
+            bin /= G.nb[d];
+        }
+        acc += gf_eval_tree(P, V, first, root, evt);
+    }
+    gf_grid_finish(&acc, 1, partials, ticket, out, red);
+}
+
+__global__ void k_check_identity(const double *col, long n, int *flag) {
+    long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if(i < n && col[i] != (double)i) *flag = 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+extern "C" gf_ctx *gf_create(int device_id) {
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if(e != cudaSuccess || ndev <= 0) {
+        gf_fail(std::string("gf_create: no CUDA device (") + cudaGetErrorString(e) + "); this library has no CPU path");
+        return nullptr;
+    }
+    if(device_id < 0 || device_id >= ndev) {
+        gf_fail("gf_create: bad device id");
+        return nullptr;
+    }
+    if(cudaSetDevice(device_id) != cudaSuccess) {
+        gf_fail("gf_create: cudaSetDevice failed");
+        return nullptr;
+    }
+    auto *c = new gf_ctx();
+    c->device = device_id;
+    cudaDeviceProp prop;
+    cudaGetDeviceProperties(&prop, device_id);
+    c->sm_count = prop.multiProcessorCount;
+    cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+    cudaEventCreate(&c->ev0);
+    cudaEventCreate(&c->ev1);
+    c->max_blocks = c->sm_count * 16;
+    cudaMalloc(&c->d_partials, sizeof(double) * GF_NPARTIAL * c->max_blocks);
+    cudaMalloc(&c->d_ticket, sizeof(unsigned) * 8);
+    cudaMemset(c->d_ticket, 0, sizeof(unsigned) * 8);
+    cudaMalloc(&c->d_result, sizeof(double) * GF_NPARTIAL * 64);
+    cudaMemset(c->d_result, 0, sizeof(double) * GF_NPARTIAL * 64);
+    cudaMallocHost(&c->h_result, sizeof(double) * GF_NPARTIAL * 64);
+    if(cudaGetLastError() != cudaSuccess) {
+        gf_fail("gf_create: allocation failed");
+        delete c;
+        return nullptr;
+    }
+    return c;
+}
+
+void gf_amp3_free(gf_ctx *c);
+void gf_amp4_free(gf_ctx *c);
+void gf_conv_free(gf_ctx *c);
+
+static void free_cols(gf_ctx *c) {
+    if(c->d_cols_base && c->cols_owned) cudaFree(c->d_cols_base);
+    c->d_cols_base = nullptr;
+    for(auto &p : c->view.cols) p = nullptr;
+    c->view.n_events = 0;
+}
+
+extern "C" void gf_destroy(gf_ctx *c) {
+    if(!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    gf_amp3_free(c);
+    gf_amp4_free(c);
+    gf_conv_free(c);
+    free_cols(c);
+    cudaFree(c->d_nodes); cudaFree(c->d_params); cudaFree(c->d_consts); cudaFree(c->d_norms); cudaFree(c->d_ints);
+    cudaFree(c->d_partials); cudaFree(c->d_ticket); cudaFree(c->d_result); cudaFree(c->d_events_out);
+    cudaFreeHost(c->h_result);
+    if(c->h_pin) cudaFreeHost(c->h_pin);
+    cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1);
+    cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+extern "C" int gf_device_info(gf_ctx *c, int *sm_count, size_t *free_bytes, size_t *total_bytes) {
+    if(!c) return gf_fail("null ctx");
+    cudaSetDevice(c->device);
+    if(sm_count) *sm_count = c->sm_count;
+    size_t f = 0, t = 0;
+    GF_CUDA(cudaMemGetInfo(&f, &t));
+    if(free_bytes) *free_bytes = f;
+    if(total_bytes) *total_bytes = t;
+    return 0;
+}
+
+extern "C" int gf_set_program(gf_ctx *c, const gf_node *nodes, int n_nodes, const double *consts, int n_consts,
+                              const int32_t *ints, int n_ints, int n_params, int n_norms) {
+    if(!c) return gf_fail("null ctx");
+    if(n_nodes <= 0 || n_params < 0 || n_norms <= 0) return gf_fail("gf_set_program: bad sizes");
+    cudaSetDevice(c->device);
+    // validate: stack depth, ranges
+    for(int k = 0; k < n_nodes; k++) {
+        const gf_node &nd = nodes[k];
+        if(nd.par_off < 0 || nd.par_off + nd.npar > n_params) return gf_fail("gf_set_program: param range, node " + std::to_string(k));
+        if(nd.con_off < 0 || nd.con_off + nd.ncon > n_consts) return gf_fail("gf_set_program: const range, node " + std::to_string(k));
+        if(nd.obs_off < 0 || nd.obs_off + nd.nobs > n_ints) return gf_fail("gf_set_program: obs range, node " + std::to_string(k));
+        if(nd.int_off < 0 || nd.int_off + nd.nint > n_ints) return gf_fail("gf_set_program: int range, node " + std::to_string(k));
+        if(nd.norm_slot < 0 || nd.norm_slot >= n_norms) return gf_fail("gf_set_program: norm slot, node " + std::to_string(k));
+        if(nd.size < 1 || nd.size > k + 1) return gf_fail("gf_set_program: subtree size, node " + std::to_string(k));
+        if(nd.nobs > GF_MAX_OBS) return gf_fail("gf_set_program: too many observables");
+    }
+    c->h_nodes.assign(nodes, nodes + n_nodes);
+    c->h_consts.assign(consts, consts + n_consts);
+    c->h_ints.assign(ints, ints + n_ints);
+    c->n_params = n_params;
+    c->n_norms = n_norms;
+    if(gf_prog_smem(c) > 160 * 1024) return gf_fail("gf_set_program: program block exceeds shared memory");
+    cudaStreamSynchronize(c->stream);
+    cudaFree(c->d_nodes); cudaFree(c->d_params); cudaFree(c->d_consts); cudaFree(c->d_norms); cudaFree(c->d_ints);
+    GF_CUDA(cudaMalloc(&c->d_nodes, sizeof(gf_node) * n_nodes));
+    GF_CUDA(cudaMalloc(&c->d_params, sizeof(double) * std::max(1, n_params)));
+    GF_CUDA(cudaMalloc(&c->d_consts, sizeof(double) * std::max(1, n_consts)));
+    GF_CUDA(cudaMalloc(&c->d_norms, sizeof(double) * n_norms));
+    GF_CUDA(cudaMalloc(&c->d_ints, sizeof(int32_t) * std::max(1, n_ints)));
+    GF_CUDA(cudaMemcpy(c->d_nodes, nodes, sizeof(gf_node) * n_nodes, cudaMemcpyHostToDevice));
+    if(n_consts) GF_CUDA(cudaMemcpy(c->d_consts, consts, sizeof(double) * n_consts, cudaMemcpyHostToDevice));
+    if(n_ints) GF_CUDA(cudaMemcpy(c->d_ints, ints, sizeof(int32_t) * n_ints, cudaMemcpyHostToDevice));
+    GF_CUDA(cudaMemset(c->d_params, 0, sizeof(double) * std::max(1, n_params)));
+    {
+        std::vector<double> ones(n_norms, 1.0);
+        GF_CUDA(cudaMemcpy(c->d_norms, ones.data(), sizeof(double) * n_norms, cudaMemcpyHostToDevice));
+    }
+    size_t need = sizeof(double) * (size_t)(n_params + n_norms + 16);
+    if(need > c->h_pin_cap) {
+        if(c->h_pin) cudaFreeHost(c->h_pin);
+        GF_CUDA(cudaMallocHost(&c->h_pin, need));
+        c->h_pin_cap = need;
+    }
+    gf_dev_view &V = c->view;
+    V.nodes = c->d_nodes; V.params = c->d_params; V.consts = c->d_consts; V.norms = c->d_norms; V.ints = c->d_ints;
+    V.n_nodes = n_nodes; V.n_params = n_params; V.n_consts = n_consts; V.n_norms = n_norms; V.n_ints = n_ints;
+    size_t sm = gf_prog_smem(c);
+    if(sm > 48 * 1024) {
+        cudaFuncSetAttribute(k_eval_sum, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        cudaFuncSetAttribute(k_eval_events, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        cudaFuncSetAttribute(k_grid_sum, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    }
+    return 0;
+}
+
+extern "C" int gf_set_params(gf_ctx *c, const double *params, int n) {
+    if(!c) return gf_fail("null ctx");
+    if(n != c->n_params) return gf_fail("gf_set_params: expected " + std::to_string(c->n_params) + " got " + std::to_string(n));
+    if(n == 0) return 0;
+    cudaSetDevice(c->device);
+    // the pinned block may still be in flight from the previous call
+    GF_CUDA(cudaStreamSynchronize(c->stream));
+    std::memcpy(c->h_pin, params, sizeof(double) * n);
+    GF_CUDA(cudaMemcpyAsync(c->d_params, c->h_pin, sizeof(double) * n, cudaMemcpyHostToDevice, c->stream));
+    return 0;
+}
+
+extern "C" int gf_set_norms(gf_ctx *c, const double *norms, int n) {
+    if(!c) return gf_fail("null ctx");
+    if(n != c->n_norms) return gf_fail("gf_set_norms: size mismatch");
+    cudaSetDevice(c->device);
+    GF_CUDA(cudaStreamSynchronize(c->stream));
+    double *dst = c->h_pin + c->n_params;
+    std::memcpy(dst, norms, sizeof(double) * n);
+    GF_CUDA(cudaMemcpyAsync(c->d_norms, dst, sizeof(double) * n, cudaMemcpyHostToDevice, c->stream));
+    return 0;
+}
+
+static int finish_columns(gf_ctx *c, int n_cols, size_t n_events, double total_events) {
+    gf_dev_view &V = c->view;
+    V.n_events = (long)n_events;
+    V.total_events = total_events;
+    c->n_cols = n_cols;
+    V.identity_mask = 0;
+    if(n_events > 0) {
+        int *d_flag = nullptr;
+        GF_CUDA(cudaMalloc(&d_flag, sizeof(int) * GF_MAX_OBS));
+        std::vector<int> ones(GF_MAX_OBS, 1);
+        GF_CUDA(cudaMemcpyAsync(d_flag, ones.data(), sizeof(int) * GF_MAX_OBS, cudaMemcpyHostToDevice, c->stream));
+        int blocks = (int)((n_events + 255) / 256);
+        for(int k = 0; k < n_cols; k++) {
+            k_check_identity<<<blocks, 256, 0, c->stream>>>(V.cols[k], (long)n_events, d_flag + k);
+            c->launches++;
+        }
+        std::vector<int> flags(GF_MAX_OBS, 0);
+        GF_CUDA(cudaMemcpyAsync(flags.data(), d_flag, sizeof(int) * GF_MAX_OBS, cudaMemcpyDeviceToHost, c->stream));
+        GF_CUDA(cudaStreamSynchronize(c->stream));
+        cudaFree(d_flag);
+        for(int k = 0; k < n_cols; k++)
+            if(flags[k]) V.identity_mask |= (1u << k);
+    }
+    return 0;
+}
+
+extern "C" int gf_upload_columns(gf_ctx *c, const double *const *cols, int n_cols, size_t n_events, double total_events) {
+    if(!c) return gf_fail("null ctx");
+    if(n_cols < 0 || n_cols > GF_MAX_OBS) return gf_fail("gf_upload_columns: 0..16 columns");
+    cudaSetDevice(c->device);
+    GF_CUDA(cudaStreamSynchronize(c->stream));
+    free_cols(c);
+    c->cols_owned = true;
+    size_t ld = (n_events + 31) & ~size_t(31); // 256-B aligned columns
+    if(ld == 0) ld = 32;
+    c->view.ld = (long)ld;
+    GF_CUDA(cudaMalloc(&c->d_cols_base, sizeof(double) * ld * std::max(1, n_cols)));
+    // pinned staging in 32 MiB chunks so pageable user memory streams at full PCIe/C2C rate
+    const size_t chunk = size_t(4) << 20; // doubles
+    double *stage[2] = {nullptr, nullptr};
+    cudaEvent_t done[2];
+    if(n_events > 0) {
+        for(int b = 0; b < 2; b++) {
+            GF_CUDA(cudaMallocHost(&stage[b], sizeof(double) * std::min(chunk, n_events)));
+            cudaEventCreateWithFlags(&done[b], cudaEventDisableTiming);
+        }
+    }
+    int buf = 0;
+    for(int k = 0; k < n_cols; k++) {
+        c->view.cols[k] = c->d_cols_base + (size_t)k * ld;
+        for(size_t off = 0; off < n_events; off += chunk) {
+            size_t n = std::min(chunk, n_events - off);
+            cudaEventSynchronize(done[buf]);
+            std::memcpy(stage[buf], cols[k] + off, sizeof(double) * n);
+            GF_CUDA(cudaMemcpyAsync(c->d_cols_base + (size_t)k * ld + off, stage[buf], sizeof(double) * n,
+                                    cudaMemcpyHostToDevice, c->stream));
+            cudaEventRecord(done[buf], c->stream);
+            buf ^= 1;
+        }
+    }
+    GF_CUDA(cudaStreamSynchronize(c->stream));
+    if(n_events > 0)
+        for(int b = 0; b < 2; b++) {
+            cudaFreeHost(stage[b]);
+            cudaEventDestroy(done[b]);
+        }
+    return finish_columns(c, n_cols, n_events, total_events);
+}
+
+extern "C" int gf_adopt_device_columns(gf_ctx *c, const double *const *dev_cols, int n_cols, size_t n_events,
+                                       double total_events) {
+    if(!c) return gf_fail("null ctx");
+    if(n_cols < 0 || n_cols > GF_MAX_OBS) return gf_fail("gf_adopt_device_columns: 0..16 columns");
+    cudaSetDevice(c->device);
+    GF_CUDA(cudaStreamSynchronize(c->stream));
+    free_cols(c);
+    c->cols_owned = false;
+    c->view.ld = (long)n_events;
+    for(int k = 0; k < n_cols; k++) c->view.cols[k] = dev_cols[k];
+    return finish_columns(c, n_cols, n_events, total_events);
+}
+
+static int check_root(gf_ctx *c, int root) {
+    if(!c) return gf_fail("null ctx");
+    if(c->h_nodes.empty()) return gf_fail("no program set");
+    if(root < 0 || root >= (int)c->h_nodes.size()) return gf_fail("bad root node");
+    return 0;
+}
+
+extern "C" int gf_eval_sum_async(gf_ctx *c, int root, int metric) {
+    if(check_root(c, root)) return 1;
+    cudaSetDevice(c->device);
+    int first = root - c->h_nodes[root].size + 1;
+    int blocks = gf_grid_blocks(c, c->view.n_events, 4);
+    cudaEventRecord(c->ev0, c->stream);
+    k_eval_sum<<<blocks, GF_THREADS, gf_prog_smem(c), c->stream>>>(c->view, first, root, metric, c->n_cols,
+                                                                  c->d_partials, c->d_ticket, c->d_result);
+    cudaEventRecord(c->ev1, c->stream);
+    c->launches++;
+    GF_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int gf_eval_sum(gf_ctx *c, int root, int metric, double *out) {
+    if(gf_eval_sum_async(c, root, metric)) return 1;
+    GF_CUDA(cudaMemcpyAsync(c->h_result, c->d_result, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    GF_CUDA(cudaStreamSynchronize(c->stream));
+    cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1);
+    *out = c->h_result[0];
+    return 0;
+}
+
+extern "C" double *gf_partial_device_ptr(gf_ctx *c) { return c ? c->d_result : nullptr; }
+extern "C" void *gf_stream(gf_ctx *c) { return c ? (void *)c->stream : nullptr; }
+extern "C" int gf_sync(gf_ctx *c) {
+    if(!c) return gf_fail("null ctx");
+    cudaSetDevice(c->device);
+    GF_CUDA(cudaStreamSynchronize(c->stream));
+    cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1);
+    return 0;
+}
+extern "C" float gf_last_kernel_ms(gf_ctx *c) { return c ? c->last_ms : 0.f; }
+extern "C" uint64_t gf_launch_count(gf_ctx *c) { return c ? c->launches : 0; }
+
+extern "C" int gf_eval_events(gf_ctx *c, int root, int metric, double *out_host, size_t n) {
+    if(check_root(c, root)) return 1;
+    if((long)n != c->view.n_events) return gf_fail("gf_eval_events: n != uploaded events");
+    if(n == 0) return 0;
+    cudaSetDevice(c->device);
+    if(n > c->events_out_cap) {
+        cudaFree(c->d_events_out);
+        GF_CUDA(cudaMalloc(&c->d_events_out, sizeof(double) * n));
+        c->events_out_cap = n;
+    }
+    int first = root - c->h_nodes[root].size + 1;
+    int blocks = gf_grid_blocks(c, c->view.n_events, 4);
+    k_eval_events<<<blocks, GF_THREADS, gf_prog_smem(c), c->stream>>>(c->view, first, root, metric, c->n_cols,
+                                                                     c->d_events_out);
+    c->launches++;
+    GF_CUDA(cudaGetLastError());
+    GF_CUDA(cudaMemcpyAsync(out_host, c->d_events_out, sizeof(double) * n, cudaMemcpyDeviceToHost, c->stream));
+    GF_CUDA(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+extern "C" int gf_integrate_grid(gf_ctx *c, int root, const double *lo_hi_n, int n_obs, double *out) {
+    if(check_root(c, root)) return 1;
+    if(n_obs < 1 || n_obs > GF_MAX_OBS) return gf_fail("gf_integrate_grid: bad n_obs");
+    const gf_node &nd = c->h_nodes[root];
+    if(nd.nobs < 1) return gf_fail("gf_integrate_grid: root has no observables");
+    cudaSetDevice(c->device);
+    gf_grid_spec G;
+    G.nobs = n_obs;
+    G.total = 1;
+    for(int d = 0; d < GF_MAX_OBS; d++) { G.lo[d] = G.hi[d] = 0; G.nb[d] = 1; G.col[d] = 0; }
+    for(int d = 0; d < n_obs; d++) {
+        G.lo[d] = lo_hi_n[3 * d];
+        G.hi[d] = lo_hi_n[3 * d + 1];
+        G.nb[d] = (int)std::floor(lo_hi_n[3 * d + 2] + 0.5);
+        if(G.nb[d] < 1) return gf_fail("gf_integrate_grid: bins < 1");
+        G.col[d] = c->h_ints[nd.obs_off + std::min(d, nd.nobs - 1)];
+        G.total *= G.nb[d];
+    }
+    int first = root - nd.size + 1;
+    int blocks = gf_grid_blocks(c, G.total, 4);
+    k_grid_sum<<<blocks, GF_THREADS, gf_prog_smem(c), c->stream>>>(c->view, first, root, G, c->d_partials + (size_t)c->max_blocks * 6,
+                                                                  c->d_ticket + 1, c->d_result + GF_NPARTIAL);
+    c->launches++;
+    GF_CUDA(cudaGetLastError());
+    GF_CUDA(cudaMemcpyAsync(c->h_result + GF_NPARTIAL, c->d_result + GF_NPARTIAL, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    GF_CUDA(cudaStreamSynchronize(c->stream));
+    *out = c->h_result[GF_NPARTIAL];
+    return 0;
+}

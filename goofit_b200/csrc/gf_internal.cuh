@@ -1,0 +1,209 @@
+// gf_internal.cuh — context, shared-memory program block and the per-event stack-machine evaluator.
+// Replaces the reference's device_function_table indirect dispatch + ParameterContainer cursor
+// (/root/reference/src/PDFs/GooPdf.cu:398-400, include/goofit/PDFs/ParameterContainer.h:9-47).
+#pragma once
+#include "../../include/goofit_b200.h"
+#include <cuda_runtime.h>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#define GF_THREADS 256
+#define GF_MAX_AUX 16
+
+struct gf_amp3_state;
+struct gf_amp4_state;
+struct gf_conv_state;
+
+// Device-visible view of everything a kernel needs; passed by value as a kernel parameter.
+struct gf_dev_view {
+    const gf_node *nodes;   // global
+    const double *params;
+    const double *consts;
+    const double *norms;
+    const int32_t *ints;
+    int n_nodes, n_params, n_consts, n_norms, n_ints;
+    const double *cols[GF_MAX_OBS]; // SoA event columns
+    unsigned identity_mask;         // bit c set: column c holds 0,1,2,... (event number == row index)
+    long n_events;
+    long ld;                        // column leading dimension (padded rows)
+    double total_events;
+    // per-node auxiliary device tables (cached waves / amplitudes / convolution tables)
+    const void *aux[GF_MAX_AUX];
+    long aux_ld[GF_MAX_AUX];
+};
+
+// Program block staged in shared memory by every block.
+struct gf_sprog {
+    const gf_node *nodes;
+    const double *params;
+    const double *consts;
+    const double *norms;
+    const int32_t *ints;
+    const double *const *cols; // staged copies of the view's pointer tables (dynamic indexing from shared)
+    const void *const *aux;
+    const long *aux_ld;
+};
+
+__host__ __device__ inline size_t gf_align16(size_t x) { return (x + 15) & ~size_t(15); }
+
+inline size_t gf_sprog_bytes(int n_nodes, int n_params, int n_consts, int n_norms, int n_ints) {
+    return gf_align16(sizeof(gf_node) * n_nodes) + gf_align16(8 * (size_t)n_params) + gf_align16(8 * (size_t)n_consts)
+           + gf_align16(8 * (size_t)n_norms) + gf_align16(4 * (size_t)n_ints) + 8 * (GF_MAX_OBS + 2 * GF_MAX_AUX) + 64;
+}
+
+// cooperative copy global -> shared; call from all threads, then __syncthreads()
+__device__ inline gf_sprog gf_stage_program(const gf_dev_view &V, unsigned char *smem) {
+    gf_sprog P;
+    unsigned char *p = smem;
+    gf_node *sn = reinterpret_cast<gf_node *>(p);
+    p += gf_align16(sizeof(gf_node) * V.n_nodes);
+    double *sp = reinterpret_cast<double *>(p);
+    p += gf_align16(8 * (size_t)V.n_params);
+    double *sc = reinterpret_cast<double *>(p);
+    p += gf_align16(8 * (size_t)V.n_consts);
+    double *sno = reinterpret_cast<double *>(p);
+    p += gf_align16(8 * (size_t)V.n_norms);
+    int32_t *si = reinterpret_cast<int32_t *>(p);
+    p += gf_align16(4 * (size_t)V.n_ints);
+    const double **scol = reinterpret_cast<const double **>(p);
+    p += 8 * GF_MAX_OBS;
+    const void **saux = reinterpret_cast<const void **>(p);
+    p += 8 * GF_MAX_AUX;
+    long *sld = reinterpret_cast<long *>(p);
+    const int t = threadIdx.x, nt = blockDim.x;
+    {
+        const int32_t *src = reinterpret_cast<const int32_t *>(V.nodes);
+        int32_t *dst = reinterpret_cast<int32_t *>(sn);
+        int n = V.n_nodes * (int)(sizeof(gf_node) / 4);
+        for(int i = t; i < n; i += nt) dst[i] = src[i];
+    }
+    for(int i = t; i < V.n_params; i += nt) sp[i] = V.params[i];
+    for(int i = t; i < V.n_consts; i += nt) sc[i] = V.consts[i];
+    for(int i = t; i < V.n_norms; i += nt) sno[i] = V.norms[i];
+    for(int i = t; i < V.n_ints; i += nt) si[i] = V.ints[i];
+    if(t < GF_MAX_OBS) scol[t] = V.cols[t];
+    if(t < GF_MAX_AUX) { saux[t] = V.aux[t]; sld[t] = V.aux_ld[t]; }
+    P.cols = scol; P.aux = saux; P.aux_ld = sld;
+    P.nodes = sn; P.params = sp; P.consts = sc; P.norms = sno; P.ints = si;
+    return P;
+}
+
+// ---- event accessors -------------------------------------------------------------------------
+struct gf_evt_soa { // coalesced column reads: consecutive threads -> consecutive rows
+    const double *const *cols;
+    unsigned identity_mask;
+    long i;
+    __device__ inline double operator()(int col) const { return __ldg(cols[col] + i); }
+    __device__ inline long event_number(int col) const {
+        if((identity_mask >> col) & 1u) return i;
+        return (long)floor(0.5 + __ldg(cols[col] + i)); // Amp3Body.cu:85-87
+    }
+};
+struct gf_evt_vals { // grid point / single point held in registers
+    double v[GF_MAX_OBS];
+    long i;
+    __device__ inline double operator()(int col) const { return v[col]; }
+    __device__ inline long event_number(int col) const { return i; }
+};
+
+#include "gf_ops.cuh"
+
+// ---- deterministic reduction -----------------------------------------------------------------
+// warp shuffle tree -> block tree (shared) -> per-block partial; the last block to arrive sums
+// the partials in index order with the same tree. Fixed grid => bit-reproducible run to run.
+__device__ inline double gf_warp_sum(double v) {
+#pragma unroll
+    for(int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ inline double gf_block_sum(double v, double *sh /* >= 32 doubles */) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    v = gf_warp_sum(v);
+    __syncthreads();
+    if(lane == 0) sh[w] = v;
+    __syncthreads();
+    double r = 0;
+    if(w == 0) {
+        r = lane < nw ? sh[lane] : 0.0;
+        r = gf_warp_sum(r);
+    }
+    return r; // valid in thread 0
+}
+// n_out independent sums laid out partials[k*gridDim.x + block]
+__device__ inline void gf_grid_finish(double *vals, int n_out, double *partials, unsigned *ticket, double *out,
+                                      double *sh) {
+    __shared__ bool is_last;
+    for(int k = 0; k < n_out; k++) {
+        double r = gf_block_sum(vals[k], sh);
+        if(threadIdx.x == 0) partials[(size_t)k * gridDim.x + blockIdx.x] = r;
+    }
+    __threadfence();
+    if(threadIdx.x == 0) {
+        unsigned t = atomicAdd(ticket, 1u);
+        is_last = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if(is_last) {
+        __threadfence();
+        for(int k = 0; k < n_out; k++) {
+            double s = 0;
+            for(unsigned b = threadIdx.x; b < gridDim.x; b += blockDim.x)
+                s += __ldcg(partials + (size_t)k * gridDim.x + b);
+            double r = gf_block_sum(s, sh);
+            if(threadIdx.x == 0) out[k] = r;
+        }
+        if(threadIdx.x == 0) *ticket = 0;
+    }
+}
+
+// ---- host-side context -----------------------------------------------------------------------
+struct gf_ctx {
+    int device = 0;
+    int sm_count = 148;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // program
+    std::vector<gf_node> h_nodes;
+    std::vector<double> h_consts;
+    std::vector<int32_t> h_ints;
+    int n_params = 0, n_norms = 0;
+    gf_node *d_nodes = nullptr;
+    double *d_params = nullptr, *d_consts = nullptr, *d_norms = nullptr;
+    int32_t *d_ints = nullptr;
+    double *h_pin = nullptr; // pinned staging for params+norms
+    size_t h_pin_cap = 0;
+    // data
+    double *d_cols_base = nullptr;
+    bool cols_owned = true;
+    gf_dev_view view{};
+    int n_cols = 0;
+    // reduction scratch
+    double *d_partials = nullptr; // [GF_NPARTIAL * max_blocks]
+    unsigned *d_ticket = nullptr;
+    double *d_result = nullptr;   // [GF_NPARTIAL]
+    double *h_result = nullptr;   // pinned [GF_NPARTIAL * 64]
+    double *d_events_out = nullptr;
+    size_t events_out_cap = 0;
+    int max_blocks = 0;
+    float last_ms = 0;
+    uint64_t launches = 0;
+    std::vector<gf_amp3_state *> amp3;
+    std::vector<gf_amp4_state *> amp4;
+    std::vector<gf_conv_state *> conv;
+};
+
+void gf_set_error(const std::string &s);
+int gf_fail(const std::string &s);
+#define GF_CUDA(x)                                                                                                     \
+    do {                                                                                                               \
+        cudaError_t e_ = (x);                                                                                          \
+        if(e_ != cudaSuccess)                                                                                          \
+            return gf_fail(std::string(#x) + ": " + cudaGetErrorString(e_) + " at " + __FILE__ + ":"                    \
+                           + std::to_string(__LINE__));                                                                \
+    } while(0)
+
+size_t gf_prog_smem(const gf_ctx *c);
+int gf_grid_blocks(const gf_ctx *c, long n_items, int per_sm);
+int gf_alloc_aux_slot(gf_ctx *c);

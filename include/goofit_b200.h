@@ -1,0 +1,153 @@
+/* goofit_b200.h — C ABI of the B200-native likelihood-evaluation engine.
+ *
+ * One gf_ctx owns every device allocation of ONE GPU (one process per GPU; multi-GPU runs shard
+ * events/MC across processes and all-reduce the partial sums the *_partial calls leave on the device).
+ * All entry points return 0 on success, non-zero on failure; gf_last_error() gives the text.
+ * No torch / Thrust / C++ types cross this boundary. Not thread-safe per ctx (the reference is
+ * single-threaded and global-state too: /root/reference/include/goofit/PDFs/detail/Globals.h:14-49).
+ *
+ * Reference interfaces replaced (file:line under /root/reference):
+ *   flat tables + fn-pointer dispatch   src/PDFs/PdfBase.cu:95-119,268-327  src/PDFs/GooPdf.cu:398-400
+ *   GooPdf::reduce_with_metric          src/PDFs/GooPdf.cu:45-78            -> gf_eval_sum
+ *   GooPdf::evaluate_with_metric        src/PDFs/GooPdf.cu:112-173          -> gf_eval_events
+ *   GooPdf::reduce_with_bins            src/PDFs/GooPdf.cu:83-108           -> gf_integrate_grid
+ *   PdfBase::setData upload             src/PDFs/PdfBase.cu:329-530         -> gf_upload_columns
+ *   SmartVector sync of params/norms    include/goofit/detail/SmartVectorGPU.h:35-56 -> gf_set_params / gf_set_norms
+ *   ConvolutionPdf workspaces           src/PDFs/combine/ConvolutionPdf.cu:313-358 -> gf_conv_*
+ *   Amp3Body caches / integrals         src/PDFs/physics/Amp3Body.cu:238-359 -> gf_amp3_*
+ *   Amp4Body caches / MC integral       src/PDFs/physics/Amp4Body.cu:398-558 -> gf_amp4_*
+ *   Amp4Body_TD / NormEvents_4Body_*    src/PDFs/physics/Amp4Body_TD.cu:744-799 -> gf_amp4_* (td=1)
+ */
+#ifndef GOOFIT_B200_H
+#define GOOFIT_B200_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct gf_ctx gf_ctx;
+
+/* ---- program block ------------------------------------------------------------------------
+ * The PDF tree is flattened host-side into an array of fixed-size node records in POST-ORDER
+ * (children before parent), so a subtree rooted at node r occupies nodes [r-size+1, r] and is
+ * evaluated by a stack machine with no indirect calls. Nodes that are not evaluated per event
+ * (ConvolutionPdf's model/resolution, resonances, lineshapes, spin factors) live in the same
+ * array outside the main range and are referenced through the node's `ints`. */
+typedef struct gf_node {
+    int32_t op;        /* gf_op */
+    int32_t nchild;    /* children evaluated per event (on the value stack) */
+    int32_t size;      /* nodes in the per-event subtree, including this one */
+    int32_t par_off;   /* first parameter in params[] */
+    int32_t npar;
+    int32_t con_off;   /* first constant in consts[] */
+    int32_t ncon;
+    int32_t obs_off;   /* first observable column index in ints[] */
+    int32_t nobs;
+    int32_t norm_slot; /* index into norms[] (every node owns one slot) */
+    int32_t int_off;   /* node-specific integer block in ints[] */
+    int32_t nint;
+} gf_node;
+
+enum gf_op {
+    GF_OP_EXP = 1,          /* ExpPdf.cu:7    exp(a x) */
+    GF_OP_EXP_OFFSET,       /* ExpPdf.cu:19   exp(a (x-x0)) */
+    GF_OP_EXP_POLY,         /* ExpPdf.cu:32 */
+    GF_OP_EXP_POLY_OFFSET,  /* ExpPdf.cu:50 */
+    GF_OP_GAUSSIAN,         /* GaussianPdf.cu:7 */
+    GF_OP_POLYNOMIAL,       /* PolynomialPdf.cu:8 */
+    GF_OP_OFFSET_POLYNOMIAL,/* PolynomialPdf.cu:27 */
+    GF_OP_MULTI_POLYNOMIAL, /* PolynomialPdf.cu:47 */
+    GF_OP_ARGUS_UPPER,      /* ArgusPdf.cu:7 */
+    GF_OP_ARGUS_LOWER,      /* ArgusPdf.cu:27 */
+    GF_OP_KINLIMITBW,       /* KinLimitBWPdf.cu:26 */
+    GF_OP_SCALED_GAUSSIAN,  /* ScaledGaussianPdf.cu:9 */
+    GF_OP_JOHNSONSU,        /* JohnsonSUPdf.cu:8 */
+    GF_OP_ADD = 32,         /* AddPdf.cu:16  ints: child norm slots */
+    GF_OP_ADD_EXT,          /* AddPdf.cu:53 */
+    GF_OP_PROD,             /* ProdPdf.cu:9 */
+    GF_OP_CONVOLVE,         /* ConvolutionPdf.cu:27  ints: conv id */
+    GF_OP_AMP3 = 48,        /* Amp3Body.cu:60  child: efficiency; ints: amp3 id */
+    GF_OP_AMP4,             /* Amp4Body.cu:53 */
+    GF_OP_AMP4_TD,          /* Amp4Body_TD.cu:167 */
+    /* resonance / lineshape / spin-factor records (never on the per-event stack) */
+    GF_OP_RES_RBW = 64,     /* resonances/RBW.cu:9 plainBW<1>; params mass,width; consts spin,cyc,norm */
+    GF_OP_RES_RBW_SYM,      /* plainBW<2> */
+    GF_OP_RES_GS,           /* resonances/GS.cu:9 */
+    GF_OP_RES_NONRES,       /* resonances/NonRes.cu:8 */
+    GF_OP_RES_GAUSS,        /* resonances/Gauss.cu:9 */
+    GF_OP_LS = 96,          /* 4-body lineshape; consts[0] = gf_ls_kind */
+    GF_OP_SF                /* 4-body spin factor; consts[0] = gf_sf_kind */
+};
+
+enum gf_metric { /* MetricPointer.cu:8-58 */
+    GF_METRIC_EVAL = 0, GF_METRIC_NLL = 1, GF_METRIC_PROB = 2,
+    GF_METRIC_BINAVG = 3, GF_METRIC_BINERR = 4, GF_METRIC_CHISQ = 5
+};
+
+const char *gf_last_error(void);
+int gf_version(void);
+
+gf_ctx *gf_create(int device_id);
+void gf_destroy(gf_ctx *);
+int gf_device_info(gf_ctx *, int *sm_count, size_t *free_bytes, size_t *total_bytes);
+
+int gf_set_program(gf_ctx *, const gf_node *nodes, int n_nodes, const double *consts, int n_consts,
+                   const int32_t *ints, int n_ints, int n_params, int n_norms);
+int gf_set_params(gf_ctx *, const double *params, int n);
+int gf_set_norms(gf_ctx *, const double *norms, int n);
+
+/* Dataset: n_cols host columns of n_events doubles -> 256-B aligned SoA columns in HBM (pinned staging).
+ * For binned data the last two columns are (content, error|volume) as PdfBase.cu:485-494.
+ * total_events feeds the binned metrics' c_totalEvents. */
+int gf_upload_columns(gf_ctx *, const double *const *cols, int n_cols, size_t n_events, double total_events);
+/* As above, but the columns are already device pointers (resident data; no host copy). */
+int gf_adopt_device_columns(gf_ctx *, const double *const *dev_cols, int n_cols, size_t n_events, double total_events);
+
+/* K1: sum over events of metric(pdf(event), norm[root]).  Deterministic: fixed grid, fixed order. */
+int gf_eval_sum(gf_ctx *, int root, int metric, double *out);
+/* Same, but leaves the partial sum on the device (for an NCCL all-reduce by the caller) */
+int gf_eval_sum_async(gf_ctx *, int root, int metric);
+double *gf_partial_device_ptr(gf_ctx *);  /* device double[GF_NPARTIAL]: [0]=NLL sum, [1..4]=MC integral sums */
+void *gf_stream(gf_ctx *);                /* cudaStream_t the ctx launches on */
+int gf_sync(gf_ctx *);
+/* K3: per-event metric values to host (out_host[n_events]) */
+int gf_eval_events(gf_ctx *, int root, int metric, double *out_host, size_t n);
+/* K2: sum over the mid-point grid of the raw pdf rooted at `root`; lo_hi_n = (lo,hi,nbins) per observable of root */
+int gf_integrate_grid(gf_ctx *, int root, const double *lo_hi_n, int n_obs, double *out);
+
+/* ConvolutionPdf (ConvolutionPdf.cu:151-358): ints of the node = {aux_slot, model_root, resol_root}; consts = lo,hi,step */
+int gf_conv_setup(gf_ctx *, int node, double lo, double hi, double step, double obs_lo, double obs_hi);
+int gf_conv_fill(gf_ctx *, int node, int fill_model, int fill_resol);
+int gf_conv_sizes(gf_ctx *, int node, int *n_model, int *n_resol, int *n_table);
+int gf_conv_get_workspace(gf_ctx *, int node, int which /*0 model,1 resolution,2 table*/, double *out, int n);
+
+/* Amp3Body: ints of the node = {aux_slot, n_res, res_node[n_res]};  consts = mother,d1,d2,d3,meson_radius,mother_radius */
+int gf_amp3_alloc(gf_ctx *, int node, size_t n_events);
+int gf_amp3_cache_waves(gf_ctx *, int node, const uint8_t *redo_mask);
+int gf_amp3_integrals(gf_ctx *, int node, const uint8_t *redo_mask, const double *lo_hi_n6, int eff_root,
+                      double *I_re_im /* n_res*n_res*2, row i col j */);
+int gf_amp3_get_wave(gf_ctx *, int node, int res, double *out_re_im, size_t n_events);
+
+/* Amp4Body / Amp4Body_TD: ints = {amp4_id, nLS, nSF, nAmp, td, ls_node[nLS], sf_node[nSF], AmpIndices...} */
+int gf_amp4_alloc(gf_ctx *, int node, size_t n_events);
+int gf_amp4_set_mc(gf_ctx *, int node, const double *const *mc_cols5, size_t n_mc, const double *weights,
+                   const double *dtime, const double *sigma);
+int gf_amp4_cache(gf_ctx *, int node, int redo_spins, const uint8_t *ls_redo, const uint8_t *amp_redo);
+int gf_amp4_norm(gf_ctx *, int node, double *out /* 1 (Amp4Body) or 4 (TD) sums over MC events */);
+int gf_amp4_norm_async(gf_ctx *, int node);
+int gf_amp4_get_amp(gf_ctx *, int node, int amp, double *out_re_im, size_t n_events);
+
+/* timing of the last kernel launched by gf_eval_sum (CUDA events on the ctx stream), ms */
+float gf_last_kernel_ms(gf_ctx *);
+/* number of kernels this ctx has launched since creation */
+uint64_t gf_launch_count(gf_ctx *);
+
+#define GF_NPARTIAL 8
+#define GF_MAX_OBS 16
+#define GF_MAX_STACK 16
+
+#ifdef __cplusplus
+}
+#endif
+#endif
