@@ -1,0 +1,508 @@
+// TEST INFRASTRUCTURE (oracle). ROOT-free driver over the UNMODIFIED reference library built by
+// oracle/Makefile.ref (libgoofit_ref.so, OpenMP Thrust backend). It is never linked into the product.
+//   ref_driver golden <outdir>          write golden fixtures (.npy + manifest.json) for tests/golden
+//   ref_driver bench <config> <N> <K>   time K calculateNLL() calls on N synthetic events (CPU baseline)
+// Models follow the reference's examples: examples/exponential/exponential.cpp, examples/dalitz/dalitz.cpp:124-322,
+// examples/zachFit/zachFit.cpp:143-230, examples/DP4/DP4.cu:51-232.
+#include <goofit/Application.h>
+#include <goofit/FitManager.h>
+#include <goofit/PDFs/basic/ArgusPdf.h>
+#include <goofit/PDFs/basic/ExpPdf.h>
+#include <goofit/PDFs/basic/GaussianPdf.h>
+#include <goofit/PDFs/basic/JohnsonSUPdf.h>
+#include <goofit/PDFs/basic/KinLimitBWPdf.h>
+#include <goofit/PDFs/basic/PolynomialPdf.h>
+#include <goofit/PDFs/basic/ScaledGaussianPdf.h>
+#include <goofit/PDFs/combine/AddPdf.h>
+#include <goofit/PDFs/combine/ConvolutionPdf.h>
+#include <goofit/PDFs/combine/ProdPdf.h>
+#include <goofit/PDFs/physics/Amp3Body.h>
+#include <goofit/PDFs/physics/ResonancePdf.h>
+#include <goofit/UnbinnedDataSet.h>
+#include <goofit/Variable.h>
+
+#include <chrono>
+#include <cstdio>
+#include <fstream>
+#include <map>
+#include <omp.h>
+#include <random>
+#include <sstream>
+#include <string>
+#include <sys/stat.h>
+#include <vector>
+
+using namespace GooFit;
+
+// ---- tiny .npy writer + manifest -----------------------------------------------------------------
+static std::string g_out;
+static std::ostringstream g_manifest;
+static bool g_first = true;
+
+static void save_npy(const std::string &name, const double *v, size_t rows, size_t cols = 0) {
+    std::string shape = cols ? "(" + std::to_string(rows) + ", " + std::to_string(cols) + ")" : "(" + std::to_string(rows) + ",)";
+    std::string hdr = "{'descr': '<f8', 'fortran_order': False, 'shape': " + shape + ", }";
+    size_t total = 10 + hdr.size() + 1;
+    size_t pad = (64 - total % 64) % 64;
+    hdr += std::string(pad, ' ') + "\n";
+    std::ofstream f(g_out + "/" + name + ".npy", std::ios::binary);
+    const char magic[] = "\x93NUMPY\x01\x00";
+    f.write(magic, 8);
+    unsigned short hl = (unsigned short)hdr.size();
+    f.write(reinterpret_cast<const char *>(&hl), 2);
+    f.write(hdr.data(), hdr.size());
+    f.write(reinterpret_cast<const char *>(v), sizeof(double) * rows * (cols ? cols : 1));
+}
+static void save_npy(const std::string &name, const std::vector<double> &v) { save_npy(name, v.data(), v.size()); }
+static void put(const std::string &key, double v) {
+    char buf[64];
+    snprintf(buf, sizeof buf, "%.17g", v);
+    g_manifest << (g_first ? "" : ",\n") << "  \"" << key << "\": " << buf;
+    g_first = false;
+}
+static void put_vec(const std::string &key, const std::vector<double> &v) {
+    g_manifest << (g_first ? "" : ",\n") << "  \"" << key << "\": [";
+    for(size_t i = 0; i < v.size(); i++) {
+        char buf[64];
+        snprintf(buf, sizeof buf, "%.17g", v[i]);
+        g_manifest << (i ? ", " : "") << buf;
+    }
+    g_manifest << "]";
+    g_first = false;
+}
+
+static std::vector<double> column(UnbinnedDataSet &d, const Observable &o) {
+    std::vector<double> r(d.getNumEvents());
+    for(size_t i = 0; i < r.size(); i++) r[i] = d.getValue(o, i);
+    return r;
+}
+
+// per-event Prob values of the root (getCompProbsAtDataPoints()[0]) and the reference's own NLL
+static void dump_pdf(const std::string &tag, GooPdf &pdf, UnbinnedDataSet &data, bool with_grid, Observable *gridvar,
+                     bool comps = true) {
+    pdf.setData(&data);
+    double nll = pdf.calculateNLL();
+    put(tag + ".nll", nll);
+    if(comps) {
+        auto probs = pdf.getCompProbsAtDataPoints();
+        save_npy(tag + ".prob", probs[0]);
+        for(size_t k = 1; k < probs.size(); k++) save_npy(tag + ".comp" + std::to_string(k - 1), probs[k]);
+    }
+    pdf.setFitControl(std::make_shared<UnbinnedNllFit>());
+    pdf.setData(&data);
+    put(tag + ".nll_again", pdf.calculateNLL());
+    if(with_grid && gridvar) {
+        auto g = pdf.evaluateAtPoints(*gridvar);
+        save_npy(tag + ".grid", g);
+        pdf.setFitControl(std::make_shared<UnbinnedNllFit>());
+        pdf.setData(&data);
+    }
+}
+
+// ---- case: 1-D basic shapes and combiners ------------------------------------------------------
+static void fill_1d(UnbinnedDataSet &d, Observable &x, size_t n, unsigned seed, int kind, double a = 1.5) {
+    std::mt19937 gen(seed);
+    std::uniform_real_distribution<double> uni(x.getLowerLimit(), x.getUpperLimit());
+    std::exponential_distribution<double> ex(a);
+    std::normal_distribution<double> ga(0.5 * (x.getLowerLimit() + x.getUpperLimit()),
+                                        0.15 * (x.getUpperLimit() - x.getLowerLimit()));
+    while(d.getNumEvents() < n) {
+        double v = kind == 0 ? uni(gen) : (kind == 1 ? x.getLowerLimit() + ex(gen) : ga(gen));
+        if(v <= x.getLowerLimit() || v >= x.getUpperLimit()) continue;
+        x.setValue(v);
+        d.addEvent();
+    }
+}
+
+static void case_basic() {
+    { // exponential example (examples/exponential/exponential.cpp) + NormalizeTest.cpp:42-44
+        Observable x{"x", 0, 10};
+        UnbinnedDataSet d{x};
+        fill_1d(d, x, 2000, 137, 1, 1.0);
+        save_npy("exp.x", column(d, x));
+        Variable alpha{"alpha", -2, 0.1, -10, 10};
+        ExpPdf pdf{"exppdf", x, alpha};
+        pdf.setData(&d);
+        put("exp.integrate_0_10", pdf.integrate(0, 10));
+        put("exp.normalize", pdf.normalize());
+        dump_pdf("exp", pdf, d, true, &x);
+        FitManager fit{&pdf};
+        fit.setVerbosity(0);
+        auto fm = fit.fit();
+        put("exp.fit_alpha", alpha.getValue());
+        put("exp.fit_alpha_err", alpha.getError());
+        put("exp.fit_nll", pdf.calculateNLL());
+        put("exp.fit_valid", (double)(int)fm.IsValid());
+    }
+    { // Gaussian (NormalizeTest.cpp:84-99,189-218)
+        Observable x{"x", -10, 10};
+        UnbinnedDataSet d{x};
+        fill_1d(d, x, 1500, 11, 2);
+        save_npy("gauss.x", column(d, x));
+        Variable m{"m", 1.5, 0.1, -10, 10}, s{"s", 2.5, 0.1, 0.5, 10};
+        GaussianPdf pdf{"gauss", x, m, s};
+        pdf.setData(&d);
+        put("gauss.normalize", pdf.normalize());
+        dump_pdf("gauss", pdf, d, true, &x);
+    }
+    { // offset exponential, exp-poly, polynomial
+        Observable x{"x", 0.5, 4};
+        UnbinnedDataSet d{x};
+        fill_1d(d, x, 1000, 5, 0);
+        save_npy("shapes.x", column(d, x));
+        Variable a{"a", -0.7, 0.1, -5, 5}, x0{"x0", 0.25, 0.1, -1, 1};
+        ExpPdf eo{"expoff", x, a, x0};
+        dump_pdf("expoff", eo, d, true, &x);
+        std::vector<Variable> w{Variable{"w0", 0.3, 0.1, -5, 5}, Variable{"w1", -0.8, 0.1, -5, 5}, Variable{"w2", 0.05, 0.1, -5, 5}};
+        ExpPdf ep{"exppoly", x, w};
+        dump_pdf("exppoly", ep, d, true, &x);
+        ExpPdf epo{"exppolyoff", x, w, x0};
+        dump_pdf("exppolyoff", epo, d, true, &x);
+        std::vector<Variable> c{Variable{"c0", 1.0, 0.1, -5, 5}, Variable{"c1", 0.4, 0.1, -5, 5}, Variable{"c2", 0.15, 0.1, -5, 5}};
+        PolynomialPdf po{"poly", x, c};
+        dump_pdf("poly", po, d, true, &x);
+        PolynomialPdf po1{"poly_low1", x, c, 1};
+        dump_pdf("poly_low1", po1, d, true, &x);
+        Variable jm{"jm", 2.0, 0.1, 0, 4}, js{"js", 0.6, 0.1, 0.1, 4}, jg{"jg", -0.4, 0.1, -3, 3}, jd{"jd", 1.3, 0.1, 0.1, 5};
+        JohnsonSUPdf jo{"johnson", x, jm, js, jg, jd};
+        dump_pdf("johnson", jo, d, true, &x);
+        Variable sm{"sm", 2.1, 0.1, 0, 4}, ss{"ss", 0.7, 0.1, 0.1, 4}, sd{"sd", 0.1, 0.1, -1, 1}, se{"se", 0.2, 0.1, -1, 1};
+        ScaledGaussianPdf sg{"scaledgauss", x, sm, ss, sd, se};
+        dump_pdf("scaledgauss", sg, d, true, &x);
+        Variable am0{"am0", 4.2, 0.1, 4, 5}, asl{"asl", -1.5, 0.1, -10, 10}, apw{"apw", 0.5, 0.1, 0.1, 3};
+        ArgusPdf au{"argus_upper", x, am0, asl, true, apw};
+        dump_pdf("argus_upper", au, d, true, &x);
+        Variable bm0{"bm0", 0.3, 0.1, 0, 0.5};
+        ArgusPdf al{"argus_lower", x, bm0, asl, false, apw};
+        // the lower Argus grows fast; fine for value parity
+        Variable asl2{"asl2", -0.02, 0.01, -1, 1};
+        ArgusPdf al2{"argus_lower", x, bm0, asl2, false, apw};
+        dump_pdf("argus_lower", al2, d, true, &x);
+    }
+    { // zachFit-like pieces: KinLimitBW and Argus on the delta-m range (zachFit.cpp:143-230)
+        Observable dm{"dm", 0.1395, 0.1665};
+        dm.setNumBins(270);
+        UnbinnedDataSet d{dm};
+        fill_1d(d, dm, 1200, 99, 0);
+        save_npy("dm.x", column(d, dm));
+        Variable mean{"kl_mean", 0.1454, 0.0001, 0.1450, 0.1458}, width{"kl_width", 0.0004, 0.0001, 0.0001, 0.001};
+        KinLimitBWPdf kl{"klbw", dm, mean, width};
+        kl.setMasses(1.8645, 0.13957);
+        dump_pdf("klbw", kl, d, true, &dm);
+        Variable m0{"arg_m0", 0.13957, 0.0001, 0.1, 0.2}, slope{"arg_slope", -1.0, 0.1, -100, 10}, power{"arg_power", 0.5, 0.01, 0.1, 2};
+        ArgusPdf bkg{"argus_dm", dm, m0, slope, false, power};
+        dump_pdf("argus_dm", bkg, d, true, &dm);
+        // convolution: KinLimitBW (x) ScaledGaussian, as zachFit.cpp:213-221 with a coarser step
+        Variable dummyzero{"dummyzero", 0}, rs{"res_sigma", 0.00025, 0.00001, 0.0001, 0.001};
+        Variable delta{"delta", 0.00002, 0.00001, -0.001, 0.001}, eps{"epsilon", 0.05, 0.01, -0.5, 0.5};
+        ScaledGaussianPdf res{"resolution", dm, dummyzero, rs, delta, eps};
+        ConvolutionPdf conv{"conv", dm, &kl, &res};
+        conv.setIntegrationConstants(0.1395, 0.1665, 0.00003);
+        dump_pdf("conv", conv, d, true, &dm, false);
+        Variable frac{"bkg_frac", 0.3, 0.01, 0, 1};
+        AddPdf total{"total", frac, &bkg, &conv};
+        dump_pdf("convadd", total, d, true, &dm);
+        // second parameter point: only the resolution moves, then only the model
+        total.setData(&d);
+        static_cast<GooPdf &>(total).calculateNLL();
+        rs.setValue(0.0003); rs.setChanged(true); mean.setChanged(false); width.setChanged(false);
+        total.updateVariable(rs, 0.0003); total.updateParameters();
+        put("convadd.nll_res_moved", static_cast<GooPdf &>(total).calculateNLL());
+        rs.setChanged(false); width.setChanged(true);
+        total.updateVariable(width, 0.0005); total.updateParameters();
+        put("convadd.nll_model_moved", static_cast<GooPdf &>(total).calculateNLL());
+    }
+    { // AddNormTest.cpp:16-44 non-extended sum, extended sum, and a 2-D product (NormalizeTest.cpp:147-169)
+        Observable x{"x", 0, 10};
+        UnbinnedDataSet d{x};
+        fill_1d(d, x, 1500, 7, 1, 0.6);
+        save_npy("add.x", column(d, x));
+        Variable m{"am", 4.0, 0.1, 0, 10}, s{"as", 1.2, 0.1, 0.1, 5}, al{"aalpha", -0.5, 0.1, -5, 5}, f{"afrac", 0.35, 0.1, 0, 1};
+        GaussianPdf g{"ag", x, m, s};
+        ExpPdf e{"ae", x, al};
+        AddPdf add{"add", f, &g, &e};
+        dump_pdf("add", add, d, true, &x);
+        Variable n1{"n1", 500, 10, 0, 5000}, n2{"n2", 1100, 10, 0, 5000};
+        AddPdf ext{"addext", std::vector<Variable>{n1, n2}, std::vector<PdfBase *>{&g, &e}};
+        dump_pdf("addext", ext, d, true, &x);
+        Observable y{"y", -5, 5};
+        UnbinnedDataSet d2{x, y};
+        std::mt19937 gen(21);
+        std::uniform_real_distribution<double> ux(0, 10), uy(-5, 5);
+        for(int i = 0; i < 800; i++) { x.setValue(ux(gen)); y.setValue(uy(gen)); d2.addEvent(); }
+        save_npy("prod.x", column(d2, x));
+        save_npy("prod.y", column(d2, y));
+        Variable my{"my", 0.5, 0.1, -5, 5}, sy{"sy", 1.7, 0.1, 0.1, 5};
+        GaussianPdf gy{"gy", y, my, sy};
+        ProdPdf prod{"prod", {&g, &gy}};
+        dump_pdf("prod", prod, d2, false, nullptr);
+    }
+}
+
+// ---- dalitz model (examples/dalitz/dalitz.cpp:124-322) -------------------------------------------
+static const fptype _mD0 = 1.86484, _mD02 = _mD0 * _mD0, _mD02inv = 1. / _mD02;
+static const fptype piPlusMass = 0.13957018, piZeroMass = 0.1349766;
+
+struct DalitzModel {
+    Observable m12{"m12", 0, 3}, m13{"m13", 0, 3};
+    EventNumber eventNumber{"eventNumber"};
+    std::vector<Variable> masses, widths; // one per resonance (NonRes: dummies)
+    DecayInfo3 info;
+    GooPdf *eff = nullptr;
+    Amp3Body *signal = nullptr;
+    std::vector<Variable> coefs; // (re, im) interleaved
+};
+
+static DalitzModel *make_dalitz(bool float_masses, int grid) {
+    auto *M = new DalitzModel();
+    M->m12.setNumBins(grid);
+    M->m13.setNumBins(grid);
+    DecayInfo3 &d = M->info;
+    d.motherMass = _mD0; d.daug1Mass = piZeroMass; d.daug2Mass = piPlusMass; d.daug3Mass = piPlusMass;
+    d.meson_radius = 1.5; d.mother_meson_radius = 5.0;
+    Variable rhoM("rho_mass", 0.7758, 0.01, 0.7, 0.8), rhoW("rho_width", 0.1503, 0.01, 0.1, 0.2);
+    Variable m1450("rhop_1450_mass", 1.465, 0.01, 1.0, 2.0), w1450("rhop_1450_width", 0.400, 0.01, 0.01, 5.0);
+    Variable m1700("rhop_1700_mass", 1.720, 0.01, 1.6, 1.9), w1700("rhop_1700_width", 0.250, 0.01, 0.1, 1.0);
+    struct R { const char *n; double re, im; Variable m, w; int spin; int cyc; };
+    std::vector<R> rs = {
+        {"rhop", 1, 0, rhoM, rhoW, 1, PAIR_12},
+        {"rho0", 0.565, 0.164, rhoM, rhoW, 1, PAIR_23},
+        {"rhom", 0.714, -0.025, rhoM, rhoW, 1, PAIR_13},
+        {"rhop_1450", -0.174, -0.117, m1450, w1450, 1, PAIR_12},
+        {"rho0_1450", 0.325, 0.057, m1450, w1450, 1, PAIR_23},
+        {"rhom_1450", 0.788, 0.226, m1450, w1450, 1, PAIR_13},
+        {"rhop_1700", 2.151, -0.658, m1700, w1700, 1, PAIR_12},
+        {"rho0_1700", 2.400, -0.734, m1700, w1700, 1, PAIR_23},
+        {"rhom_1700", 1.286, -1.532, m1700, w1700, 1, PAIR_13},
+        {"f0_980", 0.008 * (-_mD02), -0.013 * (-_mD02), Variable("f0_980_mass", 0.980, 0.01, 0.8, 1.2), Variable("f0_980_width", 0.044, 0.001, 0.001, 0.08), 0, PAIR_23},
+        {"f0_1370", -0.058 * (-_mD02), 0.026 * (-_mD02), Variable("f0_1370_mass", 1.434, 0.01, 1.2, 1.6), Variable("f0_1370_width", 0.173, 0.01, 0.01, 0.4), 0, PAIR_23},
+        {"f0_1500", 0.057 * (-_mD02), 0.012 * (-_mD02), Variable("f0_1500_mass", 1.507, 0.01, 1.3, 1.7), Variable("f0_1500_width", 0.109, 0.01, 0.01, 0.3), 0, PAIR_23},
+        {"f0_1710", 0.070 * (-_mD02), 0.087 * (-_mD02), Variable("f0_1710_mass", 1.714, 0.01, 1.5, 2.9), Variable("f0_1710_width", 0.140, 0.01, 0.01, 0.5), 0, PAIR_23},
+        {"f2_1270", -1.027 * (-_mD02inv), -0.162 * (-_mD02inv), Variable("f2_1270_mass", 1.2754, 0.01, 1.0, 1.5), Variable("f2_1270_width", 0.1851, 0.01, 0.01, 0.4), 2, PAIR_23},
+        {"f0_600", 0.068 * (-_mD02), 0.010 * (-_mD02), Variable("f0_600_mass", 0.500, 0.01, 0.3, 0.7), Variable("f0_600_width", 0.400, 0.01, 0.2, 0.6), 0, PAIR_23},
+    };
+    // order as dalitz.cpp:283-298: nonr first
+    Variable nre("nonr_amp_real", -0.5595, 0.001, 0, 0), nim("nonr_amp_imag", 0.108761, 0.1, 0, 0);
+    M->coefs.push_back(nre); M->coefs.push_back(nim);
+    d.resonances.push_back(new Resonances::NonRes("nonr", nre, nim));
+    for(size_t k = 0; k < rs.size(); k++) {
+        R &r = rs[k];
+        Variable re = k == 0 ? Variable(std::string(r.n) + "_amp_real", r.re) : Variable(std::string(r.n) + "_amp_real", r.re, 0.001, 0, 0);
+        Variable im = k == 0 ? Variable(std::string(r.n) + "_amp_imag", r.im) : Variable(std::string(r.n) + "_amp_imag", r.im, 0.1, 0, 0);
+        M->coefs.push_back(re); M->coefs.push_back(im);
+        M->masses.push_back(r.m); M->widths.push_back(r.w);
+        d.resonances.push_back(new Resonances::RBW(r.n, re, im, r.m, r.w, r.spin, r.cyc));
+    }
+    if(!float_masses)
+        for(auto *res : d.resonances) res->setParameterConstantness(true);
+    Variable one("constantOne", 1), zero("constantZero", 0);
+    M->eff = new PolynomialPdf("constantEff", std::vector<Observable>{M->m12, M->m13}, std::vector<Variable>{one},
+                               std::vector<Variable>{zero, zero}, 0);
+    M->signal = new Amp3Body("signalPDF", M->m12, M->m13, M->eventNumber, d, M->eff);
+    return M;
+}
+
+static bool cpu_in_dalitz(double m12, double m13) {
+    return inDalitz(m12, m13, _mD0, piZeroMass, piPlusMass, piPlusMass);
+}
+
+// uniform events inside the Dalitz boundary (seeded); evtNum = row
+static void fill_dalitz_uniform(DalitzModel &M, UnbinnedDataSet &d, size_t n, unsigned long seed) {
+    std::mt19937_64 gen(seed);
+    std::uniform_real_distribution<double> u(0.0, 3.0);
+    while(d.getNumEvents() < n) {
+        double a = u(gen), b = u(gen);
+        if(!cpu_in_dalitz(a, b)) continue;
+        M.m12.setValue(a); M.m13.setValue(b); M.eventNumber.setValue(d.getNumEvents());
+        d.addEvent();
+    }
+}
+
+static void case_dalitz() {
+    DalitzModel *M = make_dalitz(true, 120);
+    UnbinnedDataSet d({M->m12, M->m13, M->eventNumber});
+    fill_dalitz_uniform(*M, d, 600, 2024);
+    // a few points outside the boundary exercise the zero branch (Amp3Body.cu:74-85)
+    for(double a : {0.05, 2.9, 1.0}) {
+        M->m12.setValue(a); M->m13.setValue(a > 2 ? 2.9 : 0.01); M->eventNumber.setValue(d.getNumEvents());
+        d.addEvent();
+    }
+    save_npy("dalitz.m12", column(d, M->m12));
+    save_npy("dalitz.m13", column(d, M->m13));
+    Amp3Body *s = M->signal;
+    s->setData(&d);
+    s->setDataSize(d.getNumEvents());
+    double nll = s->calculateNLL();
+    put("dalitz.nll", nll);
+    put("dalitz.integral", 1.0 / s->getNormalization());
+    std::vector<double> waves;
+    for(size_t i = 0; i < M->info.resonances.size(); i++) {
+        auto w = s->getCachedWave(i);
+        for(auto &c : w) { waves.push_back(c.real()); waves.push_back(c.imag()); }
+    }
+    save_npy("dalitz.waves", waves.data(), M->info.resonances.size(), 2 * d.getNumEvents());
+    { // per-event probabilities through a ProdPdf wrapper, as DalitzPlotter.h:60-63 does
+        ProdPdf wrap{"wrap", {s}};
+        wrap.setData(&d);
+        s->setDataSize(d.getNumEvents());
+        auto probs = wrap.getCompProbsAtDataPoints();
+        save_npy("dalitz.prob", probs[0]);
+    }
+    s->setFitControl(std::make_shared<UnbinnedNllFit>());
+    s->setData(&d);
+    s->setDataSize(d.getNumEvents());
+    put("dalitz.nll_again", s->calculateNLL());
+    // second point: coefficients move, masses stay -> caches must be reused (Amp3Body.cu:266-275)
+    for(auto &m : M->masses) m.setChanged(false);
+    for(auto &w : M->widths) w.setChanged(false);
+    s->updateVariable(M->coefs[4], 0.6); s->updateVariable(M->coefs[7], -0.1); s->updateParameters();
+    put("dalitz.nll_coef_moved", s->calculateNLL());
+    put("dalitz.integral_coef_moved", 1.0 / s->getNormalization());
+    // third point: one mass and one width move -> waves 0-2 resp. 9 and their integrals redone
+    M->masses[0].setChanged(true); M->widths[9].setChanged(true);
+    s->updateVariable(M->masses[0], 0.77); s->updateVariable(M->widths[9], 0.05); s->updateParameters();
+    put("dalitz.nll_mass_moved", s->calculateNLL());
+    put("dalitz.integral_mass_moved", 1.0 / s->getNormalization());
+}
+
+// accept-reject toy from the model itself, then a full Minuit2 fit with the reference's FitManager
+static void case_dalitz_fit() {
+    DalitzModel *M = make_dalitz(false, 240);
+    UnbinnedDataSet cand({M->m12, M->m13, M->eventNumber});
+    fill_dalitz_uniform(*M, cand, 60000, 77);
+    Amp3Body *s = M->signal;
+    std::vector<double> probs;
+    {
+        ProdPdf wrap{"wrap", {s}};
+        wrap.setData(&cand);
+        s->setDataSize(cand.getNumEvents());
+        probs = wrap.getCompProbsAtDataPoints()[0];
+    }
+    double pmax = 0;
+    for(double p : probs) pmax = std::max(pmax, p);
+    std::mt19937_64 gen(78);
+    std::uniform_real_distribution<double> u(0, 1);
+    UnbinnedDataSet d({M->m12, M->m13, M->eventNumber});
+    for(size_t i = 0; i < probs.size(); i++) {
+        if(u(gen) * pmax > probs[i]) continue;
+        M->m12.setValue(cand.getValue(M->m12, i)); M->m13.setValue(cand.getValue(M->m13, i));
+        M->eventNumber.setValue(d.getNumEvents());
+        d.addEvent();
+    }
+    save_npy("dalitzfit.m12", column(d, M->m12));
+    save_npy("dalitzfit.m13", column(d, M->m13));
+    s->setFitControl(std::make_shared<UnbinnedNllFit>());
+    s->setData(&d);
+    s->setDataSize(d.getNumEvents());
+    put("dalitzfit.nll_start", s->calculateNLL());
+    FitManager fit(s);
+    fit.setVerbosity(0);
+    auto t0 = std::chrono::steady_clock::now();
+    auto fm = fit.fit();
+    double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    std::vector<double> val, err;
+    for(auto &c : M->coefs) { val.push_back(c.getValue()); err.push_back(c.getError()); }
+    put_vec("dalitzfit.values", val);
+    put_vec("dalitzfit.errors", err);
+    put("dalitzfit.fval", fm.Fval());
+    put("dalitzfit.nfcn", fm.NFcn());
+    put("dalitzfit.valid", (double)(int)fm.IsValid());
+    put("dalitzfit.seconds", secs);
+}
+
+// ---- CPU baseline timing ------------------------------------------------------------------------
+// Each step = one Minuit-style call: coefficients move (masses/widths fixed as dalitz.cpp:298-305),
+// Params::from_minuit_vector semantics (Params.cpp:47-57) then calculateNLL().
+static int bench(const std::string &config, size_t N, int K, int W) {
+    int threads = omp_get_max_threads();
+    double t_setup = 0, t_first = 0;
+    std::vector<double> ms;
+    double last = 0;
+    auto now = [] { return std::chrono::steady_clock::now(); };
+    auto secs = [](auto a, auto b) { return std::chrono::duration<double>(b - a).count(); };
+    if(config == "dalitz") {
+        DalitzModel *M = make_dalitz(false, 240);
+        UnbinnedDataSet d({M->m12, M->m13, M->eventNumber});
+        fill_dalitz_uniform(*M, d, N, 12345);
+        auto t0 = now();
+        M->signal->setData(&d);
+        M->signal->setDataSize(d.getNumEvents());
+        auto t1 = now();
+        last = M->signal->calculateNLL();
+        auto t2 = now();
+        t_setup = secs(t0, t1); t_first = secs(t1, t2);
+        FitManager fm(M->signal);
+        FCN *fcn = fm.getFCN();
+        std::vector<double> v0 = fm.getParams()->make_minuit_vector(), v = v0;
+        std::vector<int> idx;
+        for(size_t c = 2; c < M->coefs.size(); c++) idx.push_back(M->coefs[c].getFitterIndex());
+        for(int k = 0; k < W + K; k++) {
+            for(size_t c = 0; c < idx.size(); c++) v[idx[c]] = v0[idx[c]] * (1.0 + 1e-3 * ((k + (int)c) % 3 - 1));
+            auto a = now();
+            last = (*fcn)(v);
+            auto b = now();
+            if(k >= W) ms.push_back(1e3 * secs(a, b));
+        }
+    } else if(config == "exponential") {
+        Observable x{"x", 0, 10};
+        UnbinnedDataSet d{x};
+        fill_1d(d, x, N, 137, 1, 1.0);
+        Variable alpha{"alpha", -2, 0.1, -10, 10};
+        ExpPdf pdf{"exppdf", x, alpha};
+        auto t0 = now();
+        pdf.setData(&d);
+        auto t1 = now();
+        last = pdf.calculateNLL();
+        auto t2 = now();
+        t_setup = secs(t0, t1); t_first = secs(t1, t2);
+        FitManager fm(&pdf);
+        FCN *fcn = fm.getFCN();
+        std::vector<double> v = fm.getParams()->make_minuit_vector();
+        for(int k = 0; k < W + K; k++) {
+            v[alpha.getFitterIndex()] = -2.0 + 0.01 * (k % 5);
+            auto a = now();
+            last = (*fcn)(v);
+            auto b = now();
+            if(k >= W) ms.push_back(1e3 * secs(a, b));
+        }
+    } else {
+        fprintf(stderr, "unknown bench config %s\n", config.c_str());
+        return 2;
+    }
+    double tot = 0;
+    for(double m : ms) tot += m;
+    double mean = tot / ms.size();
+    printf("{\"config\": \"%s\", \"n_events\": %zu, \"steps\": %d, \"warmup\": %d, \"threads\": %d, \"ms_per_step\": %.6f, "
+           "\"events_x_evals_per_s\": %.6e, \"setdata_s\": %.4f, \"first_call_s\": %.4f, \"last_nll\": %.17g}\n",
+           config.c_str(), N, K, W, threads, mean, (double)N / (mean * 1e-3), t_setup, t_first, last);
+    return 0;
+}
+
+int main(int argc, char **argv) {
+    if(argc < 2) {
+        fprintf(stderr, "usage: ref_driver golden <outdir> | bench <config> <N> <K> [W]\n");
+        return 2;
+    }
+    std::string mode = argv[1];
+    try {
+        if(mode == "golden") {
+            g_out = argc > 2 ? argv[2] : ".";
+            mkdir(g_out.c_str(), 0755);
+            std::string only = argc > 3 ? argv[3] : "all";
+            if(only == "all" || only == "basic") case_basic();
+            if(only == "all" || only == "dalitz") case_dalitz();
+            if(only == "all" || only == "dalitzfit") case_dalitz_fit();
+            std::ofstream f(g_out + "/manifest" + (only == "all" ? "" : "_" + only) + ".json");
+            f << "{\n" << g_manifest.str() << "\n}\n";
+            return 0;
+        }
+        if(mode == "bench") {
+            if(argc < 5) return 2;
+            return bench(argv[2], std::stoul(argv[3]), std::stoi(argv[4]), argc > 5 ? std::stoi(argv[5]) : 1);
+        }
+    } catch(const std::exception &e) {
+        fprintf(stderr, "ref_driver: %s\n", e.what());
+        return 1;
+    }
+    return 2;
+}
