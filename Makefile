@@ -1,13 +1,33 @@
-# Builds the product: libgoofit_b200.so (hand-written sm_100a kernels behind the C ABI in include/goofit_b200.h)
+# Builds the product:
+#   goofit_b200/lib/libgoofit_b200.so   hand-written sm_100a kernels behind the C ABI (include/goofit_b200.h)
+#   goofit_b200/lib/libMinuit2.so       the reference's bundled third-party Minuit2, compiled unmodified from
+#                                       $(REF)/extern/Minuit2 (host-side minimiser; needs the reference checkout)
+#   goofit_b200/lib/libgoofit_host.so   host C++ API (GooFit class names) over the C ABI
+#   goofit_b200/_goofit*.so             pybind11 module
 NVCC     ?= /usr/local/cuda/bin/nvcc
+CXX      ?= g++
+PYTHON   ?= python
+REF      ?= /root/reference
 ARCH     := -gencode arch=compute_100a,code=sm_100a
 NVFLAGS  := -O3 -std=c++17 $(ARCH) -lineinfo -Xcompiler -fPIC -Xptxas -v --expt-relaxed-constexpr
 CSRC     := goofit_b200/csrc
+HOST     := goofit_b200/host
 LIBDIR   := goofit_b200/lib
 CU       := $(wildcard $(CSRC)/*.cu)
 OBJ      := $(patsubst $(CSRC)/%.cu,build/%.o,$(CU))
+M2INC    := $(REF)/extern/Minuit2/inc
+M2SRC    := $(filter-out %/TMinuit2TraceObject.cxx,$(wildcard $(REF)/extern/Minuit2/src/*.cxx) $(wildcard $(REF)/extern/Minuit2/src/math/*.cxx))
+M2OBJ    := $(patsubst $(REF)/extern/Minuit2/src/%.cxx,build/minuit2/%.o,$(M2SRC))
+HSRC     := $(wildcard $(HOST)/src/*.cpp)
+HOBJ     := $(patsubst $(HOST)/src/%.cpp,build/host/%.o,$(HSRC))
+HFLAGS   := -O2 -std=c++17 -fPIC -Wall -Wno-unused-function -Iinclude -I$(HOST)/include -I$(M2INC) -DMATHCORE_STANDALONE
+PYEXT    := $(shell $(PYTHON) -c "import sysconfig; print(sysconfig.get_config_var('EXT_SUFFIX'))")
+PYINC    := $(shell $(PYTHON) -c "import sysconfig, pybind11; print('-I' + sysconfig.get_paths()['include'] + ' -I' + pybind11.get_include())")
 
-all: $(LIBDIR)/libgoofit_b200.so
+all: cuda host python
+cuda: $(LIBDIR)/libgoofit_b200.so
+host: $(LIBDIR)/libgoofit_host.so
+python: goofit_b200/_goofit$(PYEXT)
 
 build/%.o: $(CSRC)/%.cu $(wildcard $(CSRC)/*.cuh) include/goofit_b200.h
 	@mkdir -p build
@@ -15,8 +35,32 @@ build/%.o: $(CSRC)/%.cu $(wildcard $(CSRC)/*.cuh) include/goofit_b200.h
 
 $(LIBDIR)/libgoofit_b200.so: $(OBJ)
 	@mkdir -p $(LIBDIR)
-	$(NVCC) -shared $(ARCH) -o $@ $(OBJ) -lcudart
+	$(NVCC) -shared $(ARCH) -o $@ $(OBJ) -lcudart -ldl
+
+build/minuit2/%.o: $(REF)/extern/Minuit2/src/%.cxx
+	@mkdir -p $(dir $@)
+	$(CXX) -std=c++17 -O2 -fPIC -w -DMATHCORE_STANDALONE -DROOT_Math_VecTypes -DMATH_NO_PLUGIN_MANAGER -I$(M2INC) -c $< -o $@
+
+$(LIBDIR)/libMinuit2.so: $(M2OBJ)
+	@mkdir -p $(LIBDIR)
+	@if [ -n "$(M2OBJ)" ]; then $(CXX) -shared -o $@ $(M2OBJ); else test -f $@ || (echo "Minuit2 sources not found under $(REF) and no prebuilt $@"; false); fi
+
+build/host/%.o: $(HOST)/src/%.cpp $(wildcard $(HOST)/include/goofit/detail/*.h) include/goofit_b200.h
+	@mkdir -p build/host
+	$(CXX) $(HFLAGS) -c $< -o $@
+
+$(LIBDIR)/libgoofit_host.so: $(HOBJ) $(LIBDIR)/libgoofit_b200.so $(LIBDIR)/libMinuit2.so
+	$(CXX) -shared -o $@ $(HOBJ) -L$(LIBDIR) -lgoofit_b200 -lMinuit2 -Wl,-rpath,'$$ORIGIN'
+
+build/py/%.o: goofit_b200/python/%.cpp $(wildcard $(HOST)/include/goofit/detail/*.h)
+	@mkdir -p build/py
+	$(CXX) $(HFLAGS) $(PYINC) -fvisibility=hidden -c $< -o $@
+
+PYSRC := $(wildcard goofit_b200/python/*.cpp)
+PYOBJ := $(patsubst goofit_b200/python/%.cpp,build/py/%.o,$(PYSRC))
+goofit_b200/_goofit$(PYEXT): $(PYOBJ) $(LIBDIR)/libgoofit_host.so
+	$(CXX) -shared -o $@ $(PYOBJ) -L$(LIBDIR) -lgoofit_host -lgoofit_b200 -lMinuit2 -Wl,-rpath,'$$ORIGIN/lib'
 
 clean:
-	rm -rf build $(LIBDIR)/*.so
-.PHONY: all clean
+	rm -rf build $(LIBDIR)/*.so goofit_b200/_goofit*.so
+.PHONY: all cuda host python clean

@@ -1,0 +1,22 @@
+"""goofit_b200 — B200-native (sm_100a) implementation of GooFit's likelihood-evaluation hot path.
+
+`from goofit_b200 import *` mirrors `from goofit import *` for the classes on that path: the pybind11 module
+`_goofit` wraps the host C++ API (GooFit class names), which calls hand-written CUDA kernels through the C ABI
+in include/goofit_b200.h. There is no CPU fallback: evaluating a PDF without a CUDA device raises GeneralError.
+"""
+import os as _os
+
+_here = _os.path.dirname(_os.path.abspath(__file__))
+LIB_DIR = _os.path.join(_here, "lib")
+CAPI_PATH = _os.path.join(LIB_DIR, "libgoofit_b200.so")
+
+try:
+    from ._goofit import *  # noqa: F401,F403
+    from . import _goofit
+    from ._goofit import Resonances  # noqa: F401
+except ImportError as e:  # pragma: no cover - build missing
+    raise ImportError(
+        "goofit_b200: the native extension is not built (run `make` or `python -c 'import __graft_entry__ as g; g.build()'`): %s" % e
+    )
+
+from . import capi  # noqa: E402,F401

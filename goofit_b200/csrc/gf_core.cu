@@ -249,6 +249,20 @@ extern "C" int gf_set_program(gf_ctx *c, const gf_node *nodes, int n_nodes, cons
     return 0;
 }
 
+extern "C" int gf_reset_aux(gf_ctx *c) {
+    if(!c) return gf_fail("null ctx");
+    cudaSetDevice(c->device);
+    GF_CUDA(cudaStreamSynchronize(c->stream));
+    gf_amp3_free(c);
+    gf_amp4_free(c);
+    gf_conv_free(c);
+    for(int i = 0; i < GF_MAX_AUX; i++) {
+        c->view.aux[i]    = nullptr;
+        c->view.aux_ld[i] = 0;
+    }
+    return 0;
+}
+
 extern "C" int gf_set_params(gf_ctx *c, const double *params, int n) {
     if(!c) return gf_fail("null ctx");
     if(n != c->n_params) return gf_fail("gf_set_params: expected " + std::to_string(c->n_params) + " got " + std::to_string(n));

@@ -1,0 +1,112 @@
+// Pdfs.h — the basic shapes and combiners named by the north star, same constructors as the
+// reference headers (/root/reference/include/goofit/PDFs/basic/*.h, PDFs/combine/*.h). Each class
+// only records an opcode + its parameters/constants; the per-event math lives in csrc/gf_ops.cuh.
+#pragma once
+#include <goofit/detail/Core.h>
+
+namespace GooFit {
+
+class ExpPdf : public GooPdf { // basic/ExpPdf.h
+  public:
+    ExpPdf(std::string n, Observable _x, Variable alpha);
+    ExpPdf(std::string n, Observable _x, std::vector<Variable> &weights);
+    ExpPdf(std::string n, Observable _x, Variable alpha, Variable offset);
+    ExpPdf(std::string n, Observable _x, std::vector<Variable> &weights, Variable offset);
+    fptype integrate(fptype lo, fptype hi) const override;
+    bool hasAnalyticIntegral() const override { return opcode_ == GF_OP_EXP; }
+};
+
+class GaussianPdf : public GooPdf { // basic/GaussianPdf.h
+  public:
+    GaussianPdf(std::string n, Observable _x, Variable m, Variable s);
+    fptype integrate(fptype lo, fptype hi) const override;
+    bool hasAnalyticIntegral() const override { return true; }
+};
+
+class PolynomialPdf : public GooPdf { // basic/PolynomialPdf.h
+  public:
+    PolynomialPdf(std::string n, Observable _x, std::vector<Variable> weights, unsigned int lowestDegree = 0);
+    PolynomialPdf(std::string n, Observable _x, std::vector<Variable> weights, Variable x0, unsigned int lowestDegree = 0);
+    PolynomialPdf(std::string n, std::vector<Observable> obses, std::vector<Variable> coeffs, std::vector<Variable> offsets,
+                  unsigned int maxDegree = 0);
+    fptype integrate(fptype lo, fptype hi) const override;
+    fptype getCoefficient(int coef);
+
+  private:
+    std::unique_ptr<Variable> center;
+};
+
+class ArgusPdf : public GooPdf { // basic/ArgusPdf.h
+  public:
+    ArgusPdf(std::string n, Observable _x, Variable m, Variable s, bool upper);
+    ArgusPdf(std::string n, Observable _x, Variable m, Variable s, bool upper, Variable power);
+    bool hasAnalyticIntegral() const override { return false; }
+    fptype integrate(fptype lo, fptype hi) const override;
+};
+
+class KinLimitBWPdf : public GooPdf { // basic/KinLimitBWPdf.h
+  public:
+    KinLimitBWPdf(std::string n, Observable _x, Variable m, Variable s);
+    bool hasAnalyticIntegral() const override { return false; }
+    void setMasses(fptype bigM, fptype smallM);
+};
+
+class ScaledGaussianPdf : public GooPdf { // basic/ScaledGaussianPdf.h
+  public:
+    ScaledGaussianPdf(std::string n, Observable _x, Variable m, Variable s, Variable d, Variable e);
+    bool hasAnalyticIntegral() const override { return false; }
+};
+
+class JohnsonSUPdf : public GooPdf { // basic/JohnsonSUPdf.h
+  public:
+    JohnsonSUPdf(std::string n, Observable _x, Variable m, Variable s, Variable g, Variable d);
+    fptype integrate(fptype lo, fptype hi) const override { return 1.0; }
+    bool hasAnalyticIntegral() const override { return true; }
+};
+
+class CombinePdf : public GooPdf { // PDFs/CombinePdf.h
+  public:
+    using GooPdf::GooPdf;
+};
+
+class AddPdf : public CombinePdf { // combine/AddPdf.h
+  public:
+    AddPdf(std::string n, std::vector<Variable> weights, std::vector<PdfBase *> comps);
+    AddPdf(std::string n, Variable frac1, PdfBase *func1, PdfBase *func2);
+    fptype normalize() override;
+    bool hasAnalyticIntegral() const override { return false; }
+    double calculateNLL() override;
+
+  private:
+    bool extended;
+};
+
+class ProdPdf : public CombinePdf { // combine/ProdPdf.h
+  public:
+    ProdPdf(std::string n, std::vector<PdfBase *> comps);
+    fptype normalize() override;
+    bool hasAnalyticIntegral() const override { return false; }
+
+  private:
+    bool varOverlaps{false};
+};
+
+class ConvolutionPdf : public CombinePdf { // combine/ConvolutionPdf.h
+  public:
+    ConvolutionPdf(std::string n, Observable _x, GooPdf *model, GooPdf *resolution);
+    fptype normalize() override;
+    void setIntegrationConstants(fptype lo, fptype hi, fptype step);
+
+    void emitAux(detail::ProgramBuilder &B) override;
+    int emit(detail::ProgramBuilder &B) override;
+    void afterProgram() override;
+
+  protected:
+
+  private:
+    GooPdf *model;
+    GooPdf *resolution;
+    bool workspacesFilled{false};
+};
+
+} // namespace GooFit

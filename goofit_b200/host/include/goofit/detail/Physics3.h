@@ -1,0 +1,136 @@
+// Physics3.h — three-body Dalitz amplitude PDF and its resonance shapes
+// (reference: include/goofit/PDFs/physics/{Amp3Body.h,Amp3BodyBase.h,DalitzPlotHelpers.h,DalitzPlotter.h},
+//  include/goofit/PDFs/physics/resonances/{Resonance,RBW,GS,NonRes,Gauss}.h).
+#pragma once
+#include <goofit/detail/Pdfs.h>
+
+namespace GooFit {
+
+enum DaughterPair { PAIR_12 = 0, PAIR_13, PAIR_23 };
+
+bool inDalitz(const fptype &m12, const fptype &m13, const fptype &bigM, const fptype &dm1, const fptype &dm2, const fptype &dm3);
+
+/// A component of an amplitude PDF: it is never evaluated per event on its own.
+class AmpComponent : public GooPdf {
+  public:
+    using GooPdf::GooPdf;
+    fptype normalize() override { return 1.0; }
+};
+
+class ResonancePdf : public AmpComponent {
+    friend class Amp3Body;
+
+  public:
+    Variable get_amp_real() const { return amp_real; }
+    Variable get_amp_img() const { return amp_imag; }
+
+  protected:
+    ResonancePdf(std::string pdf_name, std::string name, Variable ar, Variable ai)
+        : AmpComponent("Resonances::" + pdf_name, name)
+        , amp_real(ar)
+        , amp_imag(ai) {}
+  public:
+    int emit(detail::ProgramBuilder &B) override { return emitRecord(B, opcode_, 0, 1, {}); }
+
+  protected:
+    Variable amp_real;
+    Variable amp_imag;
+};
+
+namespace Resonances {
+class RBW : public ResonancePdf { // resonances/RBW.cu:93-119
+  public:
+    RBW(std::string name, Variable ar, Variable ai, Variable mass, Variable width, unsigned int sp, unsigned int cyc,
+        bool norm = true, bool sym = false);
+};
+class GS : public ResonancePdf { // resonances/GS.cu:81-101
+  public:
+    GS(std::string name, Variable ar, Variable ai, Variable mass, Variable width, unsigned int sp, unsigned int cyc,
+       bool norm = true, bool sym = false);
+};
+class NonRes : public ResonancePdf { // resonances/NonRes.cu:17-20
+  public:
+    NonRes(std::string name, Variable ar, Variable ai);
+};
+class Gauss : public ResonancePdf { // resonances/Gauss.cu:35-46
+  public:
+    Gauss(std::string name, Variable ar, Variable ai, Variable mean, Variable sigma, unsigned int cyc);
+};
+} // namespace Resonances
+
+struct DecayInfo3 { // DalitzPlotHelpers.h:83-92
+    fptype motherMass;
+    fptype daug1Mass;
+    fptype daug2Mass;
+    fptype daug3Mass;
+    fptype meson_radius;
+    fptype mother_meson_radius;
+    std::vector<ResonancePdf *> resonances;
+};
+
+class Amp3BodyBase : public GooPdf {
+  public:
+    using GooPdf::GooPdf;
+};
+
+class DalitzPlotter;
+
+class Amp3Body : public Amp3BodyBase { // Amp3Body.h:43-111
+  public:
+    Amp3Body(std::string n, Observable m12, Observable m13, EventNumber eventNumber, DecayInfo3 decay, GooPdf *eff = nullptr);
+    fptype normalize() override;
+    void setDataSize(unsigned int dataSize, unsigned int evtSize = 3, unsigned int offset = 0);
+    void setForceIntegrals(bool f = true) { forceRedoIntegrals = f; }
+    std::vector<std::complex<fptype>> getCachedWave(size_t i) const;
+    fpcomplex sumCachedWave(size_t i) const;
+    DecayInfo3 &getDecayInfo() { return decayInfo; }
+    static void resetCacheCounter() {}
+    std::vector<std::vector<fptype>> fit_fractions();
+    /// normalisation integrals I_ij of the last normalize() (row i, column j)
+    const std::vector<fpcomplex> &getIntegrals() const { return integrals; }
+    friend DalitzPlotter;
+
+    void emitAux(detail::ProgramBuilder &B) override;
+    int emit(detail::ProgramBuilder &B) override;
+    void afterProgram() override;
+
+  protected:
+    void ensureCache();
+
+    DecayInfo3 decayInfo;
+    Observable _m12, _m13;
+    EventNumber _eventNumber;
+    GooPdf *efficiency;
+    std::vector<fpcomplex> integrals;
+    bool forceRedoIntegrals{true};
+    bool cacheAllocated{false};
+    int totalEventSize{3};
+};
+
+/// Host helper that evaluates the PDF on the Dalitz grid and draws toy events from it
+/// (DalitzPlotter.h:24-141; the ROOT histogram methods are out of scope).
+class DalitzPlotter {
+  public:
+    DalitzPlotter(GooPdf *overallSignal, Amp3Body *signalDalitz);
+    void fillDataSetMC(UnbinnedDataSet &dataset, size_t nTotal, unsigned int seed = 0);
+    size_t getNumEvents() const { return data.getNumEvents(); }
+    size_t getX(size_t event) const { return xbins.at(event); }
+    size_t getY(size_t event) const { return ybins.at(event); }
+    fptype getXval(size_t event) const { return data.getValue(m12, event); }
+    fptype getYval(size_t event) const { return data.getValue(m13, event); }
+    fptype getZval(size_t event) const { return mother * mother - getXval(event) * getXval(event) - getYval(event) * getYval(event); }
+    fptype getVal(size_t event, size_t num = 0) const { return pdfValues.at(num).at(event); }
+    UnbinnedDataSet *getDataSet() { return &data; }
+    const Observable &getM12() const { return m12; }
+    const Observable &getM13() const { return m13; }
+
+  private:
+    std::vector<size_t> xbins, ybins;
+    std::vector<std::vector<fptype>> pdfValues;
+    Observable m12, m13;
+    EventNumber eventNumber;
+    UnbinnedDataSet data;
+    fptype mother;
+};
+
+} // namespace GooFit

@@ -1,0 +1,238 @@
+// amp3.cpp — host half of Amp3Body (reference: src/PDFs/physics/Amp3Body.cu:127-428). The cached
+// resonance waves and the grid integrals live in the CUDA library (csrc/gf_amp3.cu); this file keeps the
+// reference's cache state machine: what is recomputed on which call (Amp3Body.cu:266-330).
+#include <goofit/detail/Physics3.h>
+
+#include <numeric>
+#include <random>
+
+namespace GooFit {
+using detail::Engine;
+
+bool inDalitz(const fptype &m12, const fptype &m13, const fptype &bigM, const fptype &dm1, const fptype &dm2,
+              const fptype &dm3) { // DalitzPlotHelpers.cu:14-59
+    fptype dm1pdm2 = dm1 + dm2, bigMmdm3 = bigM - dm3, bigMmdm1 = bigM - dm1;
+    fptype m23 = bigM * bigM + dm1 * dm1 + dm2 * dm2 + dm3 * dm3 - m12 - m13;
+    if(m23 < 0. || m23 > bigMmdm1 * bigMmdm1) return false;
+    bool m12less = (m12 < dm1pdm2 * dm1pdm2) ? false : true;
+    bool m12grea = (m12 > bigMmdm3 * bigMmdm3) ? false : true;
+    fptype sqrtM12 = sqrt(m12), dm11 = dm1 * dm1, dm22 = dm2 * dm2, dm33 = dm3 * dm3;
+    fptype e1star = 0.5 * (m12 - dm22 + dm11) / sqrtM12;
+    fptype e3star = 0.5 * (bigM * bigM - m12 - dm33) / sqrtM12;
+    fptype r1 = sqrt(e1star * e1star - dm11), r3 = sqrt(e3star * e3star - dm33);
+    fptype es = (e1star + e3star) * (e1star + e3star);
+    fptype minimum = es - (r1 + r3) * (r1 + r3), maximum = es - (r1 - r3) * (r1 - r3);
+    bool m13less = (m13 < minimum) ? false : true, m13grea = (m13 > maximum) ? false : true;
+    return m12less && m12grea && m13less && m13grea;
+}
+
+namespace Resonances {
+RBW::RBW(std::string name, Variable ar, Variable ai, Variable mass, Variable width, unsigned int sp, unsigned int cyc,
+         bool norm, bool sym)
+    : ResonancePdf("RBW", name, ar, ai) {
+    registerParameter(mass);
+    registerParameter(width);
+    registerConstant(sp);
+    registerConstant(cyc);
+    registerConstant(norm);
+    registerFunction(sym ? "ptr_to_RBW_Sym" : "ptr_to_RBW", sym ? GF_OP_RES_RBW_SYM : GF_OP_RES_RBW);
+}
+GS::GS(std::string name, Variable ar, Variable ai, Variable mass, Variable width, unsigned int sp, unsigned int cyc,
+       bool norm, bool)
+    : ResonancePdf("GS", name, ar, ai) {
+    registerParameter(mass);
+    registerParameter(width);
+    registerConstant(sp);
+    registerConstant(cyc);
+    registerConstant(norm);
+    registerFunction("ptr_to_GOUSAK", GF_OP_RES_GS);
+}
+NonRes::NonRes(std::string name, Variable ar, Variable ai)
+    : ResonancePdf("NonRes", name, ar, ai) {
+    registerFunction("ptr_to_NONRES", GF_OP_RES_NONRES);
+}
+Gauss::Gauss(std::string name, Variable ar, Variable ai, Variable mass, Variable width, unsigned int cyc)
+    : ResonancePdf("Gauss", name, ar, ai) {
+    registerParameter(mass);
+    registerParameter(width);
+    registerConstant(cyc);
+    registerFunction("ptr_to_GAUSSIAN", GF_OP_RES_GAUSS);
+}
+} // namespace Resonances
+
+Amp3Body::Amp3Body(std::string n, Observable m12, Observable m13, EventNumber eventNumber, DecayInfo3 decay, GooPdf *eff)
+    : Amp3BodyBase("Amp3Body", n, m12, m13, eventNumber)
+    , decayInfo(decay)
+    , _m12(m12)
+    , _m13(m13)
+    , _eventNumber(eventNumber)
+    , efficiency(eff) {
+    if(decayInfo.resonances.empty()) throw GeneralError("Amp3Body {} needs at least one resonance", n);
+    if(decayInfo.resonances.size() > 64) throw GeneralError("Amp3Body supports at most 64 resonances");
+    if(!efficiency) throw GeneralError("Amp3Body {} needs an efficiency function", n);
+    // record constants: decay kinematics (the reference keeps them in __constant__ symbols, Amp3Body.cu:144-149)
+    registerConstant(decay.motherMass);
+    registerConstant(decay.daug1Mass);
+    registerConstant(decay.daug2Mass);
+    registerConstant(decay.daug3Mass);
+    registerConstant(decay.meson_radius);
+    registerConstant(decay.mother_meson_radius);
+    for(auto *res : decayInfo.resonances) {
+        registerParameter(res->amp_real);
+        registerParameter(res->amp_imag);
+        components.push_back(res);
+    }
+    components.push_back(efficiency);
+    registerFunction("ptr_to_DalitzPlot", GF_OP_AMP3);
+    integrals.assign(decayInfo.resonances.size() * decayInfo.resonances.size(), fpcomplex(0, 0));
+    setSeparateNorm();
+}
+void Amp3Body::emitAux(detail::ProgramBuilder &B) {
+    for(auto *res : decayInfo.resonances) res->emit(B);
+    efficiency->emitAux(B);
+}
+int Amp3Body::emit(detail::ProgramBuilder &B) {
+    int first = (int)B.nodes.size();
+    efficiency->emit(B);
+    std::vector<int32_t> ints{B.allocAux(), (int32_t)decayInfo.resonances.size()};
+    for(auto *res : decayInfo.resonances) ints.push_back(res->getFunctionIndex());
+    return emitRecord(B, GF_OP_AMP3, 1, (int)B.nodes.size() - first + 1, ints);
+}
+void Amp3Body::afterProgram() {
+    cacheAllocated     = false; // device caches belong to the previous program
+    forceRedoIntegrals = true;
+}
+void Amp3Body::setDataSize(unsigned int dataSize, unsigned int evtSize, unsigned int) { // Amp3Body.cu:204-236
+    totalEventSize = evtSize;
+    if(totalEventSize < 3) throw GeneralError("totalEventSize {} must be 3 or more", totalEventSize);
+    numEntries     = dataSize;
+    cacheAllocated = false;
+    setForceIntegrals();
+}
+void Amp3Body::ensureCache() {
+    if(cacheAllocated) return;
+    if(nodeIdx < 0) throw GeneralError("Amp3Body {}: call setData() on the top-level PDF before evaluating", getName());
+    Engine &E = Engine::get();
+    Engine::check(gf_amp3_alloc(E.ctx(), nodeIdx, E.localEvents), "gf_amp3_alloc");
+    cacheAllocated     = true;
+    forceRedoIntegrals = true;
+}
+fptype Amp3Body::normalize() { // Amp3Body.cu:238-359
+    recursiveSetNormalization(1.0); // the efficiency is not normalised
+    ensureCache();
+    Engine &E    = Engine::get();
+    size_t nres  = decayInfo.resonances.size();
+    std::vector<uint8_t> redo(nres);
+    bool any = false;
+    for(size_t i = 0; i < nres; ++i) {
+        redo[i] = forceRedoIntegrals || decayInfo.resonances[i]->parametersChanged();
+        any     = any || redo[i];
+    }
+    forceRedoIntegrals = false;
+    if(any) {
+        E.sync();
+        Engine::check(gf_amp3_cache_waves(E.ctx(), nodeIdx, redo.data()), "gf_amp3_cache_waves");
+        double spec[6] = {_m12.getLowerLimit(), _m12.getUpperLimit(), (double)_m12.getNumBins(),
+                          _m13.getLowerLimit(), _m13.getUpperLimit(), (double)_m13.getNumBins()};
+        std::vector<double> I(2 * nres * nres);
+        Engine::check(gf_amp3_integrals(E.ctx(), nodeIdx, redo.data(), spec, efficiency->getFunctionIndex(), I.data()),
+                      "gf_amp3_integrals");
+        for(size_t k = 0; k < nres * nres; k++) integrals[k] = fpcomplex(I[2 * k], I[2 * k + 1]);
+    }
+    fpcomplex sumIntegral(0, 0);
+    for(size_t i = 0; i < nres; ++i) {
+        fpcomplex amplitude_i(parametersList[2 * i].getValue(), parametersList[2 * i + 1].getValue());
+        for(size_t j = 0; j < nres; ++j) {
+            fpcomplex amplitude_j(parametersList[2 * j].getValue(), -parametersList[2 * j + 1].getValue());
+            sumIntegral += amplitude_i * amplitude_j * integrals[i * nres + j];
+        }
+    }
+    fptype ret           = sumIntegral.real();
+    double binSizeFactor = 1;
+    binSizeFactor *= _m12.getBinSize();
+    binSizeFactor *= _m13.getBinSize();
+    ret *= binSizeFactor;
+    setNormalization(1.0 / ret);
+    return ret;
+}
+std::vector<std::complex<fptype>> Amp3Body::getCachedWave(size_t i) const {
+    if(!cacheAllocated) throw GeneralError("Amp3Body {}: no cached waves yet", getName());
+    Engine &E = Engine::get();
+    std::vector<std::complex<fptype>> ret(E.localEvents);
+    Engine::check(gf_amp3_get_wave(E.ctx(), nodeIdx, (int)i, reinterpret_cast<double *>(ret.data()), ret.size()), "gf_amp3_get_wave");
+    return ret;
+}
+fpcomplex Amp3Body::sumCachedWave(size_t i) const {
+    auto w = getCachedWave(i);
+    return std::accumulate(w.begin(), w.end(), fpcomplex(0, 0));
+}
+std::vector<std::vector<fptype>> Amp3Body::fit_fractions() { // Amp3Body.cu:376-428, host sums over the cached waves
+    size_t n_res = decayInfo.resonances.size();
+    std::vector<std::vector<std::complex<fptype>>> w(n_res);
+    for(size_t i = 0; i < n_res; i++) w[i] = getCachedWave(i);
+    size_t nEntries = w[0].size();
+    std::vector<std::vector<fptype>> Amps_int(n_res, std::vector<fptype>(n_res)), ff = Amps_int;
+    fptype buffer_all = 0;
+    for(size_t i = 0; i < n_res; i++)
+        for(size_t j = 0; j < n_res; j++) {
+            fpcomplex ci(decayInfo.resonances[i]->amp_real.getValue(), decayInfo.resonances[i]->amp_imag.getValue());
+            fpcomplex cj(decayInfo.resonances[j]->amp_real.getValue(), decayInfo.resonances[j]->amp_imag.getValue());
+            fptype buffer = 0;
+            for(size_t e = 0; e < nEntries; e++) buffer += (ci * std::conj(cj) * w[i][e] * std::conj(w[j][e])).real();
+            buffer_all += buffer;
+            Amps_int[i][j] = buffer / nEntries;
+        }
+    fptype total_PDF = buffer_all / nEntries;
+    for(size_t i = 0; i < n_res; i++)
+        for(size_t j = 0; j < n_res; j++) ff[i][j] = Amps_int[i][j] / total_PDF;
+    return ff;
+}
+
+// ---- DalitzPlotter (include/goofit/PDFs/physics/DalitzPlotter.h:29-95) ---------------------------------
+DalitzPlotter::DalitzPlotter(GooPdf *overallSignal, Amp3Body *signalDalitz)
+    : m12(signalDalitz->_m12)
+    , m13(signalDalitz->_m13)
+    , eventNumber(signalDalitz->_eventNumber)
+    , data({m12, m13, eventNumber})
+    , mother(signalDalitz->decayInfo.motherMass) {
+    const DecayInfo3 &d = signalDalitz->decayInfo;
+    eventNumber.setValue(0);
+    for(size_t i = 0; i < m12.getNumBins(); ++i) {
+        m12.setValue(m12.getLowerLimit() + m12.getBinSize() * (i + 0.5));
+        for(size_t j = 0; j < m13.getNumBins(); ++j) {
+            m13.setValue(m13.getLowerLimit() + m13.getBinSize() * (j + 0.5));
+            if(!inDalitz(m12.getValue(), m13.getValue(), d.motherMass, d.daug1Mass, d.daug2Mass, d.daug3Mass)) continue;
+            xbins.push_back(i);
+            ybins.push_back(j);
+            data.addEvent();
+            eventNumber.setValue(eventNumber.getValue() + 1);
+        }
+    }
+    auto *old = overallSignal->getData();
+    overallSignal->setData(&data);
+    signalDalitz->setDataSize(data.getNumEvents());
+    pdfValues = overallSignal->getCompProbsAtDataPoints();
+    overallSignal->setData(old);
+}
+// Same draw sequence as the reference (one uniform for the cell, then one per coordinate); the seed is
+// an argument instead of std::random_device so toys are reproducible (seed 0 keeps the random behaviour).
+void DalitzPlotter::fillDataSetMC(UnbinnedDataSet &dataset, size_t nTotal, unsigned int seed) {
+    if(seed == 0) seed = std::random_device{}();
+    std::mt19937 gen(seed);
+    std::uniform_real_distribution<> unihalf(-.5, .5), uniwhole(0.0, 1.0);
+    std::vector<double> integral(pdfValues[0].size());
+    std::partial_sum(pdfValues[0].begin(), pdfValues[0].end(), integral.begin());
+    for(double &v : integral) v /= integral.back();
+    for(size_t i = 0; i < nTotal; i++) {
+        double r = uniwhole(gen);
+        size_t j = std::lower_bound(integral.begin(), integral.end(), r) - integral.begin();
+        double currm12 = data.getValue(m12, j) + m12.getBinSize() * unihalf(gen);
+        double currm13 = data.getValue(m13, j) + m13.getBinSize() * unihalf(gen);
+        m12.setValue(currm12);
+        m13.setValue(currm13);
+        eventNumber.setValue(i);
+        dataset.addEvent();
+    }
+}
+
+} // namespace GooFit

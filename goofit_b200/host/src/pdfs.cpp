@@ -1,0 +1,309 @@
+// pdfs.cpp — host halves of the basic shapes and combiners (reference: src/PDFs/basic/*.cu,
+// src/PDFs/combine/*.cu; line numbers cited per function).
+#include <goofit/detail/Pdfs.h>
+
+namespace GooFit {
+using detail::Engine;
+
+// ---- ExpPdf (basic/ExpPdf.cu:73-132) -----------------------------------------------------------------
+ExpPdf::ExpPdf(std::string n, Observable _x, Variable alpha)
+    : GooPdf("ExpPdf", n, _x, alpha) {
+    registerFunction("ptr_to_Exp", GF_OP_EXP);
+}
+ExpPdf::ExpPdf(std::string n, Observable _x, Variable alpha, Variable offset)
+    : GooPdf("ExpPdf", n, _x, offset, alpha) {
+    registerFunction("ptr_to_ExpOffset", GF_OP_EXP_OFFSET);
+}
+ExpPdf::ExpPdf(std::string n, Observable _x, std::vector<Variable> &weights)
+    : GooPdf("ExpPdf", n, _x) {
+    if(weights.empty()) throw GeneralError("Weights are empty!");
+    for(Variable &w : weights) registerParameter(w);
+    registerFunction("ptr_to_ExpPoly", GF_OP_EXP_POLY);
+}
+ExpPdf::ExpPdf(std::string n, Observable _x, std::vector<Variable> &weights, Variable offset)
+    : GooPdf("ExpPdf", n, _x, offset) {
+    if(weights.empty()) throw GeneralError("Weights are empty!");
+    for(Variable &w : weights) registerParameter(w);
+    registerFunction("ptr_to_ExpPolyOffset", GF_OP_EXP_POLY_OFFSET);
+}
+fptype ExpPdf::integrate(fptype lo, fptype hi) const {
+    fptype alpha = parametersList[0].getValue();
+    if(0 == alpha) return hi - lo;
+    fptype ret = exp(alpha * hi) - exp(alpha * lo);
+    ret /= alpha;
+    return ret;
+}
+
+// ---- GaussianPdf (basic/GaussianPdf.cu:20-35): the analytic integral is over all of R ------------------
+GaussianPdf::GaussianPdf(std::string n, Observable _x, Variable mean, Variable sigma)
+    : GooPdf("GaussianPdf", n, _x, mean, sigma) {
+    registerFunction("ptr_to_Gaussian", GF_OP_GAUSSIAN);
+}
+fptype GaussianPdf::integrate(fptype, fptype) const {
+    static const fptype rootPi = sqrt(atan2(0.0, -1.0));
+    static const fptype root2  = sqrt(2.0);
+    fptype sigma = parametersList[1].getValue();
+    sigma *= root2 * rootPi;
+    return sigma;
+}
+
+// ---- PolynomialPdf (basic/PolynomialPdf.cu:124-215) -----------------------------------------------------
+PolynomialPdf::PolynomialPdf(std::string n, Observable _x, std::vector<Variable> weights, unsigned int lowestDegree)
+    : GooPdf("PolynomialPdf", n, _x) {
+    registerConstant(lowestDegree);
+    for(Variable &v : weights) registerParameter(v);
+    registerFunction("ptr_to_Polynomial", GF_OP_POLYNOMIAL);
+}
+PolynomialPdf::PolynomialPdf(std::string n, Observable _x, std::vector<Variable> weights, Variable x0, unsigned int lowestDegree)
+    : GooPdf("PolynomialPdf", n, _x)
+    , center(new Variable(x0)) {
+    registerConstant(lowestDegree);
+    for(Variable &v : weights) registerParameter(v);
+    registerParameter(x0);
+    registerFunction("ptr_to_OffsetPolynomial", GF_OP_OFFSET_POLYNOMIAL);
+}
+PolynomialPdf::PolynomialPdf(std::string n, std::vector<Observable> obses, std::vector<Variable> coeffs,
+                             std::vector<Variable> offsets, unsigned int maxDegree)
+    : GooPdf("PolynomialPdf", n) {
+    unsigned int numParameters = 1;
+    registerConstant(maxDegree);
+    for(unsigned int i = 0; i < obses.size(); ++i) {
+        registerObservable(obses[i]);
+        numParameters *= (maxDegree + 1 + i);
+        registerConstant(maxDegree + 1 + i); // padding entries, as the reference
+    }
+    for(int i = (int)observablesList.size(); i > 1; --i) numParameters /= i;
+    while(numParameters > coeffs.size()) {
+        std::string varName = getName() + "_extra_coeff_" + std::to_string(coeffs.size());
+        coeffs.emplace_back(varName, 0);
+        std::cout << "Warning: " << getName() << " created dummy variable " << varName
+                  << " (fixed at zero) to account for all terms.\n";
+    }
+    while(offsets.size() < obses.size())
+        offsets.emplace_back(getName() + "_extra_offset_" + std::to_string(offsets.size()), 0);
+    for(auto &o : offsets) registerParameter(o);
+    for(auto &c : coeffs) registerParameter(c);
+    registerFunction("ptr_to_MultiPolynomial", GF_OP_MULTI_POLYNOMIAL);
+}
+fptype PolynomialPdf::integrate(fptype lo, fptype hi) const { // PolynomialPdf.cu:217-243 (marked wrong upstream; unused: no hasAnalyticIntegral)
+    fptype lowestDegree = constantsList[0];
+    if(center) {
+        hi -= center->getValue();
+        lo -= center->getValue();
+    }
+    fptype ret = 0;
+    for(size_t i = 0; i < parametersList.size() - (center ? 1 : 0); ++i) {
+        fptype powerPlusOne = lowestDegree + i + 1;
+        fptype curr = pow(hi, powerPlusOne);
+        curr -= pow(lo, powerPlusOne);
+        curr /= powerPlusOne;
+        ret += parametersList[i].getValue() * curr;
+    }
+    return ret;
+}
+fptype PolynomialPdf::getCoefficient(int coef) {
+    if(opcode_ == GF_OP_MULTI_POLYNOMIAL) throw GeneralError("getCoefficient method of PolynomialPdf not implemented for multi-dimensional polynomials.");
+    int lowest = (int)constantsList[0];
+    if(coef < lowest) return 0;
+    size_t idx = coef - lowest;
+    if(idx >= parametersList.size() - (center ? 1 : 0)) return 0;
+    return parametersList[idx].getValue();
+}
+
+// ---- ArgusPdf (basic/ArgusPdf.cu:52-96) -------------------------------------------------------------------
+ArgusPdf::ArgusPdf(std::string n, Observable _x, Variable m0, Variable slope, bool upper)
+    : ArgusPdf(n, _x, m0, slope, upper, Variable(n + "powervar", 0.5)) {}
+ArgusPdf::ArgusPdf(std::string n, Observable _x, Variable m0, Variable slope, bool upper, Variable power)
+    : GooPdf("ArgusPdf", n, _x, m0, slope, power) {
+    if(upper)
+        registerFunction("ptr_to_Argus_Upper", GF_OP_ARGUS_UPPER);
+    else
+        registerFunction("ptr_to_Argus_Lower", GF_OP_ARGUS_LOWER);
+}
+fptype ArgusPdf::integrate(fptype lo, fptype hi) const { // left-edge Riemann sum of the lower form, ArgusPdf.cu:79-96
+    double norm = 0;
+    fptype m0 = parametersList[0].getValue(), slope = parametersList[1].getValue(), power = parametersList[2].getValue();
+    for(int j = 0; j < integrationBins; ++j) {
+        double x = hi;
+        x -= lo;
+        x /= integrationBins;
+        x *= j;
+        x += lo;
+        fptype t = x / m0;
+        if(t <= 1) continue;
+        t *= t;
+        t -= 1;
+        norm += x * pow(t, power) * exp(slope * t);
+    }
+    norm *= ((hi - lo) / integrationBins);
+    return norm;
+}
+
+// ---- KinLimitBWPdf / ScaledGaussianPdf / JohnsonSUPdf -------------------------------------------------------
+KinLimitBWPdf::KinLimitBWPdf(std::string n, Observable _x, Variable mean, Variable width)
+    : GooPdf("KinLimitBWPdf", n, _x, mean, width) { // KinLimitBWPdf.cu:58-67
+    registerConstant(1.8645);
+    registerConstant(0.13957);
+    registerFunction("ptr_to_KinLimitBW", GF_OP_KINLIMITBW);
+}
+void KinLimitBWPdf::setMasses(fptype bigM, fptype smallM) {
+    constantsList[0] = bigM;
+    constantsList[1] = smallM;
+}
+ScaledGaussianPdf::ScaledGaussianPdf(std::string n, Observable _x, Variable mean, Variable sigma, Variable delta, Variable epsilon)
+    : GooPdf("ScaledGaussianPdf", n, _x, mean, sigma, delta, epsilon) { // ScaledGaussianPdf.cu:24-31
+    registerFunction("ptr_to_ScaledGaussian", GF_OP_SCALED_GAUSSIAN);
+}
+JohnsonSUPdf::JohnsonSUPdf(std::string n, Observable _x, Variable mean, Variable sigma, Variable gamma, Variable delta)
+    : GooPdf("JohnsonSUPdf", n, _x, mean, sigma, gamma, delta) { // JohnsonSUPdf.cu:28-34
+    registerFunction("ptr_to_JohnsonSU", GF_OP_JOHNSONSU);
+}
+
+// ---- AddPdf (combine/AddPdf.cu:85-204) --------------------------------------------------------------------
+AddPdf::AddPdf(std::string n, std::vector<Variable> weights, std::vector<PdfBase *> comps)
+    : CombinePdf("AddPdf", n)
+    , extended(true) {
+    if(weights.size() != comps.size() && (weights.size() + 1) != comps.size())
+        throw GeneralError("Size of weights {} (+1) != comps {}", weights.size(), comps.size());
+    for(PdfBase *p : comps) {
+        if(p == nullptr) throw GeneralError("Invalid component");
+        components.push_back(p);
+    }
+    observablesList = getObservables();
+    for(auto &w : weights) registerParameter(w);
+    if(weights.size() < components.size()) extended = false;
+    registerFunction(extended ? "ptr_to_AddPdfsExt" : "ptr_to_AddPdfs", extended ? GF_OP_ADD_EXT : GF_OP_ADD);
+}
+AddPdf::AddPdf(std::string n, Variable frac1, PdfBase *func1, PdfBase *func2)
+    : CombinePdf("AddPdf", n, frac1)
+    , extended(false) {
+    if(!func1 || !func2) throw GeneralError("Invalid component");
+    components.push_back(func1);
+    components.push_back(func2);
+    observablesList = getObservables();
+    registerFunction("ptr_to_AddPdfs", GF_OP_ADD);
+}
+fptype AddPdf::normalize() { // AddPdf.cu:143-185
+    fptype ret = 0, totalWeight = 0;
+    for(size_t i = 0; i < components.size() - 1; ++i) {
+        fptype weight = parametersList[i].getValue();
+        totalWeight += weight;
+        fptype curr = components[i]->normalize();
+        ret += curr * weight;
+    }
+    fptype last = components.back()->normalize();
+    if(extended) {
+        fptype lastWeight = parametersList[components.size() - 1].getValue();
+        totalWeight += lastWeight;
+        ret += last * lastWeight;
+        ret /= totalWeight;
+    } else
+        ret += (1 - totalWeight) * last;
+    setNormalization(1.0);
+    if(getCommonNorm())
+        for(auto *c : components) c->setNormalization(1.0 / ret);
+    return ret;
+}
+double AddPdf::calculateNLL() { // AddPdf.cu:187-204: extended term  N_exp - N log N_exp
+    double ret = GooPdf::calculateNLL();
+    if(extended) {
+        fptype expEvents = 0;
+        for(size_t i = 0; i < components.size(); ++i) expEvents += parametersList[i].getValue();
+        ret += (expEvents - numEvents * log(expEvents));
+    }
+    return ret;
+}
+
+// ---- ProdPdf (combine/ProdPdf.cu:30-99) ---------------------------------------------------------------------
+ProdPdf::ProdPdf(std::string n, std::vector<PdfBase *> comps)
+    : CombinePdf("ProdPdf", n) {
+    for(PdfBase *p : comps) {
+        if(p == nullptr) throw GeneralError("Invalid component");
+        components.push_back(p);
+    }
+    observablesList = getObservables();
+    registerConstant(components.size());
+    // the reference compares each component only with its predecessor (ProdPdf.cu:47-63)
+    std::vector<Observable> previous;
+    for(PdfBase *p : comps) {
+        if(varOverlaps) break;
+        for(Observable &o : p->getObservables())
+            if(std::find(previous.begin(), previous.end(), o) != previous.end()) {
+                varOverlaps = true;
+                break;
+            }
+        previous = p->getObservables();
+    }
+    if(varOverlaps)
+        for(PdfBase *p : comps)
+            if(p->getSeparateNorm()) varOverlaps = false;
+    registerFunction("ptr_to_ProdPdfs", GF_OP_PROD);
+}
+fptype ProdPdf::normalize() {
+    if(varOverlaps) { // shared observable: integrate the product numerically
+        recursiveSetNormalization(1.0);
+        return GooPdf::normalize();
+    }
+    for(PdfBase *c : components) c->normalize();
+    setNormalization(1.0);
+    return 1.0;
+}
+
+// ---- ConvolutionPdf (combine/ConvolutionPdf.cu:151-358) -----------------------------------------------------
+// The model and resolution sub-PDFs are emitted as auxiliary subtrees; per event the node is a single
+// gather from the per-offset table built by gf_conv_fill (see csrc/gf_conv.cu).
+ConvolutionPdf::ConvolutionPdf(std::string n, Observable x, GooPdf *m, GooPdf *r)
+    : CombinePdf("ConvolutionPdf", n, x)
+    , model(m)
+    , resolution(r) {
+    if(!m || !r) throw GeneralError("Invalid component");
+    components.push_back(model);
+    components.push_back(resolution);
+    registerConstant(-10);
+    registerConstant(10);
+    registerConstant(0.01);
+    registerFunction("ptr_to_ConvolvePdfs", GF_OP_CONVOLVE);
+}
+void ConvolutionPdf::setIntegrationConstants(fptype lo, fptype hi, fptype step) {
+    constantsList[0] = lo;
+    constantsList[1] = hi;
+    constantsList[2] = step;
+    workspacesFilled = false;
+    if(nodeIdx >= 0) { // already flattened: refresh the record and the device workspaces
+        Engine &E = Engine::get();
+        if(E.root) E.build(E.root);
+    }
+}
+void ConvolutionPdf::emitAux(detail::ProgramBuilder &B) {
+    model->emitAux(B);
+    resolution->emitAux(B);
+    model->emit(B);
+    resolution->emit(B);
+}
+int ConvolutionPdf::emit(detail::ProgramBuilder &B) {
+    int slot = B.allocAux();
+    return emitRecord(B, GF_OP_CONVOLVE, 0, 1, {slot, model->getFunctionIndex(), resolution->getFunctionIndex()});
+}
+void ConvolutionPdf::afterProgram() {
+    Observable dep = observablesList.front();
+    Engine &E      = Engine::get();
+    Engine::check(gf_conv_setup(E.ctx(), nodeIdx, constantsList[0], constantsList[1], constantsList[2], dep.getLowerLimit(),
+                                dep.getUpperLimit()),
+                  "gf_conv_setup");
+    workspacesFilled = false;
+}
+fptype ConvolutionPdf::normalize() { // ConvolutionPdf.cu:313-358
+    if(nodeIdx < 0) throw GeneralError("ConvolutionPdf {}: call setData() on the top-level PDF first", getName());
+    recursiveSetNormalization(1.0);
+    bool fm = !workspacesFilled || model->parametersChanged();
+    bool fr = !workspacesFilled || resolution->parametersChanged();
+    if(fm || fr) {
+        Engine &E = Engine::get();
+        E.sync();
+        Engine::check(gf_conv_fill(E.ctx(), nodeIdx, fm, fr), "gf_conv_fill");
+    }
+    workspacesFilled = true;
+    return GooPdf::normalize();
+}
+
+} // namespace GooFit

@@ -1,0 +1,365 @@
+// module.cpp — pybind11 module `_goofit` exposing the host API with the reference's Python names
+// (reference: python/goofit/{Variable,DataSet,UnbinnedDataSet,BinnedDataSet,PdfBase,FitManager,FitControl}.cpp,
+//  python/PDFs/GooPdf.cpp and one file per PDF under python/PDFs/). Only the classes on the north-star
+// path are bound.
+#include <pybind11/complex.h>
+#include <pybind11/functional.h>
+#include <pybind11/iostream.h>
+#include <pybind11/numpy.h>
+#include <pybind11/pybind11.h>
+#include <pybind11/stl.h>
+
+#include <Minuit2/FunctionMinimum.h>
+#include <Minuit2/MnUserParameterState.h>
+#include <goofit/detail/Fit.h>
+#include <goofit/detail/Physics3.h>
+
+namespace py = pybind11;
+using namespace pybind11::literals;
+using namespace GooFit;
+
+
+template <class DS>
+static DS *make_dataset(py::args args, py::kwargs kwargs) {
+    std::string name;
+    std::vector<Observable> vars;
+    for(auto arg : args) vars.push_back(arg.cast<Observable>());
+    if(kwargs.contains("name")) name = kwargs["name"].cast<std::string>();
+    return new DS(vars, name);
+}
+
+PYBIND11_MODULE(_goofit, m) {
+    m.doc() = "goofit_b200: B200-native GooFit likelihood engine (host API over hand-written sm_100a kernels)";
+    py::register_exception<GeneralError>(m, "GeneralError");
+
+    m.def("set_device", [](int dev) { detail::Engine::get().setDevice(dev); }, "device"_a);
+    m.def("set_shard", [](int rank, int size) { detail::Engine::get().setShard(rank, size); }, "rank"_a, "size"_a);
+    m.def("ctx_handle", [] { return reinterpret_cast<uintptr_t>(detail::Engine::get().ctx()); },
+          "raw gf_ctx* of the engine (for attaching an NCCL communicator through the C ABI)");
+    m.def("launch_count", [] { return gf_launch_count(detail::Engine::get().ctx()); });
+    m.def("last_kernel_ms", [] { return gf_last_kernel_ms(detail::Engine::get().ctx()); });
+    m.def("shutdown", [] { detail::Engine::get().shutdown(); });
+
+    // ---- variables ----
+    py::class_<Indexable>(m, "Indexable")
+        .def_property_readonly("name", &Indexable::getName)
+        .def_property("value", &Indexable::getValue, &Indexable::setValue)
+        .def_property("index", &Indexable::getIndex, &Indexable::setIndex)
+        .def_property("upperlimit", &Indexable::getUpperLimit, &Indexable::setUpperLimit)
+        .def_property("lowerlimit", &Indexable::getLowerLimit, &Indexable::setLowerLimit)
+        .def("getName", &Indexable::getName)
+        .def("getValue", &Indexable::getValue)
+        .def("setValue", &Indexable::setValue)
+        .def("getIndex", &Indexable::getIndex)
+        .def("getUpperLimit", &Indexable::getUpperLimit)
+        .def("getLowerLimit", &Indexable::getLowerLimit)
+        .def("__repr__", [](const Indexable &v) { return "<Indexable: " + v.getName() + ">"; })
+        .def("__bool__", &Indexable::inRange);
+    py::class_<Observable, Indexable>(m, "Observable")
+        .def(py::init<std::string, fptype, fptype>(), "name"_a, "min"_a, "max"_a)
+        .def_property("numbins", &Observable::getNumBins, &Observable::setNumBins)
+        .def("getNumBins", &Observable::getNumBins)
+        .def("setNumBins", &Observable::setNumBins)
+        .def("getBinSize", &Observable::getBinSize)
+        .def_property_readonly("bin_size", &Observable::getBinSize)
+        .def_property_readonly("bin_centers",
+                               [](const Observable &v) {
+                                   py::array_t<fptype> r(v.getNumBins());
+                                   for(size_t i = 0; i < v.getNumBins(); i++)
+                                       r.mutable_at(i) = v.getLowerLimit() + (i + 0.5) * v.getBinSize();
+                                   return r;
+                               })
+        .def("__repr__", [](const Observable &v) { return "<Observable: " + v.getName() + ">"; })
+        .def("__str__", [](const Observable &v) {
+            std::ostringstream o;
+            o << v;
+            return o.str();
+        });
+    py::class_<Variable, Indexable>(m, "Variable")
+        .def(py::init<std::string, fptype>(), "A constant variable", "name"_a, "value"_a)
+        .def(py::init<std::string, fptype, fptype>(), "name"_a, "value"_a, "error"_a)
+        .def(py::init<std::string, fptype, fptype, fptype>(), "name"_a, "value"_a, "min"_a, "max"_a)
+        .def(py::init<std::string, fptype, fptype, fptype, fptype, bool>(), "name"_a, "value"_a, "error"_a, "min"_a,
+             "max"_a, "fixed"_a = false)
+        .def_property("error", &Variable::getError, &Variable::setError)
+        .def_property("fixed", &Variable::IsFixed, &Variable::setFixed)
+        .def_property("fitter_index", &Variable::getFitterIndex, &Variable::setFitterIndex)
+        .def_property("changed", &Variable::getChanged, &Variable::setChanged)
+        .def("getError", &Variable::getError)
+        .def("setFixed", &Variable::setFixed)
+        .def("setBlind", &Variable::setBlind)
+        .def("__repr__", [](const Variable &v) { return "<Variable: " + v.getName() + ">"; })
+        .def("__str__", [](const Variable &v) {
+            std::ostringstream o;
+            o << v;
+            return o.str();
+        });
+    py::class_<EventNumber, Observable>(m, "EventNumber")
+        .def(py::init<std::string, fptype, fptype>(), "name"_a, "min"_a = 0, "max"_a = EventNumber::maxint)
+        .def_property_readonly_static("maxint", [](py::object) { return EventNumber::maxint; })
+        .def("__repr__", [](const EventNumber &v) { return "<EventNumber: " + v.getName() + ">"; });
+
+    // ---- datasets ----
+    py::class_<DataSet>(m, "DataSet")
+        .def("addEvent", (void (DataSet::*)()) & DataSet::addEvent)
+        .def("addWeightedEvent", &DataSet::addWeightedEvent)
+        .def("getNumEvents", &DataSet::getNumEvents)
+        .def("__len__", &DataSet::getNumEvents)
+        .def_property_readonly("name", &DataSet::getName)
+        .def_property_readonly("variables", &DataSet::getObservables)
+        .def("getObservables", &DataSet::getObservables);
+    auto to_numpy = [](const UnbinnedDataSet &d) {
+        size_t rows = d.getObservables().size(), cols = d.getNumEvents();
+        py::array_t<fptype> r({rows, cols});
+        for(size_t i = 0; i < rows; i++) std::copy(d.column(i).begin(), d.column(i).end(), r.mutable_data(i, 0));
+        return r;
+    };
+    auto from_numpy = [](UnbinnedDataSet &d, py::array_t<fptype, py::array::c_style | py::array::forcecast> a, bool filter) {
+        if(a.ndim() != 2) throw GeneralError("Expected a 2-D array (variables x events)");
+        size_t rows = a.shape(0), cols = a.shape(1), nobs = d.getObservables().size();
+        if(rows != nobs && rows + 1 != nobs)
+            throw GeneralError("The wrong number of rows, expected {}, but matrix had {}", nobs, rows);
+        if(!filter) { // bulk path: columns are appended without touching the Observables
+            std::vector<const fptype *> cp;
+            std::vector<fptype> idx;
+            for(size_t i = 0; i < rows; i++) cp.push_back(a.data(i, 0));
+            if(rows + 1 == nobs) {
+                idx.resize(cols);
+                for(size_t j = 0; j < cols; j++) idx[j] = (fptype)(d.getNumEvents() + j);
+                cp.push_back(idx.data());
+            }
+            for(size_t i = 0; i < nobs; i++) { // same range check as addEvent()
+                const Observable &o = d.getObservables()[i];
+                if(o.getLowerLimit() == o.getUpperLimit()) continue;
+                for(size_t j = 0; j < cols; j++)
+                    if(cp[i][j] > o.getUpperLimit() || cp[i][j] < o.getLowerLimit())
+                        throw OutOfRange(o.getName(), cp[i][j], o.getLowerLimit(), o.getUpperLimit());
+            }
+            d.appendColumns(cp, cols);
+            return;
+        }
+        struct View {
+            const py::array_t<fptype, py::array::c_style | py::array::forcecast> &a;
+            size_t rows() const { return a.shape(0); }
+            size_t cols() const { return a.shape(1); }
+            fptype operator()(size_t i, size_t j) const { return a.at(i, j); }
+        } v{a};
+        d.from_matrix(v, true);
+    };
+    py::class_<UnbinnedDataSet, DataSet>(m, "UnbinnedDataSet")
+        .def(py::init(&make_dataset<UnbinnedDataSet>),
+             "Takes an unlimited number of Observerables, use 'name=' to set a name if desired")
+        .def("__getitem__", [to_numpy](const UnbinnedDataSet &d, py::object idx) { return py::object(to_numpy(d)).attr("__getitem__")(idx); })
+        .def("from_numpy", from_numpy, "array"_a, "filter"_a = false)
+        .def("from_matrix", from_numpy, "matrix"_a, "filter"_a = false)
+        .def("to_numpy", to_numpy)
+        .def("to_matrix", to_numpy)
+        .def("loadEvent", &UnbinnedDataSet::loadEvent, "event_number"_a)
+        .def("clear", &UnbinnedDataSet::clear)
+        .def("fillWithGrid", &UnbinnedDataSet::fillWithGrid)
+        .def("setValueForAllEvents", &UnbinnedDataSet::setValueForAllEvents, "var"_a)
+        .def("getValue", &UnbinnedDataSet::getValue, "var"_a, "idx"_a);
+    py::class_<BinnedDataSet, DataSet>(m, "BinnedDataSet")
+        .def(py::init(&make_dataset<BinnedDataSet>))
+        .def("getBinCenter", (fptype(BinnedDataSet::*)(size_t, size_t) const) & BinnedDataSet::getBinCenter)
+        .def("getBinContent", &BinnedDataSet::getBinContent, "bin"_a)
+        .def("setBinContent", &BinnedDataSet::setBinContent, "bin"_a, "value"_a)
+        .def("getBinError", &BinnedDataSet::getBinError, "bin"_a)
+        .def("setBinError", &BinnedDataSet::setBinError, "bin"_a, "value"_a)
+        .def("getBinSize", &BinnedDataSet::getBinSize, "ivar"_a)
+        .def("getBinVolume", &BinnedDataSet::getBinVolume, "bin"_a)
+        .def("getNumBins", &BinnedDataSet::getNumBins)
+        .def("getNumWeightedEvents", &BinnedDataSet::getNumWeightedEvents);
+
+    // ---- fit control ----
+    py::enum_<EvalFunc>(m, "EvalFunc")
+        .value("Eval", EvalFunc::Eval).value("NLL", EvalFunc::NLL).value("Prob", EvalFunc::Prob)
+        .value("BinAvg", EvalFunc::BinAvg).value("BinWithError", EvalFunc::BinWithError).value("Chisq", EvalFunc::Chisq);
+    py::class_<FitControl, std::shared_ptr<FitControl>>(m, "FitControl")
+        .def("binnedFit", &FitControl::binnedFit)
+        .def("binErrors", &FitControl::binErrors)
+        .def("metricIsPdf", &FitControl::metricIsPdf)
+        .def("getMetric", &FitControl::getMetric)
+        .def("getName", &FitControl::getName);
+    py::class_<UnbinnedNllFit, FitControl, std::shared_ptr<UnbinnedNllFit>>(m, "UnbinnedNllFit").def(py::init<>());
+    py::class_<BinnedNllFit, FitControl, std::shared_ptr<BinnedNllFit>>(m, "BinnedNllFit").def(py::init<>());
+    py::class_<BinnedErrorFit, FitControl, std::shared_ptr<BinnedErrorFit>>(m, "BinnedErrorFit").def(py::init<>());
+    py::class_<BinnedChisqFit, FitControl, std::shared_ptr<BinnedChisqFit>>(m, "BinnedChisqFit").def(py::init<>());
+    py::class_<ProbFit, FitControl, std::shared_ptr<ProbFit>>(m, "ProbFit").def(py::init<>());
+    py::class_<EvalFit, FitControl, std::shared_ptr<EvalFit>>(m, "EvalFit").def(py::init<>());
+
+    // ---- PDFs ----
+    py::class_<PdfBase>(m, "PdfBase")
+        .def("setData", &PdfBase::setData, "ptr"_a = nullptr, py::keep_alive<1, 2>())
+        .def("getData", &PdfBase::getData, py::return_value_policy::reference)
+        .def("getName", &PdfBase::getName)
+        .def("getPdfName", &PdfBase::getPdfName)
+        .def("getParameters", &PdfBase::getParameters)
+        .def("getParameterByName", &PdfBase::getParameterByName, py::return_value_policy::reference_internal)
+        .def("getObservables", &PdfBase::getObservables)
+        .def("getFunctionIndex", &PdfBase::getFunctionIndex)
+        .def("getNormalization", &PdfBase::getNormalization)
+        .def("parametersChanged", &PdfBase::parametersChanged)
+        .def("updateVariable", &PdfBase::updateVariable)
+        .def("updateParameters", &PdfBase::updateParameters)
+        .def("setIntegrationFineness", &PdfBase::setIntegrationFineness)
+        .def("setCommonNorm", &PdfBase::setCommonNorm, "v"_a = true)
+        .def("__str__", [](const PdfBase &p) {
+            std::ostringstream o;
+            o << p;
+            return o.str();
+        })
+        .def("fillMCDataSimple", &PdfBase::fillMCDataSimple, "events"_a, "seed"_a = 0)
+        .def("fitTo", &PdfBase::fitTo, "data"_a, "verbosity"_a = 3, py::call_guard<py::scoped_ostream_redirect>())
+        .def("fit", &PdfBase::fit, "verbosity"_a = 3, py::call_guard<py::scoped_ostream_redirect>());
+    py::class_<GooPdf, PdfBase>(m, "GooPdf")
+        .def("get_bin_grid_size", &GooPdf::get_bin_grid_size)
+        .def("get_bin_grid_volume", &GooPdf::get_bin_grid_volume)
+        .def("reduce_with_bins", &GooPdf::reduce_with_bins)
+        .def("reduce_with_metric", &GooPdf::reduce_with_metric)
+        .def("evaluate_with_metric", [](GooPdf &p) { return py::array(py::cast(p.evaluate_with_metric())); })
+        .def("normalize", &GooPdf::normalize)
+        .def("normalise", &GooPdf::normalize)
+        .def("integrate", &GooPdf::integrate, "lo"_a, "hi"_a)
+        .def("copyParams", &GooPdf::copyParams)
+        .def("makeGrid", &GooPdf::makeGrid)
+        .def("evaluateAtPoints", &GooPdf::evaluateAtPoints)
+        .def("evaluatePdf", &GooPdf::evaluateAtPoints)
+        .def("getValue", &GooPdf::getValue, "evalfunc"_a = EvalFunc::Eval)
+        .def("setParameterConstantness", &GooPdf::setParameterConstantness, "constant"_a = true)
+        .def("hasAnalyticIntegral", &GooPdf::hasAnalyticIntegral)
+        .def("calculateNLL", &GooPdf::calculateNLL)
+        .def("scan",
+             [](GooPdf &p, Observable v) {
+                 std::vector<fptype> out;
+                 p.scan(v, out);
+                 return out;
+             })
+        .def("setFitControl", &GooPdf::setFitControl, "fit_control"_a)
+        .def("getCompProbsAtDataPoints", &GooPdf::getCompProbsAtDataPoints);
+
+    py::class_<ExpPdf, GooPdf>(m, "ExpPdf")
+        .def(py::init<std::string, Observable, Variable>(), "name"_a, "x"_a, "alpha"_a, py::keep_alive<1, 3>(), py::keep_alive<1, 4>())
+        .def(py::init<std::string, Observable, Variable, Variable>(), "name"_a, "x"_a, "alpha"_a, "offset"_a)
+        .def(py::init([](std::string n, Observable x, std::vector<Variable> w) { return new ExpPdf(n, x, w); }), "name"_a, "x"_a, "weights"_a)
+        .def(py::init([](std::string n, Observable x, std::vector<Variable> w, Variable off) { return new ExpPdf(n, x, w, off); }), "name"_a, "x"_a, "weights"_a, "offset"_a);
+    py::class_<GaussianPdf, GooPdf>(m, "GaussianPdf")
+        .def(py::init<std::string, Observable, Variable, Variable>(), "name"_a, "x"_a, "mean"_a, "sigma"_a);
+    py::class_<PolynomialPdf, GooPdf>(m, "PolynomialPdf")
+        .def(py::init<std::string, Observable, std::vector<Variable>, unsigned int>(), "name"_a, "x"_a, "weights"_a, "lowestDegree"_a = 0)
+        .def(py::init<std::string, Observable, std::vector<Variable>, Variable, unsigned int>(), "name"_a, "x"_a, "weights"_a, "x0"_a, "lowestDegree"_a = 0)
+        .def(py::init<std::string, std::vector<Observable>, std::vector<Variable>, std::vector<Variable>, unsigned int>(),
+             "name"_a, "obses"_a, "coeffs"_a, "offsets"_a, "maxDegree"_a = 0)
+        .def("getCoefficient", &PolynomialPdf::getCoefficient);
+    py::class_<ArgusPdf, GooPdf>(m, "ArgusPdf")
+        .def(py::init<std::string, Observable, Variable, Variable, bool>(), "name"_a, "x"_a, "m"_a, "s"_a, "upper"_a)
+        .def(py::init<std::string, Observable, Variable, Variable, bool, Variable>(), "name"_a, "x"_a, "m"_a, "s"_a, "upper"_a, "power"_a);
+    py::class_<KinLimitBWPdf, GooPdf>(m, "KinLimitBWPdf")
+        .def(py::init<std::string, Observable, Variable, Variable>(), "name"_a, "x"_a, "m"_a, "s"_a)
+        .def("setMasses", &KinLimitBWPdf::setMasses, "bigM"_a, "smallM"_a);
+    py::class_<ScaledGaussianPdf, GooPdf>(m, "ScaledGaussianPdf")
+        .def(py::init<std::string, Observable, Variable, Variable, Variable, Variable>(), "name"_a, "x"_a, "m"_a, "s"_a, "d"_a, "e"_a);
+    py::class_<JohnsonSUPdf, GooPdf>(m, "JohnsonSUPdf")
+        .def(py::init<std::string, Observable, Variable, Variable, Variable, Variable>(), "name"_a, "x"_a, "m"_a, "s"_a, "g"_a, "d"_a);
+    py::class_<CombinePdf, GooPdf>(m, "CombinePdf");
+    py::class_<AddPdf, CombinePdf>(m, "AddPdf")
+        .def(py::init<std::string, std::vector<Variable>, std::vector<PdfBase *>>(), "name"_a, "weights"_a, "comps"_a, py::keep_alive<1, 4>())
+        .def(py::init<std::string, Variable, PdfBase *, PdfBase *>(), "name"_a, "frac1"_a, "func1"_a, "func2"_a, py::keep_alive<1, 4>(), py::keep_alive<1, 5>());
+    py::class_<ProdPdf, CombinePdf>(m, "ProdPdf")
+        .def(py::init<std::string, std::vector<PdfBase *>>(), "name"_a, "comps"_a, py::keep_alive<1, 3>());
+    py::class_<ConvolutionPdf, CombinePdf>(m, "ConvolutionPdf")
+        .def(py::init<std::string, Observable, GooPdf *, GooPdf *>(), "name"_a, "x"_a, "model"_a, "resolution"_a, py::keep_alive<1, 4>(), py::keep_alive<1, 5>())
+        .def("setIntegrationConstants", &ConvolutionPdf::setIntegrationConstants, "lo"_a, "hi"_a, "step"_a);
+
+    // ---- three-body amplitude ----
+    py::enum_<DaughterPair>(m, "DaughterPair")
+        .value("PAIR_12", PAIR_12).value("PAIR_13", PAIR_13).value("PAIR_23", PAIR_23).export_values();
+    m.def("inDalitz", &inDalitz, "m12"_a, "m13"_a, "bigM"_a, "dm1"_a, "dm2"_a, "dm3"_a);
+    py::class_<ResonancePdf, GooPdf>(m, "ResonancePdf")
+        .def("get_amp_real", &ResonancePdf::get_amp_real)
+        .def("get_amp_img", &ResonancePdf::get_amp_img);
+    auto mres = m.def_submodule("Resonances");
+    py::class_<Resonances::RBW, ResonancePdf>(mres, "RBW")
+        .def(py::init<std::string, Variable, Variable, Variable, Variable, unsigned int, unsigned int, bool, bool>(),
+             "name"_a, "ar"_a, "ai"_a, "mass"_a, "width"_a, "sp"_a, "cyc"_a, "norm"_a = true, "sym"_a = false);
+    py::class_<Resonances::GS, ResonancePdf>(mres, "GS")
+        .def(py::init<std::string, Variable, Variable, Variable, Variable, unsigned int, unsigned int, bool, bool>(),
+             "name"_a, "ar"_a, "ai"_a, "mass"_a, "width"_a, "sp"_a, "cyc"_a, "norm"_a = true, "sym"_a = false);
+    py::class_<Resonances::NonRes, ResonancePdf>(mres, "NonRes")
+        .def(py::init<std::string, Variable, Variable>(), "name"_a, "ar"_a, "ai"_a);
+    py::class_<Resonances::Gauss, ResonancePdf>(mres, "Gauss")
+        .def(py::init<std::string, Variable, Variable, Variable, Variable, unsigned int>(), "name"_a, "ar"_a, "ai"_a, "mean"_a, "sigma"_a, "cyc"_a);
+    py::class_<DecayInfo3>(m, "DecayInfo3")
+        .def(py::init<>())
+        .def_readwrite("motherMass", &DecayInfo3::motherMass)
+        .def_readwrite("daug1Mass", &DecayInfo3::daug1Mass)
+        .def_readwrite("daug2Mass", &DecayInfo3::daug2Mass)
+        .def_readwrite("daug3Mass", &DecayInfo3::daug3Mass)
+        .def_readwrite("meson_radius", &DecayInfo3::meson_radius)
+        .def_readwrite("mother_meson_radius", &DecayInfo3::mother_meson_radius)
+        .def_readwrite("resonances", &DecayInfo3::resonances)
+        .def("add_resonance", [](DecayInfo3 &d, ResonancePdf *r) { d.resonances.push_back(r); }, py::keep_alive<1, 2>());
+    py::class_<Amp3BodyBase, GooPdf>(m, "Amp3BodyBase");
+    py::class_<Amp3Body, Amp3BodyBase>(m, "Amp3Body")
+        .def(py::init<std::string, Observable, Observable, EventNumber, DecayInfo3, GooPdf *>(), "name"_a, "m12"_a, "m13"_a,
+             "eventNumber"_a, "decay"_a, "eff"_a, py::keep_alive<1, 6>(), py::keep_alive<1, 7>())
+        .def("setDataSize", &Amp3Body::setDataSize, "dataSize"_a, "evtSize"_a = 3, "offset"_a = 0)
+        .def("setForceIntegrals", &Amp3Body::setForceIntegrals, "f"_a = true)
+        .def("getCachedWave", [](const Amp3Body &a, size_t i) { return py::array(py::cast(a.getCachedWave(i))); }, "i"_a)
+        .def("sumCachedWave", &Amp3Body::sumCachedWave, "i"_a)
+        .def("getIntegrals", [](const Amp3Body &a) { return py::array(py::cast(a.getIntegrals())); })
+        .def("fit_fractions", &Amp3Body::fit_fractions)
+        .def("getDecayInfo", &Amp3Body::getDecayInfo, py::return_value_policy::reference_internal);
+    py::class_<DalitzPlotter>(m, "DalitzPlotter")
+        .def(py::init<GooPdf *, Amp3Body *>(), "overallSignal"_a, "signalDalitz"_a, py::keep_alive<1, 2>(), py::keep_alive<1, 3>())
+        .def("fillDataSetMC", &DalitzPlotter::fillDataSetMC, "dataset"_a, "nTotal"_a, "seed"_a = 0)
+        .def("getNumEvents", &DalitzPlotter::getNumEvents)
+        .def("getX", &DalitzPlotter::getX)
+        .def("getY", &DalitzPlotter::getY)
+        .def("getXval", &DalitzPlotter::getXval)
+        .def("getYval", &DalitzPlotter::getYval)
+        .def("getZval", &DalitzPlotter::getZval)
+        .def("getVal", &DalitzPlotter::getVal, "event"_a, "num"_a = 0);
+
+    // ---- fitting ----
+    py::class_<Minuit2::FunctionMinimum>(m, "FunctionMinimum")
+        .def("Fval", &Minuit2::FunctionMinimum::Fval)
+        .def("Edm", &Minuit2::FunctionMinimum::Edm)
+        .def("NFcn", &Minuit2::FunctionMinimum::NFcn)
+        .def("IsValid", &Minuit2::FunctionMinimum::IsValid)
+        .def("HasCovariance", &Minuit2::FunctionMinimum::HasCovariance)
+        .def("HasValidCovariance", &Minuit2::FunctionMinimum::HasValidCovariance)
+        .def("HasAccurateCovar", &Minuit2::FunctionMinimum::HasAccurateCovar)
+        .def("HasReachedCallLimit", &Minuit2::FunctionMinimum::HasReachedCallLimit)
+        .def("IsAboveMaxEdm", &Minuit2::FunctionMinimum::IsAboveMaxEdm)
+        .def("values", [](const Minuit2::FunctionMinimum &f) { return f.UserState().Params(); })
+        .def("errors", [](const Minuit2::FunctionMinimum &f) { return f.UserState().Errors(); });
+    py::class_<Params>(m, "Params")
+        .def(py::init<PdfBase &>(), "pdf"_a, py::keep_alive<1, 2>())
+        .def("size", &Params::size)
+        .def("GetGooFitParams", &Params::GetGooFitParams)
+        .def("make_minuit_vector", &Params::make_minuit_vector)
+        .def("from_minuit_vector", &Params::from_minuit_vector, "values"_a, "force_changed"_a = false)
+        .def("set_record", &Params::set_record, "do_record"_a = true)
+        .def("get_recorded", &Params::get_recorded);
+    py::class_<FCN>(m, "FCN")
+        .def(py::init<Params &>(), "params"_a, py::keep_alive<1, 2>())
+        .def("__call__", (double (FCN::*)(const std::vector<double> &) const) & FCN::operator())
+        .def("__call__", (double (FCN::*)() const) & FCN::operator())
+        .def("Up", &FCN::Up);
+    py::class_<FitManagerMinuit2>(m, "FitManager")
+        .def(py::init<PdfBase *>(), py::keep_alive<1, 2>())
+        .def("fit", &FitManagerMinuit2::fit, py::call_guard<py::scoped_ostream_redirect>())
+        .def("getParams", &FitManagerMinuit2::getParams, py::return_value_policy::reference_internal)
+        .def("getFCN", &FitManagerMinuit2::getFCN, py::return_value_policy::reference_internal)
+        .def("getMinosErrors", &FitManagerMinuit2::getMinosErrors)
+        .def("setMaxCalls", &FitManagerMinuit2::setMaxCalls)
+        .def("setVerbosity", &FitManagerMinuit2::setVerbosity)
+        .def("getVerbosity", &FitManagerMinuit2::getVerbosity)
+        .def("setMinos", &FitManagerMinuit2::setMinos, "minos_flag"_a = true)
+        .def("setStrategy", &FitManagerMinuit2::setStrategy)
+        .def("lastFitSeconds", &FitManagerMinuit2::lastFitSeconds)
+        .def("lastFitCalls", &FitManagerMinuit2::lastFitCalls)
+        .def("__int__", &FitManagerMinuit2::operator int)
+        .def("__bool__", &FitManagerMinuit2::operator bool);
+}

@@ -94,6 +94,9 @@ int gf_device_info(gf_ctx *, int *sm_count, size_t *free_bytes, size_t *total_by
 
 int gf_set_program(gf_ctx *, const gf_node *nodes, int n_nodes, const double *consts, int n_consts,
                    const int32_t *ints, int n_ints, int n_params, int n_norms);
+/* Drop every per-node device cache (Amp3Body/Amp4Body caches, convolution workspaces) and clear the aux
+ * table; called by the host layer before a re-flattened program is installed. */
+int gf_reset_aux(gf_ctx *);
 int gf_set_params(gf_ctx *, const double *params, int n);
 int gf_set_norms(gf_ctx *, const double *norms, int n);
 

@@ -1,0 +1,118 @@
+"""Model builders shared by the tests, bench.py and smoke(): the same trees oracle/ref_driver.cpp builds
+with the reference's classes (examples/dalitz/dalitz.cpp:124-322 etc.), here with goofit_b200's."""
+import numpy as np
+
+import goofit_b200 as gf
+
+MD0 = 1.86484
+MD02 = MD0 * MD0
+MD02INV = 1.0 / MD02
+PIP = 0.13957018
+PI0 = 0.1349766
+
+
+class Keep:
+    """Holds Python references so C++ objects referenced by raw pointer stay alive."""
+
+    def __init__(self):
+        self.objs = []
+
+    def __call__(self, o):
+        self.objs.append(o)
+        return o
+
+
+def dataset_from_columns(observables, columns):
+    d = gf.UnbinnedDataSet(*observables)
+    d.from_matrix(np.ascontiguousarray(np.vstack([np.asarray(c, dtype=np.float64) for c in columns])))
+    return d
+
+
+class Dalitz:
+    """D0 -> pi+ pi- pi0, 16 resonances (15 RBW + NonRes), constant efficiency."""
+
+    def __init__(self, float_masses=False, grid=240):
+        k = self.keep = Keep()
+        self.m12 = gf.Observable("m12", 0, 3)
+        self.m13 = gf.Observable("m13", 0, 3)
+        self.evt = gf.EventNumber("eventNumber")
+        self.m12.numbins = grid
+        self.m13.numbins = grid
+        d = self.info = gf.DecayInfo3()
+        d.motherMass, d.daug1Mass, d.daug2Mass, d.daug3Mass = MD0, PI0, PIP, PIP
+        d.meson_radius, d.mother_meson_radius = 1.5, 5.0
+        V = gf.Variable
+        rhoM, rhoW = V("rho_mass", 0.7758, 0.01, 0.7, 0.8), V("rho_width", 0.1503, 0.01, 0.1, 0.2)
+        m1450, w1450 = V("rhop_1450_mass", 1.465, 0.01, 1.0, 2.0), V("rhop_1450_width", 0.400, 0.01, 0.01, 5.0)
+        m1700, w1700 = V("rhop_1700_mass", 1.720, 0.01, 1.6, 1.9), V("rhop_1700_width", 0.250, 0.01, 0.1, 1.0)
+        P12, P13, P23 = 0, 1, 2
+        rs = [
+            ("rhop", 1, 0, rhoM, rhoW, 1, P12),
+            ("rho0", 0.565, 0.164, rhoM, rhoW, 1, P23),
+            ("rhom", 0.714, -0.025, rhoM, rhoW, 1, P13),
+            ("rhop_1450", -0.174, -0.117, m1450, w1450, 1, P12),
+            ("rho0_1450", 0.325, 0.057, m1450, w1450, 1, P23),
+            ("rhom_1450", 0.788, 0.226, m1450, w1450, 1, P13),
+            ("rhop_1700", 2.151, -0.658, m1700, w1700, 1, P12),
+            ("rho0_1700", 2.400, -0.734, m1700, w1700, 1, P23),
+            ("rhom_1700", 1.286, -1.532, m1700, w1700, 1, P13),
+            ("f0_980", 0.008 * (-MD02), -0.013 * (-MD02), V("f0_980_mass", 0.980, 0.01, 0.8, 1.2), V("f0_980_width", 0.044, 0.001, 0.001, 0.08), 0, P23),
+            ("f0_1370", -0.058 * (-MD02), 0.026 * (-MD02), V("f0_1370_mass", 1.434, 0.01, 1.2, 1.6), V("f0_1370_width", 0.173, 0.01, 0.01, 0.4), 0, P23),
+            ("f0_1500", 0.057 * (-MD02), 0.012 * (-MD02), V("f0_1500_mass", 1.507, 0.01, 1.3, 1.7), V("f0_1500_width", 0.109, 0.01, 0.01, 0.3), 0, P23),
+            ("f0_1710", 0.070 * (-MD02), 0.087 * (-MD02), V("f0_1710_mass", 1.714, 0.01, 1.5, 2.9), V("f0_1710_width", 0.140, 0.01, 0.01, 0.5), 0, P23),
+            ("f2_1270", -1.027 * (-MD02INV), -0.162 * (-MD02INV), V("f2_1270_mass", 1.2754, 0.01, 1.0, 1.5), V("f2_1270_width", 0.1851, 0.01, 0.01, 0.4), 2, P23),
+            ("f0_600", 0.068 * (-MD02), 0.010 * (-MD02), V("f0_600_mass", 0.500, 0.01, 0.3, 0.7), V("f0_600_width", 0.400, 0.01, 0.2, 0.6), 0, P23),
+        ]
+        self.coefs, self.masses, self.widths, self.resonances = [], [], [], []
+        nre, nim = V("nonr_amp_real", -0.5595, 0.001, 0, 0), V("nonr_amp_imag", 0.108761, 0.1, 0, 0)
+        self.coefs += [nre, nim]
+        self.resonances.append(k(gf.Resonances.NonRes("nonr", nre, nim)))
+        for i, (n, re, im, m, w, spin, cyc) in enumerate(rs):
+            vre = V(n + "_amp_real", re) if i == 0 else V(n + "_amp_real", re, 0.001, 0, 0)
+            vim = V(n + "_amp_imag", im) if i == 0 else V(n + "_amp_imag", im, 0.1, 0, 0)
+            self.coefs += [vre, vim]
+            self.masses.append(m)
+            self.widths.append(w)
+            self.resonances.append(k(gf.Resonances.RBW(n, vre, vim, m, w, spin, cyc)))
+        if not float_masses:
+            for r in self.resonances:
+                r.setParameterConstantness(True)
+        for r in self.resonances:
+            d.add_resonance(r)
+        one, zero = V("constantOne", 1), V("constantZero", 0)
+        self.eff = k(gf.PolynomialPdf("constantEff", [self.m12, self.m13], [one], [zero, zero], 0))
+        self.signal = gf.Amp3Body("signalPDF", self.m12, self.m13, self.evt, d, self.eff)
+
+    def dataset(self, m12, m13):
+        n = len(m12)
+        return dataset_from_columns([self.m12, self.m13, self.evt], [m12, m13, np.arange(n, dtype=np.float64)])
+
+
+def in_dalitz(m12, m13):
+    """vectorised Dalitz boundary for the D0 -> pi0 pi+ pi+ kinematics above (DalitzPlotHelpers.cu:14-59)"""
+    bigM, dm1, dm2, dm3 = MD0, PI0, PIP, PIP
+    m23 = bigM * bigM + dm1 * dm1 + dm2 * dm2 + dm3 * dm3 - m12 - m13
+    ok = (m23 >= 0) & (m23 <= (bigM - dm1) ** 2) & (m12 >= (dm1 + dm2) ** 2) & (m12 <= (bigM - dm3) ** 2)
+    with np.errstate(invalid="ignore", divide="ignore"):
+        s = np.sqrt(m12)
+        e1 = 0.5 * (m12 - dm2 * dm2 + dm1 * dm1) / s
+        e3 = 0.5 * (bigM * bigM - m12 - dm3 * dm3) / s
+        r1 = np.sqrt(e1 * e1 - dm1 * dm1)
+        r3 = np.sqrt(e3 * e3 - dm3 * dm3)
+        es = (e1 + e3) ** 2
+        ok &= (m13 >= es - (r1 + r3) ** 2) & (m13 <= es - (r1 - r3) ** 2)
+    return ok
+
+
+def dalitz_uniform_events(n, seed):
+    """n points uniform inside the Dalitz boundary (numpy Generator; synthetic bench/test input)"""
+    rng = np.random.default_rng(seed)
+    a = np.empty(0)
+    b = np.empty(0)
+    while len(a) < n:
+        x = rng.uniform(0, 3, size=int((n - len(a)) * 3.2) + 1024)
+        y = rng.uniform(0, 3, size=len(x))
+        ok = in_dalitz(x, y)
+        a = np.concatenate([a, x[ok]])
+        b = np.concatenate([b, y[ok]])
+    return np.ascontiguousarray(a[:n]), np.ascontiguousarray(b[:n])
