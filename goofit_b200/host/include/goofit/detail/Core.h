@@ -519,6 +519,9 @@ class PdfBase {
     }
     void recursiveSetNormalization(fptype norm = 1.0, bool subpdf = false);
     void initialize() {}
+    /// value of parameter i as last pushed by updateParameters() — the reference reads host_parameters[parametersIdx+i+1]
+    /// (not the Variable) in integrate()/normalize(), which matters after a fit has rewritten the Variables
+    fptype par(size_t i) const;
 
     int emitRecord(detail::ProgramBuilder &B, int op, int nchild, int size, const std::vector<int32_t> &extraInts);
 

@@ -141,9 +141,9 @@ fptype Amp3Body::normalize() { // Amp3Body.cu:238-359
     }
     fpcomplex sumIntegral(0, 0);
     for(size_t i = 0; i < nres; ++i) {
-        fpcomplex amplitude_i(parametersList[2 * i].getValue(), parametersList[2 * i + 1].getValue());
+        fpcomplex amplitude_i(par(2 * i), par(2 * i + 1));
         for(size_t j = 0; j < nres; ++j) {
-            fpcomplex amplitude_j(parametersList[2 * j].getValue(), -parametersList[2 * j + 1].getValue());
+            fpcomplex amplitude_j(par(2 * j), -par(2 * j + 1));
             sumIntegral += amplitude_i * amplitude_j * integrals[i * nres + j];
         }
     }

@@ -363,6 +363,10 @@ void PdfBase::updateParameters() { // PdfBase.cu:131-140; one upload per call in
     for(auto *c : components) c->updateParameters();
     E.paramsDirty = true;
 }
+fptype PdfBase::par(size_t i) const {
+    if(nodeIdx >= 0 && !parOffs.empty()) return Engine::get().prog.params[parOffs.back() + i];
+    return parametersList.at(i).getValue();
+}
 void PdfBase::setNormalization(const fptype &v) {
     cachedNormalization = v;
     if(normSlot >= 0) {

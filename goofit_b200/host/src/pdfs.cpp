@@ -27,7 +27,7 @@ ExpPdf::ExpPdf(std::string n, Observable _x, std::vector<Variable> &weights, Var
     registerFunction("ptr_to_ExpPolyOffset", GF_OP_EXP_POLY_OFFSET);
 }
 fptype ExpPdf::integrate(fptype lo, fptype hi) const {
-    fptype alpha = parametersList[0].getValue();
+    fptype alpha = par(0);
     if(0 == alpha) return hi - lo;
     fptype ret = exp(alpha * hi) - exp(alpha * lo);
     ret /= alpha;
@@ -42,7 +42,7 @@ GaussianPdf::GaussianPdf(std::string n, Observable _x, Variable mean, Variable s
 fptype GaussianPdf::integrate(fptype, fptype) const {
     static const fptype rootPi = sqrt(atan2(0.0, -1.0));
     static const fptype root2  = sqrt(2.0);
-    fptype sigma = parametersList[1].getValue();
+    fptype sigma = par(1);
     sigma *= root2 * rootPi;
     return sigma;
 }

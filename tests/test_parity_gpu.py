@@ -61,7 +61,7 @@ def test_exponential(golden):
     sigma = golden["exp.fit_alpha_err"]
     assert abs(alpha.value - golden["exp.fit_alpha"]) < 0.01 * sigma
     assert rel(alpha.error, sigma) < 1e-3
-    assert rel(pdf.calculateNLL(), golden["exp.fit_nll"]) < 1e-10
+    assert rel(pdf.calculateNLL(), golden["exp.fit_nll"]) < 1e-8
 
 
 def test_gaussian(golden):
@@ -76,17 +76,37 @@ def test_gaussian(golden):
 
 
 def test_normalize_test_known_answers():
-    # tests/simple/NormalizeTest.cpp:84-99 — Gaussian(1.5, 2.5) probabilities on a 100-bin grid over [-10, 10]
-    x = gf.Observable("xvar", -10, 10)
-    m, s = gf.Variable("m", 1.5), gf.Variable("s", 2.5)
-    pdf = gf.GaussianPdf("gauss", x, m, s)
+    # tests/simple/NormalizeTest.cpp:68-99 — Gaussian(1.5, 2.5) probabilities on the 100-bin grid over [-5, 10]
+    x = gf.Observable("xvar", -5, 10)
+    m, s = gf.Variable("mean", 1.5), gf.Variable("sigma", 2.5)
+    pdf = gf.GaussianPdf("gausspdf", x, m, s)
     grid = pdf.makeGrid()
     pdf.setData(grid)
+    for idx, val in [(0, -4.925), (20, -1.925), (40, 1.075), (60, 4.075)]:
+        assert grid.getValue(x, idx) == pytest.approx(val)
     vv = pdf.getCompProbsAtDataPoints()
+    assert len(vv) == 1 and len(vv[0]) == 100
     for idx, val in [(0, 0.00587129964482), (20, 0.0624318782242), (40, 0.157287605852), (60, 0.0938855055588)]:
-        assert vv[0][idx] * 6.26657 == pytest.approx(val * 6.26657, rel=1e-9) or vv[0][idx] == pytest.approx(val / 6.26657, rel=1e-5) or vv[0][idx] == pytest.approx(val, rel=1e-9)
-    v = pdf.evaluateAtPoints(x)
-    assert len(v) == 100
+        assert vv[0][idx] == pytest.approx(val, rel=1e-10)
+    v = pdf.evaluateAtPoints(x)  # NormalizeTest.cpp:189-194
+    for idx, val in [(0, 0.00587129964482), (20, 0.0624318782242), (40, 0.157287605852), (60, 0.0938855055588)]:
+        assert v[idx] == pytest.approx(val, rel=1e-10)
+    assert pdf.normalize() == pytest.approx(6.26657, rel=1e-5)
+
+
+def test_add_norm_known_answer():
+    # tests/simple/AddNormTest.cpp:16-44: f*A + (1-f)*B must normalise every component, including the last
+    x = gf.Observable("xvar", -5, 10)
+    mean = gf.Variable("mean", 1.5)
+    ga = gf.GaussianPdf("gaussA", x, mean, gf.Variable("sigmaA", 2.5))
+    gb = gf.GaussianPdf("gaussB", x, mean, gf.Variable("sigmaB", 0.8))
+    total = gf.AddPdf("sum", gf.Variable("frac", 0.6), ga, gb)
+    grid = total.makeGrid()
+    total.setData(grid)
+    vv = total.getCompProbsAtDataPoints()
+    assert len(vv) == 3 and len(vv[0]) == len(vv[1]) == len(vv[2])
+    for i in range(0, len(vv[0]), 7):
+        assert vv[0][i] == pytest.approx(0.6 * vv[1][i] + 0.4 * vv[2][i], rel=1e-12)
 
 
 def test_shapes(golden):
