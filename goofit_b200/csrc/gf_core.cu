@@ -6,6 +6,7 @@
 #include "gf_internal.cuh"
 #include <algorithm>
 #include <cmath>
+#include <dlfcn.h>
 
 static thread_local std::string g_err;
 void gf_set_error(const std::string &s) { g_err = s; }
@@ -33,6 +34,38 @@ int gf_alloc_aux_slot(gf_ctx *c) {
             return i;
         }
     return -1;
+}
+
+// ---- NCCL through dlopen: the library keeps no link-time dependency on it ---------------------------------
+struct gf_nccl_uid { char internal[128]; };
+namespace {
+typedef int (*nccl_get_uid_t)(void *);
+typedef int (*nccl_init_rank_t)(void **, int, gf_nccl_uid, int);
+typedef int (*nccl_allreduce_t)(const void *, void *, size_t, int, int, void *, cudaStream_t);
+typedef int (*nccl_destroy_t)(void *);
+typedef const char *(*nccl_errstr_t)(int);
+}
+static void *g_nccl = nullptr;
+static nccl_get_uid_t p_uid = nullptr;
+static nccl_init_rank_t p_init = nullptr;
+static nccl_allreduce_t p_allreduce = nullptr;
+static nccl_destroy_t p_destroy = nullptr;
+static nccl_errstr_t p_errstr = nullptr;
+static int load_nccl() {
+    if(g_nccl) return 0;
+    g_nccl = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if(!g_nccl) g_nccl = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if(!g_nccl) return gf_fail(std::string("cannot dlopen libnccl.so.2: ") + dlerror());
+    p_uid = (nccl_get_uid_t)dlsym(g_nccl, "ncclGetUniqueId");
+    p_init = (nccl_init_rank_t)dlsym(g_nccl, "ncclCommInitRank");
+    p_allreduce = (nccl_allreduce_t)dlsym(g_nccl, "ncclAllReduce");
+    p_destroy = (nccl_destroy_t)dlsym(g_nccl, "ncclCommDestroy");
+    p_errstr = (nccl_errstr_t)dlsym(g_nccl, "ncclGetErrorString");
+    if(!p_uid || !p_init || !p_allreduce || !p_destroy) return gf_fail("libnccl: missing symbols");
+    return 0;
+}
+static int nccl_fail(const char *what, int rc) {
+    return gf_fail(std::string(what) + ": " + (p_errstr ? p_errstr(rc) : "NCCL error") + " (" + std::to_string(rc) + ")");
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -177,6 +210,12 @@ extern "C" void gf_destroy(gf_ctx *c) {
     cudaFree(c->d_nodes); cudaFree(c->d_params); cudaFree(c->d_consts); cudaFree(c->d_norms); cudaFree(c->d_ints);
     cudaFree(c->d_partials); cudaFree(c->d_ticket); cudaFree(c->d_result); cudaFree(c->d_events_out);
     cudaFreeHost(c->h_result);
+    if(c->nccl_comm && p_destroy) p_destroy(c->nccl_comm);
+    for(int i = 0; i < gf_ctx::RING; i++) {
+        if(c->ring_buf[i]) cudaFreeHost(c->ring_buf[i]);
+        if(c->ring_ev[i]) cudaEventDestroy(c->ring_ev[i]);
+    }
+    if(c->t0) { cudaEventDestroy(c->t0); cudaEventDestroy(c->t1); }
     if(c->h_pin) cudaFreeHost(c->h_pin);
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1);
     cudaStreamDestroy(c->stream);
@@ -246,6 +285,89 @@ extern "C" int gf_set_program(gf_ctx *c, const gf_node *nodes, int n_nodes, cons
         cudaFuncSetAttribute(k_eval_events, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
         cudaFuncSetAttribute(k_grid_sum, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
     }
+    return 0;
+}
+
+extern "C" int gf_comm_unique_id(void *id128) {
+    if(load_nccl()) return 1;
+    int rc = p_uid(id128);
+    return rc ? nccl_fail("ncclGetUniqueId", rc) : 0;
+}
+extern "C" int gf_comm_init(gf_ctx *c, const void *id128, int rank, int nranks) {
+    if(!c) return gf_fail("null ctx");
+    if(load_nccl()) return 1;
+    if(nranks < 1 || rank < 0 || rank >= nranks) return gf_fail("gf_comm_init: bad rank");
+    cudaSetDevice(c->device);
+    gf_nccl_uid uid;
+    std::memcpy(&uid, id128, sizeof uid);
+    void *comm = nullptr;
+    int rc = p_init(&comm, nranks, uid, rank);
+    if(rc) return nccl_fail("ncclCommInitRank", rc);
+    c->nccl_comm = comm;
+    c->rank = rank;
+    c->nranks = nranks;
+    return 0;
+}
+extern "C" int gf_comm_destroy(gf_ctx *c) {
+    if(!c) return gf_fail("null ctx");
+    if(c->nccl_comm) {
+        cudaSetDevice(c->device);
+        cudaStreamSynchronize(c->stream);
+        p_destroy(c->nccl_comm);
+        c->nccl_comm = nullptr;
+    }
+    c->nranks = 1;
+    c->rank = 0;
+    return 0;
+}
+int gf_allreduce_sum(gf_ctx *c, double *dev, int n) {
+    if(!c->nccl_comm) return 0;
+    int rc = p_allreduce(dev, dev, (size_t)n, /*ncclDouble*/ 8, /*ncclSum*/ 0, c->nccl_comm, c->stream);
+    return rc ? nccl_fail("ncclAllReduce", rc) : 0;
+}
+
+extern "C" int gf_timer_start(gf_ctx *c) {
+    if(!c) return gf_fail("null ctx");
+    cudaSetDevice(c->device);
+    if(!c->t0) { cudaEventCreate(&c->t0); cudaEventCreate(&c->t1); }
+    GF_CUDA(cudaEventRecord(c->t0, c->stream));
+    return 0;
+}
+extern "C" int gf_timer_stop(gf_ctx *c, float *ms) {
+    if(!c || !c->t0) return gf_fail("gf_timer_stop: timer not started");
+    cudaSetDevice(c->device);
+    GF_CUDA(cudaEventRecord(c->t1, c->stream));
+    GF_CUDA(cudaEventSynchronize(c->t1));
+    GF_CUDA(cudaEventElapsedTime(ms, c->t0, c->t1));
+    return 0;
+}
+extern "C" int gf_set_params_async(gf_ctx *c, const double *params, int n, const double *norms, int n_norms) {
+    if(!c) return gf_fail("null ctx");
+    if(n != c->n_params) return gf_fail("gf_set_params_async: size mismatch");
+    if(norms && n_norms != c->n_norms) return gf_fail("gf_set_params_async: norms size mismatch");
+    cudaSetDevice(c->device);
+    size_t need = sizeof(double) * (size_t)(c->n_params + c->n_norms + 1);
+    if(need > c->ring_cap) {
+        GF_CUDA(cudaStreamSynchronize(c->stream));
+        for(int i = 0; i < gf_ctx::RING; i++) {
+            if(c->ring_buf[i]) cudaFreeHost(c->ring_buf[i]);
+            GF_CUDA(cudaMallocHost(&c->ring_buf[i], need));
+            if(!c->ring_ev[i]) cudaEventCreateWithFlags(&c->ring_ev[i], cudaEventDisableTiming);
+        }
+        c->ring_cap = need;
+    }
+    int k = c->ring_pos;
+    c->ring_pos = (k + 1) % gf_ctx::RING;
+    cudaEventSynchronize(c->ring_ev[k]); // slot free again? (returns at once for a never-recorded event)
+    if(n) {
+        std::memcpy(c->ring_buf[k], params, sizeof(double) * n);
+        GF_CUDA(cudaMemcpyAsync(c->d_params, c->ring_buf[k], sizeof(double) * n, cudaMemcpyHostToDevice, c->stream));
+    }
+    if(norms) {
+        std::memcpy(c->ring_buf[k] + n, norms, sizeof(double) * n_norms);
+        GF_CUDA(cudaMemcpyAsync(c->d_norms, c->ring_buf[k] + n, sizeof(double) * n_norms, cudaMemcpyHostToDevice, c->stream));
+    }
+    GF_CUDA(cudaEventRecord(c->ring_ev[k], c->stream));
     return 0;
 }
 
@@ -386,6 +508,7 @@ extern "C" int gf_eval_sum_async(gf_ctx *c, int root, int metric) {
     cudaEventRecord(c->ev1, c->stream);
     c->launches++;
     GF_CUDA(cudaGetLastError());
+    if(c->nccl_comm && gf_allreduce_sum(c, c->d_result, 1)) return 1;
     return 0;
 }
 

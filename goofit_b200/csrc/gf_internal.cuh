@@ -189,6 +189,16 @@ struct gf_ctx {
     int max_blocks = 0;
     float last_ms = 0;
     uint64_t launches = 0;
+    // NCCL (dlopen'ed) communicator for the partial-sum all-reduce
+    void *nccl_comm = nullptr;
+    int nranks = 1, rank = 0;
+    // async parameter ring + stopwatch
+    static const int RING = 16;
+    double *ring_buf[RING] = {nullptr};
+    cudaEvent_t ring_ev[RING] = {nullptr};
+    size_t ring_cap = 0;
+    int ring_pos = 0;
+    cudaEvent_t t0 = nullptr, t1 = nullptr;
     std::vector<gf_amp3_state *> amp3;
     std::vector<gf_amp4_state *> amp4;
     std::vector<gf_conv_state *> conv;
@@ -207,3 +217,5 @@ int gf_fail(const std::string &s);
 size_t gf_prog_smem(const gf_ctx *c);
 int gf_grid_blocks(const gf_ctx *c, long n_items, int per_sm);
 int gf_alloc_aux_slot(gf_ctx *c);
+// all-reduce (sum) n doubles in place on the ctx stream when a communicator is attached; no-op otherwise
+int gf_allreduce_sum(gf_ctx *c, double *dev, int n);

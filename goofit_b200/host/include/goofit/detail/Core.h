@@ -497,6 +497,7 @@ class PdfBase {
     /// index of this PDF's record in the flattened program (-1 when it is not part of it)
     int getFunctionIndex() const { return nodeIdx; }
     int getParameterIndex() const { return parOffs.empty() ? -1 : parOffs.back(); }
+    int getNormalizationIndex() const { return normSlot; }
     bool areParamsandConstantsEqualByVal(const PdfBase &other) const;
 
     // ---- flattening hooks (new; called by the Engine and by parent nodes, not by user code) ----

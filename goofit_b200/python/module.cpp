@@ -38,6 +38,10 @@ PYBIND11_MODULE(_goofit, m) {
           "raw gf_ctx* of the engine (for attaching an NCCL communicator through the C ABI)");
     m.def("launch_count", [] { return gf_launch_count(detail::Engine::get().ctx()); });
     m.def("last_kernel_ms", [] { return gf_last_kernel_ms(detail::Engine::get().ctx()); });
+    m.def("program_params", [] { return py::array(py::cast(detail::Engine::get().prog.params)); },
+          "copy of the flattened parameter block as last pushed by updateParameters()");
+    m.def("program_norms", [] { return py::array(py::cast(detail::Engine::get().prog.norms)); });
+    m.def("local_events", [] { return detail::Engine::get().localEvents; });
     m.def("shutdown", [] { detail::Engine::get().shutdown(); });
 
     // ---- variables ----
@@ -198,6 +202,8 @@ PYBIND11_MODULE(_goofit, m) {
         .def("getParameterByName", &PdfBase::getParameterByName, py::return_value_policy::reference_internal)
         .def("getObservables", &PdfBase::getObservables)
         .def("getFunctionIndex", &PdfBase::getFunctionIndex)
+        .def("getParameterIndex", &PdfBase::getParameterIndex)
+        .def("getNormalizationIndex", &PdfBase::getNormalizationIndex)
         .def("getNormalization", &PdfBase::getNormalization)
         .def("parametersChanged", &PdfBase::parametersChanged)
         .def("updateVariable", &PdfBase::updateVariable)

@@ -141,6 +141,21 @@ int gf_amp4_norm(gf_ctx *, int node, double *out /* 1 (Amp4Body) or 4 (TD) sums 
 int gf_amp4_norm_async(gf_ctx *, int node);
 int gf_amp4_get_amp(gf_ctx *, int node, int amp, double *out_re_im, size_t n_events);
 
+/* ---- multi-GPU: one process per GPU, partial sums all-reduced in-stream over NCCL (NVLink/NVSwitch) --------
+ * Replaces the reference's MPI_Allreduce of the partial NLL (src/PDFs/GooPdf.cu:72-75). libnccl.so.2 is
+ * dlopen'ed on first use. gf_comm_unique_id fills 128 bytes on rank 0; the caller ships them to every rank
+ * (any side channel), then each rank calls gf_comm_init. Afterwards gf_eval_sum / gf_amp4_norm return the
+ * sum over all ranks (same value on every rank). */
+int gf_comm_unique_id(void *id128);
+int gf_comm_init(gf_ctx *, const void *id128, int rank, int nranks);
+int gf_comm_destroy(gf_ctx *);
+/* device-side stopwatch on the ctx stream (CUDA events): start, enqueue work, stop -> elapsed ms */
+int gf_timer_start(gf_ctx *);
+int gf_timer_stop(gf_ctx *, float *ms);
+/* as gf_set_params (+ gf_set_norms when norms != NULL), but never blocks on earlier kernels: the values go
+ * through a ring of pinned slots, so a caller can queue several evaluations back to back */
+int gf_set_params_async(gf_ctx *, const double *params, int n, const double *norms, int n_norms);
+
 /* timing of the last kernel launched by gf_eval_sum (CUDA events on the ctx stream), ms */
 float gf_last_kernel_ms(gf_ctx *);
 /* number of kernels this ctx has launched since creation */
