@@ -13,7 +13,7 @@ CAPI_PATH = _os.path.join(LIB_DIR, "libgoofit_b200.so")
 try:
     from ._goofit import *  # noqa: F401,F403
     from . import _goofit
-    from ._goofit import Resonances  # noqa: F401
+    from ._goofit import Resonances, Lineshapes  # noqa: F401
 except ImportError as e:  # pragma: no cover - build missing
     raise ImportError(
         "goofit_b200: the native extension is not built (run `make` or `python -c 'import __graft_entry__ as g; g.build()'`): %s" % e

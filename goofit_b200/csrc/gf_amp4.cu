@@ -1,4 +1,335 @@
-// placeholder until the Amp4Body kernels land
+// gf_amp4.cu — Amp4Body caches and the Monte-Carlo normalisation integral.
+//   k_amp4_cache  ONE pass per event set (data or MC): get4Vecs once, then every flagged spin factor and
+//                 lineshape (the reference launches one thrust::transform per spin factor / lineshape and
+//                 recomputes get4Vecs in each: Amp4Body.cu:432-525, detail/{SF,LS,NormSpin,NormLS}Calculator.cu)
+//   k_amp4_amps   A_a = 1/sqrt(nPerm) * sum_perm prod LS * prod SF for every flagged amplitude
+//                 (detail/AmpCalc.cu:14-59); also run on the MC sample so that
+//   k_amp4_norm   sum_m |sum_a c_a A_a(m)|^2 streams nAmp*16 B per MC event instead of rebuilding the
+//                 amplitudes from nLS*16 + nSF*8 B on every call (detail/NormIntegrator.cu:15-68); the
+//                 per-event arithmetic is unchanged.
+// SoA layout: ls[i*ld + e] (complex), sf[k*ld + e] (real), amps[a*ld + e] (complex).
 #include "gf_internal.cuh"
-struct gf_amp4_state { int node; };
-void gf_amp4_free(gf_ctx *c) { for(auto *s : c->amp4) delete s; c->amp4.clear(); }
+#include "gf_amp4.cuh"
+
+struct gf_amp4_set { // one event sample (data or MC) with its caches
+    long n = 0, ld = 0;
+    const double *cols[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    double *owned_cols = nullptr;
+    double *weights = nullptr;
+    double2 *ls = nullptr;
+    double *sf = nullptr;
+    double2 *amps = nullptr;
+};
+struct gf_amp4_state {
+    int node = -1, slot = -1, nLS = 0, nSF = 0, nAmp = 0, td = 0;
+    gf_amp4_set data, mc;
+};
+
+static void free_set(gf_amp4_set &s) {
+    cudaFree(s.owned_cols); cudaFree(s.weights); cudaFree(s.ls); cudaFree(s.sf); cudaFree(s.amps);
+    s = gf_amp4_set();
+}
+void gf_amp4_free(gf_ctx *c) {
+    for(auto *s : c->amp4) {
+        free_set(s->data);
+        free_set(s->mc);
+        delete s;
+    }
+    c->amp4.clear();
+}
+static gf_amp4_state *find_amp4(gf_ctx *c, int node, bool create) {
+    for(auto *s : c->amp4)
+        if(s->node == node) return s;
+    if(!create) return nullptr;
+    auto *s = new gf_amp4_state();
+    s->node = node;
+    c->amp4.push_back(s);
+    return s;
+}
+
+struct gf_amp4_args {
+    const double *cols[5];
+    long n, ld;
+    double2 *ls;
+    double *sf;
+    double2 *amps;
+};
+
+// ints of the AMP4 node: {aux slot, nLS, nSF, nAmp, td, ls_node[nLS], sf_node[nSF], start[nAmp], records...}
+// record of amplitude a = {nLS_a, nSF_a, nPerm, LS indices..., SF indices...} (Amp4Body.cu:222-231)
+__global__ void __launch_bounds__(GF_THREADS, 2)
+    k_amp4_cache(const gf_dev_view V, int node, gf_amp4_args A, int redo_spins, unsigned long long ls_mask) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    gf_sprog P = gf_stage_program(V, smem);
+    __syncthreads();
+    const gf_node &nd = P.nodes[node];
+    const int32_t *in = P.ints + nd.int_off;
+    const double *mc = P.consts + nd.con_off; // M, m1, m2, m3, m4
+    const int nLS = in[1], nSF = in[2];
+    const double M = mc[0], m1 = mc[1], m2 = mc[2], m3 = mc[3], m4 = mc[4];
+    const long stride = (long)gridDim.x * blockDim.x;
+    for(long e = (long)blockIdx.x * blockDim.x + threadIdx.x; e < A.n; e += stride) {
+        double m12 = __ldg(A.cols[0] + e), m34 = __ldg(A.cols[1] + e), c12 = __ldg(A.cols[2] + e),
+               c34 = __ldg(A.cols[3] + e), phi = __ldg(A.cols[4] + e);
+        double vecs[16];
+        gf_get4vecs(vecs, m12, m34, c12, c34, phi, M, m1, m2, m3, m4);
+        if(redo_spins) {
+            for(int k = 0; k < nSF; ++k) {
+                const gf_node &sn = P.nodes[in[5 + nLS + k]];
+                int kind = P.ints[sn.int_off];
+                A.sf[(size_t)k * A.ld + e] = gf_spinfactor(kind, P.consts + sn.con_off, vecs);
+            }
+        }
+        for(int i = 0; i < nLS; ++i) {
+            if(!((ls_mask >> i) & 1ull)) continue;
+            const gf_node &ln = P.nodes[in[5 + i]];
+            const double *lc = P.consts + ln.con_off;
+            int kind = P.ints[ln.int_off];
+            int pair = (int)lc[0];
+            double mres, d1, d2;
+            if(pair < 2) { // LSCalculator.cu:47-53
+                mres = pair == 0 ? m12 : m34;
+                d1 = pair == 0 ? m1 : m3;
+                d2 = pair == 0 ? m2 : m4;
+            } else
+                mres = gf_getmass(pair, d1, d2, vecs, m1, m2, m3, m4);
+            gf_cplx r = gf_lineshape(kind, P.params + ln.par_off, lc, mres, d1, d2);
+            A.ls[(size_t)i * A.ld + e] = make_double2(r.re, r.im);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(GF_THREADS, 2)
+    k_amp4_amps(const gf_dev_view V, int node, gf_amp4_args A, unsigned long long amp_mask) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    gf_sprog P = gf_stage_program(V, smem);
+    __syncthreads();
+    const gf_node &nd = P.nodes[node];
+    const int32_t *in = P.ints + nd.int_off;
+    const int nLS = in[1], nSF = in[2], nAmp = in[3];
+    const int32_t *start = in + 5 + nLS + nSF;
+    const int32_t *rec0 = start + nAmp;
+    const long stride = (long)gridDim.x * blockDim.x;
+    for(long e = (long)blockIdx.x * blockDim.x + threadIdx.x; e < A.n; e += stride) {
+        for(int a = 0; a < nAmp; ++a) {
+            if(!((amp_mask >> a) & 1ull)) continue;
+            const int32_t *rec = rec0 + start[a];
+            int numLS = rec[0], numSF = rec[1], nPerm = rec[2];
+            int LS_step = numLS / nPerm, SF_step = numSF / nPerm;
+            gf_cplx total = gf_c(0, 0);
+            for(int p = 0; p < nPerm; ++p) {
+                gf_cplx ret = gf_c(1, 0);
+                for(int j = p * LS_step; j < (p + 1) * LS_step; ++j) {
+                    double2 t = A.ls[(size_t)rec[3 + j] * A.ld + e];
+                    ret = ret * gf_c(t.x, t.y);
+                }
+                for(int j = p * SF_step; j < (p + 1) * SF_step; ++j) {
+                    double s = A.sf[(size_t)rec[3 + numLS + j] * A.ld + e];
+                    ret = ret * gf_c(s, 0.0); // the reference multiplies by complex(sf, 0)
+                }
+                total = total + ret;
+            }
+            total = total * (1 / sqrt((double)nPerm));
+            A.amps[(size_t)a * A.ld + e] = make_double2(total.re, total.im);
+        }
+    }
+}
+
+// sum over MC events of |sum_a A_a(m) c_a|^2 (optionally weighted); deterministic grid reduction
+__global__ void __launch_bounds__(GF_THREADS, 4)
+    k_amp4_norm(const gf_dev_view V, int node, const double2 *amps, long ld, long n, const double *weights,
+                double *partials, unsigned *ticket, double *out) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ double red[32];
+    gf_sprog P = gf_stage_program(V, smem);
+    __syncthreads();
+    const gf_node &nd = P.nodes[node];
+    const double *coef = P.params + nd.par_off;
+    const int nAmp = P.ints[nd.int_off + 3];
+    double acc = 0;
+    const long stride = (long)gridDim.x * blockDim.x;
+    for(long m = (long)blockIdx.x * blockDim.x + threadIdx.x; m < n; m += stride) {
+        gf_cplx tot = gf_c(0, 0);
+#pragma unroll 4
+        for(int a = 0; a < nAmp; ++a) {
+            double2 t = __ldg(amps + (size_t)a * ld + m);
+            tot = tot + gf_c(t.x, t.y) * gf_c(coef[2 * a], coef[2 * a + 1]);
+        }
+        double v = tot.re * tot.re + tot.im * tot.im;
+        if(weights) v *= __ldg(weights + m);
+        acc += v;
+    }
+    gf_grid_finish(&acc, 1, partials, ticket, out, red);
+}
+
+// ---- C ABI ---------------------------------------------------------------------------------------------------
+static int amp4_check(gf_ctx *c, int node, gf_amp4_state **out, bool create) {
+    if(!c) return gf_fail("null ctx");
+    if(node < 0 || node >= (int)c->h_nodes.size() || (c->h_nodes[node].op != GF_OP_AMP4 && c->h_nodes[node].op != GF_OP_AMP4_TD))
+        return gf_fail("gf_amp4: node is not an Amp4Body record");
+    const gf_node &nd = c->h_nodes[node];
+    if(nd.nint < 5 || nd.ncon < 5 || nd.nobs < 6) return gf_fail("gf_amp4: malformed Amp4Body record");
+    const int32_t *in = c->h_ints.data() + nd.int_off;
+    int nLS = in[1], nSF = in[2], nAmp = in[3];
+    if(nLS < 0 || nLS > 64 || nSF < 0 || nSF > 64 || nAmp < 1 || nAmp > 64) return gf_fail("gf_amp4: at most 64 lineshapes / spin factors / amplitudes");
+    if(nd.nint < 5 + nLS + nSF + nAmp) return gf_fail("gf_amp4: truncated index block");
+    if(nd.npar < 2 * nAmp) return gf_fail("gf_amp4: coefficient block too short");
+    int nn = (int)c->h_nodes.size();
+    for(int i = 0; i < nLS + nSF; i++)
+        if(in[5 + i] < 0 || in[5 + i] >= nn) return gf_fail("gf_amp4: bad lineshape / spin-factor record index");
+    for(int a = 0; a < nAmp; a++) {
+        int off = 5 + nLS + nSF + nAmp + in[5 + nLS + nSF + a];
+        if(off + 3 > nd.nint) return gf_fail("gf_amp4: amplitude record out of range");
+        int numLS = in[off], numSF = in[off + 1], nPerm = in[off + 2];
+        if(nPerm < 1 || off + 3 + numLS + numSF > nd.nint) return gf_fail("gf_amp4: amplitude record out of range");
+        for(int j = 0; j < numLS; j++)
+            if(in[off + 3 + j] < 0 || in[off + 3 + j] >= nLS) return gf_fail("gf_amp4: lineshape index out of range");
+        for(int j = 0; j < numSF; j++)
+            if(in[off + 3 + numLS + j] < 0 || in[off + 3 + numLS + j] >= nSF) return gf_fail("gf_amp4: spin-factor index out of range");
+    }
+    if(in[0] < 0 || in[0] >= GF_MAX_AUX) return gf_fail("gf_amp4: bad aux slot");
+    gf_amp4_state *s = find_amp4(c, node, create);
+    if(!s) return gf_fail("gf_amp4: gf_amp4_alloc / gf_amp4_set_mc not called for this node");
+    s->slot = in[0]; s->nLS = nLS; s->nSF = nSF; s->nAmp = nAmp; s->td = in[4];
+    *out = s;
+    return 0;
+}
+
+static int alloc_caches(gf_ctx *c, gf_amp4_state *s, gf_amp4_set &S, size_t n) {
+    cudaFree(S.ls); cudaFree(S.sf); cudaFree(S.amps);
+    S.ls = nullptr; S.sf = nullptr; S.amps = nullptr;
+    S.n = (long)n;
+    S.ld = (long)((n + 15) & ~size_t(15));
+    if(S.ld == 0) S.ld = 16;
+    GF_CUDA(cudaMalloc(&S.ls, sizeof(double2) * (size_t)S.ld * std::max(1, s->nLS)));
+    GF_CUDA(cudaMalloc(&S.sf, sizeof(double) * (size_t)S.ld * std::max(1, s->nSF)));
+    GF_CUDA(cudaMalloc(&S.amps, sizeof(double2) * (size_t)S.ld * s->nAmp));
+    GF_CUDA(cudaMemsetAsync(S.ls, 0, sizeof(double2) * (size_t)S.ld * std::max(1, s->nLS), c->stream));
+    GF_CUDA(cudaMemsetAsync(S.sf, 0, sizeof(double) * (size_t)S.ld * std::max(1, s->nSF), c->stream));
+    GF_CUDA(cudaMemsetAsync(S.amps, 0, sizeof(double2) * (size_t)S.ld * s->nAmp, c->stream));
+    return 0;
+}
+
+extern "C" int gf_amp4_alloc(gf_ctx *c, int node, size_t n_events) {
+    gf_amp4_state *s;
+    if(amp4_check(c, node, &s, true)) return 1;
+    if((long)n_events != c->view.n_events) return gf_fail("gf_amp4_alloc: cache size != uploaded events");
+    cudaSetDevice(c->device);
+    GF_CUDA(cudaStreamSynchronize(c->stream));
+    if(alloc_caches(c, s, s->data, n_events)) return 1;
+    const gf_node &nd = c->h_nodes[node];
+    for(int k = 0; k < 5; k++) s->data.cols[k] = c->view.cols[c->h_ints[nd.obs_off + k]];
+    c->view.aux[s->slot] = s->data.amps;
+    c->view.aux_ld[s->slot] = s->data.ld;
+    return 0;
+}
+
+extern "C" int gf_amp4_set_mc(gf_ctx *c, int node, const double *const *mc_cols5, size_t n_mc, const double *weights,
+                              const double *dtime, const double *sigma) {
+    gf_amp4_state *s;
+    if(amp4_check(c, node, &s, true)) return 1;
+    if(n_mc == 0) return gf_fail("gf_amp4_set_mc: no MC events");
+    (void)dtime; (void)sigma;
+    cudaSetDevice(c->device);
+    GF_CUDA(cudaStreamSynchronize(c->stream));
+    cudaFree(s->mc.owned_cols); cudaFree(s->mc.weights);
+    s->mc.owned_cols = nullptr; s->mc.weights = nullptr;
+    if(alloc_caches(c, s, s->mc, n_mc)) return 1;
+    GF_CUDA(cudaMalloc(&s->mc.owned_cols, sizeof(double) * 5 * (size_t)s->mc.ld));
+    for(int k = 0; k < 5; k++) {
+        GF_CUDA(cudaMemcpyAsync(s->mc.owned_cols + (size_t)k * s->mc.ld, mc_cols5[k], sizeof(double) * n_mc, cudaMemcpyHostToDevice, c->stream));
+        s->mc.cols[k] = s->mc.owned_cols + (size_t)k * s->mc.ld;
+    }
+    if(weights) {
+        GF_CUDA(cudaMalloc(&s->mc.weights, sizeof(double) * n_mc));
+        GF_CUDA(cudaMemcpyAsync(s->mc.weights, weights, sizeof(double) * n_mc, cudaMemcpyHostToDevice, c->stream));
+    }
+    GF_CUDA(cudaStreamSynchronize(c->stream)); // host columns may be freed by the caller
+    return 0;
+}
+
+static unsigned long long mask64(const uint8_t *redo, int n) {
+    unsigned long long m = 0;
+    for(int i = 0; i < n; i++)
+        if(!redo || redo[i]) m |= (1ull << i);
+    return m;
+}
+
+static int run_set(gf_ctx *c, gf_amp4_state *s, int node, gf_amp4_set &S, int redo_spins, unsigned long long ls_mask,
+                   unsigned long long amp_mask) {
+    if(S.n == 0 || !S.ls) return 0;
+    gf_amp4_args A;
+    for(int k = 0; k < 5; k++) A.cols[k] = S.cols[k];
+    A.n = S.n; A.ld = S.ld; A.ls = S.ls; A.sf = S.sf; A.amps = S.amps;
+    size_t sm = gf_prog_smem(c);
+    int blocks = gf_grid_blocks(c, S.n, 2);
+    if(redo_spins || ls_mask) {
+        if(sm > 48 * 1024) cudaFuncSetAttribute(k_amp4_cache, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        k_amp4_cache<<<blocks, GF_THREADS, sm, c->stream>>>(c->view, node, A, redo_spins, ls_mask);
+        c->launches++;
+    }
+    if(amp_mask) {
+        if(sm > 48 * 1024) cudaFuncSetAttribute(k_amp4_amps, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        k_amp4_amps<<<blocks, GF_THREADS, sm, c->stream>>>(c->view, node, A, amp_mask);
+        c->launches++;
+    }
+    GF_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ls_redo[nLS]: lineshapes whose parameters moved; amp_redo[nAmp]: data amplitudes to rebuild (the caller decides,
+// reproducing the reference's flagging, Amp4Body.cu:490-492). MC amplitudes are rebuilt whenever one of their
+// lineshapes was flagged, which is what the reference's NormIntegrator sees because it re-reads norm_LS every call.
+extern "C" int gf_amp4_cache(gf_ctx *c, int node, int redo_spins, const uint8_t *ls_redo, const uint8_t *amp_redo) {
+    gf_amp4_state *s;
+    if(amp4_check(c, node, &s, false)) return 1;
+    cudaSetDevice(c->device);
+    unsigned long long ls_mask = mask64(ls_redo, s->nLS), amp_mask = mask64(amp_redo, s->nAmp);
+    const gf_node &nd = c->h_nodes[node];
+    const int32_t *in = c->h_ints.data() + nd.int_off;
+    unsigned long long mc_amp_mask = 0;
+    for(int a = 0; a < s->nAmp; a++) {
+        int off = 5 + s->nLS + s->nSF + s->nAmp + in[5 + s->nLS + s->nSF + a];
+        bool need = redo_spins != 0;
+        for(int j = 0; j < in[off] && !need; j++) need = (ls_mask >> in[off + 3 + j]) & 1ull;
+        if(need) mc_amp_mask |= (1ull << a);
+    }
+    if(s->data.ls && s->data.n != c->view.n_events) return gf_fail("gf_amp4_cache: cache size != uploaded events");
+    if(run_set(c, s, node, s->data, redo_spins, ls_mask, amp_mask)) return 1;
+    if(run_set(c, s, node, s->mc, redo_spins, ls_mask, mc_amp_mask)) return 1;
+    return 0;
+}
+
+extern "C" int gf_amp4_norm_async(gf_ctx *c, int node) {
+    gf_amp4_state *s;
+    if(amp4_check(c, node, &s, false)) return 1;
+    if(!s->mc.amps) return gf_fail("gf_amp4_norm: no MC normalisation sample (gf_amp4_set_mc)");
+    cudaSetDevice(c->device);
+    size_t sm = gf_prog_smem(c);
+    if(sm > 48 * 1024) cudaFuncSetAttribute(k_amp4_norm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    int blocks = gf_grid_blocks(c, s->mc.n, 4);
+    k_amp4_norm<<<blocks, GF_THREADS, sm, c->stream>>>(c->view, node, s->mc.amps, s->mc.ld, s->mc.n, s->mc.weights,
+                                                      c->d_partials + (size_t)c->max_blocks * 2, c->d_ticket + 2, c->d_result + 1);
+    c->launches++;
+    GF_CUDA(cudaGetLastError());
+    if(c->nccl_comm && gf_allreduce_sum(c, c->d_result + 1, 1)) return 1;
+    return 0;
+}
+extern "C" int gf_amp4_norm(gf_ctx *c, int node, double *out) {
+    if(gf_amp4_norm_async(c, node)) return 1;
+    GF_CUDA(cudaMemcpyAsync(c->h_result + 1, c->d_result + 1, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    GF_CUDA(cudaStreamSynchronize(c->stream));
+    *out = c->h_result[1];
+    return 0;
+}
+
+extern "C" int gf_amp4_get_amp(gf_ctx *c, int node, int amp, double *out_re_im, size_t n_events) {
+    gf_amp4_state *s;
+    if(amp4_check(c, node, &s, false)) return 1;
+    if(amp < 0 || amp >= s->nAmp) return gf_fail("gf_amp4_get_amp: bad amplitude index");
+    if(!s->data.amps || (long)n_events != s->data.n) return gf_fail("gf_amp4_get_amp: size mismatch");
+    cudaSetDevice(c->device);
+    GF_CUDA(cudaMemcpyAsync(out_re_im, s->data.amps + (size_t)amp * s->data.ld, sizeof(double2) * n_events, cudaMemcpyDeviceToHost, c->stream));
+    GF_CUDA(cudaStreamSynchronize(c->stream));
+    return 0;
+}

@@ -1,0 +1,145 @@
+// Physics4.h — four-body amplitude PDF: lineshapes, spin factors, amplitudes, Amp4Body
+// (reference: include/goofit/PDFs/physics/{Amp4Body.h,Amplitude.h,SpinFactors.h,DalitzPlotHelpers.h},
+//  include/goofit/PDFs/physics/lineshapes/{Lineshape,RBW,SBW,LASS,Bugg,Bugg3}.h).
+#pragma once
+#include <goofit/detail/Physics3.h>
+
+#include <typeinfo>
+
+namespace GooFit {
+
+enum DP4Pair { // DalitzPlotHelpers.h:56-76
+    M_12 = 0, M_34, M_13, M_14, M_23, M_24, M_12_3, M_13_2, M_23_1, M_12_4, M_14_2, M_24_1, M_13_4, M_14_3, M_34_1,
+    M_23_4, M_24_3, M_34_2
+};
+enum class FF : unsigned int { One = 0, BL, BL_Prime, BL2 };
+
+class Lineshape : public AmpComponent { // lineshapes/Lineshape.h:22-49
+    friend class Amp4Body;
+    friend class Amp4Body_TD;
+
+  protected:
+    Lineshape(std::string pdf_name, std::string name, unsigned int L, unsigned int Mpair, FF FormFac, fptype radius, int kind);
+    unsigned int _L;
+    unsigned int _Mpair;
+    FF _FormFac;
+    fptype _radius;
+    int _kind; // gf_ls_kind of the device record
+
+  public:
+    virtual bool isEqualByValue(const Lineshape &other) const;
+    bool operator==(const Lineshape &L) const { return typeid(*this) == typeid(L) && isEqualByValue(L); }
+    int emit(detail::ProgramBuilder &B) override { return emitRecord(B, GF_OP_LS, 0, 1, {_kind}); }
+};
+
+namespace Lineshapes {
+#define GOOFIT_B200_LS(NAME)                                                                                           \
+    class NAME : public Lineshape {                                                                                    \
+      public:                                                                                                          \
+        NAME(std::string name, Variable mass, Variable width, unsigned int L, unsigned int Mpair,                      \
+             FF FormFac = FF::BL_Prime, fptype radius = 1.5);                                                          \
+    };
+GOOFIT_B200_LS(RBW)   // lineshapes/BW.cu:154-168
+GOOFIT_B200_LS(SBW)   // lineshapes/BW.cu:172-186
+GOOFIT_B200_LS(LASS)  // lineshapes/BW.cu:190-206
+GOOFIT_B200_LS(Bugg)  // lineshapes/Bugg.cu:133-146 (mass and width are accepted and ignored, as upstream)
+GOOFIT_B200_LS(Bugg3) // lineshapes/Bugg.cu:148-160
+#undef GOOFIT_B200_LS
+} // namespace Lineshapes
+
+enum class SF_4Body { // SpinFactors.h:18-35
+    DtoPP1_PtoSP2_StoP3P4, DtoPP1_PtoVP2_VtoP3P4, DtoV1V2_V1toP1P2_V2toP3P4_S, DtoV1V2_V1toP1P2_V2toP3P4_P,
+    DtoV1V2_V1toP1P2_V2toP3P4_D, DtoAP1_AtoVP2_VtoP3P4, DtoAP1_AtoVP2Dwave_VtoP3P4, DtoVS_VtoP1P2_StoP3P4,
+    DtoV1P1_V1toV2P2_V2toP3P4, DtoAP1_AtoSP2_StoP3P4, DtoTP1_TtoVP2_VtoP3P4, FF_12_34_L1, FF_12_34_L2, FF_123_4_L1,
+    FF_123_4_L2, ONE
+};
+
+class SpinFactor final : public AmpComponent { // SpinFactors.h:37-68
+    friend class Amp4Body;
+    SF_4Body _SF;
+    unsigned int _P0, _P1, _P2, _P3;
+
+  public:
+    SpinFactor(std::string name, SF_4Body SF, fptype mD0, unsigned int P0, unsigned int P1, unsigned int P2, unsigned int P3);
+    SpinFactor(std::string name, SF_4Body SF, unsigned int P0, unsigned int P1, unsigned int P2, unsigned int P3)
+        : SpinFactor(name, SF, 1.86484, P0, P1, P2, P3) {}
+    bool operator==(const SpinFactor &S) const {
+        return S.getName() == getName() && S._SF == _SF && S._P0 == _P0 && S._P1 == _P1 && S._P2 == _P2 && S._P3 == _P3
+               && areParamsandConstantsEqualByVal(S);
+    }
+    int emit(detail::ProgramBuilder &B) override { return emitRecord(B, GF_OP_SF, 0, 1, {static_cast<int32_t>(_SF)}); }
+};
+
+class Amplitude : public AmpComponent { // Amplitude.h:18-49
+    friend class Amp4Body;
+    friend class Amp4Body_TD;
+
+  public:
+    Amplitude(std::string uniqueDecayStr, Variable ar, Variable ai, std::vector<Lineshape *> LS, std::vector<SpinFactor *> SF,
+              unsigned int nPerm = 1);
+    bool operator==(const Amplitude &A) const;
+    std::vector<SpinFactor *> getSpinFactors() { return _SF; }
+    std::vector<Lineshape *> getLineShapes() { return _LS; }
+    bool lineshapeParametersChanged() const;
+
+  private:
+    std::string _uniqueDecayStr;
+    Variable _ar, _ai;
+    std::vector<SpinFactor *> _SF;
+    std::vector<Lineshape *> _LS;
+    unsigned int _nPerm;
+};
+
+struct DecayInfo4 { // DalitzPlotHelpers.h:108-114
+    std::vector<fptype> particle_masses;
+    fptype meson_radius;
+    std::vector<Amplitude *> amplitudes;
+    std::vector<Amplitude *> amplitudes_B;
+};
+
+class Amp4BodyBase : public GooPdf {
+  public:
+    using GooPdf::GooPdf;
+};
+
+/// Deterministic four-body phase-space sample expressed in (m12, m34, cos12, cos34, phi). Replaces the MCBooster
+/// PhaseSpace + Dim5 calls of the reference's constructor (Amp4Body.cu:243-289, detail/Dim5.h:19-111); the generator
+/// is this build's own (GENBOD sequential two-body decays, counter-based RNG), so toys differ from MCBooster's.
+std::vector<std::vector<fptype>> generatePhaseSpace5(const std::vector<fptype> &particle_masses, size_t nEvents,
+                                                      unsigned long seed, std::vector<fptype> *weights = nullptr);
+/// (m12, m34, cos12, cos34, phi) of one event given as 4 x (E, px, py, pz) — pinned by tests/simple/VectorsTest.cu
+void fourVectorsToDim5(const fptype *p4x4_Epxpypz, fptype *out5);
+
+class Amp4Body : public Amp4BodyBase { // Amp4Body.h:33-95
+  public:
+    Amp4Body(std::string n, std::vector<Observable> observables, DecayInfo4 decay, GooPdf *eff, unsigned int MCeventsNorm = 5e6);
+    fptype normalize() override;
+    void setDataSize(unsigned int dataSize, unsigned int evtSize = 6);
+    void setForceIntegrals(bool f = true) { forceRedoIntegrals = f; }
+    int getMCevents() { return static_cast<int>(MCevents); }
+    /// replace the normalisation sample: five columns (m12, m34, cos12, cos34, phi) of equal length
+    void setNormEvents(const std::vector<std::vector<fptype>> &cols5);
+    const std::vector<std::vector<fptype>> &getNormEvents() const { return normCols; }
+    std::vector<std::complex<fptype>> getCachedAmp(size_t a) const;
+    size_t numLineshapes() const { return LineShapes.size(); }
+    size_t numSpinFactors() const { return SpinFactors.size(); }
+
+    void emitAux(detail::ProgramBuilder &B) override;
+    int emit(detail::ProgramBuilder &B) override;
+    void afterProgram() override;
+
+  protected:
+    void ensureCache();
+    DecayInfo4 decayInfo;
+    GooPdf *efficiency;
+    std::vector<SpinFactor *> SpinFactors;
+    std::vector<Lineshape *> LineShapes;
+    std::vector<int32_t> ampIndex; // start[nAmp] + records
+    std::vector<std::vector<fptype>> normCols;
+    size_t MCevents{0};
+    bool forceRedoIntegrals{true};
+    bool cacheAllocated{false};
+    int totalEventSize;
+};
+
+} // namespace GooFit

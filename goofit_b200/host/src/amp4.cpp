@@ -1,0 +1,363 @@
+// amp4.cpp — host half of the four-body amplitude PDF (reference: src/PDFs/physics/Amp4Body.cu:94-558,
+// Amplitude.cu, SpinFactors.cu:570-640, lineshapes/{Lineshape,BW,Bugg}.cu). Device work lives in csrc/gf_amp4.cu.
+#include <goofit/detail/Physics4.h>
+
+#include <numeric>
+
+namespace GooFit {
+using detail::Engine;
+
+// ---- lineshapes ------------------------------------------------------------------------------------------
+Lineshape::Lineshape(std::string pdf_name, std::string name, unsigned int L, unsigned int Mpair, FF FormFac, fptype radius, int kind)
+    : AmpComponent("Lineshapes::" + pdf_name, name)
+    , _L(L)
+    , _Mpair(Mpair)
+    , _FormFac(FormFac)
+    , _radius(radius)
+    , _kind(kind) {
+    registerConstant(Mpair); // Lineshape.cu:21-35
+    registerFunction("ptr_to_" + pdf_name, GF_OP_LS);
+}
+bool Lineshape::isEqualByValue(const Lineshape &o) const { // Lineshape.cu:37-41
+    return getName() == o.getName() && _L == o._L && _Mpair == o._Mpair && _FormFac == o._FormFac && _radius == o._radius
+           && areParamsandConstantsEqualByVal(o);
+}
+namespace Lineshapes {
+// kinds: gf_ls_kind in csrc/gf_amp4.cuh {RBW, SBW, LASS, BUGG, BUGG3}
+#define GOOFIT_B200_LS_BW(NAME, KIND)                                                                                  \
+    NAME::NAME(std::string name, Variable mass, Variable width, unsigned int L, unsigned int Mpair, FF FormFac, fptype radius) \
+        : Lineshape(#NAME, name, L, Mpair, FormFac, radius, KIND) {                                                    \
+        registerParameter(mass);                                                                                       \
+        registerParameter(width);                                                                                      \
+        registerConstant(L);                                                                                           \
+        registerConstant(static_cast<unsigned int>(FormFac));                                                          \
+        registerConstant(radius);                                                                                      \
+    }
+GOOFIT_B200_LS_BW(RBW, 0)
+GOOFIT_B200_LS_BW(SBW, 1)
+GOOFIT_B200_LS_BW(LASS, 2)
+#undef GOOFIT_B200_LS_BW
+Bugg::Bugg(std::string name, Variable, Variable, unsigned int L, unsigned int Mpair, FF FormFac, fptype radius)
+    : Lineshape("Bugg", name, L, Mpair, FormFac, radius, 3) {}
+Bugg3::Bugg3(std::string name, Variable, Variable, unsigned int L, unsigned int Mpair, FF FormFac, fptype radius)
+    : Lineshape("Bugg3", name, L, Mpair, FormFac, radius, 4) {}
+} // namespace Lineshapes
+
+// ---- spin factors / amplitudes -------------------------------------------------------------------------------
+SpinFactor::SpinFactor(std::string name, SF_4Body SF, fptype mD0, unsigned int P0, unsigned int P1, unsigned int P2, unsigned int P3)
+    : AmpComponent("SpinFactor", name)
+    , _SF(SF)
+    , _P0(P0)
+    , _P1(P1)
+    , _P2(P2)
+    , _P3(P3) {
+    registerConstant(mD0);
+    registerConstant(P0);
+    registerConstant(P1);
+    registerConstant(P2);
+    registerConstant(P3);
+    registerFunction("ptr_to_SpinFactor", GF_OP_SF);
+}
+
+Amplitude::Amplitude(std::string uniqueDecayStr, Variable ar, Variable ai, std::vector<Lineshape *> LS, std::vector<SpinFactor *> SF,
+                     unsigned int nPerm)
+    : AmpComponent("Amplitude", uniqueDecayStr)
+    , _uniqueDecayStr(uniqueDecayStr)
+    , _ar(ar)
+    , _ai(ai)
+    , _SF(std::move(SF))
+    , _LS(std::move(LS))
+    , _nPerm(nPerm) {
+    if(_nPerm < 1) throw GeneralError("Amplitude {}: nPerm must be at least 1", uniqueDecayStr);
+    for(auto *l : _LS) components.push_back(l);
+    for(auto *s : _SF) components.push_back(s);
+}
+bool Amplitude::operator==(const Amplitude &A) const {
+    return _uniqueDecayStr == A._uniqueDecayStr && _ar == A._ar && _ai == A._ai && _LS == A._LS && _SF == A._SF && _nPerm == A._nPerm;
+}
+bool Amplitude::lineshapeParametersChanged() const {
+    return std::any_of(_LS.cbegin(), _LS.cend(), [](const Lineshape *p) { return p->parametersChanged(); });
+}
+
+// ---- phase space -----------------------------------------------------------------------------------------------
+namespace {
+struct V4 { // (E, px, py, pz)
+    double e, x, y, z;
+};
+inline V4 operator+(V4 a, V4 b) { return {a.e + b.e, a.x + b.x, a.y + b.y, a.z + b.z}; }
+inline V4 operator-(V4 a, V4 b) { return {a.e - b.e, a.x - b.x, a.y - b.y, a.z - b.z}; }
+inline V4 operator*(double c, V4 a) { return {a.e * c, a.x * c, a.y * c, a.z * c}; }
+inline V4 operator/(V4 a, double c) {
+    double ci = 1.0 / c;
+    return {a.e * ci, a.x * ci, a.y * ci, a.z * ci};
+}
+inline double mink(V4 a, V4 b) { return a.e * b.e - a.x * b.x - a.y * b.y - a.z * b.z; }
+inline double mass2(V4 a) { return mink(a, a); }
+inline double mass(V4 a) {
+    double m2 = mass2(a);
+    return m2 > 0 ? std::sqrt(m2) : 0.0;
+}
+inline double dot3(V4 a, V4 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+inline double mag3(V4 a) { return std::sqrt(dot3(a, a)); }
+inline V4 cross3(V4 a, V4 b) { return {0.0, a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+// helicity angle (detail/Dim5.h:22-34)
+double cosHel(V4 p, V4 q, V4 d) {
+    double pd = mink(p, d), pq = mink(p, q), qd = mink(q, d);
+    double mp2 = mass2(p), mq2 = mass2(q), md2 = mass2(d);
+    return (pd * mq2 - pq * qd) / std::sqrt((pq * pq - mq2 * mp2) * (qd * qd - mq2 * md2));
+}
+// angle between the two decay planes (detail/Dim5.h:36-92; only the second estimate is returned upstream)
+double planeAngle(V4 d1, V4 d2, V4 h1, V4 h2) {
+    V4 d1n = d1 / mag3(d1), d2n = d2 / mag3(d2), h1n = h1 / mag3(h1), h2n = h2 / mag3(h2);
+    V4 h12 = h1 + h2;
+    h12 = (1.0 / mag3(h12)) * h12;
+    V4 n1 = cross3(d1n, d2n), n2 = cross3(h1n, h2n);
+    n1 = (1.0 / mag3(n1)) * n1;
+    n2 = (1.0 / mag3(n2)) * n2;
+    V4 n3 = cross3(n1, n2);
+    double cp = dot3(n1, n2), sp = dot3(n3, h12);
+    double phi2 = std::acos(cp);
+    if(sp < 0) phi2 *= -1;
+    return phi2;
+}
+inline uint64_t mix64(uint64_t z) {
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+inline double uniform01(uint64_t seed, uint64_t event, uint64_t k) {
+    uint64_t h = mix64(mix64(seed ^ 0xD1B54A32D192ED03ull) + event * 0x2545F4914F6CDD1Dull + k);
+    return ((h >> 11) + 0.5) * (1.0 / 9007199254740992.0);
+}
+inline double pdk(double a, double b, double c) {
+    double x = (a - b - c) * (a + b + c) * (a + b - c) * (a - b + c);
+    return std::sqrt(x > 0 ? x : 0) / (2 * a);
+}
+void boost(V4 &p, double bx, double by, double bz) {
+    double b2 = bx * bx + by * by + bz * bz;
+    if(b2 <= 0) return;
+    double gamma = 1.0 / std::sqrt(1.0 - b2), bp = bx * p.x + by * p.y + bz * p.z, g2 = (gamma - 1.0) / b2;
+    p.x += g2 * bp * bx + gamma * bx * p.e;
+    p.y += g2 * bp * by + gamma * by * p.e;
+    p.z += g2 * bp * bz + gamma * bz * p.e;
+    p.e = gamma * (p.e + bp);
+}
+} // namespace
+
+void fourVectorsToDim5(const fptype *p, fptype *out) { // detail/Dim5.h:94-110
+    V4 a{p[0], p[1], p[2], p[3]}, b{p[4], p[5], p[6], p[7]}, c{p[8], p[9], p[10], p[11]}, d{p[12], p[13], p[14], p[15]};
+    V4 pM = a + b + c + d, p12 = a + b, p34 = c + d;
+    out[0] = mass(p12);
+    out[1] = mass(p34);
+    out[2] = cosHel(pM, p12, a);
+    out[3] = cosHel(pM, p34, c);
+    out[4] = planeAngle(a, b, c, d);
+}
+
+std::vector<std::vector<fptype>> generatePhaseSpace5(const std::vector<fptype> &pm, size_t n, unsigned long seed, std::vector<fptype> *weights) {
+    if(pm.size() != 5) throw GeneralError("generatePhaseSpace5 needs the mother and four daughter masses");
+    const double M = pm[0], m[4] = {pm[1], pm[2], pm[3], pm[4]};
+    double tecm = M - m[0] - m[1] - m[2] - m[3];
+    if(tecm <= 0) throw GeneralError("generatePhaseSpace5: not enough energy");
+    double emmax = tecm + m[0], emmin = 0, wtmax = 1;
+    for(int k = 1; k < 4; k++) {
+        emmin += m[k - 1];
+        emmax += m[k];
+        wtmax *= pdk(emmax, emmin, m[k]);
+    }
+    std::vector<std::vector<fptype>> cols(5, std::vector<fptype>(n));
+    if(weights) weights->assign(n, 0.0);
+    for(size_t ev = 0; ev < n; ev++) { // GENBOD: sorted uniforms -> intermediate masses -> sequential two-body decays
+        uint64_t ctr = 0;
+        double r1 = uniform01(seed, ev, ctr++), r2 = uniform01(seed, ev, ctr++);
+        if(r1 > r2) std::swap(r1, r2);
+        double rno[4] = {0, r1, r2, 1}, inv[4], pd[3], sum = 0;
+        for(int k = 0; k < 4; k++) {
+            sum += m[k];
+            inv[k] = rno[k] * tecm + sum;
+        }
+        double wt = 1.0 / wtmax;
+        for(int k = 0; k < 3; k++) {
+            pd[k] = pdk(inv[k + 1], inv[k], m[k + 1]);
+            wt *= pd[k];
+        }
+        V4 p[4];
+        p[0] = {std::sqrt(pd[0] * pd[0] + m[0] * m[0]), 0, pd[0], 0};
+        for(int i = 1;; i++) {
+            p[i] = {std::sqrt(pd[i - 1] * pd[i - 1] + m[i] * m[i]), 0, -pd[i - 1], 0};
+            double cZ = 2 * uniform01(seed, ev, ctr++) - 1, sZ = std::sqrt(1 - cZ * cZ);
+            double ang = 2 * M_PI * uniform01(seed, ev, ctr++), cY = std::cos(ang), sY = std::sin(ang);
+            for(int j = 0; j <= i; j++) {
+                double x = p[j].x, y = p[j].y;
+                p[j].x = cZ * x - sZ * y;
+                p[j].y = sZ * x + cZ * y;
+                x = p[j].x;
+                double z = p[j].z;
+                p[j].x = cY * x - sY * z;
+                p[j].z = sY * x + cY * z;
+            }
+            if(i == 3) break;
+            double beta = pd[i] / std::sqrt(pd[i] * pd[i] + inv[i] * inv[i]);
+            for(int j = 0; j <= i; j++) boost(p[j], 0, beta, 0);
+        }
+        double in[16], out[5];
+        for(int k = 0; k < 4; k++) {
+            in[4 * k] = p[k].e; in[4 * k + 1] = p[k].x; in[4 * k + 2] = p[k].y; in[4 * k + 3] = p[k].z;
+        }
+        fourVectorsToDim5(in, out);
+        for(int k = 0; k < 5; k++) cols[k][ev] = out[k];
+        if(weights) (*weights)[ev] = wt;
+    }
+    return cols;
+}
+
+// ---- Amp4Body ------------------------------------------------------------------------------------------------------
+Amp4Body::Amp4Body(std::string n, std::vector<Observable> observables, DecayInfo4 decay, GooPdf *eff, unsigned int MCeventsNorm)
+    : Amp4BodyBase("Amp4Body", n)
+    , decayInfo(decay)
+    , efficiency(eff)
+    , totalEventSize(static_cast<int>(observables.size())) {
+    if(observables.size() < 6) throw GeneralError("Amp4Body {} needs m12, m34, cos12, cos34, phi and an event number", n);
+    if(decayInfo.particle_masses.size() != 5) throw GeneralError("Amp4Body {}: particle_masses must hold the mother and four daughters", n);
+    if(decayInfo.amplitudes.empty()) throw GeneralError("Amp4Body {} needs at least one amplitude", n);
+    if(!efficiency) throw GeneralError("Amp4Body {} needs an efficiency function", n);
+    for(auto &o : observables) registerObservable(o);
+    for(double pm : decayInfo.particle_masses) registerConstant(pm);
+    // unique lineshapes / spin factors, compared by value exactly as the reference (Amp4Body.cu:120-160)
+    std::vector<int32_t> starts, records;
+    for(auto *amp : decayInfo.amplitudes) {
+        components.push_back(amp);
+        registerParameter(amp->_ar);
+        registerParameter(amp->_ai);
+        starts.push_back(static_cast<int32_t>(records.size()));
+        records.push_back(static_cast<int32_t>(amp->_LS.size()));
+        records.push_back(static_cast<int32_t>(amp->_SF.size()));
+        records.push_back(static_cast<int32_t>(amp->_nPerm));
+        if(amp->_LS.size() % amp->_nPerm || amp->_SF.size() % amp->_nPerm)
+            throw GeneralError("Amplitude {}: lineshapes and spin factors must split evenly over the permutations", amp->getName());
+        for(auto *ls : amp->_LS) {
+            auto it = std::find_if(LineShapes.begin(), LineShapes.end(), [ls](const Lineshape *L) { return *ls == *L; });
+            if(it == LineShapes.end()) {
+                LineShapes.push_back(ls);
+                it = LineShapes.end() - 1;
+            }
+            records.push_back(static_cast<int32_t>(it - LineShapes.begin()));
+        }
+        for(auto *sf : amp->_SF) {
+            auto it = std::find_if(SpinFactors.begin(), SpinFactors.end(), [sf](const SpinFactor *S) { return *sf == *S; });
+            if(it == SpinFactors.end()) {
+                SpinFactors.push_back(sf);
+                it = SpinFactors.end() - 1;
+            }
+            records.push_back(static_cast<int32_t>(it - SpinFactors.begin()));
+        }
+    }
+    if(LineShapes.size() > 64 || SpinFactors.size() > 64 || decayInfo.amplitudes.size() > 64)
+        throw GeneralError("Amp4Body supports at most 64 unique lineshapes, spin factors and amplitudes");
+    ampIndex = starts;
+    ampIndex.insert(ampIndex.end(), records.begin(), records.end());
+    components.push_back(efficiency);
+    registerFunction("ptr_to_DP", GF_OP_AMP4);
+    // Normalisation sample. The reference generates MCeventsNorm phase-space events, runs the accept-reject
+    // "Unweight" step and then keeps the FIRST nAcc events of the un-compacted sample (Amp4Body.cu:243-289: the
+    // remove_if is commented out); the same selection is made here.
+    if(MCeventsNorm > 0) {
+        std::vector<fptype> w;
+        auto cols = generatePhaseSpace5(decayInfo.particle_masses, MCeventsNorm, 0, &w);
+        size_t nAcc = 0;
+        for(size_t i = 0; i < w.size(); i++) nAcc += w[i] > uniform01(0, i, 1000) ? 1 : 0;
+        if(nAcc == 0) nAcc = 1;
+        for(auto &c : cols) c.resize(nAcc);
+        setNormEvents(cols);
+    }
+    setSeparateNorm();
+}
+void Amp4Body::setNormEvents(const std::vector<std::vector<fptype>> &cols5) {
+    if(cols5.size() != 5) throw GeneralError("setNormEvents needs five columns (m12, m34, cos12, cos34, phi)");
+    for(auto &c : cols5)
+        if(c.size() != cols5[0].size() || c.empty()) throw GeneralError("setNormEvents: columns must be non-empty and of equal length");
+    normCols       = cols5;
+    MCevents       = cols5[0].size();
+    cacheAllocated = false;
+    forceRedoIntegrals = true;
+}
+void Amp4Body::emitAux(detail::ProgramBuilder &B) {
+    for(auto *ls : LineShapes) ls->emit(B);
+    for(auto *sf : SpinFactors) sf->emit(B);
+    efficiency->emitAux(B);
+}
+int Amp4Body::emit(detail::ProgramBuilder &B) {
+    int first = (int)B.nodes.size();
+    efficiency->emit(B);
+    std::vector<int32_t> ints{B.allocAux(), (int32_t)LineShapes.size(), (int32_t)SpinFactors.size(),
+                              (int32_t)decayInfo.amplitudes.size(), 0};
+    for(auto *ls : LineShapes) ints.push_back(ls->getFunctionIndex());
+    for(auto *sf : SpinFactors) ints.push_back(sf->getFunctionIndex());
+    ints.insert(ints.end(), ampIndex.begin(), ampIndex.end());
+    return emitRecord(B, GF_OP_AMP4, 1, (int)B.nodes.size() - first + 1, ints);
+}
+void Amp4Body::afterProgram() {
+    cacheAllocated     = false;
+    forceRedoIntegrals = true;
+}
+void Amp4Body::setDataSize(unsigned int dataSize, unsigned int evtSize) { // Amp4Body.cu:348-395
+    totalEventSize = evtSize;
+    if(totalEventSize < 3) throw GeneralError("totalEventSize {} should be 3 or more", totalEventSize);
+    numEntries     = dataSize;
+    cacheAllocated = false;
+    setForceIntegrals();
+}
+void Amp4Body::ensureCache() {
+    if(cacheAllocated) return;
+    if(nodeIdx < 0) throw GeneralError("Amp4Body {}: call setData() on the top-level PDF before evaluating", getName());
+    if(MCevents == 0) throw GeneralError("Amp4Body {} has no normalisation events", getName());
+    Engine &E = Engine::get();
+    Engine::check(gf_amp4_alloc(E.ctx(), nodeIdx, E.localEvents), "gf_amp4_alloc");
+    // the MC normalisation sample is sharded over ranks like the data (the reference replicates it)
+    detail::Shard sh = E.shard();
+    size_t per = MCevents / sh.size, first = per * sh.rank, count = sh.rank == sh.size - 1 ? MCevents - first : per;
+    const double *cols[5];
+    for(int k = 0; k < 5; k++) cols[k] = normCols[k].data() + first;
+    Engine::check(gf_amp4_set_mc(E.ctx(), nodeIdx, cols, count, nullptr, nullptr, nullptr), "gf_amp4_set_mc");
+    cacheAllocated     = true;
+    forceRedoIntegrals = true;
+}
+fptype Amp4Body::normalize() { // Amp4Body.cu:398-558
+    recursiveSetNormalization(1.0);
+    ensureCache();
+    Engine &E   = Engine::get();
+    size_t nLS  = LineShapes.size(), nAmp = decayInfo.amplitudes.size();
+    std::vector<uint8_t> lsRedo(nLS), ampRedo(nAmp, 0);
+    bool any = forceRedoIntegrals;
+    for(size_t i = 0; i < nLS; ++i) {
+        lsRedo[i] = forceRedoIntegrals || LineShapes[i]->parametersChanged();
+        any       = any || lsRedo[i];
+    }
+    // Upstream flags the cached data amplitude a for recomputation with redoIntegral[a], an array that is filled per
+    // LINESHAPE index (Amp4Body.cu:407-414, 490-492); kept as is, so amplitude a follows lineshape a.
+    // Entries beyond the number of lineshapes keep their constructor value `true` upstream (Amp4Body.cu:196-199).
+    for(size_t a = 0; a < nAmp; ++a) {
+        ampRedo[a] = a < nLS ? lsRedo[a] : 1;
+        any        = any || ampRedo[a];
+    }
+    int spins          = forceRedoIntegrals ? 1 : 0;
+    forceRedoIntegrals = false;
+    E.sync();
+    if(any) Engine::check(gf_amp4_cache(E.ctx(), nodeIdx, spins, lsRedo.data(), ampRedo.data()), "gf_amp4_cache");
+    double sum = 0;
+    Engine::check(gf_amp4_norm(E.ctx(), nodeIdx, &sum), "gf_amp4_norm");
+    fptype ret = sum / static_cast<fptype>(MCevents);
+    if(std::isnan(ret)) GooFit::abort(__FILE__, __LINE__, getName() + " NAN normalization in Amp4Body", this);
+    setNormalization(1.0 / ret);
+    return ret;
+}
+std::vector<std::complex<fptype>> Amp4Body::getCachedAmp(size_t a) const {
+    if(!cacheAllocated) throw GeneralError("Amp4Body {}: no cached amplitudes yet", getName());
+    Engine &E = Engine::get();
+    std::vector<std::complex<fptype>> ret(E.localEvents);
+    Engine::check(gf_amp4_get_amp(E.ctx(), nodeIdx, (int)a, reinterpret_cast<double *>(ret.data()), ret.size()), "gf_amp4_get_amp");
+    return ret;
+}
+
+} // namespace GooFit

@@ -18,6 +18,8 @@ namespace py = pybind11;
 using namespace pybind11::literals;
 using namespace GooFit;
 
+void init_physics4(py::module &m);
+
 
 template <class DS>
 static DS *make_dataset(py::args args, py::kwargs kwargs) {
@@ -281,7 +283,8 @@ PYBIND11_MODULE(_goofit, m) {
     py::enum_<DaughterPair>(m, "DaughterPair")
         .value("PAIR_12", PAIR_12).value("PAIR_13", PAIR_13).value("PAIR_23", PAIR_23).export_values();
     m.def("inDalitz", &inDalitz, "m12"_a, "m13"_a, "bigM"_a, "dm1"_a, "dm2"_a, "dm3"_a);
-    py::class_<ResonancePdf, GooPdf>(m, "ResonancePdf")
+    py::class_<AmpComponent, GooPdf>(m, "AmpComponent");
+    py::class_<ResonancePdf, AmpComponent>(m, "ResonancePdf")
         .def("get_amp_real", &ResonancePdf::get_amp_real)
         .def("get_amp_img", &ResonancePdf::get_amp_img);
     auto mres = m.def_submodule("Resonances");
@@ -326,6 +329,8 @@ PYBIND11_MODULE(_goofit, m) {
         .def("getYval", &DalitzPlotter::getYval)
         .def("getZval", &DalitzPlotter::getZval)
         .def("getVal", &DalitzPlotter::getVal, "event"_a, "num"_a = 0);
+
+    init_physics4(m);
 
     // ---- fitting ----
     py::class_<Minuit2::FunctionMinimum>(m, "FunctionMinimum")

@@ -1,0 +1,113 @@
+// physics4.cpp — Python bindings of the four-body amplitude classes (reference: python/PDFs/physics/{Amp4Body.cu,
+// Amplitude.cpp,Lineshapes.cpp,SpinFactors.cpp,DalitzPlotHelpers.cpp}).
+#include <pybind11/complex.h>
+#include <pybind11/numpy.h>
+#include <pybind11/pybind11.h>
+#include <pybind11/stl.h>
+
+#include <goofit/detail/Physics4.h>
+
+namespace py = pybind11;
+using namespace pybind11::literals;
+using namespace GooFit;
+
+template <class LS>
+static void bind_ls(py::module &m, const char *name) {
+    py::class_<LS, Lineshape>(m, name).def(
+        py::init<std::string, Variable, Variable, unsigned int, unsigned int, FF, fptype>(), "name"_a, "mass"_a, "width"_a,
+        "L"_a, "Mpair"_a, "FormFac"_a = FF::BL_Prime, "radius"_a = 1.5);
+}
+
+void init_physics4(py::module &m) {
+    py::enum_<DP4Pair>(m, "DP4Pair")
+        .value("M_12", M_12).value("M_34", M_34).value("M_13", M_13).value("M_14", M_14).value("M_23", M_23).value("M_24", M_24)
+        .value("M_12_3", M_12_3).value("M_13_2", M_13_2).value("M_23_1", M_23_1).value("M_12_4", M_12_4).value("M_14_2", M_14_2)
+        .value("M_24_1", M_24_1).value("M_13_4", M_13_4).value("M_14_3", M_14_3).value("M_34_1", M_34_1).value("M_23_4", M_23_4)
+        .value("M_24_3", M_24_3).value("M_34_2", M_34_2)
+        .export_values();
+    py::enum_<FF>(m, "FF").value("One", FF::One).value("BL", FF::BL).value("BL_Prime", FF::BL_Prime).value("BL2", FF::BL2);
+    py::class_<Lineshape, AmpComponent>(m, "Lineshape");
+    auto mls = m.def_submodule("Lineshapes");
+    bind_ls<Lineshapes::RBW>(mls, "RBW");
+    bind_ls<Lineshapes::SBW>(mls, "SBW");
+    bind_ls<Lineshapes::LASS>(mls, "LASS");
+    bind_ls<Lineshapes::Bugg>(mls, "Bugg");
+    bind_ls<Lineshapes::Bugg3>(mls, "Bugg3");
+    py::enum_<SF_4Body>(m, "SF_4Body")
+        .value("DtoPP1_PtoSP2_StoP3P4", SF_4Body::DtoPP1_PtoSP2_StoP3P4)
+        .value("DtoPP1_PtoVP2_VtoP3P4", SF_4Body::DtoPP1_PtoVP2_VtoP3P4)
+        .value("DtoV1V2_V1toP1P2_V2toP3P4_S", SF_4Body::DtoV1V2_V1toP1P2_V2toP3P4_S)
+        .value("DtoV1V2_V1toP1P2_V2toP3P4_P", SF_4Body::DtoV1V2_V1toP1P2_V2toP3P4_P)
+        .value("DtoV1V2_V1toP1P2_V2toP3P4_D", SF_4Body::DtoV1V2_V1toP1P2_V2toP3P4_D)
+        .value("DtoAP1_AtoVP2_VtoP3P4", SF_4Body::DtoAP1_AtoVP2_VtoP3P4)
+        .value("DtoAP1_AtoVP2Dwave_VtoP3P4", SF_4Body::DtoAP1_AtoVP2Dwave_VtoP3P4)
+        .value("DtoVS_VtoP1P2_StoP3P4", SF_4Body::DtoVS_VtoP1P2_StoP3P4)
+        .value("DtoV1P1_V1toV2P2_V2toP3P4", SF_4Body::DtoV1P1_V1toV2P2_V2toP3P4)
+        .value("DtoAP1_AtoSP2_StoP3P4", SF_4Body::DtoAP1_AtoSP2_StoP3P4)
+        .value("DtoTP1_TtoVP2_VtoP3P4", SF_4Body::DtoTP1_TtoVP2_VtoP3P4)
+        .value("FF_12_34_L1", SF_4Body::FF_12_34_L1)
+        .value("FF_12_34_L2", SF_4Body::FF_12_34_L2)
+        .value("FF_123_4_L1", SF_4Body::FF_123_4_L1)
+        .value("FF_123_4_L2", SF_4Body::FF_123_4_L2)
+        .value("ONE", SF_4Body::ONE);
+    py::class_<SpinFactor, AmpComponent>(m, "SpinFactor")
+        .def(py::init<std::string, SF_4Body, fptype, unsigned int, unsigned int, unsigned int, unsigned int>(), "name"_a, "SF"_a,
+             "mD0"_a, "P0"_a, "P1"_a, "P2"_a, "P3"_a)
+        .def(py::init<std::string, SF_4Body, unsigned int, unsigned int, unsigned int, unsigned int>(), "name"_a, "SF"_a, "P0"_a,
+             "P1"_a, "P2"_a, "P3"_a);
+    py::class_<Amplitude, AmpComponent>(m, "Amplitude")
+        .def(py::init<std::string, Variable, Variable, std::vector<Lineshape *>, std::vector<SpinFactor *>, unsigned int>(),
+             "uniqueDecayStr"_a, "ar"_a, "ai"_a, "LS"_a, "SF"_a, "nPerm"_a = 1, py::keep_alive<1, 5>(), py::keep_alive<1, 6>())
+        .def("lineshapeParametersChanged", &Amplitude::lineshapeParametersChanged);
+    py::class_<DecayInfo4>(m, "DecayInfo4")
+        .def(py::init<>())
+        .def_readwrite("particle_masses", &DecayInfo4::particle_masses)
+        .def_readwrite("meson_radius", &DecayInfo4::meson_radius)
+        .def_readwrite("amplitudes", &DecayInfo4::amplitudes)
+        .def_readwrite("amplitudes_B", &DecayInfo4::amplitudes_B)
+        .def("add_amplitude", [](DecayInfo4 &d, Amplitude *a) { d.amplitudes.push_back(a); }, py::keep_alive<1, 2>())
+        .def("add_amplitude_B", [](DecayInfo4 &d, Amplitude *a) { d.amplitudes_B.push_back(a); }, py::keep_alive<1, 2>());
+    py::class_<Amp4BodyBase, GooPdf>(m, "Amp4BodyBase");
+    py::class_<Amp4Body, Amp4BodyBase>(m, "Amp4Body")
+        .def(py::init<std::string, std::vector<Observable>, DecayInfo4, GooPdf *, unsigned int>(), "name"_a, "observables"_a,
+             "decay"_a, "eff"_a, "MCeventsNorm"_a = 5000000, py::keep_alive<1, 4>(), py::keep_alive<1, 5>())
+        .def("setDataSize", &Amp4Body::setDataSize, "dataSize"_a, "evtSize"_a = 6)
+        .def("setForceIntegrals", &Amp4Body::setForceIntegrals, "f"_a = true)
+        .def("getMCevents", &Amp4Body::getMCevents)
+        .def("numLineshapes", &Amp4Body::numLineshapes)
+        .def("numSpinFactors", &Amp4Body::numSpinFactors)
+        .def("setNormEvents",
+             [](Amp4Body &a, py::array_t<fptype, py::array::c_style | py::array::forcecast> arr) {
+                 if(arr.ndim() != 2 || arr.shape(0) != 5) throw GeneralError("setNormEvents expects an array of shape (5, M)");
+                 std::vector<std::vector<fptype>> cols(5);
+                 for(int k = 0; k < 5; k++) cols[k].assign(arr.data(k, 0), arr.data(k, 0) + arr.shape(1));
+                 a.setNormEvents(cols);
+             },
+             "cols5"_a)
+        .def("getNormEvents",
+             [](const Amp4Body &a) {
+                 auto &c = a.getNormEvents();
+                 size_t n = c.empty() ? 0 : c[0].size();
+                 py::array_t<fptype> r({(size_t)5, n});
+                 for(int k = 0; k < 5 && n; k++) std::copy(c[k].begin(), c[k].end(), r.mutable_data(k, 0));
+                 return r;
+             })
+        .def("getCachedAmp", [](const Amp4Body &a, size_t i) { return py::array(py::cast(a.getCachedAmp(i))); }, "a"_a);
+    m.def("generatePhaseSpace5",
+          [](std::vector<fptype> masses, size_t n, unsigned long seed) {
+              std::vector<fptype> w;
+              auto c = generatePhaseSpace5(masses, n, seed, &w);
+              py::array_t<fptype> r({(size_t)5, n}), wa(n);
+              for(int k = 0; k < 5; k++) std::copy(c[k].begin(), c[k].end(), r.mutable_data(k, 0));
+              std::copy(w.begin(), w.end(), wa.mutable_data());
+              return py::make_tuple(r, wa);
+          },
+          "particle_masses"_a, "n"_a, "seed"_a = 0, "four-body phase-space sample as (m12, m34, cos12, cos34, phi) columns + weights");
+    m.def("fourVectorsToDim5",
+          [](py::array_t<fptype, py::array::c_style | py::array::forcecast> p) {
+              if(p.size() != 16) throw GeneralError("fourVectorsToDim5 expects 16 numbers: 4 x (E, px, py, pz)");
+              py::array_t<fptype> out(5);
+              fourVectorsToDim5(p.data(), out.mutable_data());
+              return out;
+          });
+}
