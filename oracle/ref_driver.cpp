@@ -17,11 +17,25 @@
 #include <goofit/PDFs/combine/ConvolutionPdf.h>
 #include <goofit/PDFs/combine/ProdPdf.h>
 #include <goofit/PDFs/physics/Amp3Body.h>
+#define private public // test infrastructure: read the reference's private MC sample and amplitude cache
+#include <goofit/PDFs/physics/Amp4Body.h>
+#undef private
+#include <goofit/PDFs/physics/Amplitude.h>
+#include <goofit/PDFs/physics/SpinFactors.h>
+#include <goofit/PDFs/physics/lineshapes/Bugg.h>
+#include <goofit/PDFs/physics/lineshapes/LASS.h>
+#include <goofit/PDFs/physics/lineshapes/RBW.h>
+#include <goofit/PDFs/physics/lineshapes/SBW.h>
+#include <goofit/PDFs/physics/detail/Dim5.h>
+#include <mcbooster/Generate.h>
+#include <mcbooster/EvaluateArray.h>
 #include <goofit/PDFs/physics/ResonancePdf.h>
 #include <goofit/UnbinnedDataSet.h>
 #include <goofit/Variable.h>
 
+#include <array>
 #include <chrono>
+#include <climits>
 #include <cstdio>
 #include <fstream>
 #include <map>
@@ -410,6 +424,192 @@ static void case_dalitz_fit() {
     put("dalitzfit.seconds", secs);
 }
 
+// ---- DP4 model (examples/DP4/DP4.cu:51-232) ------------------------------------------------------------
+struct DP4Model {
+    Observable m12{"m12", 0, 3}, m34{"m34", 0, 3}, cos12{"cos12", -1, 1}, cos34{"m34", -1, 1}, phi{"phi", -3.5, 3.5};
+    EventNumber eventNumber{"eventNumber", 0, INT_MAX};
+    std::vector<Variable> lsvars; // RhoMass, RhoWidth, KstarM, KstarW, ...
+    std::vector<Variable> coefs;
+    DecayInfo4 info;
+    GooPdf *eff = nullptr;
+    Amp4Body *dp = nullptr;
+    PolynomialPdf *backgr = nullptr;
+    AddPdf *signal = nullptr;
+};
+static DP4Model *make_dp4(unsigned int mcEvents, bool float_ls) {
+    auto *M = new DP4Model();
+    const fptype mD0 = 1.8645, piP = 0.13957018, Km = 0.493677;
+    M->info.meson_radius    = 1.5;
+    M->info.particle_masses = {mD0, piP, piP, Km, piP};
+    auto V = [&](const char *n, double v, double lo, double hi) {
+        Variable x = float_ls ? Variable(n, v, 0.001, lo, hi) : Variable(n, v);
+        M->lsvars.push_back(x);
+        return x;
+    };
+    Variable RhoMass = V("rho_mass", 0.77526, 0.6, 0.9), RhoWidth = V("rho_width", 0.1478, 0.05, 0.3);
+    Variable KstarM = V("KstarM", 0.89581, 0.8, 1.0), KstarW = V("KstarW", 0.0474, 0.01, 0.1);
+    Variable f600M = V("f600M", 0.519, 0.3, 0.7), f600W = V("f600W", 0.454, 0.2, 0.7);
+    Variable a1M = V("a1M", 1.23, 1.0, 1.5), a1W = V("a1W", 0.42, 0.2, 0.7);
+    Variable K1M = V("K1M", 1.272, 1.1, 1.4), K1W = V("K1W", 0.09, 0.03, 0.2);
+    Variable K1430M = V("K1430M", 1.414, 1.2, 1.6), K1430W = V("K1430W", 0.29, 0.1, 0.5);
+    auto SF2 = [&](SF_4Body k, std::array<int, 4> a, std::array<int, 4> b) {
+        return std::vector<SpinFactor *>{new SpinFactor("SF", k, mD0, a[0], a[1], a[2], a[3]),
+                                         new SpinFactor("SF", k, mD0, b[0], b[1], b[2], b[3])};
+    };
+    auto SFKRS = SF2(SF_4Body::DtoV1V2_V1toP1P2_V2toP3P4_S, {0, 1, 2, 3}, {3, 1, 2, 0});
+    auto SFKRP = SF2(SF_4Body::DtoV1V2_V1toP1P2_V2toP3P4_P, {0, 1, 2, 3}, {3, 1, 2, 0});
+    auto SFKRD = SF2(SF_4Body::DtoV1V2_V1toP1P2_V2toP3P4_D, {0, 1, 2, 3}, {3, 1, 2, 0});
+    auto SFKF  = SF2(SF_4Body::DtoVS_VtoP1P2_StoP3P4, {2, 3, 0, 1}, {2, 0, 3, 1});
+    auto SFKK  = SF2(SF_4Body::DtoAP1_AtoSP2_StoP3P4, {0, 1, 3, 2}, {3, 1, 0, 2});
+    auto SFK1R = SF2(SF_4Body::DtoAP1_AtoVP2_VtoP3P4, {3, 2, 0, 1}, {0, 2, 3, 1});
+    auto SFA1R = SF2(SF_4Body::DtoAP1_AtoVP2_VtoP3P4, {2, 3, 0, 1}, {2, 0, 3, 1});
+    auto SFA1RD = SF2(SF_4Body::DtoAP1_AtoVP2Dwave_VtoP3P4, {2, 3, 0, 1}, {2, 0, 3, 1});
+    auto rho = [&](unsigned p) { return (Lineshape *)new Lineshapes::RBW("rho(770)", RhoMass, RhoWidth, 1, p); };
+    auto kst = [&](unsigned p) { return (Lineshape *)new Lineshapes::RBW("K*(892)bar", KstarM, KstarW, 1, p); };
+    std::vector<Lineshape *> LSKRS = {rho(M_12), kst(M_34), rho(M_24), kst(M_13)};
+    std::vector<Lineshape *> LSKRP = {rho(M_12), kst(M_34), rho(M_24), kst(M_13)};
+    std::vector<Lineshape *> LSKRD = {rho(M_12), kst(M_34), rho(M_24), kst(M_13)};
+    std::vector<Lineshape *> LSKF  = {kst(M_34), new Lineshapes::Bugg("f600", f600M, f600W, 0, M_12), kst(M_13),
+                                      new Lineshapes::Bugg("f600", f600M, f600W, 0, M_24)};
+    std::vector<Lineshape *> LSKK  = {new Lineshapes::SBW("K(1)(1270)bar", K1M, K1W, 1, M_34_2),
+                                      new Lineshapes::LASS("K(0)*(1430)bar", K1430M, K1430W, 0, M_34),
+                                      new Lineshapes::SBW("K(1)(1270)bar2", K1M, K1W, 1, M_13_2),
+                                      new Lineshapes::LASS("K(0)*(1430)bar2", K1430M, K1430W, 0, M_13)};
+    std::vector<Lineshape *> LSK1R = {new Lineshapes::SBW("K(1)(1270)bar", K1M, K1W, 0, M_12_3), rho(M_12),
+                                      new Lineshapes::SBW("K(1)(1270)bar", K1M, K1W, 0, M_24_3), rho(M_24)};
+    std::vector<Lineshape *> LSA1R = {new Lineshapes::SBW("a(1)(1260)+", a1M, a1W, 0, M_12_4), rho(M_12),
+                                      new Lineshapes::SBW("a(1)(1260)+", a1M, a1W, 0, M_24_1), rho(M_24)};
+    std::vector<Lineshape *> LSA1RD = {new Lineshapes::SBW("a(1)(1260)+", a1M, a1W, 2, M_12_4), rho(M_12),
+                                       new Lineshapes::SBW("a(1)(1260)+", a1M, a1W, 2, M_24_1), rho(M_24)};
+    auto C = [&](const char *n, double v, bool fl) {
+        Variable x = fl ? Variable(n, v, 0.001, 0, 0) : Variable(n, v);
+        M->coefs.push_back(x);
+        return x;
+    };
+    auto *AS  = new Amplitude("K*(892)rho(770)_S", C("amp_real1", -0.1, true), C("amp_imag1", 0.1, true), LSKRS, SFKRS, 2);
+    auto *AP  = new Amplitude("K*(892)rho(770)_P", C("amp_real2", -0.02, true), C("amp_imag2", -0.07, true), LSKRP, SFKRP, 2);
+    auto *AD  = new Amplitude("K*(892)rho(770)_D", C("amp_real3", -0.4, true), C("amp_imag3", 0.4, true), LSKRD, SFKRD, 2);
+    auto *KF  = new Amplitude("KF", C("amp_real4", 0.0120787, false), C("amp_imag4", -0.0332525, false), LSKF, SFKF, 2);
+    auto *KK  = new Amplitude("LSKK", C("amp_real5", 0.0109033, false), C("amp_imag5", -0.00186219, false), LSKK, SFKK, 2);
+    auto *K1R = new Amplitude("LSK1R", C("amp_real6", -0.10728, false), C("amp_imag6", -0.130213, false), LSK1R, SFK1R, 2);
+    auto *A1R = new Amplitude("LSA1R", C("amp_real7", 1.0, false), C("amp_imag7", 0.0, false), LSA1R, SFA1R, 2);
+    auto *A1RD = new Amplitude("LSA1RD", C("amp_real8", -0.94921, false), C("amp_imag8", -1.73407, false), LSA1RD, SFA1RD, 2);
+    M->info.amplitudes = {KF, AS, AP, AD, KK, K1R, A1R, A1RD};
+    Variable one("constantOne", 1), zero("constantZero", 0);
+    std::vector<Observable> obs = {M->m12, M->m34, M->cos12, M->cos34, M->phi, M->eventNumber};
+    M->eff = new PolynomialPdf("constantEff", obs, std::vector<Variable>{one}, std::vector<Variable>{zero, zero}, 0);
+    M->dp  = new Amp4Body("test", obs, M->info, M->eff, mcEvents);
+    Variable constant("constant", 0.1), constant2("constant2", 1.0);
+    M->backgr = new PolynomialPdf("backgr", M->m12, {constant});
+    M->signal = new AddPdf("signal", constant2, M->dp, M->backgr);
+    return M;
+}
+// phase-space data events through the shim generator + the reference's own Dim5 map
+static void fill_dp4_phsp(DP4Model &M, UnbinnedDataSet &d, size_t n, long seed) {
+    std::vector<mcbooster::GReal_t> masses(M.info.particle_masses.begin() + 1, M.info.particle_masses.end());
+    mcbooster::PhaseSpace phsp(M.info.particle_masses[0], masses, n, seed);
+    phsp.Generate(mcbooster::Vector4R(M.info.particle_masses[0], 0.0, 0.0, 0.0));
+    auto d1 = phsp.GetDaughters(0), d2 = phsp.GetDaughters(1), d3 = phsp.GetDaughters(2), d4 = phsp.GetDaughters(3);
+    mcbooster::ParticlesSet_d pset = {&d1, &d2, &d3, &d4};
+    mcbooster::RealVector_d v0(n), v1(n), v2(n), v3(n), v4(n);
+    mcbooster::VariableSet_d vs = {&v0, &v1, &v2, &v3, &v4};
+    Dim5 eval;
+    mcbooster::EvaluateArray<Dim5>(eval, pset, vs);
+    for(size_t i = 0; i < n; i++) {
+        M.m12.setValue(v0[i]); M.m34.setValue(v1[i]); M.cos12.setValue(v2[i]); M.cos34.setValue(v3[i]); M.phi.setValue(v4[i]);
+        M.eventNumber.setValue(d.getNumEvents());
+        d.addEvent();
+    }
+}
+static std::vector<double> host_copy(const mcbooster::RealVector_d &v) { return std::vector<double>(v.begin(), v.end()); }
+
+static void case_dp4() {
+    DP4Model *M = make_dp4(12000, true);
+    UnbinnedDataSet d({M->m12, M->m34, M->cos12, M->cos34, M->phi, M->eventNumber});
+    fill_dp4_phsp(*M, d, 500, 4242);
+    save_npy("dp4.m12", column(d, M->m12)); save_npy("dp4.m34", column(d, M->m34)); save_npy("dp4.cos12", column(d, M->cos12));
+    save_npy("dp4.cos34", column(d, M->cos34)); save_npy("dp4.phi", column(d, M->phi));
+    Amp4Body *dp = M->dp;
+    save_npy("dp4.mc_m12", host_copy(dp->norm_M12)); save_npy("dp4.mc_m34", host_copy(dp->norm_M34));
+    save_npy("dp4.mc_cos12", host_copy(dp->norm_CosTheta12)); save_npy("dp4.mc_cos34", host_copy(dp->norm_CosTheta34));
+    save_npy("dp4.mc_phi", host_copy(dp->norm_phi));
+    put("dp4.mc_events", dp->getMCevents());
+    GooPdf *sig = M->signal;
+    sig->setData(&d);
+    dp->setDataSize(d.getNumEvents(), 6);
+    put("dp4.nll", sig->calculateNLL());
+    put("dp4.integral", 1.0 / dp->getNormalization());
+    { // cached data amplitudes, [evt * nAmp + a]
+        std::vector<double> amps;
+        thrust::host_vector<fpcomplex> h = *(dp->cachedAMPs);
+        for(size_t i = 0; i < h.size(); i++) { amps.push_back(h[i].real()); amps.push_back(h[i].imag()); }
+        save_npy("dp4.amps", amps.data(), d.getNumEvents(), 16);
+    }
+    auto probs = sig->getCompProbsAtDataPoints();
+    save_npy("dp4.prob", probs[0]);
+    sig->setFitControl(std::make_shared<UnbinnedNllFit>());
+    sig->setData(&d);
+    dp->setDataSize(d.getNumEvents(), 6);
+    put("dp4.nll_again", sig->calculateNLL());
+    // coefficients move, lineshapes stay
+    for(auto &v : M->lsvars) v.setChanged(false);
+    sig->updateVariable(M->coefs[0], -0.12); sig->updateVariable(M->coefs[5], 0.45); sig->updateParameters();
+    put("dp4.nll_coef_moved", sig->calculateNLL());
+    put("dp4.integral_coef_moved", 1.0 / dp->getNormalization());
+    // the K*(892) mass moves: lineshape index 0 (first unique lineshape) is flagged
+    M->lsvars[2].setChanged(true);
+    sig->updateVariable(M->lsvars[2], 0.8975); sig->updateParameters();
+    put("dp4.nll_kstar_moved", sig->calculateNLL());
+    put("dp4.integral_kstar_moved", 1.0 / dp->getNormalization());
+}
+
+static void case_dp4_fit() {
+    DP4Model *M = make_dp4(60000, false);
+    UnbinnedDataSet cand({M->m12, M->m34, M->cos12, M->cos34, M->phi, M->eventNumber});
+    fill_dp4_phsp(*M, cand, 40000, 99);
+    GooPdf *sig = M->signal;
+    Amp4Body *dp = M->dp;
+    // toy at the "correct fixed values" of DP4.cu:140-145
+    double truth[6] = {-0.115177, 0.153976, -0.0298697, -0.0722874, -0.452212, 0.426521};
+    for(int k = 0; k < 6; k++) { M->coefs[k].setValue(truth[k]); }
+    sig->setData(&cand);
+    dp->setDataSize(cand.getNumEvents(), 6);
+    auto probs = sig->getCompProbsAtDataPoints()[0];
+    double pmax = 0;
+    for(double p : probs) pmax = std::max(pmax, p);
+    std::mt19937_64 gen(100);
+    std::uniform_real_distribution<double> u(0, 1);
+    UnbinnedDataSet d({M->m12, M->m34, M->cos12, M->cos34, M->phi, M->eventNumber});
+    for(size_t i = 0; i < probs.size(); i++) {
+        if(u(gen) * pmax > probs[i]) continue;
+        M->m12.setValue(cand.getValue(M->m12, i)); M->m34.setValue(cand.getValue(M->m34, i));
+        M->cos12.setValue(cand.getValue(M->cos12, i)); M->cos34.setValue(cand.getValue(M->cos34, i));
+        M->phi.setValue(cand.getValue(M->phi, i)); M->eventNumber.setValue(d.getNumEvents());
+        d.addEvent();
+    }
+    save_npy("dp4fit.m12", column(d, M->m12)); save_npy("dp4fit.m34", column(d, M->m34)); save_npy("dp4fit.cos12", column(d, M->cos12));
+    save_npy("dp4fit.cos34", column(d, M->cos34)); save_npy("dp4fit.phi", column(d, M->phi));
+    save_npy("dp4fit.mc_m12", host_copy(dp->norm_M12)); save_npy("dp4fit.mc_m34", host_copy(dp->norm_M34));
+    save_npy("dp4fit.mc_cos12", host_copy(dp->norm_CosTheta12)); save_npy("dp4fit.mc_cos34", host_copy(dp->norm_CosTheta34));
+    save_npy("dp4fit.mc_phi", host_copy(dp->norm_phi));
+    double start[6] = {-0.1, 0.1, -0.02, -0.07, -0.4, 0.4};
+    for(int k = 0; k < 6; k++) M->coefs[k].setValue(start[k]);
+    sig->setFitControl(std::make_shared<UnbinnedNllFit>());
+    sig->setData(&d);
+    dp->setDataSize(d.getNumEvents(), 6);
+    FitManager fit(sig);
+    fit.setVerbosity(0);
+    put("dp4fit.nll_start", (*fit.getFCN())());
+    auto fm = fit.fit();
+    std::vector<double> val, err;
+    for(int k = 0; k < 6; k++) { val.push_back(M->coefs[k].getValue()); err.push_back(M->coefs[k].getError()); }
+    put_vec("dp4fit.values", val);
+    put_vec("dp4fit.errors", err);
+    put("dp4fit.fval", fm.Fval());
+    put("dp4fit.nfcn", fm.NFcn());
+    put("dp4fit.valid", (double)(int)fm.IsValid());
+}
+
 // ---- CPU baseline timing ------------------------------------------------------------------------
 // Each step = one Minuit-style call: coefficients move (masses/widths fixed as dalitz.cpp:298-305),
 // Params::from_minuit_vector semantics (Params.cpp:47-57) then calculateNLL().
@@ -492,6 +692,8 @@ int main(int argc, char **argv) {
             if(only == "all" || only == "basic") case_basic();
             if(only == "all" || only == "dalitz") case_dalitz();
             if(only == "all" || only == "dalitzfit") case_dalitz_fit();
+            if(only == "all" || only == "dp4") case_dp4();
+            if(only == "all" || only == "dp4fit") case_dp4_fit();
             std::ofstream f(g_out + "/manifest" + (only == "all" ? "" : "_" + only) + ".json");
             f << "{\n" << g_manifest.str() << "\n}\n";
             return 0;

@@ -116,3 +116,84 @@ def dalitz_uniform_events(n, seed):
         a = np.concatenate([a, x[ok]])
         b = np.concatenate([b, y[ok]])
     return np.ascontiguousarray(a[:n]), np.ascontiguousarray(b[:n])
+
+
+class DP4:
+    """D0 -> K- pi+ pi+ pi-: 8 Bose-symmetrised amplitudes (examples/DP4/DP4.cu:51-232), AddPdf(1.0; Amp4Body, flat bkg)."""
+
+    def __init__(self, mc_events=0, float_ls=False):
+        k = self.keep = Keep()
+        O, V = gf.Observable, gf.Variable
+        self.m12, self.m34 = O("m12", 0, 3), O("m34", 0, 3)
+        self.cos12, self.cos34, self.phi = O("cos12", -1, 1), O("cos34", -1, 1), O("phi", -3.5, 3.5)
+        self.evt = gf.EventNumber("eventNumber", 0, 2147483647)
+        mD0, piP, Km = 1.8645, 0.13957018, 0.493677
+        info = self.info = gf.DecayInfo4()
+        info.meson_radius = 1.5
+        info.particle_masses = [mD0, piP, piP, Km, piP]
+        self.lsvars = []
+
+        def LV(n, v, lo, hi):
+            x = V(n, v, 0.001, lo, hi) if float_ls else V(n, v)
+            self.lsvars.append(x)
+            return x
+
+        RhoMass, RhoWidth = LV("rho_mass", 0.77526, 0.6, 0.9), LV("rho_width", 0.1478, 0.05, 0.3)
+        KstarM, KstarW = LV("KstarM", 0.89581, 0.8, 1.0), LV("KstarW", 0.0474, 0.01, 0.1)
+        f600M, f600W = LV("f600M", 0.519, 0.3, 0.7), LV("f600W", 0.454, 0.2, 0.7)
+        a1M, a1W = LV("a1M", 1.23, 1.0, 1.5), LV("a1W", 0.42, 0.2, 0.7)
+        K1M, K1W = LV("K1M", 1.272, 1.1, 1.4), LV("K1W", 0.09, 0.03, 0.2)
+        K1430M, K1430W = LV("K1430M", 1.414, 1.2, 1.6), LV("K1430W", 0.29, 0.1, 0.5)
+        S = gf.SF_4Body
+
+        def SF2(kind, a, b):
+            return [k(gf.SpinFactor("SF", kind, mD0, *a)), k(gf.SpinFactor("SF", kind, mD0, *b))]
+
+        SFKRS = SF2(S.DtoV1V2_V1toP1P2_V2toP3P4_S, (0, 1, 2, 3), (3, 1, 2, 0))
+        SFKRP = SF2(S.DtoV1V2_V1toP1P2_V2toP3P4_P, (0, 1, 2, 3), (3, 1, 2, 0))
+        SFKRD = SF2(S.DtoV1V2_V1toP1P2_V2toP3P4_D, (0, 1, 2, 3), (3, 1, 2, 0))
+        SFKF = SF2(S.DtoVS_VtoP1P2_StoP3P4, (2, 3, 0, 1), (2, 0, 3, 1))
+        SFKK = SF2(S.DtoAP1_AtoSP2_StoP3P4, (0, 1, 3, 2), (3, 1, 0, 2))
+        SFK1R = SF2(S.DtoAP1_AtoVP2_VtoP3P4, (3, 2, 0, 1), (0, 2, 3, 1))
+        SFA1R = SF2(S.DtoAP1_AtoVP2_VtoP3P4, (2, 3, 0, 1), (2, 0, 3, 1))
+        SFA1RD = SF2(S.DtoAP1_AtoVP2Dwave_VtoP3P4, (2, 3, 0, 1), (2, 0, 3, 1))
+        L = gf.Lineshapes
+        rho = lambda p: k(L.RBW("rho(770)", RhoMass, RhoWidth, 1, int(p)))
+        kst = lambda p: k(L.RBW("K*(892)bar", KstarM, KstarW, 1, int(p)))
+        P = gf.DP4Pair
+        LSKRS = [rho(P.M_12), kst(P.M_34), rho(P.M_24), kst(P.M_13)]
+        LSKRP = [rho(P.M_12), kst(P.M_34), rho(P.M_24), kst(P.M_13)]
+        LSKRD = [rho(P.M_12), kst(P.M_34), rho(P.M_24), kst(P.M_13)]
+        LSKF = [kst(P.M_34), k(L.Bugg("f600", f600M, f600W, 0, int(P.M_12))), kst(P.M_13), k(L.Bugg("f600", f600M, f600W, 0, int(P.M_24)))]
+        LSKK = [k(L.SBW("K(1)(1270)bar", K1M, K1W, 1, int(P.M_34_2))), k(L.LASS("K(0)*(1430)bar", K1430M, K1430W, 0, int(P.M_34))),
+                k(L.SBW("K(1)(1270)bar2", K1M, K1W, 1, int(P.M_13_2))), k(L.LASS("K(0)*(1430)bar2", K1430M, K1430W, 0, int(P.M_13)))]
+        LSK1R = [k(L.SBW("K(1)(1270)bar", K1M, K1W, 0, int(P.M_12_3))), rho(P.M_12), k(L.SBW("K(1)(1270)bar", K1M, K1W, 0, int(P.M_24_3))), rho(P.M_24)]
+        LSA1R = [k(L.SBW("a(1)(1260)+", a1M, a1W, 0, int(P.M_12_4))), rho(P.M_12), k(L.SBW("a(1)(1260)+", a1M, a1W, 0, int(P.M_24_1))), rho(P.M_24)]
+        LSA1RD = [k(L.SBW("a(1)(1260)+", a1M, a1W, 2, int(P.M_12_4))), rho(P.M_12), k(L.SBW("a(1)(1260)+", a1M, a1W, 2, int(P.M_24_1))), rho(P.M_24)]
+        self.coefs = []
+
+        def Cf(n, v, fl):
+            x = V(n, v, 0.001, 0, 0) if fl else V(n, v)
+            self.coefs.append(x)
+            return x
+
+        A = gf.Amplitude
+        AS = k(A("K*(892)rho(770)_S", Cf("amp_real1", -0.1, True), Cf("amp_imag1", 0.1, True), LSKRS, SFKRS, 2))
+        AP = k(A("K*(892)rho(770)_P", Cf("amp_real2", -0.02, True), Cf("amp_imag2", -0.07, True), LSKRP, SFKRP, 2))
+        AD = k(A("K*(892)rho(770)_D", Cf("amp_real3", -0.4, True), Cf("amp_imag3", 0.4, True), LSKRD, SFKRD, 2))
+        KF = k(A("KF", Cf("amp_real4", 0.0120787, False), Cf("amp_imag4", -0.0332525, False), LSKF, SFKF, 2))
+        KK = k(A("LSKK", Cf("amp_real5", 0.0109033, False), Cf("amp_imag5", -0.00186219, False), LSKK, SFKK, 2))
+        K1R = k(A("LSK1R", Cf("amp_real6", -0.10728, False), Cf("amp_imag6", -0.130213, False), LSK1R, SFK1R, 2))
+        A1R = k(A("LSA1R", Cf("amp_real7", 1.0, False), Cf("amp_imag7", 0.0, False), LSA1R, SFA1R, 2))
+        A1RD = k(A("LSA1RD", Cf("amp_real8", -0.94921, False), Cf("amp_imag8", -1.73407, False), LSA1RD, SFA1RD, 2))
+        for a in (KF, AS, AP, AD, KK, K1R, A1R, A1RD):
+            info.add_amplitude(a)
+        self.observables = [self.m12, self.m34, self.cos12, self.cos34, self.phi, self.evt]
+        self.eff = k(gf.PolynomialPdf("constantEff", self.observables, [V("constantOne", 1)], [V("constantZero", 0)] * 2, 0))
+        self.dp = gf.Amp4Body("test", self.observables, info, self.eff, mc_events)
+        self.backgr = k(gf.PolynomialPdf("backgr", self.m12, [V("constant", 0.1)]))
+        self.signal = gf.AddPdf("signal", V("constant2", 1.0), self.dp, self.backgr)
+
+    def dataset(self, cols5):
+        n = len(cols5[0])
+        return dataset_from_columns(self.observables, list(cols5) + [np.arange(n, dtype=np.float64)])

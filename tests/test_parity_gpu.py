@@ -263,3 +263,46 @@ def test_run_to_run_bit_reproducible():
         M.signal.setDataSize(len(d))
         vals.append(M.signal.calculateNLL())
     assert vals[0] == vals[1] == vals[2]
+
+
+def test_dp4_values(golden):
+    from models import DP4
+    M = DP4(mc_events=0, float_ls=True)
+    cols = [golden.arr("dp4." + n) for n in ("m12", "m34", "cos12", "cos34", "phi")]
+    mc = np.vstack([golden.arr("dp4.mc_" + n) for n in ("m12", "m34", "cos12", "cos34", "phi")])
+    assert mc.shape[1] == int(golden["dp4.mc_events"])
+    M.dp.setNormEvents(mc)
+    d = M.dataset(cols)
+    sig, dp = M.signal, M.dp
+    assert dp.numLineshapes() == 12 and dp.numSpinFactors() == 16
+    sig.setData(d)
+    dp.setDataSize(len(d), 6)
+    nll = sig.calculateNLL()
+    ref = golden.arr("dp4.amps")  # [event, 2*amp]
+    for a in range(8):
+        w = np.asarray(dp.getCachedAmp(a))
+        r = ref[:, 2 * a] + 1j * ref[:, 2 * a + 1]
+        assert np.max(np.abs(w - r) / np.maximum(np.abs(r), 1e-300)) < 1e-10, a
+    assert rel(1.0 / dp.getNormalization(), golden["dp4.integral"]) < 1e-12
+    assert rel(nll, golden["dp4.nll"]) < RTOL_NLL
+    probs = sig.getCompProbsAtDataPoints()
+    np.testing.assert_allclose(probs[0], golden.arr("dp4.prob"), rtol=1e-10, atol=0)
+    sig.setFitControl(gf.UnbinnedNllFit())
+    sig.setData(d)
+    dp.setDataSize(len(d), 6)
+    assert sig.calculateNLL() == nll
+    for v in M.lsvars:
+        v.changed = False
+    sig.updateVariable(M.coefs[0], -0.12)
+    sig.updateVariable(M.coefs[5], 0.45)
+    sig.updateParameters()
+    before = gf.launch_count()
+    assert rel(sig.calculateNLL(), golden["dp4.nll_coef_moved"]) < RTOL_NLL
+    assert rel(1.0 / dp.getNormalization(), golden["dp4.integral_coef_moved"]) < 1e-12
+    # steady state: backgr grid integral + MC integral + NLL kernel
+    assert gf.launch_count() - before == 3
+    M.lsvars[2].changed = True
+    sig.updateVariable(M.lsvars[2], 0.8975)
+    sig.updateParameters()
+    assert rel(sig.calculateNLL(), golden["dp4.nll_kstar_moved"]) < RTOL_NLL
+    assert rel(1.0 / dp.getNormalization(), golden["dp4.integral_kstar_moved"]) < 1e-12
