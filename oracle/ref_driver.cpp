@@ -486,14 +486,22 @@ static DP4Model *make_dp4(unsigned int mcEvents, bool float_ls) {
         M->coefs.push_back(x);
         return x;
     };
-    auto *AS  = new Amplitude("K*(892)rho(770)_S", C("amp_real1", -0.1, true), C("amp_imag1", 0.1, true), LSKRS, SFKRS, 2);
-    auto *AP  = new Amplitude("K*(892)rho(770)_P", C("amp_real2", -0.02, true), C("amp_imag2", -0.07, true), LSKRP, SFKRP, 2);
-    auto *AD  = new Amplitude("K*(892)rho(770)_D", C("amp_real3", -0.4, true), C("amp_imag3", 0.4, true), LSKRD, SFKRD, 2);
-    auto *KF  = new Amplitude("KF", C("amp_real4", 0.0120787, false), C("amp_imag4", -0.0332525, false), LSKF, SFKF, 2);
-    auto *KK  = new Amplitude("LSKK", C("amp_real5", 0.0109033, false), C("amp_imag5", -0.00186219, false), LSKK, SFKK, 2);
-    auto *K1R = new Amplitude("LSK1R", C("amp_real6", -0.10728, false), C("amp_imag6", -0.130213, false), LSK1R, SFK1R, 2);
-    auto *A1R = new Amplitude("LSA1R", C("amp_real7", 1.0, false), C("amp_imag7", 0.0, false), LSA1R, SFA1R, 2);
-    auto *A1RD = new Amplitude("LSA1RD", C("amp_real8", -0.94921, false), C("amp_imag8", -1.73407, false), LSA1RD, SFA1RD, 2);
+    Variable AS_re = C("amp_real1", -0.1, true), AS_im = C("amp_imag1", 0.1, true);
+    auto *AS = new Amplitude("K*(892)rho(770)_S", AS_re, AS_im, LSKRS, SFKRS, 2);
+    Variable AP_re = C("amp_real2", -0.02, true), AP_im = C("amp_imag2", -0.07, true);
+    auto *AP = new Amplitude("K*(892)rho(770)_P", AP_re, AP_im, LSKRP, SFKRP, 2);
+    Variable AD_re = C("amp_real3", -0.4, true), AD_im = C("amp_imag3", 0.4, true);
+    auto *AD = new Amplitude("K*(892)rho(770)_D", AD_re, AD_im, LSKRD, SFKRD, 2);
+    Variable KF_re = C("amp_real4", 0.0120787, false), KF_im = C("amp_imag4", -0.0332525, false);
+    auto *KF = new Amplitude("KF", KF_re, KF_im, LSKF, SFKF, 2);
+    Variable KK_re = C("amp_real5", 0.0109033, false), KK_im = C("amp_imag5", -0.00186219, false);
+    auto *KK = new Amplitude("LSKK", KK_re, KK_im, LSKK, SFKK, 2);
+    Variable K1R_re = C("amp_real6", -0.10728, false), K1R_im = C("amp_imag6", -0.130213, false);
+    auto *K1R = new Amplitude("LSK1R", K1R_re, K1R_im, LSK1R, SFK1R, 2);
+    Variable A1R_re = C("amp_real7", 1.0, false), A1R_im = C("amp_imag7", 0.0, false);
+    auto *A1R = new Amplitude("LSA1R", A1R_re, A1R_im, LSA1R, SFA1R, 2);
+    Variable A1RD_re = C("amp_real8", -0.94921, false), A1RD_im = C("amp_imag8", -1.73407, false);
+    auto *A1RD = new Amplitude("LSA1RD", A1RD_re, A1RD_im, LSA1RD, SFA1RD, 2);
     M->info.amplitudes = {KF, AS, AP, AD, KK, K1R, A1R, A1RD};
     Variable one("constantOne", 1), zero("constantZero", 0);
     std::vector<Observable> obs = {M->m12, M->m34, M->cos12, M->cos34, M->phi, M->eventNumber};

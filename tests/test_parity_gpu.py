@@ -274,7 +274,7 @@ def test_dp4_values(golden):
     M.dp.setNormEvents(mc)
     d = M.dataset(cols)
     sig, dp = M.signal, M.dp
-    assert dp.numLineshapes() == 12 and dp.numSpinFactors() == 16
+    assert dp.numLineshapes() == 16 and dp.numSpinFactors() == 16
     sig.setData(d)
     dp.setDataSize(len(d), 6)
     nll = sig.calculateNLL()
@@ -306,3 +306,24 @@ def test_dp4_values(golden):
     sig.updateParameters()
     assert rel(sig.calculateNLL(), golden["dp4.nll_kstar_moved"]) < RTOL_NLL
     assert rel(1.0 / dp.getNormalization(), golden["dp4.integral_kstar_moved"]) < 1e-12
+
+
+def test_dp4_fit_matches_reference(golden):
+    from models import DP4
+    M = DP4(mc_events=0, float_ls=False)
+    names = ("m12", "m34", "cos12", "cos34", "phi")
+    M.dp.setNormEvents(np.vstack([golden.arr("dp4fit.mc_" + n) for n in names]))
+    d = M.dataset([golden.arr("dp4fit." + n) for n in names])
+    sig, dp = M.signal, M.dp
+    sig.setData(d)
+    dp.setDataSize(len(d), 6)
+    fm = gf.FitManager(sig)
+    fm.setVerbosity(0)
+    assert rel(fm.getFCN()(), golden["dp4fit.nll_start"]) < RTOL_NLL
+    res = fm.fit()
+    assert bool(fm)
+    val, err = np.array(golden["dp4fit.values"]), np.array(golden["dp4fit.errors"])
+    mine = np.array([c.value for c in M.coefs[:6]])
+    pulls = np.abs(mine - val) / err
+    assert pulls.max() < 0.01, pulls
+    assert rel(res.Fval(), golden["dp4fit.fval"]) < 1e-9
