@@ -21,6 +21,10 @@ M2OBJ    := $(patsubst $(REF)/extern/Minuit2/src/%.cxx,build/minuit2/%.o,$(M2SRC
 HSRC     := $(wildcard $(HOST)/src/*.cpp)
 HOBJ     := $(patsubst $(HOST)/src/%.cpp,build/host/%.o,$(HSRC))
 HFLAGS   := -O2 -std=c++17 -fPIC -Wall -Wno-unused-function -Iinclude -I$(HOST)/include -I$(M2INC) -DMATHCORE_STANDALONE
+# This image's g++ wrapper points -lstdc++ at a dangling symlink and silently falls back to the static libstdc++.a,
+# which must never be embedded in several shared objects of one process: link the system's shared libstdc++ explicitly.
+SYSGCC   := $(firstword $(wildcard /usr/lib/gcc/x86_64-linux-gnu/*/libstdc++.so))
+LDSTD    := $(if $(SYSGCC),-L$(dir $(SYSGCC)),)
 PYEXT    := $(shell $(PYTHON) -c "import sysconfig; print(sysconfig.get_config_var('EXT_SUFFIX'))")
 PYINC    := $(shell $(PYTHON) -c "import sysconfig, pybind11; print('-I' + sysconfig.get_paths()['include'] + ' -I' + pybind11.get_include())")
 
@@ -43,14 +47,14 @@ build/minuit2/%.o: $(REF)/extern/Minuit2/src/%.cxx
 
 $(LIBDIR)/libMinuit2.so: $(M2OBJ)
 	@mkdir -p $(LIBDIR)
-	@if [ -n "$(M2OBJ)" ]; then $(CXX) -shared -o $@ $(M2OBJ); else test -f $@ || (echo "Minuit2 sources not found under $(REF) and no prebuilt $@"; false); fi
+	@if [ -n "$(M2OBJ)" ]; then $(CXX) -shared $(LDSTD) -o $@ $(M2OBJ); else test -f $@ || (echo "Minuit2 sources not found under $(REF) and no prebuilt $@"; false); fi
 
 build/host/%.o: $(HOST)/src/%.cpp $(wildcard $(HOST)/include/goofit/detail/*.h) include/goofit_b200.h
 	@mkdir -p build/host
 	$(CXX) $(HFLAGS) -c $< -o $@
 
 $(LIBDIR)/libgoofit_host.so: $(HOBJ) $(LIBDIR)/libgoofit_b200.so $(LIBDIR)/libMinuit2.so
-	$(CXX) -shared -o $@ $(HOBJ) -L$(LIBDIR) -lgoofit_b200 -lMinuit2 -Wl,-rpath,'$$ORIGIN'
+	$(CXX) -shared $(LDSTD) -o $@ $(HOBJ) -L$(LIBDIR) -lgoofit_b200 -lMinuit2 -Wl,-rpath,'$$ORIGIN'
 
 build/py/%.o: goofit_b200/python/%.cpp $(wildcard $(HOST)/include/goofit/detail/*.h)
 	@mkdir -p build/py
@@ -59,7 +63,7 @@ build/py/%.o: goofit_b200/python/%.cpp $(wildcard $(HOST)/include/goofit/detail/
 PYSRC := $(wildcard goofit_b200/python/*.cpp)
 PYOBJ := $(patsubst goofit_b200/python/%.cpp,build/py/%.o,$(PYSRC))
 goofit_b200/_goofit$(PYEXT): $(PYOBJ) $(LIBDIR)/libgoofit_host.so
-	$(CXX) -shared -o $@ $(PYOBJ) -L$(LIBDIR) -lgoofit_host -lgoofit_b200 -lMinuit2 -Wl,-rpath,'$$ORIGIN/lib'
+	$(CXX) -shared $(LDSTD) -o $@ $(PYOBJ) -L$(LIBDIR) -lgoofit_host -lgoofit_b200 -lMinuit2 -Wl,-rpath,'$$ORIGIN/lib'
 
 clean:
 	rm -rf build $(LIBDIR)/*.so goofit_b200/_goofit*.so

@@ -44,6 +44,12 @@ PYBIND11_MODULE(_goofit, m) {
           "copy of the flattened parameter block as last pushed by updateParameters()");
     m.def("program_norms", [] { return py::array(py::cast(detail::Engine::get().prog.norms)); });
     m.def("local_events", [] { return detail::Engine::get().localEvents; });
+    m.def("shard_range",
+          [](size_t n, int rank, int size) { // the split PdfBase::setData applies (reference PdfBase.cu:364-378)
+              size_t per = n / size, first = per * rank, count = rank == size - 1 ? n - first : per;
+              return py::make_tuple(first, count);
+          },
+          "n"_a, "rank"_a, "size"_a);
     m.def("shutdown", [] { detail::Engine::get().shutdown(); });
 
     // ---- variables ----

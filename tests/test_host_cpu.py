@@ -1,0 +1,213 @@
+"""CPU-side tests (no GPU): host API semantics, the C-ABI surface, the oracle's fixtures against the reference's own
+known answers, and the multi-rank sharding logic over gloo."""
+import ctypes
+import math
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+import goofit_b200 as gf
+from goofit_b200 import capi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def header_symbols():
+    with open(os.path.join(ROOT, "include", "goofit_b200.h")) as f:
+        text = f.read()
+    return sorted(set(re.findall(r"\b(gf_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_capi_exports_every_declared_symbol():
+    lib = ctypes.CDLL(capi.PATH)
+    names = header_symbols()
+    assert len(names) >= 38
+    for n in names:
+        assert hasattr(lib, n), "libgoofit_b200.so does not export %s" % n
+    assert set(capi.SYMBOLS) <= set(names)
+    lib.gf_version.restype = ctypes.c_int
+    assert lib.gf_version() >= 100
+
+
+def test_no_cpu_fallback():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a CUDA device is present")
+    x = gf.Observable("x", 0, 10)
+    pdf = gf.ExpPdf("e", x, gf.Variable("a", -1, 0.1, -10, 10))
+    d = gf.UnbinnedDataSet(x)
+    d.from_matrix(np.array([[1.0, 2.0, 3.0]]))
+    with pytest.raises(gf.GeneralError, match="no CPU path"):
+        pdf.setData(d)
+
+
+def test_variable_semantics():
+    # reference Variable.h:148-175 and tests/simple/SimpleTest.cpp
+    c = gf.Variable("c", 1.5)
+    assert c.fixed and c.value == 1.5
+    e = gf.Variable("e", 1.0, 0.1)
+    assert e.fixed and e.error == 0.1 and e.lowerlimit == e.upperlimit == 0
+    v = gf.Variable("v", 1.0, -2, 4)
+    assert not v.fixed and v.error == pytest.approx(0.6)
+    w = gf.Variable("w", 1.0, 0.2, -2, 4)
+    assert not w.fixed and w.error == 0.2 and bool(w)
+    w.value = 7
+    assert not bool(w)
+    o = gf.Observable("o", -1, 3)
+    assert o.numbins == 100 and o.bin_size == pytest.approx(0.04)
+    o.numbins = 20
+    assert o.getBinSize() == pytest.approx(0.2)
+    en = gf.EventNumber("evt")
+    assert en.value == 0 and en.upperlimit == 2.0 ** 53
+
+
+def test_unbinned_dataset():
+    x, y = gf.Observable("x", 0, 10), gf.Observable("y", -5, 5)
+    d = gf.UnbinnedDataSet(x, y)
+    x.value, y.value = 1, 2
+    d.addEvent()
+    x.value, y.value = 3, -4
+    d.addEvent()
+    assert len(d) == 2 and d.getValue(y, 1) == -4
+    m = d.to_matrix()
+    assert m.shape == (2, 2) and m[0, 1] == 3
+    x.value = 11
+    with pytest.raises(gf.GeneralError):
+        d.addEvent()
+    d.from_matrix(np.array([[5.0, 6.0], [0.5, 0.25]]))
+    assert len(d) == 4 and d.getValue(x, 3) == 6.0
+    with pytest.raises(gf.GeneralError):
+        d.from_matrix(np.array([[50.0], [0.5]]))
+    d.from_matrix(np.array([[50.0, 2.0], [0.5, 0.5]]), filter=True)
+    assert len(d) == 5
+    d.loadEvent(1)
+    assert x.value == 3 and y.value == -4
+    evt = gf.EventNumber("evt")
+    d2 = gf.UnbinnedDataSet(x, evt)
+    d2.from_matrix(np.array([[1.0, 2.0, 3.0]]))  # missing row -> running index
+    assert [d2.getValue(evt, i) for i in range(3)] == [0, 1, 2]
+
+
+def test_grid_layout_x_fastest():
+    # tests/simple/SimpleTest.cpp:81-127: the first observable is the fastest index
+    x, y = gf.Observable("x", 0, 4), gf.Observable("y", 0, 2)
+    x.numbins, y.numbins = 4, 2
+    d = gf.UnbinnedDataSet(x, y)
+    d.fillWithGrid()
+    m = d.to_matrix()
+    assert m.shape == (2, 8)
+    np.testing.assert_allclose(m[0], [0.5, 1.5, 2.5, 3.5] * 2)
+    np.testing.assert_allclose(m[1], [0.5] * 4 + [1.5] * 4)
+
+
+def test_binned_dataset():
+    x = gf.Observable("x", 0, 10)
+    x.numbins = 5
+    b = gf.BinnedDataSet(x)
+    for v in (0.5, 1.5, 2.5, 9.9):
+        x.value = v
+        b.addEvent()
+    assert b.getNumBins() == 5 and b.getBinContent(0) == 2 and b.getBinContent(1) == 1 and b.getBinContent(4) == 1
+    assert b.getBinCenter(0, 2) == pytest.approx(5.0) and b.getBinVolume(0) == pytest.approx(2.0)
+    assert b.getBinError(0) == pytest.approx(math.sqrt(2)) and b.getNumWeightedEvents() == 4
+
+
+def test_pdf_tree_bookkeeping():
+    x = gf.Observable("x", 0, 10)
+    m, s, a, f = gf.Variable("m", 4, 0.1, 0, 10), gf.Variable("s", 1, 0.1, 0.1, 5), gf.Variable("a", -1, 0.1, -5, 5), gf.Variable("f", 0.3, 0.1, 0, 1)
+    g, e = gf.GaussianPdf("g", x, m, s), gf.ExpPdf("e", x, a)
+    total = gf.AddPdf("t", f, g, e)
+    assert [p.name for p in total.getParameters()] == ["f", "m", "s", "a"]
+    assert [o.name for o in total.getObservables()] == ["x"]
+    assert g.hasAnalyticIntegral() and e.hasAnalyticIntegral() and not total.hasAnalyticIntegral()
+    assert e.integrate(0, 10) == pytest.approx((math.exp(-10) - 1) / -1)
+    assert g.integrate(0, 10) == pytest.approx(math.sqrt(2 * math.pi))  # over all of R, GaussianPdf.cu:28-35
+    total.updateVariable(m, 5.0)
+    assert m.value == 5.0
+    p = gf.Params(total)
+    assert p.size() == 4 and p.make_minuit_vector() == [0.3, 5.0, 1.0, -1.0]
+    with pytest.raises(gf.GeneralError):
+        gf.AddPdf("bad", [f, f, f], [g, e])
+
+
+def test_dim5_known_answers():
+    # tests/simple/VectorsTest.cu:13-36,78-92: (px,py,pz,E) x 4 -> (m12, m34, cos12, cos34, phi) to 1e-5
+    rows = np.array([
+        [-0.0200374, 0.246687, 0.410008, 0.687807, 0.203659, -0.0540155, 0.125961, 0.282384, -0.30315, -0.14159, -0.593475, 0.695442, 0.119529, -0.0510815, 0.057506, 0.199206],
+        [-0.533425, 0.24162, -0.34825, 0.841379, 0.467861, -0.190084, 0.0466843, 0.526008, 0.114051, 0.00314688, 0.287416, 0.339272, -0.0484866, -0.0546832, 0.0141501, 0.158181],
+        [-0.0825251, 0.103312, 0.273959, 0.579875, 0.156211, 0.386267, -0.193338, 0.480066, 0.162955, -0.25586, 0.16105, 0.370723, -0.236641, -0.233719, -0.241672, 0.434176],
+    ])
+    want = np.array([[0.763655, 0.665051, 0.109243, 0.913621, -3.07925], [1.33111, 0.386733, 0.536461, 0.836249, 1.16468],
+                     [0.933733, 0.62948, -0.506615, -0.141132, 1.98515]])
+    for r, w in zip(rows, want):
+        p = r.reshape(4, 4)[:, [3, 0, 1, 2]].ravel()  # -> (E, px, py, pz)
+        got = gf.fourVectorsToDim5(p)
+        np.testing.assert_allclose(got, w, rtol=2e-5, atol=2e-5)
+
+
+def test_phase_space_generator():
+    masses = [1.8645, 0.13957018, 0.13957018, 0.493677, 0.13957018]
+    c, w = gf.generatePhaseSpace5(masses, 2000, 7)
+    c2, _ = gf.generatePhaseSpace5(masses, 2000, 7)
+    assert np.array_equal(c, c2), "the generator must be deterministic"
+    assert np.all(c[0] > 2 * masses[1]) and np.all(c[1] > masses[3] + masses[4]) and np.all(c[0] + c[1] < masses[0])
+    assert np.all(np.abs(c[2]) <= 1) and np.all(np.abs(c[3]) <= 1) and np.all(np.abs(c[4]) <= math.pi)
+    assert np.all(w > 0) and np.all(w <= 1)
+
+
+def test_golden_known_answers(golden):
+    # the committed fixtures are outputs of the unmodified reference; pin them on the reference's own known answers
+    assert golden["exp.integrate_0_10"] == pytest.approx(0.5, rel=1e-8)  # NormalizeTest.cpp:42-44
+    assert golden["exp.normalize"] == pytest.approx(0.5, rel=1e-8)
+    assert golden["gauss.normalize"] == pytest.approx(6.26657, rel=1e-6)  # NormalizeTest.cpp:194
+    assert -1.01 < golden["exp.fit_alpha"] < -0.98  # examples/exponential/exponential.cpp:41-44 (2000 events here)
+    x = golden.arr("gauss.x")
+    want = np.exp(-0.5 * ((x - 1.5) / 2.5) ** 2) / (2.5 * math.sqrt(2 * math.pi))
+    np.testing.assert_allclose(golden.arr("gauss.prob"), want, rtol=1e-13)
+    np.testing.assert_allclose(golden.arr("add.prob"), 0.35 * golden.arr("add.comp0") + 0.65 * golden.arr("add.comp1"), rtol=1e-13)  # AddNormTest.cpp
+    x = golden.arr("exp.x")
+    nll = -np.sum(np.log(np.exp(-2 * x) / golden["exp.normalize"]))
+    assert golden["exp.nll"] == pytest.approx(nll, rel=1e-12)
+    assert golden["exp.nll"] == golden["exp.nll_again"]
+    assert golden["dalitzfit.valid"] == 1 and golden["dp4fit.valid"] == 1
+
+
+@pytest.mark.skipif(not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "ref_driver")), reason="oracle/_ref not built")
+def test_oracle_reproduces_fixtures(tmp_path, golden):
+    out = str(tmp_path / "g")
+    for case in ("basic", "dalitz", "dp4"):
+        subprocess.run([os.path.join(ROOT, "oracle", "_ref", "ref_driver"), "golden", out, case], check=True, capture_output=True, timeout=600)
+    for name in ("exp.prob", "conv.grid", "convadd.prob", "dalitz.waves", "dalitz.prob", "dp4.amps", "dp4.prob"):
+        np.testing.assert_allclose(np.load(os.path.join(out, name + ".npy")), golden.arr(name), rtol=1e-13, atol=0)
+
+
+WORKER = r"""
+import os, sys, numpy as np, torch, torch.distributed as dist
+sys.path.insert(0, sys.argv[1])
+import goofit_b200 as gf
+rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+dist.init_process_group("gloo", rank=rank, world_size=world)
+rng = np.random.default_rng(5)
+x = rng.exponential(1.0, 100003)
+first, count = gf.shard_range(len(x), rank, world)
+part = torch.tensor([float(np.sum(2.0 * x[first:first + count])), float(count)], dtype=torch.float64)
+dist.all_reduce(part)
+if rank == 0:
+    assert int(part[1]) == len(x), part
+    assert abs(part[0].item() - float(np.sum(2.0 * x))) < 1e-9 * part[0].item()
+    print("OK")
+dist.destroy_process_group()
+"""
+
+
+def test_sharded_sum_gloo_world2(tmp_path):
+    script = tmp_path / "w.py"
+    script.write_text(WORKER)
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+                        "--master-port", "29533", str(script), ROOT], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "OK" in r.stdout, r.stderr[-2000:]
+    assert gf.shard_range(10, 0, 3) == (0, 3) and gf.shard_range(10, 2, 3) == (6, 4)
