@@ -28,7 +28,7 @@ LDSTD    := $(if $(SYSGCC),-L$(dir $(SYSGCC)),)
 PYEXT    := $(shell $(PYTHON) -c "import sysconfig; print(sysconfig.get_config_var('EXT_SUFFIX'))")
 PYINC    := $(shell $(PYTHON) -c "import sysconfig, pybind11; print('-I' + sysconfig.get_paths()['include'] + ' -I' + pybind11.get_include())")
 
-all: cuda host python
+all: cuda host python examples
 cuda: $(LIBDIR)/libgoofit_b200.so
 host: $(LIBDIR)/libgoofit_host.so
 python: goofit_b200/_goofit$(PYEXT)
@@ -65,6 +65,11 @@ PYOBJ := $(patsubst goofit_b200/python/%.cpp,build/py/%.o,$(PYSRC))
 goofit_b200/_goofit$(PYEXT): $(PYOBJ) $(LIBDIR)/libgoofit_host.so
 	$(CXX) -shared $(LDSTD) -o $@ $(PYOBJ) -L$(LIBDIR) -lgoofit_host -lgoofit_b200 -lMinuit2 -Wl,-rpath,'$$ORIGIN/lib'
 
+examples: examples/bin/exponential
+examples/bin/%: examples/%.cpp $(LIBDIR)/libgoofit_host.so
+	@mkdir -p examples/bin
+	$(CXX) $(HFLAGS) $< $(LDSTD) -L$(LIBDIR) -lgoofit_host -lgoofit_b200 -lMinuit2 -Wl,-rpath,'$$ORIGIN/../../goofit_b200/lib' -o $@
+
 clean:
 	rm -rf build $(LIBDIR)/*.so goofit_b200/_goofit*.so
-.PHONY: all cuda host python clean
+.PHONY: all cuda host python examples clean

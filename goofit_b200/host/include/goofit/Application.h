@@ -1,0 +1,58 @@
+// Application.h — minimal stand-in for the reference's CLI11-based GooFit::Application (src/goofit/Application.cpp):
+// parses --gpu-dev N, -q/--quiet and --nosplash, selects the CUDA device before the first PDF is evaluated and, when
+// launched with RANK/WORLD_SIZE/LOCAL_RANK in the environment, takes its event shard from them (the reference's MPI
+// rank -> GPU mapping, Application.cpp:163-207). The CLI11 option machinery itself is out of scope.
+#pragma once
+#include <cstdlib>
+#include <cstring>
+#include <iostream>
+#include <string>
+
+#include <goofit/detail/Core.h>
+
+namespace GooFit {
+class Application {
+  public:
+    Application(std::string description, int argc, char **argv)
+        : description_(std::move(description))
+        , argc_(argc)
+        , argv_(argv) {}
+    Application(int argc, char **argv)
+        : Application("", argc, argv) {}
+    /// parse and apply; throws GeneralError on a malformed option
+    void run() {
+        for(int i = 1; i < argc_; i++) {
+            std::string a = argv_[i];
+            if(a == "--gpu-dev" && i + 1 < argc_)
+                gpuDev_ = std::atoi(argv_[++i]);
+            else if(a == "-q" || a == "--quiet")
+                quiet_ = true;
+            else if(a == "--nosplash")
+                splash_ = false;
+        }
+        const char *lr = std::getenv("LOCAL_RANK"), *r = std::getenv("RANK"), *w = std::getenv("WORLD_SIZE");
+        if(gpuDev_ < 0 && lr) gpuDev_ = std::atoi(lr);
+        if(gpuDev_ >= 0) detail::Engine::get().setDevice(gpuDev_);
+        if(r && w && std::atoi(w) > 1) detail::Engine::get().setShard(std::atoi(r), std::atoi(w));
+        if(splash_ && !quiet_) std::cout << "GooFit (B200-native likelihood engine) " << description_ << std::endl;
+    }
+    int exit(const GeneralError &e) {
+        std::cerr << e.what() << std::endl;
+        return e.get_exit_code();
+    }
+    bool quiet() const { return quiet_; }
+
+  private:
+    std::string description_;
+    int argc_;
+    char **argv_;
+    int gpuDev_{-1};
+    bool quiet_{false}, splash_{true};
+};
+} // namespace GooFit
+#define GOOFIT_PARSE(app)                                                                                              \
+    try {                                                                                                              \
+        app.run();                                                                                                     \
+    } catch(const GooFit::GeneralError &e) {                                                                           \
+        return app.exit(e);                                                                                            \
+    }

@@ -327,3 +327,14 @@ def test_dp4_fit_matches_reference(golden):
     pulls = np.abs(mine - val) / err
     assert pulls.max() < 0.01, pulls
     assert rel(res.Fval(), golden["dp4fit.fval"]) < 1e-9
+
+
+def test_cpp_example_exponential():
+    # the reference's examples/exponential flow compiled against the drop-in C++ headers (examples/exponential.cpp)
+    import os
+    import subprocess
+    exe = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "examples", "bin", "exponential")
+    if not os.path.exists(exe):
+        pytest.skip("examples/bin/exponential not built")
+    r = subprocess.run([exe, "--nosplash", "-q"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
