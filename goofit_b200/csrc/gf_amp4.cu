@@ -162,6 +162,34 @@ __global__ void __launch_bounds__(GF_THREADS, 4)
     gf_grid_finish(&acc, 1, partials, ticket, out, red);
 }
 
+// Amp4Body_TD: four sums over MC events, |A|^2, |B|^2, Re(A B*), Im(A B*) (detail/NormIntegrator_TD.cu:15-99); the
+// time integrals are applied to the four sums on the host by the resolution's normalization().
+__global__ void __launch_bounds__(GF_THREADS, 4)
+    k_amp4_norm_td(const gf_dev_view V, int node, const double2 *amps, long ld, long n, const double *weights,
+                   double *partials, unsigned *ticket, double *out) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ double red[32];
+    gf_sprog P = gf_stage_program(V, smem);
+    __syncthreads();
+    const gf_node &nd = P.nodes[node];
+    const double *p = P.params + nd.par_off;
+    const int32_t *in = P.ints + nd.int_off;
+    const int nAmp = in[3];
+    const int32_t *flags = in + in[4] + 1;
+    double acc[4] = {0, 0, 0, 0};
+    const long stride = (long)gridDim.x * blockDim.x;
+    for(long m = (long)blockIdx.x * blockDim.x + threadIdx.x; m < n; m += stride) {
+        double Are, Aim, Bre, Bim;
+        gf_amp4td_AB(p, flags, nAmp, [&](int a) { return __ldg(amps + (size_t)a * ld + m); }, Are, Aim, Bre, Bim);
+        double w = weights ? __ldg(weights + m) : 1.0;
+        acc[0] += w * (Are * Are + Aim * Aim);
+        acc[1] += w * (Bre * Bre + Bim * Bim);
+        acc[2] += w * (Are * Bre + Aim * Bim);
+        acc[3] += w * (Aim * Bre - Are * Bim);
+    }
+    gf_grid_finish(acc, 4, partials, ticket, out, red);
+}
+
 // ---- C ABI ---------------------------------------------------------------------------------------------------
 static int amp4_check(gf_ctx *c, int node, gf_amp4_state **out, bool create) {
     if(!c) return gf_fail("null ctx");
@@ -188,9 +216,25 @@ static int amp4_check(gf_ctx *c, int node, gf_amp4_state **out, bool create) {
             if(in[off + 3 + numLS + j] < 0 || in[off + 3 + numLS + j] >= nSF) return gf_fail("gf_amp4: spin-factor index out of range");
     }
     if(in[0] < 0 || in[0] >= GF_MAX_AUX) return gf_fail("gf_amp4: bad aux slot");
+    if(c->h_nodes[node].op == GF_OP_AMP4_TD) {
+        int td = in[4];
+        if(td < 5 + nLS + nSF + nAmp || td + 1 + nAmp > nd.nint) return gf_fail("gf_amp4: bad time-dependent block offset");
+        if(in[td] < 0 || in[td] >= nn || (c->h_nodes[in[td]].op != GF_OP_TRES_TRUTH && c->h_nodes[in[td]].op != GF_OP_TRES_3GAUSS))
+            return gf_fail("gf_amp4: not a decay-time resolution record");
+        if(c->h_nodes[in[td]].op == GF_OP_TRES_3GAUSS && c->h_nodes[in[td]].npar < 13) return gf_fail("gf_amp4: ThreeGaussResolution needs 13 parameters");
+        int ncoef = 0;
+        for(int a = 0; a < nAmp; a++) {
+            int f = in[td + 1 + a];
+            if(f < 0 || f > 2) return gf_fail("gf_amp4: amplitude flag must be 0 (A), 1 (B) or 2 (both)");
+            ncoef += f == 2 ? 2 : 1;
+        }
+        if(nd.npar < 4 + 2 * ncoef) return gf_fail("gf_amp4: time-dependent coefficient block too short");
+        if(nd.nobs < 8) return gf_fail("gf_amp4: Amp4Body_TD needs m12, m34, cos12, cos34, phi, event number, dtime, sigma");
+    } else if(in[4] != 0)
+        return gf_fail("gf_amp4: td offset set on a time-integrated record");
     gf_amp4_state *s = find_amp4(c, node, create);
     if(!s) return gf_fail("gf_amp4: gf_amp4_alloc / gf_amp4_set_mc not called for this node");
-    s->slot = in[0]; s->nLS = nLS; s->nSF = nSF; s->nAmp = nAmp; s->td = in[4];
+    s->slot = in[0]; s->nLS = nLS; s->nSF = nSF; s->nAmp = nAmp; s->td = c->h_nodes[node].op == GF_OP_AMP4_TD ? 1 : 0;
     *out = s;
     return 0;
 }
@@ -308,18 +352,25 @@ extern "C" int gf_amp4_norm_async(gf_ctx *c, int node) {
     size_t sm = gf_prog_smem(c);
     if(sm > 48 * 1024) cudaFuncSetAttribute(k_amp4_norm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
     int blocks = gf_grid_blocks(c, s->mc.n, 4);
-    k_amp4_norm<<<blocks, GF_THREADS, sm, c->stream>>>(c->view, node, s->mc.amps, s->mc.ld, s->mc.n, s->mc.weights,
-                                                      c->d_partials + (size_t)c->max_blocks * 2, c->d_ticket + 2, c->d_result + 1);
+    if(s->td) {
+        if(sm > 48 * 1024) cudaFuncSetAttribute(k_amp4_norm_td, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        k_amp4_norm_td<<<blocks, GF_THREADS, sm, c->stream>>>(c->view, node, s->mc.amps, s->mc.ld, s->mc.n, s->mc.weights,
+                                                             c->d_partials + (size_t)c->max_blocks * 2, c->d_ticket + 2, c->d_result + 1);
+    } else
+        k_amp4_norm<<<blocks, GF_THREADS, sm, c->stream>>>(c->view, node, s->mc.amps, s->mc.ld, s->mc.n, s->mc.weights,
+                                                          c->d_partials + (size_t)c->max_blocks * 2, c->d_ticket + 2, c->d_result + 1);
     c->launches++;
     GF_CUDA(cudaGetLastError());
-    if(c->nccl_comm && gf_allreduce_sum(c, c->d_result + 1, 1)) return 1;
+    if(c->nccl_comm && gf_allreduce_sum(c, c->d_result + 1, s->td ? 4 : 1)) return 1;
     return 0;
 }
 extern "C" int gf_amp4_norm(gf_ctx *c, int node, double *out) {
     if(gf_amp4_norm_async(c, node)) return 1;
-    GF_CUDA(cudaMemcpyAsync(c->h_result + 1, c->d_result + 1, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    gf_amp4_state *s = find_amp4(c, node, false);
+    int n = s && s->td ? 4 : 1;
+    GF_CUDA(cudaMemcpyAsync(c->h_result + 1, c->d_result + 1, sizeof(double) * n, cudaMemcpyDeviceToHost, c->stream));
     GF_CUDA(cudaStreamSynchronize(c->stream));
-    *out = c->h_result[1];
+    for(int k = 0; k < n; k++) out[k] = c->h_result[1 + k];
     return 0;
 }
 

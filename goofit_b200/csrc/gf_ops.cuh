@@ -140,6 +140,112 @@ __device__ inline bool gf_in_dalitz(double m12, double m13, double bigM, double 
     return m12less && m12grea && m13less && m13grea;
 }
 
+// ---- decay-time resolution of Amp4Body_TD ------------------------------------------------------------------------
+// physics/ThreeGaussResolution.cu:11-60: one Gaussian-smeared set of the four time functions
+__device__ inline void gf_tres_gauss(double &P1, double &P2, double &P3, double &P4, double tau, double adjTime, double x,
+                                     double y, double adjSigma, double selbias) {
+    const double SQRTPIo2 = 1.0 / 1.12837916709551257390; // 1 / M_2_SQRTPI
+    const double SQRT1o2PI = sqrt(0.5 * 0.31830988618379067154);
+    const double R1o6 = 1.0 / 6.0;
+    double _1oSqrtA = adjSigma * 1.41421356237309504880;
+    double _1oSigma = 1 / adjSigma;
+    double _1o2SqrtA = 0.5 * _1oSqrtA;
+    double _1oSigma2 = _1oSigma * _1oSigma;
+    double NormG = SQRT1o2PI * _1oSigma;
+    double C = 0.5 * adjTime * adjTime * _1oSigma2;
+    double Bgn = -adjTime * _1oSigma2;
+    double Gamma = 1 / tau;
+    double B = Gamma + Bgn;
+    double u0 = _1o2SqrtA * (B + selbias);
+    double u02 = u0 * u0;
+    double F = _1oSqrtA * exp(-C + u02);
+    double Ig0 = SQRTPIo2 * erfc(u0);
+    double Ig1 = 0.5 * exp(-u02);
+    double Ig2 = Ig1 * u0 + 0.5 * Ig0;
+    double Ig3 = Ig1 * (u02 + 1);
+    double R = x * Gamma * _1oSqrtA;
+    double R2 = R * R;
+    double It0 = F * Ig0;
+    double It1 = F * R * (Ig1 - u0 * Ig0);
+    double It2 = F * R2 * (Ig2 - u0 * Ig1 * 2 + u02 * Ig0);
+    double It3 = F * R2 * R * (Ig3 - u0 * Ig2 * 3 + u02 * Ig1 * 3 - u0 * u02 * Ig0);
+    P2 = NormG * (It0 - 0.5 * It2);
+    P4 = NormG * (It1 - R1o6 * It3);
+    double u0py = _1o2SqrtA * (B - y * Gamma + selbias);
+    double u0my = _1o2SqrtA * (B + y * Gamma + selbias);
+    double Fpy = _1oSqrtA * exp(-C + u0py * u0py);
+    double Fmy = _1oSqrtA * exp(-C + u0my * u0my);
+    double Ipy = Fpy * SQRTPIo2 * erfc(u0py);
+    double Imy = Fmy * SQRTPIo2 * erfc(u0my);
+    P1 = NormG * 0.5 * (Ipy + Imy);
+    P3 = NormG * 0.5 * (Ipy - Imy);
+}
+// op = GF_OP_TRES_TRUTH (TruthResolution.cu:8-28) or GF_OP_TRES_3GAUSS (ThreeGaussResolution.cu:62-125; p = 13 parameters)
+__device__ inline double gf_tres(int op, const double *p, double coshterm, double costerm, double sinhterm, double sinterm,
+                                 double tau, double dtime, double x, double y, double sigma) {
+    if(op == GF_OP_TRES_TRUTH) {
+        double ret = 0;
+        dtime /= tau;
+        ret += coshterm * cosh(y * dtime);
+        ret += costerm * cos(x * dtime);
+        ret -= 2 * sinhterm * sinh(y * dtime);
+        ret -= 2 * sinterm * sin(x * dtime);
+        ret *= exp(-dtime);
+        return ret;
+    }
+    double coreFraction = p[0], tailFraction = p[1];
+    double outlFraction = 1 - coreFraction - tailFraction;
+    double coreBias = p[2], coreScale = p[3], tailBias = p[4], tailScale = p[5], outlBias = p[6], outlScale = p[7];
+    double selbias = p[8];
+    coreBias += p[9];
+    tailBias += p[11];
+    outlBias += p[11];
+    coreScale *= p[10];
+    tailScale *= p[12];
+    outlScale *= p[12];
+    double c1, c2, c3, c4, t1, t2, t3, t4, o1, o2, o3, o4;
+    gf_tres_gauss(c1, c2, c3, c4, tau, dtime - coreBias * sigma, x, y, coreScale * sigma, selbias);
+    gf_tres_gauss(t1, t2, t3, t4, tau, dtime - tailBias * sigma, x, y, tailScale * sigma, selbias);
+    gf_tres_gauss(o1, o2, o3, o4, tau, dtime - outlBias * sigma, x, y, outlScale * sigma, selbias);
+    double P1 = coreFraction * c1 + tailFraction * t1 + outlFraction * o1;
+    double P2 = coreFraction * c2 + tailFraction * t2 + outlFraction * o2;
+    double P3 = coreFraction * c3 + tailFraction * t3 + outlFraction * o3;
+    double P4 = coreFraction * c4 + tailFraction * t4 + outlFraction * o4;
+    double ret = 0;
+    ret += coshterm * P1;
+    ret += costerm * P2;
+    ret -= 2 * sinhterm * P3;
+    ret -= 2 * sinterm * P4;
+    return ret;
+}
+// A = sqrt(WS/RS) * sum_{flag 0,2} c A_a ; B = sum_{flag 1,2} c A_a with the reference's coefficient walk
+// (Amp4Body_TD.cu:186-214, NormIntegrator_TD.cu:69-88): coefficient pair (i + k), k counting earlier flag-2 amplitudes.
+template <class Load>
+__device__ inline void gf_amp4td_AB(const double *p, const int32_t *flags, int namp, const Load &amp, double &Are, double &Aim,
+                                    double &Bre, double &Bim) {
+    Are = Aim = Bre = Bim = 0;
+    int k = 0;
+    for(int i = 0; i < namp; ++i) {
+        double2 me = amp(i);
+        int flag = flags[i];
+        double cr = p[4 + 2 * (i + k)], ci = p[5 + 2 * (i + k)];
+        double re = me.x * cr - me.y * ci, im = me.x * ci + me.y * cr;
+        if(flag == 1) {
+            Bre += re; Bim += im;
+        } else {
+            Are += re; Aim += im;
+            if(flag == 2) {
+                ++k;
+                cr = p[4 + 2 * (i + k)]; ci = p[5 + 2 * (i + k)];
+                Bre += me.x * cr - me.y * ci;
+                Bim += me.x * ci + me.y * cr;
+            }
+        }
+    }
+    Are *= p[3];
+    Aim *= p[3];
+}
+
 // Post-order evaluation of nodes [first, last]; returns the root's raw value.
 template <class Evt>
 __device__ inline double gf_eval_tree(const gf_sprog &P, const gf_dev_view &V, int first, int last, const Evt &evt) {
@@ -248,6 +354,22 @@ __device__ inline double gf_eval_tree(const gf_sprog &P, const gf_dev_view &V, i
                 im += ar * me.y + ai * me.x;
             }
             st[sp++] = (re * re + im * im) * eff;
+        } break;
+        case GF_OP_AMP4_TD: { // physics/Amp4Body_TD.cu:167-261 ; ints[4] = offset of {resolution record, flags[nAmp]}
+            const int32_t *ob = P.ints + nd.obs_off;
+            double eff = st[--sp];
+            long e = evt.event_number(ob[5]);
+            const int32_t *td = in + in[4];
+            const double2 *w = static_cast<const double2 *>(P.aux[in[0]]) + e;
+            long ld = P.aux_ld[in[0]];
+            double Are, Aim, Bre, Bim;
+            gf_amp4td_AB(p, td + 1, in[3], [&](int i) { return __ldg(w + (size_t)i * ld); }, Are, Aim, Bre, Bim);
+            double nA = Are * Are + Aim * Aim, nB = Bre * Bre + Bim * Bim;
+            double t3re = Are * Bre + Aim * Bim, t3im = Aim * Bre - Are * Bim; // A conj(B)
+            const gf_node &rn = P.nodes[td[0]];
+            double ret = gf_tres(rn.op, P.params + rn.par_off, nA + nB, nA - nB, t3re, t3im, p[0], evt(ob[6]), p[1], p[2],
+                                 evt(ob[7]));
+            st[sp++] = ret * eff;
         } break;
         default: st[sp++] = 0.0; break;
         }

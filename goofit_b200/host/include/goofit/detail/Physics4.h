@@ -15,6 +15,7 @@ enum DP4Pair { // DalitzPlotHelpers.h:56-76
 enum class FF : unsigned int { One = 0, BL, BL_Prime, BL2 };
 
 class Lineshape : public AmpComponent { // lineshapes/Lineshape.h:22-49
+    friend class Amp4BodyBase;
     friend class Amp4Body;
     friend class Amp4Body_TD;
 
@@ -55,6 +56,7 @@ enum class SF_4Body { // SpinFactors.h:18-35
 };
 
 class SpinFactor final : public AmpComponent { // SpinFactors.h:37-68
+    friend class Amp4BodyBase;
     friend class Amp4Body;
     SF_4Body _SF;
     unsigned int _P0, _P1, _P2, _P3;
@@ -71,6 +73,7 @@ class SpinFactor final : public AmpComponent { // SpinFactors.h:37-68
 };
 
 class Amplitude : public AmpComponent { // Amplitude.h:18-49
+    friend class Amp4BodyBase;
     friend class Amp4Body;
     friend class Amp4Body_TD;
 
@@ -97,49 +100,121 @@ struct DecayInfo4 { // DalitzPlotHelpers.h:108-114
     std::vector<Amplitude *> amplitudes_B;
 };
 
-class Amp4BodyBase : public GooPdf {
-  public:
-    using GooPdf::GooPdf;
-};
-
 /// Deterministic four-body phase-space sample expressed in (m12, m34, cos12, cos34, phi). Replaces the MCBooster
 /// PhaseSpace + Dim5 calls of the reference's constructor (Amp4Body.cu:243-289, detail/Dim5.h:19-111); the generator
 /// is this build's own (GENBOD sequential two-body decays, counter-based RNG), so toys differ from MCBooster's.
 std::vector<std::vector<fptype>> generatePhaseSpace5(const std::vector<fptype> &particle_masses, size_t nEvents,
                                                       unsigned long seed, std::vector<fptype> *weights = nullptr);
+/// accept-reject "Unweight" flags for a weighted phase-space sample (counter-based, deterministic in (seed, index))
+std::vector<bool> unweightPhaseSpace(const std::vector<fptype> &weights, unsigned long seed);
 /// (m12, m34, cos12, cos34, phi) of one event given as 4 x (E, px, py, pz) — pinned by tests/simple/VectorsTest.cu
 void fourVectorsToDim5(const fptype *p4x4_Epxpypz, fptype *out5);
 
-class Amp4Body : public Amp4BodyBase { // Amp4Body.h:33-95
+/// What Amp4Body and Amp4Body_TD share: the unique lineshape / spin-factor lists, the amplitude index records, the MC
+/// normalisation sample and the device cache handles (reference: Amp4BodyBase.h + the duplicated bookkeeping of
+/// Amp4Body.cu:94-292 and Amp4Body_TD.cu:307-561).
+class Amp4BodyBase : public GooPdf {
   public:
-    Amp4Body(std::string n, std::vector<Observable> observables, DecayInfo4 decay, GooPdf *eff, unsigned int MCeventsNorm = 5e6);
-    fptype normalize() override;
-    void setDataSize(unsigned int dataSize, unsigned int evtSize = 6);
+    using GooPdf::GooPdf;
     void setForceIntegrals(bool f = true) { forceRedoIntegrals = f; }
-    int getMCevents() { return static_cast<int>(MCevents); }
     /// replace the normalisation sample: five columns (m12, m34, cos12, cos34, phi) of equal length
     void setNormEvents(const std::vector<std::vector<fptype>> &cols5);
     const std::vector<std::vector<fptype>> &getNormEvents() const { return normCols; }
     std::vector<std::complex<fptype>> getCachedAmp(size_t a) const;
     size_t numLineshapes() const { return LineShapes.size(); }
     size_t numSpinFactors() const { return SpinFactors.size(); }
-
+    size_t numAmplitudes() const { return nAmps; }
     void emitAux(detail::ProgramBuilder &B) override;
-    int emit(detail::ProgramBuilder &B) override;
     void afterProgram() override;
 
   protected:
+    /// registers amp's lineshapes and spin factors (unique by value) and appends its record {nLS, nSF, nPerm, idx...}
+    void addAmplitudeRecord(Amplitude *amp);
+    std::vector<int32_t> headerInts(detail::ProgramBuilder &B, int tdOffset) const;
     void ensureCache();
-    DecayInfo4 decayInfo;
-    GooPdf *efficiency;
+    void setDataSizeCommon(unsigned int dataSize, unsigned int evtSize);
+    GooPdf *efficiency{nullptr};
     std::vector<SpinFactor *> SpinFactors;
     std::vector<Lineshape *> LineShapes;
-    std::vector<int32_t> ampIndex; // start[nAmp] + records
+    std::vector<int32_t> ampStarts, ampRecords;
+    size_t nAmps{0};
     std::vector<std::vector<fptype>> normCols;
     size_t MCevents{0};
     bool forceRedoIntegrals{true};
     bool cacheAllocated{false};
-    int totalEventSize;
+    int totalEventSize{0};
+};
+
+class Amp4Body : public Amp4BodyBase { // Amp4Body.h:33-95
+  public:
+    Amp4Body(std::string n, std::vector<Observable> observables, DecayInfo4 decay, GooPdf *eff, unsigned int MCeventsNorm = 5e6);
+    fptype normalize() override;
+    void setDataSize(unsigned int dataSize, unsigned int evtSize = 6) { setDataSizeCommon(dataSize, evtSize); }
+    int getMCevents() { return static_cast<int>(MCevents); }
+    int emit(detail::ProgramBuilder &B) override;
+
+  protected:
+    DecayInfo4 decayInfo;
+};
+
+// ---- time-dependent four-body amplitude ------------------------------------------------------------------------------
+/// MixingTimeResolution.h:18-43. The per-event time functions run on the device (csrc/gf_ops.cuh gf_tres); the time
+/// integrals applied to the four MC sums stay on the host, as upstream.
+class MixingTimeResolution : public GooPdf {
+  public:
+    using GooPdf::GooPdf;
+    virtual fptype normalization(fptype di1, fptype di2, fptype di3, fptype di4, fptype tau, fptype xmixing, fptype ymixing) const = 0;
+    fptype normalize() override { return 1.0; }
+};
+class TruthResolution : public MixingTimeResolution { // TruthResolution.h / TruthResolution.cu:47-71
+  public:
+    TruthResolution();
+    fptype normalization(fptype di1, fptype di2, fptype di3, fptype di4, fptype tau, fptype xmixing, fptype ymixing) const override;
+    int emit(detail::ProgramBuilder &B) override { return emitRecord(B, GF_OP_TRES_TRUTH, 0, 1, {}); }
+};
+class ThreeGaussResolution : public MixingTimeResolution { // ThreeGaussResolution.h:19-42 / .cu:127-183
+  public:
+    ThreeGaussResolution(Variable cf, Variable tf, Variable cb, Variable cs, Variable tb, Variable ts, Variable ob, Variable os,
+                         Variable sb, Variable common_bias_offset, Variable common_width_scale, Variable common_bias_offset2,
+                         Variable common_width_scale2);
+    fptype normalization(fptype di1, fptype di2, fptype di3, fptype di4, fptype tau, fptype xmixing, fptype ymixing) const override;
+    int emit(detail::ProgramBuilder &B) override { return emitRecord(B, GF_OP_TRES_3GAUSS, 0, 1, {}); }
+
+  private:
+    Variable selectionBias;
+};
+
+struct DecayInfo4t : public DecayInfo4 { // DalitzPlotHelpers.h:122-133
+    Variable _tau, _xmixing, _ymixing, _SqWStoRSrate;
+    DecayInfo4t(Variable tau, Variable xmixing, Variable ymixing, Variable SqWStoRSrate)
+        : _tau(tau)
+        , _xmixing(xmixing)
+        , _ymixing(ymixing)
+        , _SqWStoRSrate(SqWStoRSrate) {}
+};
+
+class Amp4Body_TD final : public Amp4BodyBase { // Amp4Body_TD.h:34-137
+  public:
+    /// normalisation events generated from one seed and kept in HBM (Amp4Body_TD.cu:292-307, NormEvents_4Body_DeviceCached)
+    Amp4Body_TD(std::string n, std::vector<Observable> observables, DecayInfo4t decay, MixingTimeResolution *Tres,
+                GooPdf *efficiency, Observable *mistag, long normSeed, unsigned int numNormEventsToGen);
+    /// upstream's host-cached batches (Amp4Body_TD.cu:269-290) exist because the sample may not fit a GPU; here every batch
+    /// is generated with its own seed and the concatenation is kept in HBM (and sharded over ranks)
+    Amp4Body_TD(std::string n, std::vector<Observable> observables, DecayInfo4t decay, MixingTimeResolution *Tres,
+                GooPdf *efficiency, Observable *mistag, const std::vector<long> &normSeeds, unsigned int numNormEventsToGenPerBatch);
+    fptype normalize() override;
+    void setDataSize(unsigned int dataSize, unsigned int evtSize = 8) { setDataSizeCommon(dataSize, evtSize); }
+    int getNumAccNormEvents() const { return static_cast<int>(MCevents); }
+    fptype getSumInitNormEventWeights() const { return static_cast<fptype>(MCevents); }
+    int emit(detail::ProgramBuilder &B) override;
+    void emitAux(detail::ProgramBuilder &B) override;
+
+  private:
+    void init(std::vector<Observable> &observables, Observable *mistag, const std::vector<long> &seeds, unsigned int perBatch);
+    DecayInfo4t decayInfo;
+    MixingTimeResolution *resolution;
+    std::vector<int32_t> flags;
+    bool spinsCalculated{false};
 };
 
 } // namespace GooFit

@@ -212,68 +212,49 @@ std::vector<std::vector<fptype>> generatePhaseSpace5(const std::vector<fptype> &
     return cols;
 }
 
-// ---- Amp4Body ------------------------------------------------------------------------------------------------------
-Amp4Body::Amp4Body(std::string n, std::vector<Observable> observables, DecayInfo4 decay, GooPdf *eff, unsigned int MCeventsNorm)
-    : Amp4BodyBase("Amp4Body", n)
-    , decayInfo(decay)
-    , efficiency(eff)
-    , totalEventSize(static_cast<int>(observables.size())) {
-    if(observables.size() < 6) throw GeneralError("Amp4Body {} needs m12, m34, cos12, cos34, phi and an event number", n);
-    if(decayInfo.particle_masses.size() != 5) throw GeneralError("Amp4Body {}: particle_masses must hold the mother and four daughters", n);
-    if(decayInfo.amplitudes.empty()) throw GeneralError("Amp4Body {} needs at least one amplitude", n);
-    if(!efficiency) throw GeneralError("Amp4Body {} needs an efficiency function", n);
-    for(auto &o : observables) registerObservable(o);
-    for(double pm : decayInfo.particle_masses) registerConstant(pm);
-    // unique lineshapes / spin factors, compared by value exactly as the reference (Amp4Body.cu:120-160)
-    std::vector<int32_t> starts, records;
-    for(auto *amp : decayInfo.amplitudes) {
-        components.push_back(amp);
-        registerParameter(amp->_ar);
-        registerParameter(amp->_ai);
-        starts.push_back(static_cast<int32_t>(records.size()));
-        records.push_back(static_cast<int32_t>(amp->_LS.size()));
-        records.push_back(static_cast<int32_t>(amp->_SF.size()));
-        records.push_back(static_cast<int32_t>(amp->_nPerm));
-        if(amp->_LS.size() % amp->_nPerm || amp->_SF.size() % amp->_nPerm)
-            throw GeneralError("Amplitude {}: lineshapes and spin factors must split evenly over the permutations", amp->getName());
-        for(auto *ls : amp->_LS) {
-            auto it = std::find_if(LineShapes.begin(), LineShapes.end(), [ls](const Lineshape *L) { return *ls == *L; });
-            if(it == LineShapes.end()) {
-                LineShapes.push_back(ls);
-                it = LineShapes.end() - 1;
-            }
-            records.push_back(static_cast<int32_t>(it - LineShapes.begin()));
-        }
-        for(auto *sf : amp->_SF) {
-            auto it = std::find_if(SpinFactors.begin(), SpinFactors.end(), [sf](const SpinFactor *S) { return *sf == *S; });
-            if(it == SpinFactors.end()) {
-                SpinFactors.push_back(sf);
-                it = SpinFactors.end() - 1;
-            }
-            records.push_back(static_cast<int32_t>(it - SpinFactors.begin()));
-        }
-    }
-    if(LineShapes.size() > 64 || SpinFactors.size() > 64 || decayInfo.amplitudes.size() > 64)
-        throw GeneralError("Amp4Body supports at most 64 unique lineshapes, spin factors and amplitudes");
-    ampIndex = starts;
-    ampIndex.insert(ampIndex.end(), records.begin(), records.end());
-    components.push_back(efficiency);
-    registerFunction("ptr_to_DP", GF_OP_AMP4);
-    // Normalisation sample. The reference generates MCeventsNorm phase-space events, runs the accept-reject
-    // "Unweight" step and then keeps the FIRST nAcc events of the un-compacted sample (Amp4Body.cu:243-289: the
-    // remove_if is commented out); the same selection is made here.
-    if(MCeventsNorm > 0) {
-        std::vector<fptype> w;
-        auto cols = generatePhaseSpace5(decayInfo.particle_masses, MCeventsNorm, 0, &w);
-        size_t nAcc = 0;
-        for(size_t i = 0; i < w.size(); i++) nAcc += w[i] > uniform01(0, i, 1000) ? 1 : 0;
-        if(nAcc == 0) nAcc = 1;
-        for(auto &c : cols) c.resize(nAcc);
-        setNormEvents(cols);
-    }
-    setSeparateNorm();
+std::vector<bool> unweightPhaseSpace(const std::vector<fptype> &w, unsigned long seed) {
+    std::vector<bool> flags(w.size());
+    for(size_t i = 0; i < w.size(); i++) flags[i] = w[i] > uniform01(seed, i, 1000);
+    return flags;
 }
-void Amp4Body::setNormEvents(const std::vector<std::vector<fptype>> &cols5) {
+
+// ---- what Amp4Body and Amp4Body_TD share ------------------------------------------------------------------------
+void Amp4BodyBase::addAmplitudeRecord(Amplitude *amp) { // Amp4Body.cu:120-160 / Amp4Body_TD.cu:366-420: unique by VALUE
+    if(amp->_LS.size() % amp->_nPerm || amp->_SF.size() % amp->_nPerm)
+        throw GeneralError("Amplitude {}: lineshapes and spin factors must split evenly over the permutations", amp->getName());
+    ampStarts.push_back(static_cast<int32_t>(ampRecords.size()));
+    ampRecords.push_back(static_cast<int32_t>(amp->_LS.size()));
+    ampRecords.push_back(static_cast<int32_t>(amp->_SF.size()));
+    ampRecords.push_back(static_cast<int32_t>(amp->_nPerm));
+    for(auto *ls : amp->_LS) {
+        auto it = std::find_if(LineShapes.begin(), LineShapes.end(), [ls](const Lineshape *L) { return *ls == *L; });
+        if(it == LineShapes.end()) {
+            LineShapes.push_back(ls);
+            it = LineShapes.end() - 1;
+        }
+        ampRecords.push_back(static_cast<int32_t>(it - LineShapes.begin()));
+    }
+    for(auto *sf : amp->_SF) {
+        auto it = std::find_if(SpinFactors.begin(), SpinFactors.end(), [sf](const SpinFactor *S) { return *sf == *S; });
+        if(it == SpinFactors.end()) {
+            SpinFactors.push_back(sf);
+            it = SpinFactors.end() - 1;
+        }
+        ampRecords.push_back(static_cast<int32_t>(it - SpinFactors.begin()));
+    }
+    ++nAmps;
+    if(LineShapes.size() > 64 || SpinFactors.size() > 64 || nAmps > 64)
+        throw GeneralError("{} supports at most 64 unique lineshapes, spin factors and amplitudes", getName());
+}
+std::vector<int32_t> Amp4BodyBase::headerInts(detail::ProgramBuilder &B, int tdOffset) const {
+    std::vector<int32_t> ints{B.allocAux(), (int32_t)LineShapes.size(), (int32_t)SpinFactors.size(), (int32_t)nAmps, tdOffset};
+    for(auto *ls : LineShapes) ints.push_back(ls->getFunctionIndex());
+    for(auto *sf : SpinFactors) ints.push_back(sf->getFunctionIndex());
+    ints.insert(ints.end(), ampStarts.begin(), ampStarts.end());
+    ints.insert(ints.end(), ampRecords.begin(), ampRecords.end());
+    return ints;
+}
+void Amp4BodyBase::setNormEvents(const std::vector<std::vector<fptype>> &cols5) {
     if(cols5.size() != 5) throw GeneralError("setNormEvents needs five columns (m12, m34, cos12, cos34, phi)");
     for(auto &c : cols5)
         if(c.size() != cols5[0].size() || c.empty()) throw GeneralError("setNormEvents: columns must be non-empty and of equal length");
@@ -282,36 +263,26 @@ void Amp4Body::setNormEvents(const std::vector<std::vector<fptype>> &cols5) {
     cacheAllocated = false;
     forceRedoIntegrals = true;
 }
-void Amp4Body::emitAux(detail::ProgramBuilder &B) {
+void Amp4BodyBase::emitAux(detail::ProgramBuilder &B) {
     for(auto *ls : LineShapes) ls->emit(B);
     for(auto *sf : SpinFactors) sf->emit(B);
     efficiency->emitAux(B);
 }
-int Amp4Body::emit(detail::ProgramBuilder &B) {
-    int first = (int)B.nodes.size();
-    efficiency->emit(B);
-    std::vector<int32_t> ints{B.allocAux(), (int32_t)LineShapes.size(), (int32_t)SpinFactors.size(),
-                              (int32_t)decayInfo.amplitudes.size(), 0};
-    for(auto *ls : LineShapes) ints.push_back(ls->getFunctionIndex());
-    for(auto *sf : SpinFactors) ints.push_back(sf->getFunctionIndex());
-    ints.insert(ints.end(), ampIndex.begin(), ampIndex.end());
-    return emitRecord(B, GF_OP_AMP4, 1, (int)B.nodes.size() - first + 1, ints);
-}
-void Amp4Body::afterProgram() {
+void Amp4BodyBase::afterProgram() {
     cacheAllocated     = false;
     forceRedoIntegrals = true;
 }
-void Amp4Body::setDataSize(unsigned int dataSize, unsigned int evtSize) { // Amp4Body.cu:348-395
+void Amp4BodyBase::setDataSizeCommon(unsigned int dataSize, unsigned int evtSize) { // Amp4Body.cu:348-395, Amp4Body_TD.cu:575-604
     totalEventSize = evtSize;
     if(totalEventSize < 3) throw GeneralError("totalEventSize {} should be 3 or more", totalEventSize);
     numEntries     = dataSize;
     cacheAllocated = false;
     setForceIntegrals();
 }
-void Amp4Body::ensureCache() {
+void Amp4BodyBase::ensureCache() {
     if(cacheAllocated) return;
-    if(nodeIdx < 0) throw GeneralError("Amp4Body {}: call setData() on the top-level PDF before evaluating", getName());
-    if(MCevents == 0) throw GeneralError("Amp4Body {} has no normalisation events", getName());
+    if(nodeIdx < 0) throw GeneralError("{}: call setData() on the top-level PDF before evaluating", getName());
+    if(MCevents == 0) throw GeneralError("{} has no normalisation events", getName());
     Engine &E = Engine::get();
     Engine::check(gf_amp4_alloc(E.ctx(), nodeIdx, E.localEvents), "gf_amp4_alloc");
     // the MC normalisation sample is sharded over ranks like the data (the reference replicates it)
@@ -323,11 +294,58 @@ void Amp4Body::ensureCache() {
     cacheAllocated     = true;
     forceRedoIntegrals = true;
 }
+std::vector<std::complex<fptype>> Amp4BodyBase::getCachedAmp(size_t a) const {
+    if(!cacheAllocated) throw GeneralError("{}: no cached amplitudes yet", getName());
+    Engine &E = Engine::get();
+    std::vector<std::complex<fptype>> ret(E.localEvents);
+    Engine::check(gf_amp4_get_amp(E.ctx(), nodeIdx, (int)a, reinterpret_cast<double *>(ret.data()), ret.size()), "gf_amp4_get_amp");
+    return ret;
+}
+
+// ---- Amp4Body ------------------------------------------------------------------------------------------------------
+Amp4Body::Amp4Body(std::string n, std::vector<Observable> observables, DecayInfo4 decay, GooPdf *eff, unsigned int MCeventsNorm)
+    : Amp4BodyBase("Amp4Body", n)
+    , decayInfo(decay) {
+    efficiency     = eff;
+    totalEventSize = static_cast<int>(observables.size());
+    if(observables.size() < 6) throw GeneralError("Amp4Body {} needs m12, m34, cos12, cos34, phi and an event number", n);
+    if(decayInfo.particle_masses.size() != 5) throw GeneralError("Amp4Body {}: particle_masses must hold the mother and four daughters", n);
+    if(decayInfo.amplitudes.empty()) throw GeneralError("Amp4Body {} needs at least one amplitude", n);
+    if(!efficiency) throw GeneralError("Amp4Body {} needs an efficiency function", n);
+    for(auto &o : observables) registerObservable(o);
+    for(double pm : decayInfo.particle_masses) registerConstant(pm);
+    for(auto *amp : decayInfo.amplitudes) {
+        components.push_back(amp);
+        registerParameter(amp->_ar);
+        registerParameter(amp->_ai);
+        addAmplitudeRecord(amp);
+    }
+    components.push_back(efficiency);
+    registerFunction("ptr_to_DP", GF_OP_AMP4);
+    // Normalisation sample. The reference generates MCeventsNorm phase-space events, runs the accept-reject
+    // "Unweight" step and then keeps the FIRST nAcc events of the un-compacted sample (Amp4Body.cu:243-289: the
+    // remove_if is commented out); the same selection is made here.
+    if(MCeventsNorm > 0) {
+        std::vector<fptype> w;
+        auto cols = generatePhaseSpace5(decayInfo.particle_masses, MCeventsNorm, 0, &w);
+        auto acc  = unweightPhaseSpace(w, 0);
+        size_t nAcc = std::count(acc.begin(), acc.end(), true);
+        if(nAcc == 0) nAcc = 1;
+        for(auto &c : cols) c.resize(nAcc);
+        setNormEvents(cols);
+    }
+    setSeparateNorm();
+}
+int Amp4Body::emit(detail::ProgramBuilder &B) {
+    int first = (int)B.nodes.size();
+    efficiency->emit(B);
+    return emitRecord(B, GF_OP_AMP4, 1, (int)B.nodes.size() - first + 1, headerInts(B, 0));
+}
 fptype Amp4Body::normalize() { // Amp4Body.cu:398-558
     recursiveSetNormalization(1.0);
     ensureCache();
     Engine &E   = Engine::get();
-    size_t nLS  = LineShapes.size(), nAmp = decayInfo.amplitudes.size();
+    size_t nLS  = LineShapes.size(), nAmp = nAmps;
     std::vector<uint8_t> lsRedo(nLS), ampRedo(nAmp, 0);
     bool any = forceRedoIntegrals;
     for(size_t i = 0; i < nLS; ++i) {
@@ -352,11 +370,169 @@ fptype Amp4Body::normalize() { // Amp4Body.cu:398-558
     setNormalization(1.0 / ret);
     return ret;
 }
-std::vector<std::complex<fptype>> Amp4Body::getCachedAmp(size_t a) const {
-    if(!cacheAllocated) throw GeneralError("Amp4Body {}: no cached amplitudes yet", getName());
-    Engine &E = Engine::get();
-    std::vector<std::complex<fptype>> ret(E.localEvents);
-    Engine::check(gf_amp4_get_amp(E.ctx(), nodeIdx, (int)a, reinterpret_cast<double *>(ret.data()), ret.size()), "gf_amp4_get_amp");
+
+// ---- decay-time resolutions ------------------------------------------------------------------------------------------
+TruthResolution::TruthResolution()
+    : MixingTimeResolution("TruthResolution", "mixing_resolution") {
+    registerFunction("ptr_to_truth", GF_OP_TRES_TRUTH);
+}
+fptype TruthResolution::normalization(fptype di1, fptype di2, fptype di3, fptype di4, fptype tau, fptype xmixing, fptype ymixing) const {
+    fptype timeIntegralOne = tau / (1 - ymixing * ymixing); // TruthResolution.cu:56-70
+    fptype timeIntegralTwo = tau / (1 + xmixing * xmixing);
+    fptype timeIntegralThr = ymixing * timeIntegralOne;
+    fptype timeIntegralFou = xmixing * timeIntegralTwo;
+    fptype ret             = timeIntegralOne * (di1 + di2);
+    ret += timeIntegralTwo * (di1 - di2);
+    ret -= 2 * timeIntegralThr * di3;
+    ret -= 2 * timeIntegralFou * di4;
+    return ret;
+}
+ThreeGaussResolution::ThreeGaussResolution(Variable cf, Variable tf, Variable cb, Variable cs, Variable tb, Variable ts, Variable ob,
+                                           Variable os, Variable sb, Variable common_bias_offset, Variable common_width_scale,
+                                           Variable common_bias_offset2, Variable common_width_scale2)
+    : MixingTimeResolution("ThreeGaussResolution", "mixing_resolution", cf, tf, cb, cs, tb, ts, ob, os, sb)
+    , selectionBias(sb) {
+    registerParameter(common_bias_offset);
+    registerParameter(common_width_scale);
+    registerParameter(common_bias_offset2);
+    registerParameter(common_width_scale2);
+    registerFunction("ptr_to_threegauss", GF_OP_TRES_3GAUSS);
+}
+fptype ThreeGaussResolution::normalization(fptype di1, fptype di2, fptype di3, fptype di4, fptype tau, fptype xmixing,
+                                           fptype ymixing) const { // ThreeGaussResolution.cu:155-182
+    fptype selBias = selectionBias.getValue();
+    fptype timeIntegralOne = (selBias + 1 / tau) / (selBias * selBias + 2 * selBias / tau + (1 - ymixing * ymixing) / (tau * tau));
+    fptype timeIntegralTwo = (selBias + 1 / tau) / (selBias * selBias + 2 * selBias / tau + (1 + xmixing * xmixing) / (tau * tau));
+    fptype timeIntegralThr = (ymixing / tau) / (selBias * selBias + 2 * selBias / tau + (1 - ymixing * ymixing) / (tau * tau));
+    fptype timeIntegralFou = (xmixing / tau) / (selBias * selBias + 2 * selBias / tau + (1 + xmixing * xmixing) / (tau * tau));
+    fptype ret             = timeIntegralOne * (di1 + di2);
+    ret += timeIntegralTwo * (di1 - di2);
+    ret -= 2 * timeIntegralThr * di3;
+    ret -= 2 * timeIntegralFou * di4;
+    return ret;
+}
+
+// ---- Amp4Body_TD -------------------------------------------------------------------------------------------------
+Amp4Body_TD::Amp4Body_TD(std::string n, std::vector<Observable> observables, DecayInfo4t decay, MixingTimeResolution *Tres,
+                         GooPdf *eff, Observable *mistag, long normSeed, unsigned int numNormEventsToGen)
+    : Amp4BodyBase("Amp4Body_TD", n)
+    , decayInfo(decay)
+    , resolution(Tres) {
+    efficiency = eff;
+    init(observables, mistag, {normSeed}, numNormEventsToGen);
+}
+Amp4Body_TD::Amp4Body_TD(std::string n, std::vector<Observable> observables, DecayInfo4t decay, MixingTimeResolution *Tres,
+                         GooPdf *eff, Observable *mistag, const std::vector<long> &normSeeds, unsigned int perBatch)
+    : Amp4BodyBase("Amp4Body_TD", n)
+    , decayInfo(decay)
+    , resolution(Tres) {
+    efficiency = eff;
+    init(observables, mistag, normSeeds, perBatch);
+}
+void Amp4Body_TD::init(std::vector<Observable> &observables, Observable *mistag, const std::vector<long> &seeds, unsigned int perBatch) {
+    const std::string n = getName();
+    // m12, m34, cos12, cos34, phi, eventnumber, dtime, sigmat — in this order (Amp4Body_TD.cu:327-330)
+    if(observables.size() < 8) throw GeneralError("Amp4Body_TD {} needs m12, m34, cos12, cos34, phi, event number, dtime and sigma_t", n);
+    if(decayInfo.particle_masses.size() != 5) throw GeneralError("Amp4Body_TD {}: particle_masses must hold the mother and four daughters", n);
+    if(decayInfo.amplitudes.empty() && decayInfo.amplitudes_B.empty()) throw GeneralError("Amp4Body_TD {} needs at least one amplitude", n);
+    if(!efficiency) throw GeneralError("Amp4Body_TD {} needs an efficiency function", n);
+    if(!resolution) throw GeneralError("Amp4Body_TD {} needs a decay-time resolution", n);
+    totalEventSize = static_cast<int>(observables.size()) + 2;
+    for(auto &o : observables) registerObservable(o);
+    for(double pm : decayInfo.particle_masses) registerConstant(pm);
+    registerParameter(decayInfo._tau);
+    registerParameter(decayInfo._xmixing);
+    registerParameter(decayInfo._ymixing);
+    registerParameter(decayInfo._SqWStoRSrate);
+    // Amp4Body_TD.cu:349-476: A amplitudes first (flag 0, or 2 when the same amplitude is also in the B list, which adds a
+    // second coefficient pair right behind the first), then the B amplitudes not seen yet (flag 1)
+    std::vector<Amplitude *> seen;
+    for(auto *amp : decayInfo.amplitudes) {
+        seen.push_back(amp);
+        components.push_back(amp);
+        registerParameter(amp->_ar);
+        registerParameter(amp->_ai);
+        addAmplitudeRecord(amp);
+        auto inB = std::find_if(decayInfo.amplitudes_B.begin(), decayInfo.amplitudes_B.end(), [amp](const Amplitude *A) { return *amp == *A; });
+        if(inB != decayInfo.amplitudes_B.end()) {
+            registerParameter((*inB)->_ar);
+            registerParameter((*inB)->_ai);
+            flags.push_back(2);
+        } else
+            flags.push_back(0);
+    }
+    for(auto *amp : decayInfo.amplitudes_B) {
+        if(std::find_if(seen.begin(), seen.end(), [amp](const Amplitude *A) { return *amp == *A; }) != seen.end()) continue;
+        components.push_back(amp);
+        registerParameter(amp->_ar);
+        registerParameter(amp->_ai);
+        addAmplitudeRecord(amp);
+        flags.push_back(1);
+    }
+    components.push_back(resolution);
+    components.push_back(efficiency);
+    if(mistag) {
+        registerObservable(*mistag);
+        totalEventSize = 9;
+    }
+    registerFunction("ptr_to_Amp4Body_TD", GF_OP_AMP4_TD);
+    // Normalisation sample: per seed, phase space -> accept-reject -> COMPACTED accepted events
+    // (detail/NormEvents_4Body_Base.cu:24-78; unlike Amp4Body, upstream does run the remove_if here)
+    if(perBatch > 0 && !seeds.empty()) {
+        std::vector<std::vector<fptype>> all(5);
+        for(long seed : seeds) {
+            std::vector<fptype> w;
+            auto cols = generatePhaseSpace5(decayInfo.particle_masses, perBatch, static_cast<unsigned long>(seed), &w);
+            auto acc  = unweightPhaseSpace(w, static_cast<unsigned long>(seed));
+            for(size_t i = 0; i < w.size(); i++)
+                if(acc[i])
+                    for(int k = 0; k < 5; k++) all[k].push_back(cols[k][i]);
+        }
+        if(all[0].empty()) throw GeneralError("Amp4Body_TD {}: no normalisation event was accepted", n);
+        setNormEvents(all);
+    }
+    setSeparateNorm();
+}
+void Amp4Body_TD::emitAux(detail::ProgramBuilder &B) {
+    Amp4BodyBase::emitAux(B);
+    resolution->emit(B);
+}
+int Amp4Body_TD::emit(detail::ProgramBuilder &B) {
+    int first = (int)B.nodes.size();
+    efficiency->emit(B);
+    int tdOff = 5 + (int)LineShapes.size() + (int)SpinFactors.size() + (int)ampStarts.size() + (int)ampRecords.size();
+    std::vector<int32_t> ints = headerInts(B, tdOff);
+    ints.push_back(resolution->getFunctionIndex());
+    ints.insert(ints.end(), flags.begin(), flags.end());
+    return emitRecord(B, GF_OP_AMP4_TD, 1, (int)B.nodes.size() - first + 1, ints);
+}
+fptype Amp4Body_TD::normalize() { // Amp4Body_TD.cu:744-799
+    recursiveSetNormalization(1.0);
+    ensureCache();
+    Engine &E  = Engine::get();
+    size_t nLS = LineShapes.size();
+    std::vector<uint8_t> lsRedo(nLS), ampRedo(nAmps, 0);
+    bool any = forceRedoIntegrals;
+    for(size_t i = 0; i < nLS; ++i) { // areLineshapesChanged, Amp4Body_TD.cu:690-704
+        lsRedo[i] = forceRedoIntegrals || LineShapes[i]->parametersChanged();
+        any       = any || lsRedo[i];
+    }
+    for(size_t a = 0; a < nAmps; ++a) { // areAmplitudeComponentsChanged, Amp4Body_TD.cu:706-725: per amplitude, its own lineshapes
+        auto *amp  = dynamic_cast<Amplitude *>(components[a]);
+        ampRedo[a] = forceRedoIntegrals || (amp && amp->lineshapeParametersChanged());
+        any        = any || ampRedo[a];
+    }
+    int spins          = forceRedoIntegrals ? 1 : 0;
+    forceRedoIntegrals = false;
+    E.sync();
+    if(any) Engine::check(gf_amp4_cache(E.ctx(), nodeIdx, spins, lsRedo.data(), ampRedo.data()), "gf_amp4_cache");
+    double sums[4] = {0, 0, 0, 0};
+    Engine::check(gf_amp4_norm(E.ctx(), nodeIdx, sums), "gf_amp4_norm");
+    // the reference reads tau, x, y from the Variables here (parametersList[0..2], Amp4Body_TD.cu:770-772), while the
+    // device sums above used the parameter block last pushed by updateParameters()
+    fptype tau = parametersList[0].getValue(), x = parametersList[1].getValue(), y = parametersList[2].getValue();
+    fptype ret = resolution->normalization(sums[0], sums[1], sums[2], sums[3], tau, x, y) / getSumInitNormEventWeights();
+    setNormalization(1.0 / ret);
     return ret;
 }
 

@@ -67,17 +67,13 @@ void init_physics4(py::module &m) {
         .def_readwrite("amplitudes_B", &DecayInfo4::amplitudes_B)
         .def("add_amplitude", [](DecayInfo4 &d, Amplitude *a) { d.amplitudes.push_back(a); }, py::keep_alive<1, 2>())
         .def("add_amplitude_B", [](DecayInfo4 &d, Amplitude *a) { d.amplitudes_B.push_back(a); }, py::keep_alive<1, 2>());
-    py::class_<Amp4BodyBase, GooPdf>(m, "Amp4BodyBase");
-    py::class_<Amp4Body, Amp4BodyBase>(m, "Amp4Body")
-        .def(py::init<std::string, std::vector<Observable>, DecayInfo4, GooPdf *, unsigned int>(), "name"_a, "observables"_a,
-             "decay"_a, "eff"_a, "MCeventsNorm"_a = 5000000, py::keep_alive<1, 4>(), py::keep_alive<1, 5>())
-        .def("setDataSize", &Amp4Body::setDataSize, "dataSize"_a, "evtSize"_a = 6)
-        .def("setForceIntegrals", &Amp4Body::setForceIntegrals, "f"_a = true)
-        .def("getMCevents", &Amp4Body::getMCevents)
-        .def("numLineshapes", &Amp4Body::numLineshapes)
-        .def("numSpinFactors", &Amp4Body::numSpinFactors)
+    py::class_<Amp4BodyBase, GooPdf>(m, "Amp4BodyBase")
+        .def("setForceIntegrals", &Amp4BodyBase::setForceIntegrals, "f"_a = true)
+        .def("numLineshapes", &Amp4BodyBase::numLineshapes)
+        .def("numSpinFactors", &Amp4BodyBase::numSpinFactors)
+        .def("numAmplitudes", &Amp4BodyBase::numAmplitudes)
         .def("setNormEvents",
-             [](Amp4Body &a, py::array_t<fptype, py::array::c_style | py::array::forcecast> arr) {
+             [](Amp4BodyBase &a, py::array_t<fptype, py::array::c_style | py::array::forcecast> arr) {
                  if(arr.ndim() != 2 || arr.shape(0) != 5) throw GeneralError("setNormEvents expects an array of shape (5, M)");
                  std::vector<std::vector<fptype>> cols(5);
                  for(int k = 0; k < 5; k++) cols[k].assign(arr.data(k, 0), arr.data(k, 0) + arr.shape(1));
@@ -85,14 +81,41 @@ void init_physics4(py::module &m) {
              },
              "cols5"_a)
         .def("getNormEvents",
-             [](const Amp4Body &a) {
+             [](const Amp4BodyBase &a) {
                  auto &c = a.getNormEvents();
                  size_t n = c.empty() ? 0 : c[0].size();
                  py::array_t<fptype> r({(size_t)5, n});
                  for(int k = 0; k < 5 && n; k++) std::copy(c[k].begin(), c[k].end(), r.mutable_data(k, 0));
                  return r;
              })
-        .def("getCachedAmp", [](const Amp4Body &a, size_t i) { return py::array(py::cast(a.getCachedAmp(i))); }, "a"_a);
+        .def("getCachedAmp", [](const Amp4BodyBase &a, size_t i) { return py::array(py::cast(a.getCachedAmp(i))); }, "a"_a);
+    py::class_<Amp4Body, Amp4BodyBase>(m, "Amp4Body")
+        .def(py::init<std::string, std::vector<Observable>, DecayInfo4, GooPdf *, unsigned int>(), "name"_a, "observables"_a,
+             "decay"_a, "eff"_a, "MCeventsNorm"_a = 5000000, py::keep_alive<1, 4>(), py::keep_alive<1, 5>())
+        .def("setDataSize", &Amp4Body::setDataSize, "dataSize"_a, "evtSize"_a = 6)
+        .def("getMCevents", &Amp4Body::getMCevents);
+    // time-dependent: python/PDFs/physics/{Amp4Body_TD.cu:18-38,TruthResolution.cpp,ThreeGaussResolution.cpp,DalitzPlotHelpers.cpp}
+    py::class_<MixingTimeResolution, GooPdf>(m, "MixingTimeResolution").def("normalization", &MixingTimeResolution::normalization);
+    py::class_<TruthResolution, MixingTimeResolution>(m, "TruthResolution").def(py::init<>());
+    py::class_<ThreeGaussResolution, MixingTimeResolution>(m, "ThreeGaussResolution")
+        .def(py::init<Variable, Variable, Variable, Variable, Variable, Variable, Variable, Variable, Variable, Variable, Variable,
+                      Variable, Variable>(),
+             "cf"_a, "tf"_a, "cb"_a, "cs"_a, "tb"_a, "ts"_a, "ob"_a, "os"_a, "sb"_a, "common_bias_offset"_a, "common_width_scale"_a,
+             "common_bias_offset2"_a, "common_width_scale2"_a);
+    py::class_<DecayInfo4t, DecayInfo4>(m, "DecayInfo4t")
+        .def(py::init<Variable, Variable, Variable, Variable>(), "tau"_a, "xmixing"_a, "ymixing"_a, "SqWStoRSrate"_a)
+        .def_readonly("_tau", &DecayInfo4t::_tau)
+        .def_readonly("_xmixing", &DecayInfo4t::_xmixing)
+        .def_readonly("_ymixing", &DecayInfo4t::_ymixing)
+        .def_readonly("_SqWStoRSrate", &DecayInfo4t::_SqWStoRSrate);
+    py::class_<Amp4Body_TD, Amp4BodyBase>(m, "Amp4Body_TD")
+        .def(py::init<std::string, std::vector<Observable>, DecayInfo4t, MixingTimeResolution *, GooPdf *, Observable *, long,
+                      unsigned int>(),
+             "n"_a, "observables"_a, "decay"_a, "r"_a, "eff"_a, "mistag"_a, "normSeed"_a, "MCeventsNorm"_a = 5000000,
+             py::keep_alive<1, 4>(), py::keep_alive<1, 5>(), py::keep_alive<1, 6>(), py::keep_alive<1, 7>())
+        .def("setDataSize", &Amp4Body_TD::setDataSize, "dataSize"_a, "evtSize"_a = 8)
+        .def("getNumAccNormEvents", &Amp4Body_TD::getNumAccNormEvents)
+        .def("getSumInitNormEventWeights", &Amp4Body_TD::getSumInitNormEventWeights);
     m.def("generatePhaseSpace5",
           [](std::vector<fptype> masses, size_t n, unsigned long seed) {
               std::vector<fptype> w;

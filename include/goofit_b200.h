@@ -77,7 +77,10 @@ enum gf_op {
     GF_OP_RES_NONRES,       /* resonances/NonRes.cu:8 */
     GF_OP_RES_GAUSS,        /* resonances/Gauss.cu:9 */
     GF_OP_LS = 96,          /* 4-body lineshape; consts[0] = gf_ls_kind */
-    GF_OP_SF                /* 4-body spin factor; consts[0] = gf_sf_kind */
+    GF_OP_SF,               /* 4-body spin factor; consts[0] = gf_sf_kind */
+    /* decay-time resolution records of Amp4Body_TD (never on the per-event stack) */
+    GF_OP_TRES_TRUTH = 112, /* physics/TruthResolution.cu:8-28 ; no parameters */
+    GF_OP_TRES_3GAUSS       /* physics/ThreeGaussResolution.cu:11-125 ; 13 parameters in constructor order */
 };
 
 enum gf_metric { /* MetricPointer.cu:8-58 */
@@ -132,12 +135,19 @@ int gf_amp3_integrals(gf_ctx *, int node, const uint8_t *redo_mask, const double
                       double *I_re_im /* n_res*n_res*2, row i col j */);
 int gf_amp3_get_wave(gf_ctx *, int node, int res, double *out_re_im, size_t n_events);
 
-/* Amp4Body / Amp4Body_TD: ints = {amp4_id, nLS, nSF, nAmp, td, ls_node[nLS], sf_node[nSF], AmpIndices...} */
+/* Amp4Body / Amp4Body_TD: ints = {aux slot, nLS, nSF, nAmp, td_off, ls_node[nLS], sf_node[nSF], start[nAmp],
+ * records {nLS_a, nSF_a, nPerm, LS idx..., SF idx...}}. Amp4Body: td_off = 0, params = (re, im) per amplitude.
+ * Amp4Body_TD: td_off > 0 is the offset (within the node's ints) of {resolution record, flag[nAmp]} with
+ * flag 0 = A only, 1 = B only, 2 = both (Amp4Body_TD.cu:373-381); params = tau, x, y, sqrt(WS/RS), then one (re, im)
+ * pair per coefficient in the reference's order; obs = m12, m34, cos12, cos34, phi, event number, dtime, sigma_t. */
 int gf_amp4_alloc(gf_ctx *, int node, size_t n_events);
 int gf_amp4_set_mc(gf_ctx *, int node, const double *const *mc_cols5, size_t n_mc, const double *weights,
                    const double *dtime, const double *sigma);
 int gf_amp4_cache(gf_ctx *, int node, int redo_spins, const uint8_t *ls_redo, const uint8_t *amp_redo);
-int gf_amp4_norm(gf_ctx *, int node, double *out /* 1 (Amp4Body) or 4 (TD) sums over MC events */);
+/* sum over the (local shard of the) MC sample, all-reduced when a communicator is attached.
+ * Amp4Body: out[0] = sum |sum_a c_a A_a|^2 (detail/NormIntegrator.cu:15-68).
+ * Amp4Body_TD: out[0..3] = sum |A|^2, sum |B|^2, sum Re(A B*), sum Im(A B*) (detail/NormIntegrator_TD.cu:15-99). */
+int gf_amp4_norm(gf_ctx *, int node, double *out);
 int gf_amp4_norm_async(gf_ctx *, int node);
 int gf_amp4_get_amp(gf_ctx *, int node, int amp, double *out_re_im, size_t n_events);
 

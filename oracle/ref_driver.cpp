@@ -3,7 +3,7 @@
 //   ref_driver golden <outdir>          write golden fixtures (.npy + manifest.json) for tests/golden
 //   ref_driver bench <config> <N> <K>   time K calculateNLL() calls on N synthetic events (CPU baseline)
 // Models follow the reference's examples: examples/exponential/exponential.cpp, examples/dalitz/dalitz.cpp:124-322,
-// examples/zachFit/zachFit.cpp:143-230, examples/DP4/DP4.cu:51-232.
+// examples/zachFit/zachFit.cpp:143-230, examples/DP4/DP4.cu:51-232, examples/TDDP4/TDDP4.cu:38-156.
 #include <goofit/Application.h>
 #include <goofit/FitManager.h>
 #include <goofit/PDFs/basic/ArgusPdf.h>
@@ -19,7 +19,11 @@
 #include <goofit/PDFs/physics/Amp3Body.h>
 #define private public // test infrastructure: read the reference's private MC sample and amplitude cache
 #include <goofit/PDFs/physics/Amp4Body.h>
+#include <goofit/PDFs/physics/detail/NormEvents_4Body_DeviceCached.h>
+#include <goofit/PDFs/physics/Amp4Body_TD.h>
 #undef private
+#include <goofit/PDFs/physics/ThreeGaussResolution.h>
+#include <goofit/PDFs/physics/TruthResolution.h>
 #include <goofit/PDFs/physics/Amplitude.h>
 #include <goofit/PDFs/physics/SpinFactors.h>
 #include <goofit/PDFs/physics/lineshapes/Bugg.h>
@@ -618,6 +622,215 @@ static void case_dp4_fit() {
     put("dp4fit.valid", (double)(int)fm.IsValid());
 }
 
+// ---- TDDP4 model (examples/TDDP4/TDDP4.cu:38-156; fit set-up after examples/TDDP4WeightedMC/ToyModel.cu:114-151) ----
+struct TDModel {
+    Observable m12{"m12", 0, 3}, m34{"m34", 0, 3}, cos12{"cos12", -1, 1}, cos34{"cos34", -1, 1}, phi{"phi", -3.5, 3.5};
+    EventNumber eventNumber{"eventNumber", 0, INT_MAX};
+    Observable dtime{"dtime", 0, 10}, sigmat{"sigmat", -3, 3};
+    std::vector<Variable> mix;    // tau, x, y
+    std::vector<Variable> lsvars; // RhoMass, RhoWidth, KstarM, KstarW
+    std::vector<Variable> resvars;
+    std::vector<double> pm;
+    MixingTimeResolution *res = nullptr;
+    GooPdf *eff = nullptr;
+    Amp4Body_TD *dp = nullptr;
+    PolynomialPdf *backgr = nullptr;
+    AddPdf *signal = nullptr;
+    std::vector<Observable> obs() { return {m12, m34, cos12, cos34, phi, eventNumber, dtime, sigmat}; }
+};
+// shared: 0 = A and B lists hold distinct Amplitude objects (flags 0/1, as TDDP4.cu); 1 = the P-wave amplitude object is in
+// both lists (flag 2: one cached amplitude, two coefficients, Amp4Body_TD.cu:373-381)
+static TDModel *make_tddp4(int three_gauss, unsigned int mcToGen, bool float_ls, bool float_mix, int shared = 0) {
+    auto *M = new TDModel();
+    const fptype mD0 = 1.8645, piP = 0.13957018, Km = 0.493677;
+    Variable tau = float_mix ? Variable("tau", 0.4101, 0.001, 0.100, 0.900) : Variable("tau", 0.4101);
+    Variable xm = float_mix ? Variable("xmixing", 0.005, 0.001, -0.15, 0.15) : Variable("xmixing", 0.005);
+    Variable ym = float_mix ? Variable("ymixing", 0.01, 0.001, -0.15, 0.15) : Variable("ymixing", 0.01);
+    M->mix = {tau, xm, ym};
+    DecayInfo4t DI{tau, xm, ym, Variable("SqWStoRSrate", 1.0 / sqrt(300.0))};
+    DI.meson_radius    = 1.5;
+    DI.particle_masses = {mD0, piP, piP, Km, piP};
+    M->pm              = DI.particle_masses;
+    auto V = [&](const char *n, double v, double lo, double hi) {
+        Variable x = float_ls ? Variable(n, v, 0.001, lo, hi) : Variable(n, v);
+        M->lsvars.push_back(x);
+        return x;
+    };
+    Variable RhoMass = V("rho_mass", 0.77526, 0.7, 0.85), RhoWidth = V("rho_width", 0.1478, 0.1, 0.2);
+    Variable KstarM = V("KstarM", 0.89581, 0.85, 0.95), KstarW = V("KstarW", 0.0474, 0.03, 0.07);
+    auto SF2 = [&](SF_4Body k) {
+        return std::vector<SpinFactor *>{new SpinFactor("SF", k, mD0, 0, 1, 2, 3), new SpinFactor("SF", k, mD0, 3, 1, 2, 0)};
+    };
+    auto LS4 = [&]() {
+        return std::vector<Lineshape *>{new Lineshapes::RBW("rho(770)", RhoMass, RhoWidth, 1, M_12, FF::BL2),
+                                        new Lineshapes::RBW("K*(892)bar", KstarM, KstarW, 1, M_34, FF::BL2),
+                                        new Lineshapes::RBW("rho(770)", RhoMass, RhoWidth, 1, M_24, FF::BL2),
+                                        new Lineshapes::RBW("K*(892)bar", KstarM, KstarW, 1, M_13, FF::BL2)};
+    };
+    auto *S  = new Amplitude("K*(892)rho(770)_S", Variable("amp_real1", 1.0), Variable("amp_imag1", 0.0), LS4(),
+                            SF2(SF_4Body::DtoV1V2_V1toP1P2_V2toP3P4_S), 2);
+    auto *P  = new Amplitude("K*(892)rho(770)_P", Variable("amp_real2", 0.526), Variable("amp_imag2", -0.626), LS4(),
+                            SF2(SF_4Body::DtoV1V2_V1toP1P2_V2toP3P4_P), 2);
+    auto *D  = new Amplitude("K*(892)rho(770)_D", Variable("amp_real3", 26.537), Variable("amp_imag3", 12.284), LS4(),
+                            SF2(SF_4Body::DtoV1V2_V1toP1P2_V2toP3P4_D), 2);
+    auto *SB = new Amplitude("B_K*(892)rho(770)_S", Variable("Bamp_real1", 1.0), Variable("Bamp_imag1", 0), LS4(),
+                             SF2(SF_4Body::DtoV1V2_V1toP1P2_V2toP3P4_S), 2);
+    auto *PB = new Amplitude("B_K*(892)rho(770)_P", Variable("Bamp_real2", -0.145), Variable("Bamp_imag2", 0.86), LS4(),
+                             SF2(SF_4Body::DtoV1V2_V1toP1P2_V2toP3P4_P), 2);
+    auto *DB = new Amplitude("B_K*(892)rho(770)_D", Variable("Bamp_real3", 24.343), Variable("Bamp_imag3", 5.329), LS4(),
+                             SF2(SF_4Body::DtoV1V2_V1toP1P2_V2toP3P4_D), 2);
+    DI.amplitudes_B = {S, P, D};
+    DI.amplitudes   = shared ? std::vector<Amplitude *>{SB, P, DB} : std::vector<Amplitude *>{SB, PB, DB};
+    if(three_gauss) {
+        auto R = [&](const char *n, double v) {
+            Variable x(n, v);
+            M->resvars.push_back(x);
+            return x;
+        };
+        M->res = new ThreeGaussResolution(R("coreFrac", 0.8), R("tailFrac", 0.15), R("coreBias", 0.05), R("coreScale", 1.0),
+                                          R("tailBias", 0.1), R("tailScale", 2.0), R("outlBias", -0.05), R("outlScale", 5.0),
+                                          R("selBias", 0.02), R("cbo", 0.01), R("cws", 1.1), R("cbo2", -0.02), R("cws2", 0.9));
+    } else
+        M->res = new TruthResolution();
+    Variable one("constantOne", 1), zero("constantZero", 0);
+    M->eff = new PolynomialPdf("constantEff", M->obs(), std::vector<Variable>{one}, std::vector<Variable>{zero, zero}, 0);
+    M->dp  = new Amp4Body_TD("test", M->obs(), DI, M->res, M->eff, nullptr, (long)7, mcToGen);
+    Variable constant("constant", 0.1), constant2("constant2", 1.0);
+    M->backgr = new PolynomialPdf("backgr", M->m12, {constant});
+    M->signal = new AddPdf("signal", constant2, M->dp, M->backgr);
+    return M;
+}
+// phase-space kinematics + exponential decay time + uniform per-event resolution
+static void fill_td_phsp(TDModel &M, UnbinnedDataSet &d, size_t n, long seed) {
+    std::vector<mcbooster::GReal_t> masses(M.pm.begin() + 1, M.pm.end());
+    mcbooster::PhaseSpace phsp(M.pm[0], masses, n, seed);
+    phsp.Generate(mcbooster::Vector4R(M.pm[0], 0.0, 0.0, 0.0));
+    auto d1 = phsp.GetDaughters(0), d2 = phsp.GetDaughters(1), d3 = phsp.GetDaughters(2), d4 = phsp.GetDaughters(3);
+    mcbooster::ParticlesSet_d pset = {&d1, &d2, &d3, &d4};
+    mcbooster::RealVector_d v0(n), v1(n), v2(n), v3(n), v4(n);
+    mcbooster::VariableSet_d vs = {&v0, &v1, &v2, &v3, &v4};
+    Dim5 eval;
+    mcbooster::EvaluateArray<Dim5>(eval, pset, vs);
+    std::mt19937_64 gen(seed * 7919 + 1);
+    std::uniform_real_distribution<double> u(0, 1);
+    for(size_t i = 0; i < n; i++) {
+        M.m12.setValue(v0[i]); M.m34.setValue(v1[i]); M.cos12.setValue(v2[i]); M.cos34.setValue(v3[i]); M.phi.setValue(v4[i]);
+        double t;
+        do t = -0.4101 * std::log(1.0 - u(gen)); while(t >= 10.0);
+        M.dtime.setValue(t);
+        M.sigmat.setValue(0.02 + 0.06 * u(gen));
+        M.eventNumber.setValue(d.getNumEvents());
+        d.addEvent();
+    }
+}
+static void save_td_data(const std::string &tag, TDModel &M, UnbinnedDataSet &d) {
+    save_npy(tag + ".m12", column(d, M.m12)); save_npy(tag + ".m34", column(d, M.m34)); save_npy(tag + ".cos12", column(d, M.cos12));
+    save_npy(tag + ".cos34", column(d, M.cos34)); save_npy(tag + ".phi", column(d, M.phi));
+    save_npy(tag + ".dtime", column(d, M.dtime)); save_npy(tag + ".sigmat", column(d, M.sigmat));
+}
+static void save_td_mc(const std::string &tag, TDModel &M) {
+    auto *ne = dynamic_cast<NormEvents_4Body_DeviceCached *>(M.dp->_normEvents[0].get());
+    save_npy(tag + ".mc_m12", host_copy(ne->_norm_M12_d)); save_npy(tag + ".mc_m34", host_copy(ne->_norm_M34_d));
+    save_npy(tag + ".mc_cos12", host_copy(ne->_norm_CosTheta12_d)); save_npy(tag + ".mc_cos34", host_copy(ne->_norm_CosTheta34_d));
+    save_npy(tag + ".mc_phi", host_copy(ne->_norm_phi_d));
+    put(tag + ".mc_events", M.dp->getNumAccNormEvents());
+}
+static void td_one(const std::string &tag, int three_gauss, int shared) {
+    TDModel *M = make_tddp4(three_gauss, 16000, true, true, shared);
+    UnbinnedDataSet d(M->obs());
+    fill_td_phsp(*M, d, 400, 31337);
+    if(tag == "tddp4") { // one copy of the inputs: every td case uses the same data and MC sample
+        save_td_data(tag, *M, d);
+        save_td_mc(tag, *M);
+    }
+    GooPdf *sig = M->signal;
+    Amp4Body_TD *dp = M->dp;
+    sig->setData(&d);
+    dp->setDataSize(d.getNumEvents(), 8);
+    put(tag + ".nll", sig->calculateNLL());
+    put(tag + ".integral", 1.0 / dp->getNormalization());
+    {
+        std::vector<double> amps;
+        thrust::host_vector<fpcomplex> h = *(dp->_cachedAMPs);
+        size_t nAmp = h.size() / d.getNumEvents();
+        for(size_t i = 0; i < h.size(); i++) { amps.push_back(h[i].real()); amps.push_back(h[i].imag()); }
+        save_npy(tag + ".amps", amps.data(), d.getNumEvents(), 2 * nAmp);
+    }
+    auto probs = sig->getCompProbsAtDataPoints();
+    save_npy(tag + ".prob", probs[0]);
+    sig->setFitControl(std::make_shared<UnbinnedNllFit>());
+    sig->setData(&d);
+    dp->setDataSize(d.getNumEvents(), 8);
+    put(tag + ".nll_again", sig->calculateNLL());
+    // nothing moves, but the parameter block is re-pushed from the Variables (PdfBase.cu:131-140)
+    sig->updateParameters();
+    put(tag + ".nll_after_update", sig->calculateNLL());
+    put(tag + ".integral_after_update", 1.0 / dp->getNormalization());
+    // mixing parameters move, lineshapes stay: cached amplitudes are reused, only the MC integral's time factors change
+    for(auto &v : M->lsvars) v.setChanged(false);
+    sig->updateVariable(M->mix[0], 0.4153); sig->updateVariable(M->mix[1], 0.0123); sig->updateVariable(M->mix[2], -0.0071);
+    sig->updateParameters();
+    put(tag + ".nll_mix_moved", sig->calculateNLL());
+    put(tag + ".integral_mix_moved", 1.0 / dp->getNormalization());
+    // the K*(892) mass moves
+    M->lsvars[2].setChanged(true);
+    sig->updateVariable(M->lsvars[2], 0.8975); sig->updateParameters();
+    put(tag + ".nll_kstar_moved", sig->calculateNLL());
+    put(tag + ".integral_kstar_moved", 1.0 / dp->getNormalization());
+}
+static void case_tddp4() {
+    td_one("tddp4", 0, 0);
+    td_one("tddp4g3", 1, 0);
+    td_one("tddp4sh", 0, 1);
+}
+
+static void case_tddp4_fit() {
+    TDModel *M = make_tddp4(0, 200000, false, true);
+    UnbinnedDataSet cand(M->obs());
+    fill_td_phsp(*M, cand, 400000, 2718);
+    GooPdf *sig = M->signal;
+    Amp4Body_TD *dp = M->dp;
+    // toy: accept-reject of the candidates' kinematics against the model evaluated at each candidate's own decay time,
+    // divided by the exponential the times were drawn from (so the accepted sample follows the full time-dependent model)
+    sig->setData(&cand);
+    dp->setDataSize(cand.getNumEvents(), 8);
+    auto probs = sig->getCompProbsAtDataPoints()[0];
+    std::vector<double> w(probs.size());
+    double wmax = 0;
+    for(size_t i = 0; i < probs.size(); i++) {
+        w[i] = probs[i] / std::exp(-cand.getValue(M->dtime, i) / 0.4101);
+        wmax = std::max(wmax, w[i]);
+    }
+    std::mt19937_64 gen(101);
+    std::uniform_real_distribution<double> u(0, 1);
+    UnbinnedDataSet d(M->obs());
+    for(size_t i = 0; i < probs.size(); i++) {
+        if(u(gen) * wmax > w[i]) continue;
+        M->m12.setValue(cand.getValue(M->m12, i)); M->m34.setValue(cand.getValue(M->m34, i));
+        M->cos12.setValue(cand.getValue(M->cos12, i)); M->cos34.setValue(cand.getValue(M->cos34, i));
+        M->phi.setValue(cand.getValue(M->phi, i)); M->dtime.setValue(cand.getValue(M->dtime, i));
+        M->sigmat.setValue(cand.getValue(M->sigmat, i)); M->eventNumber.setValue(d.getNumEvents());
+        d.addEvent();
+    }
+    save_td_data("tddp4fit", *M, d);
+    save_td_mc("tddp4fit", *M);
+    M->mix[0].setValue(0.40); M->mix[1].setValue(0.01); M->mix[2].setValue(0.0);
+    sig->setFitControl(std::make_shared<UnbinnedNllFit>());
+    sig->setData(&d);
+    dp->setDataSize(d.getNumEvents(), 8);
+    FitManager fit(sig);
+    fit.setVerbosity(0);
+    put("tddp4fit.nll_start", (*fit.getFCN())());
+    auto fm = fit.fit();
+    std::vector<double> val, err;
+    for(int k = 0; k < 3; k++) { val.push_back(M->mix[k].getValue()); err.push_back(M->mix[k].getError()); }
+    put_vec("tddp4fit.values", val);
+    put_vec("tddp4fit.errors", err);
+    put("tddp4fit.fval", fm.Fval());
+    put("tddp4fit.nfcn", fm.NFcn());
+    put("tddp4fit.valid", (double)(int)fm.IsValid());
+}
+
 // ---- CPU baseline timing ------------------------------------------------------------------------
 // Each step = one Minuit-style call: coefficients move (masses/widths fixed as dalitz.cpp:298-305),
 // Params::from_minuit_vector semantics (Params.cpp:47-57) then calculateNLL().
@@ -702,6 +915,8 @@ int main(int argc, char **argv) {
             if(only == "all" || only == "dalitzfit") case_dalitz_fit();
             if(only == "all" || only == "dp4") case_dp4();
             if(only == "all" || only == "dp4fit") case_dp4_fit();
+            if(only == "all" || only == "tddp4") case_tddp4();
+            if(only == "all" || only == "tddp4fit") case_tddp4_fit();
             std::ofstream f(g_out + "/manifest" + (only == "all" ? "" : "_" + only) + ".json");
             f << "{\n" << g_manifest.str() << "\n}\n";
             return 0;

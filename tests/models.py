@@ -197,3 +197,71 @@ class DP4:
     def dataset(self, cols5):
         n = len(cols5[0])
         return dataset_from_columns(self.observables, list(cols5) + [np.arange(n, dtype=np.float64)])
+
+
+class TDDP4:
+    """Time-dependent D0 -> K- pi+ pi+ pi- (examples/TDDP4/TDDP4.cu:38-156): three Bose-symmetrised K* rho amplitudes for
+    each of A and B, TruthResolution or ThreeGaussResolution, AddPdf(1.0; Amp4Body_TD, flat bkg) — the tree
+    oracle/ref_driver.cpp make_tddp4() builds with the reference's classes."""
+
+    def __init__(self, three_gauss=False, float_ls=False, float_mix=True, shared=False, mc_to_gen=0, norm_seed=7):
+        k = self.keep = Keep()
+        O, V = gf.Observable, gf.Variable
+        self.m12, self.m34 = O("m12", 0, 3), O("m34", 0, 3)
+        self.cos12, self.cos34, self.phi = O("cos12", -1, 1), O("cos34", -1, 1), O("phi", -3.5, 3.5)
+        self.evt = gf.EventNumber("eventNumber", 0, 2147483647)
+        self.dtime, self.sigmat = O("dtime", 0, 10), O("sigmat", -3, 3)
+        mD0, piP, Km = 1.8645, 0.13957018, 0.493677
+        if float_mix:
+            tau, xm, ym = V("tau", 0.4101, 0.001, 0.100, 0.900), V("xmixing", 0.005, 0.001, -0.15, 0.15), V("ymixing", 0.01, 0.001, -0.15, 0.15)
+        else:
+            tau, xm, ym = V("tau", 0.4101), V("xmixing", 0.005), V("ymixing", 0.01)
+        self.mix = [tau, xm, ym]
+        info = self.info = gf.DecayInfo4t(tau, xm, ym, V("SqWStoRSrate", 1.0 / np.sqrt(300.0)))
+        info.meson_radius = 1.5
+        info.particle_masses = [mD0, piP, piP, Km, piP]
+        self.lsvars = []
+
+        def LV(n, v, lo, hi):
+            x = V(n, v, 0.001, lo, hi) if float_ls else V(n, v)
+            self.lsvars.append(x)
+            return x
+
+        RhoMass, RhoWidth = LV("rho_mass", 0.77526, 0.7, 0.85), LV("rho_width", 0.1478, 0.1, 0.2)
+        KstarM, KstarW = LV("KstarM", 0.89581, 0.85, 0.95), LV("KstarW", 0.0474, 0.03, 0.07)
+        S, L, P, FF = gf.SF_4Body, gf.Lineshapes, gf.DP4Pair, gf.FF
+
+        def SF2(kind):
+            return [k(gf.SpinFactor("SF", kind, mD0, 0, 1, 2, 3)), k(gf.SpinFactor("SF", kind, mD0, 3, 1, 2, 0))]
+
+        def LS4():
+            return [k(L.RBW("rho(770)", RhoMass, RhoWidth, 1, int(P.M_12), FF.BL2)), k(L.RBW("K*(892)bar", KstarM, KstarW, 1, int(P.M_34), FF.BL2)),
+                    k(L.RBW("rho(770)", RhoMass, RhoWidth, 1, int(P.M_24), FF.BL2)), k(L.RBW("K*(892)bar", KstarM, KstarW, 1, int(P.M_13), FF.BL2))]
+
+        A = gf.Amplitude
+        Sa = k(A("K*(892)rho(770)_S", V("amp_real1", 1.0), V("amp_imag1", 0.0), LS4(), SF2(S.DtoV1V2_V1toP1P2_V2toP3P4_S), 2))
+        Pa = k(A("K*(892)rho(770)_P", V("amp_real2", 0.526), V("amp_imag2", -0.626), LS4(), SF2(S.DtoV1V2_V1toP1P2_V2toP3P4_P), 2))
+        Da = k(A("K*(892)rho(770)_D", V("amp_real3", 26.537), V("amp_imag3", 12.284), LS4(), SF2(S.DtoV1V2_V1toP1P2_V2toP3P4_D), 2))
+        SB = k(A("B_K*(892)rho(770)_S", V("Bamp_real1", 1.0), V("Bamp_imag1", 0.0), LS4(), SF2(S.DtoV1V2_V1toP1P2_V2toP3P4_S), 2))
+        PB = k(A("B_K*(892)rho(770)_P", V("Bamp_real2", -0.145), V("Bamp_imag2", 0.86), LS4(), SF2(S.DtoV1V2_V1toP1P2_V2toP3P4_P), 2))
+        DB = k(A("B_K*(892)rho(770)_D", V("Bamp_real3", 24.343), V("Bamp_imag3", 5.329), LS4(), SF2(S.DtoV1V2_V1toP1P2_V2toP3P4_D), 2))
+        for a in (Sa, Pa, Da):
+            info.add_amplitude_B(a)
+        for a in ((SB, Pa, DB) if shared else (SB, PB, DB)):
+            info.add_amplitude(a)
+        if three_gauss:
+            vals = [("coreFrac", 0.8), ("tailFrac", 0.15), ("coreBias", 0.05), ("coreScale", 1.0), ("tailBias", 0.1), ("tailScale", 2.0),
+                    ("outlBias", -0.05), ("outlScale", 5.0), ("selBias", 0.02), ("cbo", 0.01), ("cws", 1.1), ("cbo2", -0.02), ("cws2", 0.9)]
+            self.res = k(gf.ThreeGaussResolution(*[V(n, v) for n, v in vals]))
+        else:
+            self.res = k(gf.TruthResolution())
+        self.observables = [self.m12, self.m34, self.cos12, self.cos34, self.phi, self.evt, self.dtime, self.sigmat]
+        self.eff = k(gf.PolynomialPdf("constantEff", self.observables, [V("constantOne", 1)], [V("constantZero", 0)] * 2, 0))
+        self.dp = gf.Amp4Body_TD("test", self.observables, info, self.res, self.eff, None, norm_seed, mc_to_gen)
+        self.backgr = k(gf.PolynomialPdf("backgr", self.m12, [V("constant", 0.1)]))
+        self.signal = gf.AddPdf("signal", V("constant2", 1.0), self.dp, self.backgr)
+
+    def dataset(self, cols7):
+        """cols7 = m12, m34, cos12, cos34, phi, dtime, sigmat"""
+        n = len(cols7[0])
+        return dataset_from_columns(self.observables, list(cols7[:5]) + [np.arange(n, dtype=np.float64)] + list(cols7[5:7]))

@@ -173,15 +173,46 @@ def test_golden_known_answers(golden):
     nll = -np.sum(np.log(np.exp(-2 * x) / golden["exp.normalize"]))
     assert golden["exp.nll"] == pytest.approx(nll, rel=1e-12)
     assert golden["exp.nll"] == golden["exp.nll_again"]
-    assert golden["dalitzfit.valid"] == 1 and golden["dp4fit.valid"] == 1
+    assert golden["dalitzfit.valid"] == 1 and golden["dp4fit.valid"] == 1 and golden["tddp4fit.valid"] == 1
+    # time-dependent fixtures: nothing moved between these calls, so the reference must repeat itself exactly
+    for tag in ("tddp4", "tddp4g3", "tddp4sh"):
+        assert golden[tag + ".nll"] == golden[tag + ".nll_again"] == golden[tag + ".nll_after_update"]
+    # an amplitude object shared by the A and B lists changes the model; truth vs three-Gauss resolution too
+    assert golden["tddp4.nll"] != golden["tddp4sh.nll"] and golden["tddp4.nll"] != golden["tddp4g3.nll"]
+
+
+def test_tddp4_host_bookkeeping():
+    """Amp4Body_TD host side without a GPU: unique lineshapes / spin factors, A/B/both amplitude lists
+    (Amp4Body_TD.cu:349-476) and the resolutions' host-side time integrals (TruthResolution.cu:56-70,
+    ThreeGaussResolution.cu:155-182)."""
+    from models import TDDP4
+    M = TDDP4()
+    assert (M.dp.numLineshapes(), M.dp.numSpinFactors(), M.dp.numAmplitudes()) == (4, 6, 6)
+    assert len(M.dp.getParameters()) >= 4
+    Msh = TDDP4(shared=True)
+    assert Msh.dp.numAmplitudes() == 5
+    di = (3.0, 700.0, 11.0, -5.0)
+    tau, x, y = 0.41, 0.006, -0.009
+    i1, i2 = tau / (1 - y * y), tau / (1 + x * x)
+    want = i1 * (di[0] + di[1]) + i2 * (di[0] - di[1]) - 2 * y * i1 * di[2] - 2 * x * i2 * di[3]
+    assert M.res.normalization(*di, tau, x, y) == pytest.approx(want, rel=1e-15)
+    G = TDDP4(three_gauss=True)
+    sb = 0.02
+    den1 = sb * sb + 2 * sb / tau + (1 - y * y) / (tau * tau)
+    den2 = sb * sb + 2 * sb / tau + (1 + x * x) / (tau * tau)
+    want = (sb + 1 / tau) / den1 * (di[0] + di[1]) + (sb + 1 / tau) / den2 * (di[0] - di[1]) - 2 * (y / tau) / den1 * di[2] - 2 * (x / tau) / den2 * di[3]
+    assert G.res.normalization(*di, tau, x, y) == pytest.approx(want, rel=1e-15)
+    with pytest.raises(Exception):
+        M.dp.normalize()  # no dataset / no GPU: must fail loudly, never fall back
 
 
 @pytest.mark.skipif(not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "ref_driver")), reason="oracle/_ref not built")
 def test_oracle_reproduces_fixtures(tmp_path, golden):
     out = str(tmp_path / "g")
-    for case in ("basic", "dalitz", "dp4"):
+    for case in ("basic", "dalitz", "dp4", "tddp4"):
         subprocess.run([os.path.join(ROOT, "oracle", "_ref", "ref_driver"), "golden", out, case], check=True, capture_output=True, timeout=600)
-    for name in ("exp.prob", "conv.grid", "convadd.prob", "dalitz.waves", "dalitz.prob", "dp4.amps", "dp4.prob"):
+    for name in ("exp.prob", "conv.grid", "convadd.prob", "dalitz.waves", "dalitz.prob", "dp4.amps", "dp4.prob", "tddp4.amps", "tddp4.prob",
+                 "tddp4g3.prob", "tddp4sh.amps", "tddp4sh.prob"):
         np.testing.assert_allclose(np.load(os.path.join(out, name + ".npy")), golden.arr(name), rtol=1e-13, atol=0)
 
 

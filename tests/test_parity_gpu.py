@@ -328,6 +328,97 @@ def test_dp4_fit_matches_reference(golden):
     assert pulls.max() < 0.01, pulls
     assert rel(res.Fval(), golden["dp4fit.fval"]) < 1e-9
 
+TD_DATA = ("m12", "m34", "cos12", "cos34", "phi", "dtime", "sigmat")
+TD_MC = ("m12", "m34", "cos12", "cos34", "phi")
+
+
+@pytest.mark.parametrize("tag,three_gauss,shared", [("tddp4", False, False), ("tddp4g3", True, False), ("tddp4sh", False, True)])
+def test_tddp4_values(golden, tag, three_gauss, shared):
+    """Amp4Body_TD (Amp4Body_TD.cu:167-261,744-799) with TruthResolution / ThreeGaussResolution, and with one amplitude
+    object shared by the A and B lists (flag 2). All three cases run on the same data and MC sample."""
+    from models import TDDP4
+    M = TDDP4(three_gauss=three_gauss, float_ls=True, float_mix=True, shared=shared)
+    mc = np.vstack([golden.arr("tddp4.mc_" + n) for n in TD_MC])
+    assert mc.shape[1] == int(golden["tddp4.mc_events"])
+    M.dp.setNormEvents(mc)
+    d = M.dataset([golden.arr("tddp4." + n) for n in TD_DATA])
+    sig, dp = M.signal, M.dp
+    namp = 5 if shared else 6
+    assert dp.numLineshapes() == 4 and dp.numSpinFactors() == 6 and dp.numAmplitudes() == namp
+    sig.setData(d)
+    dp.setDataSize(len(d), 8)
+    nll = sig.calculateNLL()
+    ref = golden.arr(tag + ".amps")  # [event, 2*amp]
+    for a in range(namp):
+        w = np.asarray(dp.getCachedAmp(a))
+        r = ref[:, 2 * a] + 1j * ref[:, 2 * a + 1]
+        assert np.max(np.abs(w - r) / np.maximum(np.abs(r), 1e-300)) < 1e-10, a
+    # The time integral tau/(1-y^2) (|A|^2+|B|^2) + tau/(1+x^2) (|A|^2-|B|^2) - ... cancels the dominant |B|^2 sum to
+    # O(x^2+y^2) on the host (TruthResolution.cu:56-70), which amplifies the ~1e-16 association differences of the four MC
+    # sums by ~|B|^2/|result| ~ 1e3-1e4: the integral is compared at 1e-11, the NLL (which sees N log(integral)) at 1e-12.
+    RTOL_INT = 1e-11
+    assert rel(1.0 / dp.getNormalization(), golden[tag + ".integral"]) < RTOL_INT
+    assert rel(nll, golden[tag + ".nll"]) < RTOL_NLL
+    probs = sig.getCompProbsAtDataPoints()
+    # per-event values: 1e-10 relative; events deep in the resolution tail (p ~ 1e-6 of the typical value) are sums of
+    # cancelling erfc/exp terms, so they additionally get an absolute allowance of a few ulp of the typical value
+    want = golden.arr(tag + ".prob")
+    np.testing.assert_allclose(probs[0], want, rtol=1e-10, atol=1e-15 * float(np.median(want)) * 16)
+    sig.setFitControl(gf.UnbinnedNllFit())
+    sig.setData(d)
+    dp.setDataSize(len(d), 8)
+    assert sig.calculateNLL() == nll
+    sig.updateParameters()
+    assert rel(sig.calculateNLL(), golden[tag + ".nll_after_update"]) < RTOL_NLL
+    for v in M.lsvars:
+        v.changed = False
+    sig.updateVariable(M.mix[0], 0.4153)
+    sig.updateVariable(M.mix[1], 0.0123)
+    sig.updateVariable(M.mix[2], -0.0071)
+    sig.updateParameters()
+    before = gf.launch_count()
+    assert rel(sig.calculateNLL(), golden[tag + ".nll_mix_moved"]) < RTOL_NLL
+    assert rel(1.0 / dp.getNormalization(), golden[tag + ".integral_mix_moved"]) < RTOL_INT
+    # steady state: backgr grid integral + MC integral (4 sums) + NLL kernel
+    assert gf.launch_count() - before == 3
+    M.lsvars[2].changed = True
+    sig.updateVariable(M.lsvars[2], 0.8975)
+    sig.updateParameters()
+    assert rel(sig.calculateNLL(), golden[tag + ".nll_kstar_moved"]) < RTOL_NLL
+    assert rel(1.0 / dp.getNormalization(), golden[tag + ".integral_kstar_moved"]) < RTOL_INT
+
+
+def test_tddp4_fit_matches_reference(golden):
+    from models import TDDP4
+    M = TDDP4(three_gauss=False, float_ls=False, float_mix=True)
+    M.dp.setNormEvents(np.vstack([golden.arr("tddp4fit.mc_" + n) for n in TD_MC]))
+    d = M.dataset([golden.arr("tddp4fit." + n) for n in TD_DATA])
+    sig, dp = M.signal, M.dp
+    M.mix[0].value, M.mix[1].value, M.mix[2].value = 0.40, 0.01, 0.0
+    sig.setData(d)
+    dp.setDataSize(len(d), 8)
+    fm = gf.FitManager(sig)
+    fm.setVerbosity(0)
+    assert rel(fm.getFCN()(), golden["tddp4fit.nll_start"]) < RTOL_NLL
+    res = fm.fit()
+    assert bool(fm)
+    val, err = np.array(golden["tddp4fit.values"]), np.array(golden["tddp4fit.errors"])
+    mine = np.array([c.value for c in M.mix])
+    pulls = np.abs(mine - val) / err
+    assert pulls.max() < 0.01, pulls
+    assert rel(res.Fval(), golden["tddp4fit.fval"]) < 1e-9
+
+
+def test_tddp4_generated_norm_sample():
+    """the constructor's own normalisation sample: phase space -> accept-reject -> compacted accepted events
+    (NormEvents_4Body_Base.cu:24-78), deterministic in the seed"""
+    from models import TDDP4
+    A, B, C = TDDP4(mc_to_gen=20000, norm_seed=7), TDDP4(mc_to_gen=20000, norm_seed=7), TDDP4(mc_to_gen=20000, norm_seed=8)
+    a, b, c = A.dp.getNormEvents(), B.dp.getNormEvents(), C.dp.getNormEvents()
+    assert a.shape[0] == 5 and 0 < a.shape[1] < 20000 and A.dp.getNumAccNormEvents() == a.shape[1]
+    assert np.array_equal(a, b) and (a.shape != c.shape or not np.array_equal(a, c))
+    assert A.dp.getSumInitNormEventWeights() == a.shape[1]
+
 
 def test_cpp_example_exponential():
     # the reference's examples/exponential flow compiled against the drop-in C++ headers (examples/exponential.cpp)
