@@ -54,23 +54,22 @@ __global__ void __launch_bounds__(GF_THREADS, 2)
     const int nres = in[1];
     const gf_decay3 D = gf_load_decay3(P.consts + nd.con_off);
     const double *c12 = P.cols[ob[0]], *c13 = P.cols[ob[1]];
+    __shared__ gf_amp3_shared S;
+    gf_amp3_prepare(S, P, in + 2, nres, mask, D);
+    __syncthreads();
     const long stride = (long)gridDim.x * blockDim.x;
     for(long e = (long)blockIdx.x * blockDim.x + threadIdx.x; e < V.n_events; e += stride) {
         double m12 = __ldg(c12 + e), m13 = __ldg(c13 + e);
         bool inside = gf_in_dalitz(m12, m13, D.M, D.d1, D.d2, D.d3);
         double m23 = D.M * D.M + D.d1 * D.d1 + D.d2 * D.d2 + D.d3 * D.d3 - m12 - m13;
-        for(int i = 0; i < nres; ++i) {
-            if(!((mask >> i) & 1ull)) continue;
-            double2 w = make_double2(0.0, 0.0);
-            if(inside) w = gf_resonance(P.nodes[in[2 + i]], P.params, P.consts, D, m12, m13, m23);
-            waves[(size_t)i * ld + e] = w;
-        }
+        // written once, next read by another kernel: streaming stores
+        gf_amp3_point(S, P, in + 2, D, inside, m12, m13, m23, [&](int i, double2 w) { __stcs(waves + (size_t)i * ld + e, w); });
     }
 }
 
 // Bin centres as SpecialResonanceIntegrator.cu:60-77, including its use of the m12 bin count for the
 // m13 step (slot [2] read twice) — identical for square grids.
-__global__ void __launch_bounds__(GF_THREADS, 2)
+__global__ void __launch_bounds__(GF_THREADS, 1) // <= 57 600 bins: latency-bound, registers are free
     k_amp3_grid(const gf_dev_view V, int node, int eff_first, int eff_root, unsigned long long mask, double lo12,
                 double hi12, int n12, double lo13, double hi13, long n_bins, double2 *gridB, double *gridEff) {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -81,6 +80,9 @@ __global__ void __launch_bounds__(GF_THREADS, 2)
     const int32_t *ob = P.ints + nd.obs_off;
     const int nres = in[1];
     const gf_decay3 D = gf_load_decay3(P.consts + nd.con_off);
+    __shared__ gf_amp3_shared S;
+    gf_amp3_prepare(S, P, in + 2, nres, mask, D);
+    __syncthreads();
     const long stride = (long)gridDim.x * blockDim.x;
     for(long b = (long)blockIdx.x * blockDim.x + threadIdx.x; b < n_bins; b += stride) {
         int b12 = (int)(b % n12);
@@ -95,12 +97,7 @@ __global__ void __launch_bounds__(GF_THREADS, 2)
         m13 += lo13;
         bool inside = gf_in_dalitz(m12, m13, D.M, D.d1, D.d2, D.d3);
         double m23 = D.M * D.M + D.d1 * D.d1 + D.d2 * D.d2 + D.d3 * D.d3 - m12 - m13;
-        for(int i = 0; i < nres; ++i) {
-            if(!((mask >> i) & 1ull)) continue;
-            double2 w = make_double2(0.0, 0.0);
-            if(inside) w = gf_resonance(P.nodes[in[2 + i]], P.params, P.consts, D, m12, m13, m23);
-            gridB[(size_t)i * n_bins + b] = w;
-        }
+        gf_amp3_point(S, P, in + 2, D, inside, m12, m13, m23, [&](int i, double2 w) { gridB[(size_t)i * n_bins + b] = w; });
         gf_evt_vals evt;
 #pragma unroll
         for(int k = 0; k < GF_MAX_OBS; k++) evt.v[k] = 0;

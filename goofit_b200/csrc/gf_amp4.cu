@@ -1,5 +1,6 @@
 // gf_amp4.cu — Amp4Body caches and the Monte-Carlo normalisation integral.
-//   k_amp4_cache  ONE pass per event set (data or MC): get4Vecs once, then every flagged spin factor and
+//   k_amp4_sf     ONE pass per event set (data or MC), once: get4Vecs, then every spin factor
+//   k_amp4_cache  ONE pass per event set: get4Vecs once (only if a flagged lineshape needs it), then every flagged
 //                 lineshape (the reference launches one thrust::transform per spin factor / lineshape and
 //                 recomputes get4Vecs in each: Amp4Body.cu:432-525, detail/{SF,LS,NormSpin,NormLS}Calculator.cu)
 //   k_amp4_amps   A_a = 1/sqrt(nPerm) * sum_perm prod LS * prod SF for every flagged amplitude
@@ -57,8 +58,10 @@ struct gf_amp4_args {
 
 // ints of the AMP4 node: {aux slot, nLS, nSF, nAmp, td, ls_node[nLS], sf_node[nSF], start[nAmp], records...}
 // record of amplitude a = {nLS_a, nSF_a, nPerm, LS indices..., SF indices...} (Amp4Body.cu:222-231)
-__global__ void __launch_bounds__(GF_THREADS, 2)
-    k_amp4_cache(const gf_dev_view V, int node, gf_amp4_args A, int redo_spins, unsigned long long ls_mask) {
+// Spin factors are computed once per event sample; their tensor algebra wants many registers, so they get their own
+// kernel at one block per SM instead of setting the register budget of the lineshape kernel, which reruns whenever a
+// mass or width moves.
+__global__ void __launch_bounds__(GF_THREADS, 1) k_amp4_sf(const gf_dev_view V, int node, gf_amp4_args A) {
     extern __shared__ __align__(16) unsigned char smem[];
     gf_sprog P = gf_stage_program(V, smem);
     __syncthreads();
@@ -73,12 +76,33 @@ __global__ void __launch_bounds__(GF_THREADS, 2)
                c34 = __ldg(A.cols[3] + e), phi = __ldg(A.cols[4] + e);
         double vecs[16];
         gf_get4vecs(vecs, m12, m34, c12, c34, phi, M, m1, m2, m3, m4);
-        if(redo_spins) {
-            for(int k = 0; k < nSF; ++k) {
-                const gf_node &sn = P.nodes[in[5 + nLS + k]];
-                int kind = P.ints[sn.int_off];
-                A.sf[(size_t)k * A.ld + e] = gf_spinfactor(kind, P.consts + sn.con_off, vecs);
-            }
+        for(int k = 0; k < nSF; ++k) {
+            const gf_node &sn = P.nodes[in[5 + nLS + k]];
+            int kind = P.ints[sn.int_off];
+            A.sf[(size_t)k * A.ld + e] = gf_spinfactor(kind, P.consts + sn.con_off, vecs);
+        }
+    }
+}
+
+// every flagged lineshape in one pass. The four-vectors (~10 sqrt, 15 div, sin, cos) are only needed by lineshapes of
+// pairs other than (12) and (34); need_vecs is uniform over the grid.
+__global__ void __launch_bounds__(GF_THREADS, 2)
+    k_amp4_cache(const gf_dev_view V, int node, gf_amp4_args A, unsigned long long ls_mask, int need_vecs) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    gf_sprog P = gf_stage_program(V, smem);
+    __syncthreads();
+    const gf_node &nd = P.nodes[node];
+    const int32_t *in = P.ints + nd.int_off;
+    const double *mc = P.consts + nd.con_off; // M, m1, m2, m3, m4
+    const int nLS = in[1];
+    const double M = mc[0], m1 = mc[1], m2 = mc[2], m3 = mc[3], m4 = mc[4];
+    const long stride = (long)gridDim.x * blockDim.x;
+    for(long e = (long)blockIdx.x * blockDim.x + threadIdx.x; e < A.n; e += stride) {
+        double m12 = __ldg(A.cols[0] + e), m34 = __ldg(A.cols[1] + e);
+        double vecs[16];
+        if(need_vecs) {
+            double c12 = __ldg(A.cols[2] + e), c34 = __ldg(A.cols[3] + e), phi = __ldg(A.cols[4] + e);
+            gf_get4vecs(vecs, m12, m34, c12, c34, phi, M, m1, m2, m3, m4);
         }
         for(int i = 0; i < nLS; ++i) {
             if(!((ls_mask >> i) & 1ull)) continue;
@@ -94,7 +118,7 @@ __global__ void __launch_bounds__(GF_THREADS, 2)
             } else
                 mres = gf_getmass(pair, d1, d2, vecs, m1, m2, m3, m4);
             gf_cplx r = gf_lineshape(kind, P.params + ln.par_off, lc, mres, d1, d2);
-            A.ls[(size_t)i * A.ld + e] = make_double2(r.re, r.im);
+            __stcs(A.ls + (size_t)i * A.ld + e, make_double2(r.re, r.im));
         }
     }
 }
@@ -307,9 +331,20 @@ static int run_set(gf_ctx *c, gf_amp4_state *s, int node, gf_amp4_set &S, int re
     A.n = S.n; A.ld = S.ld; A.ls = S.ls; A.sf = S.sf; A.amps = S.amps;
     size_t sm = gf_prog_smem(c);
     int blocks = gf_grid_blocks(c, S.n, 2);
-    if(redo_spins || ls_mask) {
+    if(redo_spins) {
+        int sf_blocks = gf_grid_blocks(c, S.n, 1);
+        if(sm > 48 * 1024) cudaFuncSetAttribute(k_amp4_sf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        k_amp4_sf<<<sf_blocks, GF_THREADS, sm, c->stream>>>(c->view, node, A);
+        c->launches++;
+    }
+    if(ls_mask) {
+        int need_vecs = 0;
+        const gf_node &nd = c->h_nodes[node];
+        const int32_t *in = c->h_ints.data() + nd.int_off;
+        for(int i = 0; i < s->nLS && !need_vecs; i++)
+            if(((ls_mask >> i) & 1ull) && (int)c->h_consts[c->h_nodes[in[5 + i]].con_off] >= 2) need_vecs = 1;
         if(sm > 48 * 1024) cudaFuncSetAttribute(k_amp4_cache, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-        k_amp4_cache<<<blocks, GF_THREADS, sm, c->stream>>>(c->view, node, A, redo_spins, ls_mask);
+        k_amp4_cache<<<blocks, GF_THREADS, sm, c->stream>>>(c->view, node, A, ls_mask, need_vecs);
         c->launches++;
     }
     if(amp_mask) {

@@ -341,6 +341,45 @@ extern "C" int gf_timer_stop(gf_ctx *c, float *ms) {
     GF_CUDA(cudaEventElapsedTime(ms, c->t0, c->t1));
     return 0;
 }
+// ---- FP64 peak micro-benchmark: the denominator of the FP64-bound kernels' roofline -------------------------------
+// 8 independent DFMA chains per thread, 1024 threads per SM-resident block pair; flops = 2 per DFMA.
+__global__ void __launch_bounds__(256) k_dfma_peak(double *out, int iters, double a, double b) {
+    double x0 = threadIdx.x * 1e-9, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+    for(int i = 0; i < iters; ++i) {
+#pragma unroll
+        for(int u = 0; u < 8; ++u) {
+            x0 = fma(x0, a, b); x1 = fma(x1, a, b); x2 = fma(x2, a, b); x3 = fma(x3, a, b);
+            x4 = fma(x4, a, b); x5 = fma(x5, a, b); x6 = fma(x6, a, b); x7 = fma(x7, a, b);
+        }
+    }
+    double s = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+    if(s == 123.456) out[0] = s; // never true; keeps the chains alive
+}
+extern "C" int gf_fp64_peak(gf_ctx *c, double *tflops) {
+    if(!c || !tflops) return gf_fail("gf_fp64_peak: null argument");
+    cudaSetDevice(c->device);
+    const int blocks = c->sm_count * 8, iters = 4096;
+    cudaEvent_t e0, e1;
+    GF_CUDA(cudaEventCreate(&e0));
+    GF_CUDA(cudaEventCreate(&e1));
+    double best = 0;
+    for(int rep = 0; rep < 6; ++rep) {
+        GF_CUDA(cudaEventRecord(e0, c->stream));
+        k_dfma_peak<<<blocks, 256, 0, c->stream>>>(c->d_result + GF_NPARTIAL - 1, iters, 0.999999, 1e-9);
+        GF_CUDA(cudaEventRecord(e1, c->stream));
+        GF_CUDA(cudaEventSynchronize(e1));
+        float ms = 0;
+        GF_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        double tf = 2.0 * 64.0 * iters * 256.0 * blocks / (ms * 1e-3) / 1e12;
+        if(rep > 0 && tf > best) best = tf;
+    }
+    c->launches += 6;
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *tflops = best;
+    return 0;
+}
+
 extern "C" int gf_set_params_async(gf_ctx *c, const double *params, int n, const double *norms, int n_norms) {
     if(!c) return gf_fail("null ctx");
     if(n != c->n_params) return gf_fail("gf_set_params_async: size mismatch");

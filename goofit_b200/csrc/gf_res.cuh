@@ -198,3 +198,159 @@ __device__ inline double2 gf_resonance(const gf_node &nd, const double *params, 
     default: return make_double2(0.0, 0.0);
     }
 }
+
+// out-of-line copy for the rare resonance kinds, so that their log/pow-heavy code does not set the register budget of
+// the cache kernels' main loop
+__device__ __noinline__ double2 gf_resonance_cold(const gf_node *nd, const double *params, const double *consts,
+                                                  const gf_decay3 *D, double m12, double m13, double m23) {
+    return gf_resonance(*nd, params, consts, *D, m12, m13, m23);
+}
+
+// ---- shared-work evaluation of all resonances of one Amp3Body ------------------------------------------------------
+// The reference evaluates every resonance from scratch (one thrust::transform per resonance). Of that work
+//   * q0, qM0 and the numerators of the normalised Blatt-Weisskopf ratios depend on the resonance parameters only
+//     -> gf_res_inv, computed once per block into shared memory;
+//   * s, sqrt(s), q(s), qM(s) and the Zemach factors depend on the event and the resonant PAIR only, and the 16
+//     resonances of examples/dalitz share 3 pairs -> gf_pair_inv, computed once per event and pair.
+// Every shared quantity is produced by the same operations as above, so it is bit-identical to the unshared path; the
+// one deliberate change is pow(q/q0, 2*spin+1) -> a multiply chain (<= 2 ulp from libm's pow; spin 0 is exact).
+struct gf_res_inv {
+    int op, spin, cyc, norm, nterm, pad;
+    double mass, width, mass2;
+    double q0[2], qM0[2], frn[2], frMn[2]; // per symmetrisation term (cyc, cyc+1)
+};
+struct gf_pair_inv {
+    double s, rs, q, qMn, qMp, z1, z2; // z1/z2: Zemach factor for spin 1 / 2
+};
+struct gf_pair_need { // what the flagged resonances need of each pair (uniform over the grid)
+    int used, norm, plain, maxspin;
+};
+
+__device__ inline void gf_pair_masses(int cyc, const gf_decay3 &D, double &da, double &db, double &bach) {
+    da = cyc == GF_PAIR_23 ? D.d2 : D.d1;
+    db = cyc == GF_PAIR_12 ? D.d2 : D.d3;
+    bach = cyc == GF_PAIR_12 ? D.d3 : (cyc == GF_PAIR_13 ? D.d2 : D.d1);
+}
+__device__ inline void gf_res_prepare(gf_res_inv &R, const gf_node &nd, const double *params, const double *consts,
+                                      const gf_decay3 &D) {
+    const double *p = params + nd.par_off;
+    const double *c = consts + nd.con_off;
+    R.op = nd.op;
+    R.spin = 0; R.cyc = 0; R.norm = 0; R.nterm = 1; R.pad = 0;
+    R.mass = R.width = R.mass2 = 0;
+    if(nd.op == GF_OP_RES_NONRES) return;
+    R.mass = p[0]; R.width = p[1]; R.mass2 = p[0] * p[0];
+    if(nd.op == GF_OP_RES_GAUSS) { R.cyc = (int)c[0]; return; }
+    R.spin = (int)c[0]; R.cyc = (int)c[1]; R.norm = c[2] != 0.0;
+    R.nterm = nd.op == GF_OP_RES_RBW_SYM ? 2 : 1;
+    int cyc = R.cyc;
+    for(int t = 0; t < R.nterm; ++t) {
+        double da, db, bach;
+        gf_pair_masses(cyc, D, da, db, bach);
+        R.q0[t] = gf_cm_mom(R.mass2, da, db);
+        R.qM0[t] = R.norm ? gf_cm_mom_mother(R.mass2, D.M, bach) : 0.0;
+        R.frn[t] = R.spin ? gf_damp_sq_norm(R.q0[t], R.spin, D.rad) : 1.0;
+        R.frMn[t] = R.spin ? gf_damp_sq_norm(R.qM0[t], R.spin, D.mrad) : 1.0;
+        cyc = (cyc + 1) % 3;
+    }
+}
+__device__ inline void gf_pair_prepare(gf_pair_inv &Q, const gf_pair_need &need, int cyc, const gf_decay3 &D, double m12,
+                                       double m13, double m23) {
+    double da, db, bach;
+    gf_pair_masses(cyc, D, da, db, bach);
+    Q.s = cyc == GF_PAIR_12 ? m12 : (cyc == GF_PAIR_13 ? m13 : m23);
+    Q.rs = sqrt(Q.s);
+    Q.q = gf_cm_mom(Q.s, da, db);
+    Q.qMn = need.norm ? gf_cm_mom_mother(Q.s, D.M, bach) : 0.0;
+    Q.qMp = need.plain ? gf_cm_mom(D.M * D.M, Q.rs, bach) : 0.0;
+    Q.z1 = Q.z2 = 1.0;
+    if(need.maxspin >= 1) Q.z1 = gf_spin3(1, D, m12, m13, m23, cyc);
+    if(need.maxspin >= 2) Q.z2 = gf_spin3(2, D, m12, m13, m23, cyc);
+}
+__device__ inline double gf_pow_odd(double r, int spin) { // r^(2 spin + 1)
+    double r2 = r * r, out = r;
+    for(int k = 0; k < spin; ++k) out *= r2;
+    return out;
+}
+// one plain-RBW term from the shared pieces (RBW.cu:9-86 with the event/pair part hoisted into P)
+__device__ inline double2 gf_rbw_term(const gf_res_inv &R, const gf_pair_inv &P, const gf_decay3 &D) {
+    const int spin = R.spin;
+    double fr = 1, frM = 1;
+    if(spin != 0) {
+        if(R.norm) {
+            fr = R.frn[0] / gf_damp_sq_norm(P.q, spin, D.rad);
+            frM = R.frMn[0] / gf_damp_sq_norm(P.qMn, spin, D.mrad);
+        } else {
+            fr = gf_damp_sq(P.q, spin, D.rad);
+            frM = gf_damp_sq(P.qMp, spin, D.mrad);
+        }
+    }
+    double A = R.mass2 - P.s;
+    double B = R.mass2 * R.width * gf_pow_odd(P.q / R.q0[0], spin) * fr / P.rs;
+    double C = 1.0 / (A * A + B * B);
+    double re = A * C, im = B * C;
+    double f = sqrt(fr);
+    re *= f; im *= f;
+    f = sqrt(frM);
+    re *= f; im *= f;
+    f = spin == 0 ? 1.0 : (spin == 1 ? P.z1 : P.z2);
+    re *= f; im *= f;
+    return make_double2(0.0 + re, 0.0 + im); // the reference accumulates into a zero-initialised result
+}
+#define GF_MAX_RES 64
+struct gf_amp3_shared {
+    gf_res_inv res[GF_MAX_RES];
+    gf_pair_need need[3];
+    int n_pair[3], n_other;
+    unsigned char by_pair[3][GF_MAX_RES]; // flagged plain RBWs grouped by resonant pair
+    unsigned char other[GF_MAX_RES];      // flagged GS / Gauss / NonRes / symmetrised RBW: evaluated unshared
+};
+// block-cooperative: fill S for the flagged resonances; call from all threads, then __syncthreads()
+__device__ inline void gf_amp3_prepare(gf_amp3_shared &S, const gf_sprog &P, const int32_t *res_nodes, int nres,
+                                       unsigned long long mask, const gf_decay3 &D) {
+    for(int i = threadIdx.x; i < nres; i += blockDim.x)
+        if((mask >> i) & 1ull) gf_res_prepare(S.res[i], P.nodes[res_nodes[i]], P.params, P.consts, D);
+    __syncthreads();
+    if(threadIdx.x < 3) {
+        gf_pair_need n = {0, 0, 0, 0};
+        const int c = threadIdx.x;
+        int cnt = 0;
+        for(int i = 0; i < nres; ++i) {
+            if(!((mask >> i) & 1ull)) continue;
+            const gf_res_inv &R = S.res[i];
+            if(R.op != GF_OP_RES_RBW || R.cyc != c) continue;
+            S.by_pair[c][cnt++] = (unsigned char)i;
+            n.used = 1;
+            if(R.norm) n.norm = 1; else n.plain = 1;
+            if(R.spin > n.maxspin) n.maxspin = R.spin;
+        }
+        S.need[c] = n;
+        S.n_pair[c] = cnt;
+    } else if(threadIdx.x == 3) {
+        int cnt = 0;
+        for(int i = 0; i < nres; ++i)
+            if(((mask >> i) & 1ull) && S.res[i].op != GF_OP_RES_RBW) S.other[cnt++] = (unsigned char)i;
+        S.n_other = cnt;
+    }
+}
+// every flagged resonance at one Dalitz point; out(i, value) receives each amplitude exactly once
+template <class Out>
+__device__ inline void gf_amp3_point(const gf_amp3_shared &S, const gf_sprog &P, const int32_t *res_nodes,
+                                     const gf_decay3 &D, bool inside, double m12, double m13, double m23, const Out &out) {
+#pragma unroll
+    for(int c = 0; c < 3; ++c) {
+        const int n = S.n_pair[c];
+        if(n == 0) continue;
+        gf_pair_inv Q;
+        if(inside) gf_pair_prepare(Q, S.need[c], c, D, m12, m13, m23);
+        for(int k = 0; k < n; ++k) {
+            const int i = S.by_pair[c][k];
+            out(i, inside ? gf_rbw_term(S.res[i], Q, D) : make_double2(0.0, 0.0));
+        }
+    }
+    for(int k = 0; k < S.n_other; ++k) {
+        const int i = S.other[k];
+        out(i, inside ? gf_resonance_cold(&P.nodes[res_nodes[i]], P.params, P.consts, &D, m12, m13, m23) : make_double2(0.0, 0.0));
+    }
+}
+

@@ -166,6 +166,9 @@ int gf_timer_stop(gf_ctx *, float *ms);
  * through a ring of pinned slots, so a caller can queue several evaluations back to back */
 int gf_set_params_async(gf_ctx *, const double *params, int n, const double *norms, int n_norms);
 
+/* measured FP64 FMA peak of this GPU (DFMA micro-benchmark, TFLOP/s, 2 flops per FMA): the roofline denominator of
+ * the FP64-bound cache kernels (k_amp3_waves, k_amp4_cache), which MEASURED_PEAKS.json does not carry */
+int gf_fp64_peak(gf_ctx *, double *tflops);
 /* timing of the last kernel launched by gf_eval_sum (CUDA events on the ctx stream), ms */
 float gf_last_kernel_ms(gf_ctx *);
 /* number of kernels this ctx has launched since creation */
