@@ -140,6 +140,7 @@ def main():
     ap.add_argument("--events", type=int, default=10_000_000, help="events per GPU")
     ap.add_argument("--ref-events", type=int, default=1_000_000, help="sample size of the CPU reference arm")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the DP4 / TDDP4 / cache-kernel / FP64-peak extras (N=1 only)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else max(args.warmup, 1)
 
@@ -305,6 +306,10 @@ def main():
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)"},
             "clocks": clocks, "nll": last,
         }
+        line["e2e"]["including_upload_and_first_call"] = total_events * K / (t_e2e + t_setdata + t_first)
+        if world == 1 and not args.no_secondary:
+            import bench_extra
+            line["workloads"] = bench_extra.run_all(gf, lib, ctx, M, N, peak)
         if not args.no_cpu_baseline:
             try:
                 r = run_reference("dalitz", args.ref_events, 5, 1)

@@ -1,0 +1,165 @@
+"""bench_extra.py — secondary measurements bench.py attaches to its JSON line at N=1 (key "workloads"):
+
+  fp64_peak    DFMA micro-benchmark (gf_fp64_peak): the measured denominator of the FP64-bound kernels
+  dalitz_cache k_amp3_waves over all 16 resonances (what reruns when masses/widths float), CUDA-event timed
+  dp4          BASELINE configs[3]: Amp4Body D0->K-pi+pi+pi-, steady-state FCN calls (MC integral + NLL kernel)
+  tddp4        BASELINE configs[4] shape at one GPU: Amp4Body_TD with TruthResolution
+
+Nothing here touches oracle/. Every number is taken through the host API or the C ABI on the ctx stream.
+"""
+import ctypes as C
+import json
+import os
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+
+
+def _profile_counts():
+    """per-launch FP64 instruction counts taken once with ncu (profiles/traffic.json), or {}"""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f)
+    except Exception:
+        return {}
+
+
+def fp64_peak(lib, ctx):
+    v = C.c_double(0)
+    if lib.gf_fp64_peak(ctx, C.byref(v)) != 0:
+        return None
+    return v.value
+
+
+def timed(lib, ctx, fn, reps):
+    ms = C.c_float(0)
+    lib.gf_sync(ctx)
+    assert lib.gf_timer_start(ctx) == 0
+    for _ in range(reps):
+        fn()
+    assert lib.gf_timer_stop(ctx, C.byref(ms)) == 0
+    return float(ms.value) / reps
+
+
+def dalitz_cache(gf, lib, ctx, M, n_events, peak_tf):
+    """all 16 waves recomputed: the per-call cost when every mass/width floats"""
+    node = M.signal.getFunctionIndex()
+    nres = 16
+    mask = (C.c_uint8 * nres)(*([1] * nres))
+
+    def run():
+        assert lib.gf_amp3_cache_waves(ctx, C.c_int(node), mask) == 0
+
+    run()
+    ms = timed(lib, ctx, run, 5)
+    out = {"kernel": "k_amp3_waves", "kernel_ms": ms, "resonance_evals_per_s": nres * n_events / (ms * 1e-3),
+           "hbm_write_gbs": 16.0 * nres * n_events / (ms * 1e-3) / 1e9}
+    flops = _profile_counts().get("k_amp3_waves_fp64_flops_per_launch")
+    if flops and peak_tf:
+        ach = flops / (ms * 1e-3) / 1e12
+        out["roofline"] = {"bound": "fp64", "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach / peak_tf,
+                           "flops_per_launch": flops, "flops_source": "ncu sass dfma*2+dmul+dadd (profiles/)",
+                           "peak_source": "gf_fp64_peak DFMA micro-benchmark, this run"}
+    return out
+
+
+def _tile(cols, n):
+    reps = (n + cols.shape[1] - 1) // cols.shape[1]
+    return np.ascontiguousarray(np.tile(cols, (1, reps))[:, :n])
+
+
+def four_body(gf, lib, ctx, kind, n_data, n_mc, steps, peak_hbm):
+    """steady-state likelihood calls of the 4-body fits: coefficients (DP4) or tau/x/y (TDDP4) move, lineshapes fixed.
+    Per call: MC-integral kernel over n_mc cached-amplitude rows + fused NLL kernel over n_data rows."""
+    from models import DP4, TDDP4
+    unique = 2_000_000
+    masses = [1.8645, 0.13957018, 0.13957018, 0.493677, 0.13957018]
+    t0 = time.perf_counter()
+    ph, _ = gf.generatePhaseSpace5(masses, unique, 4242)
+    t_gen = time.perf_counter() - t0
+    rng = np.random.default_rng(99)
+    if kind == "dp4":
+        M = DP4(mc_events=0, float_ls=False)
+        namp, bytes_evt = 8, 8 * 16 + 8
+        d = M.dataset(list(_tile(ph, n_data)))
+        movers = M.coefs[:6]
+    else:
+        M = TDDP4(three_gauss=False, float_ls=False, float_mix=True)
+        namp, bytes_evt = 6, 6 * 16 + 8 + 16
+        cols = list(_tile(ph, n_data))
+        cols.append(rng.exponential(0.4101, n_data).clip(0, 9.99))
+        cols.append(rng.uniform(0.02, 0.08, n_data))
+        d = M.dataset(cols)
+        movers = M.mix
+    M.dp.setNormEvents(_tile(ph[:, ::-1].copy(), n_mc))
+    sig, dp = M.signal, M.dp
+    t0 = time.perf_counter()
+    sig.setData(d)
+    dp.setDataSize(len(d), 6 if kind == "dp4" else 8)
+    t_setdata = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    sig.calculateNLL()
+    t_first = time.perf_counter() - t0
+    fm = gf.FitManager(sig)
+    fcn, params = fm.getFCN(), fm.getParams()
+    v0 = np.array(params.make_minuit_vector())
+    idx = [c.fitter_index for c in movers]
+
+    def vec(k):
+        v = v0.copy()
+        for j, i in enumerate(idx):
+            v[i] = v0[i] * (1.0 + 1e-3 * ((k + j) % 3 - 1))
+        return list(v)
+
+    for k in range(3):
+        fcn(vec(k))
+    lib.gf_sync(ctx)
+    l0 = gf.launch_count()
+    t0 = time.perf_counter()
+    for k in range(steps):
+        last = fcn(vec(3 + k))
+    lib.gf_sync(ctx)
+    t_e2e = (time.perf_counter() - t0) / steps
+    launches = (gf.launch_count() - l0) / steps
+    # the two streaming kernels alone, queued back to back on the ctx stream (CUDA events)
+    node, root = dp.getFunctionIndex(), sig.getFunctionIndex()
+
+    def pair():
+        assert lib.gf_amp4_norm_async(ctx, C.c_int(node)) == 0
+        assert lib.gf_eval_sum_async(ctx, C.c_int(root), C.c_int(1)) == 0
+
+    pair()
+    ms = timed(lib, ctx, pair, 10)
+    ms_norm = timed(lib, ctx, lambda: lib.gf_amp4_norm_async(ctx, C.c_int(node)), 10)
+    ms_eval = timed(lib, ctx, lambda: lib.gf_eval_sum_async(ctx, C.c_int(root), C.c_int(1)), 10)
+    bytes_step = namp * 16 * n_mc + bytes_evt * n_data
+    ach = bytes_step / (ms * 1e-3) / 1e9
+    return {"workload": "examples/DP4: Amp4Body, 8 amplitudes" if kind == "dp4" else "examples/TDDP4: Amp4Body_TD, 6 amplitudes, TruthResolution",
+            "data_events": n_data, "mc_norm_events": n_mc, "unique_generated": unique,
+            "value": n_data / (ms * 1e-3), "unit": "events*evals/s", "ms_per_step": ms,
+            "e2e": {"value": n_data / t_e2e, "ms_per_step": 1e3 * t_e2e, "launches_per_step": launches,
+                    "setdata_s": t_setdata, "first_call_s": t_first, "phase_space_gen_s": t_gen},
+            "roofline": {"bound": "hbm", "achieved": ach, "peak": peak_hbm, "unit": "GB/s", "frac": ach / peak_hbm,
+                         "kernel": "k_amp4_norm%s + k_eval_sum" % ("" if kind == "dp4" else "_td"),
+                         "algorithmic_bytes_per_step": bytes_step,
+                         "norm_kernel_ms": ms_norm, "norm_gbs": namp * 16 * n_mc / (ms_norm * 1e-3) / 1e9,
+                         "eval_kernel_ms": ms_eval, "eval_gbs": bytes_evt * n_data / (ms_eval * 1e-3) / 1e9},
+            "nll": last}
+
+
+def run_all(gf, lib, ctx, M_dalitz, n_events, peak_hbm, steps=20):
+    out = {}
+    peak_tf = fp64_peak(lib, ctx)
+    out["fp64_peak_tflops_measured"] = peak_tf
+    try:
+        out["dalitz_cache"] = dalitz_cache(gf, lib, ctx, M_dalitz, n_events, peak_tf)
+    except Exception as e:  # secondary numbers never break the headline line
+        out["dalitz_cache"] = {"error": str(e)[:200]}
+    for kind in ("dp4", "tddp4"):
+        try:
+            out[kind] = four_body(gf, lib, ctx, kind, 10_000_000, 10_000_000, steps, peak_hbm)
+        except Exception as e:
+            out[kind] = {"error": str(e)[:200]}
+    return out

@@ -11,6 +11,7 @@
 // SoA layout: ls[i*ld + e] (complex), sf[k*ld + e] (real), amps[a*ld + e] (complex).
 #include "gf_internal.cuh"
 #include "gf_amp4.cuh"
+#define GF_GRAM_T 4 // amplitudes per Gram tile side: 16 complex accumulators per thread
 
 struct gf_amp4_set { // one event sample (data or MC) with its caches
     long n = 0, ld = 0;
@@ -24,6 +25,10 @@ struct gf_amp4_set { // one event sample (data or MC) with its caches
 struct gf_amp4_state {
     int node = -1, slot = -1, nLS = 0, nSF = 0, nAmp = 0, td = 0;
     gf_amp4_set data, mc;
+    // Gram matrix of the MC amplitudes, tile by tile: [tile][GF_GRAM_T * GF_GRAM_T][re, im]
+    double *d_gram = nullptr, *d_gram_partials = nullptr, *h_gram = nullptr;
+    unsigned *d_gram_ticket = nullptr;
+    int gram_blocks = 0;
 };
 
 static void free_set(gf_amp4_set &s) {
@@ -34,6 +39,8 @@ void gf_amp4_free(gf_ctx *c) {
     for(auto *s : c->amp4) {
         free_set(s->data);
         free_set(s->mc);
+        cudaFree(s->d_gram); cudaFree(s->d_gram_partials); cudaFree(s->d_gram_ticket);
+        if(s->h_gram) cudaFreeHost(s->h_gram);
         delete s;
     }
     c->amp4.clear();
@@ -212,6 +219,41 @@ __global__ void __launch_bounds__(GF_THREADS, 4)
         acc[3] += w * (Aim * Bre - Are * Bim);
     }
     gf_grid_finish(acc, 4, partials, ticket, out, red);
+}
+
+// G_ab = sum_m w_m A_a(m) conj(A_b(m)) for one GF_GRAM_T x GF_GRAM_T tile (rows a0.., columns b0..) of the Hermitian
+// Gram matrix of the cached MC amplitudes. With G, the normalisation integral of any coefficient set is an
+// O(nAmp^2) host sum, sum_ab c_a conj(c_b) G_ab, so the per-call pass over the MC sample (detail/NormIntegrator.cu:15-68,
+// NormIntegrator_TD.cu:15-99) is only needed when a lineshape moved. This is the "complex amplitude Gram sum" of the
+// north star; plain FP64 FMAs keep it at the HBM roofline (arithmetic intensity 2 x 16 cmul per 128 B), so DMMA would
+// add nothing.
+__global__ void __launch_bounds__(GF_THREADS, 2)
+    k_amp4_gram(const double2 *amps, long ld, long n, const double *weights, int nAmp, int a0, int b0, double *partials,
+                unsigned *ticket, double *out) {
+    __shared__ double red[32];
+    double acc[2 * GF_GRAM_T * GF_GRAM_T];
+#pragma unroll
+    for(int k = 0; k < 2 * GF_GRAM_T * GF_GRAM_T; ++k) acc[k] = 0;
+    const long stride = (long)gridDim.x * blockDim.x;
+    for(long m = (long)blockIdx.x * blockDim.x + threadIdx.x; m < n; m += stride) {
+        double2 A[GF_GRAM_T], B[GF_GRAM_T];
+#pragma unroll
+        for(int i = 0; i < GF_GRAM_T; ++i) {
+            A[i] = a0 + i < nAmp ? __ldg(amps + (size_t)(a0 + i) * ld + m) : make_double2(0.0, 0.0);
+            B[i] = b0 + i < nAmp ? __ldg(amps + (size_t)(b0 + i) * ld + m) : make_double2(0.0, 0.0);
+        }
+        const double w = weights ? __ldg(weights + m) : 1.0;
+#pragma unroll
+        for(int i = 0; i < GF_GRAM_T; ++i) {
+            const double ax = w * A[i].x, ay = w * A[i].y;
+#pragma unroll
+            for(int j = 0; j < GF_GRAM_T; ++j) { // A_i conj(B_j)
+                acc[2 * (i * GF_GRAM_T + j)] += ax * B[j].x + ay * B[j].y;
+                acc[2 * (i * GF_GRAM_T + j) + 1] += ay * B[j].x - ax * B[j].y;
+            }
+        }
+    }
+    gf_grid_finish(acc, 2 * GF_GRAM_T * GF_GRAM_T, partials, ticket, out, red);
 }
 
 // ---- C ABI ---------------------------------------------------------------------------------------------------
@@ -406,6 +448,61 @@ extern "C" int gf_amp4_norm(gf_ctx *c, int node, double *out) {
     GF_CUDA(cudaMemcpyAsync(c->h_result + 1, c->d_result + 1, sizeof(double) * n, cudaMemcpyDeviceToHost, c->stream));
     GF_CUDA(cudaStreamSynchronize(c->stream));
     for(int k = 0; k < n; k++) out[k] = c->h_result[1 + k];
+    return 0;
+}
+
+// Hermitian Gram matrix of the (local shard of the) cached MC amplitudes, all-reduced when a communicator is attached.
+// G_re_im[(a * nAmp + b) * 2 + {0,1}] = sum_m w_m A_a(m) conj(A_b(m)). The caller recomputes it after gf_amp4_cache
+// touched the MC amplitudes; between such calls the integral needs no device work at all.
+extern "C" int gf_amp4_gram(gf_ctx *c, int node, double *G_re_im) {
+    gf_amp4_state *s;
+    if(amp4_check(c, node, &s, false)) return 1;
+    if(!s->mc.amps) return gf_fail("gf_amp4_gram: no MC normalisation sample (gf_amp4_set_mc)");
+    if(!G_re_im) return gf_fail("gf_amp4_gram: null output");
+    cudaSetDevice(c->device);
+    const int T = GF_GRAM_T, nT = (s->nAmp + T - 1) / T, nTiles = nT * (nT + 1) / 2, per = 2 * T * T;
+    const int blocks = gf_grid_blocks(c, s->mc.n, 2);
+    if(!s->d_gram || s->gram_blocks < blocks) {
+        cudaFree(s->d_gram); cudaFree(s->d_gram_partials); cudaFree(s->d_gram_ticket);
+        if(s->h_gram) cudaFreeHost(s->h_gram);
+        s->d_gram = s->d_gram_partials = s->h_gram = nullptr;
+        s->d_gram_ticket = nullptr;
+        const int maxTiles = (64 / T) * (64 / T + 1) / 2;
+        GF_CUDA(cudaMalloc(&s->d_gram, sizeof(double) * per * maxTiles));
+        GF_CUDA(cudaMalloc(&s->d_gram_partials, sizeof(double) * per * (size_t)blocks));
+        GF_CUDA(cudaMalloc(&s->d_gram_ticket, sizeof(unsigned)));
+        GF_CUDA(cudaMemsetAsync(s->d_gram_ticket, 0, sizeof(unsigned), c->stream));
+        GF_CUDA(cudaMallocHost(&s->h_gram, sizeof(double) * per * maxTiles));
+        s->gram_blocks = blocks;
+    }
+    int t = 0;
+    for(int ta = 0; ta < nT; ta++)
+        for(int tb = ta; tb < nT; tb++, t++) {
+            k_amp4_gram<<<blocks, GF_THREADS, 0, c->stream>>>(s->mc.amps, s->mc.ld, s->mc.n, s->mc.weights, s->nAmp, ta * T, tb * T,
+                                                             s->d_gram_partials, s->d_gram_ticket, s->d_gram + (size_t)t * per);
+            c->launches++;
+        }
+    GF_CUDA(cudaGetLastError());
+    if(c->nccl_comm && gf_allreduce_sum(c, s->d_gram, per * nTiles)) return 1;
+    GF_CUDA(cudaMemcpyAsync(s->h_gram, s->d_gram, sizeof(double) * per * nTiles, cudaMemcpyDeviceToHost, c->stream));
+    GF_CUDA(cudaStreamSynchronize(c->stream));
+    t = 0;
+    const int n = s->nAmp;
+    for(int ta = 0; ta < nT; ta++)
+        for(int tb = ta; tb < nT; tb++, t++)
+            for(int i = 0; i < T; i++)
+                for(int j = 0; j < T; j++) {
+                    int a = ta * T + i, b = tb * T + j;
+                    if(a >= n || b >= n) continue;
+                    double re = s->h_gram[(size_t)t * per + 2 * (i * T + j)], im = s->h_gram[(size_t)t * per + 2 * (i * T + j) + 1];
+                    if(ta == tb && b < a) continue; // lower triangle of a diagonal tile: taken from its mirror
+                    G_re_im[2 * (a * n + b)] = re;
+                    G_re_im[2 * (a * n + b) + 1] = a == b ? 0.0 : im;
+                    if(a != b) {
+                        G_re_im[2 * (b * n + a)] = re;
+                        G_re_im[2 * (b * n + a) + 1] = -im;
+                    }
+                }
     return 0;
 }
 

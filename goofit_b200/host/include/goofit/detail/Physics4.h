@@ -117,6 +117,12 @@ class Amp4BodyBase : public GooPdf {
   public:
     using GooPdf::GooPdf;
     void setForceIntegrals(bool f = true) { forceRedoIntegrals = f; }
+    /// How the MC normalisation integral is summed. Gram (default): G_ab = sum_m A_a conj(A_b) is rebuilt only when a
+    /// lineshape moved and every call sums c_a conj(c_b) G_ab on the host. PerEvent: the reference's association,
+    /// sum_m |sum_a c_a A_a(m)|^2 over the cached MC amplitudes on every call (detail/NormIntegrator.cu:15-68).
+    enum class NormMode { Gram, PerEvent };
+    void setNormMode(NormMode m) { normMode = m; gramValid = false; }
+    NormMode getNormMode() const { return normMode; }
     /// replace the normalisation sample: five columns (m12, m34, cos12, cos34, phi) of equal length
     void setNormEvents(const std::vector<std::vector<fptype>> &cols5);
     const std::vector<std::vector<fptype>> &getNormEvents() const { return normCols; }
@@ -133,6 +139,11 @@ class Amp4BodyBase : public GooPdf {
     std::vector<int32_t> headerInts(detail::ProgramBuilder &B, int tdOffset) const;
     void ensureCache();
     void setDataSizeCommon(unsigned int dataSize, unsigned int evtSize);
+    /// (re)build the Gram matrix if the MC amplitudes changed; returns G[a * nAmps + b]
+    const std::vector<std::complex<fptype>> &gram(bool mcAmpsChanged);
+    NormMode normMode{NormMode::Gram};
+    bool gramValid{false};
+    std::vector<std::complex<fptype>> G;
     GooPdf *efficiency{nullptr};
     std::vector<SpinFactor *> SpinFactors;
     std::vector<Lineshape *> LineShapes;

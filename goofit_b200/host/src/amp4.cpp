@@ -293,6 +293,16 @@ void Amp4BodyBase::ensureCache() {
     Engine::check(gf_amp4_set_mc(E.ctx(), nodeIdx, cols, count, nullptr, nullptr, nullptr), "gf_amp4_set_mc");
     cacheAllocated     = true;
     forceRedoIntegrals = true;
+    gramValid          = false;
+}
+const std::vector<std::complex<fptype>> &Amp4BodyBase::gram(bool mcAmpsChanged) {
+    if(mcAmpsChanged || !gramValid || G.size() != nAmps * nAmps) {
+        G.assign(nAmps * nAmps, {0.0, 0.0});
+        Engine &E = Engine::get();
+        Engine::check(gf_amp4_gram(E.ctx(), nodeIdx, reinterpret_cast<double *>(G.data())), "gf_amp4_gram");
+        gramValid = true;
+    }
+    return G;
 }
 std::vector<std::complex<fptype>> Amp4BodyBase::getCachedAmp(size_t a) const {
     if(!cacheAllocated) throw GeneralError("{}: no cached amplitudes yet", getName());
@@ -364,7 +374,20 @@ fptype Amp4Body::normalize() { // Amp4Body.cu:398-558
     E.sync();
     if(any) Engine::check(gf_amp4_cache(E.ctx(), nodeIdx, spins, lsRedo.data(), ampRedo.data()), "gf_amp4_cache");
     double sum = 0;
-    Engine::check(gf_amp4_norm(E.ctx(), nodeIdx, &sum), "gf_amp4_norm");
+    if(normMode == NormMode::Gram) {
+        // sum_m |sum_a c_a A_a(m)|^2 = sum_a |c_a|^2 G_aa + 2 sum_{a<b} Re(c_a conj(c_b) G_ab), with the coefficients of the
+        // parameter block the device would have read
+        const auto &g = gram(any);
+        for(size_t a = 0; a < nAmp; ++a) {
+            std::complex<fptype> ca(par(2 * a), par(2 * a + 1));
+            sum += std::norm(ca) * g[a * nAmp + a].real();
+            for(size_t b = a + 1; b < nAmp; ++b) {
+                std::complex<fptype> cb(par(2 * b), par(2 * b + 1));
+                sum += 2 * (ca * std::conj(cb) * g[a * nAmp + b]).real();
+            }
+        }
+    } else
+        Engine::check(gf_amp4_norm(E.ctx(), nodeIdx, &sum), "gf_amp4_norm");
     fptype ret = sum / static_cast<fptype>(MCevents);
     if(std::isnan(ret)) GooFit::abort(__FILE__, __LINE__, getName() + " NAN normalization in Amp4Body", this);
     setNormalization(1.0 / ret);
@@ -527,7 +550,36 @@ fptype Amp4Body_TD::normalize() { // Amp4Body_TD.cu:744-799
     E.sync();
     if(any) Engine::check(gf_amp4_cache(E.ctx(), nodeIdx, spins, lsRedo.data(), ampRedo.data()), "gf_amp4_cache");
     double sums[4] = {0, 0, 0, 0};
-    Engine::check(gf_amp4_norm(E.ctx(), nodeIdx, sums), "gf_amp4_norm");
+    if(normMode == NormMode::Gram) {
+        // effective coefficient vectors of A (scaled by sqrt(WS/RS)) and B with the reference's coefficient walk
+        // (NormIntegrator_TD.cu:69-92); then |A|^2, |B|^2 and A conj(B) are bilinear forms in G
+        std::vector<std::complex<fptype>> cA(nAmps, {0.0, 0.0}), cB(nAmps, {0.0, 0.0});
+        const fptype sq = par(3);
+        int k = 0;
+        for(size_t a = 0; a < nAmps; ++a) {
+            std::complex<fptype> c(par(4 + 2 * (a + k)), par(5 + 2 * (a + k)));
+            if(flags[a] == 1)
+                cB[a] = c;
+            else {
+                cA[a] = c * sq;
+                if(flags[a] == 2) {
+                    ++k;
+                    cB[a] = {par(4 + 2 * (a + k)), par(5 + 2 * (a + k))};
+                }
+            }
+        }
+        const auto &g = gram(any);
+        std::complex<fptype> AA(0, 0), BB(0, 0), AB(0, 0);
+        for(size_t a = 0; a < nAmps; ++a)
+            for(size_t b = 0; b < nAmps; ++b) {
+                const std::complex<fptype> gab = g[a * nAmps + b];
+                AA += cA[a] * std::conj(cA[b]) * gab;
+                BB += cB[a] * std::conj(cB[b]) * gab;
+                AB += cA[a] * std::conj(cB[b]) * gab;
+            }
+        sums[0] = AA.real(); sums[1] = BB.real(); sums[2] = AB.real(); sums[3] = AB.imag();
+    } else
+        Engine::check(gf_amp4_norm(E.ctx(), nodeIdx, sums), "gf_amp4_norm");
     // the reference reads tau, x, y from the Variables here (parametersList[0..2], Amp4Body_TD.cu:770-772), while the
     // device sums above used the parameter block last pushed by updateParameters()
     fptype tau = parametersList[0].getValue(), x = parametersList[1].getValue(), y = parametersList[2].getValue();

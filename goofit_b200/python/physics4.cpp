@@ -67,7 +67,10 @@ void init_physics4(py::module &m) {
         .def_readwrite("amplitudes_B", &DecayInfo4::amplitudes_B)
         .def("add_amplitude", [](DecayInfo4 &d, Amplitude *a) { d.amplitudes.push_back(a); }, py::keep_alive<1, 2>())
         .def("add_amplitude_B", [](DecayInfo4 &d, Amplitude *a) { d.amplitudes_B.push_back(a); }, py::keep_alive<1, 2>());
-    py::class_<Amp4BodyBase, GooPdf>(m, "Amp4BodyBase")
+    py::class_<Amp4BodyBase, GooPdf> a4b(m, "Amp4BodyBase");
+    py::enum_<Amp4BodyBase::NormMode>(a4b, "NormMode").value("Gram", Amp4BodyBase::NormMode::Gram).value("PerEvent", Amp4BodyBase::NormMode::PerEvent);
+    a4b.def("setNormMode", &Amp4BodyBase::setNormMode, "mode"_a)
+        .def("getNormMode", &Amp4BodyBase::getNormMode)
         .def("setForceIntegrals", &Amp4BodyBase::setForceIntegrals, "f"_a = true)
         .def("numLineshapes", &Amp4BodyBase::numLineshapes)
         .def("numSpinFactors", &Amp4BodyBase::numSpinFactors)

@@ -149,6 +149,11 @@ int gf_amp4_cache(gf_ctx *, int node, int redo_spins, const uint8_t *ls_redo, co
  * Amp4Body_TD: out[0..3] = sum |A|^2, sum |B|^2, sum Re(A B*), sum Im(A B*) (detail/NormIntegrator_TD.cu:15-99). */
 int gf_amp4_norm(gf_ctx *, int node, double *out);
 int gf_amp4_norm_async(gf_ctx *, int node);
+/* Hermitian Gram matrix of the cached MC amplitudes, G[(a*nAmp+b)*2+{re,im}] = sum_m w_m A_a(m) conj(A_b(m)), summed over
+ * ranks when a communicator is attached. With it the integral of gf_amp4_norm is the host sum  sum_ab c_a conj(c_b) G_ab
+ * (Amp4Body) or the four sums over the A / B coefficient sets (Amp4Body_TD): no per-call pass over the MC sample while
+ * the lineshapes stand still. Call it after gf_amp4_cache rebuilt MC amplitudes. */
+int gf_amp4_gram(gf_ctx *, int node, double *G_re_im /* nAmp*nAmp*2 */);
 int gf_amp4_get_amp(gf_ctx *, int node, int amp, double *out_re_im, size_t n_events);
 
 /* ---- multi-GPU: one process per GPU, partial sums all-reduced in-stream over NCCL (NVLink/NVSwitch) --------

@@ -265,9 +265,13 @@ def test_run_to_run_bit_reproducible():
     assert vals[0] == vals[1] == vals[2]
 
 
-def test_dp4_values(golden):
+@pytest.mark.parametrize("mode", ["Gram", "PerEvent"])
+def test_dp4_values(golden, mode):
+    """mode = how the MC integral is summed: Gram (default; G_ab rebuilt only when a lineshape moved, O(nAmp^2) host sum
+    per call) or PerEvent (the reference's association, one pass over the cached MC amplitudes per call)"""
     from models import DP4
     M = DP4(mc_events=0, float_ls=True)
+    M.dp.setNormMode(getattr(gf.Amp4BodyBase.NormMode, mode))
     cols = [golden.arr("dp4." + n) for n in ("m12", "m34", "cos12", "cos34", "phi")]
     mc = np.vstack([golden.arr("dp4.mc_" + n) for n in ("m12", "m34", "cos12", "cos34", "phi")])
     assert mc.shape[1] == int(golden["dp4.mc_events"])
@@ -299,8 +303,8 @@ def test_dp4_values(golden):
     before = gf.launch_count()
     assert rel(sig.calculateNLL(), golden["dp4.nll_coef_moved"]) < RTOL_NLL
     assert rel(1.0 / dp.getNormalization(), golden["dp4.integral_coef_moved"]) < 1e-12
-    # steady state: backgr grid integral + MC integral + NLL kernel
-    assert gf.launch_count() - before == 3
+    # steady state: backgr grid integral + NLL kernel (+ the per-event MC integral kernel in PerEvent mode)
+    assert gf.launch_count() - before == (2 if mode == "Gram" else 3)
     M.lsvars[2].changed = True
     sig.updateVariable(M.lsvars[2], 0.8975)
     sig.updateParameters()
@@ -332,12 +336,14 @@ TD_DATA = ("m12", "m34", "cos12", "cos34", "phi", "dtime", "sigmat")
 TD_MC = ("m12", "m34", "cos12", "cos34", "phi")
 
 
+@pytest.mark.parametrize("mode", ["Gram", "PerEvent"])
 @pytest.mark.parametrize("tag,three_gauss,shared", [("tddp4", False, False), ("tddp4g3", True, False), ("tddp4sh", False, True)])
-def test_tddp4_values(golden, tag, three_gauss, shared):
+def test_tddp4_values(golden, tag, three_gauss, shared, mode):
     """Amp4Body_TD (Amp4Body_TD.cu:167-261,744-799) with TruthResolution / ThreeGaussResolution, and with one amplitude
     object shared by the A and B lists (flag 2). All three cases run on the same data and MC sample."""
     from models import TDDP4
     M = TDDP4(three_gauss=three_gauss, float_ls=True, float_mix=True, shared=shared)
+    M.dp.setNormMode(getattr(gf.Amp4BodyBase.NormMode, mode))
     mc = np.vstack([golden.arr("tddp4.mc_" + n) for n in TD_MC])
     assert mc.shape[1] == int(golden["tddp4.mc_events"])
     M.dp.setNormEvents(mc)
@@ -379,8 +385,8 @@ def test_tddp4_values(golden, tag, three_gauss, shared):
     before = gf.launch_count()
     assert rel(sig.calculateNLL(), golden[tag + ".nll_mix_moved"]) < RTOL_NLL
     assert rel(1.0 / dp.getNormalization(), golden[tag + ".integral_mix_moved"]) < RTOL_INT
-    # steady state: backgr grid integral + MC integral (4 sums) + NLL kernel
-    assert gf.launch_count() - before == 3
+    # steady state: backgr grid integral + NLL kernel (+ the four-sum MC integral kernel in PerEvent mode)
+    assert gf.launch_count() - before == (2 if mode == "Gram" else 3)
     M.lsvars[2].changed = True
     sig.updateVariable(M.lsvars[2], 0.8975)
     sig.updateParameters()

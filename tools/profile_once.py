@@ -1,0 +1,48 @@
+"""tools/profile_once.py — launches every hot kernel a small, fixed number of times at BASELINE sizes so that one
+`ncu --set full -k regex:"k_amp|k_eval_sum"` capture holds all of them (Dalitz: k_amp3_waves/grid/gram + k_eval_sum;
+DP4 and TDDP4: k_amp4_sf, k_amp4_cache, k_amp4_amps, k_amp4_norm[_td], k_eval_sum). Not a benchmark."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import goofit_b200 as gf  # noqa: E402
+from models import DP4, TDDP4, Dalitz, dalitz_uniform_events  # noqa: E402
+
+N = int(sys.argv[1]) if len(sys.argv) > 1 else 10_000_000
+which = sys.argv[2] if len(sys.argv) > 2 else "dalitz,dp4,tddp4"
+if "dalitz" in which:
+    M = Dalitz(float_masses=False, grid=240)
+    m12, m13 = dalitz_uniform_events(N, 12345)
+    d = M.dataset(m12, m13)
+    M.signal.setData(d)
+    M.signal.setDataSize(len(d))
+    print("dalitz", M.signal.calculateNLL(), M.signal.calculateNLL())
+masses = [1.8645, 0.13957018, 0.13957018, 0.493677, 0.13957018]
+ph, _ = gf.generatePhaseSpace5(masses, min(N, 2_000_000), 4242)
+reps = (N + ph.shape[1] - 1) // ph.shape[1]
+cols = np.ascontiguousarray(np.tile(ph, (1, reps))[:, :N])
+mc = np.ascontiguousarray(np.tile(ph[:, ::-1], (1, reps))[:, :N])
+rng = np.random.default_rng(99)
+for kind in ("dp4", "tddp4"):
+    if kind not in which.split(","):
+        continue
+    if kind == "dp4":
+        M = DP4(mc_events=0, float_ls=True)
+        d = M.dataset(list(cols))
+    else:
+        M = TDDP4(three_gauss=(len(sys.argv) > 3 and sys.argv[3] == "g3"), float_ls=True, float_mix=True)
+        d = M.dataset(list(cols) + [rng.exponential(0.4101, N).clip(0, 9.99), rng.uniform(0.02, 0.08, N)])
+    M.dp.setNormEvents(mc)
+    M.signal.setData(d)
+    M.dp.setDataSize(len(d), 6 if kind == "dp4" else 8)
+    print(kind, M.signal.calculateNLL())
+    # the K*(892) mass moves: only its lineshapes and the amplitudes using them are redone
+    M.lsvars[2].changed = True
+    M.signal.updateVariable(M.lsvars[2], 0.8975)
+    M.signal.updateParameters()
+    print(kind, M.signal.calculateNLL())
+print("launches", gf.launch_count())
