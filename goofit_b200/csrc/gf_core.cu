@@ -179,7 +179,8 @@ extern "C" gf_ctx *gf_create(int device_id) {
     cudaMemset(c->d_ticket, 0, sizeof(unsigned) * 8);
     cudaMalloc(&c->d_result, sizeof(double) * GF_NPARTIAL * 64);
     cudaMemset(c->d_result, 0, sizeof(double) * GF_NPARTIAL * 64);
-    cudaMallocHost(&c->h_result, sizeof(double) * GF_NPARTIAL * 64);
+    cudaHostAlloc(&c->h_result, sizeof(double) * GF_NPARTIAL * 64, cudaHostAllocMapped);
+    if(cudaHostGetDevicePointer((void **)&c->h_result_dev, c->h_result, 0) != cudaSuccess) c->h_result_dev = nullptr;
     if(cudaGetLastError() != cudaSuccess) {
         gf_fail("gf_create: allocation failed");
         delete c;
@@ -207,7 +208,7 @@ extern "C" void gf_destroy(gf_ctx *c) {
     gf_amp4_free(c);
     gf_conv_free(c);
     free_cols(c);
-    cudaFree(c->d_nodes); cudaFree(c->d_params); cudaFree(c->d_consts); cudaFree(c->d_norms); cudaFree(c->d_ints);
+    cudaFree(c->d_nodes); cudaFree(c->d_params); cudaFree(c->d_consts); cudaFree(c->d_ints); // d_norms lives inside d_params' block
     cudaFree(c->d_partials); cudaFree(c->d_ticket); cudaFree(c->d_result); cudaFree(c->d_events_out);
     cudaFreeHost(c->h_result);
     if(c->nccl_comm && p_destroy) p_destroy(c->nccl_comm);
@@ -256,16 +257,17 @@ extern "C" int gf_set_program(gf_ctx *c, const gf_node *nodes, int n_nodes, cons
     c->n_norms = n_norms;
     if(gf_prog_smem(c) > 160 * 1024) return gf_fail("gf_set_program: program block exceeds shared memory");
     cudaStreamSynchronize(c->stream);
-    cudaFree(c->d_nodes); cudaFree(c->d_params); cudaFree(c->d_consts); cudaFree(c->d_norms); cudaFree(c->d_ints);
+    cudaFree(c->d_nodes); cudaFree(c->d_params); cudaFree(c->d_consts); cudaFree(c->d_ints); // d_norms lives inside d_params' block
     GF_CUDA(cudaMalloc(&c->d_nodes, sizeof(gf_node) * n_nodes));
-    GF_CUDA(cudaMalloc(&c->d_params, sizeof(double) * std::max(1, n_params)));
+    // parameters and normalisations share one allocation so that one copy per likelihood call uploads both
+    GF_CUDA(cudaMalloc(&c->d_params, sizeof(double) * (size_t)(n_params + n_norms)));
+    c->d_norms = c->d_params + n_params;
     GF_CUDA(cudaMalloc(&c->d_consts, sizeof(double) * std::max(1, n_consts)));
-    GF_CUDA(cudaMalloc(&c->d_norms, sizeof(double) * n_norms));
     GF_CUDA(cudaMalloc(&c->d_ints, sizeof(int32_t) * std::max(1, n_ints)));
     GF_CUDA(cudaMemcpy(c->d_nodes, nodes, sizeof(gf_node) * n_nodes, cudaMemcpyHostToDevice));
     if(n_consts) GF_CUDA(cudaMemcpy(c->d_consts, consts, sizeof(double) * n_consts, cudaMemcpyHostToDevice));
     if(n_ints) GF_CUDA(cudaMemcpy(c->d_ints, ints, sizeof(int32_t) * n_ints, cudaMemcpyHostToDevice));
-    GF_CUDA(cudaMemset(c->d_params, 0, sizeof(double) * std::max(1, n_params)));
+    if(n_params) GF_CUDA(cudaMemset(c->d_params, 0, sizeof(double) * n_params));
     {
         std::vector<double> ones(n_norms, 1.0);
         GF_CUDA(cudaMemcpy(c->d_norms, ones.data(), sizeof(double) * n_norms, cudaMemcpyHostToDevice));
@@ -398,14 +400,14 @@ extern "C" int gf_set_params_async(gf_ctx *c, const double *params, int n, const
     int k = c->ring_pos;
     c->ring_pos = (k + 1) % gf_ctx::RING;
     cudaEventSynchronize(c->ring_ev[k]); // slot free again? (returns at once for a never-recorded event)
-    if(n) {
-        std::memcpy(c->ring_buf[k], params, sizeof(double) * n);
+    if(n) std::memcpy(c->ring_buf[k], params, sizeof(double) * n);
+    if(norms) std::memcpy(c->ring_buf[k] + n, norms, sizeof(double) * n_norms);
+    if(n && norms) // one copy: d_norms directly follows d_params
+        GF_CUDA(cudaMemcpyAsync(c->d_params, c->ring_buf[k], sizeof(double) * (n + n_norms), cudaMemcpyHostToDevice, c->stream));
+    else if(n)
         GF_CUDA(cudaMemcpyAsync(c->d_params, c->ring_buf[k], sizeof(double) * n, cudaMemcpyHostToDevice, c->stream));
-    }
-    if(norms) {
-        std::memcpy(c->ring_buf[k] + n, norms, sizeof(double) * n_norms);
+    else if(norms)
         GF_CUDA(cudaMemcpyAsync(c->d_norms, c->ring_buf[k] + n, sizeof(double) * n_norms, cudaMemcpyHostToDevice, c->stream));
-    }
     GF_CUDA(cudaEventRecord(c->ring_ev[k], c->stream));
     return 0;
 }
@@ -536,24 +538,34 @@ static int check_root(gf_ctx *c, int root) {
     return 0;
 }
 
-extern "C" int gf_eval_sum_async(gf_ctx *c, int root, int metric) {
+static int eval_sum_launch(gf_ctx *c, int root, int metric, double *out_dev) {
     if(check_root(c, root)) return 1;
     cudaSetDevice(c->device);
     int first = root - c->h_nodes[root].size + 1;
     int blocks = gf_grid_blocks(c, c->view.n_events, 4);
     cudaEventRecord(c->ev0, c->stream);
     k_eval_sum<<<blocks, GF_THREADS, gf_prog_smem(c), c->stream>>>(c->view, first, root, metric, c->n_cols,
-                                                                  c->d_partials, c->d_ticket, c->d_result);
+                                                                  c->d_partials, c->d_ticket, out_dev);
     cudaEventRecord(c->ev1, c->stream);
     c->launches++;
     GF_CUDA(cudaGetLastError());
+    return 0;
+}
+extern "C" int gf_eval_sum_async(gf_ctx *c, int root, int metric) {
+    if(eval_sum_launch(c, root, metric, c ? c->d_result : nullptr)) return 1;
     if(c->nccl_comm && gf_allreduce_sum(c, c->d_result, 1)) return 1;
     return 0;
 }
 
 extern "C" int gf_eval_sum(gf_ctx *c, int root, int metric, double *out) {
-    if(gf_eval_sum_async(c, root, metric)) return 1;
-    GF_CUDA(cudaMemcpyAsync(c->h_result, c->d_result, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    if(c && !c->nccl_comm && c->h_result_dev) {
+        // single GPU: the last block of the reduction writes the sum straight into mapped pinned host memory, so the
+        // call is launch + one synchronisation, with no device-to-host copy behind the kernel
+        if(eval_sum_launch(c, root, metric, c->h_result_dev)) return 1;
+    } else {
+        if(gf_eval_sum_async(c, root, metric)) return 1;
+        GF_CUDA(cudaMemcpyAsync(c->h_result, c->d_result, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    }
     GF_CUDA(cudaStreamSynchronize(c->stream));
     cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1);
     *out = c->h_result[0];

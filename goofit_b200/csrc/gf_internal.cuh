@@ -183,7 +183,8 @@ struct gf_ctx {
     double *d_partials = nullptr; // [GF_NPARTIAL * max_blocks]
     unsigned *d_ticket = nullptr;
     double *d_result = nullptr;   // [GF_NPARTIAL]
-    double *h_result = nullptr;   // pinned [GF_NPARTIAL * 64]
+    double *h_result = nullptr;   // pinned + mapped [GF_NPARTIAL * 64]
+    double *h_result_dev = nullptr; // device alias of h_result (zero-copy result of the single-GPU gf_eval_sum)
     double *d_events_out = nullptr;
     size_t events_out_cap = 0;
     int max_blocks = 0;

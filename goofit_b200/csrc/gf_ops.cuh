@@ -2,7 +2,15 @@
 // Each case cites the reference device function it reproduces (paths under /root/reference/src/PDFs).
 #pragma once
 
-__device__ inline double gf_pow_i(double x, int k) { return pow(x, (double)k); } // std::pow(double,int) promotes
+// std::pow(double, int) of the reference promotes to pow(double, double). For k = 0, 1, 2 the results 1, x and the
+// correctly rounded x*x are what a correctly rounded pow returns, without ~200 instructions of generic pow; higher
+// powers keep calling pow so that no extra rounding steps are introduced.
+__device__ inline double gf_pow_i(double x, int k) {
+    if(k == 0) return 1.0;
+    if(k == 1) return x;
+    if(k == 2) return x * x;
+    return pow(x, (double)k);
+}
 
 // KinLimitBWPdf.cu:7-24
 __device__ inline double gf_klbw_momentum(double mass, double pimass, double d0mass) {
@@ -56,6 +64,7 @@ __device__ inline double gf_leaf(const gf_node &nd, const gf_sprog &P, const Evt
     }
     case GF_OP_MULTI_POLYNOMIAL: { // PolynomialPdf.cu:47-118
         int nobs = nd.nobs, maxDegree = (int)c[0] + 1, numBoxes = 1;
+        if(maxDegree == 1) return p[nobs]; // degree 0 (the constant efficiency of the amplitude fits): one box
         for(int i = 0; i < nobs; ++i) numBoxes *= maxDegree;
         int coeff = nobs;
         double ret = p[coeff++];

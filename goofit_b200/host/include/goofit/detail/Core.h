@@ -581,6 +581,9 @@ class GooPdf : public PdfBase {
 
   protected:
     int metric() const;
+    // memo of the last leaf grid integral (normalize()): inputs it depended on, and the sum
+    std::vector<double> gridKey;
+    fptype gridSum{0};
 };
 
 using device_function_ptr = int; // source compatibility for user code that names the type

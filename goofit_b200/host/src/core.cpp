@@ -296,8 +296,10 @@ void Engine::build(PdfBase *r) {
 }
 void Engine::sync() {
     gf_ctx *c = ctx();
-    if(paramsDirty) check(gf_set_params(c, prog.params.data(), (int)prog.params.size()), "gf_set_params");
-    if(normsDirty) check(gf_set_norms(c, prog.norms.data(), (int)prog.norms.size()), "gf_set_norms");
+    // one stream-ordered copy of the parameter + normalisation block through the pinned ring: no host-side wait
+    if(paramsDirty || normsDirty)
+        check(gf_set_params_async(c, prog.params.data(), (int)prog.params.size(), prog.norms.data(), (int)prog.norms.size()),
+              "gf_set_params_async");
     paramsDirty = normsDirty = false;
 }
 void Engine::release(const PdfBase *pdf) {
@@ -588,7 +590,27 @@ fptype GooPdf::normalize() { // GooPdf.cu:340-396
     size_t totalBins = get_bin_grid_size();
     ret *= get_bin_grid_volume();
     ret /= totalBins;
-    fptype sum = reduce_with_bins();
+    // A leaf's grid sum is a pure function of its pushed parameter block and of the grid; the reference re-sums it on
+    // every call (GooPdf.cu:366-388). Re-running the kernel only when one of those inputs moved returns the same
+    // number and saves a launch + readback per likelihood call for every fixed-shape component (e.g. a background).
+    fptype sum;
+    std::vector<double> key;
+    if(components.empty() && nodeIdx >= 0) {
+        key.push_back(static_cast<double>(Engine::get().generation));
+        for(size_t i = 0; i < parametersList.size(); ++i) key.push_back(par(i));
+        for(const Observable &v : observablesList) {
+            key.push_back(v.getLowerLimit());
+            key.push_back(v.getUpperLimit());
+            key.push_back(static_cast<double>(v.getNumBins()));
+        }
+    }
+    if(!key.empty() && key == gridKey)
+        sum = gridSum;
+    else {
+        sum     = reduce_with_bins();
+        gridKey = key;
+        gridSum = sum;
+    }
     if(std::isnan(sum))
         GooFit::abort(__FILE__, __LINE__, getName() + " NaN in normalization", this);
     else if(0 >= sum)
