@@ -93,7 +93,7 @@ __global__ void __launch_bounds__(GF_THREADS, 1) k_amp4_sf(const gf_dev_view V, 
 
 // every flagged lineshape in one pass. The four-vectors (~10 sqrt, 15 div, sin, cos) are only needed by lineshapes of
 // pairs other than (12) and (34); need_vecs is uniform over the grid.
-__global__ void __launch_bounds__(GF_THREADS, 2)
+__global__ void __launch_bounds__(GF_THREADS, 3)
     k_amp4_cache(const gf_dev_view V, int node, gf_amp4_args A, unsigned long long ls_mask, int need_vecs) {
     extern __shared__ __align__(16) unsigned char smem[];
     gf_sprog P = gf_stage_program(V, smem);
@@ -130,7 +130,33 @@ __global__ void __launch_bounds__(GF_THREADS, 2)
     }
 }
 
-__global__ void __launch_bounds__(GF_THREADS, 2)
+// One amplitude with compile-time shape: all of its lineshape / spin-factor loads are issued before the first multiply
+// (memory-level parallelism: the generic loop below has one dependent load in flight per thread), then the products are
+// formed in exactly the reference's order (AmpCalc.cu:36-57), so the result is bit-identical to the generic path.
+template <int LS_STEP, int SF_STEP, int NPERM>
+__device__ __forceinline__ double2 gf_amp4_one(const int32_t *rec, const gf_amp4_args &A, long e) {
+    constexpr int NLS = LS_STEP * NPERM, NSF = SF_STEP * NPERM;
+    double2 L[NLS];
+    double S[NSF];
+#pragma unroll
+    for(int j = 0; j < NLS; ++j) L[j] = __ldg(A.ls + (size_t)rec[3 + j] * A.ld + e);
+#pragma unroll
+    for(int j = 0; j < NSF; ++j) S[j] = __ldg(A.sf + (size_t)rec[3 + NLS + j] * A.ld + e);
+    gf_cplx total = gf_c(0, 0);
+#pragma unroll
+    for(int p = 0; p < NPERM; ++p) {
+        gf_cplx ret = gf_c(1, 0);
+#pragma unroll
+        for(int j = 0; j < LS_STEP; ++j) ret = ret * gf_c(L[p * LS_STEP + j].x, L[p * LS_STEP + j].y);
+#pragma unroll
+        for(int j = 0; j < SF_STEP; ++j) ret = ret * gf_c(S[p * SF_STEP + j], 0.0);
+        total = total + ret;
+    }
+    total = total * (1 / sqrt((double)NPERM));
+    return make_double2(total.re, total.im);
+}
+
+__global__ void __launch_bounds__(GF_THREADS, 3)
     k_amp4_amps(const gf_dev_view V, int node, gf_amp4_args A, unsigned long long amp_mask) {
     extern __shared__ __align__(16) unsigned char smem[];
     gf_sprog P = gf_stage_program(V, smem);
@@ -145,23 +171,36 @@ __global__ void __launch_bounds__(GF_THREADS, 2)
         for(int a = 0; a < nAmp; ++a) {
             if(!((amp_mask >> a) & 1ull)) continue;
             const int32_t *rec = rec0 + start[a];
-            int numLS = rec[0], numSF = rec[1], nPerm = rec[2];
-            int LS_step = numLS / nPerm, SF_step = numSF / nPerm;
-            gf_cplx total = gf_c(0, 0);
-            for(int p = 0; p < nPerm; ++p) {
-                gf_cplx ret = gf_c(1, 0);
-                for(int j = p * LS_step; j < (p + 1) * LS_step; ++j) {
-                    double2 t = A.ls[(size_t)rec[3 + j] * A.ld + e];
-                    ret = ret * gf_c(t.x, t.y);
+            const int numLS = rec[0], numSF = rec[1], nPerm = rec[2];
+            const int LS_step = numLS / nPerm, SF_step = numSF / nPerm;
+            const int shape = nPerm * 100 + LS_step * 10 + SF_step; // uniform over the grid
+            double2 out;
+            switch(shape) {
+            case 221: out = gf_amp4_one<2, 1, 2>(rec, A, e); break; // Bose-symmetrised two-resonance chains (DP4, TDDP4)
+            case 121: out = gf_amp4_one<2, 1, 1>(rec, A, e); break;
+            case 111: out = gf_amp4_one<1, 1, 1>(rec, A, e); break;
+            case 211: out = gf_amp4_one<1, 1, 2>(rec, A, e); break;
+            case 131: out = gf_amp4_one<3, 1, 1>(rec, A, e); break;
+            case 231: out = gf_amp4_one<3, 1, 2>(rec, A, e); break;
+            default: { // any other shape: the reference's loops as they are
+                gf_cplx total = gf_c(0, 0);
+                for(int p = 0; p < nPerm; ++p) {
+                    gf_cplx ret = gf_c(1, 0);
+                    for(int j = p * LS_step; j < (p + 1) * LS_step; ++j) {
+                        double2 t = A.ls[(size_t)rec[3 + j] * A.ld + e];
+                        ret = ret * gf_c(t.x, t.y);
+                    }
+                    for(int j = p * SF_step; j < (p + 1) * SF_step; ++j) {
+                        double s = A.sf[(size_t)rec[3 + numLS + j] * A.ld + e];
+                        ret = ret * gf_c(s, 0.0); // the reference multiplies by complex(sf, 0)
+                    }
+                    total = total + ret;
                 }
-                for(int j = p * SF_step; j < (p + 1) * SF_step; ++j) {
-                    double s = A.sf[(size_t)rec[3 + numLS + j] * A.ld + e];
-                    ret = ret * gf_c(s, 0.0); // the reference multiplies by complex(sf, 0)
-                }
-                total = total + ret;
+                total = total * (1 / sqrt((double)nPerm));
+                out = make_double2(total.re, total.im);
             }
-            total = total * (1 / sqrt((double)nPerm));
-            A.amps[(size_t)a * A.ld + e] = make_double2(total.re, total.im);
+            }
+            A.amps[(size_t)a * A.ld + e] = out;
         }
     }
 }
@@ -218,7 +257,7 @@ __global__ void __launch_bounds__(GF_THREADS, 4)
         acc[2] += w * (Are * Bre + Aim * Bim);
         acc[3] += w * (Aim * Bre - Are * Bim);
     }
-    gf_grid_finish(acc, 4, partials, ticket, out, red);
+    gf_grid_finish_n(acc, partials, ticket, out, red);
 }
 
 // G_ab = sum_m w_m A_a(m) conj(A_b(m)) for one GF_GRAM_T x GF_GRAM_T tile (rows a0.., columns b0..) of the Hermitian
@@ -253,7 +292,7 @@ __global__ void __launch_bounds__(GF_THREADS, 2)
             }
         }
     }
-    gf_grid_finish(acc, 2 * GF_GRAM_T * GF_GRAM_T, partials, ticket, out, red);
+    gf_grid_finish_n(acc, partials, ticket, out, red);
 }
 
 // ---- C ABI ---------------------------------------------------------------------------------------------------
@@ -372,7 +411,7 @@ static int run_set(gf_ctx *c, gf_amp4_state *s, int node, gf_amp4_set &S, int re
     for(int k = 0; k < 5; k++) A.cols[k] = S.cols[k];
     A.n = S.n; A.ld = S.ld; A.ls = S.ls; A.sf = S.sf; A.amps = S.amps;
     size_t sm = gf_prog_smem(c);
-    int blocks = gf_grid_blocks(c, S.n, 2);
+    int blocks = gf_grid_blocks(c, S.n, 3);
     if(redo_spins) {
         int sf_blocks = gf_grid_blocks(c, S.n, 1);
         if(sm > 48 * 1024) cudaFuncSetAttribute(k_amp4_sf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
@@ -391,7 +430,7 @@ static int run_set(gf_ctx *c, gf_amp4_state *s, int node, gf_amp4_set &S, int re
     }
     if(amp_mask) {
         if(sm > 48 * 1024) cudaFuncSetAttribute(k_amp4_amps, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-        k_amp4_amps<<<blocks, GF_THREADS, sm, c->stream>>>(c->view, node, A, amp_mask);
+        k_amp4_amps<<<gf_grid_blocks(c, S.n, 3), GF_THREADS, sm, c->stream>>>(c->view, node, A, amp_mask);
         c->launches++;
     }
     GF_CUDA(cudaGetLastError());

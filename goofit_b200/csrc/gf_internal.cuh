@@ -158,6 +158,35 @@ __device__ inline void gf_grid_finish(double *vals, int n_out, double *partials,
     }
 }
 
+// same, for a compile-time number of sums held in registers: the loops unroll, so `vals` is never indexed dynamically
+// (a runtime-indexed array would be demoted to local memory for the whole kernel, including its accumulation loop)
+template <int N>
+__device__ inline void gf_grid_finish_n(double (&vals)[N], double *partials, unsigned *ticket, double *out, double *sh) {
+    __shared__ bool is_last_n;
+#pragma unroll
+    for(int k = 0; k < N; k++) {
+        double r = gf_block_sum(vals[k], sh);
+        if(threadIdx.x == 0) partials[(size_t)k * gridDim.x + blockIdx.x] = r;
+    }
+    __threadfence();
+    if(threadIdx.x == 0) {
+        unsigned t = atomicAdd(ticket, 1u);
+        is_last_n = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if(is_last_n) {
+        __threadfence();
+        for(int k = 0; k < N; k++) {
+            double s = 0;
+            for(unsigned b = threadIdx.x; b < gridDim.x; b += blockDim.x)
+                s += __ldcg(partials + (size_t)k * gridDim.x + b);
+            double r = gf_block_sum(s, sh);
+            if(threadIdx.x == 0) out[k] = r;
+        }
+        if(threadIdx.x == 0) *ticket = 0;
+    }
+}
+
 // ---- host-side context -----------------------------------------------------------------------
 struct gf_ctx {
     int device = 0;

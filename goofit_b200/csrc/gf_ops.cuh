@@ -193,12 +193,19 @@ __device__ inline void gf_tres_gauss(double &P1, double &P2, double &P3, double 
 __device__ inline double gf_tres(int op, const double *p, double coshterm, double costerm, double sinhterm, double sinterm,
                                  double tau, double dtime, double x, double y, double sigma) {
     if(op == GF_OP_TRES_TRUTH) {
+        // same five terms in the same order as the reference; cos/sin share one argument reduction (sincos) and
+        // cosh/sinh share one expm1: with u = e^a - 1, sinh a = (u + u/(u+1))/2 and cosh a = 1 + u^2/(2(u+1)), both
+        // accurate to an ulp or two for the small a = y t/tau of mixing fits (no e^a - e^-a cancellation)
         double ret = 0;
         dtime /= tau;
-        ret += coshterm * cosh(y * dtime);
-        ret += costerm * cos(x * dtime);
-        ret -= 2 * sinhterm * sinh(y * dtime);
-        ret -= 2 * sinterm * sin(x * dtime);
+        double sn, cs;
+        sincos(x * dtime, &sn, &cs);
+        const double u = expm1(y * dtime), ui = u / (u + 1.0);
+        const double sh = 0.5 * (u + ui), ch = 1.0 + 0.5 * u * ui;
+        ret += coshterm * ch;
+        ret += costerm * cs;
+        ret -= 2 * sinhterm * sh;
+        ret -= 2 * sinterm * sn;
         ret *= exp(-dtime);
         return ret;
     }
