@@ -168,6 +168,78 @@ def four_body(gf, lib, ctx, kind, n_data, n_mc, steps, peak_hbm):
             "nll": last}
 
 
+def simple_fits(gf, lib, ctx, peak_hbm, steps=20):
+    """BASELINE configs[0] and [1]: the event-streaming fits. exponential = ExpPdf on 10^6 events (8 MB: L2-resident, so
+    latency- not HBM-bound; also run at 10^8 events where it streams). zachFit = AddPdf(Argus, KinLimitBW (x) resolution)
+    on 10^7 delta-M values with the reference's 2.7e-6 integration step (10 000-point model workspace)."""
+    out = {}
+    rng = np.random.default_rng(137)
+    for tag, n in (("exponential_1e6", 1_000_000), ("exponential_1e8", 100_000_000)):
+        x = gf.Observable("x", 0, 10)
+        xs = rng.exponential(1.0, n)
+        xs = xs[xs < 10.0]
+        from models import dataset_from_columns
+        d = dataset_from_columns([x], [xs])
+        alpha = gf.Variable("alpha", -2, 0.1, -10, 10)
+        pdf = gf.ExpPdf("exppdf", x, alpha)
+        pdf.setData(d)
+        pdf.calculateNLL()
+        fm = gf.FitManager(pdf)
+        fcn = fm.getFCN()
+        vecs = [[-2.0 + 0.01 * (k % 5)] for k in range(steps + 3)]
+        for k in range(3):
+            fcn(vecs[k])
+        t0 = time.perf_counter()
+        for k in range(steps):
+            fcn(vecs[3 + k])
+        lib.gf_sync(ctx)
+        t = (time.perf_counter() - t0) / steps
+        root = pdf.getFunctionIndex()
+        ms = timed(lib, ctx, lambda: lib.gf_eval_sum_async(ctx, C.c_int(root), C.c_int(1)), 10)
+        ach = 8.0 * len(xs) / (ms * 1e-3) / 1e9
+        out[tag] = {"events": int(len(xs)), "value": len(xs) / (ms * 1e-3), "ms_per_step": ms,
+                    "e2e": {"value": len(xs) / t, "ms_per_step": 1e3 * t},
+                    "roofline": {"bound": "hbm", "achieved": ach, "peak": peak_hbm, "unit": "GB/s", "frac": ach / peak_hbm,
+                                 "kernel": "k_eval_sum", "algorithmic_bytes_per_step": 8 * len(xs)}}
+        del pdf, d
+    from models import zach_model
+    n = 10_000_000
+    dmv = 0.1395 + (0.1665 - 0.1395) * rng.beta(2.0, 5.0, n)
+    o = zach_model(dmv, step=2.7e-6, numbins=2700)
+    total = o["total"]
+    t0 = time.perf_counter()
+    total.setData(o["d"])
+    first = total.calculateNLL()
+    t_first = time.perf_counter() - t0
+    fm = gf.FitManager(total)
+    fcn, params = fm.getFCN(), fm.getParams()
+    v0 = np.array(params.make_minuit_vector())
+
+    def run(var, label):
+        i = var.fitter_index
+        vecs = []
+        for k in range(steps + 2):
+            v = v0.copy()
+            v[i] = v0[i] * (1.0 + 1e-3 * (k % 3 - 1))
+            vecs.append(list(v))
+        for k in range(2):
+            fcn(vecs[k])
+        lib.gf_sync(ctx)
+        l0 = gf.launch_count()
+        t0 = time.perf_counter()
+        for k in range(steps):
+            fcn(vecs[2 + k])
+        lib.gf_sync(ctx)
+        t = (time.perf_counter() - t0) / steps
+        return {"moved": label, "ms_per_call": 1e3 * t, "value": n / t, "launches_per_call": (gf.launch_count() - l0) / steps}
+
+    out["zachfit"] = {"events": n, "workspace_points": 10000, "norm_bins": 2700, "first_call_s": t_first, "nll": first,
+                      "unit": "events*evals/s", "calls": [run(o["frac"], "bkg_frac (no workspace refill)"),
+                                                           run(o["rs"], "res_sigma (resolution workspace + table)"),
+                                                           run(o["width"], "kl_width (model workspace + table)")]}
+    return out
+
+
 def run_all(gf, lib, ctx, M_dalitz, n_events, peak_hbm, steps=20):
     out = {}
     peak_tf = fp64_peak(lib, ctx)
@@ -181,4 +253,8 @@ def run_all(gf, lib, ctx, M_dalitz, n_events, peak_hbm, steps=20):
             out[kind] = four_body(gf, lib, ctx, kind, 10_000_000, 10_000_000, steps, peak_hbm)
         except Exception as e:
             out[kind] = {"error": str(e)[:200]}
+    try:
+        out.update(simple_fits(gf, lib, ctx, peak_hbm, steps))
+    except Exception as e:
+        out["simple_fits"] = {"error": str(e)[:300]}
     return out

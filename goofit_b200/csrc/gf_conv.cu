@@ -53,21 +53,34 @@ __global__ void __launch_bounds__(GF_THREADS, 4)
     }
 }
 
-// table[k-kmin] = sum_{i<n_model} model[i] * resol[i + offset - k], i ascending (one thread per k).
+// table[k-kmin] = sum_{i<n_model} model[i] * resol[i + offset - k], i ascending: one thread per k runs the reference's
+// sequential FMA chain (same order, same rounding), but the operands come from shared memory: a block of 64 consecutive
+// k stages GF_CONV_TILE model points and the GF_CONV_TILE + 63 resolution values they meet, so the chain waits on LDS and
+// the FP64 pipe instead of on one global load per term.
+#define GF_CONV_TILE 512
 __global__ void __launch_bounds__(64)
     k_conv_table(const double *__restrict__ model, const double *__restrict__ resol, int n_model, int n_resol,
                  int offset, int kmin, int nk, double *table) {
-    int t = blockIdx.x * blockDim.x + threadIdx.x;
-    if(t >= nk) return;
-    int k = kmin + t;
-    int base = offset - k;
+    __shared__ double sm_model[GF_CONV_TILE];
+    __shared__ double sm_res[GF_CONV_TILE + 64];
+    const int tl = threadIdx.x, t = blockIdx.x * 64 + tl;
+    const int k0 = kmin + blockIdx.x * 64;
     double ret = 0;
-    for(int i = 0; i < n_model; ++i) {
-        int j = i + base;
-        double r = (j >= 0 && j < n_resol) ? __ldg(resol + j) : 0.0;
-        ret += __ldg(model + i) * r;
+    for(int i0 = 0; i0 < n_model; i0 += GF_CONV_TILE) {
+        const int n = min(GF_CONV_TILE, n_model - i0);
+        const int jmin = i0 + offset - (k0 + 63); // resolution index met by (i0, the block's last k)
+        __syncthreads();
+        for(int q = tl; q < GF_CONV_TILE; q += 64) sm_model[q] = q < n ? __ldg(model + i0 + q) : 0.0;
+        for(int q = tl; q < GF_CONV_TILE + 64; q += 64) {
+            int jj = jmin + q;
+            sm_res[q] = (jj >= 0 && jj < n_resol) ? __ldg(resol + jj) : 0.0;
+        }
+        __syncthreads();
+        const double *r = sm_res + (63 - tl);
+#pragma unroll 8
+        for(int ii = 0; ii < n; ++ii) ret += sm_model[ii] * r[ii];
     }
-    table[t] = ret;
+    if(t < nk) table[t] = ret;
 }
 
 static int conv_check(gf_ctx *c, int node, gf_conv_state **out, bool create) {

@@ -265,3 +265,24 @@ class TDDP4:
         """cols7 = m12, m34, cos12, cos34, phi, dtime, sigmat"""
         n = len(cols7[0])
         return dataset_from_columns(self.observables, list(cols7[:5]) + [np.arange(n, dtype=np.float64)] + list(cols7[5:7]))
+
+
+def zach_model(dm_values, step=0.00003, numbins=270):
+    """D* -> D0 pi delta-M shape of examples/zachFit/zachFit.cpp:143-230, one resolution component:
+    AddPdf(bkg_frac; Argus, KinLimitBW (x) ScaledGaussian) with setIntegrationConstants(0.1395, 0.1665, step)."""
+    V = gf.Variable
+    dm = gf.Observable("dm", 0.1395, 0.1665)
+    dm.numbins = numbins
+    d = dataset_from_columns([dm], [dm_values])
+    o = dict(dm=dm, d=d)
+    o["mean"], o["width"] = V("kl_mean", 0.1454, 0.0001, 0.1450, 0.1458), V("kl_width", 0.0004, 0.0001, 0.0001, 0.001)
+    o["kl"] = gf.KinLimitBWPdf("klbw", dm, o["mean"], o["width"])
+    o["kl"].setMasses(1.8645, 0.13957)
+    o["bkg"] = gf.ArgusPdf("argus_dm", dm, V("arg_m0", 0.13957, 0.0001, 0.1, 0.2), V("arg_slope", -1.0, 0.1, -100, 10), False, V("arg_power", 0.5, 0.01, 0.1, 2))
+    o["rs"] = V("res_sigma", 0.00025, 0.00001, 0.0001, 0.001)
+    o["res"] = gf.ScaledGaussianPdf("resolution", dm, V("dummyzero", 0), o["rs"], V("delta", 0.00002, 0.00001, -0.001, 0.001), V("epsilon", 0.05, 0.01, -0.5, 0.5))
+    o["conv"] = gf.ConvolutionPdf("conv", dm, o["kl"], o["res"])
+    o["conv"].setIntegrationConstants(0.1395, 0.1665, step)
+    o["frac"] = V("bkg_frac", 0.3, 0.01, 0, 1)
+    o["total"] = gf.AddPdf("total", o["frac"], o["bkg"], o["conv"])
+    return o

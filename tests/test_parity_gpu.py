@@ -131,22 +131,8 @@ def test_shapes(golden):
 
 
 def make_zach(golden):
-    V = gf.Variable
-    dm = gf.Observable("dm", 0.1395, 0.1665)
-    dm.numbins = 270
-    d = dataset_from_columns([dm], [golden.arr("dm.x")])
-    o = dict(dm=dm, d=d)
-    o["mean"], o["width"] = V("kl_mean", 0.1454, 0.0001, 0.1450, 0.1458), V("kl_width", 0.0004, 0.0001, 0.0001, 0.001)
-    o["kl"] = gf.KinLimitBWPdf("klbw", dm, o["mean"], o["width"])
-    o["kl"].setMasses(1.8645, 0.13957)
-    o["bkg"] = gf.ArgusPdf("argus_dm", dm, V("arg_m0", 0.13957, 0.0001, 0.1, 0.2), V("arg_slope", -1.0, 0.1, -100, 10), False, V("arg_power", 0.5, 0.01, 0.1, 2))
-    o["rs"] = V("res_sigma", 0.00025, 0.00001, 0.0001, 0.001)
-    o["res"] = gf.ScaledGaussianPdf("resolution", dm, V("dummyzero", 0), o["rs"], V("delta", 0.00002, 0.00001, -0.001, 0.001), V("epsilon", 0.05, 0.01, -0.5, 0.5))
-    o["conv"] = gf.ConvolutionPdf("conv", dm, o["kl"], o["res"])
-    o["conv"].setIntegrationConstants(0.1395, 0.1665, 0.00003)
-    o["frac"] = V("bkg_frac", 0.3, 0.01, 0, 1)
-    o["total"] = gf.AddPdf("total", o["frac"], o["bkg"], o["conv"])
-    return o
+    from models import zach_model
+    return zach_model(golden.arr("dm.x"))
 
 
 def test_zachfit_pieces(golden):
