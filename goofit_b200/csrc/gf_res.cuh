@@ -218,9 +218,12 @@ struct gf_res_inv {
     int op, spin, cyc, norm, nterm, pad;
     double mass, width, mass2;
     double q0[2], qM0[2], frn[2], frMn[2]; // per symmetrisation term (cyc, cyc+1)
+    double inv_q0, mw;                      // 1/q0 and mass^2 * width of the first term
 };
 struct gf_pair_inv {
-    double s, rs, q, qMn, qMp, z1, z2; // z1/z2: Zemach factor for spin 1 / 2
+    double s, rs, inv_rs, q, qMn, qMp, z1, z2; // z1/z2: Zemach factor for spin 1 / 2
+    // Blatt-Weisskopf pieces per spin 1, 2: normalised form -> 1/F(q), 1/F(qM); plain form -> F(q), F(qM)
+    double bw1, bw2, bwM1, bwM2;
 };
 struct gf_pair_need { // what the flagged resonances need of each pair (uniform over the grid)
     int used, norm, plain, maxspin;
@@ -253,6 +256,8 @@ __device__ inline void gf_res_prepare(gf_res_inv &R, const gf_node &nd, const do
         R.frMn[t] = R.spin ? gf_damp_sq_norm(R.qM0[t], R.spin, D.mrad) : 1.0;
         cyc = (cyc + 1) % 3;
     }
+    R.inv_q0 = 1.0 / R.q0[0];
+    R.mw = R.mass2 * R.width;
 }
 __device__ inline void gf_pair_prepare(gf_pair_inv &Q, const gf_pair_need &need, int cyc, const gf_decay3 &D, double m12,
                                        double m13, double m23) {
@@ -263,39 +268,46 @@ __device__ inline void gf_pair_prepare(gf_pair_inv &Q, const gf_pair_need &need,
     Q.q = gf_cm_mom(Q.s, da, db);
     Q.qMn = need.norm ? gf_cm_mom_mother(Q.s, D.M, bach) : 0.0;
     Q.qMp = need.plain ? gf_cm_mom(D.M * D.M, Q.rs, bach) : 0.0;
+    Q.inv_rs = 1.0 / Q.rs;
     Q.z1 = Q.z2 = 1.0;
+    Q.bw1 = Q.bw2 = Q.bwM1 = Q.bwM2 = 1.0;
     if(need.maxspin >= 1) Q.z1 = gf_spin3(1, D, m12, m13, m23, cyc);
     if(need.maxspin >= 2) Q.z2 = gf_spin3(2, D, m12, m13, m23, cyc);
+    if(need.norm && need.maxspin >= 1) {
+        Q.bw1 = 1.0 / gf_damp_sq_norm(Q.q, 1, D.rad);
+        Q.bwM1 = 1.0 / gf_damp_sq_norm(Q.qMn, 1, D.mrad);
+    }
+    if(need.norm && need.maxspin >= 2) {
+        Q.bw2 = 1.0 / gf_damp_sq_norm(Q.q, 2, D.rad);
+        Q.bwM2 = 1.0 / gf_damp_sq_norm(Q.qMn, 2, D.mrad);
+    }
 }
 __device__ inline double gf_pow_odd(double r, int spin) { // r^(2 spin + 1)
     double r2 = r * r, out = r;
     for(int k = 0; k < spin; ++k) out *= r2;
     return out;
 }
-// one plain-RBW term from the shared pieces (RBW.cu:9-86 with the event/pair part hoisted into P)
+// one plain-RBW term from the shared pieces (RBW.cu:9-86 with the event/pair part hoisted into P). Against the
+// reference's operation sequence this trades four divisions and one square root per resonance for multiplications by
+// reciprocals that are shared per pair (1/sqrt(s), 1/F(q), 1/F(qM)) or per resonance (1/q0), and takes
+// sqrt(fr * frM) once instead of sqrt(fr) * sqrt(frM): each substitution moves the result by at most an ulp or two.
 __device__ inline double2 gf_rbw_term(const gf_res_inv &R, const gf_pair_inv &P, const gf_decay3 &D) {
     const int spin = R.spin;
     double fr = 1, frM = 1;
     if(spin != 0) {
         if(R.norm) {
-            fr = R.frn[0] / gf_damp_sq_norm(P.q, spin, D.rad);
-            frM = R.frMn[0] / gf_damp_sq_norm(P.qMn, spin, D.mrad);
+            fr = R.frn[0] * (spin == 1 ? P.bw1 : P.bw2);
+            frM = R.frMn[0] * (spin == 1 ? P.bwM1 : P.bwM2);
         } else {
             fr = gf_damp_sq(P.q, spin, D.rad);
             frM = gf_damp_sq(P.qMp, spin, D.mrad);
         }
     }
     double A = R.mass2 - P.s;
-    double B = R.mass2 * R.width * gf_pow_odd(P.q / R.q0[0], spin) * fr / P.rs;
+    double B = R.mw * gf_pow_odd(P.q * R.inv_q0, spin) * fr * P.inv_rs;
     double C = 1.0 / (A * A + B * B);
-    double re = A * C, im = B * C;
-    double f = sqrt(fr);
-    re *= f; im *= f;
-    f = sqrt(frM);
-    re *= f; im *= f;
-    f = spin == 0 ? 1.0 : (spin == 1 ? P.z1 : P.z2);
-    re *= f; im *= f;
-    return make_double2(0.0 + re, 0.0 + im); // the reference accumulates into a zero-initialised result
+    double f = sqrt(fr * frM) * (spin == 0 ? 1.0 : (spin == 1 ? P.z1 : P.z2)) * C;
+    return make_double2(A * f, B * f);
 }
 #define GF_MAX_RES 64
 struct gf_amp3_shared {

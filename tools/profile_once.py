@@ -41,6 +41,8 @@ for kind in ("dp4", "tddp4"):
     M.dp.setDataSize(len(d), 6 if kind == "dp4" else 8)
     print(kind, M.signal.calculateNLL())
     # the K*(892) mass moves: only its lineshapes and the amplitudes using them are redone
+    for v in M.lsvars:
+        v.changed = False
     M.lsvars[2].changed = True
     M.signal.updateVariable(M.lsvars[2], 0.8975)
     M.signal.updateParameters()
