@@ -114,7 +114,7 @@ def reference_arm(args, rank):
     sample = args.ref_events
     r = run_reference("dalitz", sample, args.steps, args.warmup)
     if r is None:
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/ref_driver not built (needs /root/reference at build time)"}))
+        emit({"impl": "reference", "unavailable": "oracle/_ref/ref_driver not built (needs /root/reference at build time)"})
         return 0
     v = r["events_x_evals_per_s"]
     line = {
@@ -127,11 +127,30 @@ def reference_arm(args, rank):
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "setdata_s": r["setdata_s"], "first_call_s": r["first_call_s"],
     }
-    print(json.dumps(line))
+    emit(line)
     return 0
 
 
+_REAL_STDOUT = None
+
+
+def claim_stdout():
+    """stdout carries exactly ONE JSON line: anything a library prints there (NCCL's version banner, for one) is sent to
+    stderr by pointing fd 1 at fd 2 for the duration of the run; emit() writes the line to the saved descriptor."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    sys.stdout.flush()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, data)
+
+
 def main():
+    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=50)
@@ -320,7 +339,7 @@ def main():
                                             "ms_per_step": r["ms_per_step"], "setdata_s": r["setdata_s"], "first_call_s": r["first_call_s"]}
             except Exception as e:  # the baseline is reported, never required
                 line["cpu_baseline"] = {"error": str(e)[:200]}
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         lib.gf_comm_destroy(ctx)
         dist.barrier()

@@ -2,6 +2,8 @@
 oracle/ref_driver.cpp). Every test calls the product through the host API -> C ABI -> sm_100a kernels.
 Tolerances: per-event values 1e-12 relative (libm vs CUDA libm differ at the ulp level); NLL sums 1e-12
 relative (north star); fitted parameters 0.01 sigma (north star)."""
+import os
+
 import numpy as np
 import pytest
 
@@ -411,6 +413,20 @@ def test_tddp4_generated_norm_sample():
     assert a.shape[0] == 5 and 0 < a.shape[1] < 20000 and A.dp.getNumAccNormEvents() == a.shape[1]
     assert np.array_equal(a, b) and (a.shape != c.shape or not np.array_equal(a, c))
     assert A.dp.getSumInitNormEventWeights() == a.shape[1]
+
+
+def test_two_gpu_sharded_parity():
+    """events and MC normalisation sample sharded over two GPUs, sums all-reduced over NCCL inside the library: every
+    golden NLL / integral is reproduced (tests/mgpu_worker.py). Needs two visible GPUs."""
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    here = os.path.dirname(os.path.abspath(__file__))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+                        "--master-port", "29541", os.path.join(here, "mgpu_worker.py")], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "MGPU_OK" in r.stdout, r.stdout[-1500:] + r.stderr[-3000:]
 
 
 def test_cpp_example_exponential():
