@@ -1,7 +1,8 @@
 // gf_amp4.cu — Amp4Body caches and the Monte-Carlo normalisation integral.
-//   k_amp4_sf     ONE pass per event set (data or MC), once: get4Vecs, then every spin factor
-//   k_amp4_cache  ONE pass per event set: get4Vecs once (only if a flagged lineshape needs it), then every flagged
-//                 lineshape (the reference launches one thrust::transform per spin factor / lineshape and
+//   k_amp4_sf     ONE pass per event set (data or MC), once: get4Vecs, then every spin factor and the pair masses the
+//                 lineshapes are evaluated at (parameter-independent kinematics, cached in `kin` planes)
+//   k_amp4_cache  ONE pass per event set: every flagged lineshape from the cached pair masses, no four-vectors
+//                 (the reference launches one thrust::transform per spin factor / lineshape and
 //                 recomputes get4Vecs in each: Amp4Body.cu:432-525, detail/{SF,LS,NormSpin,NormLS}Calculator.cu)
 //   k_amp4_amps   A_a = 1/sqrt(nPerm) * sum_perm prod LS * prod SF for every flagged amplitude
 //                 (detail/AmpCalc.cu:14-59); also run on the MC sample so that
@@ -21,18 +22,28 @@ struct gf_amp4_set { // one event sample (data or MC) with its caches
     double2 *ls = nullptr;
     double *sf = nullptr;
     double2 *amps = nullptr;
+    double *kin = nullptr; // parameter-independent pair masses of the lineshapes: [n_kin][ld], filled with the spin factors
+};
+// which kin plane holds the resonant-pair mass (m) and, for three-body pairs, the two-body sub-mass d1 (d) of lineshape i;
+// -1: not needed (pairs (12), (34) are data columns; two-body pairs have constant daughters)
+struct gf_amp4_kinmap {
+    signed char m[64], d[64];
+    int n;
 };
 struct gf_amp4_state {
     int node = -1, slot = -1, nLS = 0, nSF = 0, nAmp = 0, td = 0;
+    gf_amp4_kinmap kin{};
     gf_amp4_set data, mc;
     // Gram matrix of the MC amplitudes, tile by tile: [tile][GF_GRAM_T * GF_GRAM_T][re, im]
     double *d_gram = nullptr, *d_gram_partials = nullptr, *h_gram = nullptr;
     unsigned *d_gram_ticket = nullptr;
     int gram_blocks = 0;
+    bool gram_valid = false;               // d_gram / h_gram hold every tile of the current MC amplitudes
+    unsigned long long gram_pending = 0;   // MC amplitudes rebuilt since the last gf_amp4_gram
 };
 
 static void free_set(gf_amp4_set &s) {
-    cudaFree(s.owned_cols); cudaFree(s.weights); cudaFree(s.ls); cudaFree(s.sf); cudaFree(s.amps);
+    cudaFree(s.owned_cols); cudaFree(s.weights); cudaFree(s.ls); cudaFree(s.sf); cudaFree(s.amps); cudaFree(s.kin);
     s = gf_amp4_set();
 }
 void gf_amp4_free(gf_ctx *c) {
@@ -61,6 +72,7 @@ struct gf_amp4_args {
     double2 *ls;
     double *sf;
     double2 *amps;
+    double *kin;
 };
 
 // ints of the AMP4 node: {aux slot, nLS, nSF, nAmp, td, ls_node[nLS], sf_node[nSF], start[nAmp], records...}
@@ -68,7 +80,7 @@ struct gf_amp4_args {
 // Spin factors are computed once per event sample; their tensor algebra wants many registers, so they get their own
 // kernel at one block per SM instead of setting the register budget of the lineshape kernel, which reruns whenever a
 // mass or width moves.
-__global__ void __launch_bounds__(GF_THREADS, 1) k_amp4_sf(const gf_dev_view V, int node, gf_amp4_args A) {
+__global__ void __launch_bounds__(GF_THREADS, 1) k_amp4_sf(const gf_dev_view V, int node, gf_amp4_args A, const gf_amp4_kinmap K) {
     extern __shared__ __align__(16) unsigned char smem[];
     gf_sprog P = gf_stage_program(V, smem);
     __syncthreads();
@@ -88,13 +100,28 @@ __global__ void __launch_bounds__(GF_THREADS, 1) k_amp4_sf(const gf_dev_view V, 
             int kind = P.ints[sn.int_off];
             A.sf[(size_t)k * A.ld + e] = gf_spinfactor(kind, P.consts + sn.con_off, vecs);
         }
+        // The invariant masses a lineshape is evaluated at depend on the event only, never on a fit parameter: keep them,
+        // so that the lineshape kernel (which reruns whenever a mass or width moves) needs no four-vectors at all.
+        // Each plane is written by the first lineshape that maps to it (same pair => same value).
+        for(int i = 0; i < nLS; ++i) {
+            if(K.m[i] < 0) continue;
+            bool first = true;
+            for(int j = 0; j < i; ++j) first = first && K.m[j] != K.m[i];
+            if(!first) continue;
+            const gf_node &ln = P.nodes[in[5 + i]];
+            int pair = (int)(P.consts + ln.con_off)[0];
+            double d1, d2;
+            double mres = gf_getmass(pair, d1, d2, vecs, m1, m2, m3, m4);
+            A.kin[(size_t)K.m[i] * A.ld + e] = mres;
+            if(K.d[i] >= 0) A.kin[(size_t)K.d[i] * A.ld + e] = d1;
+        }
     }
 }
 
-// every flagged lineshape in one pass. The four-vectors (~10 sqrt, 15 div, sin, cos) are only needed by lineshapes of
-// pairs other than (12) and (34); need_vecs is uniform over the grid.
+// every flagged lineshape in one pass, from the data columns (pairs (12), (34)) or the cached pair masses: no
+// four-vector reconstruction (the reference redoes get4Vecs inside every LSCalculator call, LSCalculator.cu:30-60)
 __global__ void __launch_bounds__(GF_THREADS, 3)
-    k_amp4_cache(const gf_dev_view V, int node, gf_amp4_args A, unsigned long long ls_mask, int need_vecs) {
+    k_amp4_cache(const gf_dev_view V, int node, gf_amp4_args A, unsigned long long ls_mask, const gf_amp4_kinmap K) {
     extern __shared__ __align__(16) unsigned char smem[];
     gf_sprog P = gf_stage_program(V, smem);
     __syncthreads();
@@ -102,30 +129,32 @@ __global__ void __launch_bounds__(GF_THREADS, 3)
     const int32_t *in = P.ints + nd.int_off;
     const double *mc = P.consts + nd.con_off; // M, m1, m2, m3, m4
     const int nLS = in[1];
-    const double M = mc[0], m1 = mc[1], m2 = mc[2], m3 = mc[3], m4 = mc[4];
+    const double m1 = mc[1], m2 = mc[2], m3 = mc[3], m4 = mc[4];
     const long stride = (long)gridDim.x * blockDim.x;
-    for(long e = (long)blockIdx.x * blockDim.x + threadIdx.x; e < A.n; e += stride) {
-        double m12 = __ldg(A.cols[0] + e), m34 = __ldg(A.cols[1] + e);
-        double vecs[16];
-        if(need_vecs) {
-            double c12 = __ldg(A.cols[2] + e), c34 = __ldg(A.cols[3] + e), phi = __ldg(A.cols[4] + e);
-            gf_get4vecs(vecs, m12, m34, c12, c34, phi, M, m1, m2, m3, m4);
-        }
-        for(int i = 0; i < nLS; ++i) {
-            if(!((ls_mask >> i) & 1ull)) continue;
-            const gf_node &ln = P.nodes[in[5 + i]];
-            const double *lc = P.consts + ln.con_off;
-            int kind = P.ints[ln.int_off];
-            int pair = (int)lc[0];
-            double mres, d1, d2;
-            if(pair < 2) { // LSCalculator.cu:47-53
-                mres = pair == 0 ? m12 : m34;
-                d1 = pair == 0 ? m1 : m3;
-                d2 = pair == 0 ? m2 : m4;
-            } else
-                mres = gf_getmass(pair, d1, d2, vecs, m1, m2, m3, m4);
-            gf_cplx r = gf_lineshape(kind, P.params + ln.par_off, lc, mres, d1, d2);
-            __stcs(A.ls + (size_t)i * A.ld + e, make_double2(r.re, r.im));
+    // lineshape outer, events inner: everything that depends on the lineshape's parameters only (its q0-type momenta,
+    // the k normalisation with two square roots and a division, the pair's constant daughters) is loop-invariant for the
+    // event loop and is hoisted out of it by the compiler
+    for(int i = 0; i < nLS; ++i) {
+        if(!((ls_mask >> i) & 1ull)) continue;
+        const gf_node &ln = P.nodes[in[5 + i]];
+        const double *lc = P.consts + ln.con_off;
+        const double *lp = P.params + ln.par_off;
+        const int kind = P.ints[ln.int_off];
+        const int pair = (int)lc[0];
+        double d1c, d2;
+        if(pair < 2) { // LSCalculator.cu:47-53
+            d1c = pair == 0 ? m1 : m3;
+            d2 = pair == 0 ? m2 : m4;
+        } else
+            gf_pair_daughters(pair, d1c, d2, m1, m2, m3, m4);
+        const double *mcol = pair < 2 ? A.cols[pair] : A.kin + (size_t)K.m[i] * A.ld;
+        const double *dcol = (pair >= 2 && K.d[i] >= 0) ? A.kin + (size_t)K.d[i] * A.ld : nullptr;
+        double2 *out = A.ls + (size_t)i * A.ld;
+        for(long e = (long)blockIdx.x * blockDim.x + threadIdx.x; e < A.n; e += stride) {
+            const double mres = __ldg(mcol + e);
+            const double d1 = dcol ? __ldg(dcol + e) : d1c;
+            gf_cplx r = gf_lineshape(kind, lp, lc, mres, d1, d2);
+            __stcs(out + e, make_double2(r.re, r.im));
         }
     }
 }
@@ -340,6 +369,20 @@ static int amp4_check(gf_ctx *c, int node, gf_amp4_state **out, bool create) {
     gf_amp4_state *s = find_amp4(c, node, create);
     if(!s) return gf_fail("gf_amp4: gf_amp4_alloc / gf_amp4_set_mc not called for this node");
     s->slot = in[0]; s->nLS = nLS; s->nSF = nSF; s->nAmp = nAmp; s->td = c->h_nodes[node].op == GF_OP_AMP4_TD ? 1 : 0;
+    { // kin planes: one per distinct pair >= 2 (resonant mass) and one more per distinct three-body pair (its d1)
+        int slot_m[18], slot_d[18], n = 0;
+        for(int p = 0; p < 18; p++) slot_m[p] = slot_d[p] = -1;
+        for(int i = 0; i < nLS; i++) {
+            int pair = (int)c->h_consts[c->h_nodes[in[5 + i]].con_off];
+            s->kin.m[i] = s->kin.d[i] = -1;
+            if(pair < 2 || pair > 17) continue;
+            if(slot_m[pair] < 0) slot_m[pair] = n++;
+            if(pair >= 6 && slot_d[pair] < 0) slot_d[pair] = n++;
+            s->kin.m[i] = (signed char)slot_m[pair];
+            s->kin.d[i] = (signed char)slot_d[pair];
+        }
+        s->kin.n = n;
+    }
     *out = s;
     return 0;
 }
@@ -353,6 +396,9 @@ static int alloc_caches(gf_ctx *c, gf_amp4_state *s, gf_amp4_set &S, size_t n) {
     GF_CUDA(cudaMalloc(&S.ls, sizeof(double2) * (size_t)S.ld * std::max(1, s->nLS)));
     GF_CUDA(cudaMalloc(&S.sf, sizeof(double) * (size_t)S.ld * std::max(1, s->nSF)));
     GF_CUDA(cudaMalloc(&S.amps, sizeof(double2) * (size_t)S.ld * s->nAmp));
+    cudaFree(S.kin);
+    S.kin = nullptr;
+    GF_CUDA(cudaMalloc(&S.kin, sizeof(double) * (size_t)S.ld * std::max(1, s->kin.n)));
     GF_CUDA(cudaMemsetAsync(S.ls, 0, sizeof(double2) * (size_t)S.ld * std::max(1, s->nLS), c->stream));
     GF_CUDA(cudaMemsetAsync(S.sf, 0, sizeof(double) * (size_t)S.ld * std::max(1, s->nSF), c->stream));
     GF_CUDA(cudaMemsetAsync(S.amps, 0, sizeof(double2) * (size_t)S.ld * s->nAmp, c->stream));
@@ -384,6 +430,7 @@ extern "C" int gf_amp4_set_mc(gf_ctx *c, int node, const double *const *mc_cols5
     cudaFree(s->mc.owned_cols); cudaFree(s->mc.weights);
     s->mc.owned_cols = nullptr; s->mc.weights = nullptr;
     if(alloc_caches(c, s, s->mc, n_mc)) return 1;
+    s->gram_valid = false;
     GF_CUDA(cudaMalloc(&s->mc.owned_cols, sizeof(double) * 5 * (size_t)s->mc.ld));
     for(int k = 0; k < 5; k++) {
         GF_CUDA(cudaMemcpyAsync(s->mc.owned_cols + (size_t)k * s->mc.ld, mc_cols5[k], sizeof(double) * n_mc, cudaMemcpyHostToDevice, c->stream));
@@ -409,23 +456,18 @@ static int run_set(gf_ctx *c, gf_amp4_state *s, int node, gf_amp4_set &S, int re
     if(S.n == 0 || !S.ls) return 0;
     gf_amp4_args A;
     for(int k = 0; k < 5; k++) A.cols[k] = S.cols[k];
-    A.n = S.n; A.ld = S.ld; A.ls = S.ls; A.sf = S.sf; A.amps = S.amps;
+    A.n = S.n; A.ld = S.ld; A.ls = S.ls; A.sf = S.sf; A.amps = S.amps; A.kin = S.kin;
     size_t sm = gf_prog_smem(c);
     int blocks = gf_grid_blocks(c, S.n, 3);
     if(redo_spins) {
         int sf_blocks = gf_grid_blocks(c, S.n, 1);
         if(sm > 48 * 1024) cudaFuncSetAttribute(k_amp4_sf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-        k_amp4_sf<<<sf_blocks, GF_THREADS, sm, c->stream>>>(c->view, node, A);
+        k_amp4_sf<<<sf_blocks, GF_THREADS, sm, c->stream>>>(c->view, node, A, s->kin);
         c->launches++;
     }
     if(ls_mask) {
-        int need_vecs = 0;
-        const gf_node &nd = c->h_nodes[node];
-        const int32_t *in = c->h_ints.data() + nd.int_off;
-        for(int i = 0; i < s->nLS && !need_vecs; i++)
-            if(((ls_mask >> i) & 1ull) && (int)c->h_consts[c->h_nodes[in[5 + i]].con_off] >= 2) need_vecs = 1;
         if(sm > 48 * 1024) cudaFuncSetAttribute(k_amp4_cache, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-        k_amp4_cache<<<blocks, GF_THREADS, sm, c->stream>>>(c->view, node, A, ls_mask, need_vecs);
+        k_amp4_cache<<<blocks, GF_THREADS, sm, c->stream>>>(c->view, node, A, ls_mask, s->kin);
         c->launches++;
     }
     if(amp_mask) {
@@ -457,6 +499,7 @@ extern "C" int gf_amp4_cache(gf_ctx *c, int node, int redo_spins, const uint8_t 
     if(s->data.ls && s->data.n != c->view.n_events) return gf_fail("gf_amp4_cache: cache size != uploaded events");
     if(run_set(c, s, node, s->data, redo_spins, ls_mask, amp_mask)) return 1;
     if(run_set(c, s, node, s->mc, redo_spins, ls_mask, mc_amp_mask)) return 1;
+    s->gram_pending |= mc_amp_mask;
     return 0;
 }
 
@@ -513,18 +556,27 @@ extern "C" int gf_amp4_gram(gf_ctx *c, int node, double *G_re_im) {
         GF_CUDA(cudaMemsetAsync(s->d_gram_ticket, 0, sizeof(unsigned), c->stream));
         GF_CUDA(cudaMallocHost(&s->h_gram, sizeof(double) * per * maxTiles));
         s->gram_blocks = blocks;
+        s->gram_valid = false;
     }
-    int t = 0;
+    // only the tiles with a rebuilt amplitude among their rows or columns are re-summed; the others keep their
+    // (already all-reduced) values
+    int t = 0, launched = 0;
     for(int ta = 0; ta < nT; ta++)
         for(int tb = ta; tb < nT; tb++, t++) {
+            unsigned long long rows = ((1ull << T) - 1) << (ta * T), cols = ((1ull << T) - 1) << (tb * T);
+            if(s->gram_valid && !(s->gram_pending & (rows | cols))) continue;
+            double *out = s->d_gram + (size_t)t * per;
             k_amp4_gram<<<blocks, GF_THREADS, 0, c->stream>>>(s->mc.amps, s->mc.ld, s->mc.n, s->mc.weights, s->nAmp, ta * T, tb * T,
-                                                             s->d_gram_partials, s->d_gram_ticket, s->d_gram + (size_t)t * per);
+                                                             s->d_gram_partials, s->d_gram_ticket, out);
             c->launches++;
+            launched++;
+            GF_CUDA(cudaGetLastError());
+            if(c->nccl_comm && gf_allreduce_sum(c, out, per)) return 1;
+            GF_CUDA(cudaMemcpyAsync(s->h_gram + (size_t)t * per, out, sizeof(double) * per, cudaMemcpyDeviceToHost, c->stream));
         }
-    GF_CUDA(cudaGetLastError());
-    if(c->nccl_comm && gf_allreduce_sum(c, s->d_gram, per * nTiles)) return 1;
-    GF_CUDA(cudaMemcpyAsync(s->h_gram, s->d_gram, sizeof(double) * per * nTiles, cudaMemcpyDeviceToHost, c->stream));
-    GF_CUDA(cudaStreamSynchronize(c->stream));
+    if(launched) GF_CUDA(cudaStreamSynchronize(c->stream));
+    s->gram_valid = true;
+    s->gram_pending = 0;
     t = 0;
     const int n = s->nAmp;
     for(int ta = 0; ta < nT; ta++)

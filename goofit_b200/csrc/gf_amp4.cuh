@@ -106,6 +106,22 @@ __device__ inline double gf_getmass(int pair, double &d1, double &d2, const doub
     }
 }
 
+// constant daughters of a pair as gf_getmass reports them; for three-body pairs (>= 6) d1 is the event-dependent two-body
+// sub-mass and is left untouched here
+__device__ inline void gf_pair_daughters(int pair, double &d1, double &d2, double m1, double m2, double m3, double m4) {
+    switch(pair) {
+    case 2: d1 = m1; d2 = m3; break;
+    case 3: d1 = m1; d2 = m4; break;
+    case 4: d1 = m2; d2 = m3; break;
+    case 5: d1 = m2; d2 = m4; break;
+    case 6: case 13: case 16: d1 = 0; d2 = m3; break;
+    case 7: case 10: case 17: d1 = 0; d2 = m2; break;
+    case 8: case 11: case 14: d1 = 0; d2 = m1; break;
+    case 9: case 12: case 15: d1 = 0; d2 = m4; break;
+    default: d1 = 0; d2 = 0; break;
+    }
+}
+
 // ---- lineshapes -------------------------------------------------------------------------------------
 #define GF_MPIPLUS 0.139570
 #define GF_MKPLUS 0.493677
