@@ -34,6 +34,8 @@
 #include <mcbooster/Generate.h>
 #include <mcbooster/EvaluateArray.h>
 #include <goofit/PDFs/physics/ResonancePdf.h>
+#include <goofit/BinnedDataSet.h>
+#include <goofit/FitControl.h>
 #include <goofit/UnbinnedDataSet.h>
 #include <goofit/Variable.h>
 
@@ -258,6 +260,68 @@ static void case_basic() {
 }
 
 // ---- dalitz model (examples/dalitz/dalitz.cpp:124-322) -------------------------------------------
+// ---- binned fits (tests/simple/BinningTest.cpp:20-188: binned exp / gauss fits; MetricPointer.cu:23-58 metrics) -------
+static void case_binned() {
+    { // exponential, 100 bins
+        Observable x{"x", 0, 10};
+        x.setNumBins(100);
+        UnbinnedDataSet u{x};
+        fill_1d(u, x, 20000, 137, 1, 1.5);
+        save_npy("binned.exp_x", column(u, x));
+        BinnedDataSet b{x};
+        for(size_t i = 0; i < u.getNumEvents(); i++) {
+            x.setValue(u.getValue(x, i));
+            b.addEvent();
+        }
+        Variable alpha{"alpha", -2, 0.1, -10, 10};
+        ExpPdf pdf{"exppdf", x, alpha};
+        pdf.setFitControl(std::make_shared<BinnedNllFit>());
+        pdf.setData(&b);
+        put("binned.exp_nll", pdf.calculateNLL());
+        pdf.setFitControl(std::make_shared<BinnedChisqFit>());
+        pdf.setData(&b);
+        put("binned.exp_chisq", pdf.calculateNLL());
+        pdf.setFitControl(std::make_shared<BinnedErrorFit>());
+        for(size_t i = 0; i < b.getNumBins(); i++) b.setBinError(i, std::sqrt(std::max(1.0, (double)b.getBinContent(i))));
+        pdf.setData(&b);
+        put("binned.exp_binerr", pdf.calculateNLL());
+        pdf.setFitControl(std::make_shared<BinnedNllFit>());
+        pdf.setData(&b);
+        FitManager fit{&pdf};
+        fit.setVerbosity(0);
+        auto fm = fit.fit();
+        put("binned.exp_fit_alpha", alpha.getValue());
+        put("binned.exp_fit_alpha_err", alpha.getError());
+        put("binned.exp_fit_valid", (double)(int)fm.IsValid());
+    }
+    { // Gaussian, 200 bins, chi-square fit
+        Observable x{"x", -10, 10};
+        x.setNumBins(200);
+        UnbinnedDataSet u{x};
+        fill_1d(u, x, 30000, 11, 2);
+        save_npy("binned.gauss_x", column(u, x));
+        BinnedDataSet b{x};
+        for(size_t i = 0; i < u.getNumEvents(); i++) {
+            x.setValue(u.getValue(x, i));
+            b.addEvent();
+        }
+        Variable m{"m", 1.0, 0.1, -10, 10}, sg{"s", 2.0, 0.1, 0.5, 10};
+        GaussianPdf pdf{"gauss", x, m, sg};
+        pdf.setFitControl(std::make_shared<BinnedNllFit>());
+        pdf.setData(&b);
+        put("binned.gauss_nll", pdf.calculateNLL());
+        pdf.setFitControl(std::make_shared<BinnedChisqFit>());
+        pdf.setData(&b);
+        put("binned.gauss_chisq", pdf.calculateNLL());
+        FitManager fit{&pdf};
+        fit.setVerbosity(0);
+        auto fm = fit.fit();
+        put_vec("binned.gauss_fit", {m.getValue(), sg.getValue()});
+        put_vec("binned.gauss_fit_err", {m.getError(), sg.getError()});
+        put("binned.gauss_fit_valid", (double)(int)fm.IsValid());
+    }
+}
+
 static const fptype _mD0 = 1.86484, _mD02 = _mD0 * _mD0, _mD02inv = 1. / _mD02;
 static const fptype piPlusMass = 0.13957018, piZeroMass = 0.1349766;
 
@@ -911,6 +975,7 @@ int main(int argc, char **argv) {
             mkdir(g_out.c_str(), 0755);
             std::string only = argc > 3 ? argv[3] : "all";
             if(only == "all" || only == "basic") case_basic();
+            if(only == "all" || only == "binned") case_binned();
             if(only == "all" || only == "dalitz") case_dalitz();
             if(only == "all" || only == "dalitzfit") case_dalitz_fit();
             if(only == "all" || only == "dp4") case_dp4();

@@ -415,6 +415,59 @@ def test_tddp4_generated_norm_sample():
     assert A.dp.getSumInitNormEventWeights() == a.shape[1]
 
 
+def _binned(x, values):
+    b = gf.BinnedDataSet(x)
+    for v in values:
+        x.value = float(v)
+        b.addEvent()
+    return b
+
+
+def test_binned_fits(golden):
+    """BinnedDataSet upload (PdfBase.cu:439-527) and the binned metrics BinAvg / BinWithError / Chisq
+    (MetricPointer.cu:23-58) against the reference, plus binned fits (tests/simple/BinningTest.cpp)."""
+    V = gf.Variable
+    x = gf.Observable("x", 0, 10)
+    x.numbins = 100
+    b = _binned(x, golden.arr("binned.exp_x"))
+    alpha = V("alpha", -2, 0.1, -10, 10)
+    pdf = gf.ExpPdf("exppdf", x, alpha)
+    pdf.setFitControl(gf.BinnedNllFit())
+    pdf.setData(b)
+    assert rel(pdf.calculateNLL(), golden["binned.exp_nll"]) < RTOL_NLL
+    pdf.setFitControl(gf.BinnedChisqFit())
+    pdf.setData(b)
+    assert rel(pdf.calculateNLL(), golden["binned.exp_chisq"]) < RTOL_NLL
+    pdf.setFitControl(gf.BinnedErrorFit())
+    for i in range(b.getNumBins()):
+        b.setBinError(i, np.sqrt(max(1.0, b.getBinContent(i))))
+    pdf.setData(b)
+    assert rel(pdf.calculateNLL(), golden["binned.exp_binerr"]) < RTOL_NLL
+    pdf.setFitControl(gf.BinnedNllFit())
+    pdf.setData(b)
+    fm = gf.FitManager(pdf)
+    fm.setVerbosity(0)
+    fm.fit()
+    assert bool(fm) == bool(golden["binned.exp_fit_valid"])
+    assert abs(alpha.value - golden["binned.exp_fit_alpha"]) < 0.01 * golden["binned.exp_fit_alpha_err"]
+    x = gf.Observable("x", -10, 10)
+    x.numbins = 200
+    b = _binned(x, golden.arr("binned.gauss_x"))
+    m, sg = V("m", 1.0, 0.1, -10, 10), V("s", 2.0, 0.1, 0.5, 10)
+    pdf = gf.GaussianPdf("gauss", x, m, sg)
+    pdf.setFitControl(gf.BinnedNllFit())
+    pdf.setData(b)
+    assert rel(pdf.calculateNLL(), golden["binned.gauss_nll"]) < RTOL_NLL
+    pdf.setFitControl(gf.BinnedChisqFit())
+    pdf.setData(b)
+    assert rel(pdf.calculateNLL(), golden["binned.gauss_chisq"]) < RTOL_NLL
+    fm = gf.FitManager(pdf)
+    fm.setVerbosity(0)
+    fm.fit()
+    val, err = np.array(golden["binned.gauss_fit"]), np.array(golden["binned.gauss_fit_err"])
+    assert np.max(np.abs(np.array([m.value, sg.value]) - val) / err) < 0.01
+
+
 def test_two_gpu_sharded_parity():
     """events and MC normalisation sample sharded over two GPUs, sums all-reduced over NCCL inside the library: every
     golden NLL / integral is reproduced (tests/mgpu_worker.py). Needs two visible GPUs."""
