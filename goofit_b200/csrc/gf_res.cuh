@@ -184,6 +184,84 @@ __device__ inline double2 gf_res_gauss(double mass, double width, int cyc, doubl
     return make_double2(r, 0.0);
 }
 
+// complex helpers for the shapes below ((re, im) in a double2); division as in gf_amp4.cuh
+__device__ inline double2 gf_cmul(double2 a, double2 b) { return make_double2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
+__device__ inline double2 gf_cscale(double2 a, double s) { return make_double2(a.x * s, a.y * s); }
+__device__ inline double2 gf_cdiv(double2 a, double2 b) {
+    double denom = b.x * b.x + b.y * b.y;
+    return make_double2((a.x * b.x + a.y * b.y) / denom, (a.y * b.x - a.x * b.y) / denom);
+}
+// LASS.cu:9-117 (K pi S-wave: resonance + effective-range background)
+__device__ inline double2 gf_res_lass(const double *p, int spin, int cyc, bool norm, const gf_decay3 &D, double m12,
+                                      double m13, double m23) {
+    double resmass = p[0], reswidth = p[1], _a = p[2], _r = p[3], _R = p[4], _phiR = p[5], _B = p[6], _phiB = p[7];
+    double s = cyc == GF_PAIR_12 ? m12 : (cyc == GF_PAIR_13 ? m13 : m23);
+    double bach = cyc == GF_PAIR_12 ? D.d3 : (cyc == GF_PAIR_13 ? D.d2 : D.d1);
+    double da = cyc == GF_PAIR_23 ? D.d2 : D.d1;
+    double db = cyc == GF_PAIR_12 ? D.d2 : D.d3;
+    double fr = 1, frD = 1;
+    resmass *= resmass;
+    double q = gf_cm_mom(s, da, db), q0 = gf_cm_mom(resmass, da, db);
+    double qM, qM0 = 0;
+    if(norm) {
+        qM = gf_cm_mom_mother(s, D.M, bach);
+        qM0 = gf_cm_mom_mother(resmass, D.M, bach);
+    } else {
+        qM = gf_cm_mom(D.M * D.M, sqrt(s), bach);
+    }
+    if(spin != 0) {
+        if(norm) {
+            fr = gf_damp_sq_norm(q0, spin, D.rad) / gf_damp_sq_norm(q, spin, D.rad);
+            frD = gf_damp_sq_norm(qM0, spin, D.mrad) / gf_damp_sq_norm(qM, spin, D.mrad);
+        } else {
+            fr = gf_damp_sq(q, spin, D.rad);
+            frD = gf_damp_sq(qM, spin, D.mrad);
+        }
+    }
+    double g = reswidth * pow(q / q0, 2.0 * spin + 1) * fr / sqrt(s);
+    double cot_deltaB = (1.0 / (_a * q)) + 0.5 * _r * q;
+    double qcot_deltaB = (1.0 / _a) + 0.5 * _r * q * q;
+    double2 expi2deltaB = gf_cdiv(make_double2(qcot_deltaB, q), make_double2(qcot_deltaB, -q));
+    double2 resT = gf_cscale(make_double2(cos(_phiR + 2 * _phiB), sin(_phiR + 2 * _phiB)), _R);
+    double2 prop = gf_cdiv(make_double2(1, 0), make_double2(resmass - s, sqrt(resmass) * g));
+    resT = gf_cmul(resT, gf_cmul(gf_cscale(prop, resmass * reswidth / q0), expi2deltaB));
+    double2 bg = gf_cscale(gf_cscale(gf_cscale(make_double2(cos(_phiB), sin(_phiB)), _B), cos(_phiB) + cot_deltaB * sin(_phiB)), sqrt(s));
+    bg = gf_cdiv(bg, make_double2(qcot_deltaB, -q));
+    resT.x += bg.x;
+    resT.y += bg.y;
+    resT = gf_cscale(resT, sqrt(fr));
+    resT = gf_cscale(resT, sqrt(frD));
+    resT = gf_cscale(resT, gf_spin3(spin, D, m12, m13, m23, cyc));
+    return resT;
+}
+// FLATTE.cu:18-74 (coupled pi pi / K K channels; symmDP adds the m12 <-> m13 swapped term)
+__device__ inline double2 gf_res_flatte(const double *p, int cyc, int doSwap, double m12, double m13, double m23) {
+    const double resmass = p[0], g1 = p[1], g2 = p[2] * g1;
+    const double pipmass = 0.13957018, pi0mass = 0.1349766, kpmass = 0.493677, k0mass = 0.497614;
+    const double twopimasssq = 4 * pipmass * pipmass, twopi0masssq = 4 * pi0mass * pi0mass;
+    const double twokmasssq = 4 * kpmass * kpmass, twok0masssq = 4 * k0mass * k0mass;
+    double2 ret = make_double2(0.0, 0.0);
+    for(int i = 0; i < 1 + doSwap; i++) {
+        double rpr = 0, rpi = 0, rkr = 0, rki = 0;
+        double s = cyc == GF_PAIR_12 ? m12 : (cyc == GF_PAIR_13 ? m13 : m23);
+        if(s >= twopimasssq) rpr += (2. / 3) * sqrt(1 - twopimasssq / s); else rpi += (2. / 3) * sqrt(-1 + twopimasssq / s);
+        if(s >= twopi0masssq) rpr += (1. / 3) * sqrt(1 - twopi0masssq / s); else rpi += (1. / 3) * sqrt(-1 + twopi0masssq / s);
+        if(s >= twokmasssq) rkr += 0.5 * sqrt(1 - twokmasssq / s); else rki += 0.5 * sqrt(-1 + twokmasssq / s);
+        if(s >= twok0masssq) rkr += 0.5 * sqrt(1 - twok0masssq / s); else rki += 0.5 * sqrt(-1 + twok0masssq / s);
+        double A = (resmass * resmass - s) + resmass * (rpi * g1 + rki * g2);
+        double B = resmass * (rpr * g1 + rkr * g2);
+        double C = 1.0 / (A * A + B * B);
+        ret.x += A * C;
+        ret.y += B * C;
+        if(doSwap) {
+            double t = m12;
+            m12 = m13;
+            m13 = t;
+        }
+    }
+    return ret;
+}
+
 // Dispatch on the resonance record (Amp3Body_TD.cu:36-39 getResonanceAmplitude)
 __device__ inline double2 gf_resonance(const gf_node &nd, const double *params, const double *consts,
                                        const gf_decay3 &D, double m12, double m13, double m23) {
@@ -195,6 +273,8 @@ __device__ inline double2 gf_resonance(const gf_node &nd, const double *params, 
     case GF_OP_RES_GS: return gf_res_gs(p[0], p[1], (int)c[0], (int)c[1], c[2] != 0.0, D, m12, m13, m23);
     case GF_OP_RES_NONRES: return make_double2(1.0, 0.0); // NonRes.cu:8-11
     case GF_OP_RES_GAUSS: return gf_res_gauss(p[0], p[1], (int)c[0], m12, m13, m23);
+    case GF_OP_RES_LASS: return gf_res_lass(p, (int)c[0], (int)c[1], c[2] != 0.0, D, m12, m13, m23);
+    case GF_OP_RES_FLATTE: return gf_res_flatte(p, (int)c[0], (int)c[1], m12, m13, m23);
     default: return make_double2(0.0, 0.0);
     }
 }
@@ -241,9 +321,8 @@ __device__ inline void gf_res_prepare(gf_res_inv &R, const gf_node &nd, const do
     R.op = nd.op;
     R.spin = 0; R.cyc = 0; R.norm = 0; R.nterm = 1; R.pad = 0;
     R.mass = R.width = R.mass2 = 0;
-    if(nd.op == GF_OP_RES_NONRES) return;
+    if(nd.op != GF_OP_RES_RBW && nd.op != GF_OP_RES_RBW_SYM) return; // only plain RBWs take the shared-work path
     R.mass = p[0]; R.width = p[1]; R.mass2 = p[0] * p[0];
-    if(nd.op == GF_OP_RES_GAUSS) { R.cyc = (int)c[0]; return; }
     R.spin = (int)c[0]; R.cyc = (int)c[1]; R.norm = c[2] != 0.0;
     R.nterm = nd.op == GF_OP_RES_RBW_SYM ? 2 : 1;
     int cyc = R.cyc;
@@ -296,8 +375,8 @@ __device__ inline double2 gf_rbw_term(const gf_res_inv &R, const gf_pair_inv &P,
     double fr = 1, frM = 1;
     if(spin != 0) {
         if(R.norm) {
-            fr = R.frn[0] * (spin == 1 ? P.bw1 : P.bw2);
-            frM = R.frMn[0] * (spin == 1 ? P.bwM1 : P.bwM2);
+            fr = R.frn[0] * (spin == 2 ? P.bw2 : P.bw1); // as Resonance.cu:91-100: anything but spin 2 takes the spin-1 form
+            frM = R.frMn[0] * (spin == 2 ? P.bwM2 : P.bwM1);
         } else {
             fr = gf_damp_sq(P.q, spin, D.rad);
             frM = gf_damp_sq(P.qMp, spin, D.mrad);
@@ -306,7 +385,7 @@ __device__ inline double2 gf_rbw_term(const gf_res_inv &R, const gf_pair_inv &P,
     double A = R.mass2 - P.s;
     double B = R.mw * gf_pow_odd(P.q * R.inv_q0, spin) * fr * P.inv_rs;
     double C = 1.0 / (A * A + B * B);
-    double f = sqrt(fr * frM) * (spin == 0 ? 1.0 : (spin == 1 ? P.z1 : P.z2)) * C;
+    double f = sqrt(fr * frM) * (spin == 0 ? 1.0 : (spin == 2 ? P.z2 : P.z1)) * C;
     return make_double2(A * f, B * f);
 }
 #define GF_MAX_RES 64

@@ -56,6 +56,15 @@ class Gauss : public ResonancePdf { // resonances/Gauss.cu:35-46
   public:
     Gauss(std::string name, Variable ar, Variable ai, Variable mean, Variable sigma, unsigned int cyc);
 };
+class LASS : public ResonancePdf { // resonances/LASS.cu:123-153
+  public:
+    LASS(std::string name, Variable ar, Variable ai, Variable mass, Variable width, Variable _a, Variable _r, Variable _R,
+         Variable _phiR, Variable _B, Variable _phiB, unsigned int sp, unsigned int cyc, bool norm = true);
+};
+class FLATTE : public ResonancePdf { // resonances/FLATTE.cu:80-97
+  public:
+    FLATTE(std::string name, Variable ar, Variable ai, Variable mean, Variable g1, Variable rg2og1, unsigned int cyc, bool symmDP);
+};
 } // namespace Resonances
 
 struct DecayInfo3 { // DalitzPlotHelpers.h:83-92

@@ -58,6 +58,24 @@ Gauss::Gauss(std::string name, Variable ar, Variable ai, Variable mass, Variable
     registerConstant(cyc);
     registerFunction("ptr_to_GAUSSIAN", GF_OP_RES_GAUSS);
 }
+LASS::LASS(std::string name, Variable ar, Variable ai, Variable mass, Variable width, Variable _a, Variable _r, Variable _R,
+           Variable _phiR, Variable _B, Variable _phiB, unsigned int sp, unsigned int cyc, bool norm)
+    : ResonancePdf("LASS", name, ar, ai) {
+    for(const Variable &v : {mass, width, _a, _r, _R, _phiR, _B, _phiB}) registerParameter(v);
+    registerConstant(sp);
+    registerConstant(cyc);
+    registerConstant(norm);
+    registerFunction("ptr_to_LASS", GF_OP_RES_LASS);
+}
+FLATTE::FLATTE(std::string name, Variable ar, Variable ai, Variable mean, Variable g1, Variable rg2og1, unsigned int cyc, bool symmDP)
+    : ResonancePdf("FLATTE", name, ar, ai) {
+    registerParameter(mean);
+    registerParameter(g1);
+    registerParameter(rg2og1);
+    registerConstant(cyc);
+    registerConstant(symmDP);
+    registerFunction("ptr_to_FLATTE", GF_OP_RES_FLATTE);
+}
 } // namespace Resonances
 
 Amp3Body::Amp3Body(std::string n, Observable m12, Observable m13, EventNumber eventNumber, DecayInfo3 decay, GooPdf *eff)

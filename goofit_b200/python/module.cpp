@@ -304,6 +304,14 @@ PYBIND11_MODULE(_goofit, m) {
         .def(py::init<std::string, Variable, Variable>(), "name"_a, "ar"_a, "ai"_a);
     py::class_<Resonances::Gauss, ResonancePdf>(mres, "Gauss")
         .def(py::init<std::string, Variable, Variable, Variable, Variable, unsigned int>(), "name"_a, "ar"_a, "ai"_a, "mean"_a, "sigma"_a, "cyc"_a);
+    py::class_<Resonances::LASS, ResonancePdf>(mres, "LASS")
+        .def(py::init<std::string, Variable, Variable, Variable, Variable, Variable, Variable, Variable, Variable, Variable, Variable,
+                      unsigned int, unsigned int, bool>(),
+             "name"_a, "ar"_a, "ai"_a, "mass"_a, "width"_a, "_a"_a, "_r"_a, "_R"_a, "_phiR"_a, "_B"_a, "_phiB"_a, "sp"_a, "cyc"_a,
+             "norm"_a = true);
+    py::class_<Resonances::FLATTE, ResonancePdf>(mres, "FLATTE")
+        .def(py::init<std::string, Variable, Variable, Variable, Variable, Variable, unsigned int, bool>(), "name"_a, "ar"_a, "ai"_a,
+             "mean"_a, "g1"_a, "rg2og1"_a, "cyc"_a, "symmDP"_a);
     py::class_<DecayInfo3>(m, "DecayInfo3")
         .def(py::init<>())
         .def_readwrite("motherMass", &DecayInfo3::motherMass)

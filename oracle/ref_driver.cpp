@@ -34,6 +34,8 @@
 #include <mcbooster/Generate.h>
 #include <mcbooster/EvaluateArray.h>
 #include <goofit/PDFs/physics/ResonancePdf.h>
+#include <goofit/PDFs/physics/resonances/FLATTE.h>
+#include <goofit/PDFs/physics/resonances/LASS.h>
 #include <goofit/BinnedDataSet.h>
 #include <goofit/FitControl.h>
 #include <goofit/UnbinnedDataSet.h>
@@ -445,6 +447,80 @@ static void case_dalitz() {
     s->updateVariable(M->masses[0], 0.77); s->updateVariable(M->widths[9], 0.05); s->updateParameters();
     put("dalitz.nll_mass_moved", s->calculateNLL());
     put("dalitz.integral_mass_moved", 1.0 / s->getNormalization());
+}
+
+// ---- the other three-body resonance shapes: LASS, FLATTE (with and without the m12<->m13 swap), GS, Gauss, symmetrised RBW ----
+// (resonances/{LASS,FLATTE,GS,Gauss,RBW}.cu), on a K K pi-like Dalitz plot with every shape parameter free
+static void case_zoo3() {
+    Observable m12{"m12", 0, 3}, m13{"m13", 0, 3};
+    EventNumber eventNumber{"eventNumber"};
+    m12.setNumBins(90);
+    m13.setNumBins(90);
+    DecayInfo3 info;
+    info.motherMass = _mD0; info.daug1Mass = piZeroMass; info.daug2Mass = piPlusMass; info.daug3Mass = piPlusMass;
+    info.meson_radius = 1.5; info.mother_meson_radius = 5.0;
+    std::vector<Variable> pars;
+    auto F = [&](const char *n, double v, double lo, double hi) {
+        Variable x(n, v, 0.001, lo, hi);
+        pars.push_back(x);
+        return x;
+    };
+    Variable one("one", 1), zero("zero", 0);
+    info.resonances = {
+        new Resonances::LASS("lass", Variable("lass_r", 0.8), Variable("lass_i", -0.3), F("lass_m", 1.425, 1.3, 1.5), F("lass_w", 0.27, 0.1, 0.4),
+                             F("lass_a", 2.07, 1, 3), F("lass_r_", 3.32, 2, 4), F("lass_R", 1.0, 0.5, 1.5), F("lass_phiR", -1.9, -3, 3),
+                             F("lass_B", 0.96, 0.5, 1.5), F("lass_phiB", 0.0017, -1, 1), 0, PAIR_12, true),
+        new Resonances::LASS("lass1", Variable("lass1_r", 0.2), Variable("lass1_i", 0.1), F("lass1_m", 0.896, 0.8, 1.0), F("lass1_w", 0.05, 0.01, 0.1),
+                             F("lass1_a", 1.8, 1, 3), F("lass1_r_", 1.76, 1, 4), F("lass1_R", 1.0, 0.5, 1.5), F("lass1_phiR", 0.3, -3, 3),
+                             F("lass1_B", 0.6, 0.1, 1.5), F("lass1_phiB", -0.2, -1, 1), 1, PAIR_13, false),
+        new Resonances::FLATTE("f0", Variable("f0_r", 0.5), Variable("f0_i", 0.4), F("f0_m", 0.965, 0.9, 1.0), F("f0_g1", 0.165, 0.1, 0.3),
+                               F("f0_rg", 4.21, 3, 5), PAIR_23, false),
+        new Resonances::FLATTE("f0s", Variable("f0s_r", -0.3), Variable("f0s_i", 0.2), F("f0s_m", 0.98, 0.9, 1.05), F("f0s_g1", 0.2, 0.1, 0.3),
+                               F("f0s_rg", 3.5, 3, 5), PAIR_12, true),
+        new Resonances::GS("rho_gs", Variable("gs_r", 1.0), Variable("gs_i", 0.0), F("gs_m", 0.7758, 0.7, 0.85), F("gs_w", 0.1503, 0.1, 0.2), 1, PAIR_23),
+        new Resonances::Gauss("gauss", Variable("ga_r", 0.1), Variable("ga_i", 0.05), F("ga_m", 1.2, 1.0, 1.4), F("ga_s", 0.1, 0.05, 0.3), PAIR_13),
+        new Resonances::RBW("rho_sym", Variable("rs_r", 0.3), Variable("rs_i", -0.2), F("rs_m", 0.7758, 0.7, 0.85), F("rs_w", 0.15, 0.1, 0.2), 1, PAIR_12,
+                            true, true),
+        new Resonances::RBW("f2_plain", Variable("f2_r", 0.2), Variable("f2_i", 0.3), F("f2_m", 1.2754, 1.2, 1.35), F("f2_w", 0.1851, 0.1, 0.3), 2, PAIR_23,
+                            false),
+    };
+    std::vector<Observable> obs = {m12, m13};
+    auto *eff = new PolynomialPdf("constantEff", obs, std::vector<Variable>{one}, std::vector<Variable>{zero, zero}, 0);
+    auto *s = new Amp3Body("zoo3", m12, m13, eventNumber, info, eff);
+    UnbinnedDataSet d({m12, m13, eventNumber});
+    std::mt19937_64 gen(77);
+    std::uniform_real_distribution<double> u(0, 3);
+    while(d.getNumEvents() < 500) {
+        double a = u(gen), b = u(gen);
+        if(!inDalitz(a, b, _mD0, piZeroMass, piPlusMass, piPlusMass)) continue;
+        m12.setValue(a); m13.setValue(b); eventNumber.setValue(d.getNumEvents());
+        d.addEvent();
+    }
+    save_npy("zoo3.m12", column(d, m12));
+    save_npy("zoo3.m13", column(d, m13));
+    s->setData(&d);
+    s->setDataSize(d.getNumEvents());
+    put("zoo3.nll", s->calculateNLL());
+    put("zoo3.integral", 1.0 / s->getNormalization());
+    std::vector<double> waves;
+    for(size_t i = 0; i < info.resonances.size(); i++) {
+        auto w = s->getCachedWave(i);
+        for(auto &c : w) { waves.push_back(c.real()); waves.push_back(c.imag()); }
+    }
+    save_npy("zoo3.waves", waves.data(), info.resonances.size(), 2 * d.getNumEvents());
+    // the LASS effective range, the FLATTE g1 coupling and the GS mass move
+    for(auto &v : pars) v.setChanged(false);
+    // (looked up by name: the order in which F() ran inside each constructor call is the compiler's choice)
+    auto P = [&](const char *n) -> Variable & {
+        for(auto &v : pars)
+            if(v.getName() == n) return v;
+        throw std::runtime_error(n);
+    };
+    P("lass_r_").setChanged(true); P("f0_g1").setChanged(true); P("gs_m").setChanged(true);
+    s->updateVariable(P("lass_r_"), 3.1); s->updateVariable(P("f0_g1"), 0.18); s->updateVariable(P("gs_m"), 0.79);
+    s->updateParameters();
+    put("zoo3.nll_moved", s->calculateNLL());
+    put("zoo3.integral_moved", 1.0 / s->getNormalization());
 }
 
 // accept-reject toy from the model itself, then a full Minuit2 fit with the reference's FitManager
@@ -977,6 +1053,7 @@ int main(int argc, char **argv) {
             if(only == "all" || only == "basic") case_basic();
             if(only == "all" || only == "binned") case_binned();
             if(only == "all" || only == "dalitz") case_dalitz();
+            if(only == "all" || only == "zoo3") case_zoo3();
             if(only == "all" || only == "dalitzfit") case_dalitz_fit();
             if(only == "all" || only == "dp4") case_dp4();
             if(only == "all" || only == "dp4fit") case_dp4_fit();

@@ -88,6 +88,56 @@ class Dalitz:
         return dataset_from_columns([self.m12, self.m13, self.evt], [m12, m13, np.arange(n, dtype=np.float64)])
 
 
+class Zoo3:
+    """The other three-body shapes on one Dalitz plot: LASS (spin 0 and 1), FLATTE (plain and swapped), GS, Gauss, symmetrised RBW, spin-2 RBW;
+    every shape parameter free (mirrors oracle/ref_driver.cpp case_zoo3)."""
+
+    def __init__(self, grid=90):
+        k = self.keep = Keep()
+        self.m12 = gf.Observable("m12", 0, 3)
+        self.m13 = gf.Observable("m13", 0, 3)
+        self.evt = gf.EventNumber("eventNumber")
+        self.m12.numbins = grid
+        self.m13.numbins = grid
+        d = self.info = gf.DecayInfo3()
+        d.motherMass, d.daug1Mass, d.daug2Mass, d.daug3Mass = MD0, PI0, PIP, PIP
+        d.meson_radius, d.mother_meson_radius = 1.5, 5.0
+        V = gf.Variable
+        self.pars = []
+
+        def F(n, v, lo, hi):
+            x = V(n, v, 0.001, lo, hi)
+            self.pars.append(x)
+            return x
+
+        P12, P13, P23 = 0, 1, 2
+        R = gf.Resonances
+        self.resonances = [
+            R.LASS("lass", V("lass_r", 0.8), V("lass_i", -0.3), F("lass_m", 1.425, 1.3, 1.5), F("lass_w", 0.27, 0.1, 0.4), F("lass_a", 2.07, 1, 3),
+                   F("lass_r_", 3.32, 2, 4), F("lass_R", 1.0, 0.5, 1.5), F("lass_phiR", -1.9, -3, 3), F("lass_B", 0.96, 0.5, 1.5),
+                   F("lass_phiB", 0.0017, -1, 1), 0, P12, True),
+            R.LASS("lass1", V("lass1_r", 0.2), V("lass1_i", 0.1), F("lass1_m", 0.896, 0.8, 1.0), F("lass1_w", 0.05, 0.01, 0.1), F("lass1_a", 1.8, 1, 3),
+                   F("lass1_r_", 1.76, 1, 4), F("lass1_R", 1.0, 0.5, 1.5), F("lass1_phiR", 0.3, -3, 3), F("lass1_B", 0.6, 0.1, 1.5),
+                   F("lass1_phiB", -0.2, -1, 1), 1, P13, False),
+            R.FLATTE("f0", V("f0_r", 0.5), V("f0_i", 0.4), F("f0_m", 0.965, 0.9, 1.0), F("f0_g1", 0.165, 0.1, 0.3), F("f0_rg", 4.21, 3, 5), P23, False),
+            R.FLATTE("f0s", V("f0s_r", -0.3), V("f0s_i", 0.2), F("f0s_m", 0.98, 0.9, 1.05), F("f0s_g1", 0.2, 0.1, 0.3), F("f0s_rg", 3.5, 3, 5), P12,
+                     True),
+            R.GS("rho_gs", V("gs_r", 1.0), V("gs_i", 0.0), F("gs_m", 0.7758, 0.7, 0.85), F("gs_w", 0.1503, 0.1, 0.2), 1, P23),
+            R.Gauss("gauss", V("ga_r", 0.1), V("ga_i", 0.05), F("ga_m", 1.2, 1.0, 1.4), F("ga_s", 0.1, 0.05, 0.3), P13),
+            R.RBW("rho_sym", V("rs_r", 0.3), V("rs_i", -0.2), F("rs_m", 0.7758, 0.7, 0.85), F("rs_w", 0.15, 0.1, 0.2), 1, P12, True, True),
+            R.RBW("f2_plain", V("f2_r", 0.2), V("f2_i", 0.3), F("f2_m", 1.2754, 1.2, 1.35), F("f2_w", 0.1851, 0.1, 0.3), 2, P23, False),
+        ]
+        for r in self.resonances:
+            d.add_resonance(k(r))
+        one, zero = V("one", 1), V("zero", 0)
+        self.eff = k(gf.PolynomialPdf("constantEff", [self.m12, self.m13], [one], [zero, zero], 0))
+        self.signal = gf.Amp3Body("zoo3", self.m12, self.m13, self.evt, d, self.eff)
+
+    def dataset(self, m12, m13):
+        n = len(m12)
+        return dataset_from_columns([self.m12, self.m13, self.evt], [m12, m13, np.arange(n, dtype=np.float64)])
+
+
 def in_dalitz(m12, m13):
     """vectorised Dalitz boundary for the D0 -> pi0 pi+ pi+ kinematics above (DalitzPlotHelpers.cu:14-59)"""
     bigM, dm1, dm2, dm3 = MD0, PI0, PIP, PIP

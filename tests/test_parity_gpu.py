@@ -8,7 +8,7 @@ import numpy as np
 import pytest
 
 import goofit_b200 as gf
-from models import Dalitz, dataset_from_columns
+from models import Dalitz, Zoo3, dataset_from_columns
 
 pytestmark = pytest.mark.gpu
 
@@ -219,6 +219,33 @@ def test_dalitz_values(golden):
     s.updateParameters()
     assert rel(s.calculateNLL(), golden["dalitz.nll_mass_moved"]) < RTOL_NLL
     assert rel(1.0 / s.getNormalization(), golden["dalitz.integral_mass_moved"]) < 1e-12
+
+
+def test_zoo3_resonance_shapes(golden):
+    """LASS / FLATTE / GS / Gauss / symmetrised and unnormalised RBW against the reference's resonances/*.cu"""
+    M = Zoo3(grid=90)
+    d = M.dataset(golden.arr("zoo3.m12"), golden.arr("zoo3.m13"))
+    s = M.signal
+    s.setData(d)
+    s.setDataSize(len(d))
+    nll = s.calculateNLL()
+    ref = golden.arr("zoo3.waves")
+    for i in range(len(M.resonances)):
+        w = np.asarray(s.getCachedWave(i))
+        r = ref[i, 0::2] + 1j * ref[i, 1::2]
+        scale = np.maximum(np.abs(r), 1e-300)
+        assert np.max(np.abs(w - r) / scale) < 1e-11, (i, np.max(np.abs(w - r) / scale))
+    assert rel(1.0 / s.getNormalization(), golden["zoo3.integral"]) < 1e-12
+    assert rel(nll, golden["zoo3.nll"]) < RTOL_NLL
+    for v in M.pars:
+        v.changed = False
+    byname = {v.name: v for v in M.pars}
+    for n, v in (("lass_r_", 3.1), ("f0_g1", 0.18), ("gs_m", 0.79)):  # LASS effective range, FLATTE coupling, GS mass
+        byname[n].changed = True
+        s.updateVariable(byname[n], v)
+    s.updateParameters()
+    assert rel(s.calculateNLL(), golden["zoo3.nll_moved"]) < RTOL_NLL
+    assert rel(1.0 / s.getNormalization(), golden["zoo3.integral_moved"]) < 1e-12
 
 
 def test_dalitz_fit_matches_reference(golden):
