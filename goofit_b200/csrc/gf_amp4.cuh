@@ -6,7 +6,7 @@
 //   spin factors              src/PDFs/physics/SpinFactors.cu:83-568, detail/SpinHelper.h
 #pragma once
 
-enum gf_ls_kind { GF_LS_RBW = 0, GF_LS_SBW, GF_LS_LASS, GF_LS_BUGG, GF_LS_BUGG3, GF_LS_ONE };
+enum gf_ls_kind { GF_LS_RBW = 0, GF_LS_SBW, GF_LS_LASS, GF_LS_BUGG, GF_LS_BUGG3, GF_LS_ONE, GF_LS_NONRES, GF_LS_FLATTE, GF_LS_GLASS, GF_LS_FOCUS };
 // same order as the reference's SF_4Body enum (SpinFactors.h:18-35)
 enum gf_sf_kind {
     GF_SF_DtoPP1_PtoSP2_StoP3P4 = 0, GF_SF_DtoPP1_PtoVP2_VtoP3P4, GF_SF_DtoV1V2_S, GF_SF_DtoV1V2_P, GF_SF_DtoV1V2_D,
@@ -277,6 +277,83 @@ __device__ inline gf_cplx gf_ls_bugg3(double Mpair) {
     gf_cplx den = gf_c(M * M - s - adlerZero * g1sq * z, 0) - gf_c(0, 1) * Gamma_tot;
     return 1.0 / den;
 }
+// NonRes.cu:8-25 : the Blatt-Weisskopf barrier alone
+__device__ inline gf_cplx gf_ls_nonres(double Mpair, double m1, double m2, int orbital, double meson_radius) {
+    double M2 = Mpair * Mpair;
+    double mpsq = (m1 + m2) * (m1 + m2), mmsq = (m1 - m2) * (m1 - m2);
+    double pABSq = (M2 - mpsq) * (M2 - mmsq) / (4 * M2);
+    return gf_c(sqrt(gf_bl2(pABSq * meson_radius * meson_radius, orbital)), 0.0);
+}
+// Flatte.cu:8-12 : sqrt(1 - (2 m0/m)^2), continued below threshold
+__device__ inline gf_cplx gf_flatte_asqrt(double m0, double m) {
+    double a2 = 1 - (2 * m0 / m) * (2 * m0 / m);
+    return a2 > 0 ? gf_c(sqrt(a2), 0) : gf_c(0, sqrt(-a2));
+}
+// Flatte.cu:14-55 : f0(980) with the couplings hard-wired upstream (gPi 0.165, gK/gPi 4.21)
+__device__ inline gf_cplx gf_ls_flatte(double Mpair, double m1, double m2, double resmass, int orbital, double meson_radius) {
+    double rMass2 = Mpair * Mpair;
+    const double gPi = .165, gK = gPi * 4.21, mPi0 = .1349766, mK0 = .497648;
+    double mpsq = (m1 + m2) * (m1 + m2), mmsq = (m1 - m2) * (m1 - m2);
+    double pABSq = (rMass2 - mpsq) * (rMass2 - mmsq) / (4 * rMass2);
+    gf_cplx Gpipi = (1. / 3.) * gf_flatte_asqrt(mPi0, Mpair) + (2. / 3.) * gf_flatte_asqrt(GF_MPIPLUS, Mpair);
+    gf_cplx GKK = (1. / 2.) * gf_flatte_asqrt(mK0, Mpair) + (1. / 2.) * gf_flatte_asqrt(GF_MKPLUS, Mpair);
+    gf_cplx width = gPi * Gpipi + gK * GKK;
+    double fr = gf_bl2(pABSq * meson_radius * meson_radius, orbital);
+    return sqrt(fr) / (gf_c(resmass * resmass - rMass2, 0) - gf_c(0, resmass) * width);
+}
+// GLASS.cu:12-60 : generalised LASS; params mass,width,a,r,phiF,phiR,F (R fixed to 1 upstream)
+__device__ inline gf_cplx gf_ls_glass(double Mpair, double m1, double m2, const double *p, int orbital, double meson_radius) {
+    double resmass = p[0], reswidth = p[1], a = p[2], r = p[3], phiF = p[4], phiR = p[5], F = p[6];
+    double rMass2 = Mpair * Mpair;
+    double mpsq = (m1 + m2) * (m1 + m2), mmsq = (m1 - m2) * (m1 - m2);
+    double num = (rMass2 - mpsq) * (rMass2 - mmsq);
+    double num2 = (resmass * resmass - mpsq) * (resmass * resmass - mmsq);
+    double pABSq = num / (4 * rMass2);
+    double prSq = fabs(num2 / (4 * resmass * resmass));
+    double pratio = sqrt(pABSq / prSq);
+    double pr2J1 = 1;
+    for(int i = 0; i < 2 * orbital + 1; i++) pr2J1 *= pratio;
+    double mratio = resmass / Mpair;
+    double r2 = meson_radius * meson_radius;
+    double thisFR = gf_bl_prime(pABSq * r2, prSq * r2, orbital);
+    double GofM = reswidth * pr2J1 * mratio * thisFR;
+    double y = 2.0 * a * sqrt(pABSq);
+    double x = 2.0 + a * r * pABSq;
+    double scattphase = phiF + atan(y / x);
+    double resphase = phiR + atan(resmass * GofM / (resmass * resmass - rMass2));
+    double rho = 1.0 / sqrt(pABSq / rMass2);
+    double ss, cs, s2, c2;
+    sincos(scattphase, &ss, &cs);
+    sincos(resphase + 2 * scattphase, &s2, &c2);
+    return ((F * ss) * gf_c(cs, ss) + (1.0 * sin(resphase)) * gf_c(c2, s2)) * rho;
+}
+// FOCUS.cu:12-17 : two-body phase space, continued below threshold (principal square root of a real number)
+__device__ inline gf_cplx gf_focus_phsp(double s, double m0, double m1) {
+    double mp = m0 + m1, mm = m0 - m1;
+    double a2 = (1.0 - mp * mp / s) * (1.0 - mm * mm / s);
+    return a2 >= 0 ? gf_c(sqrt(a2), 0) : gf_c(0, sqrt(-a2));
+}
+// FOCUS.cu:19-78 : K pi S-wave K-matrix; mod 0 = Kpi, 1 = KEta, anything else = I 3/2
+#define GF_METAP 0.96778
+__device__ inline gf_cplx gf_ls_focus(double Mpair, int mod) {
+    const gf_cplx I = gf_c(0, 1);
+    double s = Mpair * Mpair;
+    const double sNorm = GF_MKPLUS * GF_MKPLUS + GF_MPIPLUS * GF_MPIPLUS, s12 = 0.23, s32 = 0.27;
+    double I12 = (s - s12) / sNorm, I32 = (s - s32) / sNorm;
+    gf_cplx rho1 = gf_focus_phsp(s, GF_MKPLUS, GF_MPIPLUS), rho2 = gf_focus_phsp(s, GF_MKPLUS, GF_METAP);
+    const double pmass = 1.7919, g0 = 0.31072, g1 = -0.02323;
+    double X = s / sNorm - 1;
+    double k00 = g0 * g0 / (pmass - s) + 0.79299 - 0.15099 * X + 0.00811 * (X * X);
+    double k11 = g1 * g1 / (pmass - s) + 0.17054 - 0.0219 * X + 0.00085655 * (X * X);
+    double k01 = g0 * g1 / (pmass - s) + 0.15040 - 0.038266 * X + 0.0022596 * (X * X);
+    double K11 = I12 * k00, K12 = I12 * k01, K22 = I12 * k11;
+    double K32 = I32 * (-0.22147 + 0.026637 * X - 0.00092057 * (X * X));
+    double detK = K11 * K22 - K12 * K12;
+    gf_cplx del = gf_c(1., 0) - rho1 * rho2 * detK - I * (rho1 * K11 + rho2 * K22);
+    if(mod == 0) return (gf_c(K11, 0) - I * rho2 * detK) / del;
+    if(mod == 1) return K12 / del;
+    return 1. / (gf_c(1., 0) - I * rho2 * K32);
+}
 // dispatch on the lineshape record: params mass,width ; consts Mpair,L,FF,radius ; ints[0] kind
 __device__ inline gf_cplx gf_lineshape(int kind, const double *p, const double *c, double Mpair, double d1, double d2) {
     switch(kind) {
@@ -285,6 +362,10 @@ __device__ inline gf_cplx gf_lineshape(int kind, const double *p, const double *
     case GF_LS_LASS: return gf_ls_lass(Mpair, d1, d2, p[0], p[1], (int)c[1], (int)c[2], c[3]);
     case GF_LS_BUGG: return gf_ls_bugg(Mpair);
     case GF_LS_BUGG3: return gf_ls_bugg3(Mpair);
+    case GF_LS_NONRES: return gf_ls_nonres(Mpair, d1, d2, (int)c[1], c[3]);
+    case GF_LS_FLATTE: return gf_ls_flatte(Mpair, d1, d2, p[0], (int)c[1], c[3]);
+    case GF_LS_GLASS: return gf_ls_glass(Mpair, d1, d2, p, (int)c[1], c[3]);
+    case GF_LS_FOCUS: return gf_ls_focus(Mpair, (int)c[4]);
     default: return gf_c(1.0, 0.0);
     }
 }

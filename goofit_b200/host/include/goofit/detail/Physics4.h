@@ -45,7 +45,21 @@ GOOFIT_B200_LS(SBW)   // lineshapes/BW.cu:172-186
 GOOFIT_B200_LS(LASS)  // lineshapes/BW.cu:190-206
 GOOFIT_B200_LS(Bugg)  // lineshapes/Bugg.cu:133-146 (mass and width are accepted and ignored, as upstream)
 GOOFIT_B200_LS(Bugg3) // lineshapes/Bugg.cu:148-160
+GOOFIT_B200_LS(One)    // lineshapes/One.cu:8-24 (always 1; mass, width ignored)
+GOOFIT_B200_LS(NonRes) // lineshapes/NonRes.cu:8-40 (barrier factor only; mass, width ignored)
+GOOFIT_B200_LS(Flatte) // lineshapes/Flatte.cu:14-67 (mass floats; width ignored, couplings hard-wired upstream)
 #undef GOOFIT_B200_LS
+class GLASS final : public Lineshape { // lineshapes/GLASS.cu:64-88 ; AdditionalVars = a, r, phiF, phiR, F
+  public:
+    GLASS(std::string name, Variable mass, Variable width, unsigned int L, unsigned int Mpair, FF FormFac, fptype radius,
+          std::vector<Variable> AdditionalVars);
+};
+class FOCUS final : public Lineshape { // lineshapes/FOCUS.cu:80-95
+  public:
+    enum class Mod { Kpi = 0, KEta, I32 };
+    FOCUS(std::string name, Mod mod, Variable mass, Variable width, unsigned int L, unsigned int Mpair, FF FormFac = FF::BL_Prime,
+          fptype radius = 1.5);
+};
 } // namespace Lineshapes
 
 enum class SF_4Body { // SpinFactors.h:18-35

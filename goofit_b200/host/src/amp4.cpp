@@ -23,7 +23,7 @@ bool Lineshape::isEqualByValue(const Lineshape &o) const { // Lineshape.cu:37-41
            && areParamsandConstantsEqualByVal(o);
 }
 namespace Lineshapes {
-// kinds: gf_ls_kind in csrc/gf_amp4.cuh {RBW, SBW, LASS, BUGG, BUGG3}
+// kinds: gf_ls_kind in csrc/gf_amp4.cuh {RBW, SBW, LASS, BUGG, BUGG3, ONE, NONRES, FLATTE, GLASS, FOCUS}
 #define GOOFIT_B200_LS_BW(NAME, KIND)                                                                                  \
     NAME::NAME(std::string name, Variable mass, Variable width, unsigned int L, unsigned int Mpair, FF FormFac, fptype radius) \
         : Lineshape(#NAME, name, L, Mpair, FormFac, radius, KIND) {                                                    \
@@ -41,6 +41,39 @@ Bugg::Bugg(std::string name, Variable, Variable, unsigned int L, unsigned int Mp
     : Lineshape("Bugg", name, L, Mpair, FormFac, radius, 3) {}
 Bugg3::Bugg3(std::string name, Variable, Variable, unsigned int L, unsigned int Mpair, FF FormFac, fptype radius)
     : Lineshape("Bugg3", name, L, Mpair, FormFac, radius, 4) {}
+// The shapes below keep the common constant block {Mpair, L, FormFac, radius} so the device dispatch reads one layout.
+#define GOOFIT_B200_LS_CONSTS                                                                                          \
+    registerConstant(L);                                                                                               \
+    registerConstant(static_cast<unsigned int>(FormFac));                                                              \
+    registerConstant(radius);
+One::One(std::string name, Variable, Variable, unsigned int L, unsigned int Mpair, FF FormFac, fptype radius)
+    : Lineshape("One", name, L, Mpair, FormFac, radius, 5) {}
+NonRes::NonRes(std::string name, Variable, Variable, unsigned int L, unsigned int Mpair, FF FormFac, fptype radius)
+    : Lineshape("NonRes", name, L, Mpair, FormFac, radius, 6) {
+    GOOFIT_B200_LS_CONSTS
+}
+Flatte::Flatte(std::string name, Variable mass, Variable, unsigned int L, unsigned int Mpair, FF FormFac, fptype radius)
+    : Lineshape("Flatte", name, L, Mpair, FormFac, radius, 7) {
+    registerParameter(mass);
+    GOOFIT_B200_LS_CONSTS
+}
+GLASS::GLASS(std::string name, Variable mass, Variable width, unsigned int L, unsigned int Mpair, FF FormFac, fptype radius,
+             std::vector<Variable> AdditionalVars)
+    : Lineshape("GLASS", name, L, Mpair, FormFac, radius, 8) {
+    if(5 != AdditionalVars.size())
+        throw GeneralError("It seems you forgot to provide the vector with the five necessary variables for GLASS, a, "
+                           "r, phiF, phiR and F (in that order)");
+    registerParameter(mass);
+    registerParameter(width);
+    for(auto &v : AdditionalVars) registerParameter(v);
+    GOOFIT_B200_LS_CONSTS
+}
+FOCUS::FOCUS(std::string name, Mod mod, Variable, Variable, unsigned int L, unsigned int Mpair, FF FormFac, fptype radius)
+    : Lineshape("FOCUS", name, L, Mpair, FormFac, radius, 9) {
+    GOOFIT_B200_LS_CONSTS
+    registerConstant(static_cast<unsigned int>(mod));
+}
+#undef GOOFIT_B200_LS_CONSTS
 } // namespace Lineshapes
 
 // ---- spin factors / amplitudes -------------------------------------------------------------------------------

@@ -33,6 +33,17 @@ void init_physics4(py::module &m) {
     bind_ls<Lineshapes::LASS>(mls, "LASS");
     bind_ls<Lineshapes::Bugg>(mls, "Bugg");
     bind_ls<Lineshapes::Bugg3>(mls, "Bugg3");
+    bind_ls<Lineshapes::One>(mls, "One");
+    bind_ls<Lineshapes::NonRes>(mls, "NonRes");
+    bind_ls<Lineshapes::Flatte>(mls, "Flatte");
+    py::class_<Lineshapes::GLASS, Lineshape>(mls, "GLASS")
+        .def(py::init<std::string, Variable, Variable, unsigned int, unsigned int, FF, fptype, std::vector<Variable>>(), "name"_a, "mass"_a,
+             "width"_a, "L"_a, "Mpair"_a, "FormFac"_a, "radius"_a, "AdditionalVars"_a);
+    py::class_<Lineshapes::FOCUS, Lineshape> focus(mls, "FOCUS");
+    py::enum_<Lineshapes::FOCUS::Mod>(focus, "Mod")
+        .value("Kpi", Lineshapes::FOCUS::Mod::Kpi).value("KEta", Lineshapes::FOCUS::Mod::KEta).value("I32", Lineshapes::FOCUS::Mod::I32);
+    focus.def(py::init<std::string, Lineshapes::FOCUS::Mod, Variable, Variable, unsigned int, unsigned int, FF, fptype>(), "name"_a, "mod"_a,
+              "mass"_a, "width"_a, "L"_a, "Mpair"_a, "FormFac"_a = FF::BL_Prime, "radius"_a = 1.5);
     py::enum_<SF_4Body>(m, "SF_4Body")
         .value("DtoPP1_PtoSP2_StoP3P4", SF_4Body::DtoPP1_PtoSP2_StoP3P4)
         .value("DtoPP1_PtoVP2_VtoP3P4", SF_4Body::DtoPP1_PtoVP2_VtoP3P4)

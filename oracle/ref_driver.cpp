@@ -26,6 +26,11 @@
 #include <goofit/PDFs/physics/TruthResolution.h>
 #include <goofit/PDFs/physics/Amplitude.h>
 #include <goofit/PDFs/physics/SpinFactors.h>
+#include <goofit/PDFs/physics/lineshapes/FOCUS.h>
+#include <goofit/PDFs/physics/lineshapes/Flatte.h>
+#include <goofit/PDFs/physics/lineshapes/GLASS.h>
+#include <goofit/PDFs/physics/lineshapes/NonRes.h>
+#include <goofit/PDFs/physics/lineshapes/One.h>
 #include <goofit/PDFs/physics/lineshapes/Bugg.h>
 #include <goofit/PDFs/physics/lineshapes/LASS.h>
 #include <goofit/PDFs/physics/lineshapes/RBW.h>
@@ -715,6 +720,99 @@ static void case_dp4() {
     put("dp4.integral_kstar_moved", 1.0 / dp->getNormalization());
 }
 
+// ---- the remaining four-body lineshapes (One, NonRes, Flatte, GLASS, FOCUS x3) and the nine spin factors DP4 does not use ----
+static void case_zoo4() {
+    Observable m12{"m12", 0, 3}, m34{"m34", 0, 3}, cos12{"cos12", -1, 1}, cos34{"m34", -1, 1}, phi{"phi", -3.5, 3.5};
+    EventNumber eventNumber{"eventNumber", 0, INT_MAX};
+    const fptype mD0 = 1.8645, piP = 0.13957018, Km = 0.493677;
+    DecayInfo4 info;
+    info.meson_radius    = 1.5;
+    info.particle_masses = {mD0, piP, piP, Km, piP};
+    std::vector<Variable> pars;
+    auto F = [&](const char *n, double v, double lo, double hi) {
+        Variable x(n, v, 0.001, lo, hi);
+        pars.push_back(x);
+        return x;
+    };
+    auto P = [&](const char *n) -> Variable & {
+        for(auto &v : pars)
+            if(v.getName() == n) return v;
+        throw std::runtime_error(n);
+    };
+    Variable dm = F("dummy_m", 1.0, 0.5, 1.5), dw = F("dummy_w", 0.1, 0.05, 0.5);
+    Variable k0m = F("K0s1430_m", 1.425, 1.3, 1.5), k0w = F("K0s1430_w", 0.27, 0.1, 0.4);
+    Variable ga = F("glass_a", 2.07, 1, 3), gr = F("glass_r", 3.32, 2, 4), gphiF = F("glass_phiF", 0.2, -1, 1);
+    Variable gphiR = F("glass_phiR", -0.3, -1, 1), gF = F("glass_F", 0.9, 0.5, 1.5);
+    Variable f0m = F("f0_m", 0.965, 0.9, 1.0);
+    Variable rhoM = F("rho_m", 0.77526, 0.6, 0.9), rhoW = F("rho_w", 0.1478, 0.05, 0.3);
+    Variable ksM = F("Kstar_m", 0.89581, 0.8, 1.0), ksW = F("Kstar_w", 0.0474, 0.01, 0.1);
+    auto SF = [&](SF_4Body k, int a, int b, int c, int d) { return new SpinFactor("SF", k, mD0, a, b, c, d); };
+    using LSv = std::vector<Lineshape *>;
+    using SFv = std::vector<SpinFactor *>;
+    LSv L1 = {new Lineshapes::FOCUS("focus_kpi", Lineshapes::FOCUS::Mod::Kpi, dm, dw, 0, M_34),
+              new Lineshapes::NonRes("nonres_p", dm, dw, 1, M_12)};
+    SFv S1 = {SF(SF_4Body::DtoPP1_PtoSP2_StoP3P4, 0, 1, 2, 3), SF(SF_4Body::FF_12_34_L1, 0, 1, 2, 3)};
+    LSv L2 = {new Lineshapes::FOCUS("focus_keta", Lineshapes::FOCUS::Mod::KEta, dm, dw, 0, M_13),
+              new Lineshapes::FOCUS("focus_i32", Lineshapes::FOCUS::Mod::I32, dm, dw, 0, M_24)};
+    SFv S2 = {SF(SF_4Body::DtoPP1_PtoVP2_VtoP3P4, 3, 2, 0, 1), SF(SF_4Body::FF_12_34_L2, 0, 1, 2, 3)};
+    LSv L3 = {new Lineshapes::GLASS("glass", k0m, k0w, 0, M_34, FF::BL2, 1.5, {ga, gr, gphiF, gphiR, gF}),
+              new Lineshapes::One("one", dm, dw, 0, M_12)};
+    SFv S3 = {SF(SF_4Body::DtoV1P1_V1toV2P2_V2toP3P4, 0, 1, 2, 3), SF(SF_4Body::FF_123_4_L1, 0, 1, 2, 3)};
+    LSv L4 = {new Lineshapes::Flatte("f0_980", f0m, dw, 0, M_12), new Lineshapes::NonRes("nonres_d", dm, dw, 2, M_34_2)};
+    SFv S4 = {SF(SF_4Body::DtoTP1_TtoVP2_VtoP3P4, 2, 3, 0, 1), SF(SF_4Body::FF_123_4_L2, 0, 1, 2, 3)};
+    LSv L5 = {new Lineshapes::RBW("rho", rhoM, rhoW, 1, M_12), new Lineshapes::RBW("Kstar", ksM, ksW, 1, M_34)};
+    SFv S5 = {SF(SF_4Body::ONE, 0, 1, 2, 3)};
+    info.amplitudes = {new Amplitude("A1", Variable("a1r", 1.0), Variable("a1i", 0.0), L1, S1, 1),
+                       new Amplitude("A2", Variable("a2r", 0.4), Variable("a2i", -0.7), L2, S2, 1),
+                       new Amplitude("A3", Variable("a3r", -0.3), Variable("a3i", 0.5), L3, S3, 1),
+                       new Amplitude("A4", Variable("a4r", 0.8), Variable("a4i", 0.2), L4, S4, 1),
+                       new Amplitude("A5", Variable("a5r", -0.05), Variable("a5i", 0.02), L5, S5, 1)};
+    Variable one("constantOne", 1), zero("constantZero", 0);
+    std::vector<Observable> obs = {m12, m34, cos12, cos34, phi, eventNumber};
+    auto *eff = new PolynomialPdf("constantEff", obs, std::vector<Variable>{one}, std::vector<Variable>{zero, zero}, 0);
+    auto *dp  = new Amp4Body("zoo4", obs, info, eff, 40000);
+    UnbinnedDataSet d(obs);
+    { // phase-space data events (shim generator + the reference's Dim5 map), as fill_dp4_phsp
+        size_t n = 400;
+        std::vector<mcbooster::GReal_t> masses(info.particle_masses.begin() + 1, info.particle_masses.end());
+        mcbooster::PhaseSpace phsp(mD0, masses, n, 991);
+        phsp.Generate(mcbooster::Vector4R(mD0, 0.0, 0.0, 0.0));
+        auto d1 = phsp.GetDaughters(0), d2 = phsp.GetDaughters(1), d3 = phsp.GetDaughters(2), d4 = phsp.GetDaughters(3);
+        mcbooster::ParticlesSet_d pset = {&d1, &d2, &d3, &d4};
+        mcbooster::RealVector_d v0(n), v1(n), v2(n), v3(n), v4(n);
+        mcbooster::VariableSet_d vs = {&v0, &v1, &v2, &v3, &v4};
+        Dim5 eval;
+        mcbooster::EvaluateArray<Dim5>(eval, pset, vs);
+        for(size_t i = 0; i < n; i++) {
+            m12.setValue(v0[i]); m34.setValue(v1[i]); cos12.setValue(v2[i]); cos34.setValue(v3[i]); phi.setValue(v4[i]);
+            eventNumber.setValue(d.getNumEvents());
+            d.addEvent();
+        }
+    }
+    save_npy("zoo4.m12", column(d, m12)); save_npy("zoo4.m34", column(d, m34)); save_npy("zoo4.cos12", column(d, cos12));
+    save_npy("zoo4.cos34", column(d, cos34)); save_npy("zoo4.phi", column(d, phi));
+    save_npy("zoo4.mc_m12", host_copy(dp->norm_M12)); save_npy("zoo4.mc_m34", host_copy(dp->norm_M34));
+    save_npy("zoo4.mc_cos12", host_copy(dp->norm_CosTheta12)); save_npy("zoo4.mc_cos34", host_copy(dp->norm_CosTheta34));
+    save_npy("zoo4.mc_phi", host_copy(dp->norm_phi));
+    put("zoo4.mc_events", dp->getMCevents());
+    dp->setData(&d);
+    dp->setDataSize(d.getNumEvents(), 6);
+    put("zoo4.nll", dp->calculateNLL());
+    put("zoo4.integral", 1.0 / dp->getNormalization());
+    {
+        std::vector<double> amps;
+        thrust::host_vector<fpcomplex> h = *(dp->cachedAMPs);
+        for(size_t i = 0; i < h.size(); i++) { amps.push_back(h[i].real()); amps.push_back(h[i].imag()); }
+        save_npy("zoo4.amps", amps.data(), d.getNumEvents(), 10);
+    }
+    for(auto &v : pars) v.setChanged(false);
+    P("glass_phiF").setChanged(true); P("f0_m").setChanged(true);
+    dp->updateVariable(P("glass_phiF"), 0.35); dp->updateVariable(P("f0_m"), 0.98);
+    dp->updateParameters();
+    put("zoo4.nll_moved", dp->calculateNLL());
+    put("zoo4.integral_moved", 1.0 / dp->getNormalization());
+}
+
 static void case_dp4_fit() {
     DP4Model *M = make_dp4(60000, false);
     UnbinnedDataSet cand({M->m12, M->m34, M->cos12, M->cos34, M->phi, M->eventNumber});
@@ -1054,6 +1152,7 @@ int main(int argc, char **argv) {
             if(only == "all" || only == "binned") case_binned();
             if(only == "all" || only == "dalitz") case_dalitz();
             if(only == "all" || only == "zoo3") case_zoo3();
+            if(only == "all" || only == "zoo4") case_zoo4();
             if(only == "all" || only == "dalitzfit") case_dalitz_fit();
             if(only == "all" || only == "dp4") case_dp4();
             if(only == "all" || only == "dp4fit") case_dp4_fit();

@@ -249,6 +249,59 @@ class DP4:
         return dataset_from_columns(self.observables, list(cols5) + [np.arange(n, dtype=np.float64)])
 
 
+class Zoo4:
+    """The four-body lineshapes DP4 does not use (One, NonRes, Flatte, GLASS, FOCUS Kpi/KEta/I32) and the nine remaining spin
+    factors, one permutation each (mirrors oracle/ref_driver.cpp case_zoo4)."""
+
+    def __init__(self):
+        k = self.keep = Keep()
+        O, V = gf.Observable, gf.Variable
+        self.m12, self.m34 = O("m12", 0, 3), O("m34", 0, 3)
+        self.cos12, self.cos34, self.phi = O("cos12", -1, 1), O("cos34", -1, 1), O("phi", -3.5, 3.5)
+        self.evt = gf.EventNumber("eventNumber", 0, 2147483647)
+        mD0, piP, Km = 1.8645, 0.13957018, 0.493677
+        info = self.info = gf.DecayInfo4()
+        info.meson_radius = 1.5
+        info.particle_masses = [mD0, piP, piP, Km, piP]
+        self.pars = {}
+
+        def F(n, v, lo, hi):
+            self.pars[n] = V(n, v, 0.001, lo, hi)
+            return self.pars[n]
+
+        dm, dw = F("dummy_m", 1.0, 0.5, 1.5), F("dummy_w", 0.1, 0.05, 0.5)
+        k0m, k0w = F("K0s1430_m", 1.425, 1.3, 1.5), F("K0s1430_w", 0.27, 0.1, 0.4)
+        glass = [F("glass_a", 2.07, 1, 3), F("glass_r", 3.32, 2, 4), F("glass_phiF", 0.2, -1, 1), F("glass_phiR", -0.3, -1, 1),
+                 F("glass_F", 0.9, 0.5, 1.5)]
+        f0m = F("f0_m", 0.965, 0.9, 1.0)
+        rhoM, rhoW = F("rho_m", 0.77526, 0.6, 0.9), F("rho_w", 0.1478, 0.05, 0.3)
+        ksM, ksW = F("Kstar_m", 0.89581, 0.8, 1.0), F("Kstar_w", 0.0474, 0.01, 0.1)
+        S, L, P = gf.SF_4Body, gf.Lineshapes, gf.DP4Pair
+        SF = lambda kind, *idx: k(gf.SpinFactor("SF", kind, mD0, *idx))
+        Mod = L.FOCUS.Mod
+        L1 = [k(L.FOCUS("focus_kpi", Mod.Kpi, dm, dw, 0, int(P.M_34))), k(L.NonRes("nonres_p", dm, dw, 1, int(P.M_12)))]
+        S1 = [SF(S.DtoPP1_PtoSP2_StoP3P4, 0, 1, 2, 3), SF(S.FF_12_34_L1, 0, 1, 2, 3)]
+        L2 = [k(L.FOCUS("focus_keta", Mod.KEta, dm, dw, 0, int(P.M_13))), k(L.FOCUS("focus_i32", Mod.I32, dm, dw, 0, int(P.M_24)))]
+        S2 = [SF(S.DtoPP1_PtoVP2_VtoP3P4, 3, 2, 0, 1), SF(S.FF_12_34_L2, 0, 1, 2, 3)]
+        L3 = [k(L.GLASS("glass", k0m, k0w, 0, int(P.M_34), gf.FF.BL2, 1.5, glass)), k(L.One("one", dm, dw, 0, int(P.M_12)))]
+        S3 = [SF(S.DtoV1P1_V1toV2P2_V2toP3P4, 0, 1, 2, 3), SF(S.FF_123_4_L1, 0, 1, 2, 3)]
+        L4 = [k(L.Flatte("f0_980", f0m, dw, 0, int(P.M_12))), k(L.NonRes("nonres_d", dm, dw, 2, int(P.M_34_2)))]
+        S4 = [SF(S.DtoTP1_TtoVP2_VtoP3P4, 2, 3, 0, 1), SF(S.FF_123_4_L2, 0, 1, 2, 3)]
+        L5 = [k(L.RBW("rho", rhoM, rhoW, 1, int(P.M_12))), k(L.RBW("Kstar", ksM, ksW, 1, int(P.M_34)))]
+        S5 = [SF(S.ONE, 0, 1, 2, 3)]
+        A = gf.Amplitude
+        for n, re, im, ls, sf in (("A1", 1.0, 0.0, L1, S1), ("A2", 0.4, -0.7, L2, S2), ("A3", -0.3, 0.5, L3, S3), ("A4", 0.8, 0.2, L4, S4),
+                                  ("A5", -0.05, 0.02, L5, S5)):
+            info.add_amplitude(k(A(n, V(n.lower() + "r", re), V(n.lower() + "i", im), ls, sf, 1)))
+        self.observables = [self.m12, self.m34, self.cos12, self.cos34, self.phi, self.evt]
+        self.eff = k(gf.PolynomialPdf("constantEff", self.observables, [V("constantOne", 1)], [V("constantZero", 0)] * 2, 0))
+        self.dp = gf.Amp4Body("zoo4", self.observables, info, self.eff, 0)
+
+    def dataset(self, cols5):
+        n = len(cols5[0])
+        return dataset_from_columns(self.observables, list(cols5) + [np.arange(n, dtype=np.float64)])
+
+
 class TDDP4:
     """Time-dependent D0 -> K- pi+ pi+ pi- (examples/TDDP4/TDDP4.cu:38-156): three Bose-symmetrised K* rho amplitudes for
     each of A and B, TruthResolution or ThreeGaussResolution, AddPdf(1.0; Amp4Body_TD, flat bkg) — the tree

@@ -210,13 +210,13 @@ def test_tddp4_host_bookkeeping():
 @pytest.mark.skipif(not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "ref_driver")), reason="oracle/_ref not built")
 def test_oracle_reproduces_fixtures(tmp_path, golden):
     out = str(tmp_path / "g")
-    for case in ("basic", "binned", "dalitz", "zoo3", "dp4", "tddp4"):
+    for case in ("basic", "binned", "dalitz", "zoo3", "dp4", "zoo4", "tddp4"):
         subprocess.run([os.path.join(ROOT, "oracle", "_ref", "ref_driver"), "golden", out, case], check=True, capture_output=True, timeout=600)
     with open(os.path.join(out, "manifest_binned.json")) as f:
         again = json.load(f)
     for k in ("binned.exp_nll", "binned.exp_chisq", "binned.exp_binerr", "binned.gauss_nll", "binned.gauss_chisq"):
         assert again[k] == pytest.approx(golden[k], rel=1e-13)
-    for name in ("exp.prob", "conv.grid", "convadd.prob", "dalitz.waves", "dalitz.prob", "zoo3.waves", "dp4.amps", "dp4.prob", "tddp4.amps", "tddp4.prob",
+    for name in ("exp.prob", "conv.grid", "convadd.prob", "dalitz.waves", "dalitz.prob", "zoo3.waves", "dp4.amps", "zoo4.amps", "dp4.prob", "tddp4.amps", "tddp4.prob",
                  "tddp4g3.prob", "tddp4sh.amps", "tddp4sh.prob"):
         np.testing.assert_allclose(np.load(os.path.join(out, name + ".npy")), golden.arr(name), rtol=1e-13, atol=0)
 

@@ -328,6 +328,39 @@ def test_dp4_values(golden, mode):
     assert rel(1.0 / dp.getNormalization(), golden["dp4.integral_kstar_moved"]) < 1e-12
 
 
+@pytest.mark.parametrize("mode", ["Gram", "PerEvent"])
+def test_zoo4_lineshapes_and_spin_factors(golden, mode):
+    """One / NonRes / Flatte / GLASS / FOCUS lineshapes and the spin factors DP4 leaves out, against lineshapes/*.cu and SpinFactors.cu"""
+    from models import Zoo4
+    M = Zoo4()
+    dp = M.dp
+    dp.setNormMode(getattr(gf.Amp4BodyBase.NormMode, mode))
+    cols = [golden.arr("zoo4." + n) for n in ("m12", "m34", "cos12", "cos34", "phi")]
+    mc = np.vstack([golden.arr("zoo4.mc_" + n) for n in ("m12", "m34", "cos12", "cos34", "phi")])
+    assert mc.shape[1] == int(golden["zoo4.mc_events"])
+    dp.setNormEvents(mc)
+    d = M.dataset(cols)
+    dp.setData(d)
+    dp.setDataSize(len(d), 6)
+    nll = dp.calculateNLL()
+    ref = golden.arr("zoo4.amps")
+    for a in range(5):
+        w = np.asarray(dp.getCachedAmp(a))
+        r = ref[:, 2 * a] + 1j * ref[:, 2 * a + 1]
+        err = np.max(np.abs(w - r) / np.maximum(np.abs(r), 1e-300))
+        assert err < 1e-10, (a, err)
+    assert rel(1.0 / dp.getNormalization(), golden["zoo4.integral"]) < 1e-12
+    assert rel(nll, golden["zoo4.nll"]) < RTOL_NLL
+    for v in M.pars.values():
+        v.changed = False
+    for n, v in (("glass_phiF", 0.35), ("f0_m", 0.98)):
+        M.pars[n].changed = True
+        dp.updateVariable(M.pars[n], v)
+    dp.updateParameters()
+    assert rel(dp.calculateNLL(), golden["zoo4.nll_moved"]) < RTOL_NLL
+    assert rel(1.0 / dp.getNormalization(), golden["zoo4.integral_moved"]) < 1e-12
+
+
 def test_dp4_fit_matches_reference(golden):
     from models import DP4
     M = DP4(mc_events=0, float_ls=False)
