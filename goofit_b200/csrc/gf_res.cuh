@@ -262,6 +262,19 @@ __device__ inline double2 gf_res_flatte(const double *p, int cyc, int doSwap, do
     return ret;
 }
 
+// RhoOmegaMix.cu:9-135 : rho (Gounaris-Sakurai) times (1 + B * omega), B = (real + i imag) * delta * (m_rho + m_omega).
+// Upstream writes the omega term out as RBW.cu's plain Breit-Wigner and the rho term as GS.cu's, operation for
+// operation, so both are taken from the functions above. params: omega mass,width, rho mass,width, real, imag, delta.
+__device__ inline double2 gf_res_rhoomega(const double *p, int spin, int cyc, bool norm, const gf_decay3 &D, double m12,
+                                          double m13, double m23) {
+    double2 omega = gf_res_rbw(1, p[0], p[1], spin, cyc, norm, D, m12, m13, m23);
+    double2 rho = gf_res_gs(p[2], p[3], spin, cyc, norm, D, m12, m13, m23);
+    double Delta = p[6] * (p[2] + p[0]);
+    double2 mix = gf_cmul(make_double2(p[4] * Delta, p[5] * Delta), omega);
+    mix.x += 1.0;
+    return gf_cmul(rho, mix);
+}
+
 // Dispatch on the resonance record (Amp3Body_TD.cu:36-39 getResonanceAmplitude)
 __device__ inline double2 gf_resonance(const gf_node &nd, const double *params, const double *consts,
                                        const gf_decay3 &D, double m12, double m13, double m23) {
@@ -275,6 +288,7 @@ __device__ inline double2 gf_resonance(const gf_node &nd, const double *params, 
     case GF_OP_RES_GAUSS: return gf_res_gauss(p[0], p[1], (int)c[0], m12, m13, m23);
     case GF_OP_RES_LASS: return gf_res_lass(p, (int)c[0], (int)c[1], c[2] != 0.0, D, m12, m13, m23);
     case GF_OP_RES_FLATTE: return gf_res_flatte(p, (int)c[0], (int)c[1], m12, m13, m23);
+    case GF_OP_RES_RHOOMEGA: return gf_res_rhoomega(p, (int)c[0], (int)c[1], c[2] != 0.0, D, m12, m13, m23);
     default: return make_double2(0.0, 0.0);
     }
 }

@@ -65,6 +65,11 @@ class FLATTE : public ResonancePdf { // resonances/FLATTE.cu:80-97
   public:
     FLATTE(std::string name, Variable ar, Variable ai, Variable mean, Variable g1, Variable rg2og1, unsigned int cyc, bool symmDP);
 };
+class RhoOmegaMix : public ResonancePdf { // resonances/RhoOmegaMix.cu:139-167 (sym is accepted and ignored, as upstream)
+  public:
+    RhoOmegaMix(std::string name, Variable ar, Variable ai, Variable omega_mass, Variable omega_width, Variable rho_mass,
+                Variable rho_width, Variable real, Variable imag, Variable delta, unsigned int sp, unsigned int cyc, bool norm, bool sym);
+};
 } // namespace Resonances
 
 struct DecayInfo3 { // DalitzPlotHelpers.h:83-92

@@ -76,6 +76,15 @@ FLATTE::FLATTE(std::string name, Variable ar, Variable ai, Variable mean, Variab
     registerConstant(symmDP);
     registerFunction("ptr_to_FLATTE", GF_OP_RES_FLATTE);
 }
+RhoOmegaMix::RhoOmegaMix(std::string name, Variable ar, Variable ai, Variable omega_mass, Variable omega_width, Variable rho_mass,
+                         Variable rho_width, Variable real, Variable imag, Variable delta, unsigned int sp, unsigned int cyc, bool norm, bool)
+    : ResonancePdf("RHOOMEGAMIX", name, ar, ai) {
+    for(auto &v : {omega_mass, omega_width, rho_mass, rho_width, real, imag, delta}) registerParameter(v);
+    registerConstant(sp);
+    registerConstant(cyc);
+    registerConstant(norm);
+    registerFunction("ptr_to_RHOOMEGAMIX", GF_OP_RES_RHOOMEGA);
+}
 } // namespace Resonances
 
 Amp3Body::Amp3Body(std::string n, Observable m12, Observable m13, EventNumber eventNumber, DecayInfo3 decay, GooPdf *eff)

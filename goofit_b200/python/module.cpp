@@ -312,6 +312,11 @@ PYBIND11_MODULE(_goofit, m) {
     py::class_<Resonances::FLATTE, ResonancePdf>(mres, "FLATTE")
         .def(py::init<std::string, Variable, Variable, Variable, Variable, Variable, unsigned int, bool>(), "name"_a, "ar"_a, "ai"_a,
              "mean"_a, "g1"_a, "rg2og1"_a, "cyc"_a, "symmDP"_a);
+    py::class_<Resonances::RhoOmegaMix, ResonancePdf>(mres, "RhoOmegaMix")
+        .def(py::init<std::string, Variable, Variable, Variable, Variable, Variable, Variable, Variable, Variable, Variable, unsigned int,
+                      unsigned int, bool, bool>(),
+             "name"_a, "ar"_a, "ai"_a, "omega_mass"_a, "omega_width"_a, "rho_mass"_a, "rho_width"_a, "real"_a, "imag"_a, "delta"_a,
+             "sp"_a, "cyc"_a, "norm"_a, "sym"_a);
     py::class_<DecayInfo3>(m, "DecayInfo3")
         .def(py::init<>())
         .def_readwrite("motherMass", &DecayInfo3::motherMass)

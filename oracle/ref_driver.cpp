@@ -41,6 +41,7 @@
 #include <goofit/PDFs/physics/ResonancePdf.h>
 #include <goofit/PDFs/physics/resonances/FLATTE.h>
 #include <goofit/PDFs/physics/resonances/LASS.h>
+#include <goofit/PDFs/physics/resonances/RhoOmegaMix.h>
 #include <goofit/BinnedDataSet.h>
 #include <goofit/FitControl.h>
 #include <goofit/UnbinnedDataSet.h>
@@ -488,6 +489,14 @@ static void case_zoo3() {
                             true, true),
         new Resonances::RBW("f2_plain", Variable("f2_r", 0.2), Variable("f2_i", 0.3), F("f2_m", 1.2754, 1.2, 1.35), F("f2_w", 0.1851, 0.1, 0.3), 2, PAIR_23,
                             false),
+        new Resonances::RhoOmegaMix("rho_omega", Variable("ro_r", 0.7), Variable("ro_i", 0.1), F("om_m", 0.78265, 0.75, 0.8),
+                                    F("om_w", 0.00849, 0.005, 0.02), F("ro_m", 0.7690, 0.7, 0.85), F("ro_w", 0.1509, 0.1, 0.2),
+                                    F("mix_re", 0.00185, -0.1, 0.1), F("mix_im", -0.0007, -0.1, 0.1), F("mix_delta", 1.0, 0.5, 1.5), 1, PAIR_23,
+                                    true, false),
+        new Resonances::RhoOmegaMix("rho_omega_u", Variable("rou_r", -0.2), Variable("rou_i", 0.3), F("omu_m", 0.78265, 0.75, 0.8),
+                                    F("omu_w", 0.00849, 0.005, 0.02), F("rou_m", 0.7690, 0.7, 0.85), F("rou_w", 0.1509, 0.1, 0.2),
+                                    F("mixu_re", 0.003, -1, 1), F("mixu_im", -0.002, -1, 1), F("mixu_delta", 0.8, 0.5, 1.5), 1, PAIR_12,
+                                    false, false),
     };
     std::vector<Observable> obs = {m12, m13};
     auto *eff = new PolynomialPdf("constantEff", obs, std::vector<Variable>{one}, std::vector<Variable>{zero, zero}, 0);
@@ -521,8 +530,9 @@ static void case_zoo3() {
             if(v.getName() == n) return v;
         throw std::runtime_error(n);
     };
-    P("lass_r_").setChanged(true); P("f0_g1").setChanged(true); P("gs_m").setChanged(true);
+    P("lass_r_").setChanged(true); P("f0_g1").setChanged(true); P("gs_m").setChanged(true); P("mix_im").setChanged(true);
     s->updateVariable(P("lass_r_"), 3.1); s->updateVariable(P("f0_g1"), 0.18); s->updateVariable(P("gs_m"), 0.79);
+    s->updateVariable(P("mix_im"), 0.004);
     s->updateParameters();
     put("zoo3.nll_moved", s->calculateNLL());
     put("zoo3.integral_moved", 1.0 / s->getNormalization());

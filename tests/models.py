@@ -89,7 +89,8 @@ class Dalitz:
 
 
 class Zoo3:
-    """The other three-body shapes on one Dalitz plot: LASS (spin 0 and 1), FLATTE (plain and swapped), GS, Gauss, symmetrised RBW, spin-2 RBW;
+    """The other three-body shapes on one Dalitz plot: LASS (spin 0 and 1), FLATTE (plain and swapped), GS, Gauss, symmetrised RBW, spin-2 RBW,
+    RhoOmegaMix (normalised and plain barrier factors);
     every shape parameter free (mirrors oracle/ref_driver.cpp case_zoo3)."""
 
     def __init__(self, grid=90):
@@ -126,6 +127,12 @@ class Zoo3:
             R.Gauss("gauss", V("ga_r", 0.1), V("ga_i", 0.05), F("ga_m", 1.2, 1.0, 1.4), F("ga_s", 0.1, 0.05, 0.3), P13),
             R.RBW("rho_sym", V("rs_r", 0.3), V("rs_i", -0.2), F("rs_m", 0.7758, 0.7, 0.85), F("rs_w", 0.15, 0.1, 0.2), 1, P12, True, True),
             R.RBW("f2_plain", V("f2_r", 0.2), V("f2_i", 0.3), F("f2_m", 1.2754, 1.2, 1.35), F("f2_w", 0.1851, 0.1, 0.3), 2, P23, False),
+            R.RhoOmegaMix("rho_omega", V("ro_r", 0.7), V("ro_i", 0.1), F("om_m", 0.78265, 0.75, 0.8), F("om_w", 0.00849, 0.005, 0.02),
+                          F("ro_m", 0.7690, 0.7, 0.85), F("ro_w", 0.1509, 0.1, 0.2), F("mix_re", 0.00185, -0.1, 0.1),
+                          F("mix_im", -0.0007, -0.1, 0.1), F("mix_delta", 1.0, 0.5, 1.5), 1, P23, True, False),
+            R.RhoOmegaMix("rho_omega_u", V("rou_r", -0.2), V("rou_i", 0.3), F("omu_m", 0.78265, 0.75, 0.8), F("omu_w", 0.00849, 0.005, 0.02),
+                          F("rou_m", 0.7690, 0.7, 0.85), F("rou_w", 0.1509, 0.1, 0.2), F("mixu_re", 0.003, -1, 1), F("mixu_im", -0.002, -1, 1),
+                          F("mixu_delta", 0.8, 0.5, 1.5), 1, P12, False, False),
         ]
         for r in self.resonances:
             d.add_resonance(k(r))

@@ -222,7 +222,7 @@ def test_dalitz_values(golden):
 
 
 def test_zoo3_resonance_shapes(golden):
-    """LASS / FLATTE / GS / Gauss / symmetrised and unnormalised RBW against the reference's resonances/*.cu"""
+    """LASS / FLATTE / GS / Gauss / RhoOmegaMix / symmetrised and unnormalised RBW against the reference's resonances/*.cu"""
     M = Zoo3(grid=90)
     d = M.dataset(golden.arr("zoo3.m12"), golden.arr("zoo3.m13"))
     s = M.signal
@@ -240,7 +240,7 @@ def test_zoo3_resonance_shapes(golden):
     for v in M.pars:
         v.changed = False
     byname = {v.name: v for v in M.pars}
-    for n, v in (("lass_r_", 3.1), ("f0_g1", 0.18), ("gs_m", 0.79)):  # LASS effective range, FLATTE coupling, GS mass
+    for n, v in (("lass_r_", 3.1), ("f0_g1", 0.18), ("gs_m", 0.79), ("mix_im", 0.004)):  # LASS range, FLATTE coupling, GS mass, rho-omega mixing
         byname[n].changed = True
         s.updateVariable(byname[n], v)
     s.updateParameters()
