@@ -275,6 +275,34 @@ __device__ inline double2 gf_res_rhoomega(const double *p, int spin, int cyc, bo
     return gf_cmul(rho, mix);
 }
 
+// Spline.cu:10-87 : complex cubic spline in the pair's squared mass (plus, with doSwap, the same spline in the second
+// pair). consts: cyc, doSwap, nKnots, knot[nKnots], then the 2*nKnots second derivatives (re, im per knot) the host
+// computed when the resonance was built -- upstream keeps those in one __device__ array filled by the constructor only
+// (Spline.cu:8,112), so they do NOT follow the knot values during a fit; params: re, im per knot.
+__device__ inline double2 gf_res_spline(const double *p, const double *c, double m12, double m13, double m23) {
+    const int cyc = (int)c[0], runs = 1 + (int)c[1], n = (int)c[2];
+    const double *knot = c + 3, *d2 = c + 3 + n;
+    double mAB = m12, mAC = m13;
+    if(cyc == GF_PAIR_13) { mAB = m13; mAC = m12; }
+    if(cyc == GF_PAIR_23) { mAB = m23; mAC = m12; }
+    double re = 0, im = 0;
+    for(int it = 0; it < runs; ++it) {
+        int hi = 0;
+        while(hi < n && !(mAB < knot[hi])) hi++;
+        if(hi > 0 && hi < n) {
+            int lo = hi - 1;
+            double dm = knot[hi] - knot[lo];
+            double aa = (knot[hi] - mAB) / dm, bb = 1 - aa;
+            double aa3 = aa * aa * aa, bb3 = bb * bb * bb;
+            re = re + aa * p[2 * lo] + bb * p[2 * hi] + ((aa3 - aa) * d2[2 * lo] + (bb3 - bb) * d2[2 * hi]) * (dm * dm) / 6.0;
+            im = im + aa * p[2 * lo + 1] + bb * p[2 * hi + 1]
+                 + ((aa3 - aa) * d2[2 * lo + 1] + (bb3 - bb) * d2[2 * hi + 1]) * (dm * dm) / 6.0;
+        }
+        mAB = mAC;
+    }
+    return make_double2(re, im);
+}
+
 // Dispatch on the resonance record (Amp3Body_TD.cu:36-39 getResonanceAmplitude)
 __device__ inline double2 gf_resonance(const gf_node &nd, const double *params, const double *consts,
                                        const gf_decay3 &D, double m12, double m13, double m23) {
@@ -288,6 +316,7 @@ __device__ inline double2 gf_resonance(const gf_node &nd, const double *params, 
     case GF_OP_RES_GAUSS: return gf_res_gauss(p[0], p[1], (int)c[0], m12, m13, m23);
     case GF_OP_RES_LASS: return gf_res_lass(p, (int)c[0], (int)c[1], c[2] != 0.0, D, m12, m13, m23);
     case GF_OP_RES_FLATTE: return gf_res_flatte(p, (int)c[0], (int)c[1], m12, m13, m23);
+    case GF_OP_RES_SPLINE: return gf_res_spline(p, c, m12, m13, m23);
     case GF_OP_RES_RHOOMEGA: return gf_res_rhoomega(p, (int)c[0], (int)c[1], c[2] != 0.0, D, m12, m13, m23);
     default: return make_double2(0.0, 0.0);
     }

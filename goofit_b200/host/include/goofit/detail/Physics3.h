@@ -65,6 +65,13 @@ class FLATTE : public ResonancePdf { // resonances/FLATTE.cu:80-97
   public:
     FLATTE(std::string name, Variable ar, Variable ai, Variable mean, Variable g1, Variable rg2og1, unsigned int cyc, bool symmDP);
 };
+class Spline : public ResonancePdf { // resonances/Spline.cu:91-134
+  public:
+    Spline(std::string name, Variable ar, Variable ai, std::vector<fptype> &HH_bin_limits, std::vector<Variable> &pwa_coefs_reals,
+           std::vector<Variable> &pwa_coefs_imags, unsigned int cyc, bool symmDP = false);
+    /// second derivatives of the natural-end-slope cubic spline through (x, y), per component (detail/ComplexUtils.h:20-92)
+    static std::vector<fptype> secondDerivatives(const std::vector<fptype> &x, const std::vector<fptype> &y);
+};
 class RhoOmegaMix : public ResonancePdf { // resonances/RhoOmegaMix.cu:139-167 (sym is accepted and ignored, as upstream)
   public:
     RhoOmegaMix(std::string name, Variable ar, Variable ai, Variable omega_mass, Variable omega_width, Variable rho_mass,

@@ -76,6 +76,63 @@ FLATTE::FLATTE(std::string name, Variable ar, Variable ai, Variable mean, Variab
     registerConstant(symmDP);
     registerFunction("ptr_to_FLATTE", GF_OP_RES_FLATTE);
 }
+// Tridiagonal solve for the spline's second derivatives with the end slopes fixed to twice the chord slope, as
+// complex_derivative() does for the real and the imaginary component independently.
+std::vector<fptype> Spline::secondDerivatives(const std::vector<fptype> &x, const std::vector<fptype> &y) {
+    if(x.size() != y.size()) throw GeneralError("x and y must have the same dimensions!");
+    const int n = static_cast<int>(x.size());
+    if(n < 2) throw GeneralError("Spline needs at least two knots");
+    std::vector<fptype> u(n), y2(n);
+    const fptype slope1 = 2. * (y[1] - y[0]) / (x[1] - x[0]);
+    const fptype slopeN = 2. * (y[n - 1] - y[n - 2]) / (x[n - 1] - x[n - 2]);
+    if(slope1 > 0.99e30) {
+        y2[0] = u[0] = 0.;
+    } else {
+        y2[0] = -0.5;
+        u[0]  = 3.0 / (x[1] - x[0]) * ((y[1] - y[0]) / (x[1] - x[0]) - slope1);
+    }
+    for(int i = 1; i < n - 1; i++) {
+        fptype sig = (x[i] - x[i - 1]) / (x[i + 1] - x[i - 1]);
+        fptype p   = sig * y2[i - 1] + 2.0;
+        y2[i]      = (sig - 1.0) / p;
+        u[i]       = (y[i + 1] - y[i]) / (x[i + 1] - x[i]) - (y[i] - y[i - 1]) / (x[i] - x[i - 1]);
+        u[i]       = (6.0 * u[i] / (x[i + 1] - x[i - 1]) - sig * u[i - 1]) / p;
+    }
+    fptype qn = 0., un = 0.;
+    if(!(slopeN > 0.99e30)) {
+        qn = 0.5;
+        un = (3.0 / (x[n - 1] - x[n - 2])) * (slopeN - (y[n - 1] - y[n - 2]) / (x[n - 1] - x[n - 2]));
+    }
+    y2[n - 1] = (un - qn * u[n - 2]) / (qn * y2[n - 2] + 1.0);
+    for(int k = n - 2; k >= 0; k--) y2[k] = y2[k] * y2[k + 1] + u[k];
+    return y2;
+}
+Spline::Spline(std::string name, Variable ar, Variable ai, std::vector<fptype> &HH_bin_limits, std::vector<Variable> &pwa_coefs_reals,
+               std::vector<Variable> &pwa_coefs_imags, unsigned int cyc, bool symmDP)
+    : ResonancePdf("Spline", name, ar, ai) {
+    const unsigned int nKnobs = HH_bin_limits.size();
+    if(pwa_coefs_reals.size() != nKnobs || pwa_coefs_imags.size() != nKnobs)
+        throw GeneralError("Spline {}: {} knots need as many real and imaginary coefficients", name, nKnobs);
+    registerConstant(cyc);
+    registerConstant(symmDP);
+    registerConstant(nKnobs);
+    std::vector<fptype> re(nKnobs), im(nKnobs);
+    for(unsigned int i = 0; i < nKnobs; i++) {
+        registerConstant(HH_bin_limits[i]);
+        registerParameter(pwa_coefs_reals[i]);
+        registerParameter(pwa_coefs_imags[i]);
+        re[i] = pwa_coefs_reals[i].getValue();
+        im[i] = pwa_coefs_imags[i].getValue();
+    }
+    // Frozen at construction, like upstream's cDeriatives table (Spline.cu:112 is the only recalculateCache() call); kept per
+    // resonance here, where upstream shares one table between all Spline objects.
+    auto d2re = secondDerivatives(HH_bin_limits, re), d2im = secondDerivatives(HH_bin_limits, im);
+    for(unsigned int i = 0; i < nKnobs; i++) {
+        registerConstant(d2re[i]);
+        registerConstant(d2im[i]);
+    }
+    registerFunction("ptr_to_SPLINE", GF_OP_RES_SPLINE);
+}
 RhoOmegaMix::RhoOmegaMix(std::string name, Variable ar, Variable ai, Variable omega_mass, Variable omega_width, Variable rho_mass,
                          Variable rho_width, Variable real, Variable imag, Variable delta, unsigned int sp, unsigned int cyc, bool norm, bool)
     : ResonancePdf("RHOOMEGAMIX", name, ar, ai) {

@@ -312,6 +312,13 @@ PYBIND11_MODULE(_goofit, m) {
     py::class_<Resonances::FLATTE, ResonancePdf>(mres, "FLATTE")
         .def(py::init<std::string, Variable, Variable, Variable, Variable, Variable, unsigned int, bool>(), "name"_a, "ar"_a, "ai"_a,
              "mean"_a, "g1"_a, "rg2og1"_a, "cyc"_a, "symmDP"_a);
+    py::class_<Resonances::Spline, ResonancePdf>(mres, "Spline")
+        .def(py::init([](std::string name, Variable ar, Variable ai, std::vector<fptype> limits, std::vector<Variable> re,
+                         std::vector<Variable> im, unsigned int cyc, bool symmDP) {
+                 return new Resonances::Spline(name, ar, ai, limits, re, im, cyc, symmDP);
+             }),
+             "name"_a, "ar"_a, "ai"_a, "HH_bin_limits"_a, "pwa_coefs_reals"_a, "pwa_coefs_imags"_a, "cyc"_a, "symmDP"_a = false)
+        .def_static("secondDerivatives", &Resonances::Spline::secondDerivatives, "x"_a, "y"_a);
     py::class_<Resonances::RhoOmegaMix, ResonancePdf>(mres, "RhoOmegaMix")
         .def(py::init<std::string, Variable, Variable, Variable, Variable, Variable, Variable, Variable, Variable, Variable, unsigned int,
                       unsigned int, bool, bool>(),

@@ -78,6 +78,7 @@ enum gf_op {
     GF_OP_RES_GAUSS,        /* resonances/Gauss.cu:9 */
     GF_OP_RES_LASS,         /* resonances/LASS.cu:9  params mass,width,a,r,R,phiR,B,phiB; consts spin,cyc,norm */
     GF_OP_RES_FLATTE,       /* resonances/FLATTE.cu:18  params mass,g1,g2/g1; consts cyc,symmDP */
+    GF_OP_RES_SPLINE,       /* resonances/Spline.cu:10  params re,im per knot; consts cyc,doSwap,nKnots,knots[n],second derivatives[2n] */
     GF_OP_RES_RHOOMEGA,     /* resonances/RhoOmegaMix.cu:9  params omega mass,width, rho mass,width, real, imag, delta; consts spin,cyc,norm */
     GF_OP_LS = 96,          /* 4-body lineshape; consts[0] = gf_ls_kind */
     GF_OP_SF,               /* 4-body spin factor; consts[0] = gf_sf_kind */

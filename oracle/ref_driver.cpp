@@ -42,6 +42,7 @@
 #include <goofit/PDFs/physics/resonances/FLATTE.h>
 #include <goofit/PDFs/physics/resonances/LASS.h>
 #include <goofit/PDFs/physics/resonances/RhoOmegaMix.h>
+#include <goofit/PDFs/physics/resonances/Spline.h>
 #include <goofit/BinnedDataSet.h>
 #include <goofit/FitControl.h>
 #include <goofit/UnbinnedDataSet.h>
@@ -472,7 +473,15 @@ static void case_zoo3() {
         return x;
     };
     Variable one("one", 1), zero("zero", 0);
+    // one Spline only: upstream keeps the second derivatives of every Spline in the same __device__ table
+    std::vector<fptype> knots = {0.1, 0.45, 0.8, 1.2, 1.6, 2.0, 2.5, 2.95};
+    std::vector<Variable> sp_re, sp_im;
+    for(size_t i = 0; i < knots.size(); i++) {
+        sp_re.push_back(F(("sp_re" + std::to_string(i)).c_str(), 0.4 * std::cos(1.3 * i) + 0.1 * i, -5, 5));
+        sp_im.push_back(F(("sp_im" + std::to_string(i)).c_str(), 0.3 * std::sin(0.9 * i) - 0.05 * i, -5, 5));
+    }
     info.resonances = {
+        new Resonances::Spline("spline", Variable("sp_r", 0.6), Variable("sp_i", -0.2), knots, sp_re, sp_im, PAIR_13, true),
         new Resonances::LASS("lass", Variable("lass_r", 0.8), Variable("lass_i", -0.3), F("lass_m", 1.425, 1.3, 1.5), F("lass_w", 0.27, 0.1, 0.4),
                              F("lass_a", 2.07, 1, 3), F("lass_r_", 3.32, 2, 4), F("lass_R", 1.0, 0.5, 1.5), F("lass_phiR", -1.9, -3, 3),
                              F("lass_B", 0.96, 0.5, 1.5), F("lass_phiB", 0.0017, -1, 1), 0, PAIR_12, true),
@@ -533,6 +542,8 @@ static void case_zoo3() {
     P("lass_r_").setChanged(true); P("f0_g1").setChanged(true); P("gs_m").setChanged(true); P("mix_im").setChanged(true);
     s->updateVariable(P("lass_r_"), 3.1); s->updateVariable(P("f0_g1"), 0.18); s->updateVariable(P("gs_m"), 0.79);
     s->updateVariable(P("mix_im"), 0.004);
+    P("sp_re3").setChanged(true); // the spline's second derivatives stay at their construction values upstream
+    s->updateVariable(P("sp_re3"), 0.9);
     s->updateParameters();
     put("zoo3.nll_moved", s->calculateNLL());
     put("zoo3.integral_moved", 1.0 / s->getNormalization());

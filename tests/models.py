@@ -1,5 +1,7 @@
 """Model builders shared by the tests, bench.py and smoke(): the same trees oracle/ref_driver.cpp builds
 with the reference's classes (examples/dalitz/dalitz.cpp:124-322 etc.), here with goofit_b200's."""
+import math
+
 import numpy as np
 
 import goofit_b200 as gf
@@ -90,7 +92,7 @@ class Dalitz:
 
 class Zoo3:
     """The other three-body shapes on one Dalitz plot: LASS (spin 0 and 1), FLATTE (plain and swapped), GS, Gauss, symmetrised RBW, spin-2 RBW,
-    RhoOmegaMix (normalised and plain barrier factors);
+    RhoOmegaMix (normalised and plain barrier factors), Spline (swapped);
     every shape parameter free (mirrors oracle/ref_driver.cpp case_zoo3)."""
 
     def __init__(self, grid=90):
@@ -113,7 +115,11 @@ class Zoo3:
 
         P12, P13, P23 = 0, 1, 2
         R = gf.Resonances
+        knots = [0.1, 0.45, 0.8, 1.2, 1.6, 2.0, 2.5, 2.95]
+        sp_re = [F("sp_re%d" % i, 0.4 * math.cos(1.3 * i) + 0.1 * i, -5, 5) for i in range(len(knots))]
+        sp_im = [F("sp_im%d" % i, 0.3 * math.sin(0.9 * i) - 0.05 * i, -5, 5) for i in range(len(knots))]
         self.resonances = [
+            R.Spline("spline", V("sp_r", 0.6), V("sp_i", -0.2), knots, sp_re, sp_im, P13, True),
             R.LASS("lass", V("lass_r", 0.8), V("lass_i", -0.3), F("lass_m", 1.425, 1.3, 1.5), F("lass_w", 0.27, 0.1, 0.4), F("lass_a", 2.07, 1, 3),
                    F("lass_r_", 3.32, 2, 4), F("lass_R", 1.0, 0.5, 1.5), F("lass_phiR", -1.9, -3, 3), F("lass_B", 0.96, 0.5, 1.5),
                    F("lass_phiB", 0.0017, -1, 1), 0, P12, True),

@@ -247,3 +247,17 @@ def test_sharded_sum_gloo_world2(tmp_path):
                         "--master-port", "29533", str(script), ROOT], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and "OK" in r.stdout, r.stderr[-2000:]
     assert gf.shard_range(10, 0, 3) == (0, 3) and gf.shard_range(10, 2, 3) == (6, 4)
+
+
+def test_spline_second_derivatives_against_scipy():
+    """Resonances::Spline's host table (detail/ComplexUtils.h:20-92): a clamped cubic spline whose end slopes are twice the
+    chord slope; scipy solves the same system independently."""
+    from scipy.interpolate import CubicSpline
+    x = np.array([0.1, 0.45, 0.8, 1.2, 1.6, 2.0, 2.5, 2.95])
+    y = 0.4 * np.cos(1.3 * np.arange(8)) + 0.1 * np.arange(8)
+    got = np.asarray(gf.Resonances.Spline.secondDerivatives(list(x), list(y)))
+    s1, sn = 2 * (y[1] - y[0]) / (x[1] - x[0]), 2 * (y[-1] - y[-2]) / (x[-1] - x[-2])
+    want = CubicSpline(x, y, bc_type=((1, s1), (1, sn)))(x, 2)
+    np.testing.assert_allclose(got, want, rtol=1e-10, atol=1e-12)
+    with pytest.raises(Exception):
+        gf.Resonances.Spline.secondDerivatives([0.0, 1.0], [1.0])

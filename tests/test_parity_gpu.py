@@ -240,7 +240,8 @@ def test_zoo3_resonance_shapes(golden):
     for v in M.pars:
         v.changed = False
     byname = {v.name: v for v in M.pars}
-    for n, v in (("lass_r_", 3.1), ("f0_g1", 0.18), ("gs_m", 0.79), ("mix_im", 0.004)):  # LASS range, FLATTE coupling, GS mass, rho-omega mixing
+    for n, v in (("lass_r_", 3.1), ("f0_g1", 0.18), ("gs_m", 0.79), ("mix_im", 0.004), ("sp_re3", 0.9)):
+        # LASS range, FLATTE coupling, GS mass, rho-omega mixing, one spline knot (its second derivatives stay frozen, as upstream)
         byname[n].changed = True
         s.updateVariable(byname[n], v)
     s.updateParameters()
