@@ -69,7 +69,13 @@ static int nccl_fail(const char *what, int rc) {
 }
 
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(GF_THREADS, 4)
+// One copy per class of program (HAS = the heavy node kinds compiled in, gf_ops.cuh); eval_sum_launch picks the copy.
+// Measured on 10^7 events against the single all-kinds kernel: Amp3Body-only 0.416 ms (was 0.431, no spills left),
+// Amp4Body_TD + TruthResolution 0.387 ms (was 0.452). An Amp4Body-only copy came out slower than the all-kinds one
+// (0.304 against 0.275 ms, same source, different schedule), so Amp4Body programs keep the all-kinds copy.
+constexpr int eval_sum_blocks_per_sm(int) { return 4; } // 3 and 5 measured slower for every copy (tools/ab_compare.sh)
+template <int HAS>
+__global__ void __launch_bounds__(GF_THREADS, eval_sum_blocks_per_sm(HAS))
     k_eval_sum(const gf_dev_view V, int first, int root, int metric, int n_cols, double *partials, unsigned *ticket,
                double *out) {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -82,10 +88,39 @@ __global__ void __launch_bounds__(GF_THREADS, 4)
     const long stride = (long)gridDim.x * blockDim.x;
     for(long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < V.n_events; i += stride) {
         evt.i = i;
-        double raw = gf_eval_tree(P, V, first, root, evt);
+        double raw = gf_eval_tree<HAS>(P, V, first, root, evt);
         acc += gf_metric(metric, raw, norm, evt, V, n_cols);
     }
     gf_grid_finish(&acc, 1, partials, ticket, out, red);
+}
+// heavy node kinds among nodes [first, root] of the installed program
+static int program_class(const gf_ctx *c, int first, int root) {
+    int has = 0;
+    for(int k = first; k <= root; ++k) {
+        switch(c->h_nodes[k].op) {
+        case GF_OP_CONVOLVE: has |= GF_HAS_CONV; break;
+        case GF_OP_AMP3: has |= GF_HAS_AMP3; break;
+        case GF_OP_AMP4: has |= GF_HAS_AMP4; break;
+        case GF_OP_AMP4_TD: {
+            has |= GF_HAS_AMP4_TD;
+            const int32_t *in = c->h_ints.data() + c->h_nodes[k].int_off; // ints[4] -> {resolution record, flags}
+            if(c->h_nodes[in[in[4]]].op != GF_OP_TRES_TRUTH) has |= GF_HAS_3GAUSS;
+        } break;
+        default: break;
+        }
+    }
+    return has;
+}
+typedef void (*eval_sum_kernel_t)(const gf_dev_view, int, int, int, int, double *, unsigned *, double *);
+static eval_sum_kernel_t eval_sum_kernel(int has) {
+    switch(has) {
+    case 0: return k_eval_sum<0>;
+    case GF_HAS_CONV: return k_eval_sum<GF_HAS_CONV>;
+    case GF_HAS_AMP3: return k_eval_sum<GF_HAS_AMP3>;
+    case GF_HAS_AMP4_TD: return k_eval_sum<GF_HAS_AMP4_TD>;
+    case GF_HAS_AMP4_TD | GF_HAS_3GAUSS: return k_eval_sum<GF_HAS_AMP4_TD | GF_HAS_3GAUSS>;
+    default: return k_eval_sum<GF_HAS_ALL>;
+    }
 }
 
 __global__ void __launch_bounds__(GF_THREADS, 4)
@@ -283,7 +318,8 @@ extern "C" int gf_set_program(gf_ctx *c, const gf_node *nodes, int n_nodes, cons
     V.n_nodes = n_nodes; V.n_params = n_params; V.n_consts = n_consts; V.n_norms = n_norms; V.n_ints = n_ints;
     size_t sm = gf_prog_smem(c);
     if(sm > 48 * 1024) {
-        cudaFuncSetAttribute(k_eval_sum, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        for(int has : {0, (int)GF_HAS_CONV, (int)GF_HAS_AMP3, (int)GF_HAS_AMP4_TD, GF_HAS_AMP4_TD | GF_HAS_3GAUSS, (int)GF_HAS_ALL})
+            cudaFuncSetAttribute(eval_sum_kernel(has), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
         cudaFuncSetAttribute(k_eval_events, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
         cudaFuncSetAttribute(k_grid_sum, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
     }
@@ -542,10 +578,11 @@ static int eval_sum_launch(gf_ctx *c, int root, int metric, double *out_dev) {
     if(check_root(c, root)) return 1;
     cudaSetDevice(c->device);
     int first = root - c->h_nodes[root].size + 1;
-    int blocks = gf_grid_blocks(c, c->view.n_events, 4);
+    const int has = program_class(c, first, root);
+    int blocks = gf_grid_blocks(c, c->view.n_events, eval_sum_blocks_per_sm(has));
     cudaEventRecord(c->ev0, c->stream);
-    k_eval_sum<<<blocks, GF_THREADS, gf_prog_smem(c), c->stream>>>(c->view, first, root, metric, c->n_cols,
-                                                                  c->d_partials, c->d_ticket, out_dev);
+    eval_sum_kernel(has)<<<blocks, GF_THREADS, gf_prog_smem(c), c->stream>>>(
+        c->view, first, root, metric, c->n_cols, c->d_partials, c->d_ticket, out_dev);
     cudaEventRecord(c->ev1, c->stream);
     c->launches++;
     GF_CUDA(cudaGetLastError());

@@ -190,9 +190,10 @@ __device__ inline void gf_tres_gauss(double &P1, double &P2, double &P3, double 
     P3 = NormG * 0.5 * (Ipy - Imy);
 }
 // op = GF_OP_TRES_TRUTH (TruthResolution.cu:8-28) or GF_OP_TRES_3GAUSS (ThreeGaussResolution.cu:62-125; p = 13 parameters)
+template <bool WITH_3GAUSS = true>
 __device__ inline double gf_tres(int op, const double *p, double coshterm, double costerm, double sinhterm, double sinterm,
                                  double tau, double dtime, double x, double y, double sigma) {
-    if(op == GF_OP_TRES_TRUTH) {
+    if(!WITH_3GAUSS || op == GF_OP_TRES_TRUTH) {
         // same five terms in the same order as the reference; cos/sin share one argument reduction (sincos) and
         // cosh/sinh share one expm1: with u = e^a - 1, sinh a = (u + u/(u+1))/2 and cosh a = 1 + u^2/(2(u+1)), both
         // accurate to an ulp or two for the small a = y t/tau of mixing fits (no e^a - e^-a cancellation)
@@ -236,25 +237,36 @@ __device__ inline double gf_tres(int op, const double *p, double coshterm, doubl
 }
 // A = sqrt(WS/RS) * sum_{flag 0,2} c A_a ; B = sum_{flag 1,2} c A_a with the reference's coefficient walk
 // (Amp4Body_TD.cu:186-214, NormIntegrator_TD.cu:69-88): coefficient pair (i + k), k counting earlier flag-2 amplitudes.
-template <class Load>
+template <int GF_TD_CHUNK = 4, class Load>
 __device__ inline void gf_amp4td_AB(const double *p, const int32_t *flags, int namp, const Load &amp, double &Are, double &Aim,
                                     double &Bre, double &Bim) {
     Are = Aim = Bre = Bim = 0;
     int k = 0;
-    for(int i = 0; i < namp; ++i) {
-        double2 me = amp(i);
-        int flag = flags[i];
-        double cr = p[4 + 2 * (i + k)], ci = p[5 + 2 * (i + k)];
-        double re = me.x * cr - me.y * ci, im = me.x * ci + me.y * cr;
-        if(flag == 1) {
-            Bre += re; Bim += im;
-        } else {
-            Are += re; Aim += im;
-            if(flag == 2) {
-                ++k;
-                cr = p[4 + 2 * (i + k)]; ci = p[5 + 2 * (i + k)];
-                Bre += me.x * cr - me.y * ci;
-                Bim += me.x * ci + me.y * cr;
+    // the cached amplitudes are fetched GF_TD_CHUNK at a time before the walk starts: one load per trip of a dependent
+    // loop leaves a single 16-byte request per thread in flight, about half of what HBM needs at this occupancy
+    for(int i0 = 0; i0 < namp; i0 += GF_TD_CHUNK) {
+        double2 chunk[GF_TD_CHUNK];
+#pragma unroll
+        for(int j = 0; j < GF_TD_CHUNK; ++j)
+            if(i0 + j < namp) chunk[j] = amp(i0 + j);
+#pragma unroll
+        for(int j = 0; j < GF_TD_CHUNK; ++j) {
+            const int i = i0 + j;
+            if(i >= namp) break;
+            double2 me = chunk[j];
+            int flag = flags[i];
+            double cr = p[4 + 2 * (i + k)], ci = p[5 + 2 * (i + k)];
+            double re = me.x * cr - me.y * ci, im = me.x * ci + me.y * cr;
+            if(flag == 1) {
+                Bre += re; Bim += im;
+            } else {
+                Are += re; Aim += im;
+                if(flag == 2) {
+                    ++k;
+                    cr = p[4 + 2 * (i + k)]; ci = p[5 + 2 * (i + k)];
+                    Bre += me.x * cr - me.y * ci;
+                    Bim += me.x * ci + me.y * cr;
+                }
             }
         }
     }
@@ -262,8 +274,17 @@ __device__ inline void gf_amp4td_AB(const double *p, const int32_t *flags, int n
     Aim *= p[3];
 }
 
+// Which of the heavy node kinds a compiled copy of the interpreter contains. The NLL kernel is instantiated once per
+// class of program (gf_core.cu picks the copy from the nodes of the installed program), so that the registers and the
+// load batching of, say, the Amp4Body_TD case are not paid by a Dalitz fit whose program has no such node.
+// amplitudes fetched together by the TruthResolution-only copy: 4 measured best (2: 0.403 ms, 4: 0.387, 6: 0.425, 8: 0.566,
+// the larger batches spill under the 64-register cap)
+#define GF_TD_CH 4
+// GF_HAS_3GAUSS: the Amp4Body_TD node may carry a ThreeGaussResolution (else TruthResolution only)
+enum : int { GF_HAS_CONV = 1, GF_HAS_AMP3 = 2, GF_HAS_AMP4 = 4, GF_HAS_AMP4_TD = 8, GF_HAS_3GAUSS = 16, GF_HAS_ALL = 31 };
+
 // Post-order evaluation of nodes [first, last]; returns the root's raw value.
-template <class Evt>
+template <int HAS = GF_HAS_ALL, class Evt>
 __device__ inline double gf_eval_tree(const gf_sprog &P, const gf_dev_view &V, int first, int last, const Evt &evt) {
     double st[GF_MAX_STACK];
     int sp = 0;
@@ -313,7 +334,7 @@ __device__ inline double gf_eval_tree(const gf_sprog &P, const gf_dev_view &V, i
             sp -= n;
             st[sp++] = ret;
         } break;
-        case GF_OP_CONVOLVE: { // combine/ConvolutionPdf.cu:27-75 via the per-offset table (gf_conv.cu)
+        case GF_OP_CONVOLVE: if constexpr((HAS & GF_HAS_CONV) != 0) { // combine/ConvolutionPdf.cu:27-75 via the per-offset table (gf_conv.cu)
             // ints = {aux slot, model root, resolution root}; consts = lo, hi, step
             const double *c = P.consts + nd.con_off;
             const int32_t *ob = P.ints + nd.obs_off;
@@ -331,7 +352,7 @@ __device__ inline double gf_eval_tree(const gf_sprog &P, const gf_dev_view &V, i
             ret *= P.norms[P.nodes[in[2]].norm_slot];
             st[sp++] = ret;
         } break;
-        case GF_OP_AMP3: { // physics/Amp3Body.cu:60-122 ; child = efficiency ; ints = {aux slot, nRes, ...}
+        case GF_OP_AMP3: if constexpr((HAS & GF_HAS_AMP3) != 0) { // physics/Amp3Body.cu:60-122 ; child = efficiency ; ints = {aux slot, nRes, ...}
             const double *c = P.consts + nd.con_off;
             const int32_t *ob = P.ints + nd.obs_off;
             double eff = st[--sp];
@@ -354,7 +375,7 @@ __device__ inline double gf_eval_tree(const gf_sprog &P, const gf_dev_view &V, i
             }
             st[sp++] = ret;
         } break;
-        case GF_OP_AMP4: { // physics/Amp4Body.cu:53-90 ; ints = {aux slot, nLS, nSF, nAmp, td, ...}
+        case GF_OP_AMP4: if constexpr((HAS & GF_HAS_AMP4) != 0) { // physics/Amp4Body.cu:53-90 ; ints = {aux slot, nLS, nSF, nAmp, td, ...}
             const int32_t *ob = P.ints + nd.obs_off;
             double eff = st[--sp];
             long e = evt.event_number(ob[5]);
@@ -371,20 +392,22 @@ __device__ inline double gf_eval_tree(const gf_sprog &P, const gf_dev_view &V, i
             }
             st[sp++] = (re * re + im * im) * eff;
         } break;
-        case GF_OP_AMP4_TD: { // physics/Amp4Body_TD.cu:167-261 ; ints[4] = offset of {resolution record, flags[nAmp]}
+        case GF_OP_AMP4_TD: if constexpr((HAS & GF_HAS_AMP4_TD) != 0) { // physics/Amp4Body_TD.cu:167-261 ; ints[4] = offset of {resolution record, flags[nAmp]}
             const int32_t *ob = P.ints + nd.obs_off;
             double eff = st[--sp];
             long e = evt.event_number(ob[5]);
             const int32_t *td = in + in[4];
             const double2 *w = static_cast<const double2 *>(P.aux[in[0]]) + e;
             long ld = P.aux_ld[in[0]];
+            const double dtime = evt(ob[6]), sigma = evt(ob[7]); // requested before the amplitude walk, used after it
             double Are, Aim, Bre, Bim;
-            gf_amp4td_AB(p, td + 1, in[3], [&](int i) { return __ldg(w + (size_t)i * ld); }, Are, Aim, Bre, Bim);
+            gf_amp4td_AB<(HAS == GF_HAS_AMP4_TD) ? GF_TD_CH : ((HAS == (GF_HAS_AMP4_TD | GF_HAS_3GAUSS)) ? 4 : 1)>(p, td + 1, in[3], [&](int i) { return __ldg(w + (size_t)i * ld); }, Are, Aim,
+                                                          Bre, Bim);
             double nA = Are * Are + Aim * Aim, nB = Bre * Bre + Bim * Bim;
             double t3re = Are * Bre + Aim * Bim, t3im = Aim * Bre - Are * Bim; // A conj(B)
             const gf_node &rn = P.nodes[td[0]];
-            double ret = gf_tres(rn.op, P.params + rn.par_off, nA + nB, nA - nB, t3re, t3im, p[0], evt(ob[6]), p[1], p[2],
-                                 evt(ob[7]));
+            double ret = gf_tres<(HAS & GF_HAS_3GAUSS) != 0>(rn.op, P.params + rn.par_off, nA + nB, nA - nB, t3re, t3im, p[0], dtime, p[1],
+                                                             p[2], sigma);
             st[sp++] = ret * eff;
         } break;
         default: st[sp++] = 0.0; break;

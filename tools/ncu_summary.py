@@ -24,7 +24,7 @@ scale = {"ns": 1e-3, "us": 1.0, "ms": 1e3, "s": 1e6, "byte": 1.0, "Kbyte": 1e3, 
 out = [["kernel"] + list(K) + ["fp64_flops", "fp64_tflops", "dram_GBps"]]
 traffic = {}
 for r in data:
-    name = r[col["Kernel Name"]].split("(")[0]
+    name = r[col["Kernel Name"]].split("(")[0].split("<")[0].replace("void ", "").strip()  # "void k_eval_sum<2>(...)" -> k_eval_sum
     row = [name]
     vals = {}
     for k, m in K.items():
