@@ -97,12 +97,12 @@ def four_body(gf, lib, ctx, kind, n_data, n_mc, steps, peak_hbm):
     rng = np.random.default_rng(99)
     if kind == "dp4":
         M = DP4(mc_events=0, float_ls=True)
-        namp, bytes_evt = 8, 8 * 16 + 8
+        namp, bytes_evt = 8, 8 * 16  # cached amplitudes only: the flat background and constant efficiency read no column
         d = M.dataset(list(_tile(ph, n_data)))
         movers = M.coefs[:6]
     else:
         M = TDDP4(three_gauss=False, float_ls=True, float_mix=True)
-        namp, bytes_evt = 6, 6 * 16 + 8 + 16
+        namp, bytes_evt = 6, 6 * 16 + 16  # cached amplitudes + decay time and its error
         cols = list(_tile(ph, n_data))
         cols.append(rng.exponential(0.4101, n_data).clip(0, 9.99))
         cols.append(rng.uniform(0.02, 0.08, n_data))

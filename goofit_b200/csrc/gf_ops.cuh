@@ -50,6 +50,7 @@ __device__ inline double gf_leaf(const gf_node &nd, const gf_sprog &P, const Evt
         double x = evt(ob[0]), mean = p[0], sigma = p[1];
         return exp(-0.5 * (x - mean) * (x - mean) / (sigma * sigma));
     }
+    case GF_OP_CONSTANT: return p[nd.npar - 1]; // p * pow(x, 0): the flat background / constant efficiency of every shipped example
     case GF_OP_POLYNOMIAL: { // basic/PolynomialPdf.cu:8-25
         int lowest = (int)c[0];
         double x = evt(ob[0]), ret = 0;

@@ -34,6 +34,7 @@ class PolynomialPdf : public GooPdf { // basic/PolynomialPdf.h
 
   private:
     std::unique_ptr<Variable> center;
+    bool multiDim = false;
 };
 
 class ArgusPdf : public GooPdf { // basic/ArgusPdf.h

@@ -52,7 +52,8 @@ PolynomialPdf::PolynomialPdf(std::string n, Observable _x, std::vector<Variable>
     : GooPdf("PolynomialPdf", n, _x) {
     registerConstant(lowestDegree);
     for(Variable &v : weights) registerParameter(v);
-    registerFunction("ptr_to_Polynomial", GF_OP_POLYNOMIAL);
+    // w0 * pow(x, 0) is w0 for every x (NaN included): the record needs no observable read on the device
+    registerFunction("ptr_to_Polynomial", (weights.size() == 1 && lowestDegree == 0) ? GF_OP_CONSTANT : GF_OP_POLYNOMIAL);
 }
 PolynomialPdf::PolynomialPdf(std::string n, Observable _x, std::vector<Variable> weights, Variable x0, unsigned int lowestDegree)
     : GooPdf("PolynomialPdf", n, _x)
@@ -83,7 +84,8 @@ PolynomialPdf::PolynomialPdf(std::string n, std::vector<Observable> obses, std::
         offsets.emplace_back(getName() + "_extra_offset_" + std::to_string(offsets.size()), 0);
     for(auto &o : offsets) registerParameter(o);
     for(auto &c : coeffs) registerParameter(c);
-    registerFunction("ptr_to_MultiPolynomial", GF_OP_MULTI_POLYNOMIAL);
+    multiDim = true;
+    registerFunction("ptr_to_MultiPolynomial", maxDegree == 0 ? GF_OP_CONSTANT : GF_OP_MULTI_POLYNOMIAL); // degree 0: the one coefficient
 }
 fptype PolynomialPdf::integrate(fptype lo, fptype hi) const { // PolynomialPdf.cu:217-243 (marked wrong upstream; unused: no hasAnalyticIntegral)
     fptype lowestDegree = constantsList[0];
@@ -102,7 +104,7 @@ fptype PolynomialPdf::integrate(fptype lo, fptype hi) const { // PolynomialPdf.c
     return ret;
 }
 fptype PolynomialPdf::getCoefficient(int coef) {
-    if(opcode_ == GF_OP_MULTI_POLYNOMIAL) throw GeneralError("getCoefficient method of PolynomialPdf not implemented for multi-dimensional polynomials.");
+    if(multiDim) throw GeneralError("getCoefficient method of PolynomialPdf not implemented for multi-dimensional polynomials.");
     int lowest = (int)constantsList[0];
     if(coef < lowest) return 0;
     size_t idx = coef - lowest;

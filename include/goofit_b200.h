@@ -63,6 +63,8 @@ enum gf_op {
     GF_OP_KINLIMITBW,       /* KinLimitBWPdf.cu:26 */
     GF_OP_SCALED_GAUSSIAN,  /* ScaledGaussianPdf.cu:9 */
     GF_OP_JOHNSONSU,        /* JohnsonSUPdf.cu:8 */
+    GF_OP_CONSTANT,         /* a polynomial with only its x^0 term (PolynomialPdf.cu:8-25 with one weight and lowest degree 0,
+                               :47-118 with maxDegree 0): the last parameter of the record; no observable is read */
     GF_OP_ADD = 32,         /* AddPdf.cu:16  ints: child norm slots */
     GF_OP_ADD_EXT,          /* AddPdf.cu:53 */
     GF_OP_PROD,             /* ProdPdf.cu:9 */
