@@ -79,6 +79,23 @@ class RhoOmegaMix : public ResonancePdf { // resonances/RhoOmegaMix.cu:139-167 (
 };
 } // namespace Resonances
 
+/// What GenerateSig returns (Amp3Body.cu:430-547, Amp4Body.cu:560-677 return the same four things as MCBooster
+/// containers): particles[d][4*event + {E, px, py, pz}], variables[v][event], the phase-space weight times the
+/// un-normalised PDF value, and the accept/reject flag of each event.
+struct GeneratedSignal {
+    std::vector<std::vector<fptype>> particles;
+    std::vector<std::vector<fptype>> variables;
+    std::vector<fptype> weights;
+    std::vector<bool> flags;
+};
+/// GENBOD phase-space events of mother -> 3 or 4 daughters from a counter-based generator: event i of a given seed is
+/// the same whatever the batch it is generated in (`offset` = index of the first event). Stand-in for
+/// mcbooster::PhaseSpace (not part of the reference checkout); weights are relative to the largest possible weight.
+void generatePhaseSpaceParticles(const std::vector<fptype> &mother_and_daughter_masses, size_t nEvents, unsigned long seed,
+                                 size_t offset, std::vector<std::vector<fptype>> &particles, std::vector<fptype> &weights);
+/// Amp3BodyBase::fillMCFlags (Amp3BodyBase.cu:13-21): accept event i when weight_i / max weight beats a uniform number
+std::vector<bool> acceptRejectFlags(const std::vector<fptype> &weights, unsigned long seed, size_t offset);
+
 struct DecayInfo3 { // DalitzPlotHelpers.h:83-92
     fptype motherMass;
     fptype daug1Mass;
@@ -107,6 +124,11 @@ class Amp3Body : public Amp3BodyBase { // Amp3Body.h:43-111
     DecayInfo3 &getDecayInfo() { return decayInfo; }
     static void resetCacheCounter() {}
     std::vector<std::vector<fptype>> fit_fractions();
+    /// Amp3Body.cu:430-547: phase-space events, their (m12^2, m23^2, m13^2), weight x |sum c A|^2 x efficiency, and
+    /// accept/reject flags. As upstream, the generated events REPLACE the PDF's dataset. seed 0 = seed 0 (upstream draws one).
+    GeneratedSignal GenerateSig(unsigned int numEvents, int seed = 0);
+    void setGenerationOffset(int off) { generation_offset = off; }
+    int getGenerationOffset() const { return generation_offset; }
     /// normalisation integrals I_ij of the last normalize() (row i, column j)
     const std::vector<fpcomplex> &getIntegrals() const { return integrals; }
     friend DalitzPlotter;
@@ -126,6 +148,8 @@ class Amp3Body : public Amp3BodyBase { // Amp3Body.h:43-111
     bool forceRedoIntegrals{true};
     bool cacheAllocated{false};
     int totalEventSize{3};
+    int generation_offset{0};
+    std::unique_ptr<UnbinnedDataSet> generated; // keeps the events of the last GenerateSig alive while they are the dataset
 };
 
 /// Host helper that evaluates the PDF on the Dalitz grid and draws toy events from it

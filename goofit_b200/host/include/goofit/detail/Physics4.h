@@ -177,9 +177,16 @@ class Amp4Body : public Amp4BodyBase { // Amp4Body.h:33-95
     void setDataSize(unsigned int dataSize, unsigned int evtSize = 6) { setDataSizeCommon(dataSize, evtSize); }
     int getMCevents() { return static_cast<int>(MCevents); }
     int emit(detail::ProgramBuilder &B) override;
+    /// Amp4Body.cu:560-677: phase-space events, their (m12, m34, cos12, cos34, phi), weight x |sum c A|^2 x efficiency,
+    /// accept/reject flags. As upstream, the generated events REPLACE the PDF's dataset.
+    GeneratedSignal GenerateSig(unsigned int numEvents, int seed = 0);
+    void setGenerationOffset(int off) { generation_offset = off; }
+    int getGenerationOffset() const { return generation_offset; }
 
   protected:
     DecayInfo4 decayInfo;
+    int generation_offset{0};
+    std::unique_ptr<UnbinnedDataSet> generated;
 };
 
 // ---- time-dependent four-body amplitude ------------------------------------------------------------------------------

@@ -250,6 +250,37 @@ fpcomplex Amp3Body::sumCachedWave(size_t i) const {
     auto w = getCachedWave(i);
     return std::accumulate(w.begin(), w.end(), fpcomplex(0, 0));
 }
+GeneratedSignal Amp3Body::GenerateSig(unsigned int numEvents, int seed) {
+    GeneratedSignal G;
+    generatePhaseSpaceParticles({decayInfo.motherMass, decayInfo.daug1Mass, decayInfo.daug2Mass, decayInfo.daug3Mass}, numEvents,
+                                static_cast<unsigned long>(seed), generation_offset, G.particles, G.weights);
+    auto pairMass2 = [&](int a, int b, size_t i) { // detail/Dim2.h:22-35
+        const fptype *p = G.particles[a].data() + 4 * i, *q = G.particles[b].data() + 4 * i;
+        fptype e = p[0] + q[0], x = p[1] + q[1], y = p[2] + q[2], z = p[3] + q[3];
+        return e * e - x * x - y * y - z * z;
+    };
+    G.variables.assign(3, std::vector<fptype>(numEvents)); // m12^2, m23^2, m13^2 in upstream's order
+    std::vector<fptype> evt(numEvents);
+    for(size_t i = 0; i < numEvents; i++) {
+        G.variables[0][i] = pairMass2(0, 1, i);
+        G.variables[1][i] = pairMass2(1, 2, i);
+        G.variables[2][i] = pairMass2(0, 2, i);
+        evt[i]            = static_cast<fptype>(i);
+    }
+    generated = std::make_unique<UnbinnedDataSet>(std::vector<Observable>{_m12, _m13, _eventNumber});
+    generated->appendColumns({G.variables[0].data(), G.variables[2].data(), evt.data()}, numEvents);
+    setData(generated.get());
+    setDataSize(numEvents, 3);
+    auto fc = fitControl;
+    setFitControl(std::make_shared<EvalFit>()); // the un-normalised value, upstream's ProbFit with the normalisation forced to 1
+    normalize();
+    std::vector<fptype> values = evaluate_with_metric();
+    setFitControl(fc);
+    for(size_t i = 0; i < numEvents; i++) G.weights[i] *= values[i];
+    G.flags = acceptRejectFlags(G.weights, static_cast<unsigned long>(seed), generation_offset);
+    return G;
+}
+
 std::vector<std::vector<fptype>> Amp3Body::fit_fractions() { // Amp3Body.cu:376-428, host sums over the cached waves
     size_t n_res = decayInfo.resonances.size();
     std::vector<std::vector<std::complex<fptype>>> w(n_res);

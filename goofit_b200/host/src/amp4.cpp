@@ -245,10 +245,108 @@ std::vector<std::vector<fptype>> generatePhaseSpace5(const std::vector<fptype> &
     return cols;
 }
 
+void generatePhaseSpaceParticles(const std::vector<fptype> &pm, size_t n, unsigned long seed, size_t offset,
+                                 std::vector<std::vector<fptype>> &particles, std::vector<fptype> &weights) {
+    const int nd = static_cast<int>(pm.size()) - 1;
+    if(nd != 3 && nd != 4) throw GeneralError("generatePhaseSpaceParticles: 3 or 4 daughters, got {}", nd);
+    const double M = pm[0];
+    const double *m = pm.data() + 1;
+    double tecm = M;
+    for(int k = 0; k < nd; k++) tecm -= m[k];
+    if(tecm <= 0) throw GeneralError("generatePhaseSpaceParticles: not enough energy");
+    double emmax = tecm + m[0], emmin = 0, wtmax = 1;
+    for(int k = 1; k < nd; k++) {
+        emmin += m[k - 1];
+        emmax += m[k];
+        wtmax *= pdk(emmax, emmin, m[k]);
+    }
+    particles.assign(nd, std::vector<fptype>(4 * n));
+    weights.assign(n, 0.0);
+    for(size_t i = 0; i < n; i++) {
+        const uint64_t ev = i + offset;
+        uint64_t ctr = 0;
+        double rno[4] = {0, 0, 0, 0}, inv[4], pd[3], sum = 0;
+        for(int k = 1; k < nd - 1; k++) rno[k] = uniform01(seed, ev, ctr++);
+        if(nd == 4 && rno[1] > rno[2]) std::swap(rno[1], rno[2]);
+        rno[nd - 1] = 1;
+        for(int k = 0; k < nd; k++) {
+            sum += m[k];
+            inv[k] = rno[k] * tecm + sum;
+        }
+        double wt = 1.0 / wtmax;
+        for(int k = 0; k < nd - 1; k++) {
+            pd[k] = pdk(inv[k + 1], inv[k], m[k + 1]);
+            wt *= pd[k];
+        }
+        V4 p[4];
+        p[0] = {std::sqrt(pd[0] * pd[0] + m[0] * m[0]), 0, pd[0], 0};
+        for(int d = 1;; d++) { // sequential two-body decays, each rotated at random and boosted into its parent's frame
+            p[d] = {std::sqrt(pd[d - 1] * pd[d - 1] + m[d] * m[d]), 0, -pd[d - 1], 0};
+            double cZ = 2 * uniform01(seed, ev, ctr++) - 1, sZ = std::sqrt(1 - cZ * cZ);
+            double ang = 2 * M_PI * uniform01(seed, ev, ctr++), cY = std::cos(ang), sY = std::sin(ang);
+            for(int j = 0; j <= d; j++) {
+                double x = p[j].x, y = p[j].y;
+                p[j].x = cZ * x - sZ * y;
+                p[j].y = sZ * x + cZ * y;
+                x = p[j].x;
+                double z = p[j].z;
+                p[j].x = cY * x - sY * z;
+                p[j].z = sY * x + cY * z;
+            }
+            if(d == nd - 1) break;
+            double beta = pd[d] / std::sqrt(pd[d] * pd[d] + inv[d] * inv[d]);
+            for(int j = 0; j <= d; j++) boost(p[j], 0, beta, 0);
+        }
+        for(int d = 0; d < nd; d++) {
+            fptype *o = particles[d].data() + 4 * i;
+            o[0] = p[d].e; o[1] = p[d].x; o[2] = p[d].y; o[3] = p[d].z;
+        }
+        weights[i] = wt;
+    }
+}
+std::vector<bool> acceptRejectFlags(const std::vector<fptype> &w, unsigned long seed, size_t offset) {
+    fptype wmax = 0;
+    for(fptype v : w) wmax = std::max(wmax, v);
+    std::vector<bool> flags(w.size());
+    for(size_t i = 0; i < w.size(); i++) flags[i] = wmax > 0 && w[i] / wmax > uniform01(seed, i + offset, 2000);
+    return flags;
+}
+
 std::vector<bool> unweightPhaseSpace(const std::vector<fptype> &w, unsigned long seed) {
     std::vector<bool> flags(w.size());
     for(size_t i = 0; i < w.size(); i++) flags[i] = w[i] > uniform01(seed, i, 1000);
     return flags;
+}
+
+GeneratedSignal Amp4Body::GenerateSig(unsigned int numEvents, int seed) {
+    GeneratedSignal G;
+    generatePhaseSpaceParticles(decayInfo.particle_masses, numEvents, static_cast<unsigned long>(seed), generation_offset, G.particles,
+                                G.weights);
+    G.variables.assign(5, std::vector<fptype>(numEvents));
+    for(size_t i = 0; i < numEvents; i++) {
+        fptype in[16], out[5];
+        for(int d = 0; d < 4; d++)
+            for(int k = 0; k < 4; k++) in[4 * d + k] = G.particles[d][4 * i + k];
+        fourVectorsToDim5(in, out);
+        for(int k = 0; k < 5; k++) G.variables[k][i] = out[k];
+    }
+    std::vector<fptype> evt(numEvents);
+    std::iota(evt.begin(), evt.end(), 0.0);
+    std::vector<Observable> obs(observablesList.begin(), observablesList.begin() + 6);
+    generated = std::make_unique<UnbinnedDataSet>(obs);
+    generated->appendColumns({G.variables[0].data(), G.variables[1].data(), G.variables[2].data(), G.variables[3].data(),
+                              G.variables[4].data(), evt.data()},
+                             numEvents);
+    setData(generated.get());
+    setDataSize(numEvents, 6);
+    auto fc = fitControl;
+    setFitControl(std::make_shared<EvalFit>()); // the un-normalised value, upstream's ProbFit with the normalisation forced to 1
+    normalize();
+    std::vector<fptype> values = evaluate_with_metric();
+    setFitControl(fc);
+    for(size_t i = 0; i < numEvents; i++) G.weights[i] *= values[i];
+    G.flags = acceptRejectFlags(G.weights, static_cast<unsigned long>(seed), generation_offset);
+    return G;
 }
 
 // ---- what Amp4Body and Amp4Body_TD share ------------------------------------------------------------------------

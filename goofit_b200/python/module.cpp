@@ -19,6 +19,7 @@ using namespace pybind11::literals;
 using namespace GooFit;
 
 void init_physics4(py::module &m);
+py::tuple generated_to_numpy(const GooFit::GeneratedSignal &G, int ncomp);
 
 
 template <class DS>
@@ -344,6 +345,13 @@ PYBIND11_MODULE(_goofit, m) {
         .def("sumCachedWave", &Amp3Body::sumCachedWave, "i"_a)
         .def("getIntegrals", [](const Amp3Body &a) { return py::array(py::cast(a.getIntegrals())); })
         .def("fit_fractions", &Amp3Body::fit_fractions)
+        .def("setGenerationOffset", &Amp3Body::setGenerationOffset, "off"_a)
+        .def("getGenerationOffset", &Amp3Body::getGenerationOffset)
+        // upstream's binding exports three of the four components of each particle (python/PDFs/physics/Amp3Body.cpp:49-62)
+        .def(
+            "GenerateSig",
+            [](Amp3Body &self, size_t numEvents, int seed) { return generated_to_numpy(self.GenerateSig(numEvents, seed), 3); },
+            "numEvents"_a, "seed"_a = 0)
         .def("getDecayInfo", &Amp3Body::getDecayInfo, py::return_value_policy::reference_internal);
     py::class_<DalitzPlotter>(m, "DalitzPlotter")
         .def(py::init<GooPdf *, Amp3Body *>(), "overallSignal"_a, "signalDalitz"_a, py::keep_alive<1, 2>(), py::keep_alive<1, 3>())

@@ -18,6 +18,27 @@ static void bind_ls(py::module &m, const char *name) {
         "L"_a, "Mpair"_a, "FormFac"_a = FF::BL_Prime, "radius"_a = 1.5);
 }
 
+// (particles[nd, N, 4] as (E, px, py, pz), variables[nv, N], weights[N], flags[N]) -- python/PDFs/physics/Amp4Body.cu:36-74
+py::tuple generated_to_numpy(const GeneratedSignal &G, int ncomp) {
+    const size_t nd = G.particles.size(), nv = G.variables.size(), n = G.weights.size();
+    py::array_t<fptype> particles({nd, n, (size_t)ncomp}), variables({nv, n}), weights((py::ssize_t)n);
+    py::array_t<bool> flags((py::ssize_t)n);
+    auto P = particles.mutable_unchecked<3>();
+    auto V = variables.mutable_unchecked<2>();
+    auto W = weights.mutable_unchecked<1>();
+    auto F = flags.mutable_unchecked<1>();
+    for(size_t d = 0; d < nd; d++)
+        for(size_t i = 0; i < n; i++)
+            for(int k = 0; k < ncomp; k++) P(d, i, k) = G.particles[d][4 * i + k];
+    for(size_t v = 0; v < nv; v++)
+        for(size_t i = 0; i < n; i++) V(v, i) = G.variables[v][i];
+    for(size_t i = 0; i < n; i++) {
+        W(i) = G.weights[i];
+        F(i) = G.flags[i];
+    }
+    return py::make_tuple(particles, variables, weights, flags);
+}
+
 void init_physics4(py::module &m) {
     py::enum_<DP4Pair>(m, "DP4Pair")
         .value("M_12", M_12).value("M_34", M_34).value("M_13", M_13).value("M_14", M_14).value("M_23", M_23).value("M_24", M_24)
@@ -107,6 +128,12 @@ void init_physics4(py::module &m) {
         .def(py::init<std::string, std::vector<Observable>, DecayInfo4, GooPdf *, unsigned int>(), "name"_a, "observables"_a,
              "decay"_a, "eff"_a, "MCeventsNorm"_a = 5000000, py::keep_alive<1, 4>(), py::keep_alive<1, 5>())
         .def("setDataSize", &Amp4Body::setDataSize, "dataSize"_a, "evtSize"_a = 6)
+        .def("setGenerationOffset", &Amp4Body::setGenerationOffset, "off"_a)
+        .def("getGenerationOffset", &Amp4Body::getGenerationOffset)
+        .def(
+            "GenerateSig",
+            [](Amp4Body &self, size_t numEvents, int seed) { return generated_to_numpy(self.GenerateSig(numEvents, seed), 4); },
+            "numEvents"_a, "seed"_a = 0)
         .def("getMCevents", &Amp4Body::getMCevents);
     // time-dependent: python/PDFs/physics/{Amp4Body_TD.cu:18-38,TruthResolution.cpp,ThreeGaussResolution.cpp,DalitzPlotHelpers.cpp}
     py::class_<MixingTimeResolution, GooPdf>(m, "MixingTimeResolution").def("normalization", &MixingTimeResolution::normalization);
@@ -130,6 +157,17 @@ void init_physics4(py::module &m) {
         .def("setDataSize", &Amp4Body_TD::setDataSize, "dataSize"_a, "evtSize"_a = 8)
         .def("getNumAccNormEvents", &Amp4Body_TD::getNumAccNormEvents)
         .def("getSumInitNormEventWeights", &Amp4Body_TD::getSumInitNormEventWeights);
+    m.def(
+        "generatePhaseSpaceParticles",
+        [](std::vector<fptype> masses, size_t n, unsigned long seed, size_t offset) {
+            GeneratedSignal G;
+            generatePhaseSpaceParticles(masses, n, seed, offset, G.particles, G.weights);
+            G.flags.assign(n, false);
+            py::tuple t = generated_to_numpy(G, 4);
+            return py::make_tuple(t[0], t[2]);
+        },
+        "mother_and_daughter_masses"_a, "nEvents"_a, "seed"_a = 0, "offset"_a = 0,
+        "GENBOD phase-space events for 3 or 4 daughters: (particles[nd, N, 4] as (E, px, py, pz), weights[N])");
     m.def("generatePhaseSpace5",
           [](std::vector<fptype> masses, size_t n, unsigned long seed) {
               std::vector<fptype> w;

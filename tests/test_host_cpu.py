@@ -261,3 +261,32 @@ def test_spline_second_derivatives_against_scipy():
     np.testing.assert_allclose(got, want, rtol=1e-10, atol=1e-12)
     with pytest.raises(Exception):
         gf.Resonances.Spline.secondDerivatives([0.0, 1.0], [1.0])
+
+
+def test_phase_space_generator_properties():
+    """generatePhaseSpaceParticles (stand-in for mcbooster::PhaseSpace in GenerateSig): momentum conservation, on-shell
+    daughters, counter-based reproducibility across batches, and agreement with the 4-body generator behind the
+    normalisation samples."""
+    for masses in ([1.86484, 0.1349766, 0.13957018, 0.13957018], [1.8645, 0.13957018, 0.13957018, 0.493677, 0.13957018]):
+        P, w = gf.generatePhaseSpaceParticles(masses, 2000, 17, 0)
+        nd = len(masses) - 1
+        assert P.shape == (nd, 2000, 4) and w.shape == (2000,)
+        tot = P.sum(axis=0)
+        np.testing.assert_allclose(tot[:, 0], masses[0], rtol=1e-12)
+        np.testing.assert_allclose(tot[:, 1:], 0, atol=1e-12)
+        for d in range(nd):
+            m2 = P[d, :, 0] ** 2 - (P[d, :, 1:] ** 2).sum(axis=1)
+            np.testing.assert_allclose(m2, masses[1 + d] ** 2, atol=1e-12)
+        assert np.all(w > 0) and np.all(w <= 1.0)
+        P2, w2 = gf.generatePhaseSpaceParticles(masses, 500, 17, 1500)  # events 1500..1999 of the same stream
+        assert np.array_equal(P2, P[:, 1500:, :]) and np.array_equal(w2, w[1500:])
+        P3, _ = gf.generatePhaseSpaceParticles(masses, 100, 18, 0)
+        assert not np.array_equal(P3, P[:, :100, :])
+    masses = [1.8645, 0.13957018, 0.13957018, 0.493677, 0.13957018]
+    P, w = gf.generatePhaseSpaceParticles(masses, 300, 4242, 0)
+    cols, w5 = gf.generatePhaseSpace5(masses, 300, 4242)
+    m12 = np.sqrt((P[0, :, 0] + P[1, :, 0]) ** 2 - ((P[0, :, 1:] + P[1, :, 1:]) ** 2).sum(axis=1))
+    np.testing.assert_allclose(m12, cols[0], rtol=1e-12)
+    np.testing.assert_allclose(w, w5, rtol=1e-14)
+    with pytest.raises(Exception):
+        gf.generatePhaseSpaceParticles([1.0, 0.6, 0.6, 0.1], 10, 1, 0)

@@ -2,6 +2,7 @@
 oracle/ref_driver.cpp). Every test calls the product through the host API -> C ABI -> sm_100a kernels.
 Tolerances: per-event values 1e-12 relative (libm vs CUDA libm differ at the ulp level); NLL sums 1e-12
 relative (north star); fitted parameters 0.01 sigma (north star)."""
+import math
 import os
 
 import numpy as np
@@ -552,3 +553,51 @@ def test_cpp_example_exponential():
         pytest.skip("examples/bin/exponential not built")
     r = subprocess.run([exe, "--nosplash", "-q"], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+def test_generate_sig_three_and_four_body():
+    """Amp3Body::GenerateSig / Amp4Body::GenerateSig (Amp3Body.cu:430-547, Amp4Body.cu:560-677): the returned weight is the
+    phase-space weight times the un-normalised PDF value at the generated point; checked against the cached waves /
+    amplitudes of those very events, which the call leaves installed as the PDF's dataset (as upstream does)."""
+    from models import DP4
+    M = Dalitz(float_masses=False, grid=120)
+    s = M.signal
+    n = 20000
+    P, V, w, flags = s.GenerateSig(n, 11)
+    assert P.shape == (3, n, 3) and V.shape == (3, n) and w.shape == (n,) and flags.shape == (n,)
+    masses = [1.86484, 0.1349766, 0.13957018, 0.13957018]
+    P4, w_ps = gf.generatePhaseSpaceParticles(masses, n, 11, 0)
+    assert np.array_equal(P, P4[:, :, :3])
+    m12 = (P4[0, :, 0] + P4[1, :, 0]) ** 2 - ((P4[0, :, 1:] + P4[1, :, 1:]) ** 2).sum(axis=1)
+    np.testing.assert_allclose(V[0], m12, rtol=1e-13)
+    np.testing.assert_allclose(V.sum(axis=0), sum(m * m for m in masses), rtol=1e-12)  # m12^2 + m23^2 + m13^2
+    coef = np.array([M.coefs[2 * i].value + 1j * M.coefs[2 * i + 1].value for i in range(16)])
+    tot = sum(coef[i] * np.asarray(s.getCachedWave(i)) for i in range(16))
+    np.testing.assert_allclose(w, w_ps * np.abs(tot) ** 2, rtol=1e-11)
+    frac = flags.mean()
+    assert abs(frac - w.mean() / w.max()) < 5 * math.sqrt(frac * (1 - frac) / n) + 1e-3
+    # a second batch continues the stream
+    s.setGenerationOffset(n)
+    P2, _, _, _ = s.GenerateSig(100, 11)
+    assert np.array_equal(P2, gf.generatePhaseSpaceParticles(masses, 100, 11, n)[0][:, :, :3])
+    # the model can still be fitted to a dataset afterwards
+    acc = np.flatnonzero(flags)
+    d = M.dataset(V[0][acc], V[2][acc])
+    s.setData(d)
+    s.setDataSize(len(d))
+    assert np.isfinite(s.calculateNLL())
+
+    D = DP4(mc_events=20000, float_ls=False)
+    n4 = 5000
+    P, V, w, flags = D.dp.GenerateSig(n4, 5)
+    assert P.shape == (4, n4, 4) and V.shape == (5, n4)
+    masses4 = [1.8645, 0.13957018, 0.13957018, 0.493677, 0.13957018]
+    _, w_ps = gf.generatePhaseSpaceParticles(masses4, n4, 5, 0)
+    cols, _ = gf.generatePhaseSpace5(masses4, n4, 5)
+    np.testing.assert_allclose(V, np.asarray(cols), rtol=1e-12, atol=1e-12)
+    # info.amplitudes order is (KF, AS, AP, AD, KK, K1R, A1R, A1RD); coefs were created AS, AP, AD, KF, ...
+    order = [3, 0, 1, 2, 4, 5, 6, 7]
+    coef = np.array([D.coefs[2 * k].value + 1j * D.coefs[2 * k + 1].value for k in order])
+    tot = sum(coef[a] * np.asarray(D.dp.getCachedAmp(a)) for a in range(8))
+    np.testing.assert_allclose(w, w_ps * np.abs(tot) ** 2, rtol=1e-10)
+    assert 0 < flags.mean() < 1
