@@ -290,3 +290,22 @@ def test_phase_space_generator_properties():
     np.testing.assert_allclose(w, w5, rtol=1e-14)
     with pytest.raises(Exception):
         gf.generatePhaseSpaceParticles([1.0, 0.6, 0.6, 0.1], 10, 1, 0)
+
+
+def test_resonance_and_lineshape_zoo_host_side():
+    """The zoo3 / zoo4 models build without a GPU (records are only flattened at setData), reject malformed input the way
+    the reference does, and refuse to evaluate without a device."""
+    from models import Zoo3, Zoo4
+    Z3 = Zoo3(grid=30)
+    assert len(Z3.resonances) == 11
+    assert len([v for v in Z3.pars if v.name.startswith("sp_")]) == 16
+    Z4 = Zoo4()
+    assert Z4.dp.numAmplitudes() == 5 and Z4.dp.numLineshapes() == 10 and Z4.dp.numSpinFactors() == 9
+    V = gf.Variable
+    with pytest.raises(Exception, match="five necessary variables"):
+        gf.Lineshapes.GLASS("g", V("m", 1.4), V("w", 0.3), 0, int(gf.DP4Pair.M_34), gf.FF.BL2, 1.5, [V("a", 1.0)])
+    with pytest.raises(Exception):
+        gf.Resonances.Spline("s", V("r", 1), V("i", 0), [0.1, 0.5, 1.0], [V("a0", 1), V("a1", 1)], [V("b0", 0), V("b1", 0)], 0)
+    assert int(gf.Lineshapes.FOCUS.Mod.Kpi) == 0 and int(gf.Lineshapes.FOCUS.Mod.I32) == 2
+    with pytest.raises(Exception):
+        Z3.signal.GenerateSig(10, 1)  # no device: must fail loudly, never fall back
