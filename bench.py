@@ -48,7 +48,9 @@ def run_reference(config, n_events, steps, warmup):
     if not os.path.exists(REF_DRIVER):
         return None
     env = dict(os.environ)
-    env.setdefault("OMP_NUM_THREADS", str(host_cores()))
+    # torch.distributed.run exports OMP_NUM_THREADS=1 to its workers: the reference arm must not inherit that
+    env["OMP_NUM_THREADS"] = str(host_cores())
+    env.pop("OMP_PROC_BIND", None)
     out = subprocess.run([REF_DRIVER, "bench", config, str(n_events), str(steps), str(warmup)], env=env,
                          capture_output=True, text=True, timeout=1500)
     for line in out.stdout.splitlines()[::-1]:

@@ -16,6 +16,8 @@ struct gf_amp3_state {
     double2 *d_gridB = nullptr; // [n_res][n_bins]
     double *d_gridEff = nullptr;
     double *d_I = nullptr;      // [n_res*n_res*2]
+    int *d_pairs = nullptr;     // [n_res*(n_res+1)] pair list of the Gram kernel, uploaded through h_pairs (pinned)
+    int *h_pairs = nullptr;
     bool grid_valid = false;
 };
 
@@ -31,7 +33,8 @@ static gf_amp3_state *find_amp3(gf_ctx *c, int node, bool create) {
 
 void gf_amp3_free(gf_ctx *c) {
     for(auto *s : c->amp3) {
-        cudaFree(s->d_waves); cudaFree(s->d_gridB); cudaFree(s->d_gridEff); cudaFree(s->d_I);
+        cudaFree(s->d_waves); cudaFree(s->d_gridB); cudaFree(s->d_gridEff); cudaFree(s->d_I); cudaFree(s->d_pairs);
+        if(s->h_pairs) cudaFreeHost(s->h_pairs);
         delete s;
     }
     c->amp3.clear();
@@ -166,6 +169,10 @@ extern "C" int gf_amp3_alloc(gf_ctx *c, int node, size_t n_events) {
     GF_CUDA(cudaMalloc(&s->d_waves, sizeof(double2) * (size_t)s->ld * s->n_res));
     GF_CUDA(cudaMemsetAsync(s->d_waves, 0, sizeof(double2) * (size_t)s->ld * s->n_res, c->stream));
     if(!s->d_I) GF_CUDA(cudaMalloc(&s->d_I, sizeof(double) * 2 * s->n_res * s->n_res));
+    if(!s->d_pairs) {
+        GF_CUDA(cudaMalloc(&s->d_pairs, sizeof(int) * s->n_res * (s->n_res + 1)));
+        GF_CUDA(cudaMallocHost(&s->h_pairs, sizeof(int) * s->n_res * (s->n_res + 1)));
+    }
     c->view.aux[s->slot] = s->d_waves;
     c->view.aux_ld[s->slot] = s->ld;
     return 0;
@@ -236,15 +243,13 @@ extern "C" int gf_amp3_integrals(gf_ctx *c, int node, const uint8_t *redo_mask, 
         for(int j = i; j < s->n_res; j++)
             if(((mask >> i) & 1ull) || ((mask >> j) & 1ull)) { pairs.push_back(i); pairs.push_back(j); }
     if(!pairs.empty()) {
-        int *d_pairs = nullptr;
-        GF_CUDA(cudaMalloc(&d_pairs, sizeof(int) * pairs.size()));
-        GF_CUDA(cudaMemcpyAsync(d_pairs, pairs.data(), sizeof(int) * pairs.size(), cudaMemcpyHostToDevice, c->stream));
+        // the pinned list is free again: every earlier call ended with the stream synchronisation below
+        std::memcpy(s->h_pairs, pairs.data(), sizeof(int) * pairs.size());
+        GF_CUDA(cudaMemcpyAsync(s->d_pairs, s->h_pairs, sizeof(int) * pairs.size(), cudaMemcpyHostToDevice, c->stream));
         k_amp3_gram<<<(int)(pairs.size() / 2), GF_THREADS, 0, c->stream>>>(s->d_gridB, s->d_gridEff, n_bins, s->n_res,
-                                                                         d_pairs, s->d_I);
+                                                                         s->d_pairs, s->d_I);
         c->launches++;
         GF_CUDA(cudaGetLastError());
-        GF_CUDA(cudaStreamSynchronize(c->stream));
-        cudaFree(d_pairs);
     }
     GF_CUDA(cudaMemcpyAsync(I_re_im, s->d_I, sizeof(double) * 2 * s->n_res * s->n_res, cudaMemcpyDeviceToHost, c->stream));
     GF_CUDA(cudaStreamSynchronize(c->stream));

@@ -205,20 +205,32 @@ extern "C" gf_ctx *gf_create(int device_id) {
     cudaDeviceProp prop;
     cudaGetDeviceProperties(&prop, device_id);
     c->sm_count = prop.multiProcessorCount;
-    cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
-    cudaEventCreate(&c->ev0);
-    cudaEventCreate(&c->ev1);
     c->max_blocks = c->sm_count * 16;
-    cudaMalloc(&c->d_partials, sizeof(double) * GF_NPARTIAL * c->max_blocks);
-    cudaMalloc(&c->d_ticket, sizeof(unsigned) * 8);
-    cudaMemset(c->d_ticket, 0, sizeof(unsigned) * 8);
-    cudaMalloc(&c->d_result, sizeof(double) * GF_NPARTIAL * 64);
-    cudaMemset(c->d_result, 0, sizeof(double) * GF_NPARTIAL * 64);
-    cudaHostAlloc(&c->h_result, sizeof(double) * GF_NPARTIAL * 64, cudaHostAllocMapped);
-    if(cudaHostGetDevicePointer((void **)&c->h_result_dev, c->h_result, 0) != cudaSuccess) c->h_result_dev = nullptr;
-    if(cudaGetLastError() != cudaSuccess) {
-        gf_fail("gf_create: allocation failed");
-        delete c;
+    // every allocation is checked on its own: a context with a null scratch buffer must never be handed out
+    auto ok = [&](cudaError_t e, const char *what) {
+        if(e == cudaSuccess) return true;
+        gf_fail(std::string("gf_create: ") + what + ": " + cudaGetErrorString(e));
+        return false;
+    };
+    bool good = ok(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking), "stream")
+                && ok(cudaEventCreate(&c->ev0), "event") && ok(cudaEventCreate(&c->ev1), "event")
+                && ok(cudaMalloc(&c->d_partials, sizeof(double) * GF_NPARTIAL * c->max_blocks), "partials")
+                && ok(cudaMalloc(&c->d_ticket, sizeof(unsigned) * 8), "ticket")
+                && ok(cudaMemset(c->d_ticket, 0, sizeof(unsigned) * 8), "ticket memset")
+                && ok(cudaMalloc(&c->d_result, sizeof(double) * GF_NPARTIAL * 64), "result")
+                && ok(cudaMemset(c->d_result, 0, sizeof(double) * GF_NPARTIAL * 64), "result memset")
+                && ok(cudaHostAlloc(&c->h_result, sizeof(double) * GF_NPARTIAL * 64, cudaHostAllocMapped), "pinned result");
+    if(good) {
+        std::memset(c->h_result, 0, sizeof(double) * GF_NPARTIAL * 64);
+        if(cudaHostGetDevicePointer((void **)&c->h_result_dev, c->h_result, 0) != cudaSuccess) {
+            c->h_result_dev = nullptr;
+            cudaGetLastError();
+        }
+    }
+    if(!good) {
+        std::string msg = gf_last_error();
+        gf_destroy(c);
+        gf_fail(msg);
         return nullptr;
     }
     return c;
@@ -269,60 +281,109 @@ extern "C" int gf_device_info(gf_ctx *c, int *sm_count, size_t *free_bytes, size
     return 0;
 }
 
+// Pure host-side check of a flattened program (no context, no device): index ranges, then the value stack of every
+// evaluable subtree. gf_set_program runs it before anything is committed.
+extern "C" int gf_validate_program(const gf_node *nodes, int n_nodes, int n_consts, int n_ints, int n_params, int n_norms) {
+    if(!nodes || n_nodes <= 0 || n_params < 0 || n_norms <= 0 || n_consts < 0 || n_ints < 0) return gf_fail("gf_set_program: bad sizes");
+    for(int k = 0; k < n_nodes; k++) {
+        const gf_node &nd = nodes[k];
+        if(nd.par_off < 0 || nd.npar < 0 || nd.par_off + nd.npar > n_params) return gf_fail("gf_set_program: param range, node " + std::to_string(k));
+        if(nd.con_off < 0 || nd.ncon < 0 || nd.con_off + nd.ncon > n_consts) return gf_fail("gf_set_program: const range, node " + std::to_string(k));
+        if(nd.obs_off < 0 || nd.nobs < 0 || nd.obs_off + nd.nobs > n_ints) return gf_fail("gf_set_program: obs range, node " + std::to_string(k));
+        if(nd.int_off < 0 || nd.nint < 0 || nd.int_off + nd.nint > n_ints) return gf_fail("gf_set_program: int range, node " + std::to_string(k));
+        if(nd.norm_slot < 0 || nd.norm_slot >= n_norms) return gf_fail("gf_set_program: norm slot, node " + std::to_string(k));
+        if(nd.size < 1 || nd.size > k + 1) return gf_fail("gf_set_program: subtree size, node " + std::to_string(k));
+        if(nd.nobs > GF_MAX_OBS) return gf_fail("gf_set_program: too many observables");
+        if(nd.nchild < 0) return gf_fail("gf_set_program: negative child count, node " + std::to_string(k));
+    }
+    // Post-order walk of each subtree [k - size + 1, k]: a leaf pushes one value, a combiner pops nchild and pushes one.
+    // depth[k] = values on the stack after node k when evaluation starts at the first node of k's subtree. The walk of a
+    // larger subtree passes through the same states shifted by what is already pending, so one pass from each root's first
+    // node covers it: require pops to be available and the peak to fit GF_MAX_STACK (gf_eval_tree's fixed array).
+    {
+        auto is_eval = [](int op) { return op < GF_OP_RES_RBW; }; // resonance / lineshape / resolution records never run on the stack
+        for(int r = 0; r < n_nodes; r++) {
+            if(!is_eval(nodes[r].op)) continue;
+            int first = r - nodes[r].size + 1, sp = 0, peak = 0;
+            for(int k = first; k <= r; k++) {
+                const gf_node &nd = nodes[k];
+                if(!is_eval(nd.op)) return gf_fail("gf_set_program: non-evaluable record inside the subtree of node " + std::to_string(r));
+                int pops = nd.op < GF_OP_ADD ? 0 : (nd.op == GF_OP_CONVOLVE ? 0 : nd.nchild);
+                if(nd.op >= GF_OP_ADD && nd.op <= GF_OP_PROD && (nd.nint < nd.nchild || nd.nchild < 1))
+                    return gf_fail("gf_set_program: combiner without child norm slots, node " + std::to_string(k));
+                if(nd.op == GF_OP_ADD && nd.npar < nd.nchild - 1) return gf_fail("gf_set_program: AddPdf weights, node " + std::to_string(k));
+                if(nd.op == GF_OP_ADD_EXT && nd.npar < nd.nchild) return gf_fail("gf_set_program: AddPdf weights, node " + std::to_string(k));
+                if(nd.op >= GF_OP_AMP3 && nd.op <= GF_OP_AMP4_TD) pops = 1; // the efficiency
+                if(sp < pops) return gf_fail("gf_set_program: value-stack underflow at node " + std::to_string(k));
+                sp += 1 - pops;
+                if(sp > peak) peak = sp;
+            }
+            if(sp != 1) return gf_fail("gf_set_program: subtree of node " + std::to_string(r) + " does not reduce to one value");
+            if(peak > GF_MAX_STACK)
+                return gf_fail("gf_set_program: subtree of node " + std::to_string(r) + " needs a value stack of " + std::to_string(peak)
+                               + " > GF_MAX_STACK = " + std::to_string(GF_MAX_STACK) + " (nest the components in smaller AddPdf/ProdPdf groups)");
+        }
+    }
+    if(gf_sprog_bytes(n_nodes, n_params, n_consts, n_norms, n_ints) > 160 * 1024) return gf_fail("gf_set_program: program block exceeds shared memory");
+    return 0;
+}
+
 extern "C" int gf_set_program(gf_ctx *c, const gf_node *nodes, int n_nodes, const double *consts, int n_consts,
                               const int32_t *ints, int n_ints, int n_params, int n_norms) {
     if(!c) return gf_fail("null ctx");
     if(n_nodes <= 0 || n_params < 0 || n_norms <= 0) return gf_fail("gf_set_program: bad sizes");
     cudaSetDevice(c->device);
-    // validate: stack depth, ranges
-    for(int k = 0; k < n_nodes; k++) {
-        const gf_node &nd = nodes[k];
-        if(nd.par_off < 0 || nd.par_off + nd.npar > n_params) return gf_fail("gf_set_program: param range, node " + std::to_string(k));
-        if(nd.con_off < 0 || nd.con_off + nd.ncon > n_consts) return gf_fail("gf_set_program: const range, node " + std::to_string(k));
-        if(nd.obs_off < 0 || nd.obs_off + nd.nobs > n_ints) return gf_fail("gf_set_program: obs range, node " + std::to_string(k));
-        if(nd.int_off < 0 || nd.int_off + nd.nint > n_ints) return gf_fail("gf_set_program: int range, node " + std::to_string(k));
-        if(nd.norm_slot < 0 || nd.norm_slot >= n_norms) return gf_fail("gf_set_program: norm slot, node " + std::to_string(k));
-        if(nd.size < 1 || nd.size > k + 1) return gf_fail("gf_set_program: subtree size, node " + std::to_string(k));
-        if(nd.nobs > GF_MAX_OBS) return gf_fail("gf_set_program: too many observables");
+    if(gf_validate_program(nodes, n_nodes, n_consts, n_ints, n_params, n_norms)) return 1;
+    const size_t sm = gf_sprog_bytes(n_nodes, n_params, n_consts, n_norms, n_ints);
+    // allocate into temporaries; host and device state is replaced only when every step succeeded
+    gf_node *t_nodes = nullptr;
+    double *t_params = nullptr, *t_consts = nullptr, *t_pin = nullptr;
+    int32_t *t_ints = nullptr;
+    auto bail = [&](const std::string &what) {
+        cudaFree(t_nodes); cudaFree(t_params); cudaFree(t_consts); cudaFree(t_ints);
+        if(t_pin) cudaFreeHost(t_pin);
+        cudaGetLastError();
+        return gf_fail("gf_set_program: " + what);
+    };
+    GF_CUDA(cudaStreamSynchronize(c->stream));
+    std::vector<double> ones(n_norms, 1.0);
+    const size_t need = sizeof(double) * (size_t)(n_params + n_norms + 16);
+    // parameters and normalisations share one allocation so that one copy per likelihood call uploads both
+    if(cudaMalloc(&t_nodes, sizeof(gf_node) * n_nodes) != cudaSuccess || cudaMalloc(&t_params, sizeof(double) * (size_t)(n_params + n_norms)) != cudaSuccess
+       || cudaMalloc(&t_consts, sizeof(double) * std::max(1, n_consts)) != cudaSuccess || cudaMalloc(&t_ints, sizeof(int32_t) * std::max(1, n_ints)) != cudaSuccess)
+        return bail("device allocation failed");
+    if(need > c->h_pin_cap && cudaMallocHost(&t_pin, need) != cudaSuccess) return bail("pinned allocation failed");
+    if(cudaMemcpy(t_nodes, nodes, sizeof(gf_node) * n_nodes, cudaMemcpyHostToDevice) != cudaSuccess
+       || (n_consts && cudaMemcpy(t_consts, consts, sizeof(double) * n_consts, cudaMemcpyHostToDevice) != cudaSuccess)
+       || (n_ints && cudaMemcpy(t_ints, ints, sizeof(int32_t) * n_ints, cudaMemcpyHostToDevice) != cudaSuccess)
+       || (n_params && cudaMemset(t_params, 0, sizeof(double) * n_params) != cudaSuccess)
+       || cudaMemcpy(t_params + n_params, ones.data(), sizeof(double) * n_norms, cudaMemcpyHostToDevice) != cudaSuccess)
+        return bail("upload failed");
+    if(sm > 48 * 1024) {
+        cudaError_t e = cudaSuccess;
+        for(int has : {0, (int)GF_HAS_CONV, (int)GF_HAS_AMP3, (int)GF_HAS_AMP4_TD, GF_HAS_AMP4_TD | GF_HAS_3GAUSS, (int)GF_HAS_ALL})
+            if(e == cudaSuccess) e = cudaFuncSetAttribute(eval_sum_kernel(has), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        if(e == cudaSuccess) e = cudaFuncSetAttribute(k_eval_events, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        if(e == cudaSuccess) e = cudaFuncSetAttribute(k_grid_sum, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        if(e != cudaSuccess) return bail(std::string("cannot reserve ") + std::to_string(sm) + " B of shared memory for the program block: " + cudaGetErrorString(e));
+    }
+    // commit
+    cudaFree(c->d_nodes); cudaFree(c->d_params); cudaFree(c->d_consts); cudaFree(c->d_ints); // d_norms lives inside d_params' block
+    c->d_nodes = t_nodes; c->d_params = t_params; c->d_consts = t_consts; c->d_ints = t_ints;
+    c->d_norms = c->d_params + n_params;
+    if(t_pin) {
+        if(c->h_pin) cudaFreeHost(c->h_pin);
+        c->h_pin = t_pin;
+        c->h_pin_cap = need;
     }
     c->h_nodes.assign(nodes, nodes + n_nodes);
     c->h_consts.assign(consts, consts + n_consts);
     c->h_ints.assign(ints, ints + n_ints);
     c->n_params = n_params;
     c->n_norms = n_norms;
-    if(gf_prog_smem(c) > 160 * 1024) return gf_fail("gf_set_program: program block exceeds shared memory");
-    cudaStreamSynchronize(c->stream);
-    cudaFree(c->d_nodes); cudaFree(c->d_params); cudaFree(c->d_consts); cudaFree(c->d_ints); // d_norms lives inside d_params' block
-    GF_CUDA(cudaMalloc(&c->d_nodes, sizeof(gf_node) * n_nodes));
-    // parameters and normalisations share one allocation so that one copy per likelihood call uploads both
-    GF_CUDA(cudaMalloc(&c->d_params, sizeof(double) * (size_t)(n_params + n_norms)));
-    c->d_norms = c->d_params + n_params;
-    GF_CUDA(cudaMalloc(&c->d_consts, sizeof(double) * std::max(1, n_consts)));
-    GF_CUDA(cudaMalloc(&c->d_ints, sizeof(int32_t) * std::max(1, n_ints)));
-    GF_CUDA(cudaMemcpy(c->d_nodes, nodes, sizeof(gf_node) * n_nodes, cudaMemcpyHostToDevice));
-    if(n_consts) GF_CUDA(cudaMemcpy(c->d_consts, consts, sizeof(double) * n_consts, cudaMemcpyHostToDevice));
-    if(n_ints) GF_CUDA(cudaMemcpy(c->d_ints, ints, sizeof(int32_t) * n_ints, cudaMemcpyHostToDevice));
-    if(n_params) GF_CUDA(cudaMemset(c->d_params, 0, sizeof(double) * n_params));
-    {
-        std::vector<double> ones(n_norms, 1.0);
-        GF_CUDA(cudaMemcpy(c->d_norms, ones.data(), sizeof(double) * n_norms, cudaMemcpyHostToDevice));
-    }
-    size_t need = sizeof(double) * (size_t)(n_params + n_norms + 16);
-    if(need > c->h_pin_cap) {
-        if(c->h_pin) cudaFreeHost(c->h_pin);
-        GF_CUDA(cudaMallocHost(&c->h_pin, need));
-        c->h_pin_cap = need;
-    }
     gf_dev_view &V = c->view;
     V.nodes = c->d_nodes; V.params = c->d_params; V.consts = c->d_consts; V.norms = c->d_norms; V.ints = c->d_ints;
     V.n_nodes = n_nodes; V.n_params = n_params; V.n_consts = n_consts; V.n_norms = n_norms; V.n_ints = n_ints;
-    size_t sm = gf_prog_smem(c);
-    if(sm > 48 * 1024) {
-        for(int has : {0, (int)GF_HAS_CONV, (int)GF_HAS_AMP3, (int)GF_HAS_AMP4_TD, GF_HAS_AMP4_TD | GF_HAS_3GAUSS, (int)GF_HAS_ALL})
-            cudaFuncSetAttribute(eval_sum_kernel(has), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-        cudaFuncSetAttribute(k_eval_events, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-        cudaFuncSetAttribute(k_grid_sum, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-    }
     return 0;
 }
 
@@ -358,6 +419,7 @@ extern "C" int gf_comm_destroy(gf_ctx *c) {
     c->rank = 0;
     return 0;
 }
+extern "C" int gf_comm_attached(gf_ctx *c) { return c && c->nccl_comm ? c->nranks : 0; }
 int gf_allreduce_sum(gf_ctx *c, double *dev, int n) {
     if(!c->nccl_comm) return 0;
     int rc = p_allreduce(dev, dev, (size_t)n, /*ncclDouble*/ 8, /*ncclSum*/ 0, c->nccl_comm, c->stream);

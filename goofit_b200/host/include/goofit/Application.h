@@ -1,7 +1,8 @@
 // Application.h — minimal stand-in for the reference's CLI11-based GooFit::Application (src/goofit/Application.cpp):
 // parses --gpu-dev N, -q/--quiet and --nosplash, selects the CUDA device before the first PDF is evaluated and, when
-// launched with RANK/WORLD_SIZE/LOCAL_RANK in the environment, takes its event shard from them (the reference's MPI
-// rank -> GPU mapping, Application.cpp:163-207). The CLI11 option machinery itself is out of scope.
+// launched with RANK/WORLD_SIZE/LOCAL_RANK in the environment, takes its event shard from them AND attaches the NCCL
+// communicator the partial sums are reduced over (Engine::attachCommFromEnv; the reference's MPI rank -> GPU mapping
+// plus its MPI_Init, Application.cpp:163-207): sharding without the reduction never happens. The CLI11 option machinery itself is out of scope.
 #pragma once
 #include <cstdlib>
 #include <cstring>
@@ -33,7 +34,7 @@ class Application {
         const char *lr = std::getenv("LOCAL_RANK"), *r = std::getenv("RANK"), *w = std::getenv("WORLD_SIZE");
         if(gpuDev_ < 0 && lr) gpuDev_ = std::atoi(lr);
         if(gpuDev_ >= 0) detail::Engine::get().setDevice(gpuDev_);
-        if(r && w && std::atoi(w) > 1) detail::Engine::get().setShard(std::atoi(r), std::atoi(w));
+        if(r && w && std::atoi(w) > 1) detail::Engine::get().attachCommFromEnv(std::atoi(r), std::atoi(w));
         if(splash_ && !quiet_) std::cout << "GooFit (B200-native likelihood engine) " << description_ << std::endl;
     }
     int exit(const GeneralError &e) {

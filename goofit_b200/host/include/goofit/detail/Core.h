@@ -396,7 +396,12 @@ class Engine {
     gf_ctx *ctx();
     void setDevice(int dev);
     int device() const { return device_; }
-    void setShard(int rank, int size) { shard_ = {rank, size}; }
+    void setShard(int rank, int size); // throws unless 0 <= rank < size
+    /// throws when the dataset is sharded but no communicator of the same size is attached to the context
+    void requireComm(const char *what);
+    /// rendezvous over a file (rank 0 writes the NCCL id, the others read it) keyed on MASTER_PORT / TORCHELASTIC_RUN_ID,
+    /// then gf_comm_init + setShard: what a C++ program launched by torchrun / SLURM needs to run sharded
+    void attachCommFromEnv(int rank, int size);
     Shard shard() const { return shard_; }
     void build(PdfBase *root);
     void sync();
@@ -415,6 +420,7 @@ class Engine {
     gf_ctx *ctx_ = nullptr;
     int device_  = -1;
     Shard shard_;
+    int commEpoch_ = 0;
 };
 } // namespace detail
 

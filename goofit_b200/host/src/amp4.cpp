@@ -415,6 +415,7 @@ void Amp4BodyBase::ensureCache() {
     if(nodeIdx < 0) throw GeneralError("{}: call setData() on the top-level PDF before evaluating", getName());
     if(MCevents == 0) throw GeneralError("{} has no normalisation events", getName());
     Engine &E = Engine::get();
+    E.requireComm("Amp4Body normalisation");
     Engine::check(gf_amp4_alloc(E.ctx(), nodeIdx, E.localEvents), "gf_amp4_alloc");
     // the MC normalisation sample is sharded over ranks like the data (the reference replicates it)
     detail::Shard sh = E.shard();

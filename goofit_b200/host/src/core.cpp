@@ -2,9 +2,13 @@
 // and upload), PdfBase and GooPdf. Reference behaviour cited per function (paths under /root/reference).
 #include <goofit/detail/Core.h>
 
+#include <chrono>
+#include <cstdio>
 #include <cstdlib>
+#include <fstream>
 #include <numeric>
 #include <random>
+#include <thread>
 
 namespace GooFit {
 
@@ -302,6 +306,58 @@ void Engine::sync() {
               "gf_set_params_async");
     paramsDirty = normsDirty = false;
 }
+void Engine::setShard(int rank, int size) {
+    if(size < 1 || rank < 0 || rank >= size) throw GeneralError("setShard: need 0 <= rank < size, got rank {} of {}", rank, size);
+    shard_ = {rank, size};
+}
+// Sharding and the reduction are one operation (upstream pairs its MPI split with MPI_Allreduce, GooPdf.cu:72-75): a
+// sharded dataset without a communicator of the same size would hand each rank a different, partial likelihood.
+void Engine::requireComm(const char *what) {
+    if(shard_.size <= 1) return;
+    int n = gf_comm_attached(ctx());
+    if(n != shard_.size)
+        throw GeneralError("{}: the dataset is sharded over {} ranks but {} — attach one with gf_comm_init / "
+                           "Engine::attachCommFromEnv() before evaluating, or do not shard",
+                           what, shard_.size, n == 0 ? std::string("no communicator is attached") : "the communicator has " + std::to_string(n) + " ranks");
+}
+void Engine::attachCommFromEnv(int rank, int size) {
+    if(size < 1 || rank < 0 || rank >= size) throw GeneralError("attachCommFromEnv: need 0 <= rank < size, got rank {} of {}", rank, size);
+    if(size == 1) return;
+    gf_ctx *c = ctx();
+    if(gf_comm_attached(c) == size) {
+        setShard(rank, size);
+        return;
+    }
+    // the 128-byte NCCL id travels through a file: rank 0 writes it under a temporary name and renames it into place
+    // (atomic on one filesystem), the other ranks poll for it. One node only, which is what this library targets.
+    const char *dir = std::getenv("GOOFIT_B200_RENDEZVOUS_DIR");
+    const char *port = std::getenv("MASTER_PORT"), *run = std::getenv("TORCHELASTIC_RUN_ID");
+    std::string path = std::string(dir ? dir : "/tmp") + "/goofit_b200_nccl_" + (port ? port : "0") + "_" + (run ? run : "none") + "_"
+                       + std::to_string(commEpoch_++) + ".id";
+    char id[128];
+    if(rank == 0) {
+        check(gf_comm_unique_id(id), "gf_comm_unique_id");
+        std::string tmp = path + ".tmp";
+        {
+            std::ofstream f(tmp, std::ios::binary | std::ios::trunc);
+            f.write(id, sizeof id);
+            if(!f) throw GeneralError("attachCommFromEnv: cannot write {}", tmp);
+        }
+        if(std::rename(tmp.c_str(), path.c_str()) != 0) throw GeneralError("attachCommFromEnv: cannot publish {}", path);
+    } else {
+        auto t0 = std::chrono::steady_clock::now();
+        for(;;) {
+            std::ifstream f(path, std::ios::binary);
+            if(f && f.read(id, sizeof id) && f.gcount() == (std::streamsize)sizeof id) break;
+            if(std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() > 120)
+                throw GeneralError("attachCommFromEnv: rank {} waited 120 s for {} (is rank 0 running?)", rank, path);
+            std::this_thread::sleep_for(std::chrono::milliseconds(20));
+        }
+    }
+    check(gf_comm_init(c, id, rank, size), "gf_comm_init"); // collective: returns once every rank has joined
+    if(rank == 0) std::remove(path.c_str());
+    setShard(rank, size);
+}
 void Engine::release(const PdfBase *pdf) {
     auto it = std::find(members.begin(), members.end(), pdf);
     if(it != members.end()) members.erase(it);
@@ -561,6 +617,7 @@ double GooPdf::reduce_with_bins() const { // GooPdf.cu:83-108 -> k_grid_sum
 double GooPdf::reduce_with_metric() const { // GooPdf.cu:45-78 -> k_eval_sum (+ NCCL all-reduce when sharded)
     require_in_program(this, nodeIdx);
     Engine &E = Engine::get();
+    E.requireComm("reduce_with_metric");
     E.sync();
     double out = 0;
     Engine::check(gf_eval_sum(E.ctx(), nodeIdx, metric(), &out), "gf_eval_sum");
@@ -597,6 +654,8 @@ fptype GooPdf::normalize() { // GooPdf.cu:340-396
     std::vector<double> key;
     if(components.empty() && nodeIdx >= 0) {
         key.push_back(static_cast<double>(Engine::get().generation));
+        key.push_back(static_cast<double>(integrationBins));
+        for(fptype cst : constantsList) key.push_back(cst);
         for(size_t i = 0; i < parametersList.size(); ++i) key.push_back(par(i));
         for(const Observable &v : observablesList) {
             key.push_back(v.getLowerLimit());

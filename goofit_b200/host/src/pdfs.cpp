@@ -85,7 +85,9 @@ PolynomialPdf::PolynomialPdf(std::string n, std::vector<Observable> obses, std::
     for(auto &o : offsets) registerParameter(o);
     for(auto &c : coeffs) registerParameter(c);
     multiDim = true;
-    registerFunction("ptr_to_MultiPolynomial", maxDegree == 0 ? GF_OP_CONSTANT : GF_OP_MULTI_POLYNOMIAL); // degree 0: the one coefficient
+    registerFunction("ptr_to_MultiPolynomial", (maxDegree == 0 && coeffs.size() == 1) ? GF_OP_CONSTANT : GF_OP_MULTI_POLYNOMIAL);
+    // degree 0 with exactly its one coefficient: the constant leaf (last parameter of the record == p[nobs]); with surplus
+    // coefficients (legal: the constructor pads, never truncates) the general opcode keeps reading p[nobs] as upstream
 }
 fptype PolynomialPdf::integrate(fptype lo, fptype hi) const { // PolynomialPdf.cu:217-243 (marked wrong upstream; unused: no hasAnalyticIntegral)
     fptype lowestDegree = constantsList[0];
@@ -151,6 +153,12 @@ KinLimitBWPdf::KinLimitBWPdf(std::string n, Observable _x, Variable mean, Variab
 void KinLimitBWPdf::setMasses(fptype bigM, fptype smallM) {
     constantsList[0] = bigM;
     constantsList[1] = smallM;
+    // the constants live in the flattened program: re-install it so the device sees them (and every cached grid sum,
+    // keyed on the program generation, is dropped)
+    if(nodeIdx >= 0) {
+        Engine &E = Engine::get();
+        if(E.root) E.build(E.root);
+    }
 }
 ScaledGaussianPdf::ScaledGaussianPdf(std::string n, Observable _x, Variable mean, Variable sigma, Variable delta, Variable epsilon)
     : GooPdf("ScaledGaussianPdf", n, _x, mean, sigma, delta, epsilon) { // ScaledGaussianPdf.cu:24-31

@@ -37,6 +37,9 @@ PYBIND11_MODULE(_goofit, m) {
 
     m.def("set_device", [](int dev) { detail::Engine::get().setDevice(dev); }, "device"_a);
     m.def("set_shard", [](int rank, int size) { detail::Engine::get().setShard(rank, size); }, "rank"_a, "size"_a);
+    m.def("attach_comm_from_env", [](int rank, int size) { detail::Engine::get().attachCommFromEnv(rank, size); }, "rank"_a, "size"_a,
+          "file rendezvous of the NCCL id (keyed on MASTER_PORT), gf_comm_init and set_shard in one call");
+    m.def("comm_attached", [] { return gf_comm_attached(detail::Engine::get().ctx()); });
     m.def("ctx_handle", [] { return reinterpret_cast<uintptr_t>(detail::Engine::get().ctx()); },
           "raw gf_ctx* of the engine (for attaching an NCCL communicator through the C ABI)");
     m.def("launch_count", [] { return gf_launch_count(detail::Engine::get().ctx()); });

@@ -103,6 +103,9 @@ int gf_device_info(gf_ctx *, int *sm_count, size_t *free_bytes, size_t *total_by
 
 int gf_set_program(gf_ctx *, const gf_node *nodes, int n_nodes, const double *consts, int n_consts,
                    const int32_t *ints, int n_ints, int n_params, int n_norms);
+/* the checks gf_set_program applies, without a context or a device: index ranges of every record, and a simulated
+ * post-order walk of every evaluable subtree (pops available at each combiner, peak depth <= GF_MAX_STACK) */
+int gf_validate_program(const gf_node *nodes, int n_nodes, int n_consts, int n_ints, int n_params, int n_norms);
 /* Drop every per-node device cache (Amp3Body/Amp4Body caches, convolution workspaces) and clear the aux
  * table; called by the host layer before a re-flattened program is installed. */
 int gf_reset_aux(gf_ctx *);
@@ -170,6 +173,9 @@ int gf_amp4_get_amp(gf_ctx *, int node, int amp, double *out_re_im, size_t n_eve
 int gf_comm_unique_id(void *id128);
 int gf_comm_init(gf_ctx *, const void *id128, int rank, int nranks);
 int gf_comm_destroy(gf_ctx *);
+/* number of ranks of the attached communicator, 0 when none is attached (the host layer refuses to evaluate a
+ * sharded dataset without one: a partial sum must never be mistaken for the likelihood) */
+int gf_comm_attached(gf_ctx *);
 /* device-side stopwatch on the ctx stream (CUDA events): start, enqueue work, stop -> elapsed ms */
 int gf_timer_start(gf_ctx *);
 int gf_timer_stop(gf_ctx *, float *ms);

@@ -311,3 +311,44 @@ def test_resonance_and_lineshape_zoo_host_side():
     if not torch.cuda.is_available():
         with pytest.raises(Exception):
             Z3.signal.GenerateSig(10, 1)  # no device: must fail loudly, never fall back
+
+
+class _Node(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_int32) for n in ("op", "nchild", "size", "par_off", "npar", "con_off", "ncon", "obs_off", "nobs",
+                                             "norm_slot", "int_off", "nint")]
+
+
+def _validate(nodes, n_consts=0, n_ints=0, n_params=0, n_norms=1):
+    lib = capi.lib()
+    arr = (_Node * len(nodes))(*nodes)
+    rc = lib.gf_validate_program(arr, len(nodes), n_consts, n_ints, n_params, n_norms)
+    return rc, capi.last_error()
+
+
+def test_program_validation_catches_stack_overflow_and_underflow():
+    """an AddPdf with more components than the evaluator's fixed value stack must be refused, not corrupt
+    local memory; a combiner that pops more than was pushed must be refused too."""
+    EXP, ADD = 1, 32
+    leaf = lambda k: _Node(EXP, 0, 1, 0, 1, 0, 0, 0, 1, k, 0, 0)
+    n = 17  # GF_MAX_STACK + 1 leaves under one AddPdf
+    nodes = [leaf(k) for k in range(n)] + [_Node(ADD, n, n + 1, 0, n - 1, 0, 0, 0, 1, n, 0, n)]
+    rc, err = _validate(nodes, n_ints=n, n_params=n, n_norms=n + 1)
+    assert rc != 0 and "GF_MAX_STACK" in err
+    nodes = [leaf(k) for k in range(16)] + [_Node(ADD, 16, 17, 0, 15, 0, 0, 0, 1, 16, 0, 16)]
+    rc, err = _validate(nodes, n_ints=16, n_params=16, n_norms=17)
+    assert rc == 0, err
+    nodes = [leaf(0), _Node(ADD, 2, 2, 0, 1, 0, 0, 0, 1, 1, 0, 2)]  # claims two children, only one value was pushed
+    rc, err = _validate(nodes, n_ints=2, n_params=1, n_norms=2)
+    assert rc != 0 and "underflow" in err
+    nodes = [leaf(0)]
+    nodes[0].par_off = 5  # parameter range outside the block
+    rc, err = _validate(nodes, n_ints=1, n_params=1, n_norms=1)
+    assert rc != 0 and "param range" in err
+
+
+def test_shard_needs_valid_rank_and_a_communicator():
+    """setShard validates 0 <= rank < size (size 0 divided by zero in the split arithmetic)."""
+    for bad in ((0, 0), (2, 2), (-1, 2)):
+        with pytest.raises(gf.GeneralError, match="rank"):
+            gf.set_shard(*bad)
+    gf.set_shard(0, 1)
