@@ -255,7 +255,7 @@ def simple_fits(gf, lib, ctx, peak_hbm, steps=20):
     return out
 
 
-def run_all(gf, lib, ctx, M_dalitz, n_events, peak_hbm, steps=20):
+def run_all(gf, lib, ctx, M_dalitz, n_events, peak_hbm, steps=20, with_reference=True):
     out = {}
     peak_tf = fp64_peak(lib, ctx)
     out["fp64_peak_tflops_measured"] = peak_tf

@@ -237,7 +237,7 @@ __global__ void __launch_bounds__(GF_THREADS, 3)
 // sum over MC events of |sum_a A_a(m) c_a|^2 (optionally weighted); deterministic grid reduction
 __global__ void __launch_bounds__(GF_THREADS, 4)
     k_amp4_norm(const gf_dev_view V, int node, const double2 *amps, long ld, long n, const double *weights,
-                double *partials, unsigned *ticket, double *out) {
+                double *partials, unsigned *ticket, double *out, const gf_peer_view PV) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ double red[32];
     gf_sprog P = gf_stage_program(V, smem);
@@ -258,14 +258,14 @@ __global__ void __launch_bounds__(GF_THREADS, 4)
         if(weights) v *= __ldg(weights + m);
         acc += v;
     }
-    gf_grid_finish(&acc, 1, partials, ticket, out, red);
+    gf_grid_finish(&acc, 1, partials, ticket, out, red, PV);
 }
 
 // Amp4Body_TD: four sums over MC events, |A|^2, |B|^2, Re(A B*), Im(A B*) (detail/NormIntegrator_TD.cu:15-99); the
 // time integrals are applied to the four sums on the host by the resolution's normalization().
 __global__ void __launch_bounds__(GF_THREADS, 4)
     k_amp4_norm_td(const gf_dev_view V, int node, const double2 *amps, long ld, long n, const double *weights,
-                   double *partials, unsigned *ticket, double *out) {
+                   double *partials, unsigned *ticket, double *out, const gf_peer_view PV) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ double red[32];
     gf_sprog P = gf_stage_program(V, smem);
@@ -286,7 +286,7 @@ __global__ void __launch_bounds__(GF_THREADS, 4)
         acc[2] += w * (Are * Bre + Aim * Bim);
         acc[3] += w * (Aim * Bre - Are * Bim);
     }
-    gf_grid_finish_n(acc, partials, ticket, out, red);
+    gf_grid_finish_n(acc, partials, ticket, out, red, PV);
 }
 
 // G_ab = sum_m w_m A_a(m) conj(A_b(m)) for one GF_GRAM_T x GF_GRAM_T tile (rows a0.., columns b0..) of the Hermitian
@@ -297,7 +297,7 @@ __global__ void __launch_bounds__(GF_THREADS, 4)
 // add nothing.
 __global__ void __launch_bounds__(GF_THREADS, 2)
     k_amp4_gram(const double2 *amps, long ld, long n, const double *weights, int nAmp, int a0, int b0, double *partials,
-                unsigned *ticket, double *out) {
+                unsigned *ticket, double *out, const gf_peer_view PV) {
     __shared__ double red[32];
     double acc[2 * GF_GRAM_T * GF_GRAM_T];
 #pragma unroll
@@ -321,7 +321,7 @@ __global__ void __launch_bounds__(GF_THREADS, 2)
             }
         }
     }
-    gf_grid_finish_n(acc, partials, ticket, out, red);
+    gf_grid_finish_n(acc, partials, ticket, out, red, PV);
 }
 
 // ---- C ABI ---------------------------------------------------------------------------------------------------
@@ -514,13 +514,13 @@ extern "C" int gf_amp4_norm_async(gf_ctx *c, int node) {
     if(s->td) {
         if(sm > 48 * 1024) cudaFuncSetAttribute(k_amp4_norm_td, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
         k_amp4_norm_td<<<blocks, GF_THREADS, sm, c->stream>>>(c->view, node, s->mc.amps, s->mc.ld, s->mc.n, s->mc.weights,
-                                                             c->d_partials + (size_t)c->max_blocks * 2, c->d_ticket + 2, c->d_result + 1);
+                                                             c->d_partials + (size_t)c->max_blocks * 2, c->d_ticket + 2, c->d_result + 1, gf_next_peer_view(c));
     } else
         k_amp4_norm<<<blocks, GF_THREADS, sm, c->stream>>>(c->view, node, s->mc.amps, s->mc.ld, s->mc.n, s->mc.weights,
-                                                          c->d_partials + (size_t)c->max_blocks * 2, c->d_ticket + 2, c->d_result + 1);
+                                                          c->d_partials + (size_t)c->max_blocks * 2, c->d_ticket + 2, c->d_result + 1, gf_next_peer_view(c));
     c->launches++;
     GF_CUDA(cudaGetLastError());
-    if(c->nccl_comm && gf_allreduce_sum(c, c->d_result + 1, s->td ? 4 : 1)) return 1;
+    if(c->nccl_comm && !gf_peer_active(c) && gf_allreduce_sum(c, c->d_result + 1, s->td ? 4 : 1)) return 1;
     return 0;
 }
 extern "C" int gf_amp4_norm(gf_ctx *c, int node, double *out) {
@@ -567,11 +567,11 @@ extern "C" int gf_amp4_gram(gf_ctx *c, int node, double *G_re_im) {
             if(s->gram_valid && !(s->gram_pending & (rows | cols))) continue;
             double *out = s->d_gram + (size_t)t * per;
             k_amp4_gram<<<blocks, GF_THREADS, 0, c->stream>>>(s->mc.amps, s->mc.ld, s->mc.n, s->mc.weights, s->nAmp, ta * T, tb * T,
-                                                             s->d_gram_partials, s->d_gram_ticket, out);
+                                                             s->d_gram_partials, s->d_gram_ticket, out, gf_next_peer_view(c));
             c->launches++;
             launched++;
             GF_CUDA(cudaGetLastError());
-            if(c->nccl_comm && gf_allreduce_sum(c, out, per)) return 1;
+            if(c->nccl_comm && !gf_peer_active(c) && gf_allreduce_sum(c, out, per)) return 1;
             GF_CUDA(cudaMemcpyAsync(s->h_gram + (size_t)t * per, out, sizeof(double) * per, cudaMemcpyDeviceToHost, c->stream));
         }
     if(launched) GF_CUDA(cudaStreamSynchronize(c->stream));

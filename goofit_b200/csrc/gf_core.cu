@@ -6,6 +6,7 @@
 #include "gf_internal.cuh"
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <dlfcn.h>
 
 static thread_local std::string g_err;
@@ -42,6 +43,7 @@ namespace {
 typedef int (*nccl_get_uid_t)(void *);
 typedef int (*nccl_init_rank_t)(void **, int, gf_nccl_uid, int);
 typedef int (*nccl_allreduce_t)(const void *, void *, size_t, int, int, void *, cudaStream_t);
+typedef int (*nccl_allgather_t)(const void *, void *, size_t, int, void *, cudaStream_t);
 typedef int (*nccl_destroy_t)(void *);
 typedef const char *(*nccl_errstr_t)(int);
 }
@@ -49,6 +51,7 @@ static void *g_nccl = nullptr;
 static nccl_get_uid_t p_uid = nullptr;
 static nccl_init_rank_t p_init = nullptr;
 static nccl_allreduce_t p_allreduce = nullptr;
+static nccl_allgather_t p_allgather = nullptr;
 static nccl_destroy_t p_destroy = nullptr;
 static nccl_errstr_t p_errstr = nullptr;
 static int load_nccl() {
@@ -59,6 +62,7 @@ static int load_nccl() {
     p_uid = (nccl_get_uid_t)dlsym(g_nccl, "ncclGetUniqueId");
     p_init = (nccl_init_rank_t)dlsym(g_nccl, "ncclCommInitRank");
     p_allreduce = (nccl_allreduce_t)dlsym(g_nccl, "ncclAllReduce");
+    p_allgather = (nccl_allgather_t)dlsym(g_nccl, "ncclAllGather");
     p_destroy = (nccl_destroy_t)dlsym(g_nccl, "ncclCommDestroy");
     p_errstr = (nccl_errstr_t)dlsym(g_nccl, "ncclGetErrorString");
     if(!p_uid || !p_init || !p_allreduce || !p_destroy) return gf_fail("libnccl: missing symbols");
@@ -77,7 +81,7 @@ constexpr int eval_sum_blocks_per_sm(int) { return 4; } // 3 and 5 measured slow
 template <int HAS>
 __global__ void __launch_bounds__(GF_THREADS, eval_sum_blocks_per_sm(HAS))
     k_eval_sum(const gf_dev_view V, int first, int root, int metric, int n_cols, double *partials, unsigned *ticket,
-               double *out) {
+               double *out, const gf_peer_view PV) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ double red[32];
     gf_sprog P = gf_stage_program(V, smem);
@@ -91,7 +95,7 @@ __global__ void __launch_bounds__(GF_THREADS, eval_sum_blocks_per_sm(HAS))
         double raw = gf_eval_tree<HAS>(P, V, first, root, evt);
         acc += gf_metric(metric, raw, norm, evt, V, n_cols);
     }
-    gf_grid_finish(&acc, 1, partials, ticket, out, red);
+    gf_grid_finish(&acc, 1, partials, ticket, out, red, PV);
 }
 // heavy node kinds among nodes [first, root] of the installed program
 static int program_class(const gf_ctx *c, int first, int root) {
@@ -111,7 +115,7 @@ static int program_class(const gf_ctx *c, int first, int root) {
     }
     return has;
 }
-typedef void (*eval_sum_kernel_t)(const gf_dev_view, int, int, int, int, double *, unsigned *, double *);
+typedef void (*eval_sum_kernel_t)(const gf_dev_view, int, int, int, int, double *, unsigned *, double *, const gf_peer_view);
 static eval_sum_kernel_t eval_sum_kernel(int has) {
     switch(has) {
     case 0: return k_eval_sum<0>;
@@ -176,7 +180,9 @@ __global__ void __launch_bounds__(GF_THREADS, 4)
         }
         acc += gf_eval_tree(P, V, first, root, evt);
     }
-    gf_grid_finish(&acc, 1, partials, ticket, out, red);
+    gf_peer_view none{};
+    none.nranks = 1;
+    gf_grid_finish(&acc, 1, partials, ticket, out, red, none); // normalisation grids are replicated on every rank
 }
 
 __global__ void k_check_identity(const double *col, long n, int *flag) {
@@ -236,6 +242,18 @@ extern "C" gf_ctx *gf_create(int device_id) {
     return c;
 }
 
+static void peer_teardown(gf_ctx *c) {
+    for(int r = 0; r < GF_MAX_PEERS; r++)
+        if(c->peer_mapped[r]) {
+            cudaIpcCloseMemHandle(c->peer_mapped[r]);
+            c->peer_mapped[r] = nullptr;
+        }
+    cudaFree(c->peer_buf);
+    c->peer_buf = nullptr;
+    c->peer_on = false;
+    c->peer = gf_peer_view{};
+    cudaGetLastError();
+}
 void gf_amp3_free(gf_ctx *c);
 void gf_amp4_free(gf_ctx *c);
 void gf_conv_free(gf_ctx *c);
@@ -258,7 +276,9 @@ extern "C" void gf_destroy(gf_ctx *c) {
     cudaFree(c->d_nodes); cudaFree(c->d_params); cudaFree(c->d_consts); cudaFree(c->d_ints); // d_norms lives inside d_params' block
     cudaFree(c->d_partials); cudaFree(c->d_ticket); cudaFree(c->d_result); cudaFree(c->d_events_out);
     cudaFreeHost(c->h_result);
+    peer_teardown(c);
     if(c->nccl_comm && p_destroy) p_destroy(c->nccl_comm);
+    if(c->h_err) cudaFreeHost(c->h_err);
     for(int i = 0; i < gf_ctx::RING; i++) {
         if(c->ring_buf[i]) cudaFreeHost(c->ring_buf[i]);
         if(c->ring_ev[i]) cudaEventDestroy(c->ring_ev[i]);
@@ -392,11 +412,105 @@ extern "C" int gf_comm_unique_id(void *id128) {
     int rc = p_uid(id128);
     return rc ? nccl_fail("ncclGetUniqueId", rc) : 0;
 }
+// small all-reduce of n <= GF_PEER_SLOT doubles that already sit in device memory (one block)
+__global__ void __launch_bounds__(GF_THREADS) k_peer_allreduce(double *vals, int n, const gf_peer_view PV) {
+    __shared__ double in[GF_PEER_SLOT];
+    for(int k = threadIdx.x; k < n; k += blockDim.x) in[k] = vals[k];
+    __syncthreads();
+    gf_peer_allreduce(PV, in, n, vals);
+}
+
+// Map every rank's exchange buffer into this process (cudaIpc over NVLink / NVSwitch). Collective: every rank calls it with
+// the communicator attached. Returns 0 and leaves c->peer_on = false when any rank could not map its peers (all ranks then
+// agree to stay on NCCL); fails only on NCCL errors.
+static int peer_setup(gf_ctx *c) {
+    c->peer_on = false;
+    const char *off = std::getenv("GOOFIT_B200_NO_PEER");
+    int ok = (off && off[0] == '1') || c->nranks > GF_MAX_PEERS || !p_allgather ? 0 : 1;
+    const size_t slots_bytes = sizeof(double) * 2 * GF_MAX_PEERS * GF_PEER_SLOT, flags_bytes = sizeof(unsigned long long) * 2 * GF_MAX_PEERS;
+    cudaIpcMemHandle_t mine;
+    std::memset(&mine, 0, sizeof mine);
+    if(ok) {
+        if(!c->h_err) {
+            if(cudaHostAlloc(&c->h_err, sizeof(int), cudaHostAllocMapped) != cudaSuccess || cudaHostGetDevicePointer((void **)&c->h_err_dev, c->h_err, 0) != cudaSuccess) ok = 0;
+            else *c->h_err = 0;
+        }
+        if(ok && (cudaMalloc(&c->peer_buf, slots_bytes + flags_bytes) != cudaSuccess || cudaMemset(c->peer_buf, 0, slots_bytes + flags_bytes) != cudaSuccess
+                  || cudaDeviceSynchronize() != cudaSuccess || cudaIpcGetMemHandle(&mine, c->peer_buf) != cudaSuccess))
+            ok = 0;
+        cudaGetLastError();
+    }
+    // exchange {ok, handle} of every rank through the communicator that was just created
+    struct rec { long long ok; cudaIpcMemHandle_t h; };
+    rec my{ok, mine};
+    rec *d_all = nullptr;
+    std::vector<rec> all(c->nranks);
+    GF_CUDA(cudaMalloc(&d_all, sizeof(rec) * c->nranks));
+    GF_CUDA(cudaMemcpy(d_all + c->rank, &my, sizeof(rec), cudaMemcpyHostToDevice));
+    if(p_allgather) {
+        int rc = p_allgather(d_all + c->rank, d_all, sizeof(rec), /*ncclChar*/ 0, c->nccl_comm, c->stream);
+        if(rc) { cudaFree(d_all); return nccl_fail("ncclAllGather", rc); }
+        GF_CUDA(cudaStreamSynchronize(c->stream));
+        GF_CUDA(cudaMemcpy(all.data(), d_all, sizeof(rec) * c->nranks, cudaMemcpyDeviceToHost));
+    } else
+        all[c->rank] = my;
+    for(auto &r : all) ok = ok && r.ok;
+    if(ok) {
+        for(int r = 0; r < c->nranks && ok; r++) {
+            void *base = c->peer_buf;
+            if(r != c->rank) {
+                if(cudaIpcOpenMemHandle(&base, all[r].h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { ok = 0; cudaGetLastError(); break; }
+                c->peer_mapped[r] = base;
+            }
+            c->peer.slots[r] = static_cast<double *>(base);
+            c->peer.flags[r] = reinterpret_cast<unsigned long long *>(static_cast<char *>(base) + slots_bytes);
+        }
+    }
+    // second round: did every rank manage to map every peer?
+    double *d_flag = reinterpret_cast<double *>(d_all);
+    double v = ok ? 0.0 : 1.0;
+    GF_CUDA(cudaMemcpy(d_flag, &v, sizeof v, cudaMemcpyHostToDevice));
+    int rc = p_allreduce(d_flag, d_flag, 1, /*ncclDouble*/ 8, /*ncclSum*/ 0, c->nccl_comm, c->stream); // also NCCL's warm-up: channels are set up here, not in the first likelihood call
+    if(rc) { cudaFree(d_all); return nccl_fail("ncclAllReduce", rc); }
+    GF_CUDA(cudaStreamSynchronize(c->stream));
+    GF_CUDA(cudaMemcpy(&v, d_flag, sizeof v, cudaMemcpyDeviceToHost));
+    cudaFree(d_all);
+    if(v != 0.0) {
+        peer_teardown(c);
+        return 0;
+    }
+    c->peer.rank = c->rank;
+    c->peer.nranks = c->nranks;
+    c->peer.seq = 0;
+    c->peer.err = c->h_err_dev;
+    c->peer_on = true;
+    // one exchange now, so that the first likelihood call finds every mapping touched
+    gf_peer_view PV = gf_next_peer_view(c);
+    GF_CUDA(cudaMemcpy(c->d_result + GF_NPARTIAL * 8, &v, sizeof v, cudaMemcpyHostToDevice));
+    k_peer_allreduce<<<1, GF_THREADS, 0, c->stream>>>(c->d_result + GF_NPARTIAL * 8, 1, PV);
+    GF_CUDA(cudaStreamSynchronize(c->stream));
+    if(*c->h_err) {
+        peer_teardown(c);
+        return gf_fail("gf_comm_init: peer-memory warm-up exchange timed out");
+    }
+    return 0;
+}
+gf_peer_view gf_next_peer_view(gf_ctx *c) {
+    if(!gf_peer_active(c)) {
+        gf_peer_view none{};
+        none.nranks = 1;
+        return none;
+    }
+    c->peer.seq++;
+    return c->peer;
+}
+
 extern "C" int gf_comm_init(gf_ctx *c, const void *id128, int rank, int nranks) {
     if(!c) return gf_fail("null ctx");
     if(load_nccl()) return 1;
     if(nranks < 1 || rank < 0 || rank >= nranks) return gf_fail("gf_comm_init: bad rank");
     cudaSetDevice(c->device);
+    if(c->nccl_comm) gf_comm_destroy(c);
     gf_nccl_uid uid;
     std::memcpy(&uid, id128, sizeof uid);
     void *comm = nullptr;
@@ -405,13 +519,14 @@ extern "C" int gf_comm_init(gf_ctx *c, const void *id128, int rank, int nranks) 
     c->nccl_comm = comm;
     c->rank = rank;
     c->nranks = nranks;
-    return 0;
+    return nranks > 1 ? peer_setup(c) : 0;
 }
 extern "C" int gf_comm_destroy(gf_ctx *c) {
     if(!c) return gf_fail("null ctx");
     if(c->nccl_comm) {
         cudaSetDevice(c->device);
         cudaStreamSynchronize(c->stream);
+        peer_teardown(c);
         p_destroy(c->nccl_comm);
         c->nccl_comm = nullptr;
     }
@@ -419,9 +534,20 @@ extern "C" int gf_comm_destroy(gf_ctx *c) {
     c->rank = 0;
     return 0;
 }
+extern "C" const char *gf_comm_path(gf_ctx *c) {
+    if(!c || !c->nccl_comm || c->nranks <= 1) return "none";
+    return c->peer_on ? "peer-memory exchange over NVLink inside the reduction kernel (cudaIpc-mapped slots, rank-ordered sum)"
+                      : "in-stream ncclAllReduce";
+}
 extern "C" int gf_comm_attached(gf_ctx *c) { return c && c->nccl_comm ? c->nranks : 0; }
 int gf_allreduce_sum(gf_ctx *c, double *dev, int n) {
     if(!c->nccl_comm) return 0;
+    if(gf_peer_active(c) && n <= GF_PEER_SLOT) {
+        k_peer_allreduce<<<1, GF_THREADS, 0, c->stream>>>(dev, n, gf_next_peer_view(c));
+        c->launches++;
+        GF_CUDA(cudaGetLastError());
+        return 0;
+    }
     int rc = p_allreduce(dev, dev, (size_t)n, /*ncclDouble*/ 8, /*ncclSum*/ 0, c->nccl_comm, c->stream);
     return rc ? nccl_fail("ncclAllReduce", rc) : 0;
 }
@@ -644,7 +770,7 @@ static int eval_sum_launch(gf_ctx *c, int root, int metric, double *out_dev) {
     int blocks = gf_grid_blocks(c, c->view.n_events, eval_sum_blocks_per_sm(has));
     cudaEventRecord(c->ev0, c->stream);
     eval_sum_kernel(has)<<<blocks, GF_THREADS, gf_prog_smem(c), c->stream>>>(
-        c->view, first, root, metric, c->n_cols, c->d_partials, c->d_ticket, out_dev);
+        c->view, first, root, metric, c->n_cols, c->d_partials, c->d_ticket, out_dev, gf_next_peer_view(c));
     cudaEventRecord(c->ev1, c->stream);
     c->launches++;
     GF_CUDA(cudaGetLastError());
@@ -652,14 +778,15 @@ static int eval_sum_launch(gf_ctx *c, int root, int metric, double *out_dev) {
 }
 extern "C" int gf_eval_sum_async(gf_ctx *c, int root, int metric) {
     if(eval_sum_launch(c, root, metric, c ? c->d_result : nullptr)) return 1;
-    if(c->nccl_comm && gf_allreduce_sum(c, c->d_result, 1)) return 1;
+    if(c->nccl_comm && !gf_peer_active(c) && gf_allreduce_sum(c, c->d_result, 1)) return 1; // peer path: already summed in the kernel
     return 0;
 }
 
 extern "C" int gf_eval_sum(gf_ctx *c, int root, int metric, double *out) {
-    if(c && !c->nccl_comm && c->h_result_dev) {
-        // single GPU: the last block of the reduction writes the sum straight into mapped pinned host memory, so the
-        // call is launch + one synchronisation, with no device-to-host copy behind the kernel
+    if(c && (!c->nccl_comm || gf_peer_active(c)) && c->h_result_dev) {
+        // one GPU, or several with the peer-memory exchange: the last block of the reduction writes the (all-rank) sum
+        // straight into mapped pinned host memory, so the call is launch + one synchronisation, with no collective
+        // kernel and no device-to-host copy behind it
         if(eval_sum_launch(c, root, metric, c->h_result_dev)) return 1;
     } else {
         if(gf_eval_sum_async(c, root, metric)) return 1;
@@ -667,6 +794,7 @@ extern "C" int gf_eval_sum(gf_ctx *c, int root, int metric, double *out) {
     }
     GF_CUDA(cudaStreamSynchronize(c->stream));
     cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1);
+    if(c->h_err && *c->h_err) return gf_fail("gf_eval_sum: a rank did not join the peer-memory exchange within the time limit");
     *out = c->h_result[0];
     return 0;
 }

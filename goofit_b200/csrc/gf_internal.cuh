@@ -110,6 +110,72 @@ struct gf_evt_vals { // grid point / single point held in registers
 
 #include "gf_ops.cuh"
 
+// ---- peer-memory exchange of partial sums (multi-GPU, one process per GPU) ---------------------------------------------
+// Replaces MPI_Allreduce of the partial NLL (reference GooPdf.cu:72-75) and the in-stream NCCL all-reduce of round 1. Every
+// rank owns an exchange buffer that all peers map over NVLink (cudaIpc). The LAST block of a reduction kernel
+//   1. stores this rank's n partial sums into slot [parity][rank] of EVERY rank's buffer (remote stores over NVLink),
+//   2. releases a sequence-number flag next to them (fence.sys; st.release.sys),
+//   3. waits until all ranks' flags of this sequence number have arrived in its OWN buffer (ld.acquire.sys, local memory),
+//   4. adds the n_ranks slots in rank order -> the same bits on every rank, run to run, for a fixed number of ranks.
+// One kernel launch, no collective kernel behind it, the result written where the caller wants it (mapped pinned host
+// memory on the likelihood path). Two parities suffice: a rank cannot start exchange s+2 before every rank finished s+1,
+// which needs every rank to have left exchange s (all exchanges of a context are ordered on its one stream).
+#define GF_MAX_PEERS 16
+#define GF_PEER_SLOT 256 // doubles per rank and exchange (the largest payload is a 8x8 complex Gram block: 128)
+struct gf_peer_view {
+    double *slots[GF_MAX_PEERS];             // rank r's buffer as mapped here: [2][n_ranks][GF_PEER_SLOT]
+    unsigned long long *flags[GF_MAX_PEERS]; // rank r's flags: [2][n_ranks]
+    int rank, nranks;
+    unsigned long long seq; // sequence number of this exchange (host-incremented per launch), starts at 1
+    int *err;               // mapped host flag: set when a peer did not show up in time
+};
+__device__ inline unsigned long long gf_ld_acquire_sys(const unsigned long long *p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ inline void gf_st_release_sys(unsigned long long *p, unsigned long long v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ inline double gf_ld_relaxed_sys(const double *p) {
+    double v;
+    asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+    return v;
+}
+// Called by ALL threads of ONE block. vals[n] must be visible to the whole block (shared or global memory written before a
+// __syncthreads). out[k] receives the sum over ranks of vals[k] (written by thread k).
+__device__ inline void gf_peer_allreduce(const gf_peer_view &PV, const double *vals, int n, double *out) {
+    const int t = threadIdx.x, nr = PV.nranks, par = (int)(PV.seq & 1ull);
+    __shared__ int timed_out;
+    if(t == 0) timed_out = 0;
+    for(int i = t; i < n * nr; i += blockDim.x) {
+        const int peer = i / n, k = i - peer * n;
+        PV.slots[peer][((size_t)par * nr + PV.rank) * GF_PEER_SLOT + k] = vals[k];
+    }
+    __threadfence_system();
+    __syncthreads();
+    if(t < nr) gf_st_release_sys(PV.flags[t] + (size_t)par * nr + PV.rank, PV.seq);
+    if(t < nr) {
+        const unsigned long long *f = PV.flags[PV.rank] + (size_t)par * nr + t;
+        const long long t0 = clock64();
+        while(gf_ld_acquire_sys(f) < PV.seq) {
+            if(clock64() - t0 > 40000000000ll) { // ~20 s at 2 GHz: a rank is missing; fail loudly instead of hanging the GPU
+                *PV.err = 1;
+                timed_out = 1;
+                break;
+            }
+        }
+    }
+    __syncthreads();
+    if(t < n) {
+        const double *src = PV.slots[PV.rank] + (size_t)par * nr * GF_PEER_SLOT + t;
+        double s = 0;
+        for(int r = 0; r < nr; ++r) s += gf_ld_relaxed_sys(src + (size_t)r * GF_PEER_SLOT);
+        if(timed_out) s = __longlong_as_double(0x7ff8000000000000ll);
+        out[t] = s;
+    }
+}
+
 // ---- deterministic reduction -----------------------------------------------------------------
 // warp shuffle tree -> block tree (shared) -> per-block partial; the last block to arrive sums
 // the partials in index order with the same tree. Fixed grid => bit-reproducible run to run.
@@ -132,9 +198,11 @@ __device__ inline double gf_block_sum(double v, double *sh /* >= 32 doubles */) 
     return r; // valid in thread 0
 }
 // n_out independent sums laid out partials[k*gridDim.x + block]
+// PV.nranks > 1: the per-GPU sums are exchanged over peer memory by the last block and `out` receives the all-rank sums
 __device__ inline void gf_grid_finish(double *vals, int n_out, double *partials, unsigned *ticket, double *out,
-                                      double *sh) {
+                                      double *sh, const gf_peer_view &PV) {
     __shared__ bool is_last;
+    __shared__ double fin[GF_NPARTIAL];
     for(int k = 0; k < n_out; k++) {
         double r = gf_block_sum(vals[k], sh);
         if(threadIdx.x == 0) partials[(size_t)k * gridDim.x + blockIdx.x] = r;
@@ -152,17 +220,25 @@ __device__ inline void gf_grid_finish(double *vals, int n_out, double *partials,
             for(unsigned b = threadIdx.x; b < gridDim.x; b += blockDim.x)
                 s += __ldcg(partials + (size_t)k * gridDim.x + b);
             double r = gf_block_sum(s, sh);
-            if(threadIdx.x == 0) out[k] = r;
+            if(threadIdx.x == 0) {
+                if(PV.nranks > 1) fin[k] = r; else out[k] = r;
+            }
         }
         if(threadIdx.x == 0) *ticket = 0;
+        if(PV.nranks > 1) {
+            __syncthreads();
+            gf_peer_allreduce(PV, fin, n_out, out);
+        }
     }
 }
 
 // same, for a compile-time number of sums held in registers: the loops unroll, so `vals` is never indexed dynamically
 // (a runtime-indexed array would be demoted to local memory for the whole kernel, including its accumulation loop)
 template <int N>
-__device__ inline void gf_grid_finish_n(double (&vals)[N], double *partials, unsigned *ticket, double *out, double *sh) {
+__device__ inline void gf_grid_finish_n(double (&vals)[N], double *partials, unsigned *ticket, double *out, double *sh,
+                                        const gf_peer_view &PV) {
     __shared__ bool is_last_n;
+    __shared__ double fin_n[N];
 #pragma unroll
     for(int k = 0; k < N; k++) {
         double r = gf_block_sum(vals[k], sh);
@@ -181,9 +257,15 @@ __device__ inline void gf_grid_finish_n(double (&vals)[N], double *partials, uns
             for(unsigned b = threadIdx.x; b < gridDim.x; b += blockDim.x)
                 s += __ldcg(partials + (size_t)k * gridDim.x + b);
             double r = gf_block_sum(s, sh);
-            if(threadIdx.x == 0) out[k] = r;
+            if(threadIdx.x == 0) {
+                if(PV.nranks > 1) fin_n[k] = r; else out[k] = r;
+            }
         }
         if(threadIdx.x == 0) *ticket = 0;
+        if(PV.nranks > 1) {
+            __syncthreads();
+            gf_peer_allreduce(PV, fin_n, N, out);
+        }
     }
 }
 
@@ -222,6 +304,12 @@ struct gf_ctx {
     // NCCL (dlopen'ed) communicator for the partial-sum all-reduce
     void *nccl_comm = nullptr;
     int nranks = 1, rank = 0;
+    // peer-memory exchange (preferred over NCCL for payloads <= GF_PEER_SLOT doubles)
+    gf_peer_view peer{};
+    bool peer_on = false;
+    void *peer_buf = nullptr;                 // this rank's exchange buffer (slots + flags)
+    void *peer_mapped[GF_MAX_PEERS] = {nullptr}; // cudaIpcOpenMemHandle mappings of the other ranks' buffers
+    int *h_err = nullptr, *h_err_dev = nullptr; // mapped pinned error flag
     // async parameter ring + stopwatch
     static const int RING = 16;
     double *ring_buf[RING] = {nullptr};
@@ -249,3 +337,8 @@ int gf_grid_blocks(const gf_ctx *c, long n_items, int per_sm);
 int gf_alloc_aux_slot(gf_ctx *c);
 // all-reduce (sum) n doubles in place on the ctx stream when a communicator is attached; no-op otherwise
 int gf_allreduce_sum(gf_ctx *c, double *dev, int n);
+// the peer view of the NEXT exchange (sequence number advanced) when the peer path is on, else a view with nranks = 1:
+// pass it to a reduction kernel; kernels given a view with nranks > 1 leave the all-rank sums in `out`
+gf_peer_view gf_next_peer_view(gf_ctx *c);
+// after a kernel that was NOT given a peer view: all-reduce through NCCL when a communicator is attached
+inline bool gf_peer_active(const gf_ctx *c) { return c->peer_on && c->nranks > 1; }

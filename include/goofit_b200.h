@@ -169,10 +169,17 @@ int gf_amp4_get_amp(gf_ctx *, int node, int amp, double *out_re_im, size_t n_eve
  * Replaces the reference's MPI_Allreduce of the partial NLL (src/PDFs/GooPdf.cu:72-75). libnccl.so.2 is
  * dlopen'ed on first use. gf_comm_unique_id fills 128 bytes on rank 0; the caller ships them to every rank
  * (any side channel), then each rank calls gf_comm_init. Afterwards gf_eval_sum / gf_amp4_norm return the
- * sum over all ranks (same value on every rank). */
+ * sum over all ranks (same value on every rank).
+ * gf_comm_init also maps every rank's exchange buffer into every process (cudaIpc over NVLink): sums of up to 256
+ * doubles are then exchanged by the LAST BLOCK of the reduction kernel itself - remote stores into every peer's slot, a
+ * release/acquire flag per rank, a rank-ordered (bit-reproducible) sum - so a likelihood call on N GPUs is still one
+ * kernel launch and one synchronisation, with no collective kernel behind it. NCCL stays the fallback (no peer access,
+ * GOOFIT_B200_NO_PEER=1) and carries the handles at start-up, where its channel set-up is also paid (not in the fit). */
 int gf_comm_unique_id(void *id128);
 int gf_comm_init(gf_ctx *, const void *id128, int rank, int nranks);
 int gf_comm_destroy(gf_ctx *);
+/* how partial sums travel between ranks: "none", the peer-memory exchange, or NCCL (GOOFIT_B200_NO_PEER=1 forces NCCL) */
+const char *gf_comm_path(gf_ctx *);
 /* number of ranks of the attached communicator, 0 when none is attached (the host layer refuses to evaluate a
  * sharded dataset without one: a partial sum must never be mistaken for the likelihood) */
 int gf_comm_attached(gf_ctx *);

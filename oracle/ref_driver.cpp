@@ -1,7 +1,13 @@
 // TEST INFRASTRUCTURE (oracle). ROOT-free driver over the UNMODIFIED reference library built by
 // oracle/Makefile.ref (libgoofit_ref.so, OpenMP Thrust backend). It is never linked into the product.
 //   ref_driver golden <outdir>          write golden fixtures (.npy + manifest.json) for tests/golden
-//   ref_driver bench <config> <N> <K>   time K calculateNLL() calls on N synthetic events (CPU baseline)
+//   ref_driver bench <config> <N> <K> [W] [--data DIR] [--neumaier] [--fit] [--lsmove]
+//                                       time K FCN calls on N events (CPU baseline); with --data the events (and the MC
+//                                       normalisation sample) are read from DIR/*.npy, so that the product and the
+//                                       reference see identical inputs at any size; --neumaier adds a compensated sum of
+//                                       the reference's own per-event terms; --fit runs FitManager::fit() and reports the
+//                                       wall time, call count and fitted values; --lsmove also times calls on which a
+//                                       lineshape mass moves (DP4 / TDDP4)
 // Models follow the reference's examples: examples/exponential/exponential.cpp, examples/dalitz/dalitz.cpp:124-322,
 // examples/zachFit/zachFit.cpp:143-230, examples/DP4/DP4.cu:51-232, examples/TDDP4/TDDP4.cu:38-156.
 #include <goofit/Application.h>
@@ -17,11 +23,13 @@
 #include <goofit/PDFs/combine/ConvolutionPdf.h>
 #include <goofit/PDFs/combine/ProdPdf.h>
 #include <goofit/PDFs/physics/Amp3Body.h>
-#define private public // test infrastructure: read the reference's private MC sample and amplitude cache
+#define private public // test infrastructure: read (and, for the at-scale cases, inject) the reference's private MC sample
+#define protected public
 #include <goofit/PDFs/physics/Amp4Body.h>
 #include <goofit/PDFs/physics/detail/NormEvents_4Body_DeviceCached.h>
 #include <goofit/PDFs/physics/Amp4Body_TD.h>
 #undef private
+#undef protected
 #include <goofit/PDFs/physics/ThreeGaussResolution.h>
 #include <goofit/PDFs/physics/TruthResolution.h>
 #include <goofit/PDFs/physics/Amplitude.h>
@@ -53,6 +61,9 @@
 #include <climits>
 #include <cstdio>
 #include <fstream>
+#include <functional>
+#include <iomanip>
+#include <memory>
 #include <map>
 #include <omp.h>
 #include <random>
@@ -1090,32 +1101,269 @@ static void case_tddp4_fit() {
     put("tddp4fit.valid", (double)(int)fm.IsValid());
 }
 
-// ---- CPU baseline timing ------------------------------------------------------------------------
-// Each step = one Minuit-style call: coefficients move (masses/widths fixed as dalitz.cpp:298-305),
-// Params::from_minuit_vector semantics (Params.cpp:47-57) then calculateNLL().
-static int bench(const std::string &config, size_t N, int K, int W) {
+// ---- .npy reader (float64, C order, 1-D) --------------------------------------------------------------------------------
+static std::vector<double> load_npy(const std::string &path) {
+    std::ifstream f(path, std::ios::binary);
+    if(!f) throw std::runtime_error("cannot open " + path);
+    char magic[8];
+    f.read(magic, 8);
+    if(std::string(magic, 6) != "\x93NUMPY") throw std::runtime_error(path + ": not a .npy file");
+    size_t hl = 0;
+    if(magic[6] == 1) {
+        unsigned short h;
+        f.read(reinterpret_cast<char *>(&h), 2);
+        hl = h;
+    } else {
+        unsigned int h;
+        f.read(reinterpret_cast<char *>(&h), 4);
+        hl = h;
+    }
+    std::string hdr(hl, ' ');
+    f.read(&hdr[0], hl);
+    if(hdr.find("'<f8'") == std::string::npos || hdr.find("'fortran_order': False") == std::string::npos)
+        throw std::runtime_error(path + ": need little-endian float64 in C order");
+    size_t p0 = hdr.find("'shape': (") + 10, p1 = hdr.find(')', p0), total = 1;
+    std::stringstream ss(hdr.substr(p0, p1 - p0));
+    std::string tok;
+    bool any = false;
+    while(std::getline(ss, tok, ',')) {
+        if(tok.find_first_of("0123456789") == std::string::npos) continue;
+        total *= std::stoul(tok);
+        any = true;
+    }
+    if(!any) total = 1;
+    std::vector<double> v(total);
+    f.read(reinterpret_cast<char *>(v.data()), sizeof(double) * total);
+    if(!f) throw std::runtime_error(path + ": truncated");
+    return v;
+}
+static bool file_exists(const std::string &p) {
+    struct stat st;
+    return stat(p.c_str(), &st) == 0;
+}
+
+// compensated sum (MathUtils.cpp:11-30 is the reference's own Neumaier summation; restated here for a host vector)
+static double neumaier(const std::vector<double> &v) {
+    double sum = 0, c = 0;
+    for(double x : v) {
+        double t = sum + x;
+        c += std::fabs(sum) >= std::fabs(x) ? (sum - t) + x : (x - t) + sum;
+        sum = t;
+    }
+    return sum + c;
+}
+static double neumaier_nll_of_probs(const std::vector<double> &probs) {
+    std::vector<double> t(probs.size());
+    for(size_t i = 0; i < probs.size(); i++) t[i] = probs[i] > 0 ? -std::log(probs[i]) : 0.0; // MetricPointer.cu:13-21
+    return neumaier(t);
+}
+
+// ---- the full zachFit tree (examples/zachFit/zachFit.cpp:143-230), MC-stage variables fixed at their start values --------
+struct ZachModel {
+    Observable dm{"dm", 0.1395, 0.1665};
+    std::vector<Variable> free; // width_bw, delta, epsilon, slope, bkg_frac
+    std::vector<GooPdf *> keep;
+    AddPdf *total = nullptr;
+};
+static ZachModel *make_zach(bool johnson) {
+    auto *Z = new ZachModel();
+    Observable &dm = Z->dm;
+    dm.setNumBins(2700);
+    Variable mean1("kpi_mc_mean1", 0.145402), mean2("kpi_mc_mean2", 0.145465), mean3("kpi_mc_mean3", 0.145404);
+    Variable sigma1("kpi_mc_sigma1", 0.00010), sigma2("kpi_mc_sigma2", 0.00075), sigma3("kpi_mc_sigma3", 0.00020);
+    Variable pimass("kpi_mc_pimass", 0.13957), aslope("kpi_mc_aslope", -20.0), apower("kpi_mc_apower", 1.3);
+    Variable gfrac1("kpi_mc_gfrac1", 0.65), gfrac2("kpi_mc_gfrac2", 0.02), afrac("kpi_mc_afrac", 0.005);
+    auto *argus = new ArgusPdf("argus", dm, pimass, aslope, false, apower);
+    Variable dummyzero("kpi_rd_dummyzero", 0);
+    Variable delta("kpi_rd_delta", 0.000002, -0.00005, 0.00005), epsilon("kpi_rd_epsilon", 0.05, -0.1, 0.2);
+    auto *r1 = new ScaledGaussianPdf("resolution1", dm, dummyzero, sigma1, delta, epsilon);
+    auto *r2 = new ScaledGaussianPdf("resolution2", dm, dummyzero, sigma2, delta, epsilon);
+    auto *r3 = new ScaledGaussianPdf("resolution3", dm, dummyzero, sigma3, delta, epsilon);
+    Variable width_bw("kpi_rd_width_bw", 0.0001, 0.00001, 0.0005);
+    GooPdf *m1, *m2, *m3;
+    if(johnson) { // BASELINE.json words the config as "JohnsonSU (x) resolution": same tree, JohnsonSU as the convolved model
+        Variable jg("kpi_rd_jsu_gamma", -0.3), jd("kpi_rd_jsu_delta", 1.1);
+        m1 = new JohnsonSUPdf("jsu1", dm, mean1, width_bw, jg, jd);
+        m2 = new JohnsonSUPdf("jsu2", dm, mean2, width_bw, jg, jd);
+        m3 = new JohnsonSUPdf("jsu3", dm, mean3, width_bw, jg, jd);
+    } else {
+        m1 = new KinLimitBWPdf("rbw1", dm, mean1, width_bw);
+        m2 = new KinLimitBWPdf("rbw2", dm, mean2, width_bw);
+        m3 = new KinLimitBWPdf("rbw3", dm, mean3, width_bw);
+    }
+    auto *s1 = new ConvolutionPdf("signal1", dm, m1, r1);
+    auto *s2 = new ConvolutionPdf("signal2", dm, m2, r2);
+    auto *s3 = new ConvolutionPdf("signal3", dm, m3, r3);
+    s1->setIntegrationConstants(0.1395, 0.1665, 0.0000027);
+    s2->setIntegrationConstants(0.1395, 0.1665, 0.0000027);
+    s3->setIntegrationConstants(0.1395, 0.1665, 0.0000027);
+    auto *signal = new AddPdf("signal", {gfrac1, gfrac2, afrac}, {s1, s2, argus, s3});
+    Variable slope("kpi_rd_slope", -1.0, 0.1, -35.0, 25.0);
+    auto *bkg = new ArgusPdf("bkg", dm, pimass, slope, false);
+    Variable bkg_frac("kpi_rd_bkg_frac", 0.03, 0.0, 0.3);
+    Z->total = new AddPdf("total", {bkg_frac}, {bkg, signal});
+    Z->free  = {width_bw, delta, epsilon, slope, bkg_frac};
+    return Z;
+}
+
+// ---- CPU baseline timing / at-scale parity values ------------------------------------------------------------------------
+// Each step = one Minuit-style call through the reference's own FCN::operator(): Params::from_minuit_vector semantics
+// (Params.cpp:47-57) then calculateNLL(). The movers follow the schedule bench.py uses on the product side:
+// value_j(k) = start_j * (1 + 1e-3 * ((k + j) % 3 - 1)).
+struct ScaleOpts {
+    std::string data;
+    bool neumaier = false, fit = false, lsmove = false;
+};
+static int bench(const std::string &config, size_t N, int K, int W, const ScaleOpts &opt) {
     int threads = omp_get_max_threads();
     double t_setup = 0, t_first = 0;
     std::vector<double> ms;
-    double last = 0;
+    double last = 0, first_nll = 0, neum = 0, ms_lsmove = 0, last_lsmove = 0;
+    size_t n_mc = 0;
     auto now = [] { return std::chrono::steady_clock::now(); };
     auto secs = [](auto a, auto b) { return std::chrono::duration<double>(b - a).count(); };
+    auto col = [&](const std::string &name) {
+        std::vector<double> v = load_npy(opt.data + "/" + name + ".npy");
+        if(N && v.size() > N) v.resize(N);
+        return v;
+    };
+    GooPdf *top = nullptr;
+    std::vector<Variable> movers, report;          // Minuit-vector entries that move per call; values reported after a fit
+    std::function<void()> after_setdata = [] {};   // setDataSize of the amplitude PDFs
+    std::function<std::vector<double>()> probs;    // per-event normalised probabilities (for the compensated sum)
+    Variable *ls_var = nullptr;                    // lineshape mass moved by --lsmove
+    std::unique_ptr<UnbinnedDataSet> d;
     if(config == "dalitz") {
         DalitzModel *M = make_dalitz(false, 240);
-        UnbinnedDataSet d({M->m12, M->m13, M->eventNumber});
-        fill_dalitz_uniform(*M, d, N, 12345);
-        auto t0 = now();
-        M->signal->setData(&d);
-        M->signal->setDataSize(d.getNumEvents());
-        auto t1 = now();
-        last = M->signal->calculateNLL();
-        auto t2 = now();
-        t_setup = secs(t0, t1); t_first = secs(t1, t2);
-        FitManager fm(M->signal);
+        d.reset(new UnbinnedDataSet({M->m12, M->m13, M->eventNumber}));
+        if(opt.data.empty())
+            fill_dalitz_uniform(*M, *d, N, 12345);
+        else {
+            auto a = col("m12"), b = col("m13");
+            for(size_t i = 0; i < a.size(); i++) {
+                M->m12.setValue(a[i]); M->m13.setValue(b[i]); M->eventNumber.setValue(i);
+                d->addEvent();
+            }
+        }
+        top = M->signal;
+        after_setdata = [M, &d] { M->signal->setDataSize(d->getNumEvents()); };
+        for(size_t c = 2; c < M->coefs.size(); c++) movers.push_back(M->coefs[c]);
+        report = M->coefs;
+        probs = [M, &d] {
+            ProdPdf wrap{"wrap", {M->signal}};
+            wrap.setData(d.get());
+            M->signal->setDataSize(d->getNumEvents());
+            return wrap.getCompProbsAtDataPoints()[0];
+        };
+    } else if(config == "exponential") {
+        auto *x = new Observable("x", 0, 10);
+        d.reset(new UnbinnedDataSet(*x));
+        if(opt.data.empty())
+            fill_1d(*d, *x, N, 137, 1, 1.0);
+        else
+            for(double v : col("x")) { x->setValue(v); d->addEvent(); }
+        auto *alpha = new Variable("alpha", -2, 0.1, -10, 10);
+        auto *pdf = new ExpPdf("exppdf", *x, *alpha);
+        top = pdf;
+        movers = {*alpha};
+        report = movers;
+        probs = [pdf] { return pdf->getCompProbsAtDataPoints()[0]; };
+    } else if(config == "zachfit" || config == "zachfit_jsu") {
+        ZachModel *Z = make_zach(config == "zachfit_jsu");
+        d.reset(new UnbinnedDataSet(Z->dm));
+        if(opt.data.empty()) throw std::runtime_error("zachfit needs --data DIR with dm.npy");
+        for(double v : col("dm")) { Z->dm.setValue(v); d->addEvent(); }
+        top = Z->total;
+        movers = Z->free;
+        report = movers;
+        probs = [Z] { return Z->total->getCompProbsAtDataPoints()[0]; };
+    } else if(config == "dp4") {
+        DP4Model *M = make_dp4(opt.data.empty() ? (unsigned)std::max<size_t>(N, 1000) : 1000u, opt.lsmove);
+        d.reset(new UnbinnedDataSet({M->m12, M->m34, M->cos12, M->cos34, M->phi, M->eventNumber}));
+        if(opt.data.empty())
+            fill_dp4_phsp(*M, *d, N, 4242);
+        else {
+            auto a = col("m12"), b = col("m34"), c = col("cos12"), e = col("cos34"), f = col("phi");
+            for(size_t i = 0; i < a.size(); i++) {
+                M->m12.setValue(a[i]); M->m34.setValue(b[i]); M->cos12.setValue(c[i]); M->cos34.setValue(e[i]); M->phi.setValue(f[i]);
+                M->eventNumber.setValue(i);
+                d->addEvent();
+            }
+            // inject the product's MC normalisation sample into the reference's private containers (Amp4Body.cu:270-289)
+            Amp4Body *dp = M->dp;
+            size_t keepN = N;
+            N = 0; // MC columns are read whole
+            auto m0 = col("mc_m12"), m1 = col("mc_m34"), m2 = col("mc_cos12"), m3 = col("mc_cos34"), m4 = col("mc_phi");
+            N = keepN;
+            dp->norm_M12 = mcbooster::RealVector_d(m0.begin(), m0.end());
+            dp->norm_M34 = mcbooster::RealVector_d(m1.begin(), m1.end());
+            dp->norm_CosTheta12 = mcbooster::RealVector_d(m2.begin(), m2.end());
+            dp->norm_CosTheta34 = mcbooster::RealVector_d(m3.begin(), m3.end());
+            dp->norm_phi = mcbooster::RealVector_d(m4.begin(), m4.end());
+            dp->MCevents = m0.size();
+            dp->norm_SF = mcbooster::RealVector_d(m0.size() * dp->SpinFactors.size());
+            dp->norm_LS = mcbooster::mc_device_vector<fpcomplex>(m0.size() * dp->LineShapes.size());
+        }
+        n_mc = M->dp->getMCevents();
+        top = M->signal;
+        after_setdata = [M, &d] { M->dp->setDataSize(d->getNumEvents(), 6); };
+        for(int c = 0; c < 6; c++) movers.push_back(M->coefs[c]);
+        report = movers;
+        if(opt.lsmove) ls_var = &M->lsvars[2]; // K*(892) mass; a fit floats the six coefficients only (DP4.cu:140-177)
+        probs = [M] { return M->signal->getCompProbsAtDataPoints()[0]; };
+    } else if(config == "tddp4") {
+        TDModel *M = make_tddp4(0, opt.data.empty() ? (unsigned)std::max<size_t>(N, 1000) : 1000u, opt.lsmove, true);
+        d.reset(new UnbinnedDataSet(M->obs()));
+        if(opt.data.empty())
+            fill_td_phsp(*M, *d, N, 31337);
+        else {
+            auto a = col("m12"), b = col("m34"), c = col("cos12"), e = col("cos34"), f = col("phi"), t = col("dtime"), g = col("sigmat");
+            for(size_t i = 0; i < a.size(); i++) {
+                M->m12.setValue(a[i]); M->m34.setValue(b[i]); M->cos12.setValue(c[i]); M->cos34.setValue(e[i]); M->phi.setValue(f[i]);
+                M->dtime.setValue(t[i]); M->sigmat.setValue(g[i]); M->eventNumber.setValue(i);
+                d->addEvent();
+            }
+            auto *ne = dynamic_cast<NormEvents_4Body_DeviceCached *>(M->dp->_normEvents[0].get());
+            size_t keepN = N;
+            N = 0;
+            auto m0 = col("mc_m12"), m1 = col("mc_m34"), m2 = col("mc_cos12"), m3 = col("mc_cos34"), m4 = col("mc_phi");
+            N = keepN;
+            ne->_norm_M12_d = mcbooster::RealVector_d(m0.begin(), m0.end());
+            ne->_norm_M34_d = mcbooster::RealVector_d(m1.begin(), m1.end());
+            ne->_norm_CosTheta12_d = mcbooster::RealVector_d(m2.begin(), m2.end());
+            ne->_norm_CosTheta34_d = mcbooster::RealVector_d(m3.begin(), m3.end());
+            ne->_norm_phi_d = mcbooster::RealVector_d(m4.begin(), m4.end());
+            ne->_totNumAccNormEvents = m0.size();
+            ne->_sumInitWeights = m0.size();
+            ne->_norm_SF_d.resize(0);
+            ne->_norm_LS_d.resize(0);
+        }
+        n_mc = M->dp->getNumAccNormEvents();
+        top = M->signal;
+        after_setdata = [M, &d] { M->dp->setDataSize(d->getNumEvents(), 8); };
+        movers = M->mix;
+        report = movers;
+        if(opt.lsmove) ls_var = &M->lsvars[2];
+        probs = [M] { return M->signal->getCompProbsAtDataPoints()[0]; };
+    } else {
+        fprintf(stderr, "unknown bench config %s\n", config.c_str());
+        return 2;
+    }
+    const size_t n_events = d->getNumEvents();
+    auto t0 = now();
+    top->setData(d.get());
+    after_setdata();
+    auto t1 = now();
+    first_nll = top->calculateNLL();
+    auto t2 = now();
+    t_setup = secs(t0, t1); t_first = secs(t1, t2);
+    std::string fit_json;
+    {
+        FitManager fm(top);
         FCN *fcn = fm.getFCN();
         std::vector<double> v0 = fm.getParams()->make_minuit_vector(), v = v0;
         std::vector<int> idx;
-        for(size_t c = 2; c < M->coefs.size(); c++) idx.push_back(M->coefs[c].getFitterIndex());
+        for(auto &m : movers) idx.push_back(m.getFitterIndex());
         for(int k = 0; k < W + K; k++) {
             for(size_t c = 0; c < idx.size(); c++) v[idx[c]] = v0[idx[c]] * (1.0 + 1e-3 * ((k + (int)c) % 3 - 1));
             auto a = now();
@@ -1123,38 +1371,55 @@ static int bench(const std::string &config, size_t N, int K, int W) {
             auto b = now();
             if(k >= W) ms.push_back(1e3 * secs(a, b));
         }
-    } else if(config == "exponential") {
-        Observable x{"x", 0, 10};
-        UnbinnedDataSet d{x};
-        fill_1d(d, x, N, 137, 1, 1.0);
-        Variable alpha{"alpha", -2, 0.1, -10, 10};
-        ExpPdf pdf{"exppdf", x, alpha};
-        auto t0 = now();
-        pdf.setData(&d);
-        auto t1 = now();
-        last = pdf.calculateNLL();
-        auto t2 = now();
-        t_setup = secs(t0, t1); t_first = secs(t1, t2);
-        FitManager fm(&pdf);
-        FCN *fcn = fm.getFCN();
-        std::vector<double> v = fm.getParams()->make_minuit_vector();
-        for(int k = 0; k < W + K; k++) {
-            v[alpha.getFitterIndex()] = -2.0 + 0.01 * (k % 5);
-            auto a = now();
-            last = (*fcn)(v);
-            auto b = now();
-            if(k >= W) ms.push_back(1e3 * secs(a, b));
+        if(opt.lsmove && ls_var && !ls_var->IsFixed()) { // a lineshape mass moves on every call: caches + integral rebuilt
+            int li = ls_var->getFitterIndex();
+            std::vector<double> t;
+            for(int k = 0; k < 4; k++) {
+                v[li] = v0[li] * (1.0 + 1e-4 * (k + 1));
+                auto a = now();
+                last_lsmove = (*fcn)(v);
+                auto b = now();
+                if(k >= 1) t.push_back(1e3 * secs(a, b));
+            }
+            for(double x : t) ms_lsmove += x / t.size();
+            v[li] = v0[li];
         }
-    } else {
-        fprintf(stderr, "unknown bench config %s\n", config.c_str());
-        return 2;
+        // back to the last steady-state point, so that last_nll is what the caches hold from here on
+        last = (*fcn)(v);
+        if(opt.neumaier) {
+            neum = neumaier_nll_of_probs(probs());
+            top->setFitControl(std::make_shared<UnbinnedNllFit>());
+            top->setData(d.get());
+            after_setdata();
+        }
+        if(opt.fit) (*fcn)(v0); // the schedule moved the Variables: a fit starts from the constructor values again
+    }
+    if(opt.fit) {
+        FitManager fit(top);
+        fit.setVerbosity(0);
+        auto a = now();
+        auto fmin = fit.fit();
+        double wall = secs(a, now());
+        std::ostringstream o;
+        o << std::setprecision(17) << ", \"fit\": {\"wall_s\": " << wall << ", \"nfcn\": " << fmin.NFcn() << ", \"valid\": " << (bool(fit) ? "true" : "false")
+          << ", \"fval\": " << fmin.Fval() << ", \"edm\": " << fmin.Edm() << ", \"names\": [";
+        for(size_t i = 0; i < report.size(); i++) o << (i ? ", " : "") << "\"" << report[i].getName() << "\"";
+        o << "], \"values\": [";
+        for(size_t i = 0; i < report.size(); i++) o << (i ? ", " : "") << report[i].getValue();
+        o << "], \"errors\": [";
+        for(size_t i = 0; i < report.size(); i++) o << (i ? ", " : "") << report[i].getError();
+        o << "]}";
+        fit_json = o.str();
     }
     double tot = 0;
     for(double m : ms) tot += m;
-    double mean = tot / ms.size();
-    printf("{\"config\": \"%s\", \"n_events\": %zu, \"steps\": %d, \"warmup\": %d, \"threads\": %d, \"ms_per_step\": %.6f, "
-           "\"events_x_evals_per_s\": %.6e, \"setdata_s\": %.4f, \"first_call_s\": %.4f, \"last_nll\": %.17g}\n",
-           config.c_str(), N, K, W, threads, mean, (double)N / (mean * 1e-3), t_setup, t_first, last);
+    double mean = ms.empty() ? 0 : tot / ms.size();
+    printf("{\"config\": \"%s\", \"n_events\": %zu, \"n_mc\": %zu, \"steps\": %d, \"warmup\": %d, \"threads\": %d, \"ms_per_step\": %.6f, "
+           "\"events_x_evals_per_s\": %.6e, \"setdata_s\": %.4f, \"first_call_s\": %.4f, \"first_nll\": %.17g, \"last_nll\": %.17g",
+           config.c_str(), n_events, n_mc, K, W, threads, mean, mean > 0 ? (double)n_events / (mean * 1e-3) : 0.0, t_setup, t_first, first_nll, last);
+    if(opt.neumaier) printf(", \"neumaier_last_nll\": %.17g", neum);
+    if(opt.lsmove && ls_var) printf(", \"lsmove_ms_per_step\": %.6f, \"lsmove_last_nll\": %.17g", ms_lsmove, last_lsmove);
+    printf("%s}\n", fit_json.c_str());
     return 0;
 }
 
@@ -1185,7 +1450,17 @@ int main(int argc, char **argv) {
         }
         if(mode == "bench") {
             if(argc < 5) return 2;
-            return bench(argv[2], std::stoul(argv[3]), std::stoi(argv[4]), argc > 5 ? std::stoi(argv[5]) : 1);
+            ScaleOpts opt;
+            int W = 1;
+            for(int i = 5; i < argc; i++) {
+                std::string a = argv[i];
+                if(a == "--data" && i + 1 < argc) opt.data = argv[++i];
+                else if(a == "--neumaier") opt.neumaier = true;
+                else if(a == "--fit") opt.fit = true;
+                else if(a == "--lsmove") opt.lsmove = true;
+                else W = std::stoi(a);
+            }
+            return bench(argv[2], std::stoul(argv[3]), std::stoi(argv[4]), W, opt);
         }
     } catch(const std::exception &e) {
         fprintf(stderr, "ref_driver: %s\n", e.what());

@@ -32,6 +32,8 @@ box = [bytes(uid)]
 dist.broadcast_object_list(box, src=0)
 uid = (C.c_char * 128).from_buffer_copy(box[0])
 assert lib.gf_comm_init(ctx, uid, rank, world) == 0, capi.last_error()
+path = capi.comm_path(ctx)
+assert gf.comm_attached() == world
 
 G = os.path.join(ROOT, "tests", "golden")
 gold = {}
@@ -73,5 +75,5 @@ assert not bad, (rank, bad)
 dist.barrier()
 lib.gf_comm_destroy(ctx)
 if rank == 0:
-    print("MGPU_OK", json.dumps(res))
+    print("MGPU_OK", path, "|", json.dumps(res))
 dist.destroy_process_group()

@@ -402,3 +402,46 @@ def zach_model(dm_values, step=0.00003, numbins=270):
     o["frac"] = V("bkg_frac", 0.3, 0.01, 0, 1)
     o["total"] = gf.AddPdf("total", o["frac"], o["bkg"], o["conv"])
     return o
+
+
+class ZachFull:
+    """The complete zachFit tree (examples/zachFit/zachFit.cpp:143-230), MC-stage variables fixed at their start values:
+    total = AddPdf(bkg_frac; Argus bkg, AddPdf(gfrac1, gfrac2, afrac; conv1, conv2, Argus, conv3)) with
+    conv_i = KinLimitBW(mean_i, width_bw) (x) ScaledGaussian(0, sigma_i, delta, epsilon), 2.7e-6 integration step and a 2700-bin
+    normalisation grid. johnson=True swaps the convolved model for JohnsonSUPdf (the variant BASELINE.json words).
+    Mirrors oracle/ref_driver.cpp make_zach()."""
+
+    def __init__(self, johnson=False):
+        k = self.keep = Keep()
+        V = gf.Variable
+        dm = self.dm = gf.Observable("dm", 0.1395, 0.1665)
+        dm.numbins = 2700
+        mean = [V("kpi_mc_mean1", 0.145402), V("kpi_mc_mean2", 0.145465), V("kpi_mc_mean3", 0.145404)]
+        sigma = [V("kpi_mc_sigma1", 0.00010), V("kpi_mc_sigma2", 0.00075), V("kpi_mc_sigma3", 0.00020)]
+        pimass, aslope, apower = V("kpi_mc_pimass", 0.13957), V("kpi_mc_aslope", -20.0), V("kpi_mc_apower", 1.3)
+        gfrac1, gfrac2, afrac = V("kpi_mc_gfrac1", 0.65), V("kpi_mc_gfrac2", 0.02), V("kpi_mc_afrac", 0.005)
+        argus = k(gf.ArgusPdf("argus", dm, pimass, aslope, False, apower))
+        dummyzero = V("kpi_rd_dummyzero", 0)
+        delta, epsilon = V("kpi_rd_delta", 0.000002, -0.00005, 0.00005), V("kpi_rd_epsilon", 0.05, -0.1, 0.2)
+        width_bw = V("kpi_rd_width_bw", 0.0001, 0.00001, 0.0005)
+        convs = []
+        for i in range(3):
+            res = k(gf.ScaledGaussianPdf("resolution%d" % (i + 1), dm, dummyzero, sigma[i], delta, epsilon))
+            if johnson:
+                jg, jd = V("kpi_rd_jsu_gamma", -0.3), V("kpi_rd_jsu_delta", 1.1)
+                model = k(gf.JohnsonSUPdf("jsu%d" % (i + 1), dm, mean[i], width_bw, jg, jd))
+            else:
+                model = k(gf.KinLimitBWPdf("rbw%d" % (i + 1), dm, mean[i], width_bw))
+            c = k(gf.ConvolutionPdf("signal%d" % (i + 1), dm, model, res))
+            c.setIntegrationConstants(0.1395, 0.1665, 0.0000027)
+            convs.append(c)
+        self.convs = convs
+        signal = k(gf.AddPdf("signal", [gfrac1, gfrac2, afrac], [convs[0], convs[1], argus, convs[2]]))
+        slope = V("kpi_rd_slope", -1.0, 0.1, -35.0, 25.0)
+        bkg = k(gf.ArgusPdf("bkg", dm, pimass, slope, False))
+        bkg_frac = V("kpi_rd_bkg_frac", 0.03, 0.0, 0.3)
+        self.total = gf.AddPdf("total", [bkg_frac], [bkg, signal])
+        self.free = [width_bw, delta, epsilon, slope, bkg_frac]
+
+    def dataset(self, dm_values):
+        return dataset_from_columns([self.dm], [dm_values])
