@@ -506,6 +506,14 @@ class PdfBase {
     int getNormalizationIndex() const { return normSlot; }
     bool areParamsandConstantsEqualByVal(const PdfBase &other) const;
 
+    /// bumped whenever a parameter list of any PDF changes: holders of pointers into the lists (Params) re-resolve
+    static uint64_t &structureEpoch() {
+        static uint64_t e = 0;
+        return e;
+    }
+    /// every parameter entry of this tree whose NAME is `n`, one per distinct shared state (what updateVariable touches)
+    void collectParametersByName(const std::string &n, std::vector<Variable *> &out);
+
     // ---- flattening hooks (new; called by the Engine and by parent nodes, not by user code) ----
     /// emit records that are NOT evaluated per event (sub-PDFs of a convolution, resonances, ...)
     virtual void emitAux(detail::ProgramBuilder &B);
@@ -515,7 +523,10 @@ class PdfBase {
     virtual void afterProgram() {}
 
   protected:
-    void registerParameter(Variable var) { parametersList.push_back(var); }
+    void registerParameter(Variable var) {
+        parametersList.push_back(var);
+        ++structureEpoch();
+    }
     void unregisterParameter(Variable var);
     void registerConstant(fptype value) { constantsList.push_back(value); }
     void registerObservable(Observable obs);

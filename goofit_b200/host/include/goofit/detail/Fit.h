@@ -22,6 +22,11 @@ class Params : public Minuit2::MnUserParameters {
     PdfBase *pdf_;
     bool do_record_{false};
     std::vector<std::vector<double>> recorded_;
+    // updateVariable() matches parameters by NAME over the whole tree (PdfBase.cu:121-129): resolved once per tree
+    // structure instead of once per Minuit call (30 parameters x ~100 string compares is most of a 50 us call otherwise)
+    std::vector<std::vector<Variable *>> targets_;
+    uint64_t targets_epoch_{~uint64_t(0)};
+    void resolveTargets();
 
   public:
     using MnUserParameters::MnUserParameters;

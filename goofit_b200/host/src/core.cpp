@@ -367,7 +367,10 @@ void Engine::release(const PdfBase *pdf) {
 using detail::Engine;
 
 // ---- PdfBase ------------------------------------------------------------------------------------------
-PdfBase::~PdfBase() { Engine::get().release(this); }
+PdfBase::~PdfBase() {
+    ++structureEpoch();
+    Engine::get().release(this);
+}
 
 template <typename T>
 static bool find_in(const std::vector<T> &list, const T &item) {
@@ -397,7 +400,13 @@ std::vector<Observable> PdfBase::getObservables() const { // PdfBase.cpp:88-100
 void PdfBase::registerObservable(Observable obs) {
     if(!find_in(observablesList, obs)) observablesList.push_back(obs);
 }
+void PdfBase::collectParametersByName(const std::string &n, std::vector<Variable *> &out) {
+    for(auto &p : parametersList)
+        if(p.getName() == n && std::none_of(out.begin(), out.end(), [&](const Variable *q) { return *q == p; })) out.push_back(&p);
+    for(auto *c : components) c->collectParametersByName(n, out);
+}
 void PdfBase::unregisterParameter(Variable var) {
+    ++structureEpoch();
     auto it = std::find(parametersList.begin(), parametersList.end(), var);
     if(it != parametersList.end()) parametersList.erase(it);
     for(auto *c : components) c->unregisterParameter(var);

@@ -45,11 +45,19 @@ std::vector<double> Params::make_minuit_vector() const {
     for(const Variable &var : vars_) v.at(var.getFitterIndex()) = var.getValue();
     return v;
 }
+void Params::resolveTargets() {
+    targets_.assign(vars_.size(), {});
+    for(size_t i = 0; i < vars_.size(); i++) pdf_->collectParametersByName(vars_[i].getName(), targets_[i]);
+    targets_epoch_ = PdfBase::structureEpoch();
+}
 void Params::from_minuit_vector(const std::vector<double> &values, bool force_changed) {
-    for(Variable &var : vars_) {
+    if(targets_epoch_ != PdfBase::structureEpoch()) resolveTargets();
+    for(size_t i = 0; i < vars_.size(); i++) {
+        Variable &var = vars_[i];
         double nv = values.at(var.getFitterIndex());
         var.setChanged(force_changed ? true : var.getValue() != nv);
-        pdf_->updateVariable(var, nv - var.getBlind(Variable::Key()));
+        const double v = nv - var.getBlind(Variable::Key());
+        for(Variable *t : targets_[i]) t->setValue(v); // == pdf_->updateVariable(var, v)
     }
     if(do_record_) recorded_.push_back(values);
     pdf_->updateParameters();

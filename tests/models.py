@@ -425,10 +425,10 @@ class ZachFull:
         delta, epsilon = V("kpi_rd_delta", 0.000002, -0.00005, 0.00005), V("kpi_rd_epsilon", 0.05, -0.1, 0.2)
         width_bw = V("kpi_rd_width_bw", 0.0001, 0.00001, 0.0005)
         convs = []
+        jg, jd = V("kpi_rd_jsu_gamma", -0.3), V("kpi_rd_jsu_delta", 1.1)
         for i in range(3):
             res = k(gf.ScaledGaussianPdf("resolution%d" % (i + 1), dm, dummyzero, sigma[i], delta, epsilon))
             if johnson:
-                jg, jd = V("kpi_rd_jsu_gamma", -0.3), V("kpi_rd_jsu_delta", 1.1)
                 model = k(gf.JohnsonSUPdf("jsu%d" % (i + 1), dm, mean[i], width_bw, jg, jd))
             else:
                 model = k(gf.KinLimitBWPdf("rbw%d" % (i + 1), dm, mean[i], width_bw))
