@@ -255,8 +255,55 @@ def simple_fits(gf, lib, ctx, peak_hbm, steps=20):
     return out
 
 
+def call_latency(gf, lib, ctx, reps=400):
+    """the per-call floor: a Dalitz likelihood on 2 000 events (kernel ~ 10 us), so what is left is launch + parameter upload +
+    completion wait + host code. host_api = FCN::operator() from Python; c_abi = gf_set_params_async + gf_eval_sum."""
+    from models import Dalitz, dalitz_uniform_events
+    M = Dalitz(float_masses=False, grid=60)
+    a, b = dalitz_uniform_events(2000, 3)
+    d = M.dataset(a, b)
+    M.signal.setData(d)
+    M.signal.setDataSize(len(d))
+    M.signal.calculateNLL()
+    fm = gf.FitManager(M.signal)
+    fcn, params = fm.getFCN(), fm.getParams()
+    v = list(params.make_minuit_vector())
+    for _ in range(20):
+        fcn(v)
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        fcn(v)
+    t_host = (time.perf_counter() - t0) / reps
+    root = M.signal.getFunctionIndex()
+    p = np.array(gf.program_params(), dtype=np.float64)
+    n = np.array(gf.program_norms(), dtype=np.float64)
+    dptr = C.POINTER(C.c_double)
+    pp, np_ = p.ctypes.data_as(dptr), n.ctypes.data_as(dptr)
+    out = C.c_double(0)
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        lib.gf_set_params_async(ctx, pp, C.c_int(len(p)), np_, C.c_int(len(n)))
+        lib.gf_eval_sum(ctx, C.c_int(root), C.c_int(1), C.byref(out))
+    t_abi = (time.perf_counter() - t0) / reps
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        lib.gf_eval_sum(ctx, C.c_int(root), C.c_int(1), C.byref(out))
+    t_eval = (time.perf_counter() - t0) / reps
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        params.from_minuit_vector(v)
+    t_params = (time.perf_counter() - t0) / reps
+    ms = timed(lib, ctx, lambda: lib.gf_eval_sum_async(ctx, C.c_int(root), C.c_int(1)), 50)
+    return {"events": 2000, "host_api_us_per_call": 1e6 * t_host, "c_abi_upload_plus_eval_us": 1e6 * t_abi, "c_abi_eval_only_us": 1e6 * t_eval,
+            "from_minuit_vector_us": 1e6 * t_params, "kernel_us_queued": 1e3 * ms}
+
+
 def run_all(gf, lib, ctx, M_dalitz, n_events, peak_hbm, steps=20, with_reference=True):
     out = {}
+    try:
+        out["call_latency"] = call_latency(gf, lib, ctx)
+    except Exception as e:
+        out["call_latency"] = {"error": str(e)[:200]}
     peak_tf = fp64_peak(lib, ctx)
     out["fp64_peak_tflops_measured"] = peak_tf
     try:

@@ -226,7 +226,13 @@ extern "C" gf_ctx *gf_create(int device_id) {
                 && ok(cudaMalloc(&c->d_result, sizeof(double) * GF_NPARTIAL * 64), "result")
                 && ok(cudaMemset(c->d_result, 0, sizeof(double) * GF_NPARTIAL * 64), "result memset")
                 && ok(cudaHostAlloc(&c->h_result, sizeof(double) * GF_NPARTIAL * 64, cudaHostAllocMapped), "pinned result");
+    good = good && ok(cudaHostAlloc(&c->h_done, 64, cudaHostAllocMapped), "pinned completion flag");
     if(good) {
+        std::memset(c->h_done, 0, 64);
+        if(cudaHostGetDevicePointer((void **)&c->h_done_dev, c->h_done, 0) != cudaSuccess) {
+            c->h_done_dev = nullptr;
+            cudaGetLastError();
+        }
         std::memset(c->h_result, 0, sizeof(double) * GF_NPARTIAL * 64);
         if(cudaHostGetDevicePointer((void **)&c->h_result_dev, c->h_result, 0) != cudaSuccess) {
             c->h_result_dev = nullptr;
@@ -276,6 +282,9 @@ extern "C" void gf_destroy(gf_ctx *c) {
     cudaFree(c->d_nodes); cudaFree(c->d_params); cudaFree(c->d_consts); cudaFree(c->d_ints); // d_norms lives inside d_params' block
     cudaFree(c->d_partials); cudaFree(c->d_ticket); cudaFree(c->d_result); cudaFree(c->d_events_out);
     cudaFreeHost(c->h_result);
+    if(c->h_done) cudaFreeHost(c->h_done);
+    for(auto &e : c->prof_ev)
+        if(e) cudaEventDestroy(e);
     peer_teardown(c);
     if(c->nccl_comm && p_destroy) p_destroy(c->nccl_comm);
     if(c->h_err) cudaFreeHost(c->h_err);
@@ -502,6 +511,7 @@ gf_peer_view gf_next_peer_view(gf_ctx *c) {
         return none;
     }
     c->peer.seq++;
+    c->peer.done = nullptr;
     return c->peer;
 }
 
@@ -762,16 +772,22 @@ static int check_root(gf_ctx *c, int root) {
     return 0;
 }
 
-static int eval_sum_launch(gf_ctx *c, int root, int metric, double *out_dev) {
+static int eval_sum_launch(gf_ctx *c, int root, int metric, double *out_dev, bool signal_done = false) {
     if(check_root(c, root)) return 1;
     cudaSetDevice(c->device);
     int first = root - c->h_nodes[root].size + 1;
     const int has = program_class(c, first, root);
     int blocks = gf_grid_blocks(c, c->view.n_events, eval_sum_blocks_per_sm(has));
-    cudaEventRecord(c->ev0, c->stream);
+    gf_peer_view PV = gf_next_peer_view(c);
+    if(signal_done) {
+        PV.done = c->h_done_dev;
+        PV.done_seq = ++c->done_seq;
+    }
+    const bool prof = c->profiling && c->prof_n < gf_ctx::PROF;
+    if(prof) cudaEventRecord(c->prof_ev[2 * c->prof_n], c->stream);
     eval_sum_kernel(has)<<<blocks, GF_THREADS, gf_prog_smem(c), c->stream>>>(
-        c->view, first, root, metric, c->n_cols, c->d_partials, c->d_ticket, out_dev, gf_next_peer_view(c));
-    cudaEventRecord(c->ev1, c->stream);
+        c->view, first, root, metric, c->n_cols, c->d_partials, c->d_ticket, out_dev, PV);
+    if(prof) cudaEventRecord(c->prof_ev[2 * c->prof_n++ + 1], c->stream);
     c->launches++;
     GF_CUDA(cudaGetLastError());
     return 0;
@@ -782,20 +798,70 @@ extern "C" int gf_eval_sum_async(gf_ctx *c, int root, int metric) {
     return 0;
 }
 
+// Wait for the completion flag the last block writes behind the result: the host polls one pinned cache line (a few hundred
+// ns of latency) instead of a stream synchronisation. The stream is queried now and then so that a faulted kernel cannot
+// hang the caller.
+static int wait_done(gf_ctx *c) {
+    volatile unsigned long long *f = c->h_done;
+    const unsigned long long want = c->done_seq;
+    for(unsigned spin = 1;; ++spin) {
+        if(*f == want) return 0;
+        if((spin & 0x3fff) == 0) {
+            cudaError_t e = cudaStreamQuery(c->stream);
+            if(e == cudaSuccess) { // everything retired: the flag is visible by now (or the kernel never wrote it)
+                if(*f == want) return 0;
+                return gf_fail("gf_eval_sum: kernel finished without signalling completion");
+            }
+            if(e != cudaErrorNotReady) return gf_fail(std::string("gf_eval_sum: ") + cudaGetErrorString(e));
+        }
+#if defined(__x86_64__)
+        __builtin_ia32_pause();
+#endif
+    }
+}
+
 extern "C" int gf_eval_sum(gf_ctx *c, int root, int metric, double *out) {
-    if(c && (!c->nccl_comm || gf_peer_active(c)) && c->h_result_dev) {
+    if(c && (!c->nccl_comm || gf_peer_active(c)) && c->h_result_dev && c->h_done_dev) {
         // one GPU, or several with the peer-memory exchange: the last block of the reduction writes the (all-rank) sum
-        // straight into mapped pinned host memory, so the call is launch + one synchronisation, with no collective
-        // kernel and no device-to-host copy behind it
-        if(eval_sum_launch(c, root, metric, c->h_result_dev)) return 1;
+        // straight into mapped pinned host memory and then a completion flag, so the call is one launch and a poll of one
+        // cache line: no collective kernel, no device-to-host copy, no stream synchronisation
+        if(eval_sum_launch(c, root, metric, c->h_result_dev, true)) return 1;
+        if(wait_done(c)) return 1;
     } else {
         if(gf_eval_sum_async(c, root, metric)) return 1;
         GF_CUDA(cudaMemcpyAsync(c->h_result, c->d_result, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+        GF_CUDA(cudaStreamSynchronize(c->stream));
     }
-    GF_CUDA(cudaStreamSynchronize(c->stream));
-    cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1);
     if(c->h_err && *c->h_err) return gf_fail("gf_eval_sum: a rank did not join the peer-memory exchange within the time limit");
     *out = c->h_result[0];
+    return 0;
+}
+
+// opt-in per-kernel timing of the likelihood kernel: CUDA events around each of the next (up to 256) launches
+extern "C" int gf_profile_begin(gf_ctx *c) {
+    if(!c) return gf_fail("null ctx");
+    cudaSetDevice(c->device);
+    for(auto &e : c->prof_ev)
+        if(!e) GF_CUDA(cudaEventCreate(&e));
+    c->prof_n = 0;
+    c->profiling = true;
+    return 0;
+}
+// average duration (ms) of the launches recorded since gf_profile_begin; *n_launches = how many
+extern "C" int gf_profile_end(gf_ctx *c, float *avg_ms, int *n_launches) {
+    if(!c || !avg_ms) return gf_fail("gf_profile_end: null argument");
+    cudaSetDevice(c->device);
+    c->profiling = false;
+    GF_CUDA(cudaStreamSynchronize(c->stream));
+    double tot = 0;
+    for(int i = 0; i < c->prof_n; i++) {
+        float ms = 0;
+        GF_CUDA(cudaEventElapsedTime(&ms, c->prof_ev[2 * i], c->prof_ev[2 * i + 1]));
+        tot += ms;
+    }
+    *avg_ms = c->prof_n ? (float)(tot / c->prof_n) : 0.f;
+    c->last_ms = *avg_ms;
+    if(n_launches) *n_launches = c->prof_n;
     return 0;
 }
 
@@ -805,7 +871,6 @@ extern "C" int gf_sync(gf_ctx *c) {
     if(!c) return gf_fail("null ctx");
     cudaSetDevice(c->device);
     GF_CUDA(cudaStreamSynchronize(c->stream));
-    cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1);
     return 0;
 }
 extern "C" float gf_last_kernel_ms(gf_ctx *c) { return c ? c->last_ms : 0.f; }

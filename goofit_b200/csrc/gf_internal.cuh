@@ -128,7 +128,21 @@ struct gf_peer_view {
     int rank, nranks;
     unsigned long long seq; // sequence number of this exchange (host-incremented per launch), starts at 1
     int *err;               // mapped host flag: set when a peer did not show up in time
+    // completion flag in mapped pinned host memory (optional): written with `done_seq` after the results, so that the host
+    // can wait for a likelihood value by polling one cache line instead of paying a stream synchronisation
+    unsigned long long *done;
+    unsigned long long done_seq;
 };
+// results (written by threads 0..n-1 of this block before the call) -> system-visible, then the completion flag
+__device__ inline void gf_signal_done(const gf_peer_view &PV) {
+    if(PV.done == nullptr) return;
+    __threadfence_system();
+    __syncthreads();
+    if(threadIdx.x == 0) {
+        *reinterpret_cast<volatile unsigned long long *>(PV.done) = PV.done_seq;
+        __threadfence_system();
+    }
+}
 __device__ inline unsigned long long gf_ld_acquire_sys(const unsigned long long *p) {
     unsigned long long v;
     asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
@@ -229,6 +243,7 @@ __device__ inline void gf_grid_finish(double *vals, int n_out, double *partials,
             __syncthreads();
             gf_peer_allreduce(PV, fin, n_out, out);
         }
+        gf_signal_done(PV);
     }
 }
 
@@ -266,6 +281,7 @@ __device__ inline void gf_grid_finish_n(double (&vals)[N], double *partials, uns
             __syncthreads();
             gf_peer_allreduce(PV, fin_n, N, out);
         }
+        gf_signal_done(PV);
     }
 }
 
@@ -301,6 +317,14 @@ struct gf_ctx {
     int max_blocks = 0;
     float last_ms = 0;
     uint64_t launches = 0;
+    // per-kernel CUDA-event timing is opt-in (gf_profile_begin): two event records per launch are not free on a 50 us call
+    static const int PROF = 256;
+    bool profiling = false;
+    int prof_n = 0;
+    cudaEvent_t prof_ev[2 * PROF] = {nullptr};
+    // completion flag of the synchronous likelihood call (mapped pinned; the last block writes done_seq into it)
+    unsigned long long *h_done = nullptr, *h_done_dev = nullptr;
+    unsigned long long done_seq = 0;
     // NCCL (dlopen'ed) communicator for the partial-sum all-reduce
     void *nccl_comm = nullptr;
     int nranks = 1, rank = 0;

@@ -193,7 +193,11 @@ int gf_set_params_async(gf_ctx *, const double *params, int n, const double *nor
 /* measured FP64 FMA peak of this GPU (DFMA micro-benchmark, TFLOP/s, 2 flops per FMA): the roofline denominator of
  * the FP64-bound cache kernels (k_amp3_waves, k_amp4_cache), which MEASURED_PEAKS.json does not carry */
 int gf_fp64_peak(gf_ctx *, double *tflops);
-/* timing of the last kernel launched by gf_eval_sum (CUDA events on the ctx stream), ms */
+/* opt-in timing of the likelihood kernel: gf_profile_begin arms CUDA events around each of the next (up to 256)
+ * k_eval_sum launches on the ctx stream; gf_profile_end synchronises and returns their average duration. Off by default:
+ * two event records per launch are not free on a 50 us call. gf_last_kernel_ms returns the last such average. */
+int gf_profile_begin(gf_ctx *);
+int gf_profile_end(gf_ctx *, float *avg_ms, int *n_launches);
 float gf_last_kernel_ms(gf_ctx *);
 /* number of kernels this ctx has launched since creation */
 uint64_t gf_launch_count(gf_ctx *);
