@@ -150,6 +150,13 @@ def four_body(gf, lib, ctx, kind, n_data, n_mc, steps, peak_hbm):
     ms_pair = timed(lib, ctx, pair, 10)
     ms_norm = timed(lib, ctx, lambda: lib.gf_amp4_norm_async(ctx, C.c_int(node)), 10)
     ms_eval = timed(lib, ctx, lambda: lib.gf_eval_sum_async(ctx, C.c_int(root), C.c_int(1)), 10)
+    kernel_name = lib.gf_last_kernel_name(ctx).decode()
+    # A/B: the same call on the interpreter copy of the kernel
+    was = lib.gf_fast_enable(ctx, C.c_int(0))
+    lib.gf_eval_sum_async(ctx, C.c_int(root), C.c_int(1))
+    ms_interp = timed(lib, ctx, lambda: lib.gf_eval_sum_async(ctx, C.c_int(root), C.c_int(1)), 10)
+    lib.gf_fast_enable(ctx, C.c_int(was))
+    lib.gf_eval_sum_async(ctx, C.c_int(root), C.c_int(1))
     # default (Gram) mode: with the lineshapes fixed the MC integral is a host sum over G_ab, so the step is k_eval_sum
     ms = ms_eval
     bytes_step = bytes_evt * n_data
@@ -176,7 +183,7 @@ def four_body(gf, lib, ctx, kind, n_data, n_mc, steps, peak_hbm):
             "e2e": {"value": n_data / t_e2e, "ms_per_step": 1e3 * t_e2e, "launches_per_step": launches,
                     "setdata_s": t_setdata, "first_call_s": t_first, "phase_space_gen_s": t_gen},
             "roofline": {"bound": "hbm", "achieved": ach, "peak": peak_hbm, "unit": "GB/s", "frac": ach / peak_hbm,
-                         "kernel": "k_eval_sum",
+                         "kernel": kernel_name, "interpreter_kernel_ms": ms_interp,
                          "algorithmic_bytes_per_step": bytes_step,
                          "norm_kernel_ms": ms_norm, "norm_gbs": namp * 16 * n_mc / (ms_norm * 1e-3) / 1e9,
                          "eval_kernel_ms": ms_eval, "eval_gbs": bytes_evt * n_data / (ms_eval * 1e-3) / 1e9},
@@ -211,11 +218,16 @@ def simple_fits(gf, lib, ctx, peak_hbm, steps=20):
         t = (time.perf_counter() - t0) / steps
         root = pdf.getFunctionIndex()
         ms = timed(lib, ctx, lambda: lib.gf_eval_sum_async(ctx, C.c_int(root), C.c_int(1)), 10)
+        kname = lib.gf_last_kernel_name(ctx).decode()
+        was = lib.gf_fast_enable(ctx, C.c_int(0))
+        lib.gf_eval_sum_async(ctx, C.c_int(root), C.c_int(1))
+        ms_interp = timed(lib, ctx, lambda: lib.gf_eval_sum_async(ctx, C.c_int(root), C.c_int(1)), 10)
+        lib.gf_fast_enable(ctx, C.c_int(was))
         ach = 8.0 * len(xs) / (ms * 1e-3) / 1e9
         out[tag] = {"events": int(len(xs)), "value": len(xs) / (ms * 1e-3), "ms_per_step": ms,
                     "e2e": {"value": len(xs) / t, "ms_per_step": 1e3 * t},
                     "roofline": {"bound": "hbm", "achieved": ach, "peak": peak_hbm, "unit": "GB/s", "frac": ach / peak_hbm,
-                                 "kernel": "k_eval_sum", "algorithmic_bytes_per_step": 8 * len(xs)}}
+                                 "kernel": kname, "interpreter_kernel_ms": ms_interp, "algorithmic_bytes_per_step": 8 * len(xs)}}
         del pdf, d
     from models import zach_model
     n = 10_000_000

@@ -18,6 +18,10 @@ int gf_fail(const std::string &s) {
 extern "C" const char *gf_last_error(void) { return g_err.c_str(); }
 extern "C" int gf_version(void) { return 100; }
 
+// gf_fast.cu: shape-specialised copies of the likelihood kernel (no interpreter); 0 = shape not recognised
+int gf_fast_launch(gf_ctx *c, int first, int root, int metric, double *out_dev, const gf_peer_view &PV, const char **which);
+int gf_fast_reserve_smem(size_t sm);
+
 size_t gf_prog_smem(const gf_ctx *c) {
     return gf_sprog_bytes((int)c->h_nodes.size(), c->n_params, (int)c->h_consts.size(), c->n_norms, (int)c->h_ints.size());
 }
@@ -208,6 +212,10 @@ extern "C" gf_ctx *gf_create(int device_id) {
     }
     auto *c = new gf_ctx();
     c->device = device_id;
+    {
+        const char *e = std::getenv("GOOFIT_B200_NO_FAST");
+        c->fast_on = !(e && e[0] == '1');
+    }
     cudaDeviceProp prop;
     cudaGetDeviceProperties(&prop, device_id);
     c->sm_count = prop.multiProcessorCount;
@@ -392,6 +400,7 @@ extern "C" int gf_set_program(gf_ctx *c, const gf_node *nodes, int n_nodes, cons
         cudaError_t e = cudaSuccess;
         for(int has : {0, (int)GF_HAS_CONV, (int)GF_HAS_AMP3, (int)GF_HAS_AMP4_TD, GF_HAS_AMP4_TD | GF_HAS_3GAUSS, (int)GF_HAS_ALL})
             if(e == cudaSuccess) e = cudaFuncSetAttribute(eval_sum_kernel(has), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        if(e == cudaSuccess && gf_fast_reserve_smem(sm)) e = cudaGetLastError();
         if(e == cudaSuccess) e = cudaFuncSetAttribute(k_eval_events, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
         if(e == cudaSuccess) e = cudaFuncSetAttribute(k_grid_sum, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
         if(e != cudaSuccess) return bail(std::string("cannot reserve ") + std::to_string(sm) + " B of shared memory for the program block: " + cudaGetErrorString(e));
@@ -785,8 +794,13 @@ static int eval_sum_launch(gf_ctx *c, int root, int metric, double *out_dev, boo
     }
     const bool prof = c->profiling && c->prof_n < gf_ctx::PROF;
     if(prof) cudaEventRecord(c->prof_ev[2 * c->prof_n], c->stream);
-    eval_sum_kernel(has)<<<blocks, GF_THREADS, gf_prog_smem(c), c->stream>>>(
-        c->view, first, root, metric, c->n_cols, c->d_partials, c->d_ticket, out_dev, PV);
+    const char *which = "k_eval_sum";
+    const int fast = gf_fast_launch(c, first, root, metric, out_dev, PV, &which);
+    if(fast < 0) return gf_fail(std::string("likelihood kernel launch failed: ") + cudaGetErrorString(cudaGetLastError()));
+    if(fast == 0)
+        eval_sum_kernel(has)<<<blocks, GF_THREADS, gf_prog_smem(c), c->stream>>>(
+            c->view, first, root, metric, c->n_cols, c->d_partials, c->d_ticket, out_dev, PV);
+    c->last_kernel = which;
     if(prof) cudaEventRecord(c->prof_ev[2 * c->prof_n++ + 1], c->stream);
     c->launches++;
     GF_CUDA(cudaGetLastError());
@@ -874,6 +888,7 @@ extern "C" int gf_sync(gf_ctx *c) {
     return 0;
 }
 extern "C" float gf_last_kernel_ms(gf_ctx *c) { return c ? c->last_ms : 0.f; }
+extern "C" const char *gf_last_kernel_name(gf_ctx *c) { return c ? c->last_kernel : ""; }
 extern "C" uint64_t gf_launch_count(gf_ctx *c) { return c ? c->launches : 0; }
 
 extern "C" int gf_eval_events(gf_ctx *c, int root, int metric, double *out_host, size_t n) {

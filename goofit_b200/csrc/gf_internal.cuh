@@ -316,6 +316,8 @@ struct gf_ctx {
     size_t events_out_cap = 0;
     int max_blocks = 0;
     float last_ms = 0;
+    bool fast_on = true; // shape-specialised likelihood kernels (gf_fast.cu); GOOFIT_B200_NO_FAST=1 or gf_fast_enable(c, 0) turns them off
+    const char *last_kernel = ""; // which copy of the likelihood kernel the last gf_eval_sum launched
     uint64_t launches = 0;
     // per-kernel CUDA-event timing is opt-in (gf_profile_begin): two event records per launch are not free on a 50 us call
     static const int PROF = 256;

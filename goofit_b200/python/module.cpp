@@ -44,6 +44,10 @@ PYBIND11_MODULE(_goofit, m) {
           "raw gf_ctx* of the engine (for attaching an NCCL communicator through the C ABI)");
     m.def("launch_count", [] { return gf_launch_count(detail::Engine::get().ctx()); });
     m.def("last_kernel_ms", [] { return gf_last_kernel_ms(detail::Engine::get().ctx()); });
+    m.def("fast_enable", [](bool on) { return gf_fast_enable(detail::Engine::get().ctx(), on ? 1 : 0) != 0; }, "on"_a,
+          "shape-specialised likelihood kernels on/off (off = interpreter for every program); returns the previous setting");
+    m.def("last_kernel_name", [] { return std::string(gf_last_kernel_name(detail::Engine::get().ctx())); },
+          "which copy of the likelihood kernel the last NLL evaluation launched");
     m.def("program_params", [] { return py::array(py::cast(detail::Engine::get().prog.params)); },
           "copy of the flattened parameter block as last pushed by updateParameters()");
     m.def("program_norms", [] { return py::array(py::cast(detail::Engine::get().prog.norms)); });

@@ -199,6 +199,10 @@ int gf_fp64_peak(gf_ctx *, double *tflops);
 int gf_profile_begin(gf_ctx *);
 int gf_profile_end(gf_ctx *, float *avg_ms, int *n_launches);
 float gf_last_kernel_ms(gf_ctx *);
+/* which copy of the likelihood kernel the last gf_eval_sum / gf_eval_sum_async launched: "k_eval_sum" (the interpreter) or
+ * one of the shape-specialised copies of csrc/gf_fast.cu. GOOFIT_B200_NO_FAST=1 forces the interpreter (A/B runs). */
+const char *gf_last_kernel_name(gf_ctx *);
+int gf_fast_enable(gf_ctx *, int on); /* returns the previous setting */
 /* number of kernels this ctx has launched since creation */
 uint64_t gf_launch_count(gf_ctx *);
 

@@ -21,6 +21,21 @@ def rel(a, b):
     return abs(a - b) / max(abs(b), 1e-300)
 
 
+def fast_vs_interpreter(pdf, expect):
+    """The shape-specialised likelihood kernel (csrc/gf_fast.cu) and the interpreter on the same program and data: `expect`
+    is the copy that must have been launched; returns (fast NLL, interpreter NLL)."""
+    fast = pdf.calculateNLL()
+    assert gf.last_kernel_name() == expect, gf.last_kernel_name()
+    was = gf.fast_enable(False)
+    try:
+        slow = pdf.calculateNLL()
+        assert gf.last_kernel_name() == "k_eval_sum"
+    finally:
+        gf.fast_enable(was)
+    assert rel(fast, slow) < RTOL_NLL, (fast, slow)  # two compiled copies of the same arithmetic: FMA contraction differs
+    return fast, slow
+
+
 def check_pdf(golden, tag, pdf, data, gridvar=None, comps=True, rtol_evt=RTOL_EVT):
     pdf.setData(data)
     nll = pdf.calculateNLL()
@@ -57,6 +72,9 @@ def test_exponential(golden):
     assert rel(pdf.normalize(), golden["exp.normalize"]) < 1e-15
     check_pdf(golden, "exp", pdf, d, x)
     pdf.setData(d)
+    fast, slow = fast_vs_interpreter(pdf, "k_eval_logleaf")  # -(a x + log norm) against -log(exp(a x) norm)
+    assert rel(fast, golden["exp.nll"]) < RTOL_NLL and rel(slow, golden["exp.nll"]) < RTOL_NLL
+    pdf.setData(d)
     fm = gf.FitManager(pdf)
     fm.setVerbosity(0)
     fm.fit()
@@ -76,6 +94,9 @@ def test_gaussian(golden):
     assert rel(pdf.normalize(), golden["gauss.normalize"]) < 1e-15
     assert abs(pdf.normalize() - 6.26657) < 1e-5  # tests/simple/NormalizeTest.cpp:194
     check_pdf(golden, "gauss", pdf, d, x)
+    pdf.setData(d)
+    fast, slow = fast_vs_interpreter(pdf, "k_eval_logleaf")
+    assert rel(fast, golden["gauss.nll"]) < RTOL_NLL and rel(slow, golden["gauss.nll"]) < RTOL_NLL
 
 
 def test_normalize_test_known_answers():
@@ -306,6 +327,8 @@ def test_dp4_values(golden, mode):
         assert np.max(np.abs(w - r) / np.maximum(np.abs(r), 1e-300)) < 1e-10, a
     assert rel(1.0 / dp.getNormalization(), golden["dp4.integral"]) < 1e-12
     assert rel(nll, golden["dp4.nll"]) < RTOL_NLL
+    fast, slow = fast_vs_interpreter(sig, "k_eval_fast_amp4")
+    assert fast == nll and rel(slow, golden["dp4.nll"]) < RTOL_NLL
     probs = sig.getCompProbsAtDataPoints()
     np.testing.assert_allclose(probs[0], golden.arr("dp4.prob"), rtol=1e-10, atol=0)
     sig.setFitControl(gf.UnbinnedNllFit())
@@ -416,6 +439,8 @@ def test_tddp4_values(golden, tag, three_gauss, shared, mode):
     RTOL_INT = 1e-11
     assert rel(1.0 / dp.getNormalization(), golden[tag + ".integral"]) < RTOL_INT
     assert rel(nll, golden[tag + ".nll"]) < RTOL_NLL
+    fast, slow = fast_vs_interpreter(sig, "k_eval_fast_amp4_td")
+    assert fast == nll and rel(slow, golden[tag + ".nll"]) < RTOL_NLL
     probs = sig.getCompProbsAtDataPoints()
     # per-event values: 1e-10 relative; events deep in the resolution tail (p ~ 1e-6 of the typical value) are sums of
     # cancelling erfc/exp terms, so they additionally get an absolute allowance of a few ulp of the typical value

@@ -209,7 +209,9 @@ def test_dalitz_fit_at_scale():
     """10^6 events drawn from the model, fitted on both sides from the same start values (30 free coefficients)."""
     n = 1_000_000
     M = Dalitz(float_masses=False, grid=240)
-    m12, m13 = scale.dalitz_model_events(gf, M, n, 31)
+    # Whether Migrad ends below its EDM goal with 30 free coefficients depends on the sample (tools/diag_fit.py: valid at 10^5
+    # and 10^6 events of this draw, "above max EDM" at 3x10^5); this draw converges, and both arms must agree on that.
+    m12, m13 = scale.dalitz_model_events(gf, M, n, 31, chunk=4_000_000)
     d = scale.write_columns(scale.scratch_dir("dalitzfit"), {"m12": m12, "m13": m13})
     try:
         ref = scale.run_reference("dalitz", 0, 1, 0, data=d, fit=True)
@@ -226,9 +228,10 @@ def test_dalitz_fit_at_scale():
     p = scale.pulls(vals, rf["values"], rf["errors"])
     print("dalitz fit 1e6: nfcn %d vs %d, fval %.6f vs %.6f, max pull %.2e, wall %.2f s vs reference %.1f s (%d threads)"
           % (res.NFcn(), rf["nfcn"], res.Fval(), rf["fval"], p.max(), fm.lastFitSeconds(), rf["wall_s"], ref["threads"]))
-    assert rf["valid"] and bool(fm)
+    assert bool(fm) == rf["valid"], (bool(fm), rf["valid"], res.Edm(), res.IsAboveMaxEdm())
     assert p.max() < 0.01, p
     assert scale.rel(res.Fval(), rf["fval"]) < 1e-10
+    assert rf["valid"] and bool(fm)
 
 
 def test_dp4_fit_at_scale():
