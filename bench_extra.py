@@ -152,32 +152,46 @@ def four_body(gf, lib, ctx, kind, n_data, n_mc, steps, peak_hbm):
     ms_eval = timed(lib, ctx, lambda: lib.gf_eval_sum_async(ctx, C.c_int(root), C.c_int(1)), 10)
     kernel_name = lib.gf_last_kernel_name(ctx).decode()
     # A/B: the same call on the interpreter copy of the kernel
-    was = lib.gf_fast_enable(ctx, C.c_int(0))
+    was = lib.gf_set_option(ctx, b"fast", C.c_int(0))
     lib.gf_eval_sum_async(ctx, C.c_int(root), C.c_int(1))
     ms_interp = timed(lib, ctx, lambda: lib.gf_eval_sum_async(ctx, C.c_int(root), C.c_int(1)), 10)
-    lib.gf_fast_enable(ctx, C.c_int(was))
+    lib.gf_set_option(ctx, b"fast", C.c_int(was))
     lib.gf_eval_sum_async(ctx, C.c_int(root), C.c_int(1))
     # default (Gram) mode: with the lineshapes fixed the MC integral is a host sum over G_ab, so the step is k_eval_sum
     ms = ms_eval
     bytes_step = bytes_evt * n_data
     ach = bytes_step / (ms * 1e-3) / 1e9
     # lineshape move: K*(892) mass changes -> its lineshapes, the amplitudes using them and the Gram matrix are redone
-    l0 = gf.launch_count()
-    t0 = time.perf_counter()
-    for k in range(3):
-        M.lsvars[2].changed = True
-        sig.updateVariable(M.lsvars[2], 0.8958 + 1e-4 * (k + 1))
-        sig.updateParameters()
-        sig.calculateNLL()
-    lib.gf_sync(ctx)
-    t_ls = (time.perf_counter() - t0) / 3
-    launches_ls = (gf.launch_count() - l0) / 3
+    def ls_move(reps=5):
+        for k in range(2):  # warm-up (first use of a path allocates its scratch)
+            M.lsvars[2].changed = True
+            sig.updateVariable(M.lsvars[2], 0.8958 + 1e-4 * (k + 7))
+            sig.updateParameters()
+            sig.calculateNLL()
+        lib.gf_sync(ctx)
+        l0 = gf.launch_count()
+        t0 = time.perf_counter()
+        for k in range(reps):
+            M.lsvars[2].changed = True
+            sig.updateVariable(M.lsvars[2], 0.8958 + 1e-4 * (k + 1))
+            sig.updateParameters()
+            sig.calculateNLL()
+        lib.gf_sync(ctx)
+        return (time.perf_counter() - t0) / reps, (gf.launch_count() - l0) / reps
+
+    t_ls, launches_ls = ls_move()
+    was = lib.gf_set_option(ctx, b"fused", C.c_int(0))
+    t_ls_sep, launches_ls_sep = ls_move()
+    lib.gf_set_option(ctx, b"fused", C.c_int(was))
+    ls_move(1)
     return {"workload": "examples/DP4: Amp4Body, 8 amplitudes" if kind == "dp4" else "examples/TDDP4: Amp4Body_TD, 6 amplitudes, TruthResolution",
             "data_events": n_data, "mc_norm_events": n_mc, "unique_generated": unique,
             "value": n_data / (ms * 1e-3), "unit": "events*evals/s", "ms_per_step": ms,
             "norm_mode": "Gram (default): per-call MC pass only when a lineshape moved",
             "lineshape_move": {"ms_per_call": 1e3 * t_ls, "launches_per_call": launches_ls,
-                               "note": "K*(892) mass moves: lineshape + amplitude caches (data and MC) and G_ab rebuilt"},
+                               "separate_kernels_ms_per_call": 1e3 * t_ls_sep, "separate_kernels_launches": launches_ls_sep,
+                               "note": "K*(892) mass moves. One pass per sample (k_amp4_update): flagged lineshapes -> amplitudes -> G_ab on FP64 "
+                                       "tensor-core MMAs (MC), then the NLL kernel; 'separate' = k_amp4_cache + k_amp4_amps per sample + 4x4-tile k_amp4_gram"},
             "per_event_mode": {"ms_per_step": ms_pair, "value": n_data / (ms_pair * 1e-3),
                                "note": "reference association: MC-integral kernel every call"},
             "e2e": {"value": n_data / t_e2e, "ms_per_step": 1e3 * t_e2e, "launches_per_step": launches,
@@ -219,10 +233,10 @@ def simple_fits(gf, lib, ctx, peak_hbm, steps=20):
         root = pdf.getFunctionIndex()
         ms = timed(lib, ctx, lambda: lib.gf_eval_sum_async(ctx, C.c_int(root), C.c_int(1)), 10)
         kname = lib.gf_last_kernel_name(ctx).decode()
-        was = lib.gf_fast_enable(ctx, C.c_int(0))
+        was = lib.gf_set_option(ctx, b"fast", C.c_int(0))
         lib.gf_eval_sum_async(ctx, C.c_int(root), C.c_int(1))
         ms_interp = timed(lib, ctx, lambda: lib.gf_eval_sum_async(ctx, C.c_int(root), C.c_int(1)), 10)
-        lib.gf_fast_enable(ctx, C.c_int(was))
+        lib.gf_set_option(ctx, b"fast", C.c_int(was))
         ach = 8.0 * len(xs) / (ms * 1e-3) / 1e9
         out[tag] = {"events": int(len(xs)), "value": len(xs) / (ms * 1e-3), "ms_per_step": ms,
                     "e2e": {"value": len(xs) / t, "ms_per_step": 1e3 * t},

@@ -38,6 +38,11 @@ struct gf_amp4_state {
     double *d_gram = nullptr, *d_gram_partials = nullptr, *h_gram = nullptr;
     unsigned *d_gram_ticket = nullptr;
     int gram_blocks = 0;
+    // Gram matrix as the 8x8 MMA tiles of k_amp4_update (gf_amp4_cache_gram)
+    double *d_mma = nullptr, *d_mma_partials = nullptr, *h_mma = nullptr;
+    unsigned *d_mma_ticket = nullptr;
+    int mma_blocks = 0;
+    bool mma_valid = false;
     bool gram_valid = false;               // d_gram / h_gram hold every tile of the current MC amplitudes
     unsigned long long gram_pending = 0;   // MC amplitudes rebuilt since the last gf_amp4_gram
 };
@@ -52,6 +57,8 @@ void gf_amp4_free(gf_ctx *c) {
         free_set(s->mc);
         cudaFree(s->d_gram); cudaFree(s->d_gram_partials); cudaFree(s->d_gram_ticket);
         if(s->h_gram) cudaFreeHost(s->h_gram);
+        cudaFree(s->d_mma); cudaFree(s->d_mma_partials); cudaFree(s->d_mma_ticket);
+        if(s->h_mma) cudaFreeHost(s->h_mma);
         delete s;
     }
     c->amp4.clear();
@@ -162,13 +169,15 @@ __global__ void __launch_bounds__(GF_THREADS, 3)
 // One amplitude with compile-time shape: all of its lineshape / spin-factor loads are issued before the first multiply
 // (memory-level parallelism: the generic loop below has one dependent load in flight per thread), then the products are
 // formed in exactly the reference's order (AmpCalc.cu:36-57), so the result is bit-identical to the generic path.
-template <int LS_STEP, int SF_STEP, int NPERM>
+// COHERENT: the lineshape planes may have been written earlier in this very kernel (k_amp4_update), so they are read with
+// ordinary loads instead of the read-only path.
+template <int LS_STEP, int SF_STEP, int NPERM, bool COHERENT = false>
 __device__ __forceinline__ double2 gf_amp4_one(const int32_t *rec, const gf_amp4_args &A, long e) {
     constexpr int NLS = LS_STEP * NPERM, NSF = SF_STEP * NPERM;
     double2 L[NLS];
     double S[NSF];
 #pragma unroll
-    for(int j = 0; j < NLS; ++j) L[j] = __ldg(A.ls + (size_t)rec[3 + j] * A.ld + e);
+    for(int j = 0; j < NLS; ++j) L[j] = COHERENT ? A.ls[(size_t)rec[3 + j] * A.ld + e] : __ldg(A.ls + (size_t)rec[3 + j] * A.ld + e);
 #pragma unroll
     for(int j = 0; j < NSF; ++j) S[j] = __ldg(A.sf + (size_t)rec[3 + NLS + j] * A.ld + e);
     gf_cplx total = gf_c(0, 0);
@@ -185,6 +194,39 @@ __device__ __forceinline__ double2 gf_amp4_one(const int32_t *rec, const gf_amp4
     return make_double2(total.re, total.im);
 }
 
+// amplitude a of event e from the lineshape / spin-factor planes: A_a = 1/sqrt(nPerm) sum_perm prod LS prod SF (AmpCalc.cu:14-59)
+template <bool COHERENT>
+__device__ __forceinline__ double2 gf_amp4_build(const int32_t *rec, const gf_amp4_args &A, long e) {
+    const int numLS = rec[0], numSF = rec[1], nPerm = rec[2];
+    const int LS_step = numLS / nPerm, SF_step = numSF / nPerm;
+    const int shape = nPerm * 100 + LS_step * 10 + SF_step; // uniform over the grid
+    switch(shape) {
+    case 221: return gf_amp4_one<2, 1, 2, COHERENT>(rec, A, e); // Bose-symmetrised two-resonance chains (DP4, TDDP4)
+    case 121: return gf_amp4_one<2, 1, 1, COHERENT>(rec, A, e);
+    case 111: return gf_amp4_one<1, 1, 1, COHERENT>(rec, A, e);
+    case 211: return gf_amp4_one<1, 1, 2, COHERENT>(rec, A, e);
+    case 131: return gf_amp4_one<3, 1, 1, COHERENT>(rec, A, e);
+    case 231: return gf_amp4_one<3, 1, 2, COHERENT>(rec, A, e);
+    default: { // any other shape: the reference's loops as they are
+        gf_cplx total = gf_c(0, 0);
+        for(int p = 0; p < nPerm; ++p) {
+            gf_cplx ret = gf_c(1, 0);
+            for(int j = p * LS_step; j < (p + 1) * LS_step; ++j) {
+                double2 t = A.ls[(size_t)rec[3 + j] * A.ld + e];
+                ret = ret * gf_c(t.x, t.y);
+            }
+            for(int j = p * SF_step; j < (p + 1) * SF_step; ++j) {
+                double s = A.sf[(size_t)rec[3 + numLS + j] * A.ld + e];
+                ret = ret * gf_c(s, 0.0); // the reference multiplies by complex(sf, 0)
+            }
+            total = total + ret;
+        }
+        total = total * (1 / sqrt((double)nPerm));
+        return make_double2(total.re, total.im);
+    }
+    }
+}
+
 __global__ void __launch_bounds__(GF_THREADS, 3)
     k_amp4_amps(const gf_dev_view V, int node, gf_amp4_args A, unsigned long long amp_mask) {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -199,36 +241,7 @@ __global__ void __launch_bounds__(GF_THREADS, 3)
     for(long e = (long)blockIdx.x * blockDim.x + threadIdx.x; e < A.n; e += stride) {
         for(int a = 0; a < nAmp; ++a) {
             if(!((amp_mask >> a) & 1ull)) continue;
-            const int32_t *rec = rec0 + start[a];
-            const int numLS = rec[0], numSF = rec[1], nPerm = rec[2];
-            const int LS_step = numLS / nPerm, SF_step = numSF / nPerm;
-            const int shape = nPerm * 100 + LS_step * 10 + SF_step; // uniform over the grid
-            double2 out;
-            switch(shape) {
-            case 221: out = gf_amp4_one<2, 1, 2>(rec, A, e); break; // Bose-symmetrised two-resonance chains (DP4, TDDP4)
-            case 121: out = gf_amp4_one<2, 1, 1>(rec, A, e); break;
-            case 111: out = gf_amp4_one<1, 1, 1>(rec, A, e); break;
-            case 211: out = gf_amp4_one<1, 1, 2>(rec, A, e); break;
-            case 131: out = gf_amp4_one<3, 1, 1>(rec, A, e); break;
-            case 231: out = gf_amp4_one<3, 1, 2>(rec, A, e); break;
-            default: { // any other shape: the reference's loops as they are
-                gf_cplx total = gf_c(0, 0);
-                for(int p = 0; p < nPerm; ++p) {
-                    gf_cplx ret = gf_c(1, 0);
-                    for(int j = p * LS_step; j < (p + 1) * LS_step; ++j) {
-                        double2 t = A.ls[(size_t)rec[3 + j] * A.ld + e];
-                        ret = ret * gf_c(t.x, t.y);
-                    }
-                    for(int j = p * SF_step; j < (p + 1) * SF_step; ++j) {
-                        double s = A.sf[(size_t)rec[3 + numLS + j] * A.ld + e];
-                        ret = ret * gf_c(s, 0.0); // the reference multiplies by complex(sf, 0)
-                    }
-                    total = total + ret;
-                }
-                total = total * (1 / sqrt((double)nPerm));
-                out = make_double2(total.re, total.im);
-            }
-            }
+            const double2 out = gf_amp4_build<false>(rec0 + start[a], A, e);
             A.amps[(size_t)a * A.ld + e] = out;
         }
     }
@@ -322,6 +335,199 @@ __global__ void __launch_bounds__(GF_THREADS, 2)
         }
     }
     gf_grid_finish_n(acc, partials, ticket, out, red, PV);
+}
+
+// ---- fused update: lineshapes -> amplitudes -> Gram matrix in ONE pass over a sample -----------------------------------------
+// When a mass or width moves, the reference re-runs one thrust::transform per changed lineshape, one per amplitude, and then
+// its NormIntegrator over the whole MC sample (Amp4Body.cu:462-558, detail/NormLSCalculator.cu:11-62, NormIntegrator.cu:15-68).
+// k_amp4_update does the whole update of one sample in one pass: per event it evaluates the flagged lineshapes from the cached
+// pair masses (stored: a later call may move a different lineshape), rebuilds the amplitudes that contain them (stored), and
+// - on the MC sample in Gram mode - accumulates the full Hermitian Gram matrix G_ab = sum_m w_m A_a(m) conj(A_b(m)) with FP64
+// tensor-core MMAs (mma.sync m8n8k4): the amplitudes of 32 events are staged per warp in shared memory as the real 16 x 32
+// matrix X = [Re A; Im A]; with one 8-amplitude block, Re G = Re.Re^T + Im.Im^T and C2 = Im.Re^T (Im G_ab = C2_ab - C2_ba)
+// are three MMAs per four events whose 8x8 accumulators live distributed over the warp (4 registers per thread, instead of the
+// 72 a per-thread 8x8 complex accumulator would need - the reason k_amp4_gram tiles 4x4 and re-reads the planes per tile).
+// The rebuilt amplitudes never travel through HBM on their way to the sum, and the untouched ones are read once.
+#define GF_UPD_TS 36 // tile row stride in doubles: 4 mod 16, so the MMA fragment reads (8 rows x 4 events) of a half-warp hit 16 different 8-byte banks
+struct gf_ls_slot { // per-lineshape record in shared memory, filled once per block for the flagged lineshapes
+    gf_bw_inv inv;  // parameter-only part (valid when has_inv: constant daughters and a Breit-Wigner-type kind)
+    const double *mcol, *dcol, *lp, *lc;
+    double d1c, d2;
+    int kind, has_inv;
+};
+__device__ __forceinline__ void gf_dmma(double &c0, double &c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+constexpr int upd_tiles(int nb) { return nb == 1 ? 2 : (nb == 2 ? 6 : 0); } // 8x8 accumulator tiles: (C1, C2) per block pair (0,0) [, (0,1), (1,1)]
+constexpr int upd_blocks_per_sm(int) { return 2; }
+inline size_t gf_upd_smem(size_t prog, int nLS, int nb) {
+    return gf_align16(prog) + gf_align16(sizeof(gf_ls_slot) * (size_t)std::max(1, nLS)) + sizeof(double) * (GF_THREADS / 32) * 16 * nb * GF_UPD_TS;
+}
+// NB = 0: no Gram sum (data sample); 1: up to 8 amplitudes; 2: up to 16
+template <int NB>
+__global__ void __launch_bounds__(GF_THREADS, upd_blocks_per_sm(NB))
+    k_amp4_update(const gf_dev_view V, int node, gf_amp4_args A, unsigned long long ls_mask, unsigned long long amp_mask, const gf_amp4_kinmap K,
+                  const double *weights, double *partials, unsigned *ticket, double *out, const gf_peer_view PV) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ unsigned char flagged[64], untouched[64];
+    __shared__ int nflag, nun;
+    __shared__ bool is_last;
+    gf_sprog P = gf_stage_program(V, smem);
+    __syncthreads();
+    const gf_node &nd = P.nodes[node];
+    const int32_t *in = P.ints + nd.int_off;
+    const double *mc = P.consts + nd.con_off; // M, m1, m2, m3, m4
+    const int nLS = in[1], nSF = in[2], nAmp = in[3];
+    const int32_t *start = in + 5 + nLS + nSF;
+    const int32_t *rec0 = start + nAmp;
+    gf_ls_slot *slots = reinterpret_cast<gf_ls_slot *>(smem + gf_align16(gf_sprog_bytes(V.n_nodes, V.n_params, V.n_consts, V.n_norms, V.n_ints)));
+    double *tiles = reinterpret_cast<double *>(reinterpret_cast<unsigned char *>(slots) + gf_align16(sizeof(gf_ls_slot) * (size_t)(nLS > 1 ? nLS : 1)));
+    if((int)threadIdx.x < nLS && ((ls_mask >> threadIdx.x) & 1ull)) {
+        const int i = threadIdx.x;
+        const gf_node &ln = P.nodes[in[5 + i]];
+        gf_ls_slot L;
+        L.lc = P.consts + ln.con_off;
+        L.lp = P.params + ln.par_off;
+        L.kind = P.ints[ln.int_off];
+        const int pair = (int)L.lc[0];
+        if(pair < 2) { // LSCalculator.cu:47-53
+            L.d1c = pair == 0 ? mc[1] : mc[3];
+            L.d2 = pair == 0 ? mc[2] : mc[4];
+        } else
+            gf_pair_daughters(pair, L.d1c, L.d2, mc[1], mc[2], mc[3], mc[4]);
+        L.mcol = pair < 2 ? A.cols[pair] : A.kin + (size_t)K.m[i] * A.ld;
+        L.dcol = (pair >= 2 && K.d[i] >= 0) ? A.kin + (size_t)K.d[i] * A.ld : nullptr;
+        L.has_inv = (L.dcol == nullptr && gf_ls_has_inv(L.kind)) ? 1 : 0;
+        if(L.has_inv) L.inv = gf_bw_invariants(L.kind == GF_LS_SBW, L.d1c, L.d2, L.lp[0], L.lp[1]);
+        slots[i] = L;
+    }
+    if(threadIdx.x == 0) {
+        int nf = 0, nu = 0;
+        for(int i = 0; i < nLS; ++i)
+            if((ls_mask >> i) & 1ull) flagged[nf++] = (unsigned char)i;
+        for(int a = 0; a < nAmp; ++a)
+            if(!((amp_mask >> a) & 1ull)) untouched[nu++] = (unsigned char)a;
+        nflag = nf;
+        nun = nu;
+    }
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    double *T = tiles + (size_t)wib * 16 * NB * GF_UPD_TS; // rows: block b -> [16 b, 16 b + 8) = Re, [16 b + 8, 16 b + 16) = Im
+    if(NB > 0)
+        for(int k = threadIdx.x; k < (GF_THREADS / 32) * 16 * NB * GF_UPD_TS; k += blockDim.x) tiles[k] = 0.0; // rows of amplitudes >= nAmp stay zero
+    __syncthreads();
+    constexpr int NT = upd_tiles(NB);
+    double C[NT > 0 ? NT : 1][2];
+#pragma unroll
+    for(int t = 0; t < (NT > 0 ? NT : 1); ++t) C[t][0] = C[t][1] = 0.0;
+    const long warp_stride = (long)gridDim.x * (GF_THREADS / 32) * 32;
+    for(long base = ((long)blockIdx.x * (GF_THREADS / 32) + wib) * 32; base < A.n; base += warp_stride) {
+        const long e = base + lane;
+        const bool live = e < A.n;
+        if(live) {
+            if(NB > 0) { // amplitudes that stand: requested first, four at a time, so that their latency overlaps the lineshape arithmetic
+                for(int g = 0; g < nun; g += 4) {
+                    double2 v[4];
+#pragma unroll
+                    for(int j = 0; j < 4; ++j)
+                        if(g + j < nun) v[j] = __ldg(A.amps + (size_t)untouched[g + j] * A.ld + e);
+#pragma unroll
+                    for(int j = 0; j < 4; ++j)
+                        if(g + j < nun) {
+                            const int a = untouched[g + j];
+                            T[((a >> 3) * 16 + (a & 7)) * GF_UPD_TS + lane] = v[j].x;
+                            T[((a >> 3) * 16 + 8 + (a & 7)) * GF_UPD_TS + lane] = v[j].y;
+                        }
+                }
+            }
+            for(int f = 0; f < nflag; ++f) {
+                const int i = flagged[f];
+                const gf_ls_slot &L = slots[i];
+                const double mres = __ldg(L.mcol + e);
+                gf_cplx r;
+                if(L.has_inv)
+                    r = gf_lineshape_inv(L.kind, L.lp, L.lc, mres, L.inv);
+                else
+                    r = gf_lineshape(L.kind, L.lp, L.lc, mres, L.dcol ? __ldg(L.dcol + e) : L.d1c, L.d2);
+                A.ls[(size_t)i * A.ld + e] = make_double2(r.re, r.im);
+            }
+            for(int a = 0; a < nAmp; ++a) {
+                if(!((amp_mask >> a) & 1ull)) continue;
+                const double2 v = gf_amp4_build<true>(rec0 + start[a], A, e);
+                A.amps[(size_t)a * A.ld + e] = v;
+                if(NB > 0) {
+                    T[((a >> 3) * 16 + (a & 7)) * GF_UPD_TS + lane] = v.x;
+                    T[((a >> 3) * 16 + 8 + (a & 7)) * GF_UPD_TS + lane] = v.y;
+                }
+            }
+        } else if(NB > 0) {
+            for(int a = 0; a < nAmp; ++a) {
+                T[((a >> 3) * 16 + (a & 7)) * GF_UPD_TS + lane] = 0.0;
+                T[((a >> 3) * 16 + 8 + (a & 7)) * GF_UPD_TS + lane] = 0.0;
+            }
+        }
+        if(NB > 0) {
+            __syncwarp();
+            const double wv = weights ? (live ? __ldg(weights + e) : 0.0) : 1.0;
+            const int row = lane >> 2;
+#pragma unroll
+            for(int r = 0; r < 8; ++r) {
+                const int col = 4 * r + (lane & 3);
+                const double w = weights ? __shfl_sync(0xffffffffu, wv, col) : 1.0;
+                const double re0 = T[row * GF_UPD_TS + col], im0 = T[(8 + row) * GF_UPD_TS + col];
+                const double wre0 = weights ? w * re0 : re0, wim0 = weights ? w * im0 : im0;
+                gf_dmma(C[0][0], C[0][1], wre0, re0);
+                gf_dmma(C[0][0], C[0][1], wim0, im0);
+                gf_dmma(C[1][0], C[1][1], wim0, re0);
+                if(NB > 1) {
+                    const double re1 = T[(16 + row) * GF_UPD_TS + col], im1 = T[(24 + row) * GF_UPD_TS + col];
+                    const double wre1 = weights ? w * re1 : re1, wim1 = weights ? w * im1 : im1;
+                    gf_dmma(C[2][0], C[2][1], wre0, re1); // block pair (0,1): Re G
+                    gf_dmma(C[2][0], C[2][1], wim0, im1);
+                    gf_dmma(C[3][0], C[3][1], wim0, re1); // Im G = Im.Re^T - Re.Im^T
+                    gf_dmma(C[3][0], C[3][1], -wre0, im1);
+                    gf_dmma(C[4][0], C[4][1], wre1, re1); // block pair (1,1)
+                    gf_dmma(C[4][0], C[4][1], wim1, im1);
+                    gf_dmma(C[5][0], C[5][1], wim1, re1);
+                }
+            }
+            __syncwarp();
+        }
+    }
+    if(NB == 0) return;
+    // deterministic reduction of the NT 8x8 tiles: warps in order -> block partial; blocks in order by the last block to arrive
+    __syncthreads();
+    double *red = tiles; // [warp][NT][64], the amplitude tiles are no longer needed
+#pragma unroll
+    for(int t = 0; t < NT; ++t) {
+        red[((size_t)wib * NT + t) * 64 + (lane >> 2) * 8 + 2 * (lane & 3)] = C[t][0];
+        red[((size_t)wib * NT + t) * 64 + (lane >> 2) * 8 + 2 * (lane & 3) + 1] = C[t][1];
+    }
+    __syncthreads();
+    for(int k = threadIdx.x; k < NT * 64; k += blockDim.x) {
+        double sum = 0;
+        for(int w = 0; w < GF_THREADS / 32; ++w) sum += red[(size_t)w * NT * 64 + k];
+        partials[(size_t)k * gridDim.x + blockIdx.x] = sum;
+    }
+    __threadfence();
+    __syncthreads();
+    if(threadIdx.x == 0) {
+        unsigned t = atomicAdd(ticket, 1u);
+        is_last = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if(!is_last) return;
+    __threadfence();
+    double *fin = tiles + (size_t)(GF_THREADS / 32) * NT * 64;
+    for(int k = threadIdx.x; k < NT * 64; k += blockDim.x) {
+        double sum = 0;
+        for(unsigned b = 0; b < gridDim.x; ++b) sum += __ldcg(partials + (size_t)k * gridDim.x + b);
+        if(PV.nranks > 1) fin[k] = sum; else out[k] = sum;
+    }
+    if(threadIdx.x == 0) *ticket = 0;
+    if(PV.nranks > 1) {
+        __syncthreads();
+        gf_peer_allreduce(PV, fin, NT * 64, out);
+    }
 }
 
 // ---- C ABI ---------------------------------------------------------------------------------------------------
@@ -431,6 +637,7 @@ extern "C" int gf_amp4_set_mc(gf_ctx *c, int node, const double *const *mc_cols5
     s->mc.owned_cols = nullptr; s->mc.weights = nullptr;
     if(alloc_caches(c, s, s->mc, n_mc)) return 1;
     s->gram_valid = false;
+    s->mma_valid = false;
     GF_CUDA(cudaMalloc(&s->mc.owned_cols, sizeof(double) * 5 * (size_t)s->mc.ld));
     for(int k = 0; k < 5; k++) {
         GF_CUDA(cudaMemcpyAsync(s->mc.owned_cols + (size_t)k * s->mc.ld, mc_cols5[k], sizeof(double) * n_mc, cudaMemcpyHostToDevice, c->stream));
@@ -500,6 +707,120 @@ extern "C" int gf_amp4_cache(gf_ctx *c, int node, int redo_spins, const uint8_t 
     if(run_set(c, s, node, s->data, redo_spins, ls_mask, amp_mask)) return 1;
     if(run_set(c, s, node, s->mc, redo_spins, ls_mask, mc_amp_mask)) return 1;
     s->gram_pending |= mc_amp_mask;
+    if(mc_amp_mask) s->mma_valid = false;
+    return 0;
+}
+
+// host view of the Gram matrix from the tiles of k_amp4_update<NB>: tile 2p = Re part, 2p + 1 = Im part of block pair p
+static void gram_from_mma_tiles(const double *t, int nb, int n, double *G) {
+    auto re = [&](int tile, int i, int j) { return t[(size_t)tile * 64 + i * 8 + j]; };
+    for(int a = 0; a < n; a++)
+        for(int b = a; b < n; b++) {
+            const int ba = a >> 3, bb = b >> 3, i = a & 7, j = b & 7;
+            double gr, gi;
+            if(ba == bb) { // diagonal block: C1 = Re.Re^T + Im.Im^T, C2 = Im.Re^T, Im G_ab = C2_ab - C2_ba
+                const int p = (nb == 1 || ba == 0) ? 0 : 2;
+                gr = re(2 * p, i, j);
+                gi = re(2 * p + 1, i, j) - re(2 * p + 1, j, i);
+            } else { // block pair (0,1): C2 already holds Im.Re^T - Re.Im^T
+                gr = re(2, i, j);
+                gi = re(3, i, j);
+            }
+            G[2 * (a * n + b)] = gr;
+            G[2 * (a * n + b) + 1] = a == b ? 0.0 : gi;
+            if(a != b) {
+                G[2 * (b * n + a)] = gr;
+                G[2 * (b * n + a) + 1] = -gi;
+            }
+        }
+}
+typedef void (*upd_kernel_t)(const gf_dev_view, int, gf_amp4_args, unsigned long long, unsigned long long, const gf_amp4_kinmap, const double *,
+                             double *, unsigned *, double *, const gf_peer_view);
+static int launch_update(gf_ctx *c, gf_amp4_state *s, int node, gf_amp4_set &S, int nb, unsigned long long ls_mask, unsigned long long amp_mask,
+                         double *partials, unsigned *ticket, double *out, const gf_peer_view &PV) {
+    gf_amp4_args A;
+    for(int k = 0; k < 5; k++) A.cols[k] = S.cols[k];
+    A.n = S.n; A.ld = S.ld; A.ls = S.ls; A.sf = S.sf; A.amps = S.amps; A.kin = S.kin;
+    upd_kernel_t k = nb == 0 ? k_amp4_update<0> : (nb == 1 ? k_amp4_update<1> : k_amp4_update<2>);
+    const size_t sm = gf_upd_smem(gf_prog_smem(c), s->nLS, nb);
+    if(sm > 48 * 1024) GF_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    k<<<gf_grid_blocks(c, S.n, upd_blocks_per_sm(nb)), GF_THREADS, sm, c->stream>>>(c->view, node, A, ls_mask, amp_mask, s->kin, S.weights, partials, ticket, out, PV);
+    c->launches++;
+    GF_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// gf_amp4_cache followed by gf_amp4_gram, as ONE pass per sample (k_amp4_update): the call the host layer makes in Gram mode
+// when a lineshape moved. Falls back to the separate kernels for more than 16 amplitudes or with GOOFIT_B200_NO_FUSED=1.
+extern "C" int gf_amp4_cache_gram(gf_ctx *c, int node, int redo_spins, const uint8_t *ls_redo, const uint8_t *amp_redo, double *G_re_im) {
+    gf_amp4_state *s;
+    if(amp4_check(c, node, &s, false)) return 1;
+    if(!s->mc.amps) return gf_fail("gf_amp4_cache_gram: no MC normalisation sample (gf_amp4_set_mc)");
+    if(!G_re_im) return gf_fail("gf_amp4_cache_gram: null output");
+    if(!c->fused_on || s->nAmp > 16) {
+        if(gf_amp4_cache(c, node, redo_spins, ls_redo, amp_redo)) return 1;
+        return gf_amp4_gram(c, node, G_re_im);
+    }
+    cudaSetDevice(c->device);
+    if(s->data.ls && s->data.n != c->view.n_events) return gf_fail("gf_amp4_cache_gram: cache size != uploaded events");
+    const unsigned long long ls_mask = mask64(ls_redo, s->nLS), amp_mask = mask64(amp_redo, s->nAmp);
+    const gf_node &nd = c->h_nodes[node];
+    const int32_t *in = c->h_ints.data() + nd.int_off;
+    unsigned long long mc_amp_mask = 0;
+    for(int a = 0; a < s->nAmp; a++) {
+        int off = 5 + s->nLS + s->nSF + s->nAmp + in[5 + s->nLS + s->nSF + a];
+        bool need = redo_spins != 0;
+        for(int j = 0; j < in[off] && !need; j++) need = (ls_mask >> in[off + 3 + j]) & 1ull;
+        if(need) mc_amp_mask |= (1ull << a);
+    }
+    const int nb = s->nAmp <= 8 ? 1 : 2, nt = upd_tiles(nb), blocks = gf_grid_blocks(c, s->mc.n, upd_blocks_per_sm(nb));
+    if(!s->d_mma || s->mma_blocks < blocks) {
+        cudaFree(s->d_mma); cudaFree(s->d_mma_partials); cudaFree(s->d_mma_ticket);
+        if(s->h_mma) cudaFreeHost(s->h_mma);
+        s->d_mma = s->d_mma_partials = s->h_mma = nullptr;
+        s->d_mma_ticket = nullptr;
+        GF_CUDA(cudaMalloc(&s->d_mma, sizeof(double) * 6 * 64));
+        GF_CUDA(cudaMalloc(&s->d_mma_partials, sizeof(double) * 6 * 64 * (size_t)blocks));
+        GF_CUDA(cudaMalloc(&s->d_mma_ticket, sizeof(unsigned)));
+        GF_CUDA(cudaMemsetAsync(s->d_mma_ticket, 0, sizeof(unsigned), c->stream));
+        GF_CUDA(cudaMallocHost(&s->h_mma, sizeof(double) * 6 * 64));
+        s->mma_blocks = blocks;
+        s->mma_valid = false;
+    }
+    gf_amp4_args A;
+    size_t sm = gf_prog_smem(c);
+    if(redo_spins) {
+        if(sm > 48 * 1024) cudaFuncSetAttribute(k_amp4_sf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        for(gf_amp4_set *S : {&s->mc, &s->data}) {
+            if(S->n == 0 || !S->ls) continue;
+            for(int k = 0; k < 5; k++) A.cols[k] = S->cols[k];
+            A.n = S->n; A.ld = S->ld; A.ls = S->ls; A.sf = S->sf; A.amps = S->amps; A.kin = S->kin;
+            k_amp4_sf<<<gf_grid_blocks(c, S->n, 1), GF_THREADS, sm, c->stream>>>(c->view, node, A, s->kin);
+            c->launches++;
+        }
+        GF_CUDA(cudaGetLastError());
+    }
+    // MC sample first: its Gram sum is what the host waits for; the data sample's update runs behind it on the stream
+    const bool mc_work = (ls_mask | mc_amp_mask) != 0 || !s->mma_valid;
+    if(mc_work) {
+        gf_peer_view PV = gf_next_peer_view(c);
+        if(launch_update(c, s, node, s->mc, nb, ls_mask, mc_amp_mask, s->d_mma_partials, s->d_mma_ticket, s->d_mma, PV)) return 1;
+        if(c->nccl_comm && !gf_peer_active(c) && gf_allreduce_sum(c, s->d_mma, nt * 64)) return 1;
+        GF_CUDA(cudaMemcpyAsync(s->h_mma, s->d_mma, sizeof(double) * nt * 64, cudaMemcpyDeviceToHost, c->stream));
+        GF_CUDA(cudaEventRecord(c->ev1, c->stream));
+    }
+    if(s->data.n > 0 && s->data.ls && (ls_mask | amp_mask)) {
+        gf_peer_view none{};
+        none.nranks = 1;
+        if(launch_update(c, s, node, s->data, 0, ls_mask, amp_mask, nullptr, nullptr, nullptr, none)) return 1;
+    }
+    if(mc_work) {
+        GF_CUDA(cudaEventSynchronize(c->ev1)); // the Gram tiles only: the data-sample update keeps running behind the host sum
+        if(c->h_err && *c->h_err) return gf_fail("gf_amp4_cache_gram: a rank did not join the peer-memory exchange within the time limit");
+        s->mma_valid = true;
+    }
+    gram_from_mma_tiles(s->h_mma, nb, s->nAmp, G_re_im);
+    s->gram_pending |= mc_amp_mask; // the 4x4-tile copy of gf_amp4_gram (if it is ever asked for) is stale for these
     return 0;
 }
 

@@ -145,18 +145,40 @@ __device__ inline double gf_bl2(double z2, int L) { // Common.cu:38-51
     if(L == 2) return 1.0 / (z2 * z2 + 3 * z2 + 9);
     return 0;
 }
+// Parameter-only part of BW / SBW / lass_MINT / GLASS (BW.cu:19-27,62-63; :77-82,106-107; :127-131; GLASS.cu:22-27): what does
+// not depend on the event while the pair's daughters are constants. The lineshape kernels evaluate it once per block for such
+// pairs (three-body pairs have an event-dependent d1 and evaluate it per event); the operations and their order are the
+// reference's, only where they are executed changes.
+struct gf_bw_inv {
+    double mpsq, mmsq;
+    double prSq;  // |num2 / (4 mass^2)|
+    double prSq2; // max(num2 / (4 mass^2), 0)
+    double k;     // normalisation of the relativistic (RBW) or simple (SBW) Breit-Wigner
+};
+__device__ inline gf_bw_inv gf_bw_invariants(bool sbw, double m1, double m2, double mass, double width) {
+    gf_bw_inv I;
+    I.mpsq = (m1 + m2) * (m1 + m2);
+    I.mmsq = (m1 - m2) * (m1 - m2);
+    double num2 = (mass * mass - I.mpsq) * (mass * mass - I.mmsq);
+    double pr = num2 / (4 * mass * mass);
+    I.prSq2 = pr < 0 ? 0 : pr;
+    I.prSq = fabs(pr);
+    if(sbw) {
+        double gamma = sqrt(mass * mass * (mass * mass + width * width));
+        I.k = mass * width * gamma / sqrt(mass * mass + gamma);
+    } else {
+        double gamma = mass * sqrt((mass * mass + width * width));
+        I.k = (2.0 * sqrt(2.0) / M_PI) * mass * width * gamma / sqrt(mass * mass + gamma);
+    }
+    return I;
+}
 // BW.cu:14-69
-__device__ inline gf_cplx gf_ls_bw(double Mpair, double m1, double m2, double mass, double width, int orbital, int FF,
-                                   double meson_radius) {
+__device__ inline gf_cplx gf_ls_bw_pt(double Mpair, double mass, double width, int orbital, int FF, double meson_radius, const gf_bw_inv &I) {
     const int to2Lplus1 = 2 * orbital + 1;
     double M2 = Mpair * Mpair;
-    double mpsq = (m1 + m2) * (m1 + m2), mmsq = (m1 - m2) * (m1 - m2);
-    double num = (M2 - mpsq) * (M2 - mmsq);
-    double num2 = (mass * mass - mpsq) * (mass * mass - mmsq);
+    double num = (M2 - I.mpsq) * (M2 - I.mmsq);
     double pABSq = num / (4 * M2);
-    double prSqForGofM = num2 / (4 * mass * mass);
-    double prSq2 = prSqForGofM < 0 ? 0 : prSqForGofM;
-    prSqForGofM = fabs(prSqForGofM);
+    double prSqForGofM = I.prSq, prSq2 = I.prSq2;
     double pratio = sqrt(pABSq / prSqForGofM);
     double pr2J1 = 1;
     for(int i = 0; i < to2Lplus1; i++) pr2J1 *= pratio;
@@ -169,22 +191,20 @@ __device__ inline gf_cplx gf_ls_bw(double Mpair, double m1, double m2, double ma
         frFactor = (FF == 3 ? gf_bl2(pABSq * r2, orbital) : frFactor);
     }
     double GofM = width * pr2J1 * mratio * thisFR;
-    double gamma = mass * sqrt((mass * mass + width * width));
-    double k = (2.0 * sqrt(2.0) / M_PI) * mass * width * gamma / sqrt(mass * mass + gamma);
     gf_cplx bw = gf_c(mass * mass - M2, mass * GofM);
     double den = (mass * mass - M2) * (mass * mass - M2) + mass * GofM * mass * GofM;
-    return ((sqrt(k * frFactor)) / den) * bw;
+    return ((sqrt(I.k * frFactor)) / den) * bw;
+}
+__device__ inline gf_cplx gf_ls_bw(double Mpair, double m1, double m2, double mass, double width, int orbital, int FF,
+                                   double meson_radius) {
+    return gf_ls_bw_pt(Mpair, mass, width, orbital, FF, meson_radius, gf_bw_invariants(false, m1, m2, mass, width));
 }
 // BW.cu:72-115
-__device__ inline gf_cplx gf_ls_sbw(double Mpair, double m1, double m2, double mass, double width, int orbital, int FF,
-                                    double meson_radius) {
+__device__ inline gf_cplx gf_ls_sbw_pt(double Mpair, double mass, double width, int orbital, int FF, double meson_radius, const gf_bw_inv &I) {
     double M2 = Mpair * Mpair;
-    double mpsq = (m1 + m2) * (m1 + m2), mmsq = (m1 - m2) * (m1 - m2);
-    double num = (M2 - mpsq) * (M2 - mmsq);
-    double num2 = (mass * mass - mpsq) * (mass * mass - mmsq);
+    double num = (M2 - I.mpsq) * (M2 - I.mmsq);
     double pABSq = num / (4 * M2);
-    double prSq = num2 / (4 * mass * mass);
-    double prSq2 = prSq < 0 ? 0 : prSq;
+    double prSq2 = I.prSq2;
     double r2 = meson_radius * meson_radius;
     double frFactor = 1;
     if(0 != orbital && 0 != FF) {
@@ -192,22 +212,22 @@ __device__ inline gf_cplx gf_ls_sbw(double Mpair, double m1, double m2, double m
         frFactor = (FF == 3 ? gf_bl2(pABSq * r2, orbital) : frFactor);
     }
     double GofM = width;
-    double gamma = sqrt(mass * mass * (mass * mass + width * width));
-    double k = mass * width * gamma / sqrt(mass * mass + gamma);
     gf_cplx bw = gf_c(mass * mass - M2, mass * GofM);
     double den = (mass * mass - M2) * (mass * mass - M2) + mass * GofM * mass * GofM;
-    return ((sqrt(k * frFactor)) / den) * bw;
+    return ((sqrt(I.k * frFactor)) / den) * bw;
+}
+__device__ inline gf_cplx gf_ls_sbw(double Mpair, double m1, double m2, double mass, double width, int orbital, int FF,
+                                    double meson_radius) {
+    return gf_ls_sbw_pt(Mpair, mass, width, orbital, FF, meson_radius, gf_bw_invariants(true, m1, m2, mass, width));
 }
 // BW.cu:118-148
-__device__ inline gf_cplx gf_ls_lass(double Mpair, double m1, double m2, double resmass, double reswidth, int orbital,
-                                     int FF, double meson_radius) {
+__device__ inline gf_cplx gf_ls_lass_pt(double Mpair, double resmass, double reswidth, int orbital, int FF, double meson_radius,
+                                        const gf_bw_inv &I) {
     double rMass2 = Mpair * Mpair;
     double a = 2.07, r = 3.32;
-    double mpsq = (m1 + m2) * (m1 + m2), mmsq = (m1 - m2) * (m1 - m2);
-    double num = (rMass2 - mpsq) * (rMass2 - mmsq);
-    double num2 = (resmass * resmass - mpsq) * (resmass * resmass - mmsq);
+    double num = (rMass2 - I.mpsq) * (rMass2 - I.mmsq);
     double pABSq = num / (4 * rMass2);
-    double prSq = fabs(num2 / (4 * resmass * resmass));
+    double prSq = I.prSq;
     double y = 2.0 * a * sqrt(pABSq);
     double x = 2.0 + a * r * pABSq;
     double cot = x / y;
@@ -215,7 +235,11 @@ __device__ inline gf_cplx gf_ls_lass(double Mpair, double m1, double m2, double 
     gf_cplx den = gf_c(sqrt(pABSq) * cot, (-1.) * sqrt(pABSq));
     double SF = Mpair * sqrt(prSq) / (resmass * resmass * reswidth);
     gf_cplx BG = SF / den;
-    return BG + phaseshift * gf_ls_bw(Mpair, m1, m2, resmass, reswidth, orbital, FF, meson_radius);
+    return BG + phaseshift * gf_ls_bw_pt(Mpair, resmass, reswidth, orbital, FF, meson_radius, I);
+}
+__device__ inline gf_cplx gf_ls_lass(double Mpair, double m1, double m2, double resmass, double reswidth, int orbital,
+                                     int FF, double meson_radius) {
+    return gf_ls_lass_pt(Mpair, resmass, reswidth, orbital, FF, meson_radius, gf_bw_invariants(false, m1, m2, resmass, reswidth));
 }
 // Bugg.cu:11-36
 __device__ inline gf_cplx gf_bugg_rho2(double s, double m) {
@@ -353,6 +377,16 @@ __device__ inline gf_cplx gf_ls_focus(double Mpair, int mod) {
     if(mod == 0) return (gf_c(K11, 0) - I * rho2 * detK) / del;
     if(mod == 1) return K12 / del;
     return 1. / (gf_c(1., 0) - I * rho2 * K32);
+}
+// which kinds have a parameter-only part worth keeping per block (gf_bw_inv), and whether it is the SBW form
+__device__ __host__ inline bool gf_ls_has_inv(int kind) { return kind == GF_LS_RBW || kind == GF_LS_SBW || kind == GF_LS_LASS; }
+// as gf_lineshape below for the kinds of gf_ls_has_inv, with the parameter-only part supplied by the caller
+__device__ inline gf_cplx gf_lineshape_inv(int kind, const double *p, const double *c, double Mpair, const gf_bw_inv &I) {
+    switch(kind) {
+    case GF_LS_RBW: return gf_ls_bw_pt(Mpair, p[0], p[1], (int)c[1], (int)c[2], c[3], I);
+    case GF_LS_SBW: return gf_ls_sbw_pt(Mpair, p[0], p[1], (int)c[1], (int)c[2], c[3], I);
+    default: return gf_ls_lass_pt(Mpair, p[0], p[1], (int)c[1], (int)c[2], c[3], I);
+    }
 }
 // dispatch on the lineshape record: params mass,width ; consts Mpair,L,FF,radius ; ints[0] kind
 __device__ inline gf_cplx gf_lineshape(int kind, const double *p, const double *c, double Mpair, double d1, double d2) {

@@ -213,8 +213,9 @@ extern "C" gf_ctx *gf_create(int device_id) {
     auto *c = new gf_ctx();
     c->device = device_id;
     {
-        const char *e = std::getenv("GOOFIT_B200_NO_FAST");
+        const char *e = std::getenv("GOOFIT_B200_NO_FAST"), *f = std::getenv("GOOFIT_B200_NO_FUSED");
         c->fast_on = !(e && e[0] == '1');
+        c->fused_on = !(f && f[0] == '1');
     }
     cudaDeviceProp prop;
     cudaGetDeviceProperties(&prop, device_id);

@@ -264,10 +264,14 @@ int gf_fast_launch(gf_ctx *c, int first, int root, int metric, double *out_dev, 
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 
-// A/B switch: 0 forces the interpreter for every program (returns the previous setting)
-extern "C" int gf_fast_enable(gf_ctx *c, int on) {
-    if(!c) return 0;
-    int was = c->fast_on ? 1 : 0;
-    c->fast_on = on != 0;
+// A/B switches (return the previous setting, -1 for an unknown name):
+//   "fast"  shape-specialised likelihood kernels of this file (0: interpreter for every program)
+//   "fused" one-pass lineshape -> amplitude -> Gram update of gf_amp4.cu (0: separate kernels + 4x4-tile Gram sums)
+extern "C" int gf_set_option(gf_ctx *c, const char *name, int value) {
+    if(!c || !name) return -1;
+    bool *flag = !std::strcmp(name, "fast") ? &c->fast_on : (!std::strcmp(name, "fused") ? &c->fused_on : nullptr);
+    if(!flag) return -1;
+    int was = *flag ? 1 : 0;
+    *flag = value != 0;
     return was;
 }

@@ -48,7 +48,7 @@ struct gf_sprog {
 
 __host__ __device__ inline size_t gf_align16(size_t x) { return (x + 15) & ~size_t(15); }
 
-inline size_t gf_sprog_bytes(int n_nodes, int n_params, int n_consts, int n_norms, int n_ints) {
+__host__ __device__ inline size_t gf_sprog_bytes(int n_nodes, int n_params, int n_consts, int n_norms, int n_ints) {
     return gf_align16(sizeof(gf_node) * n_nodes) + gf_align16(8 * (size_t)n_params) + gf_align16(8 * (size_t)n_consts)
            + gf_align16(8 * (size_t)n_norms) + gf_align16(4 * (size_t)n_ints) + 8 * (GF_MAX_OBS + 2 * GF_MAX_AUX) + 64;
 }
@@ -121,7 +121,7 @@ struct gf_evt_vals { // grid point / single point held in registers
 // memory on the likelihood path). Two parities suffice: a rank cannot start exchange s+2 before every rank finished s+1,
 // which needs every rank to have left exchange s (all exchanges of a context are ordered on its one stream).
 #define GF_MAX_PEERS 16
-#define GF_PEER_SLOT 256 // doubles per rank and exchange (the largest payload is a 8x8 complex Gram block: 128)
+#define GF_PEER_SLOT 512 // doubles per rank and exchange (the largest payload: the six 8x8 tiles of a 16-amplitude Gram matrix, 384)
 struct gf_peer_view {
     double *slots[GF_MAX_PEERS];             // rank r's buffer as mapped here: [2][n_ranks][GF_PEER_SLOT]
     unsigned long long *flags[GF_MAX_PEERS]; // rank r's flags: [2][n_ranks]
@@ -157,7 +157,7 @@ __device__ inline double gf_ld_relaxed_sys(const double *p) {
     return v;
 }
 // Called by ALL threads of ONE block. vals[n] must be visible to the whole block (shared or global memory written before a
-// __syncthreads). out[k] receives the sum over ranks of vals[k] (written by thread k).
+// __syncthreads). out[k] receives the sum over ranks of vals[k] (written by thread k mod blockDim.x).
 __device__ inline void gf_peer_allreduce(const gf_peer_view &PV, const double *vals, int n, double *out) {
     const int t = threadIdx.x, nr = PV.nranks, par = (int)(PV.seq & 1ull);
     __shared__ int timed_out;
@@ -181,12 +181,12 @@ __device__ inline void gf_peer_allreduce(const gf_peer_view &PV, const double *v
         }
     }
     __syncthreads();
-    if(t < n) {
-        const double *src = PV.slots[PV.rank] + (size_t)par * nr * GF_PEER_SLOT + t;
+    for(int k = t; k < n; k += blockDim.x) {
+        const double *src = PV.slots[PV.rank] + (size_t)par * nr * GF_PEER_SLOT + k;
         double s = 0;
         for(int r = 0; r < nr; ++r) s += gf_ld_relaxed_sys(src + (size_t)r * GF_PEER_SLOT);
         if(timed_out) s = __longlong_as_double(0x7ff8000000000000ll);
-        out[t] = s;
+        out[k] = s;
     }
 }
 
@@ -317,6 +317,7 @@ struct gf_ctx {
     int max_blocks = 0;
     float last_ms = 0;
     bool fast_on = true; // shape-specialised likelihood kernels (gf_fast.cu); GOOFIT_B200_NO_FAST=1 or gf_fast_enable(c, 0) turns them off
+    bool fused_on = true; // one-pass lineshape -> amplitude -> Gram update (k_amp4_update); GOOFIT_B200_NO_FUSED=1 turns it off
     const char *last_kernel = ""; // which copy of the likelihood kernel the last gf_eval_sum launched
     uint64_t launches = 0;
     // per-kernel CUDA-event timing is opt-in (gf_profile_begin): two event records per launch are not free on a 50 us call

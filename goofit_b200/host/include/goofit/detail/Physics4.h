@@ -155,6 +155,7 @@ class Amp4BodyBase : public GooPdf {
     void setDataSizeCommon(unsigned int dataSize, unsigned int evtSize);
     /// (re)build the Gram matrix if the MC amplitudes changed; returns G[a * nAmps + b]
     const std::vector<std::complex<fptype>> &gram(bool mcAmpsChanged);
+    void refreshCaches(bool any, int spins, const std::vector<uint8_t> &lsRedo, const std::vector<uint8_t> &ampRedo);
     NormMode normMode{NormMode::Gram};
     bool gramValid{false};
     std::vector<std::complex<fptype>> G;

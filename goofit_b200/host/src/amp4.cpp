@@ -427,6 +427,19 @@ void Amp4BodyBase::ensureCache() {
     forceRedoIntegrals = true;
     gramValid          = false;
 }
+// Rebuild what a moved mass or width invalidated. In Gram mode the lineshapes, the amplitudes that contain them and G_ab are
+// refreshed in one pass per sample (gf_amp4_cache_gram); in PerEvent mode only the caches are (the MC integral follows per call).
+void Amp4BodyBase::refreshCaches(bool any, int spins, const std::vector<uint8_t> &lsRedo, const std::vector<uint8_t> &ampRedo) {
+    if(!any) return;
+    Engine &E = Engine::get();
+    if(normMode == NormMode::Gram) {
+        G.assign(nAmps * nAmps, {0.0, 0.0});
+        Engine::check(gf_amp4_cache_gram(E.ctx(), nodeIdx, spins, lsRedo.data(), ampRedo.data(), reinterpret_cast<double *>(G.data())),
+                      "gf_amp4_cache_gram");
+        gramValid = true;
+    } else
+        Engine::check(gf_amp4_cache(E.ctx(), nodeIdx, spins, lsRedo.data(), ampRedo.data()), "gf_amp4_cache");
+}
 const std::vector<std::complex<fptype>> &Amp4BodyBase::gram(bool mcAmpsChanged) {
     if(mcAmpsChanged || !gramValid || G.size() != nAmps * nAmps) {
         G.assign(nAmps * nAmps, {0.0, 0.0});
@@ -504,12 +517,12 @@ fptype Amp4Body::normalize() { // Amp4Body.cu:398-558
     int spins          = forceRedoIntegrals ? 1 : 0;
     forceRedoIntegrals = false;
     E.sync();
-    if(any) Engine::check(gf_amp4_cache(E.ctx(), nodeIdx, spins, lsRedo.data(), ampRedo.data()), "gf_amp4_cache");
+    refreshCaches(any, spins, lsRedo, ampRedo);
     double sum = 0;
     if(normMode == NormMode::Gram) {
         // sum_m |sum_a c_a A_a(m)|^2 = sum_a |c_a|^2 G_aa + 2 sum_{a<b} Re(c_a conj(c_b) G_ab), with the coefficients of the
         // parameter block the device would have read
-        const auto &g = gram(any);
+        const auto &g = gram(false); // refreshCaches left G current
         for(size_t a = 0; a < nAmp; ++a) {
             std::complex<fptype> ca(par(2 * a), par(2 * a + 1));
             sum += std::norm(ca) * g[a * nAmp + a].real();
@@ -680,7 +693,7 @@ fptype Amp4Body_TD::normalize() { // Amp4Body_TD.cu:744-799
     int spins          = forceRedoIntegrals ? 1 : 0;
     forceRedoIntegrals = false;
     E.sync();
-    if(any) Engine::check(gf_amp4_cache(E.ctx(), nodeIdx, spins, lsRedo.data(), ampRedo.data()), "gf_amp4_cache");
+    refreshCaches(any, spins, lsRedo, ampRedo);
     double sums[4] = {0, 0, 0, 0};
     if(normMode == NormMode::Gram) {
         // effective coefficient vectors of A (scaled by sqrt(WS/RS)) and B with the reference's coefficient walk
@@ -700,7 +713,7 @@ fptype Amp4Body_TD::normalize() { // Amp4Body_TD.cu:744-799
                 }
             }
         }
-        const auto &g = gram(any);
+        const auto &g = gram(false); // refreshCaches left G current
         std::complex<fptype> AA(0, 0), BB(0, 0), AB(0, 0);
         for(size_t a = 0; a < nAmps; ++a)
             for(size_t b = 0; b < nAmps; ++b) {

@@ -44,8 +44,10 @@ PYBIND11_MODULE(_goofit, m) {
           "raw gf_ctx* of the engine (for attaching an NCCL communicator through the C ABI)");
     m.def("launch_count", [] { return gf_launch_count(detail::Engine::get().ctx()); });
     m.def("last_kernel_ms", [] { return gf_last_kernel_ms(detail::Engine::get().ctx()); });
-    m.def("fast_enable", [](bool on) { return gf_fast_enable(detail::Engine::get().ctx(), on ? 1 : 0) != 0; }, "on"_a,
+    m.def("fast_enable", [](bool on) { return gf_set_option(detail::Engine::get().ctx(), "fast", on ? 1 : 0) != 0; }, "on"_a,
           "shape-specialised likelihood kernels on/off (off = interpreter for every program); returns the previous setting");
+    m.def("fused_enable", [](bool on) { return gf_set_option(detail::Engine::get().ctx(), "fused", on ? 1 : 0) != 0; }, "on"_a,
+          "one-pass lineshape -> amplitude -> Gram update on/off (off = separate kernels); returns the previous setting");
     m.def("last_kernel_name", [] { return std::string(gf_last_kernel_name(detail::Engine::get().ctx())); },
           "which copy of the likelihood kernel the last NLL evaluation launched");
     m.def("program_params", [] { return py::array(py::cast(detail::Engine::get().prog.params)); },

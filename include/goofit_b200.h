@@ -163,6 +163,11 @@ int gf_amp4_norm_async(gf_ctx *, int node);
  * (Amp4Body) or the four sums over the A / B coefficient sets (Amp4Body_TD): no per-call pass over the MC sample while
  * the lineshapes stand still. Call it after gf_amp4_cache rebuilt MC amplitudes. */
 int gf_amp4_gram(gf_ctx *, int node, double *G_re_im /* nAmp*nAmp*2 */);
+/* gf_amp4_cache + gf_amp4_gram as ONE pass per sample: the flagged lineshapes, the amplitudes that contain them and - on the MC
+ * sample - the whole Gram matrix, accumulated with FP64 tensor-core MMAs (replaces the re-run of NormLSCalculator + NormIntegrator
+ * when a mass or width moves: Amp4Body.cu:462-558, detail/NormLSCalculator.cu:11-62, NormIntegrator.cu:15-68). Up to 16 amplitudes;
+ * beyond that (or with the "fused" option off) it is exactly gf_amp4_cache followed by gf_amp4_gram. */
+int gf_amp4_cache_gram(gf_ctx *, int node, int redo_spins, const uint8_t *ls_redo, const uint8_t *amp_redo, double *G_re_im);
 int gf_amp4_get_amp(gf_ctx *, int node, int amp, double *out_re_im, size_t n_events);
 
 /* ---- multi-GPU: one process per GPU, partial sums all-reduced in-stream over NCCL (NVLink/NVSwitch) --------
@@ -202,7 +207,10 @@ float gf_last_kernel_ms(gf_ctx *);
 /* which copy of the likelihood kernel the last gf_eval_sum / gf_eval_sum_async launched: "k_eval_sum" (the interpreter) or
  * one of the shape-specialised copies of csrc/gf_fast.cu. GOOFIT_B200_NO_FAST=1 forces the interpreter (A/B runs). */
 const char *gf_last_kernel_name(gf_ctx *);
-int gf_fast_enable(gf_ctx *, int on); /* returns the previous setting */
+/* A/B switches: "fast" (shape-specialised likelihood kernels, csrc/gf_fast.cu) and "fused" (one-pass lineshape -> amplitude ->
+ * Gram update, gf_amp4_cache_gram); value 0 = off. Returns the previous setting, -1 for an unknown name. Both default to on;
+ * GOOFIT_B200_NO_FAST=1 / GOOFIT_B200_NO_FUSED=1 in the environment start a context with them off. */
+int gf_set_option(gf_ctx *, const char *name, int value);
 /* number of kernels this ctx has launched since creation */
 uint64_t gf_launch_count(gf_ctx *);
 

@@ -36,6 +36,23 @@ def fast_vs_interpreter(pdf, expect):
     return fast, slow
 
 
+def kstar_move_fused_vs_separate(sig, dp, var, want_nll, want_integral, rtol_int):
+    """Move the K*(892) mass away and back with the one-pass update (k_amp4_update: DMMA Gram sum) switched off, i.e. through
+    k_amp4_cache + k_amp4_amps + the 4x4-tile k_amp4_gram, then once more with it on: same NLL and integral both ways."""
+    for fused in (False, True):
+        was = gf.fused_enable(fused)
+        try:
+            for value in (0.8931, 0.8975):
+                var.changed = True
+                sig.updateVariable(var, value)
+                sig.updateParameters()
+                nll = sig.calculateNLL()
+        finally:
+            gf.fused_enable(was)
+        assert rel(nll, want_nll) < RTOL_NLL, (fused, nll, want_nll)
+        assert rel(1.0 / dp.getNormalization(), want_integral) < rtol_int, fused
+
+
 def check_pdf(golden, tag, pdf, data, gridvar=None, comps=True, rtol_evt=RTOL_EVT):
     pdf.setData(data)
     nll = pdf.calculateNLL()
@@ -349,8 +366,13 @@ def test_dp4_values(golden, mode):
     M.lsvars[2].changed = True
     sig.updateVariable(M.lsvars[2], 0.8975)
     sig.updateParameters()
+    before = gf.launch_count()
     assert rel(sig.calculateNLL(), golden["dp4.nll_kstar_moved"]) < RTOL_NLL
     assert rel(1.0 / dp.getNormalization(), golden["dp4.integral_kstar_moved"]) < 1e-12
+    if mode == "Gram":
+        # a mass moved: ONE pass over the MC sample (lineshapes -> amplitudes -> G_ab on FP64 MMAs), one over the data, the NLL
+        assert gf.launch_count() - before == 3
+        kstar_move_fused_vs_separate(sig, dp, M.lsvars[2], golden["dp4.nll_kstar_moved"], golden["dp4.integral_kstar_moved"], 1e-12)
 
 
 @pytest.mark.parametrize("mode", ["Gram", "PerEvent"])
@@ -466,8 +488,12 @@ def test_tddp4_values(golden, tag, three_gauss, shared, mode):
     M.lsvars[2].changed = True
     sig.updateVariable(M.lsvars[2], 0.8975)
     sig.updateParameters()
+    before = gf.launch_count()
     assert rel(sig.calculateNLL(), golden[tag + ".nll_kstar_moved"]) < RTOL_NLL
     assert rel(1.0 / dp.getNormalization(), golden[tag + ".integral_kstar_moved"]) < RTOL_INT
+    if mode == "Gram":
+        assert gf.launch_count() - before == 3
+        kstar_move_fused_vs_separate(sig, dp, M.lsvars[2], golden[tag + ".nll_kstar_moved"], golden[tag + ".integral_kstar_moved"], RTOL_INT)
 
 
 def test_tddp4_fit_matches_reference(golden):
