@@ -87,7 +87,10 @@ struct gf_amp4_args {
 // Spin factors are computed once per event sample; their tensor algebra wants many registers, so they get their own
 // kernel at one block per SM instead of setting the register budget of the lineshape kernel, which reruns whenever a
 // mass or width moves.
-__global__ void __launch_bounds__(GF_THREADS, 1) k_amp4_sf(const gf_dev_view V, int node, gf_amp4_args A, const gf_amp4_kinmap K) {
+#ifndef GF_SF_BLOCKS
+#define GF_SF_BLOCKS 2 // measured: first Amp4Body call 75 -> 58 ms at two resident blocks (128 registers) against one (158)
+#endif
+__global__ void __launch_bounds__(GF_THREADS, GF_SF_BLOCKS) k_amp4_sf(const gf_dev_view V, int node, gf_amp4_args A, const gf_amp4_kinmap K) {
     extern __shared__ __align__(16) unsigned char smem[];
     gf_sprog P = gf_stage_program(V, smem);
     __syncthreads();
@@ -198,7 +201,8 @@ __device__ __forceinline__ double2 gf_amp4_one(const int32_t *rec, const gf_amp4
 template <bool COHERENT>
 __device__ __forceinline__ double2 gf_amp4_build(const int32_t *rec, const gf_amp4_args &A, long e) {
     const int numLS = rec[0], numSF = rec[1], nPerm = rec[2];
-    const int LS_step = numLS / nPerm, SF_step = numSF / nPerm;
+    // nPerm is 1 or 2 in every decay chain upstream builds: no integer division on the per-event path
+    const int LS_step = nPerm == 1 ? numLS : (nPerm == 2 ? numLS >> 1 : numLS / nPerm), SF_step = nPerm == 1 ? numSF : (nPerm == 2 ? numSF >> 1 : numSF / nPerm);
     const int shape = nPerm * 100 + LS_step * 10 + SF_step; // uniform over the grid
     switch(shape) {
     case 221: return gf_amp4_one<2, 1, 2, COHERENT>(rec, A, e); // Bose-symmetrised two-resonance chains (DP4, TDDP4)
@@ -359,7 +363,8 @@ __device__ __forceinline__ void gf_dmma(double &c0, double &c1, double a, double
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 constexpr int upd_tiles(int nb) { return nb == 1 ? 2 : (nb == 2 ? 6 : 0); } // 8x8 accumulator tiles: (C1, C2) per block pair (0,0) [, (0,1), (1,1)]
-constexpr int upd_blocks_per_sm(int) { return 2; }
+// resident blocks per SM: the data-sample copy (no Gram accumulators) fits three at 80 registers
+constexpr int upd_blocks_per_sm(int nb) { return nb == 0 ? 3 : 2; }
 inline size_t gf_upd_smem(size_t prog, int nLS, int nb) {
     return gf_align16(prog) + gf_align16(sizeof(gf_ls_slot) * (size_t)std::max(1, nLS)) + sizeof(double) * (GF_THREADS / 32) * 16 * nb * GF_UPD_TS;
 }
@@ -369,9 +374,14 @@ __global__ void __launch_bounds__(GF_THREADS, upd_blocks_per_sm(NB))
     k_amp4_update(const gf_dev_view V, int node, gf_amp4_args A, unsigned long long ls_mask, unsigned long long amp_mask, const gf_amp4_kinmap K,
                   const double *weights, double *partials, unsigned *ticket, double *out, const gf_peer_view PV) {
     extern __shared__ __align__(16) unsigned char smem[];
-    __shared__ unsigned char flagged[64], untouched[64];
-    __shared__ int nflag, nun;
+    __shared__ unsigned char flagged[64], untouched[64], rebuilt[64];
+    __shared__ int nflag, nun, nre;
     __shared__ bool is_last;
+    // planes this launch reads, as (base pointer, bytes per event): the 128-byte lines of a warp's NEXT 32 events are requested
+    // into L2 while the current ones compute (measured on the DP4 K*(892) move: 1.96 -> 1.77 ms per likelihood call)
+    __shared__ const char *pf_base[160];
+    __shared__ unsigned char pf_bytes[160];
+    __shared__ int npf;
     gf_sprog P = gf_stage_program(V, smem);
     __syncthreads();
     const gf_node &nd = P.nodes[node];
@@ -409,6 +419,24 @@ __global__ void __launch_bounds__(GF_THREADS, upd_blocks_per_sm(NB))
             if(!((amp_mask >> a) & 1ull)) untouched[nu++] = (unsigned char)a;
         nflag = nf;
         nun = nu;
+        int np = 0, nr = 0;
+        unsigned long long ls_in = 0, sf_in = 0; // standing lineshapes / spin factors of the amplitudes to rebuild
+        for(int a = 0; a < nAmp; ++a) {
+            if(!((amp_mask >> a) & 1ull)) continue;
+            rebuilt[nr++] = (unsigned char)a;
+            const int32_t *rec = rec0 + start[a];
+            for(int j = 0; j < rec[0]; ++j) ls_in |= 1ull << rec[3 + j];
+            for(int j = 0; j < rec[1]; ++j) sf_in |= 1ull << rec[3 + rec[0] + j];
+        }
+        nre = nr;
+        ls_in &= ~ls_mask;
+        for(int i = 0; i < nLS; ++i)
+            if((ls_in >> i) & 1ull) { pf_base[np] = reinterpret_cast<const char *>(A.ls + (size_t)i * A.ld); pf_bytes[np++] = 16; }
+        for(int k = 0; k < nSF; ++k)
+            if((sf_in >> k) & 1ull) { pf_base[np] = reinterpret_cast<const char *>(A.sf + (size_t)k * A.ld); pf_bytes[np++] = 8; }
+        if(NB > 0)
+            for(int u = 0; u < nu; ++u) { pf_base[np] = reinterpret_cast<const char *>(A.amps + (size_t)untouched[u] * A.ld); pf_bytes[np++] = 16; }
+        npf = np;
     }
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     double *T = tiles + (size_t)wib * 16 * NB * GF_UPD_TS; // rows: block b -> [16 b, 16 b + 8) = Re, [16 b + 8, 16 b + 16) = Im
@@ -423,6 +451,27 @@ __global__ void __launch_bounds__(GF_THREADS, upd_blocks_per_sm(NB))
     for(long base = ((long)blockIdx.x * (GF_THREADS / 32) + wib) * 32; base < A.n; base += warp_stride) {
         const long e = base + lane;
         const bool live = e < A.n;
+        { // lane l requests line (l & 3) of planes l >> 2, l >> 2 + 8, ... of this warp's next 32 events
+            const long nb0 = base + warp_stride;
+            if(nb0 < A.n) {
+                for(int j = lane >> 2; j < npf; j += 8) {
+                    const int bytes = pf_bytes[j];
+                    if((lane & 3) * 128 < 32 * bytes) {
+                        const char *q = pf_base[j] + (size_t)nb0 * bytes + (lane & 3) * 128;
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(q));
+                    }
+                }
+                for(int f = lane; f < nflag; f += 32) { // pair masses of the flagged lineshapes (8 B per event: two lines)
+                    const gf_ls_slot &L = slots[flagged[f]];
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(L.mcol + nb0));
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(L.mcol + nb0 + 16));
+                    if(L.dcol) {
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(L.dcol + nb0));
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(L.dcol + nb0 + 16));
+                    }
+                }
+            }
+        }
         if(live) {
             if(NB > 0) { // amplitudes that stand: requested first, four at a time, so that their latency overlaps the lineshape arithmetic
                 for(int g = 0; g < nun; g += 4) {
@@ -450,8 +499,8 @@ __global__ void __launch_bounds__(GF_THREADS, upd_blocks_per_sm(NB))
                     r = gf_lineshape(L.kind, L.lp, L.lc, mres, L.dcol ? __ldg(L.dcol + e) : L.d1c, L.d2);
                 A.ls[(size_t)i * A.ld + e] = make_double2(r.re, r.im);
             }
-            for(int a = 0; a < nAmp; ++a) {
-                if(!((amp_mask >> a) & 1ull)) continue;
+            for(int k = 0; k < nre; ++k) {
+                const int a = rebuilt[k];
                 const double2 v = gf_amp4_build<true>(rec0 + start[a], A, e);
                 A.amps[(size_t)a * A.ld + e] = v;
                 if(NB > 0) {
@@ -644,7 +693,8 @@ extern "C" int gf_amp4_set_mc(gf_ctx *c, int node, const double *const *mc_cols5
         s->mc.cols[k] = s->mc.owned_cols + (size_t)k * s->mc.ld;
     }
     if(weights) {
-        GF_CUDA(cudaMalloc(&s->mc.weights, sizeof(double) * n_mc));
+        GF_CUDA(cudaMalloc(&s->mc.weights, sizeof(double) * (size_t)s->mc.ld)); // padded like the planes: the one-pass update copies 16-byte units
+        GF_CUDA(cudaMemsetAsync(s->mc.weights, 0, sizeof(double) * (size_t)s->mc.ld, c->stream));
         GF_CUDA(cudaMemcpyAsync(s->mc.weights, weights, sizeof(double) * n_mc, cudaMemcpyHostToDevice, c->stream));
     }
     GF_CUDA(cudaStreamSynchronize(c->stream)); // host columns may be freed by the caller
@@ -667,7 +717,7 @@ static int run_set(gf_ctx *c, gf_amp4_state *s, int node, gf_amp4_set &S, int re
     size_t sm = gf_prog_smem(c);
     int blocks = gf_grid_blocks(c, S.n, 3);
     if(redo_spins) {
-        int sf_blocks = gf_grid_blocks(c, S.n, 1);
+        int sf_blocks = gf_grid_blocks(c, S.n, GF_SF_BLOCKS);
         if(sm > 48 * 1024) cudaFuncSetAttribute(k_amp4_sf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
         k_amp4_sf<<<sf_blocks, GF_THREADS, sm, c->stream>>>(c->view, node, A, s->kin);
         c->launches++;
@@ -774,6 +824,10 @@ extern "C" int gf_amp4_cache_gram(gf_ctx *c, int node, int redo_spins, const uin
         if(need) mc_amp_mask |= (1ull << a);
     }
     const int nb = s->nAmp <= 8 ? 1 : 2, nt = upd_tiles(nb), blocks = gf_grid_blocks(c, s->mc.n, upd_blocks_per_sm(nb));
+    const bool mc_work = (ls_mask | mc_amp_mask) != 0 || !s->mma_valid;
+    const bool data_work = s->data.n > 0 && s->data.ls && (ls_mask | amp_mask);
+    gf_peer_view none{};
+    none.nranks = 1;
     if(!s->d_mma || s->mma_blocks < blocks) {
         cudaFree(s->d_mma); cudaFree(s->d_mma_partials); cudaFree(s->d_mma_ticket);
         if(s->h_mma) cudaFreeHost(s->h_mma);
@@ -795,13 +849,12 @@ extern "C" int gf_amp4_cache_gram(gf_ctx *c, int node, int redo_spins, const uin
             if(S->n == 0 || !S->ls) continue;
             for(int k = 0; k < 5; k++) A.cols[k] = S->cols[k];
             A.n = S->n; A.ld = S->ld; A.ls = S->ls; A.sf = S->sf; A.amps = S->amps; A.kin = S->kin;
-            k_amp4_sf<<<gf_grid_blocks(c, S->n, 1), GF_THREADS, sm, c->stream>>>(c->view, node, A, s->kin);
+            k_amp4_sf<<<gf_grid_blocks(c, S->n, GF_SF_BLOCKS), GF_THREADS, sm, c->stream>>>(c->view, node, A, s->kin);
             c->launches++;
         }
         GF_CUDA(cudaGetLastError());
     }
     // MC sample first: its Gram sum is what the host waits for; the data sample's update runs behind it on the stream
-    const bool mc_work = (ls_mask | mc_amp_mask) != 0 || !s->mma_valid;
     if(mc_work) {
         gf_peer_view PV = gf_next_peer_view(c);
         if(launch_update(c, s, node, s->mc, nb, ls_mask, mc_amp_mask, s->d_mma_partials, s->d_mma_ticket, s->d_mma, PV)) return 1;
@@ -809,11 +862,7 @@ extern "C" int gf_amp4_cache_gram(gf_ctx *c, int node, int redo_spins, const uin
         GF_CUDA(cudaMemcpyAsync(s->h_mma, s->d_mma, sizeof(double) * nt * 64, cudaMemcpyDeviceToHost, c->stream));
         GF_CUDA(cudaEventRecord(c->ev1, c->stream));
     }
-    if(s->data.n > 0 && s->data.ls && (ls_mask | amp_mask)) {
-        gf_peer_view none{};
-        none.nranks = 1;
-        if(launch_update(c, s, node, s->data, 0, ls_mask, amp_mask, nullptr, nullptr, nullptr, none)) return 1;
-    }
+    if(data_work && launch_update(c, s, node, s->data, 0, ls_mask, amp_mask, nullptr, nullptr, nullptr, none)) return 1;
     if(mc_work) {
         GF_CUDA(cudaEventSynchronize(c->ev1)); // the Gram tiles only: the data-sample update keeps running behind the host sum
         if(c->h_err && *c->h_err) return gf_fail("gf_amp4_cache_gram: a rank did not join the peer-memory exchange within the time limit");

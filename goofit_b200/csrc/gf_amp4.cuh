@@ -145,15 +145,15 @@ __device__ inline double gf_bl2(double z2, int L) { // Common.cu:38-51
     if(L == 2) return 1.0 / (z2 * z2 + 3 * z2 + 9);
     return 0;
 }
-// Parameter-only part of BW / SBW / lass_MINT / GLASS (BW.cu:19-27,62-63; :77-82,106-107; :127-131; GLASS.cu:22-27): what does
-// not depend on the event while the pair's daughters are constants. The lineshape kernels evaluate it once per block for such
-// pairs (three-body pairs have an event-dependent d1 and evaluate it per event); the operations and their order are the
-// reference's, only where they are executed changes.
+// Parameter-only part of BW / SBW / lass_MINT (BW.cu:19-27,62-63; :77-82,106-107; :127-131): what does not depend on the event
+// while the pair's daughters are constants. The lineshape kernels evaluate it once per block for such pairs (three-body
+// pairs have an event-dependent d1 and evaluate it per event).
 struct gf_bw_inv {
     double mpsq, mmsq;
-    double prSq;  // |num2 / (4 mass^2)|
-    double prSq2; // max(num2 / (4 mass^2), 0)
-    double k;     // normalisation of the relativistic (RBW) or simple (SBW) Breit-Wigner
+    double prSq;     // |num2 / (4 mass^2)|
+    double prSq2;    // max(num2 / (4 mass^2), 0)
+    double inv_prSq; // 1 / prSq
+    double k;        // normalisation of the relativistic (RBW) or simple (SBW) Breit-Wigner
 };
 __device__ inline gf_bw_inv gf_bw_invariants(bool sbw, double m1, double m2, double mass, double width) {
     gf_bw_inv I;
@@ -163,6 +163,7 @@ __device__ inline gf_bw_inv gf_bw_invariants(bool sbw, double m1, double m2, dou
     double pr = num2 / (4 * mass * mass);
     I.prSq2 = pr < 0 ? 0 : pr;
     I.prSq = fabs(pr);
+    I.inv_prSq = 1.0 / I.prSq;
     if(sbw) {
         double gamma = sqrt(mass * mass * (mass * mass + width * width));
         I.k = mass * width * gamma / sqrt(mass * mass + gamma);
@@ -172,23 +173,50 @@ __device__ inline gf_bw_inv gf_bw_invariants(bool sbw, double m1, double m2, dou
     }
     return I;
 }
-// BW.cu:14-69
+// Blatt-Weisskopf pieces of one event for orbital L, all from ONE reciprocal of the shared denominator D(z2) = 1 + z2 (L = 1)
+// or z2^2 + 3 z2 + 9 (L = 2):  BL' = N(z02) / D(z2) (Common.cu:8-21), BL = 2 z2 / D or 13 z2^2 / D (:23-36), BL2 = 1 / D (:38-51)
+struct gf_bl_set { double inv_d, z2; int L; };
+__device__ __forceinline__ gf_bl_set gf_bl_prepare(double z2, int L) {
+    gf_bl_set B;
+    B.z2 = z2;
+    B.L = L;
+    B.inv_d = L == 0 ? 1.0 : 1.0 / (L == 1 ? 1 + z2 : z2 * z2 + 3 * z2 + 9);
+    return B;
+}
+__device__ __forceinline__ double gf_bl_prime_s(const gf_bl_set &B, double z02) {
+    if(B.L == 0) return 1.0;
+    if(B.L == 1) return (1 + z02) * B.inv_d;
+    if(B.L == 2) return (z02 * z02 + 3 * z02 + 9) * B.inv_d;
+    return 0;
+}
+__device__ __forceinline__ double gf_bl_s(const gf_bl_set &B) {
+    if(B.L == 0) return 1.0;
+    if(B.L == 1) return 2 * B.z2 * B.inv_d;
+    if(B.L == 2) return (13 * B.z2 * B.z2) * B.inv_d;
+    return 0;
+}
+__device__ __forceinline__ double gf_bl2_s(const gf_bl_set &B) { return B.L <= 2 ? (B.L == 0 ? 1.0 : B.inv_d) : 0; }
+// BW.cu:14-69. Against the reference's operation sequence the per-event part shares reciprocals: 1/Mpair serves num / (4 M^2)
+// and mass / Mpair, 1 / prSq is parameter-only, and the Blatt-Weisskopf ratios share the reciprocal of their common
+// denominator: three divisions and two square roots per event instead of six and two. Each substitution moves the result by
+// an ulp or two (the amplitudes are compared with the reference at 1e-10, the NLL at 1e-12: tests/test_parity_gpu.py).
 __device__ inline gf_cplx gf_ls_bw_pt(double Mpair, double mass, double width, int orbital, int FF, double meson_radius, const gf_bw_inv &I) {
     const int to2Lplus1 = 2 * orbital + 1;
     double M2 = Mpair * Mpair;
     double num = (M2 - I.mpsq) * (M2 - I.mmsq);
-    double pABSq = num / (4 * M2);
-    double prSqForGofM = I.prSq, prSq2 = I.prSq2;
-    double pratio = sqrt(pABSq / prSqForGofM);
+    double rM = 1.0 / Mpair;
+    double pABSq = num * (0.25 * (rM * rM));
+    double pratio = sqrt(pABSq * I.inv_prSq);
     double pr2J1 = 1;
     for(int i = 0; i < to2Lplus1; i++) pr2J1 *= pratio;
-    double mratio = mass / Mpair;
+    double mratio = mass * rM;
     double r2 = meson_radius * meson_radius;
-    double thisFR = gf_bl_prime(pABSq * r2, prSqForGofM * r2, orbital);
+    const gf_bl_set B = gf_bl_prepare(pABSq * r2, orbital);
+    double thisFR = gf_bl_prime_s(B, I.prSq * r2);
     double frFactor = 1;
     if(0 != orbital && 0 != FF) {
-        frFactor = (FF == 1 ? gf_bl(pABSq * r2, orbital) : gf_bl_prime(pABSq * r2, prSq2 * r2, orbital));
-        frFactor = (FF == 3 ? gf_bl2(pABSq * r2, orbital) : frFactor);
+        frFactor = (FF == 1 ? gf_bl_s(B) : gf_bl_prime_s(B, I.prSq2 * r2));
+        frFactor = (FF == 3 ? gf_bl2_s(B) : frFactor);
     }
     double GofM = width * pr2J1 * mratio * thisFR;
     gf_cplx bw = gf_c(mass * mass - M2, mass * GofM);
@@ -202,14 +230,14 @@ __device__ inline gf_cplx gf_ls_bw(double Mpair, double m1, double m2, double ma
 // BW.cu:72-115
 __device__ inline gf_cplx gf_ls_sbw_pt(double Mpair, double mass, double width, int orbital, int FF, double meson_radius, const gf_bw_inv &I) {
     double M2 = Mpair * Mpair;
-    double num = (M2 - I.mpsq) * (M2 - I.mmsq);
-    double pABSq = num / (4 * M2);
-    double prSq2 = I.prSq2;
-    double r2 = meson_radius * meson_radius;
     double frFactor = 1;
     if(0 != orbital && 0 != FF) {
-        frFactor = (FF == 1 ? gf_bl(pABSq * r2, orbital) : gf_bl_prime(pABSq * r2, prSq2 * r2, orbital));
-        frFactor = (FF == 3 ? gf_bl2(pABSq * r2, orbital) : frFactor);
+        double num = (M2 - I.mpsq) * (M2 - I.mmsq);
+        double pABSq = num / (4 * M2);
+        double r2 = meson_radius * meson_radius;
+        const gf_bl_set B = gf_bl_prepare(pABSq * r2, orbital);
+        frFactor = (FF == 1 ? gf_bl_s(B) : gf_bl_prime_s(B, I.prSq2 * r2));
+        frFactor = (FF == 3 ? gf_bl2_s(B) : frFactor);
     }
     double GofM = width;
     gf_cplx bw = gf_c(mass * mass - M2, mass * GofM);
@@ -416,7 +444,13 @@ __device__ inline gf_lv operator*(double s, gf_lv a) { return gf_v(a.x * s, a.y 
 __device__ inline double gf_dot(gf_lv a, gf_lv b) { return a.e * b.e - a.x * b.x - a.y * b.y - a.z * b.z; }
 __device__ inline double gf_mag2(gf_lv a) { return gf_dot(a, a); }
 __device__ inline double gf_m(gf_lv a) { return sqrt(gf_mag2(a)); }
-__device__ inline gf_lv gf_load_lv(const double *V, int p) { return gf_v(V[4 * p], V[4 * p + 1], V[4 * p + 2], V[4 * p + 3]); }
+// Daughter p (uniform over the grid) of the four four-vectors. Written as selects over compile-time offsets: a runtime-indexed
+// read would force the sixteen components into local memory for the whole spin-factor kernel (4x10^7 local loads per 10^7
+// events in the round-1 profile); four predicated moves per component keep them in registers.
+__device__ __forceinline__ gf_lv gf_load_lv(const double *V, int p) {
+    return gf_v(p == 0 ? V[0] : (p == 1 ? V[4] : (p == 2 ? V[8] : V[12])), p == 0 ? V[1] : (p == 1 ? V[5] : (p == 2 ? V[9] : V[13])),
+                p == 0 ? V[2] : (p == 1 ? V[6] : (p == 2 ? V[10] : V[14])), p == 0 ? V[3] : (p == 1 ? V[7] : (p == 2 ? V[11] : V[15])));
+}
 // ZTspin1: q - (q.p) p / mR^2   (SpinHelper.h:77-84)
 __device__ inline gf_lv gf_zt1(gf_lv q, gf_lv p, double mR) { return q - gf_dot(q, p) * p * (1. / (mR * mR)); }
 // SpinSumV::Dot (SpinHelper.h:86-97)
