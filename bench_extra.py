@@ -77,7 +77,8 @@ def dalitz_fit(gf, lib, ctx, M, n_events):
     return {"wall_s": wall, "nfcn": nfcn, "valid": bool(fm), "fval": res.Fval(), "ms_per_call": 1e3 * wall / max(nfcn, 1),
             "events_x_evals_per_s": n_events * nfcn / wall, "kernel_launches": int(gf.launch_count() - l0),
             "note": "synthetic events are uniform in the Dalitz plot, so the minimum is wherever Migrad finds it; the number is the "
-                    "cost of a full Minuit2 minimisation with Hesse on 10^7 events"}
+                    "cost of a full Minuit2 minimisation with Hesse on 10^7 events. Fits of model-drawn events, valid on both arms and "
+                    "timed beside the reference: workloads.reference_side"}
 
 
 def _tile(cols, n):
@@ -324,6 +325,132 @@ def call_latency(gf, lib, ctx, reps=400):
             "from_minuit_vector_us": 1e6 * t_params, "kernel_us_queued": 1e3 * ms}
 
 
+def reference_side(gf, lib, ctx, n=1_000_000):
+    """The other half of BASELINE's metric: fit wall time, Dalitz and DP4, on BOTH arms from the same model-drawn events and
+    start values (the reference prints its own at FitManagerMinuit2.cpp:43,52,86-87), plus the reference's per-call cost of
+    the DP4 / TDDP4 / zachFit likelihoods (steady state and with the K*(892) mass moving) on a bounded sample: n events
+    (+ n MC normalisation events) on all host cores. Inputs go to the reference as .npy columns (tests/scale.py)."""
+    import shutil
+    import scale
+    from models import DP4, Dalitz
+    out = {"sample": "%d events (+ %d MC normalisation events for the four-body fits), identical on both arms" % (n, n)}
+
+    def both(tag, cfg, cols, fit_model, fit_vars, ndims=None, ref_kwargs=None):
+        d = scale.write_columns(scale.scratch_dir(tag), cols)
+        try:
+            ref = scale.run_reference(cfg, 0, 1, 0, data=d, fit=True, **(ref_kwargs or {}))
+        finally:
+            shutil.rmtree(d, ignore_errors=True)
+        t0 = time.perf_counter()
+        fm, res = scale.fit_with(gf, fit_model)
+        wall = time.perf_counter() - t0
+        rf = ref["fit"]
+        pulls = scale.pulls([v.value for v in fit_vars], rf["values"][:len(fit_vars)], rf["errors"][:len(fit_vars)])
+        return {"events": n, "fit_wall_s": wall, "nfcn": int(res.NFcn()), "valid": bool(fm), "fval": res.Fval(),
+                "reference": {"fit_wall_s": rf["wall_s"], "nfcn": rf["nfcn"], "valid": rf["valid"], "fval": rf["fval"], "cores": ref["threads"],
+                              "ms_per_call": 1e3 * rf["wall_s"] / max(rf["nfcn"], 1)},
+                "max_pull_vs_reference_sigma": float(pulls.max()), "speedup_fit_wall": rf["wall_s"] / wall}
+
+    try:  # ---- Dalitz: 30 free coefficients
+        M = Dalitz(float_masses=False, grid=240)
+        m12, m13 = scale.dalitz_model_events(gf, M, n, 31, chunk=4_000_000)
+        M = Dalitz(float_masses=False, grid=240)
+        data = M.dataset(m12, m13)
+        M.signal.setData(data)
+        M.signal.setDataSize(len(data))
+        M.signal.calculateNLL()
+        out["dalitz_fit"] = both("dalitzfit", "dalitz", {"m12": m12, "m13": m13}, M.signal, M.coefs)
+    except Exception as e:
+        out["dalitz_fit"] = {"error": str(e)[:300]}
+    try:  # ---- DP4: six free coefficients, 10^6 MC normalisation events; and the reference's per-call cost
+        mc = scale.unweighted_phase_space(gf, n, 99)
+        M = DP4(mc_events=0, float_ls=False)
+        ev = scale.dp4_model_events(gf, M, n, 8, mc)
+        cols = {nm: ev[k] for k, nm in enumerate(scale.NAMES5)}
+        cols.update({"mc_" + nm: mc[k] for k, nm in enumerate(scale.NAMES5)})
+        M = DP4(mc_events=0, float_ls=False)
+        M.dp.setNormEvents(mc)
+        data = M.dataset(list(ev))
+        M.signal.setData(data)
+        M.dp.setDataSize(len(data), 6)
+        M.signal.calculateNLL()
+        out["dp4_fit"] = both("dp4fit", "dp4", cols, M.signal, M.coefs[:6])
+        d = scale.write_columns(scale.scratch_dir("dp4cpu"), cols)
+        try:
+            r = scale.run_reference("dp4", 0, 3, 1, data=d, lsmove=True)
+        finally:
+            shutil.rmtree(d, ignore_errors=True)
+        out["dp4_cpu_baseline"] = {"value": r["events_x_evals_per_s"], "unit": "events*evals/s", "cores": r["threads"], "kind": "reference",
+                                   "ms_per_step": r["ms_per_step"], "lineshape_move_ms_per_step": r.get("lsmove_ms_per_step"),
+                                   "sample": "%d data + %d MC events x 3 FCN calls, unmodified reference (OMP backend, all host cores)" % (n, n)}
+    except Exception as e:
+        out.setdefault("dp4_fit", {"error": str(e)[:300]})
+    try:  # ---- TDDP4 per-call cost of the reference
+        rng = np.random.default_rng(5)
+        mc = scale.unweighted_phase_space(gf, n, 7)
+        data_cols, _ = scale.phase_space(gf, n, 31337)
+        cols = {nm: data_cols[k] for k, nm in enumerate(scale.NAMES5)}
+        cols.update({"mc_" + nm: mc[k] for k, nm in enumerate(scale.NAMES5)})
+        cols.update({"dtime": rng.exponential(0.4101, n).clip(0, 9.99), "sigmat": rng.uniform(0.02, 0.08, n)})
+        d = scale.write_columns(scale.scratch_dir("tdcpu"), cols)
+        try:
+            r = scale.run_reference("tddp4", 0, 3, 1, data=d, lsmove=True)
+        finally:
+            shutil.rmtree(d, ignore_errors=True)
+        out["tddp4_cpu_baseline"] = {"value": r["events_x_evals_per_s"], "unit": "events*evals/s", "cores": r["threads"], "kind": "reference",
+                                     "ms_per_step": r["ms_per_step"], "lineshape_move_ms_per_step": r.get("lsmove_ms_per_step"),
+                                     "sample": "%d data + %d MC events x 3 FCN calls, unmodified reference (OMP backend, all host cores)" % (n, n)}
+    except Exception as e:
+        out["tddp4_cpu_baseline"] = {"error": str(e)[:300]}
+    try:  # ---- zachFit as configured (BASELINE configs[1]): three ConvolutionPdfs inside nested AddPdfs, 10 000-point workspaces
+        from models import ZachFull
+
+        def dm_sample(m, seed):
+            rng = np.random.default_rng(seed)
+            core = rng.normal(0.14543, 0.0004, m)
+            tail = 0.1395 + (0.1665 - 0.1395) * rng.beta(1.5, 4.0, m)
+            dm = np.where(rng.uniform(size=m) < 0.9, core, tail)
+            return dm[(dm > 0.1396) & (dm < 0.1664)]
+
+        zres = {}
+        for cfg, johnson in (("zachfit", False), ("zachfit_jsu", True)):
+            dm_small = dm_sample(100_000, 11)  # the reference convolves per event (6e4 flop/event): bounded to 10^5 events
+            d = scale.write_columns(scale.scratch_dir("zach"), {"dm": dm_small})
+            try:
+                r = scale.run_reference(cfg, 0, 2, 1, data=d)
+            finally:
+                shutil.rmtree(d, ignore_errors=True)
+            dm = dm_sample(10_000_000, 12)
+            Z = ZachFull(johnson=johnson)
+            Z.total.setData(Z.dataset(dm))
+            t0 = time.perf_counter()
+            Z.total.calculateNLL()
+            t_first = time.perf_counter() - t0
+            fm = gf.FitManager(Z.total)
+            fcn = fm.getFCN()
+            v0 = np.array(fm.getParams().make_minuit_vector())
+            idx = [v.fitter_index for v in Z.free]
+            for k in range(3):
+                fcn(list(scale.mover_vector(v0, idx, k)))
+            lib.gf_sync(ctx)
+            l0 = gf.launch_count()
+            t0 = time.perf_counter()
+            for k in range(10):
+                fcn(list(scale.mover_vector(v0, idx, 3 + k)))
+            lib.gf_sync(ctx)
+            t = (time.perf_counter() - t0) / 10
+            zres[cfg] = {"events": int(len(dm)), "ms_per_call": 1e3 * t, "value": len(dm) / t, "unit": "events*evals/s",
+                         "launches_per_call": (gf.launch_count() - l0) / 10, "first_call_s": t_first,
+                         "moved_per_call": "width, delta, epsilon, slope, bkg_frac (all three convolution tables refilled)",
+                         "cpu_baseline": {"value": r["events_x_evals_per_s"], "unit": "events*evals/s", "cores": r["threads"], "kind": "reference",
+                                          "ms_per_step": r["ms_per_step"],
+                                          "sample": "%d events x 2 FCN calls (the reference convolves per event), same tree and schedule" % r["n_events"]}}
+        out["zachfit_full"] = zres
+    except Exception as e:
+        out["zachfit_full"] = {"error": str(e)[:300]}
+    return out
+
+
 def run_all(gf, lib, ctx, M_dalitz, n_events, peak_hbm, steps=20, with_reference=True):
     out = {}
     peak_tf = fp64_peak(lib, ctx)
@@ -345,6 +472,13 @@ def run_all(gf, lib, ctx, M_dalitz, n_events, peak_hbm, steps=20, with_reference
         out.update(simple_fits(gf, lib, ctx, peak_hbm, steps))
     except Exception as e:
         out["simple_fits"] = {"error": str(e)[:300]}
+    if with_reference:
+        try:
+            import scale
+            if scale.have_reference():
+                out["reference_side"] = reference_side(gf, lib, ctx)
+        except Exception as e:
+            out["reference_side"] = {"error": str(e)[:300]}
     try:  # installs its own small program: after everything that uses the caller's model
         out["call_latency"] = call_latency(gf, lib, ctx)
     except Exception as e:

@@ -138,6 +138,31 @@ __global__ void __launch_bounds__(GF_THREADS)
     }
 }
 
+// W_ij = sum_e w_i(e) conj(w_j(e)) over the cached waves, for the fit fractions (Amp3Body.cu:376-428: the reference runs one
+// transform_reduce of CoefSumFunctor per ordered pair over the whole sample). One block per (pair i <= j, chunk of events);
+// the chunk partials are added on the host in chunk order (deterministic), W_ji = conj(W_ij).
+#define GF_WG_CHUNKS 8
+__global__ void __launch_bounds__(GF_THREADS)
+    k_amp3_wave_gram(const double2 *waves, long ld, long n, int nres, double *partials /* [pair][chunk][2] */) {
+    __shared__ double red[32];
+    int p = blockIdx.x, i = 0;
+    while(p >= nres - i) { p -= nres - i; ++i; } // pair index -> (i, j = i + p)
+    const int j = i + p;
+    const long per = (n + GF_WG_CHUNKS - 1) / GF_WG_CHUNKS, lo = per * blockIdx.y, hi = lo + per < n ? lo + per : n;
+    const double2 *A = waves + (size_t)i * ld, *B = waves + (size_t)j * ld;
+    double sr = 0, si = 0;
+    for(long e = lo + threadIdx.x; e < hi; e += blockDim.x) {
+        const double2 a = __ldg(A + e), b = __ldg(B + e);
+        sr += a.x * b.x + a.y * b.y; // a conj(b)
+        si += a.y * b.x - a.x * b.y;
+    }
+    const double r = gf_block_sum(sr, red), q = gf_block_sum(si, red);
+    if(threadIdx.x == 0) {
+        partials[2 * ((size_t)blockIdx.x * GF_WG_CHUNKS + blockIdx.y)] = r;
+        partials[2 * ((size_t)blockIdx.x * GF_WG_CHUNKS + blockIdx.y) + 1] = q;
+    }
+}
+
 static int amp3_check(gf_ctx *c, int node, gf_amp3_state **out, bool create) {
     if(!c) return gf_fail("null ctx");
     if(node < 0 || node >= (int)c->h_nodes.size() || c->h_nodes[node].op != GF_OP_AMP3)
@@ -265,5 +290,49 @@ extern "C" int gf_amp3_get_wave(gf_ctx *c, int node, int res, double *out_re_im,
     GF_CUDA(cudaMemcpyAsync(out_re_im, s->d_waves + (size_t)res * s->ld, sizeof(double2) * n_events,
                             cudaMemcpyDeviceToHost, c->stream));
     GF_CUDA(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+// Hermitian matrix of the cached waves, W[(i * n_res + j) * 2 + {re, im}] = sum_e w_i(e) conj(w_j(e)) over the local events
+// (summed over ranks when a communicator is attached): what Amp3Body::fit_fractions needs, without moving the waves off the device.
+extern "C" int gf_amp3_wave_gram(gf_ctx *c, int node, double *W_re_im) {
+    gf_amp3_state *s;
+    if(amp3_check(c, node, &s, false)) return 1;
+    if(!s->d_waves) return gf_fail("gf_amp3_wave_gram: no cached waves (gf_amp3_cache_waves)");
+    if(!W_re_im) return gf_fail("gf_amp3_wave_gram: null output");
+    cudaSetDevice(c->device);
+    const int n = s->n_res, npairs = n * (n + 1) / 2, nv = 2 * npairs * GF_WG_CHUNKS;
+    double *d_part = nullptr;
+    GF_CUDA(cudaMalloc(&d_part, sizeof(double) * nv));
+    k_amp3_wave_gram<<<dim3(npairs, GF_WG_CHUNKS), GF_THREADS, 0, c->stream>>>(s->d_waves, s->ld, s->n_events, n, d_part);
+    c->launches++;
+    cudaError_t e = cudaGetLastError();
+    std::vector<double> part(nv);
+    if(e == cudaSuccess) e = cudaMemcpyAsync(part.data(), d_part, sizeof(double) * nv, cudaMemcpyDeviceToHost, c->stream);
+    if(e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    std::vector<double> tri(2 * npairs, 0.0);
+    for(int p = 0; p < npairs; p++)
+        for(int k = 0; k < GF_WG_CHUNKS; k++) {
+            tri[2 * p] += part[2 * (p * GF_WG_CHUNKS + k)];
+            tri[2 * p + 1] += part[2 * (p * GF_WG_CHUNKS + k) + 1];
+        }
+    if(e == cudaSuccess && c->nccl_comm) { // event-sharded: the matrix is a sum over ranks
+        e = cudaMemcpyAsync(d_part, tri.data(), sizeof(double) * 2 * npairs, cudaMemcpyHostToDevice, c->stream);
+        if(e == cudaSuccess && gf_allreduce_sum(c, d_part, 2 * npairs)) { cudaFree(d_part); return 1; }
+        if(e == cudaSuccess) e = cudaMemcpyAsync(tri.data(), d_part, sizeof(double) * 2 * npairs, cudaMemcpyDeviceToHost, c->stream);
+        if(e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    }
+    cudaFree(d_part);
+    if(e != cudaSuccess) return gf_fail(std::string("gf_amp3_wave_gram: ") + cudaGetErrorString(e));
+    int p = 0;
+    for(int i = 0; i < n; i++)
+        for(int j = i; j < n; j++, p++) {
+            W_re_im[2 * (i * n + j)] = tri[2 * p];
+            W_re_im[2 * (i * n + j) + 1] = i == j ? 0.0 : tri[2 * p + 1];
+            if(i != j) {
+                W_re_im[2 * (j * n + i)] = tri[2 * p];
+                W_re_im[2 * (j * n + i) + 1] = -tri[2 * p + 1];
+            }
+        }
     return 0;
 }

@@ -572,6 +572,37 @@ int gf_allreduce_sum(gf_ctx *c, double *dev, int n) {
     return rc ? nccl_fail("ncclAllReduce", rc) : 0;
 }
 
+// Per-event results of a sharded evaluation, gathered on every rank in rank order: the counterpart of the reference's
+// MPI_Allgather(v) of evaluate_with_metric (GooPdf.cu:139-172). counts[r] = events of rank r (the caller knows the split).
+extern "C" int gf_allgather_events(gf_ctx *c, const double *local, const size_t *counts, double *all) {
+    if(!c || !counts || !all) return gf_fail("gf_allgather_events: null argument");
+    if(!c->nccl_comm || c->nranks <= 1) {
+        if(counts[0] && local) std::memcpy(all, local, sizeof(double) * counts[0]);
+        return 0;
+    }
+    if(!p_allgather) return gf_fail("gf_allgather_events: libnccl has no ncclAllGather");
+    cudaSetDevice(c->device);
+    size_t mx = 0, total = 0;
+    for(int r = 0; r < c->nranks; r++) { mx = std::max(mx, counts[r]); total += counts[r]; }
+    if(mx == 0) return 0;
+    double *d = nullptr; // [nranks + 1][mx]: the gathered blocks, then this rank's padded block
+    GF_CUDA(cudaMalloc(&d, sizeof(double) * mx * (size_t)(c->nranks + 1)));
+    double *d_send = d + mx * (size_t)c->nranks;
+    cudaError_t e = cudaMemsetAsync(d_send, 0, sizeof(double) * mx, c->stream);
+    if(e == cudaSuccess && counts[c->rank]) e = cudaMemcpyAsync(d_send, local, sizeof(double) * counts[c->rank], cudaMemcpyHostToDevice, c->stream);
+    int rc = e == cudaSuccess ? p_allgather(d_send, d, mx, /*ncclDouble*/ 8, c->nccl_comm, c->stream) : 0;
+    size_t off = 0;
+    for(int r = 0; r < c->nranks && e == cudaSuccess && !rc; r++) {
+        if(counts[r]) e = cudaMemcpyAsync(all + off, d + mx * (size_t)r, sizeof(double) * counts[r], cudaMemcpyDeviceToHost, c->stream);
+        off += counts[r];
+    }
+    if(e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(d);
+    if(rc) return nccl_fail("ncclAllGather", rc);
+    if(e != cudaSuccess) return gf_fail(std::string("gf_allgather_events: ") + cudaGetErrorString(e));
+    return 0;
+}
+
 extern "C" int gf_timer_start(gf_ctx *c) {
     if(!c) return gf_fail("null ctx");
     cudaSetDevice(c->device);

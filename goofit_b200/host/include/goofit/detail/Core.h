@@ -413,7 +413,7 @@ class Engine {
     PdfBase *root = nullptr;
     std::vector<PdfBase *> members; // every node object in the current program
     bool paramsDirty = true, normsDirty = true;
-    size_t localEvents = 0, firstEvent = 0;
+    size_t localEvents = 0, firstEvent = 0, totalEvents = 0; // this rank's shard [firstEvent, firstEvent + localEvents) of totalEvents
     uint64_t generation = 0; // bumped by every build(); PDFs use it to notice stale device caches
 
   private:

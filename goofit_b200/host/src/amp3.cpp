@@ -281,19 +281,23 @@ GeneratedSignal Amp3Body::GenerateSig(unsigned int numEvents, int seed) {
     return G;
 }
 
-std::vector<std::vector<fptype>> Amp3Body::fit_fractions() { // Amp3Body.cu:376-428, host sums over the cached waves
+// Amp3Body.cu:376-428. The reference sums Re(c_i conj(c_j) w_i conj(w_j)) over the events with one transform_reduce per ordered
+// pair; here the event sums W_ij = sum_e w_i conj(w_j) are taken once on the device (gf_amp3_wave_gram) and the coefficients are
+// applied to the n_res^2 results on the host: no wave leaves the GPU.
+std::vector<std::vector<fptype>> Amp3Body::fit_fractions() {
     size_t n_res = decayInfo.resonances.size();
-    std::vector<std::vector<std::complex<fptype>>> w(n_res);
-    for(size_t i = 0; i < n_res; i++) w[i] = getCachedWave(i);
-    size_t nEntries = w[0].size();
+    if(!cacheAllocated) throw GeneralError("{}: no cached waves yet (evaluate the PDF first)", getName());
+    Engine &E = Engine::get();
+    std::vector<std::complex<fptype>> W(n_res * n_res);
+    Engine::check(gf_amp3_wave_gram(E.ctx(), nodeIdx, reinterpret_cast<double *>(W.data())), "gf_amp3_wave_gram");
+    size_t nEntries = numEntries;
     std::vector<std::vector<fptype>> Amps_int(n_res, std::vector<fptype>(n_res)), ff = Amps_int;
     fptype buffer_all = 0;
     for(size_t i = 0; i < n_res; i++)
         for(size_t j = 0; j < n_res; j++) {
             fpcomplex ci(decayInfo.resonances[i]->amp_real.getValue(), decayInfo.resonances[i]->amp_imag.getValue());
             fpcomplex cj(decayInfo.resonances[j]->amp_real.getValue(), decayInfo.resonances[j]->amp_imag.getValue());
-            fptype buffer = 0;
-            for(size_t e = 0; e < nEntries; e++) buffer += (ci * std::conj(cj) * w[i][e] * std::conj(w[j][e])).real();
+            fptype buffer = (ci * std::conj(cj) * W[i * n_res + j]).real();
             buffer_all += buffer;
             Amps_int[i][j] = buffer / nEntries;
         }

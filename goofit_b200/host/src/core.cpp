@@ -538,6 +538,7 @@ void PdfBase::setData(DataSet *data) {
         if(c == nullptr) c = owned[k++].data();
     E.localEvents = count;
     E.firstEvent  = first;
+    E.totalEvents = numEntries;
     Engine::check(gf_upload_columns(E.ctx(), cols.data(), (int)cols.size(), count, (double)numEntries), "gf_upload_columns");
 }
 
@@ -638,6 +639,16 @@ std::vector<fptype> GooPdf::evaluate_with_metric() const { // GooPdf.cu:112-173 
     E.sync();
     std::vector<fptype> out(E.localEvents);
     Engine::check(gf_eval_events(E.ctx(), nodeIdx, metric(), out.data(), out.size()), "gf_eval_events");
+    detail::Shard sh = E.shard();
+    if(sh.size > 1) { // every rank returns the values of ALL events, in event order (the reference's MPI_Allgatherv, GooPdf.cu:139-172)
+        E.requireComm("evaluate_with_metric");
+        std::vector<size_t> counts(sh.size);
+        size_t per = E.totalEvents / sh.size;
+        for(int r = 0; r < sh.size; r++) counts[r] = r == sh.size - 1 ? E.totalEvents - per * r : per;
+        std::vector<fptype> all(E.totalEvents);
+        Engine::check(gf_allgather_events(E.ctx(), out.data(), counts.data(), all.data()), "gf_allgather_events");
+        return all;
+    }
     return out;
 }
 

@@ -143,6 +143,9 @@ int gf_amp3_cache_waves(gf_ctx *, int node, const uint8_t *redo_mask);
 int gf_amp3_integrals(gf_ctx *, int node, const uint8_t *redo_mask, const double *lo_hi_n6, int eff_root,
                       double *I_re_im /* n_res*n_res*2, row i col j */);
 int gf_amp3_get_wave(gf_ctx *, int node, int res, double *out_re_im, size_t n_events);
+/* Hermitian matrix of the cached waves, W[(i*n_res+j)*2+{re,im}] = sum_e w_i(e) conj(w_j(e)), summed over ranks when a communicator
+ * is attached: the device side of Amp3Body::fit_fractions (Amp3Body.cu:376-428, one transform_reduce of CoefSumFunctor per pair) */
+int gf_amp3_wave_gram(gf_ctx *, int node, double *W_re_im /* n_res*n_res*2 */);
 
 /* Amp4Body / Amp4Body_TD: ints = {aux slot, nLS, nSF, nAmp, td_off, ls_node[nLS], sf_node[nSF], start[nAmp],
  * records {nLS_a, nSF_a, nPerm, LS idx..., SF idx...}}. Amp4Body: td_off = 0, params = (re, im) per amplitude.
@@ -188,6 +191,10 @@ const char *gf_comm_path(gf_ctx *);
 /* number of ranks of the attached communicator, 0 when none is attached (the host layer refuses to evaluate a
  * sharded dataset without one: a partial sum must never be mistaken for the likelihood) */
 int gf_comm_attached(gf_ctx *);
+/* Per-event results of a sharded evaluation gathered on every rank, in rank order: replaces MPI_Allgather(v) of
+ * evaluate_with_metric (src/PDFs/GooPdf.cu:139-172). counts[r] = events of rank r; `all` receives sum(counts) doubles.
+ * Without a communicator it copies `local`. */
+int gf_allgather_events(gf_ctx *, const double *local, const size_t *counts, double *all);
 /* device-side stopwatch on the ctx stream (CUDA events): start, enqueue work, stop -> elapsed ms */
 int gf_timer_start(gf_ctx *);
 int gf_timer_stop(gf_ctx *, float *ms);

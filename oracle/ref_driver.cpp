@@ -465,6 +465,12 @@ static void case_dalitz() {
     s->updateVariable(M->masses[0], 0.77); s->updateVariable(M->widths[9], 0.05); s->updateParameters();
     put("dalitz.nll_mass_moved", s->calculateNLL());
     put("dalitz.integral_mass_moved", 1.0 / s->getNormalization());
+    { // fit fractions from the cached waves at this point (Amp3Body.cu:376-428)
+        auto ff = s->fit_fractions();
+        std::vector<double> flat;
+        for(auto &row : ff) flat.insert(flat.end(), row.begin(), row.end());
+        save_npy("dalitz.fitfrac", flat.data(), ff.size(), ff.size());
+    }
 }
 
 // ---- the other three-body resonance shapes: LASS, FLATTE (with and without the m12<->m13 swap), GS, Gauss, symmetrised RBW ----

@@ -50,6 +50,16 @@ M.signal.setData(d)
 M.signal.setDataSize(len(d))
 res["dalitz"] = rel(M.signal.calculateNLL(), gold["dalitz.nll"])
 assert gf.local_events() < len(d)
+# per-event values under sharding: every rank gets ALL events back in event order (the reference's MPI_Allgatherv, GooPdf.cu:139-172)
+probs = np.asarray(M.signal.getCompProbsAtDataPoints()[0])
+want = arr("dalitz.prob")
+assert probs.shape == want.shape, (probs.shape, want.shape)
+res["dalitz.prob"] = float(np.max(np.abs(probs - want) / np.maximum(np.abs(want), 1e-300)))
+# fit fractions: the wave Gram matrix is a sum over ranks
+for v in M.masses + M.widths:
+    v.changed = False
+ff = np.asarray(M.signal.fit_fractions())
+res["dalitz.fitfrac_sum"] = abs(float(ff.sum()) - 1.0)
 
 names = ("m12", "m34", "cos12", "cos34", "phi")
 for mode in ("Gram", "PerEvent"):
@@ -70,7 +80,7 @@ for mode in ("Gram", "PerEvent"):
     res["tddp4." + mode] = rel(M.signal.calculateNLL(), gold["tddp4.nll"])
     res["tddp4.int." + mode] = rel(1.0 / M.dp.getNormalization(), gold["tddp4.integral"])
 
-bad = {k: v for k, v in res.items() if v > (1e-11 if k.startswith("tddp4.int") else 1e-12)}
+bad = {k: v for k, v in res.items() if v > (1e-11 if k.startswith("tddp4.int") or k == "dalitz.prob" else 1e-12)}
 assert not bad, (rank, bad)
 dist.barrier()
 lib.gf_comm_destroy(ctx)

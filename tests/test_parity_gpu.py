@@ -258,6 +258,13 @@ def test_dalitz_values(golden):
     s.updateParameters()
     assert rel(s.calculateNLL(), golden["dalitz.nll_mass_moved"]) < RTOL_NLL
     assert rel(1.0 / s.getNormalization(), golden["dalitz.integral_mass_moved"]) < 1e-12
+    # fit fractions from the cached waves at this point: W_ij summed on the device (gf_amp3_wave_gram), coefficients applied on the
+    # host; the reference sums Re(c_i conj(c_j) w_i conj(w_j)) event by event for every ordered pair (Amp3Body.cu:376-428)
+    ff = np.asarray(s.fit_fractions())
+    want = golden.arr("dalitz.fitfrac")
+    assert ff.shape == want.shape == (16, 16)
+    np.testing.assert_allclose(ff, want, rtol=1e-11, atol=1e-13 * np.abs(want).max())
+    assert abs(ff.sum() - 1.0) < 1e-12
 
 
 def test_zoo3_resonance_shapes(golden):
