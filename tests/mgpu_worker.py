@@ -51,10 +51,17 @@ M.signal.setDataSize(len(d))
 res["dalitz"] = rel(M.signal.calculateNLL(), gold["dalitz.nll"])
 assert gf.local_events() < len(d)
 # per-event values under sharding: every rank gets ALL events back in event order (the reference's MPI_Allgatherv, GooPdf.cu:139-172)
-probs = np.asarray(M.signal.getCompProbsAtDataPoints()[0])
+wrap = gf.ProdPdf("wrap", [M.signal])  # as DalitzPlotter.h:60-63 and tests/test_parity_gpu.py::test_dalitz_values do
+wrap.setData(d)
+M.signal.setDataSize(len(d))
+probs = np.asarray(wrap.getCompProbsAtDataPoints()[0])
 want = arr("dalitz.prob")
 assert probs.shape == want.shape, (probs.shape, want.shape)
 res["dalitz.prob"] = float(np.max(np.abs(probs - want) / np.maximum(np.abs(want), 1e-300)))
+M.signal.setFitControl(gf.UnbinnedNllFit())
+M.signal.setData(d)
+M.signal.setDataSize(len(d))
+M.signal.calculateNLL()
 # fit fractions: the wave Gram matrix is a sum over ranks
 for v in M.masses + M.widths:
     v.changed = False
