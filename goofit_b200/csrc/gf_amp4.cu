@@ -873,6 +873,16 @@ extern "C" int gf_amp4_cache_gram(gf_ctx *c, int node, int redo_spins, const uin
     return 0;
 }
 
+// the data-sample half of gf_amp4_cache alone: what toy generation needs (Amp4Body_TD::GenerateSig evaluates the PDF with the
+// normalisation forced to 1, Amp4Body_TD.cu:764-765,946-950), so no pass over the MC sample is made
+extern "C" int gf_amp4_cache_data(gf_ctx *c, int node, int redo_spins, const uint8_t *ls_redo, const uint8_t *amp_redo) {
+    gf_amp4_state *s;
+    if(amp4_check(c, node, &s, false)) return 1;
+    cudaSetDevice(c->device);
+    if(s->data.ls && s->data.n != c->view.n_events) return gf_fail("gf_amp4_cache_data: cache size != uploaded events");
+    return run_set(c, s, node, s->data, redo_spins, mask64(ls_redo, s->nLS), mask64(amp_redo, s->nAmp));
+}
+
 extern "C" int gf_amp4_norm_async(gf_ctx *c, int node) {
     gf_amp4_state *s;
     if(amp4_check(c, node, &s, false)) return 1;

@@ -93,6 +93,11 @@ struct GeneratedSignal {
 /// mcbooster::PhaseSpace (not part of the reference checkout); weights are relative to the largest possible weight.
 void generatePhaseSpaceParticles(const std::vector<fptype> &mother_and_daughter_masses, size_t nEvents, unsigned long seed,
                                  size_t offset, std::vector<std::vector<fptype>> &particles, std::vector<fptype> &weights);
+/// The same stream generated on the GPU (csrc/gf_gen.cu k_genbod, one thread per event): what GenerateSig and the four-body
+/// normalisation samples use. `dim5` (four daughters only) receives (m12, m34, cos12, cos34, phi) when not null. Needs a device.
+void devicePhaseSpace(const std::vector<fptype> &mother_and_daughter_masses, size_t nEvents, unsigned long seed, size_t offset,
+                      std::vector<std::vector<fptype>> *particles, std::vector<fptype> &weights,
+                      std::vector<std::vector<fptype>> *dim5 = nullptr);
 /// Amp3BodyBase::fillMCFlags (Amp3BodyBase.cu:13-21): accept event i when weight_i / max weight beats a uniform number
 std::vector<bool> acceptRejectFlags(const std::vector<fptype> &weights, unsigned long seed, size_t offset);
 

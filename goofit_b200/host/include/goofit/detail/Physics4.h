@@ -121,6 +121,10 @@ std::vector<std::vector<fptype>> generatePhaseSpace5(const std::vector<fptype> &
                                                       unsigned long seed, std::vector<fptype> *weights = nullptr);
 /// accept-reject "Unweight" flags for a weighted phase-space sample (counter-based, deterministic in (seed, index))
 std::vector<bool> unweightPhaseSpace(const std::vector<fptype> &weights, unsigned long seed);
+namespace detail {
+/// uniform number in (0, 1) of the counter-based generator: stream `stream` of event `event` of `seed`
+double counterUniform(unsigned long seed, size_t event, unsigned long stream);
+} // namespace detail
 /// (m12, m34, cos12, cos34, phi) of one event given as 4 x (E, px, py, pz) — pinned by tests/simple/VectorsTest.cu
 void fourVectorsToDim5(const fptype *p4x4_Epxpypz, fptype *out5);
 
@@ -139,7 +143,10 @@ class Amp4BodyBase : public GooPdf {
     NormMode getNormMode() const { return normMode; }
     /// replace the normalisation sample: five columns (m12, m34, cos12, cos34, phi) of equal length
     void setNormEvents(const std::vector<std::vector<fptype>> &cols5);
-    const std::vector<std::vector<fptype>> &getNormEvents() const { return normCols; }
+    const std::vector<std::vector<fptype>> &getNormEvents() {
+        materialiseNormEvents();
+        return normCols;
+    }
     std::vector<std::complex<fptype>> getCachedAmp(size_t a) const;
     size_t numLineshapes() const { return LineShapes.size(); }
     size_t numSpinFactors() const { return SpinFactors.size(); }
@@ -152,6 +159,14 @@ class Amp4BodyBase : public GooPdf {
     void addAmplitudeRecord(Amplitude *amp);
     std::vector<int32_t> headerInts(detail::ProgramBuilder &B, int tdOffset) const;
     void ensureCache();
+    /// a normalisation sample still to be generated: GENBOD candidates per seed, accept-reject, compacted or "first nAcc"
+    struct NormSpec {
+        std::vector<long> seeds;
+        unsigned int perBatch = 0;
+        bool compact = true;
+        std::vector<fptype> masses;
+    } normSpec;
+    void materialiseNormEvents();
     void setDataSizeCommon(unsigned int dataSize, unsigned int evtSize);
     /// (re)build the Gram matrix if the MC amplitudes changed; returns G[a * nAmps + b]
     const std::vector<std::complex<fptype>> &gram(bool mcAmpsChanged);
@@ -176,7 +191,10 @@ class Amp4Body : public Amp4BodyBase { // Amp4Body.h:33-95
     Amp4Body(std::string n, std::vector<Observable> observables, DecayInfo4 decay, GooPdf *eff, unsigned int MCeventsNorm = 5e6);
     fptype normalize() override;
     void setDataSize(unsigned int dataSize, unsigned int evtSize = 6) { setDataSizeCommon(dataSize, evtSize); }
-    int getMCevents() { return static_cast<int>(MCevents); }
+    int getMCevents() {
+        materialiseNormEvents();
+        return static_cast<int>(MCevents);
+    }
     int emit(detail::ProgramBuilder &B) override;
     /// Amp4Body.cu:560-677: phase-space events, their (m12, m34, cos12, cos34, phi), weight x |sum c A|^2 x efficiency,
     /// accept/reject flags. As upstream, the generated events REPLACE the PDF's dataset.
@@ -237,8 +255,21 @@ class Amp4Body_TD final : public Amp4BodyBase { // Amp4Body_TD.h:34-137
                 GooPdf *efficiency, Observable *mistag, const std::vector<long> &normSeeds, unsigned int numNormEventsToGenPerBatch);
     fptype normalize() override;
     void setDataSize(unsigned int dataSize, unsigned int evtSize = 8) { setDataSizeCommon(dataSize, evtSize); }
-    int getNumAccNormEvents() const { return static_cast<int>(MCevents); }
-    fptype getSumInitNormEventWeights() const { return static_cast<fptype>(MCevents); }
+    int getNumAccNormEvents() {
+        materialiseNormEvents();
+        return static_cast<int>(MCevents);
+    }
+    fptype getSumInitNormEventWeights() {
+        materialiseNormEvents();
+        return static_cast<fptype>(MCevents);
+    }
+    /// Amp4Body_TD.cu:825-1018: unweighted phase space, decay times under an exponential envelope, accept/reject flags.
+    /// As upstream, the generated events REPLACE the PDF's dataset.
+    GeneratedSignal GenerateSig(unsigned int numEvents, int seed = 0);
+    void setGenerationOffset(int off) { generation_offset = off; }
+    int getGenerationOffset() const { return generation_offset; }
+    void setMaxWeight(fptype wmax) { maxWeight = wmax; }
+    fptype getMaxWeight() const { return maxWeight; }
     int emit(detail::ProgramBuilder &B) override;
     void emitAux(detail::ProgramBuilder &B) override;
 
@@ -248,6 +279,10 @@ class Amp4Body_TD final : public Amp4BodyBase { // Amp4Body_TD.h:34-137
     MixingTimeResolution *resolution;
     std::vector<int32_t> flags;
     bool spinsCalculated{false};
+    bool generation_no_norm{false};
+    int generation_offset{0};
+    fptype maxWeight{0};
+    std::unique_ptr<UnbinnedDataSet> generated;
 };
 
 } // namespace GooFit

@@ -252,8 +252,8 @@ fpcomplex Amp3Body::sumCachedWave(size_t i) const {
 }
 GeneratedSignal Amp3Body::GenerateSig(unsigned int numEvents, int seed) {
     GeneratedSignal G;
-    generatePhaseSpaceParticles({decayInfo.motherMass, decayInfo.daug1Mass, decayInfo.daug2Mass, decayInfo.daug3Mass}, numEvents,
-                                static_cast<unsigned long>(seed), generation_offset, G.particles, G.weights);
+    devicePhaseSpace({decayInfo.motherMass, decayInfo.daug1Mass, decayInfo.daug2Mass, decayInfo.daug3Mass}, numEvents,
+                     static_cast<unsigned long>(seed), generation_offset, &G.particles, G.weights);
     auto pairMass2 = [&](int a, int b, size_t i) { // detail/Dim2.h:22-35
         const fptype *p = G.particles[a].data() + 4 * i, *q = G.particles[b].data() + 4 * i;
         fptype e = p[0] + q[0], x = p[1] + q[1], y = p[2] + q[2], z = p[3] + q[3];

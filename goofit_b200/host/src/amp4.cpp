@@ -163,6 +163,11 @@ inline double uniform01(uint64_t seed, uint64_t event, uint64_t k) {
     uint64_t h = mix64(mix64(seed ^ 0xD1B54A32D192ED03ull) + event * 0x2545F4914F6CDD1Dull + k);
     return ((h >> 11) + 0.5) * (1.0 / 9007199254740992.0);
 }
+} // namespace
+namespace detail {
+double counterUniform(unsigned long seed, size_t event, unsigned long stream) { return uniform01(seed, event, stream); }
+} // namespace detail
+namespace {
 inline double pdk(double a, double b, double c) {
     double x = (a - b - c) * (a + b + c) * (a + b - c) * (a - b + c);
     return std::sqrt(x > 0 ? x : 0) / (2 * a);
@@ -304,6 +309,25 @@ void generatePhaseSpaceParticles(const std::vector<fptype> &pm, size_t n, unsign
         weights[i] = wt;
     }
 }
+void devicePhaseSpace(const std::vector<fptype> &pm, size_t n, unsigned long seed, size_t offset, std::vector<std::vector<fptype>> *particles,
+                      std::vector<fptype> &weights, std::vector<std::vector<fptype>> *dim5) {
+    const int nd = static_cast<int>(pm.size()) - 1;
+    if(nd != 3 && nd != 4) throw GeneralError("devicePhaseSpace: 3 or 4 daughters, got {}", nd);
+    if(dim5 && nd != 4) throw GeneralError("devicePhaseSpace: the five-variable form needs four daughters");
+    weights.assign(n, 0.0);
+    std::vector<fptype> flatP(particles ? 4 * n * nd : 0), flatV(dim5 ? 5 * n : 0);
+    Engine &E = Engine::get();
+    Engine::check(gf_genbod(E.ctx(), pm.data(), nd, n, seed, offset, particles ? flatP.data() : nullptr, weights.data(), dim5 ? flatV.data() : nullptr),
+                  "gf_genbod");
+    if(particles) {
+        particles->assign(nd, std::vector<fptype>());
+        for(int d = 0; d < nd; d++) (*particles)[d].assign(flatP.begin() + (size_t)d * 4 * n, flatP.begin() + (size_t)(d + 1) * 4 * n);
+    }
+    if(dim5) {
+        dim5->assign(5, std::vector<fptype>());
+        for(int k = 0; k < 5; k++) (*dim5)[k].assign(flatV.begin() + (size_t)k * n, flatV.begin() + (size_t)(k + 1) * n);
+    }
+}
 std::vector<bool> acceptRejectFlags(const std::vector<fptype> &w, unsigned long seed, size_t offset) {
     fptype wmax = 0;
     for(fptype v : w) wmax = std::max(wmax, v);
@@ -320,16 +344,7 @@ std::vector<bool> unweightPhaseSpace(const std::vector<fptype> &w, unsigned long
 
 GeneratedSignal Amp4Body::GenerateSig(unsigned int numEvents, int seed) {
     GeneratedSignal G;
-    generatePhaseSpaceParticles(decayInfo.particle_masses, numEvents, static_cast<unsigned long>(seed), generation_offset, G.particles,
-                                G.weights);
-    G.variables.assign(5, std::vector<fptype>(numEvents));
-    for(size_t i = 0; i < numEvents; i++) {
-        fptype in[16], out[5];
-        for(int d = 0; d < 4; d++)
-            for(int k = 0; k < 4; k++) in[4 * d + k] = G.particles[d][4 * i + k];
-        fourVectorsToDim5(in, out);
-        for(int k = 0; k < 5; k++) G.variables[k][i] = out[k];
-    }
+    devicePhaseSpace(decayInfo.particle_masses, numEvents, static_cast<unsigned long>(seed), generation_offset, &G.particles, G.weights, &G.variables);
     std::vector<fptype> evt(numEvents);
     std::iota(evt.begin(), evt.end(), 0.0);
     std::vector<Observable> obs(observablesList.begin(), observablesList.begin() + 6);
@@ -385,7 +400,36 @@ std::vector<int32_t> Amp4BodyBase::headerInts(detail::ProgramBuilder &B, int tdO
     ints.insert(ints.end(), ampRecords.begin(), ampRecords.end());
     return ints;
 }
+// The generated normalisation sample: per seed, GENBOD candidates and their five variables on the GPU (k_genbod), the
+// accept-reject "Unweight" step against the counter-based uniform stream, then either the COMPACTED accepted events
+// (Amp4Body_TD: detail/NormEvents_4Body_Base.cu:24-78 does run the remove_if) or the FIRST nAcc events of the un-compacted sample
+// (Amp4Body.cu:243-289: the remove_if is commented out there). Generation is deferred to the first use so that building a model
+// needs no device and a 10^8-event sample costs no host loop over GENBOD.
+void Amp4BodyBase::materialiseNormEvents() {
+    if(normSpec.perBatch == 0) return;
+    NormSpec spec = normSpec;
+    normSpec.perBatch = 0;
+    std::vector<std::vector<fptype>> all(5);
+    for(long seed : spec.seeds) {
+        std::vector<fptype> w;
+        std::vector<std::vector<fptype>> v5;
+        devicePhaseSpace(spec.masses, spec.perBatch, static_cast<unsigned long>(seed), 0, nullptr, w, &v5);
+        auto acc = unweightPhaseSpace(w, static_cast<unsigned long>(seed));
+        if(spec.compact) {
+            for(size_t i = 0; i < w.size(); i++)
+                if(acc[i])
+                    for(int k = 0; k < 5; k++) all[k].push_back(v5[k][i]);
+        } else {
+            size_t nAcc = std::count(acc.begin(), acc.end(), true);
+            if(nAcc == 0) nAcc = 1;
+            for(int k = 0; k < 5; k++) all[k].insert(all[k].end(), v5[k].begin(), v5[k].begin() + nAcc);
+        }
+    }
+    if(all[0].empty()) throw GeneralError("{}: no normalisation event was accepted", getName());
+    setNormEvents(all);
+}
 void Amp4BodyBase::setNormEvents(const std::vector<std::vector<fptype>> &cols5) {
+    normSpec.perBatch = 0; // an explicit sample replaces a pending generated one
     if(cols5.size() != 5) throw GeneralError("setNormEvents needs five columns (m12, m34, cos12, cos34, phi)");
     for(auto &c : cols5)
         if(c.size() != cols5[0].size() || c.empty()) throw GeneralError("setNormEvents: columns must be non-empty and of equal length");
@@ -413,6 +457,7 @@ void Amp4BodyBase::setDataSizeCommon(unsigned int dataSize, unsigned int evtSize
 void Amp4BodyBase::ensureCache() {
     if(cacheAllocated) return;
     if(nodeIdx < 0) throw GeneralError("{}: call setData() on the top-level PDF before evaluating", getName());
+    materialiseNormEvents();
     if(MCevents == 0) throw GeneralError("{} has no normalisation events", getName());
     Engine &E = Engine::get();
     E.requireComm("Amp4Body normalisation");
@@ -480,15 +525,8 @@ Amp4Body::Amp4Body(std::string n, std::vector<Observable> observables, DecayInfo
     // Normalisation sample. The reference generates MCeventsNorm phase-space events, runs the accept-reject
     // "Unweight" step and then keeps the FIRST nAcc events of the un-compacted sample (Amp4Body.cu:243-289: the
     // remove_if is commented out); the same selection is made here.
-    if(MCeventsNorm > 0) {
-        std::vector<fptype> w;
-        auto cols = generatePhaseSpace5(decayInfo.particle_masses, MCeventsNorm, 0, &w);
-        auto acc  = unweightPhaseSpace(w, 0);
-        size_t nAcc = std::count(acc.begin(), acc.end(), true);
-        if(nAcc == 0) nAcc = 1;
-        for(auto &c : cols) c.resize(nAcc);
-        setNormEvents(cols);
-    }
+    // The sample itself is generated on the device when it is first needed (materialiseNormEvents).
+    if(MCeventsNorm > 0) normSpec = NormSpec{{0}, MCeventsNorm, false, decayInfo.particle_masses};
     setSeparateNorm();
 }
 int Amp4Body::emit(detail::ProgramBuilder &B) {
@@ -646,19 +684,8 @@ void Amp4Body_TD::init(std::vector<Observable> &observables, Observable *mistag,
     registerFunction("ptr_to_Amp4Body_TD", GF_OP_AMP4_TD);
     // Normalisation sample: per seed, phase space -> accept-reject -> COMPACTED accepted events
     // (detail/NormEvents_4Body_Base.cu:24-78; unlike Amp4Body, upstream does run the remove_if here)
-    if(perBatch > 0 && !seeds.empty()) {
-        std::vector<std::vector<fptype>> all(5);
-        for(long seed : seeds) {
-            std::vector<fptype> w;
-            auto cols = generatePhaseSpace5(decayInfo.particle_masses, perBatch, static_cast<unsigned long>(seed), &w);
-            auto acc  = unweightPhaseSpace(w, static_cast<unsigned long>(seed));
-            for(size_t i = 0; i < w.size(); i++)
-                if(acc[i])
-                    for(int k = 0; k < 5; k++) all[k].push_back(cols[k][i]);
-        }
-        if(all[0].empty()) throw GeneralError("Amp4Body_TD {}: no normalisation event was accepted", n);
-        setNormEvents(all);
-    }
+    // The sample itself is generated on the device when it is first needed (materialiseNormEvents).
+    if(perBatch > 0 && !seeds.empty()) normSpec = NormSpec{seeds, perBatch, true, decayInfo.particle_masses};
     setSeparateNorm();
 }
 void Amp4Body_TD::emitAux(detail::ProgramBuilder &B) {
@@ -693,6 +720,11 @@ fptype Amp4Body_TD::normalize() { // Amp4Body_TD.cu:744-799
     int spins          = forceRedoIntegrals ? 1 : 0;
     forceRedoIntegrals = false;
     E.sync();
+    if(generation_no_norm) { // GenerateSig: data-side caches only, normalisation 1 (Amp4Body_TD.cu:764-765,946-950)
+        if(any) Engine::check(gf_amp4_cache_data(E.ctx(), nodeIdx, spins, lsRedo.data(), ampRedo.data()), "gf_amp4_cache_data");
+        setNormalization(1.0);
+        return 1.0;
+    }
     refreshCaches(any, spins, lsRedo, ampRedo);
     double sums[4] = {0, 0, 0, 0};
     if(normMode == NormMode::Gram) {
@@ -731,6 +763,75 @@ fptype Amp4Body_TD::normalize() { // Amp4Body_TD.cu:744-799
     fptype ret = resolution->normalization(sums[0], sums[1], sums[2], sums[3], tau, x, y) / getSumInitNormEventWeights();
     setNormalization(1.0 / ret);
     return ret;
+}
+
+
+// Amp4Body_TD.cu:825-1018. Phase-space candidates are unweighted and COMPACTED first (the remove_if over the accept flags), decay
+// times are drawn from exp(-gammamin t) with gammamin = (1 - |y|) / tau, the PDF (normalisation forced to 1) is evaluated once at
+// t = 0 to find the envelope's height (1.1 x the largest value) and once at the drawn times; event i is accepted when
+// u_i x wmax x exp(-gammamin t_i) < pdf_i. Returned: the accepted candidates' four-vectors, (m12, m34, cos12, cos34, phi, t), the
+// t = 0 values ("weights") and the flags. The uniform numbers come from this build's counter-based generator (MCBooster's
+// stream and thrust's minstd are not reproduced), keyed on (seed, generation_offset + index) like the phase space.
+GeneratedSignal Amp4Body_TD::GenerateSig(unsigned int numEvents, int seed) {
+    GeneratedSignal G;
+    std::vector<std::vector<fptype>> P, V5;
+    std::vector<fptype> w;
+    devicePhaseSpace(decayInfo.particle_masses, numEvents, static_cast<unsigned long>(seed), generation_offset, &P, w, &V5);
+    std::vector<bool> acc(numEvents);
+    size_t nAcc = 0;
+    for(size_t i = 0; i < numEvents; i++) { // mcbooster::PhaseSpace::Unweight: weight / max weight against a uniform number
+        acc[i] = w[i] > detail::counterUniform(static_cast<unsigned long>(seed), i + generation_offset, 1000);
+        nAcc += acc[i];
+    }
+    if(nAcc == 0) throw GeneralError("{}: no phase-space candidate was accepted", getName());
+    G.particles.assign(4, std::vector<fptype>(4 * nAcc));
+    G.variables.assign(6, std::vector<fptype>(nAcc));
+    const fptype tau = parametersList[0].getValue(), ymixing = parametersList[2].getValue();
+    const fptype gammamin = 1.0 / tau - std::fabs(ymixing) / tau;
+    for(size_t i = 0, k = 0; i < numEvents; i++) {
+        if(!acc[i]) continue;
+        for(int d = 0; d < 4; d++) std::copy(P[d].begin() + 4 * i, P[d].begin() + 4 * i + 4, G.particles[d].begin() + 4 * k);
+        for(int v = 0; v < 5; v++) G.variables[v][k] = V5[v][i];
+        G.variables[5][k] = -std::log(detail::counterUniform(static_cast<unsigned long>(seed), k + generation_offset, 3000)) / gammamin; // genExp
+        k++;
+    }
+    std::vector<fptype> evt(nAcc), zeros(nAcc, 0.0);
+    std::iota(evt.begin(), evt.end(), 0.0);
+    std::vector<Observable> obs(observablesList.begin(), observablesList.begin() + 8);
+    auto upload = [&](const std::vector<fptype> &times) {
+        generated = std::make_unique<UnbinnedDataSet>(obs);
+        generated->appendColumns({G.variables[0].data(), G.variables[1].data(), G.variables[2].data(), G.variables[3].data(), G.variables[4].data(),
+                                  evt.data(), times.data(), zeros.data()},
+                                 nAcc);
+        setData(generated.get());
+        setDataSize(nAcc, 8);
+    };
+    auto fc = fitControl;
+    const bool hadNorm = generation_no_norm;
+    generation_no_norm = true; // no MC integral while generating: the value is used un-normalised (Amp4Body_TD.cu:946-950)
+    setFitControl(std::make_shared<EvalFit>());
+    upload(zeros); // the envelope's height: the PDF at t = 0
+    normalize();
+    G.weights = evaluate_with_metric();
+    fptype wmax = 1.1 * *std::max_element(G.weights.begin(), G.weights.end());
+    if(wmax > maxWeight && maxWeight != 0)
+        throw GeneralError("WARNING: you just encountered a higher maximum weight than observed in previous iterations.\n"
+                           "WARNING: Consider recalculating your AccRej flags and accepting based upon these.\n"
+                           "WARNING: previous weight: {}, new weight: {}\n",
+                           maxWeight, wmax);
+    maxWeight = wmax > maxWeight ? wmax : maxWeight;
+    upload(G.variables[5]);
+    normalize();
+    std::vector<fptype> results = evaluate_with_metric();
+    setFitControl(fc);
+    generation_no_norm = hadNorm;
+    setForceIntegrals();
+    G.flags.resize(nAcc);
+    for(size_t k = 0; k < nAcc; k++) { // exp_functor, Amp4Body_TD.cu:76-117
+        const fptype envelope = std::exp(-G.variables[5][k] * gammamin) * maxWeight;
+        G.flags[k] = detail::counterUniform(static_cast<unsigned long>(seed), k + generation_offset, 4000) * envelope < results[k];
+    }
+    return G;
 }
 
 } // namespace GooFit

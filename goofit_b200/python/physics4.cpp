@@ -116,7 +116,7 @@ void init_physics4(py::module &m) {
              },
              "cols5"_a)
         .def("getNormEvents",
-             [](const Amp4BodyBase &a) {
+             [](Amp4BodyBase &a) {
                  auto &c = a.getNormEvents();
                  size_t n = c.empty() ? 0 : c[0].size();
                  py::array_t<fptype> r({(size_t)5, n});
@@ -156,7 +156,16 @@ void init_physics4(py::module &m) {
              py::keep_alive<1, 4>(), py::keep_alive<1, 5>(), py::keep_alive<1, 6>(), py::keep_alive<1, 7>())
         .def("setDataSize", &Amp4Body_TD::setDataSize, "dataSize"_a, "evtSize"_a = 8)
         .def("getNumAccNormEvents", &Amp4Body_TD::getNumAccNormEvents)
-        .def("getSumInitNormEventWeights", &Amp4Body_TD::getSumInitNormEventWeights);
+        .def("getSumInitNormEventWeights", &Amp4Body_TD::getSumInitNormEventWeights)
+        .def("setGenerationOffset", &Amp4Body_TD::setGenerationOffset, "off"_a)
+        .def("getGenerationOffset", &Amp4Body_TD::getGenerationOffset)
+        .def("setMaxWeight", &Amp4Body_TD::setMaxWeight, "wmax"_a)
+        .def("getMaxWeight", &Amp4Body_TD::getMaxWeight)
+        .def(
+            "GenerateSig",
+            [](Amp4Body_TD &self, size_t numEvents, int seed) { return generated_to_numpy(self.GenerateSig(numEvents, seed), 4); },
+            "numEvents"_a, "seed"_a = 0,
+            "(particles[4, nAcc, 3 or 4], variables[6, nAcc] = m12, m34, cos12, cos34, phi, dtime, weights[nAcc] = PDF at t = 0, flags[nAcc])");
     m.def(
         "generatePhaseSpaceParticles",
         [](std::vector<fptype> masses, size_t n, unsigned long seed, size_t offset) {
@@ -168,6 +177,20 @@ void init_physics4(py::module &m) {
         },
         "mother_and_daughter_masses"_a, "nEvents"_a, "seed"_a = 0, "offset"_a = 0,
         "GENBOD phase-space events for 3 or 4 daughters: (particles[nd, N, 4] as (E, px, py, pz), weights[N])");
+    m.def(
+        "devicePhaseSpace",
+        [](std::vector<fptype> masses, size_t n, unsigned long seed, size_t offset) {
+            GeneratedSignal G;
+            std::vector<std::vector<fptype>> v5;
+            devicePhaseSpace(masses, n, seed, offset, &G.particles, G.weights, masses.size() == 5 ? &v5 : nullptr);
+            G.flags.assign(n, false);
+            py::tuple t = generated_to_numpy(G, (int)masses.size() - 1);
+            py::array_t<fptype> r({(size_t)(v5.empty() ? 0 : 5), n});
+            for(size_t k = 0; k < v5.size(); k++) std::copy(v5[k].begin(), v5[k].end(), r.mutable_data(k, 0));
+            return py::make_tuple(t[0], t[2], r);
+        },
+        "mother_and_daughter_masses"_a, "nEvents"_a, "seed"_a = 0, "offset"_a = 0,
+        "the stream of generatePhaseSpaceParticles generated on the GPU: (particles[nd, N, 4], weights[N], dim5[5, N] for four daughters)");
     m.def("generatePhaseSpace5",
           [](std::vector<fptype> masses, size_t n, unsigned long seed) {
               std::vector<fptype> w;

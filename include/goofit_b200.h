@@ -171,6 +171,8 @@ int gf_amp4_gram(gf_ctx *, int node, double *G_re_im /* nAmp*nAmp*2 */);
  * when a mass or width moves: Amp4Body.cu:462-558, detail/NormLSCalculator.cu:11-62, NormIntegrator.cu:15-68). Up to 16 amplitudes;
  * beyond that (or with the "fused" option off) it is exactly gf_amp4_cache followed by gf_amp4_gram. */
 int gf_amp4_cache_gram(gf_ctx *, int node, int redo_spins, const uint8_t *ls_redo, const uint8_t *amp_redo, double *G_re_im);
+/* the data-sample half of gf_amp4_cache alone (toy generation evaluates the PDF un-normalised: Amp4Body_TD.cu:946-950) */
+int gf_amp4_cache_data(gf_ctx *, int node, int redo_spins, const uint8_t *ls_redo, const uint8_t *amp_redo);
 int gf_amp4_get_amp(gf_ctx *, int node, int amp, double *out_re_im, size_t n_events);
 
 /* ---- multi-GPU: one process per GPU, partial sums all-reduced in-stream over NCCL (NVLink/NVSwitch) --------
@@ -202,6 +204,12 @@ int gf_timer_stop(gf_ctx *, float *ms);
  * through a ring of pinned slots, so a caller can queue several evaluations back to back */
 int gf_set_params_async(gf_ctx *, const double *params, int n, const double *norms, int n_norms);
 
+/* GENBOD phase space of mother -> 3 or 4 daughters on the device, events [offset, offset + n) of the counter-based stream `seed`
+ * (replaces mcbooster::PhaseSpace::Generate + EvaluateArray<Dim5>: Amp4Body.cu:243-289,560-677, Amp4Body_TD.cu:825-1018,
+ * detail/Dim5.h:19-111; MCBooster itself is not part of the reference checkout). masses = mother, daughters. Host outputs, each
+ * optional: particles[nd][n][4] = (E, px, py, pz), weights[n] relative to the largest possible weight, dim5[5][n] = (m12, m34,
+ * cos12, cos34, phi) for four daughters. */
+int gf_genbod(gf_ctx *, const double *masses, int nd, size_t n, uint64_t seed, uint64_t offset, double *particles, double *weights, double *dim5);
 /* measured FP64 FMA peak of this GPU (DFMA micro-benchmark, TFLOP/s, 2 flops per FMA): the roofline denominator of
  * the FP64-bound cache kernels (k_amp3_waves, k_amp4_cache), which MEASURED_PEAKS.json does not carry */
 int gf_fp64_peak(gf_ctx *, double *tflops);

@@ -637,7 +637,8 @@ def test_generate_sig_three_and_four_body():
     # a second batch continues the stream
     s.setGenerationOffset(n)
     P2, _, _, _ = s.GenerateSig(100, 11)
-    assert np.array_equal(P2, gf.generatePhaseSpaceParticles(masses, 100, 11, n)[0][:, :, :3])
+    # the GPU generator draws the host generator's stream (same counter-based numbers; libm differences only)
+    np.testing.assert_allclose(P2, gf.generatePhaseSpaceParticles(masses, 100, 11, n)[0][:, :, :3], rtol=1e-11, atol=1e-13)
     # the model can still be fitted to a dataset afterwards
     acc = np.flatnonzero(flags)
     d = M.dataset(V[0][acc], V[2][acc])
@@ -659,3 +660,50 @@ def test_generate_sig_three_and_four_body():
     tot = sum(coef[a] * np.asarray(D.dp.getCachedAmp(a)) for a in range(8))
     np.testing.assert_allclose(w, w_ps * np.abs(tot) ** 2, rtol=1e-10)
     assert 0 < flags.mean() < 1
+
+
+def test_device_phase_space_matches_host_stream():
+    """k_genbod (csrc/gf_gen.cu) against the host restatement of the same GENBOD stream: four-vectors, weights and the
+    five-variable form (detail/Dim5.h:19-111), for three and four daughters and with an offset into the stream."""
+    for masses in ([1.8645, 0.13957018, 0.13957018, 0.493677, 0.13957018], [1.86484, 0.13957018, 0.13957018, 0.1349766]):
+        n = 20000
+        Pd, wd, v5 = gf.devicePhaseSpace(masses, n, 17, 0)
+        Ph, wh = gf.generatePhaseSpaceParticles(masses, n, 17, 0)
+        np.testing.assert_allclose(Pd, Ph, rtol=1e-10, atol=1e-12)
+        np.testing.assert_allclose(wd, wh, rtol=1e-11)
+        if len(masses) == 5:
+            cols, w5 = gf.generatePhaseSpace5(masses, n, 17)
+            np.testing.assert_allclose(v5, np.asarray(cols), rtol=1e-9, atol=1e-9)
+        Po, wo, _ = gf.devicePhaseSpace(masses, 500, 17, 1500)
+        assert np.array_equal(Po, Pd[:, 1500:2000]) and np.array_equal(wo, wd[1500:2000])  # counter-based: batch-independent
+
+
+def test_generate_sig_time_dependent():
+    """Amp4Body_TD::GenerateSig (Amp4Body_TD.cu:825-1018): unweighted phase space, decay times under exp(-gammamin t), the PDF at
+    t = 0 as `weights`, accept/reject against the envelope. Properties: deterministic in (seed, offset); the returned weights are
+    the un-normalised PDF at t = 0; the accepted decay times follow the model's own time dependence."""
+    from models import TDDP4
+    M = TDDP4(three_gauss=False, float_ls=False, float_mix=True, mc_to_gen=20000)
+    n = 200000
+    P, V, w, flags = M.dp.GenerateSig(n, 23)
+    nacc = V.shape[1]
+    assert 0.01 * n < nacc < n and P.shape == (4, nacc, 4) and V.shape == (6, nacc) and w.shape == (nacc,) and flags.shape == (nacc,)
+    assert np.all(V[5] > 0) and np.all(w >= 0)
+    M.dp.setMaxWeight(0)
+    P2, V2, w2, f2 = M.dp.GenerateSig(n, 23)
+    assert np.array_equal(V, V2) and np.array_equal(w, w2) and np.array_equal(flags, f2)
+    # the PDF at t = 0, evaluated independently through the ordinary path
+    d = M.dataset([V[k] for k in range(5)] + [np.zeros(nacc), np.zeros(nacc)])
+    M.signal.setData(d)
+    M.dp.setDataSize(nacc, 8)
+    M.dp.setFitControl(gf.EvalFit())
+    M.dp.normalize()
+    direct = np.asarray(M.dp.evaluate_with_metric())
+    M.dp.setFitControl(gf.UnbinnedNllFit())
+    np.testing.assert_allclose(w, direct, rtol=1e-10)
+    # accepted times: x, y ~ 1e-2, so the time dependence is exp(-t / tau) to a per cent
+    tau = 0.4101
+    t_acc = V[5][flags]
+    assert 0.02 < flags.mean() < 0.95
+    assert abs(t_acc.mean() / tau - 1.0) < 0.05, t_acc.mean()
+    assert abs(V[5].mean() * (1.0 / tau - abs(M.mix[2].value) / tau) - 1.0) < 0.02  # candidates follow exp(-gammamin t)
