@@ -19,6 +19,7 @@ struct gf_amp4_set { // one event sample (data or MC) with its caches
     const double *cols[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     double *owned_cols = nullptr;
     double *weights = nullptr;
+    double *dtime = nullptr, *sigma = nullptr; // per-event decay time and resolution of a WEIGHTED normalisation sample (Amp4Body_TD)
     double2 *ls = nullptr;
     double *sf = nullptr;
     double2 *amps = nullptr;
@@ -48,7 +49,7 @@ struct gf_amp4_state {
 };
 
 static void free_set(gf_amp4_set &s) {
-    cudaFree(s.owned_cols); cudaFree(s.weights); cudaFree(s.ls); cudaFree(s.sf); cudaFree(s.amps); cudaFree(s.kin);
+    cudaFree(s.owned_cols); cudaFree(s.weights); cudaFree(s.dtime); cudaFree(s.sigma); cudaFree(s.ls); cudaFree(s.sf); cudaFree(s.amps); cudaFree(s.kin);
     s = gf_amp4_set();
 }
 void gf_amp4_free(gf_ctx *c) {
@@ -304,6 +305,39 @@ __global__ void __launch_bounds__(GF_THREADS, 4)
         acc[3] += w * (Aim * Bre - Are * Bim);
     }
     gf_grid_finish_n(acc, partials, ticket, out, red, PV);
+}
+
+// Weighted normalisation events of Amp4Body_TD (detail/NormIntegrator_TD_Weighted.cu:15-122): every MC event carries its own decay
+// time, resolution and weight, and the integrand is the time-dependent PDF itself, sum_m w_m R(|A|^2 + |B|^2, |A|^2 - |B|^2,
+// A conj(B); tau, t_m, x, y, sigma_m) - no analytic time integral. The amplitudes come from the cached MC planes.
+template <bool G3>
+__global__ void __launch_bounds__(GF_THREADS, 3)
+    k_amp4_norm_tdw(const gf_dev_view V, int node, const double2 *amps, long ld, long n, const double *weights, const double *dtime, const double *sigma,
+                    double *partials, unsigned *ticket, double *out, const gf_peer_view PV) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ double red[32];
+    gf_sprog P = gf_stage_program(V, smem);
+    __syncthreads();
+    const gf_node &nd = P.nodes[node];
+    const double *p = P.params + nd.par_off;
+    const int32_t *in = P.ints + nd.int_off;
+    const int nAmp = in[3];
+    const int32_t *td = in + in[4];
+    const gf_node &rn = P.nodes[td[0]];
+    const double *rp = P.params + rn.par_off;
+    double acc = 0;
+    const long stride = (long)gridDim.x * blockDim.x;
+    for(long m = (long)blockIdx.x * blockDim.x + threadIdx.x; m < n; m += stride) {
+        const double t = __ldg(dtime + m), sg = __ldg(sigma + m), w = __ldg(weights + m);
+        double Are, Aim, Bre, Bim;
+        gf_amp4td_AB(p, td + 1, nAmp, [&](int a) { return __ldg(amps + (size_t)a * ld + m); }, Are, Aim, Bre, Bim);
+        const double nA = Are * Are + Aim * Aim, nB = Bre * Bre + Bim * Bim;
+        const double t3re = Are * Bre + Aim * Bim, t3im = Aim * Bre - Are * Bim; // A conj(B)
+        double ret = gf_tres<G3>(rn.op, rp, nA + nB, nA - nB, t3re, t3im, p[0], t, p[1], p[2], sg);
+        ret *= w;
+        acc += ret;
+    }
+    gf_grid_finish(&acc, 1, partials, ticket, out, red, PV);
 }
 
 // G_ab = sum_m w_m A_a(m) conj(A_b(m)) for one GF_GRAM_T x GF_GRAM_T tile (rows a0.., columns b0..) of the Hermitian
@@ -679,11 +713,12 @@ extern "C" int gf_amp4_set_mc(gf_ctx *c, int node, const double *const *mc_cols5
     gf_amp4_state *s;
     if(amp4_check(c, node, &s, true)) return 1;
     if(n_mc == 0) return gf_fail("gf_amp4_set_mc: no MC events");
-    (void)dtime; (void)sigma;
+    if((dtime == nullptr) != (sigma == nullptr)) return gf_fail("gf_amp4_set_mc: decay times and resolutions come together");
+    if(dtime && !weights) return gf_fail("gf_amp4_set_mc: a sample with decay times is a weighted sample");
     cudaSetDevice(c->device);
     GF_CUDA(cudaStreamSynchronize(c->stream));
-    cudaFree(s->mc.owned_cols); cudaFree(s->mc.weights);
-    s->mc.owned_cols = nullptr; s->mc.weights = nullptr;
+    cudaFree(s->mc.owned_cols); cudaFree(s->mc.weights); cudaFree(s->mc.dtime); cudaFree(s->mc.sigma);
+    s->mc.owned_cols = nullptr; s->mc.weights = nullptr; s->mc.dtime = nullptr; s->mc.sigma = nullptr;
     if(alloc_caches(c, s, s->mc, n_mc)) return 1;
     s->gram_valid = false;
     s->mma_valid = false;
@@ -696,6 +731,12 @@ extern "C" int gf_amp4_set_mc(gf_ctx *c, int node, const double *const *mc_cols5
         GF_CUDA(cudaMalloc(&s->mc.weights, sizeof(double) * (size_t)s->mc.ld)); // padded like the planes: the one-pass update copies 16-byte units
         GF_CUDA(cudaMemsetAsync(s->mc.weights, 0, sizeof(double) * (size_t)s->mc.ld, c->stream));
         GF_CUDA(cudaMemcpyAsync(s->mc.weights, weights, sizeof(double) * n_mc, cudaMemcpyHostToDevice, c->stream));
+    }
+    if(dtime) {
+        GF_CUDA(cudaMalloc(&s->mc.dtime, sizeof(double) * (size_t)s->mc.ld));
+        GF_CUDA(cudaMalloc(&s->mc.sigma, sizeof(double) * (size_t)s->mc.ld));
+        GF_CUDA(cudaMemcpyAsync(s->mc.dtime, dtime, sizeof(double) * n_mc, cudaMemcpyHostToDevice, c->stream));
+        GF_CUDA(cudaMemcpyAsync(s->mc.sigma, sigma, sizeof(double) * n_mc, cudaMemcpyHostToDevice, c->stream));
     }
     GF_CUDA(cudaStreamSynchronize(c->stream)); // host columns may be freed by the caller
     return 0;
@@ -891,6 +932,18 @@ extern "C" int gf_amp4_norm_async(gf_ctx *c, int node) {
     size_t sm = gf_prog_smem(c);
     if(sm > 48 * 1024) cudaFuncSetAttribute(k_amp4_norm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
     int blocks = gf_grid_blocks(c, s->mc.n, 4);
+    if(s->td && s->mc.dtime) { // weighted sample with per-event decay times: ONE sum, the time-dependent PDF itself
+        const int32_t *in = c->h_ints.data() + c->h_nodes[node].int_off;
+        const bool g3 = c->h_nodes[in[in[4]]].op != GF_OP_TRES_TRUTH;
+        auto k = g3 ? k_amp4_norm_tdw<true> : k_amp4_norm_tdw<false>;
+        if(sm > 48 * 1024) cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        k<<<gf_grid_blocks(c, s->mc.n, 3), GF_THREADS, sm, c->stream>>>(c->view, node, s->mc.amps, s->mc.ld, s->mc.n, s->mc.weights, s->mc.dtime, s->mc.sigma,
+                                                                         c->d_partials + (size_t)c->max_blocks * 2, c->d_ticket + 2, c->d_result + 1, gf_next_peer_view(c));
+        c->launches++;
+        GF_CUDA(cudaGetLastError());
+        if(c->nccl_comm && !gf_peer_active(c) && gf_allreduce_sum(c, c->d_result + 1, 1)) return 1;
+        return 0;
+    }
     if(s->td) {
         if(sm > 48 * 1024) cudaFuncSetAttribute(k_amp4_norm_td, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
         k_amp4_norm_td<<<blocks, GF_THREADS, sm, c->stream>>>(c->view, node, s->mc.amps, s->mc.ld, s->mc.n, s->mc.weights,
@@ -906,7 +959,7 @@ extern "C" int gf_amp4_norm_async(gf_ctx *c, int node) {
 extern "C" int gf_amp4_norm(gf_ctx *c, int node, double *out) {
     if(gf_amp4_norm_async(c, node)) return 1;
     gf_amp4_state *s = find_amp4(c, node, false);
-    int n = s && s->td ? 4 : 1;
+    int n = s && s->td && !s->mc.dtime ? 4 : 1;
     GF_CUDA(cudaMemcpyAsync(c->h_result + 1, c->d_result + 1, sizeof(double) * n, cudaMemcpyDeviceToHost, c->stream));
     GF_CUDA(cudaStreamSynchronize(c->stream));
     for(int k = 0; k < n; k++) out[k] = c->h_result[1 + k];

@@ -180,6 +180,7 @@ class Amp4BodyBase : public GooPdf {
     std::vector<int32_t> ampStarts, ampRecords;
     size_t nAmps{0};
     std::vector<std::vector<fptype>> normCols;
+    std::vector<fptype> normDtime, normSigma, normWeights; // weighted normalisation sample (Amp4Body_TD only)
     size_t MCevents{0};
     bool forceRedoIntegrals{true};
     bool cacheAllocated{false};
@@ -244,6 +245,40 @@ struct DecayInfo4t : public DecayInfo4 { // DalitzPlotHelpers.h:122-133
         , _SqWStoRSrate(SqWStoRSrate) {}
 };
 
+// ---- normalisation-event containers of Amp4Body_TD (detail/NormEvents_4Body_{Base,DeviceCached,HostCached,Weighted,WeightedDevice}.h)
+/// Upstream these own the MC columns and their cached lineshapes / spin factors, in device or host memory, and compute the
+/// integral batch by batch. Here they only describe a batch - the caches and the integral live in the engine, where every batch
+/// is resident in HBM (and sharded over ranks) - so DeviceCached and HostCached differ in name only.
+class NormEvents_4Body_Base {
+  public:
+    virtual ~NormEvents_4Body_Base() = default;
+    bool isWeighted() const { return !weights.empty(); }
+    std::vector<std::vector<fptype>> cols;     // m12, m34, cos12, cos34, phi (empty while a generated batch is still pending)
+    std::vector<fptype> dtime, sigma, weights; // weighted batches only
+    long seed{0};                              // pending generation: GENBOD candidates of this seed, accept-reject, compacted
+    unsigned int toGenerate{0};
+    std::vector<fptype> masses;
+};
+class NormEvents_4Body_DeviceCached : public NormEvents_4Body_Base { // NormEvents_4Body_DeviceCached.cu:17-40
+  public:
+    static std::vector<NormEvents_4Body_Base *> buildBatches(const std::vector<long> &normSeeds, unsigned int numNormEventsToGenPerBatch,
+                                                             const std::vector<fptype> &motherAndDaughterMasses);
+};
+class NormEvents_4Body_HostCached : public NormEvents_4Body_Base { // NormEvents_4Body_HostCached.cu:17-45
+  public:
+    static std::vector<NormEvents_4Body_Base *> buildBatches(const std::vector<long> &normSeeds, unsigned int numNormEventsToGenPerBatch,
+                                                             const std::vector<fptype> &motherAndDaughterMasses);
+};
+class NormEvents_4Body_Weighted : public NormEvents_4Body_Base { // NormEvents_4Body_Weighted.cu:19-40
+  public:
+    NormEvents_4Body_Weighted(std::vector<fptype> m12, std::vector<fptype> m34, std::vector<fptype> cos12, std::vector<fptype> cos34,
+                              std::vector<fptype> phi, std::vector<fptype> dtime, std::vector<fptype> sigma, std::vector<fptype> weights);
+};
+class NormEvents_4Body_WeightedDevice : public NormEvents_4Body_Weighted { // NormEvents_4Body_WeightedDevice.cu:19-36
+  public:
+    using NormEvents_4Body_Weighted::NormEvents_4Body_Weighted;
+};
+
 class Amp4Body_TD final : public Amp4BodyBase { // Amp4Body_TD.h:34-137
   public:
     /// normalisation events generated from one seed and kept in HBM (Amp4Body_TD.cu:292-307, NormEvents_4Body_DeviceCached)
@@ -253,16 +288,23 @@ class Amp4Body_TD final : public Amp4BodyBase { // Amp4Body_TD.h:34-137
     /// is generated with its own seed and the concatenation is kept in HBM (and sharded over ranks)
     Amp4Body_TD(std::string n, std::vector<Observable> observables, DecayInfo4t decay, MixingTimeResolution *Tres,
                 GooPdf *efficiency, Observable *mistag, const std::vector<long> &normSeeds, unsigned int numNormEventsToGenPerBatch);
+    /// caller-supplied batches (Amp4Body_TD.cu:309-325); takes ownership of the pointers as upstream does. Either all batches
+    /// are generated ones (DeviceCached / HostCached) or all are weighted.
+    Amp4Body_TD(std::string n, std::vector<Observable> observables, DecayInfo4t decay, MixingTimeResolution *Tres,
+                GooPdf *efficiency, Observable *mistag, const std::vector<NormEvents_4Body_Base *> &normEvents);
     fptype normalize() override;
     void setDataSize(unsigned int dataSize, unsigned int evtSize = 8) { setDataSizeCommon(dataSize, evtSize); }
     int getNumAccNormEvents() {
         materialiseNormEvents();
         return static_cast<int>(MCevents);
     }
+    /// sum of the batches' initial weights: the number of accepted events for generated batches; for weighted batches the sum
+    /// upstream forms with an INTEGER accumulator (thrust::reduce(..., 0), NormEvents_4Body_Weighted.cu:36), i.e. sum of floor(w)
     fptype getSumInitNormEventWeights() {
         materialiseNormEvents();
-        return static_cast<fptype>(MCevents);
+        return weightedNorm ? sumInitWeights : static_cast<fptype>(MCevents);
     }
+    bool hasWeightedNormEvents() const { return weightedNorm; }
     /// Amp4Body_TD.cu:825-1018: unweighted phase space, decay times under an exponential envelope, accept/reject flags.
     /// As upstream, the generated events REPLACE the PDF's dataset.
     GeneratedSignal GenerateSig(unsigned int numEvents, int seed = 0);
@@ -280,6 +322,8 @@ class Amp4Body_TD final : public Amp4BodyBase { // Amp4Body_TD.h:34-137
     std::vector<int32_t> flags;
     bool spinsCalculated{false};
     bool generation_no_norm{false};
+    bool weightedNorm{false};
+    fptype sumInitWeights{0};
     int generation_offset{0};
     fptype maxWeight{0};
     std::unique_ptr<UnbinnedDataSet> generated;

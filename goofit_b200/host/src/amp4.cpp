@@ -430,6 +430,9 @@ void Amp4BodyBase::materialiseNormEvents() {
 }
 void Amp4BodyBase::setNormEvents(const std::vector<std::vector<fptype>> &cols5) {
     normSpec.perBatch = 0; // an explicit sample replaces a pending generated one
+    normWeights.clear();
+    normDtime.clear();
+    normSigma.clear();
     if(cols5.size() != 5) throw GeneralError("setNormEvents needs five columns (m12, m34, cos12, cos34, phi)");
     for(auto &c : cols5)
         if(c.size() != cols5[0].size() || c.empty()) throw GeneralError("setNormEvents: columns must be non-empty and of equal length");
@@ -467,7 +470,10 @@ void Amp4BodyBase::ensureCache() {
     size_t per = MCevents / sh.size, first = per * sh.rank, count = sh.rank == sh.size - 1 ? MCevents - first : per;
     const double *cols[5];
     for(int k = 0; k < 5; k++) cols[k] = normCols[k].data() + first;
-    Engine::check(gf_amp4_set_mc(E.ctx(), nodeIdx, cols, count, nullptr, nullptr, nullptr), "gf_amp4_set_mc");
+    const bool wtd = !normWeights.empty();
+    Engine::check(gf_amp4_set_mc(E.ctx(), nodeIdx, cols, count, wtd ? normWeights.data() + first : nullptr, wtd ? normDtime.data() + first : nullptr,
+                                 wtd ? normSigma.data() + first : nullptr),
+                  "gf_amp4_set_mc");
     cacheAllocated     = true;
     forceRedoIntegrals = true;
     gramValid          = false;
@@ -635,6 +641,89 @@ Amp4Body_TD::Amp4Body_TD(std::string n, std::vector<Observable> observables, Dec
     efficiency = eff;
     init(observables, mistag, normSeeds, perBatch);
 }
+// ---- normalisation-event containers ----------------------------------------------------------------------------------------
+static std::vector<NormEvents_4Body_Base *> pendingBatches(const std::vector<long> &seeds, unsigned int perBatch, const std::vector<fptype> &masses,
+                                                            bool device) {
+    std::vector<NormEvents_4Body_Base *> ret;
+    for(long seed : seeds) {
+        NormEvents_4Body_Base *b = device ? static_cast<NormEvents_4Body_Base *>(new NormEvents_4Body_DeviceCached())
+                                          : static_cast<NormEvents_4Body_Base *>(new NormEvents_4Body_HostCached());
+        b->seed       = seed;
+        b->toGenerate = perBatch;
+        b->masses     = masses;
+        ret.push_back(b);
+    }
+    return ret;
+}
+std::vector<NormEvents_4Body_Base *> NormEvents_4Body_DeviceCached::buildBatches(const std::vector<long> &seeds, unsigned int perBatch,
+                                                                                 const std::vector<fptype> &masses) {
+    return pendingBatches(seeds, perBatch, masses, true);
+}
+std::vector<NormEvents_4Body_Base *> NormEvents_4Body_HostCached::buildBatches(const std::vector<long> &seeds, unsigned int perBatch,
+                                                                               const std::vector<fptype> &masses) {
+    return pendingBatches(seeds, perBatch, masses, false);
+}
+NormEvents_4Body_Weighted::NormEvents_4Body_Weighted(std::vector<fptype> m12, std::vector<fptype> m34, std::vector<fptype> cos12,
+                                                     std::vector<fptype> cos34, std::vector<fptype> phi, std::vector<fptype> t,
+                                                     std::vector<fptype> s, std::vector<fptype> w) {
+    size_t n = w.size();
+    if(n == 0 || m12.size() != n || m34.size() != n || cos12.size() != n || cos34.size() != n || phi.size() != n || t.size() != n || s.size() != n)
+        throw GeneralError("NormEvents_4Body_Weighted: eight non-empty columns of equal length are needed");
+    cols    = {std::move(m12), std::move(m34), std::move(cos12), std::move(cos34), std::move(phi)};
+    dtime   = std::move(t);
+    sigma   = std::move(s);
+    weights = std::move(w);
+}
+Amp4Body_TD::Amp4Body_TD(std::string n, std::vector<Observable> observables, DecayInfo4t decay, MixingTimeResolution *Tres, GooPdf *eff,
+                         Observable *mistag, const std::vector<NormEvents_4Body_Base *> &normEvents)
+    : Amp4BodyBase("Amp4Body_TD", n)
+    , decayInfo(decay)
+    , resolution(Tres) {
+    efficiency = eff;
+    std::vector<std::unique_ptr<NormEvents_4Body_Base>> own;
+    for(auto *b : normEvents) own.emplace_back(b);
+    if(own.empty()) throw GeneralError("Amp4Body_TD {}: no normalisation events", n);
+    bool anyW = false, allW = true;
+    for(auto &b : own) {
+        if(!b) throw GeneralError("Amp4Body_TD {}: null normalisation-event batch", n);
+        anyW = anyW || b->isWeighted();
+        allW = allW && b->isWeighted();
+    }
+    if(anyW && !allW) throw GeneralError("Amp4Body_TD {}: weighted and unweighted normalisation batches cannot be mixed", n);
+    std::vector<long> seeds;
+    unsigned int perBatch = 0;
+    if(!anyW) {
+        for(auto &b : own) {
+            if(b->toGenerate == 0) throw GeneralError("Amp4Body_TD {}: an unweighted batch must come from buildBatches()", n);
+            if(perBatch && b->toGenerate != perBatch) throw GeneralError("Amp4Body_TD {}: batches of different sizes", n);
+            perBatch = b->toGenerate;
+            seeds.push_back(b->seed);
+        }
+    }
+    init(observables, mistag, seeds, perBatch);
+    if(anyW) {
+        std::vector<std::vector<fptype>> all(5);
+        sumInitWeights = 0;
+        for(auto &b : own) {
+            for(int k = 0; k < 5; k++) all[k].insert(all[k].end(), b->cols[k].begin(), b->cols[k].end());
+            normDtime.insert(normDtime.end(), b->dtime.begin(), b->dtime.end());
+            normSigma.insert(normSigma.end(), b->sigma.begin(), b->sigma.end());
+            normWeights.insert(normWeights.end(), b->weights.begin(), b->weights.end());
+            int acc = 0; // thrust::reduce(thrust::host, weights.begin(), weights.end(), 0): the accumulator has the type of the init value
+            for(fptype w : b->weights) acc = acc + static_cast<int>(w);
+            sumInitWeights += acc;
+        }
+        auto wkeep = normWeights; // setNormEvents describes an unweighted sample: keep the weighted columns across it
+        auto tkeep = normDtime, skeep = normSigma;
+        setNormEvents(all);
+        normWeights  = wkeep;
+        normDtime    = tkeep;
+        normSigma    = skeep;
+        weightedNorm = true;
+        normMode     = NormMode::PerEvent; // the integrand depends on tau, x, y event by event: there is no Gram form
+    }
+}
+
 void Amp4Body_TD::init(std::vector<Observable> &observables, Observable *mistag, const std::vector<long> &seeds, unsigned int perBatch) {
     const std::string n = getName();
     // m12, m34, cos12, cos34, phi, eventnumber, dtime, sigmat — in this order (Amp4Body_TD.cu:327-330)
@@ -724,6 +813,14 @@ fptype Amp4Body_TD::normalize() { // Amp4Body_TD.cu:744-799
         if(any) Engine::check(gf_amp4_cache_data(E.ctx(), nodeIdx, spins, lsRedo.data(), ampRedo.data()), "gf_amp4_cache_data");
         setNormalization(1.0);
         return 1.0;
+    }
+    if(weightedNorm) { // NormEvents_4Body_Weighted::computeNorm_TD: sum_m w_m pdf(x_m, t_m, sigma_m) / sum of the initial weights
+        if(any) Engine::check(gf_amp4_cache(E.ctx(), nodeIdx, spins, lsRedo.data(), ampRedo.data()), "gf_amp4_cache");
+        double sum = 0;
+        Engine::check(gf_amp4_norm(E.ctx(), nodeIdx, &sum), "gf_amp4_norm");
+        fptype ret = sum / getSumInitNormEventWeights();
+        setNormalization(1.0 / ret);
+        return ret;
     }
     refreshCaches(any, spins, lsRedo, ampRedo);
     double sums[4] = {0, 0, 0, 0};

@@ -149,7 +149,33 @@ void init_physics4(py::module &m) {
         .def_readonly("_xmixing", &DecayInfo4t::_xmixing)
         .def_readonly("_ymixing", &DecayInfo4t::_ymixing)
         .def_readonly("_SqWStoRSrate", &DecayInfo4t::_SqWStoRSrate);
+    // normalisation-event batches (python/PDFs/physics/detail/NormEvents_4Body_*.cpp upstream)
+    py::class_<NormEvents_4Body_Base>(m, "NormEvents_4Body_Base")
+        .def("isWeighted", &NormEvents_4Body_Base::isWeighted);
+    py::class_<NormEvents_4Body_DeviceCached, NormEvents_4Body_Base>(m, "NormEvents_4Body_DeviceCached")
+        .def_static("buildBatches", &NormEvents_4Body_DeviceCached::buildBatches, "normSeeds"_a, "numNormEventsToGenPerBatch"_a,
+                    "motherAndDaughterMasses"_a, py::return_value_policy::take_ownership);
+    py::class_<NormEvents_4Body_HostCached, NormEvents_4Body_Base>(m, "NormEvents_4Body_HostCached")
+        .def_static("buildBatches", &NormEvents_4Body_HostCached::buildBatches, "normSeeds"_a, "numNormEventsToGenPerBatch"_a,
+                    "motherAndDaughterMasses"_a, py::return_value_policy::take_ownership);
+    py::class_<NormEvents_4Body_Weighted, NormEvents_4Body_Base>(m, "NormEvents_4Body_Weighted")
+        .def(py::init<std::vector<fptype>, std::vector<fptype>, std::vector<fptype>, std::vector<fptype>, std::vector<fptype>,
+                      std::vector<fptype>, std::vector<fptype>, std::vector<fptype>>(),
+             "m12"_a, "m34"_a, "cos12"_a, "cos34"_a, "phi"_a, "dtime"_a, "sigma"_a, "weights"_a);
+    py::class_<NormEvents_4Body_WeightedDevice, NormEvents_4Body_Weighted>(m, "NormEvents_4Body_WeightedDevice")
+        .def(py::init<std::vector<fptype>, std::vector<fptype>, std::vector<fptype>, std::vector<fptype>, std::vector<fptype>,
+                      std::vector<fptype>, std::vector<fptype>, std::vector<fptype>>(),
+             "m12"_a, "m34"_a, "cos12"_a, "cos34"_a, "phi"_a, "dtime"_a, "sigma"_a, "weights"_a);
     py::class_<Amp4Body_TD, Amp4BodyBase>(m, "Amp4Body_TD")
+        .def(py::init([](std::string n, std::vector<Observable> observables, DecayInfo4t decay, MixingTimeResolution *r, GooPdf *eff,
+                         Observable *mistag, std::vector<NormEvents_4Body_Base *> normEvents) {
+                 std::vector<NormEvents_4Body_Base *> copies; // the C++ constructor takes ownership; Python keeps its own objects
+                 for(auto *b : normEvents) copies.push_back(new NormEvents_4Body_Base(*b));
+                 return new Amp4Body_TD(n, observables, decay, r, eff, mistag, copies);
+             }),
+             "n"_a, "observables"_a, "decay"_a, "r"_a, "eff"_a, "mistag"_a, "normEvents"_a, py::keep_alive<1, 4>(), py::keep_alive<1, 5>(),
+             py::keep_alive<1, 6>(), py::keep_alive<1, 7>())
+        .def("hasWeightedNormEvents", &Amp4Body_TD::hasWeightedNormEvents)
         .def(py::init<std::string, std::vector<Observable>, DecayInfo4t, MixingTimeResolution *, GooPdf *, Observable *, long,
                       unsigned int>(),
              "n"_a, "observables"_a, "decay"_a, "r"_a, "eff"_a, "mistag"_a, "normSeed"_a, "MCeventsNorm"_a = 5000000,

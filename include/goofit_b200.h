@@ -158,7 +158,9 @@ int gf_amp4_set_mc(gf_ctx *, int node, const double *const *mc_cols5, size_t n_m
 int gf_amp4_cache(gf_ctx *, int node, int redo_spins, const uint8_t *ls_redo, const uint8_t *amp_redo);
 /* sum over the (local shard of the) MC sample, all-reduced when a communicator is attached.
  * Amp4Body: out[0] = sum |sum_a c_a A_a|^2 (detail/NormIntegrator.cu:15-68).
- * Amp4Body_TD: out[0..3] = sum |A|^2, sum |B|^2, sum Re(A B*), sum Im(A B*) (detail/NormIntegrator_TD.cu:15-99). */
+ * Amp4Body_TD: out[0..3] = sum |A|^2, sum |B|^2, sum Re(A B*), sum Im(A B*) (detail/NormIntegrator_TD.cu:15-99).
+ * Amp4Body_TD with a WEIGHTED sample (gf_amp4_set_mc given weights, dtime and sigma): out[0] = sum_m w_m pdf(x_m, t_m, sigma_m), the
+ * time-dependent PDF at every MC event's own decay time (detail/NormIntegrator_TD_Weighted.cu:15-122). */
 int gf_amp4_norm(gf_ctx *, int node, double *out);
 int gf_amp4_norm_async(gf_ctx *, int node);
 /* Hermitian Gram matrix of the cached MC amplitudes, G[(a*nAmp+b)*2+{re,im}] = sum_m w_m A_a(m) conj(A_b(m)), summed over

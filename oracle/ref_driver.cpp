@@ -27,6 +27,7 @@
 #define protected public
 #include <goofit/PDFs/physics/Amp4Body.h>
 #include <goofit/PDFs/physics/detail/NormEvents_4Body_DeviceCached.h>
+#include <goofit/PDFs/physics/detail/NormEvents_4Body_Weighted.h>
 #include <goofit/PDFs/physics/Amp4Body_TD.h>
 #undef private
 #undef protected
@@ -916,7 +917,8 @@ struct TDModel {
 };
 // shared: 0 = A and B lists hold distinct Amplitude objects (flags 0/1, as TDDP4.cu); 1 = the P-wave amplitude object is in
 // both lists (flag 2: one cached amplitude, two coefficients, Amp4Body_TD.cu:373-381)
-static TDModel *make_tddp4(int three_gauss, unsigned int mcToGen, bool float_ls, bool float_mix, int shared = 0) {
+static TDModel *make_tddp4(int three_gauss, unsigned int mcToGen, bool float_ls, bool float_mix, int shared = 0,
+                           const std::vector<NormEvents_4Body_Base *> *normEvents = nullptr) {
     auto *M = new TDModel();
     const fptype mD0 = 1.8645, piP = 0.13957018, Km = 0.493677;
     Variable tau = float_mix ? Variable("tau", 0.4101, 0.001, 0.100, 0.900) : Variable("tau", 0.4101);
@@ -970,7 +972,8 @@ static TDModel *make_tddp4(int three_gauss, unsigned int mcToGen, bool float_ls,
         M->res = new TruthResolution();
     Variable one("constantOne", 1), zero("constantZero", 0);
     M->eff = new PolynomialPdf("constantEff", M->obs(), std::vector<Variable>{one}, std::vector<Variable>{zero, zero}, 0);
-    M->dp  = new Amp4Body_TD("test", M->obs(), DI, M->res, M->eff, nullptr, (long)7, mcToGen);
+    M->dp  = normEvents ? new Amp4Body_TD("test", M->obs(), DI, M->res, M->eff, nullptr, *normEvents)
+                        : new Amp4Body_TD("test", M->obs(), DI, M->res, M->eff, nullptr, (long)7, mcToGen);
     Variable constant("constant", 0.1), constant2("constant2", 1.0);
     M->backgr = new PolynomialPdf("backgr", M->m12, {constant});
     M->signal = new AddPdf("signal", constant2, M->dp, M->backgr);
@@ -1053,6 +1056,51 @@ static void td_one(const std::string &tag, int three_gauss, int shared) {
     sig->updateVariable(M->lsvars[2], 0.8975); sig->updateParameters();
     put(tag + ".nll_kstar_moved", sig->calculateNLL());
     put(tag + ".integral_kstar_moved", 1.0 / dp->getNormalization());
+}
+// Weighted normalisation events (detail/NormEvents_4Body_Weighted.cu, NormIntegrator_TD_Weighted.cu): the MC sample of the other
+// td cases, each event with its own decay time, resolution and weight; the integral is sum_m w_m pdf(x_m, t_m) / sum of weights.
+static void td_weighted(const std::string &tag, int three_gauss) {
+    TDModel *M0 = make_tddp4(0, 16000, true, true, 0);
+    auto *ne0 = dynamic_cast<NormEvents_4Body_DeviceCached *>(M0->dp->_normEvents[0].get());
+    auto c0 = host_copy(ne0->_norm_M12_d), c1 = host_copy(ne0->_norm_M34_d), c2 = host_copy(ne0->_norm_CosTheta12_d),
+         c3 = host_copy(ne0->_norm_CosTheta34_d), c4 = host_copy(ne0->_norm_phi_d);
+    size_t n = c0.size();
+    std::mt19937_64 gen(20261105);
+    std::uniform_real_distribution<double> u(0, 1);
+    std::vector<double> t(n), sg(n), w(n);
+    for(size_t i = 0; i < n; i++) {
+        do t[i] = -0.4101 * std::log(1.0 - u(gen)); while(t[i] >= 10.0);
+        sg[i] = 0.02 + 0.06 * u(gen);
+        w[i]  = 1.0 + 2.0 * u(gen); // the reference sums these into an INT accumulator (thrust::reduce(..., 0)): see sum_init_weights
+    }
+    if(tag == "tddp4w") {
+        save_npy("tddp4w.mc_dtime", t); save_npy("tddp4w.mc_sigma", sg); save_npy("tddp4w.mc_weight", w);
+    }
+    auto H = [](const std::vector<double> &v) { return mcbooster::RealVector_h(v.begin(), v.end()); };
+    std::vector<NormEvents_4Body_Base *> ne = {new NormEvents_4Body_Weighted(H(c0), H(c1), H(c2), H(c3), H(c4), H(t), H(sg), H(w))};
+    TDModel *M = make_tddp4(three_gauss, 0, true, true, 0, &ne);
+    UnbinnedDataSet d(M->obs());
+    fill_td_phsp(*M, d, 400, 31337); // the data of the other td cases
+    GooPdf *sig = M->signal;
+    Amp4Body_TD *dp = M->dp;
+    sig->setData(&d);
+    dp->setDataSize(d.getNumEvents(), 8);
+    put(tag + ".sum_init_weights", dp->getSumInitNormEventWeights());
+    put(tag + ".nll", sig->calculateNLL());
+    put(tag + ".integral", 1.0 / dp->getNormalization());
+    for(auto &v : M->lsvars) v.setChanged(false);
+    sig->updateVariable(M->mix[0], 0.4153); sig->updateVariable(M->mix[1], 0.0123); sig->updateVariable(M->mix[2], -0.0071);
+    sig->updateParameters();
+    put(tag + ".nll_mix_moved", sig->calculateNLL());
+    put(tag + ".integral_mix_moved", 1.0 / dp->getNormalization());
+    M->lsvars[2].setChanged(true);
+    sig->updateVariable(M->lsvars[2], 0.8975); sig->updateParameters();
+    put(tag + ".nll_kstar_moved", sig->calculateNLL());
+    put(tag + ".integral_kstar_moved", 1.0 / dp->getNormalization());
+}
+static void case_tddp4w() {
+    td_weighted("tddp4w", 0);
+    td_weighted("tddp4wg3", 1);
 }
 static void case_tddp4() {
     td_one("tddp4", 0, 0);
@@ -1449,6 +1497,7 @@ int main(int argc, char **argv) {
             if(only == "all" || only == "dp4") case_dp4();
             if(only == "all" || only == "dp4fit") case_dp4_fit();
             if(only == "all" || only == "tddp4") case_tddp4();
+            if(only == "all" || only == "tddp4w") case_tddp4w();
             if(only == "all" || only == "tddp4fit") case_tddp4_fit();
             std::ofstream f(g_out + "/manifest" + (only == "all" ? "" : "_" + only) + ".json");
             f << "{\n" << g_manifest.str() << "\n}\n";

@@ -320,7 +320,7 @@ class TDDP4:
     each of A and B, TruthResolution or ThreeGaussResolution, AddPdf(1.0; Amp4Body_TD, flat bkg) — the tree
     oracle/ref_driver.cpp make_tddp4() builds with the reference's classes."""
 
-    def __init__(self, three_gauss=False, float_ls=False, float_mix=True, shared=False, mc_to_gen=0, norm_seed=7):
+    def __init__(self, three_gauss=False, float_ls=False, float_mix=True, shared=False, mc_to_gen=0, norm_seed=7, norm_events=None):
         k = self.keep = Keep()
         O, V = gf.Observable, gf.Variable
         self.m12, self.m34 = O("m12", 0, 3), O("m34", 0, 3)
@@ -373,7 +373,10 @@ class TDDP4:
             self.res = k(gf.TruthResolution())
         self.observables = [self.m12, self.m34, self.cos12, self.cos34, self.phi, self.evt, self.dtime, self.sigmat]
         self.eff = k(gf.PolynomialPdf("constantEff", self.observables, [V("constantOne", 1)], [V("constantZero", 0)] * 2, 0))
-        self.dp = gf.Amp4Body_TD("test", self.observables, info, self.res, self.eff, None, norm_seed, mc_to_gen)
+        if norm_events is not None:  # caller-supplied batches (e.g. weighted normalisation events)
+            self.dp = gf.Amp4Body_TD("test", self.observables, info, self.res, self.eff, None, norm_events)
+        else:
+            self.dp = gf.Amp4Body_TD("test", self.observables, info, self.res, self.eff, None, norm_seed, mc_to_gen)
         self.backgr = k(gf.PolynomialPdf("backgr", self.m12, [V("constant", 0.1)]))
         self.signal = gf.AddPdf("signal", V("constant2", 1.0), self.dp, self.backgr)
 

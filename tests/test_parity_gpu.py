@@ -503,6 +503,41 @@ def test_tddp4_values(golden, tag, three_gauss, shared, mode):
         kstar_move_fused_vs_separate(sig, dp, M.lsvars[2], golden[tag + ".nll_kstar_moved"], golden[tag + ".integral_kstar_moved"], RTOL_INT)
 
 
+@pytest.mark.parametrize("tag,three_gauss", [("tddp4w", False), ("tddp4wg3", True)])
+def test_tddp4_weighted_norm_events(golden, tag, three_gauss):
+    """NormEvents_4Body_Weighted (detail/NormEvents_4Body_Weighted.cu, NormIntegrator_TD_Weighted.cu:15-122): every MC event has
+    its own decay time, resolution and weight; the integral is sum_m w_m pdf(x_m, t_m) over the sum of the initial weights -
+    which upstream forms with an integer accumulator (sum of floor(w)), reproduced and pinned here."""
+    from models import TDDP4
+    mc = [golden.arr("tddp4.mc_" + n) for n in TD_MC]
+    t, sg, w = golden.arr("tddp4w.mc_dtime"), golden.arr("tddp4w.mc_sigma"), golden.arr("tddp4w.mc_weight")
+    ne = [gf.NormEvents_4Body_Weighted(*mc, t, sg, w)]
+    M = TDDP4(three_gauss=three_gauss, float_ls=True, float_mix=True, norm_events=ne)
+    d = M.dataset([golden.arr("tddp4." + n) for n in TD_DATA])
+    sig, dp = M.signal, M.dp
+    assert dp.hasWeightedNormEvents() and dp.getNumAccNormEvents() == len(w)
+    assert dp.getSumInitNormEventWeights() == golden[tag + ".sum_init_weights"] == np.floor(w).sum()
+    sig.setData(d)
+    dp.setDataSize(len(d), 8)
+    assert rel(sig.calculateNLL(), golden[tag + ".nll"]) < RTOL_NLL
+    assert rel(1.0 / dp.getNormalization(), golden[tag + ".integral"]) < 1e-11
+    for v in M.lsvars:
+        v.changed = False
+    sig.updateVariable(M.mix[0], 0.4153)
+    sig.updateVariable(M.mix[1], 0.0123)
+    sig.updateVariable(M.mix[2], -0.0071)
+    sig.updateParameters()
+    before = gf.launch_count()
+    assert rel(sig.calculateNLL(), golden[tag + ".nll_mix_moved"]) < RTOL_NLL
+    assert rel(1.0 / dp.getNormalization(), golden[tag + ".integral_mix_moved"]) < 1e-11
+    assert gf.launch_count() - before == 2  # the weighted MC integral (it depends on tau, x, y event by event) and the NLL
+    M.lsvars[2].changed = True
+    sig.updateVariable(M.lsvars[2], 0.8975)
+    sig.updateParameters()
+    assert rel(sig.calculateNLL(), golden[tag + ".nll_kstar_moved"]) < RTOL_NLL
+    assert rel(1.0 / dp.getNormalization(), golden[tag + ".integral_kstar_moved"]) < 1e-11
+
+
 def test_tddp4_fit_matches_reference(golden):
     from models import TDDP4
     M = TDDP4(three_gauss=False, float_ls=False, float_mix=True)
