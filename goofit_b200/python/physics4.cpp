@@ -210,13 +210,21 @@ void init_physics4(py::module &m) {
             std::vector<std::vector<fptype>> v5;
             devicePhaseSpace(masses, n, seed, offset, &G.particles, G.weights, masses.size() == 5 ? &v5 : nullptr);
             G.flags.assign(n, false);
-            py::tuple t = generated_to_numpy(G, (int)masses.size() - 1);
+            py::tuple t = generated_to_numpy(G, 4);
             py::array_t<fptype> r({(size_t)(v5.empty() ? 0 : 5), n});
             for(size_t k = 0; k < v5.size(); k++) std::copy(v5[k].begin(), v5[k].end(), r.mutable_data(k, 0));
             return py::make_tuple(t[0], t[2], r);
         },
         "mother_and_daughter_masses"_a, "nEvents"_a, "seed"_a = 0, "offset"_a = 0,
         "the stream of generatePhaseSpaceParticles generated on the GPU: (particles[nd, N, 4], weights[N], dim5[5, N] for four daughters)");
+    m.def(
+        "counterUniform",
+        [](unsigned long seed, py::array_t<long long, py::array::c_style | py::array::forcecast> events, unsigned long stream) {
+            py::array_t<fptype> out(events.size());
+            for(py::ssize_t i = 0; i < events.size(); i++) out.mutable_data()[i] = detail::counterUniform(seed, (size_t)events.data()[i], stream);
+            return out;
+        },
+        "seed"_a, "events"_a, "stream"_a, "uniform numbers in (0, 1) of the counter-based generator (stream `stream` of each event index)");
     m.def("generatePhaseSpace5",
           [](std::vector<fptype> masses, size_t n, unsigned long seed) {
               std::vector<fptype> w;
