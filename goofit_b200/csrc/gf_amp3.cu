@@ -46,7 +46,10 @@ __device__ inline gf_decay3 gf_load_decay3(const double *c) {
     return D;
 }
 
-__global__ void __launch_bounds__(GF_THREADS, 2) // measured: 2 blocks/SM at 128 registers beats 3 at 80 (spills)
+#ifndef GF_WAVES_BLOCKS
+#define GF_WAVES_BLOCKS 2 // measured: 2 blocks/SM at 128 registers beats 3 at 80 (spills)
+#endif
+__global__ void __launch_bounds__(GF_THREADS, GF_WAVES_BLOCKS)
     k_amp3_waves(const gf_dev_view V, int node, unsigned long long mask, double2 *waves, long ld) {
     extern __shared__ __align__(16) unsigned char smem[];
     gf_sprog P = gf_stage_program(V, smem);
@@ -219,7 +222,7 @@ extern "C" int gf_amp3_cache_waves(gf_ctx *c, int node, const uint8_t *redo_mask
     cudaSetDevice(c->device);
     size_t sm = gf_prog_smem(c);
     if(sm > 48 * 1024) cudaFuncSetAttribute(k_amp3_waves, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-    int blocks = gf_grid_blocks(c, s->n_events, 2);
+    int blocks = gf_grid_blocks(c, s->n_events, GF_WAVES_BLOCKS);
     k_amp3_waves<<<blocks, GF_THREADS, sm, c->stream>>>(c->view, node, mask, s->d_waves, s->ld);
     c->launches++;
     GF_CUDA(cudaGetLastError());

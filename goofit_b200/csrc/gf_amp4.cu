@@ -975,7 +975,7 @@ extern "C" int gf_amp4_gram(gf_ctx *c, int node, double *G_re_im) {
     if(!s->mc.amps) return gf_fail("gf_amp4_gram: no MC normalisation sample (gf_amp4_set_mc)");
     if(!G_re_im) return gf_fail("gf_amp4_gram: null output");
     cudaSetDevice(c->device);
-    const int T = GF_GRAM_T, nT = (s->nAmp + T - 1) / T, nTiles = nT * (nT + 1) / 2, per = 2 * T * T;
+    const int T = GF_GRAM_T, nT = (s->nAmp + T - 1) / T, per = 2 * T * T;
     const int blocks = gf_grid_blocks(c, s->mc.n, 2);
     if(!s->d_gram || s->gram_blocks < blocks) {
         cudaFree(s->d_gram); cudaFree(s->d_gram_partials); cudaFree(s->d_gram_ticket);
