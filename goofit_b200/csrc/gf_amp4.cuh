@@ -5,8 +5,9 @@
 //   bugg_MINT / bugg_MINT3    src/PDFs/physics/lineshapes/Bugg.cu:11-128
 //   spin factors              src/PDFs/physics/SpinFactors.cu:83-568, detail/SpinHelper.h
 #pragma once
+#include "gf_kmatrix.cuh"
 
-enum gf_ls_kind { GF_LS_RBW = 0, GF_LS_SBW, GF_LS_LASS, GF_LS_BUGG, GF_LS_BUGG3, GF_LS_ONE, GF_LS_NONRES, GF_LS_FLATTE, GF_LS_GLASS, GF_LS_FOCUS };
+enum gf_ls_kind { GF_LS_RBW = 0, GF_LS_SBW, GF_LS_LASS, GF_LS_BUGG, GF_LS_BUGG3, GF_LS_ONE, GF_LS_NONRES, GF_LS_FLATTE, GF_LS_GLASS, GF_LS_FOCUS, GF_LS_KMATRIX, GF_LS_GSPLINE };
 // same order as the reference's SF_4Body enum (SpinFactors.h:18-35)
 enum gf_sf_kind {
     GF_SF_DtoPP1_PtoSP2_StoP3P4 = 0, GF_SF_DtoPP1_PtoVP2_VtoP3P4, GF_SF_DtoV1V2_S, GF_SF_DtoV1V2_P, GF_SF_DtoV1V2_D,
@@ -416,6 +417,36 @@ __device__ inline gf_cplx gf_lineshape_inv(int kind, const double *p, const doub
     default: return gf_ls_lass_pt(Mpair, p[0], p[1], (int)c[1], (int)c[2], c[3], I);
     }
 }
+// GSpline.cu:31-95 (AmpGen's GSpline.EFF): a Breit-Wigner whose running width follows a cubic spline in s.
+// consts = Mpair, L, FF, radius, s_min, s_max, nBins, n, then the n constants the constructor registers after them (the
+// curvature terms). As upstream, getSpline reads the knot values from those nBins constants and the curvatures from the nBins AFTER them;
+// upstream registers only nBins constants there, so its second read runs past its own block into whatever follows in the flat
+// constant table. Here a read past the record's n constants yields 0.
+__device__ inline double gf_gspline_at(double x, bool continued, const double *c) {
+    const double s_min = c[4], s_max = c[5];
+    const int nBins = (int)c[6], n = (int)c[7], start = 8;
+    auto C = [&](int k) { return (k >= start && k < start + n) ? c[k] : 0.0; };
+    if(x <= s_min) return continued ? C(start) : 0;
+    if(x >= s_max) return continued ? C(start + nBins - 1) : 0;
+    const double spacing = (s_max - s_min) / (nBins - 1.);
+    const double dx = fmod((x - s_min), spacing);
+    const int bin = (int)((x - s_min) / spacing);
+    const double m_x_0 = C(start + bin), m_x_1 = C(start + bin + 1), m_xf_0 = C(start + bin + nBins), m_xf_1 = C(start + bin + nBins + 1);
+    return m_x_0 + dx * ((m_x_1 - m_x_0) / spacing - (m_xf_1 + 2 * m_xf_0) * spacing / 6) + dx * dx * m_xf_0 + dx * dx * dx * (m_xf_1 - m_xf_0) / (6 * spacing);
+}
+__device__ inline gf_cplx gf_ls_gspline(double Mpair, double m1, double m2, const double *p, const double *c) {
+    const double mass = p[0], width = p[1], radius = c[3];
+    const double s = Mpair * Mpair, s1 = m1 * m1, s2 = m2 * m2;
+    const double q2 = fabs(s / 4. - (s1 + s2) / 2. + (s1 - s2) * (s1 - s2) / (4 * s));
+    const double BF = exp(-q2 * (radius * radius) / 2);
+    const double width_shape = width * gf_gspline_at(s, true, c);
+    const double width_norm = width * gf_gspline_at(mass * mass, false, c);
+    const double gamma = mass * sqrt(mass * mass + width * width);
+    const double k = 2 * sqrt(2.) * mass * width * gamma / (M_PI * sqrt(mass * mass + gamma));
+    const double norm = sqrt(k) * BF;
+    const double running_width = width_norm == 0 ? 0 : width * width_shape / width_norm;
+    return norm / gf_c(mass * mass - s, -mass * running_width);
+}
 // dispatch on the lineshape record: params mass,width ; consts Mpair,L,FF,radius ; ints[0] kind
 __device__ inline gf_cplx gf_lineshape(int kind, const double *p, const double *c, double Mpair, double d1, double d2) {
     switch(kind) {
@@ -428,6 +459,11 @@ __device__ inline gf_cplx gf_lineshape(int kind, const double *p, const double *
     case GF_LS_FLATTE: return gf_ls_flatte(Mpair, d1, d2, p[0], (int)c[1], c[3]);
     case GF_LS_GLASS: return gf_ls_glass(Mpair, d1, d2, p, (int)c[1], c[3]);
     case GF_LS_FOCUS: return gf_ls_focus(Mpair, (int)c[4]);
+    case GF_LS_KMATRIX: { // lineshapes/kMatrix.cu:18-119
+        const gf_kc r = gf_kmatrix(Mpair * Mpair, p);
+        return gf_c(r.re, r.im);
+    }
+    case GF_LS_GSPLINE: return gf_ls_gspline(Mpair, d1, d2, p, c);
     default: return gf_c(1.0, 0.0);
     }
 }

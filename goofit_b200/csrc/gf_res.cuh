@@ -2,6 +2,7 @@
 // Arithmetic follows /root/reference/src/PDFs/physics/resonances/{Resonance,RBW,GS,NonRes,Gauss}.cu
 // operation for operation (same association order) so cached waves agree to the last few ulp.
 #pragma once
+#include "gf_kmatrix.cuh"
 
 struct gf_decay3 { // Amp3Body node consts: Amp3Body.cu:144-149
     double M, d1, d2, d3, rad, mrad;
@@ -318,6 +319,11 @@ __device__ inline double2 gf_resonance(const gf_node &nd, const double *params, 
     case GF_OP_RES_FLATTE: return gf_res_flatte(p, (int)c[0], (int)c[1], m12, m13, m23);
     case GF_OP_RES_SPLINE: return gf_res_spline(p, c, m12, m13, m23);
     case GF_OP_RES_RHOOMEGA: return gf_res_rhoomega(p, (int)c[0], (int)c[1], c[2] != 0.0, D, m12, m13, m23);
+    case GF_OP_RES_KMATRIX: { // resonances/kMatrix.cu:19-121: s is the pair's squared mass
+        const int cyc = (int)c[0];
+        const gf_kc r = gf_kmatrix(cyc == GF_PAIR_12 ? m12 : (cyc == GF_PAIR_13 ? m13 : m23), p);
+        return make_double2(r.re, r.im);
+    }
     default: return make_double2(0.0, 0.0);
     }
 }

@@ -65,6 +65,12 @@ class FLATTE : public ResonancePdf { // resonances/FLATTE.cu:80-97
   public:
     FLATTE(std::string name, Variable ar, Variable ai, Variable mean, Variable g1, Variable rg2og1, unsigned int cyc, bool symmDP);
 };
+class kMatrix : public ResonancePdf { // resonances/kMatrix.cu:127-177: pi pi S-wave K-matrix, five channels and five poles
+  public:
+    kMatrix(std::string name, Variable a_r, Variable a_i, Variable sA0, Variable sA, Variable s0_prod, Variable s0_scatt,
+            std::vector<Variable> beta_r, std::vector<Variable> beta_i, std::vector<Variable> f_prod_r, std::vector<Variable> f_prod_i,
+            std::vector<Variable> fscat, std::vector<Variable> poles, unsigned int L, unsigned int Mpair);
+};
 class Spline : public ResonancePdf { // resonances/Spline.cu:91-134
   public:
     Spline(std::string name, Variable ar, Variable ai, std::vector<fptype> &HH_bin_limits, std::vector<Variable> &pwa_coefs_reals,

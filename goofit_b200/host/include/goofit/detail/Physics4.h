@@ -60,6 +60,22 @@ class FOCUS final : public Lineshape { // lineshapes/FOCUS.cu:80-95
     FOCUS(std::string name, Mod mod, Variable mass, Variable width, unsigned int L, unsigned int Mpair, FF FormFac = FF::BL_Prime,
           fptype radius = 1.5);
 };
+/// lineshapes/kMatrix.cu:121-171: the pi pi S-wave K-matrix (five channels, five poles); a_r, a_i are ignored as upstream
+class kMatrix final : public Lineshape {
+  public:
+    kMatrix(std::string name, Variable a_r, Variable a_i, Variable sA0, Variable sA, Variable s0_prod, Variable s0_scatt,
+            std::vector<Variable> beta_r, std::vector<Variable> beta_i, std::vector<Variable> f_prod_r, std::vector<Variable> f_prod_i,
+            std::vector<Variable> fscat, std::vector<Variable> poles, unsigned int L, unsigned int Mpair, FF FormFac = FF::BL_Prime,
+            fptype radius = 1.5);
+};
+/// lineshapes/GSpline.cu:126-161. spline_t = (min, max, bins) as in lineshapes/GSpline.h
+using spline_t = std::tuple<fptype, fptype, unsigned int>;
+class GSpline final : public Lineshape {
+  public:
+    GSpline(std::string name, Variable mass, Variable width, unsigned int L, unsigned int Mpair, FF FormFac, fptype radius,
+            std::vector<Variable> AdditionalVars, spline_t SplineInfo);
+    static std::vector<fptype> curvatures(const std::vector<Variable> &vars, const spline_t &info);
+};
 } // namespace Lineshapes
 
 enum class SF_4Body { // SpinFactors.h:18-35

@@ -67,6 +67,27 @@ LASS::LASS(std::string name, Variable ar, Variable ai, Variable mass, Variable w
     registerConstant(norm);
     registerFunction("ptr_to_LASS", GF_OP_RES_LASS);
 }
+kMatrix::kMatrix(std::string name, Variable ar, Variable ai, Variable sA0, Variable sA, Variable s0_prod, Variable s0_scatt,
+                 std::vector<Variable> beta_r, std::vector<Variable> beta_i, std::vector<Variable> f_prod_r, std::vector<Variable> f_prod_i,
+                 std::vector<Variable> fscat, std::vector<Variable> poles, unsigned int L, unsigned int Mpair)
+    : ResonancePdf("kMatrix", name, ar, ai) { // resonances/kMatrix.cu:127-177
+    (void)L;
+    if(fscat.size() != 5) throw GeneralError("You must have {} channels in fscat, not {}", 5, fscat.size());
+    if(poles.size() != 5 * 6) throw GeneralError("You must have {}x{} channels in poles, not {}", 5, 6, poles.size());
+    registerConstant(Mpair);
+    for(const Variable &v : {sA0, sA, s0_prod, s0_scatt}) registerParameter(v);
+    for(int i = 0; i < 5; i++) registerParameter(fscat.at(i));
+    for(int i = 0; i < 5; i++) {
+        registerParameter(beta_r.at(i));
+        registerParameter(beta_i.at(i));
+    }
+    for(int i = 0; i < 5; i++) {
+        registerParameter(f_prod_r.at(i));
+        registerParameter(f_prod_i.at(i));
+    }
+    for(int i = 0; i < 30; i++) registerParameter(poles.at(i));
+    registerFunction("ptr_to_kMatrix_res", GF_OP_RES_KMATRIX);
+}
 FLATTE::FLATTE(std::string name, Variable ar, Variable ai, Variable mean, Variable g1, Variable rg2og1, unsigned int cyc, bool symmDP)
     : ResonancePdf("FLATTE", name, ar, ai) {
     registerParameter(mean);

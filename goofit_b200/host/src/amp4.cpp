@@ -2,6 +2,7 @@
 // Amplitude.cu, SpinFactors.cu:570-640, lineshapes/{Lineshape,BW,Bugg}.cu). Device work lives in csrc/gf_amp4.cu.
 #include <goofit/detail/Physics4.h>
 
+#include <functional>
 #include <numeric>
 
 namespace GooFit {
@@ -72,6 +73,94 @@ FOCUS::FOCUS(std::string name, Mod mod, Variable, Variable, unsigned int L, unsi
     : Lineshape("FOCUS", name, L, Mpair, FormFac, radius, 9) {
     GOOFIT_B200_LS_CONSTS
     registerConstant(static_cast<unsigned int>(mod));
+}
+static void registerKMatrix(Lineshape *self, std::vector<Variable> heads, std::vector<Variable> &beta_r, std::vector<Variable> &beta_i,
+                           std::vector<Variable> &f_prod_r, std::vector<Variable> &f_prod_i, std::vector<Variable> &fscat,
+                           std::vector<Variable> &poles, const std::function<void(Variable)> &reg) {
+    if(fscat.size() != 5) throw GeneralError("You must have {} channels in fscat, not {}", 5, fscat.size());
+    if(poles.size() != 5 * 6) throw GeneralError("You must have {}x{} channels in poles, not {}", 5, 6, poles.size());
+    if(beta_r.size() < 5 || beta_i.size() < 5 || f_prod_r.size() < 5 || f_prod_i.size() < 5)
+        throw GeneralError("kMatrix {}: beta and f_prod need five (real, imaginary) pairs", self->getName());
+    for(auto &v : heads) reg(v);
+    for(int i = 0; i < 5; i++) reg(fscat.at(i));
+    for(int i = 0; i < 5; i++) {
+        reg(beta_r.at(i));
+        reg(beta_i.at(i));
+    }
+    for(int i = 0; i < 5; i++) {
+        reg(f_prod_r.at(i));
+        reg(f_prod_i.at(i));
+    }
+    for(int i = 0; i < 30; i++) reg(poles.at(i));
+}
+kMatrix::kMatrix(std::string name, Variable, Variable, Variable sA0, Variable sA, Variable s0_prod, Variable s0_scatt, std::vector<Variable> beta_r,
+                 std::vector<Variable> beta_i, std::vector<Variable> f_prod_r, std::vector<Variable> f_prod_i, std::vector<Variable> fscat,
+                 std::vector<Variable> poles, unsigned int L, unsigned int Mpair, FF FormFac, fptype radius)
+    : Lineshape("kMatrix", name, L, Mpair, FormFac, radius, 10) {
+    registerKMatrix(this, {sA0, sA, s0_prod, s0_scatt}, beta_r, beta_i, f_prod_r, f_prod_i, fscat, poles, [this](Variable v) { registerParameter(v); });
+    GOOFIT_B200_LS_CONSTS
+}
+// GSpline.cu:97-124 make_spline_curvatures, as written upstream: the (n-2) x (n-2) system has 4 on the diagonal, 1 on the
+// super-diagonal and 1 in COLUMN 1 of every row below the first (`m(i + 1, 1) = 1`), it is inverted, applied to the second
+// differences of the knot values, and scaled by 6 / spacing^2 with spacing = (first - second entry of SplineInfo) / bins.
+// Upstream leaves the other matrix elements uninitialised (Eigen::Matrix is not zero-filled); they are zero here.
+std::vector<fptype> GSpline::curvatures(const std::vector<Variable> &vars, const spline_t &info) {
+    const size_t size = std::get<2>(info) - 2;
+    std::vector<std::vector<fptype>> m(size, std::vector<fptype>(size, 0.0)), inv(size, std::vector<fptype>(size, 0.0));
+    for(size_t i = 0; i < size; i++) {
+        m[i][i] = 4;
+        if(i != size - 1) {
+            m[i][i + 1] = 1;
+            m[i + 1][1] = 1;
+        }
+        inv[i][i] = 1;
+    }
+    for(size_t col = 0; col < size; col++) { // Gauss-Jordan with partial pivoting
+        size_t piv = col;
+        for(size_t r = col + 1; r < size; r++)
+            if(std::fabs(m[r][col]) > std::fabs(m[piv][col])) piv = r;
+        if(m[piv][col] == 0) throw GeneralError("GSpline: singular curvature system");
+        std::swap(m[piv], m[col]);
+        std::swap(inv[piv], inv[col]);
+        const fptype d = m[col][col];
+        for(size_t k = 0; k < size; k++) {
+            m[col][k] /= d;
+            inv[col][k] /= d;
+        }
+        for(size_t r = 0; r < size; r++) {
+            if(r == col || m[r][col] == 0) continue;
+            const fptype f = m[r][col];
+            for(size_t k = 0; k < size; k++) {
+                m[r][k] -= f * m[col][k];
+                inv[r][k] -= f * inv[col][k];
+            }
+        }
+    }
+    std::vector<fptype> Lv(size);
+    for(size_t i = 0; i < size; ++i) Lv[i] = vars[i + 2].getValue() - 2 * vars[i + 1].getValue() + vars[i].getValue();
+    const fptype spacing = (std::get<0>(info) - std::get<1>(info)) / std::get<2>(info);
+    std::vector<fptype> ret(vars.size(), 0);
+    for(size_t i = 0; i < size; ++i) {
+        fptype mtv = 0;
+        for(size_t k = 0; k < size; k++) mtv += inv[i][k] * Lv[k];
+        ret.at(i + 1) = 6 * mtv / (spacing * spacing);
+    }
+    return ret;
+}
+GSpline::GSpline(std::string name, Variable mass, Variable width, unsigned int L, unsigned int Mpair, FF FormFac, fptype radius,
+                 std::vector<Variable> AdditionalVars, spline_t SplineInfo)
+    : Lineshape("GSpline", name, L, Mpair, FormFac, radius, 11) {
+    registerParameter(mass);
+    registerParameter(width);
+    GOOFIT_B200_LS_CONSTS
+    if(std::get<2>(SplineInfo) != AdditionalVars.size()) throw GeneralError("bins {} != vars {}", std::get<2>(SplineInfo), AdditionalVars.size());
+    if(AdditionalVars.size() < 3) throw GeneralError("GSpline {} needs at least three knots", name);
+    registerConstant(std::get<0>(SplineInfo));
+    registerConstant(std::get<1>(SplineInfo));
+    registerConstant(std::get<2>(SplineInfo));
+    std::vector<fptype> terms = curvatures(AdditionalVars, SplineInfo);
+    registerConstant(static_cast<fptype>(terms.size()));
+    for(fptype t : terms) registerConstant(t);
 }
 #undef GOOFIT_B200_LS_CONSTS
 } // namespace Lineshapes

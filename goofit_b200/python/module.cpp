@@ -322,6 +322,11 @@ PYBIND11_MODULE(_goofit, m) {
     py::class_<Resonances::FLATTE, ResonancePdf>(mres, "FLATTE")
         .def(py::init<std::string, Variable, Variable, Variable, Variable, Variable, unsigned int, bool>(), "name"_a, "ar"_a, "ai"_a,
              "mean"_a, "g1"_a, "rg2og1"_a, "cyc"_a, "symmDP"_a);
+    py::class_<Resonances::kMatrix, ResonancePdf>(mres, "kMatrix")
+        .def(py::init<std::string, Variable, Variable, Variable, Variable, Variable, Variable, std::vector<Variable>, std::vector<Variable>,
+                      std::vector<Variable>, std::vector<Variable>, std::vector<Variable>, std::vector<Variable>, unsigned int, unsigned int>(),
+             "name"_a, "a_r"_a, "a_i"_a, "sA0"_a, "sA"_a, "s0_prod"_a, "s0_scatt"_a, "beta_r"_a, "beta_i"_a, "f_prod_r"_a, "f_prod_i"_a, "fscat"_a,
+             "poles"_a, "L"_a, "Mpair"_a);
     py::class_<Resonances::Spline, ResonancePdf>(mres, "Spline")
         .def(py::init([](std::string name, Variable ar, Variable ai, std::vector<fptype> limits, std::vector<Variable> re,
                          std::vector<Variable> im, unsigned int cyc, bool symmDP) {

@@ -60,6 +60,16 @@ void init_physics4(py::module &m) {
     py::class_<Lineshapes::GLASS, Lineshape>(mls, "GLASS")
         .def(py::init<std::string, Variable, Variable, unsigned int, unsigned int, FF, fptype, std::vector<Variable>>(), "name"_a, "mass"_a,
              "width"_a, "L"_a, "Mpair"_a, "FormFac"_a, "radius"_a, "AdditionalVars"_a);
+    py::class_<Lineshapes::kMatrix, Lineshape>(mls, "kMatrix")
+        .def(py::init<std::string, Variable, Variable, Variable, Variable, Variable, Variable, std::vector<Variable>, std::vector<Variable>,
+                      std::vector<Variable>, std::vector<Variable>, std::vector<Variable>, std::vector<Variable>, unsigned int, unsigned int, FF,
+                      fptype>(),
+             "name"_a, "a_r"_a, "a_i"_a, "sA0"_a, "sA"_a, "s0_prod"_a, "s0_scatt"_a, "beta_r"_a, "beta_i"_a, "f_prod_r"_a, "f_prod_i"_a, "fscat"_a,
+             "poles"_a, "L"_a, "Mpair"_a, "FormFac"_a = FF::BL_Prime, "radius"_a = 1.5);
+    py::class_<Lineshapes::GSpline, Lineshape>(mls, "GSpline")
+        .def(py::init<std::string, Variable, Variable, unsigned int, unsigned int, FF, fptype, std::vector<Variable>, Lineshapes::spline_t>(),
+             "name"_a, "mass"_a, "width"_a, "L"_a, "Mpair"_a, "FormFac"_a, "radius"_a, "AdditionalVars"_a, "SplineInfo"_a)
+        .def_static("curvatures", &Lineshapes::GSpline::curvatures, "vars"_a, "SplineInfo"_a);
     py::class_<Lineshapes::FOCUS, Lineshape> focus(mls, "FOCUS");
     py::enum_<Lineshapes::FOCUS::Mod>(focus, "Mod")
         .value("Kpi", Lineshapes::FOCUS::Mod::Kpi).value("KEta", Lineshapes::FOCUS::Mod::KEta).value("I32", Lineshapes::FOCUS::Mod::I32);

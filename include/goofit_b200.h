@@ -82,6 +82,7 @@ enum gf_op {
     GF_OP_RES_FLATTE,       /* resonances/FLATTE.cu:18  params mass,g1,g2/g1; consts cyc,symmDP */
     GF_OP_RES_SPLINE,       /* resonances/Spline.cu:10  params re,im per knot; consts cyc,doSwap,nKnots,knots[n],second derivatives[2n] */
     GF_OP_RES_RHOOMEGA,     /* resonances/RhoOmegaMix.cu:9  params omega mass,width, rho mass,width, real, imag, delta; consts spin,cyc,norm */
+    GF_OP_RES_KMATRIX,      /* resonances/kMatrix.cu:19  params sA0,sA,s0_prod,s0_scatt, fscat[5], beta(re,im)[5], f_prod(re,im)[5], per pole couplings[5]+mass; consts cyc */
     GF_OP_LS = 96,          /* 4-body lineshape; consts[0] = gf_ls_kind */
     GF_OP_SF,               /* 4-body spin factor; consts[0] = gf_sf_kind */
     /* decay-time resolution records of Amp4Body_TD (never on the per-event stack) */

@@ -38,6 +38,8 @@
 #include <goofit/PDFs/physics/lineshapes/FOCUS.h>
 #include <goofit/PDFs/physics/lineshapes/Flatte.h>
 #include <goofit/PDFs/physics/lineshapes/GLASS.h>
+#include <goofit/PDFs/physics/lineshapes/kMatrix.h>
+#include <goofit/PDFs/physics/resonances/kMatrix.h>
 #include <goofit/PDFs/physics/lineshapes/NonRes.h>
 #include <goofit/PDFs/physics/lineshapes/One.h>
 #include <goofit/PDFs/physics/lineshapes/Bugg.h>
@@ -852,6 +854,132 @@ static void case_zoo4() {
     put("zoo4.integral_moved", 1.0 / dp->getNormalization());
 }
 
+// ---- pi pi S-wave K-matrix: three-body resonance (resonances/kMatrix.cu) and four-body lineshape (lineshapes/kMatrix.cu) ----
+// Anisovich-Sarantsev pole masses and couplings (the values AmpGen / the BaBar D0 -> KS pi pi analyses use); production vector
+// and direct terms arbitrary. Inputs are those of the zoo3 / zoo4 cases (same seeds), so no new event files are written.
+struct KMatrixPars {
+    Variable sA0{"sA0", -0.15}, sA{"sA", 1.0}, s0_prod{"s0_prod", -0.07, 0.001, -5, 5}, s0_scatt{"s0_scatt", -3.92637};
+    std::vector<Variable> beta_r, beta_i, fprod_r, fprod_i, fscat, poles;
+    KMatrixPars() {
+        const double br[5] = {8.5, 12.2, 29.2, 10.8, 3.1}, bi[5] = {-4.2, 9.6, -2.1, -5.3, 7.7};
+        const double fr[5] = {-4.7, -23.2, -1.9, -14.7, 5.0}, fi[5] = {6.4, -10.9, 15.3, 2.0, -3.3};
+        const double fs[5] = {0.23399, 0.15044, -0.20545, 0.32825, 0.35412};
+        const double g[5][5] = {{0.22889, -0.55377, 0.00000, -0.39899, -0.34639},
+                                {0.94128, 0.55095, 0.00000, 0.39065, 0.31503},
+                                {0.36856, 0.23888, 0.55639, 0.18340, 0.18681},
+                                {0.33650, 0.40907, 0.85679, 0.19906, -0.00984},
+                                {0.18171, -0.17558, -0.79658, -0.00355, 0.22358}};
+        const double pm[5] = {0.65100, 1.20360, 1.55817, 1.21000, 1.82206};
+        for(int i = 0; i < 5; i++) {
+            std::string k = std::to_string(i);
+            beta_r.emplace_back("beta_r" + k, br[i], 0.01, -100, 100);
+            beta_i.emplace_back("beta_i" + k, bi[i], 0.01, -100, 100);
+            fprod_r.emplace_back("fprod_r" + k, fr[i]);
+            fprod_i.emplace_back("fprod_i" + k, fi[i]);
+            fscat.emplace_back("fscat" + k, fs[i]);
+            for(int j = 0; j < 5; j++) poles.emplace_back("g" + k + std::to_string(j), g[i][j]);
+            poles.emplace_back("pmass" + k, pm[i]);
+        }
+    }
+};
+static void case_kmatrix() {
+    { // three-body: D0 -> pi0 pi+ pi- with the pi+ pi- S-wave as a K-matrix and a rho+
+        Observable m12{"m12", 0, 3}, m13{"m13", 0, 3};
+        EventNumber eventNumber{"eventNumber"};
+        m12.setNumBins(90);
+        m13.setNumBins(90);
+        DecayInfo3 info;
+        info.motherMass = _mD0; info.daug1Mass = piZeroMass; info.daug2Mass = piPlusMass; info.daug3Mass = piPlusMass;
+        info.meson_radius = 1.5; info.mother_meson_radius = 5.0;
+        auto *K = new KMatrixPars();
+        info.resonances = {
+            new Resonances::kMatrix("kmat", Variable("km_r", 0.7), Variable("km_i", -0.4), K->sA0, K->sA, K->s0_prod, K->s0_scatt, K->beta_r, K->beta_i,
+                                    K->fprod_r, K->fprod_i, K->fscat, K->poles, 0, PAIR_23),
+            new Resonances::RBW("rhop", Variable("rhop_r", 1.0), Variable("rhop_i", 0.0), Variable("rhop_m", 0.7758), Variable("rhop_w", 0.1503), 1, PAIR_12),
+        };
+        Variable one("one", 1), zero("zero", 0);
+        std::vector<Observable> obs = {m12, m13};
+        auto *eff = new PolynomialPdf("constantEff", obs, std::vector<Variable>{one}, std::vector<Variable>{zero, zero}, 0);
+        auto *s = new Amp3Body("kmatrix3", m12, m13, eventNumber, info, eff);
+        UnbinnedDataSet d({m12, m13, eventNumber});
+        std::mt19937_64 gen(77); // the events of case_zoo3
+        std::uniform_real_distribution<double> u(0, 3);
+        while(d.getNumEvents() < 500) {
+            double a = u(gen), b = u(gen);
+            if(!inDalitz(a, b, _mD0, piZeroMass, piPlusMass, piPlusMass)) continue;
+            m12.setValue(a); m13.setValue(b); eventNumber.setValue(d.getNumEvents());
+            d.addEvent();
+        }
+        s->setData(&d);
+        s->setDataSize(d.getNumEvents());
+        put("kmatrix3.nll", s->calculateNLL());
+        put("kmatrix3.integral", 1.0 / s->getNormalization());
+        std::vector<double> waves;
+        auto w = s->getCachedWave(0);
+        for(auto &c : w) { waves.push_back(c.real()); waves.push_back(c.imag()); }
+        save_npy("kmatrix3.wave", waves.data(), 1, 2 * d.getNumEvents());
+        K->beta_r[1].setChanged(true); K->s0_prod.setChanged(true);
+        s->updateVariable(K->beta_r[1], 11.0); s->updateVariable(K->s0_prod, -0.2); s->updateParameters();
+        put("kmatrix3.nll_moved", s->calculateNLL());
+        put("kmatrix3.integral_moved", 1.0 / s->getNormalization());
+    }
+    { // four-body: D0 -> K- pi+ pi+ pi- with a (pi pi)_S K-matrix x K*(892) amplitude and a rho x K* one
+        Observable m12{"m12", 0, 3}, m34{"m34", 0, 3}, cos12{"cos12", -1, 1}, cos34{"m34", -1, 1}, phi{"phi", -3.5, 3.5};
+        EventNumber eventNumber{"eventNumber", 0, INT_MAX};
+        const fptype mD0 = 1.8645, piP = 0.13957018, Km = 0.493677;
+        DecayInfo4 info;
+        info.meson_radius    = 1.5;
+        info.particle_masses = {mD0, piP, piP, Km, piP};
+        auto *K = new KMatrixPars();
+        Variable rhoM("rho_m", 0.77526), rhoW("rho_w", 0.1478), ksM("Kstar_m", 0.89581), ksW("Kstar_w", 0.0474);
+        std::vector<Lineshape *> L1 = {new Lineshapes::kMatrix("kmat", Variable("km_r", 1), Variable("km_i", 0), K->sA0, K->sA, K->s0_prod, K->s0_scatt,
+                                                                K->beta_r, K->beta_i, K->fprod_r, K->fprod_i, K->fscat, K->poles, 0, M_12, FF::BL_Prime, 1.5),
+                                       new Lineshapes::RBW("Kstar", ksM, ksW, 1, M_34)};
+        std::vector<SpinFactor *> S1 = {new SpinFactor("SF", SF_4Body::DtoVS_VtoP1P2_StoP3P4, mD0, 2, 3, 0, 1)};
+        std::vector<Lineshape *> L2 = {new Lineshapes::RBW("rho", rhoM, rhoW, 1, M_12), new Lineshapes::RBW("Kstar", ksM, ksW, 1, M_34)};
+        std::vector<SpinFactor *> S2 = {new SpinFactor("SF", SF_4Body::DtoV1V2_V1toP1P2_V2toP3P4_S, mD0, 0, 1, 2, 3)};
+        info.amplitudes = {new Amplitude("KS", Variable("a1r", 0.02), Variable("a1i", 0.01), L1, S1, 1),
+                           new Amplitude("RK", Variable("a2r", 1.0), Variable("a2i", 0.0), L2, S2, 1)};
+        Variable one("constantOne", 1), zero("constantZero", 0);
+        std::vector<Observable> obs = {m12, m34, cos12, cos34, phi, eventNumber};
+        auto *eff = new PolynomialPdf("constantEff", obs, std::vector<Variable>{one}, std::vector<Variable>{zero, zero}, 0);
+        auto *dp  = new Amp4Body("kmatrix4", obs, info, eff, 40000); // the MC sample of case_zoo4
+        UnbinnedDataSet d(obs);
+        { // the data events of case_zoo4
+            size_t n = 400;
+            std::vector<mcbooster::GReal_t> masses(info.particle_masses.begin() + 1, info.particle_masses.end());
+            mcbooster::PhaseSpace phsp(mD0, masses, n, 991);
+            phsp.Generate(mcbooster::Vector4R(mD0, 0.0, 0.0, 0.0));
+            auto d1 = phsp.GetDaughters(0), d2 = phsp.GetDaughters(1), d3 = phsp.GetDaughters(2), d4 = phsp.GetDaughters(3);
+            mcbooster::ParticlesSet_d pset = {&d1, &d2, &d3, &d4};
+            mcbooster::RealVector_d v0(n), v1(n), v2(n), v3(n), v4(n);
+            mcbooster::VariableSet_d vs = {&v0, &v1, &v2, &v3, &v4};
+            Dim5 eval;
+            mcbooster::EvaluateArray<Dim5>(eval, pset, vs);
+            for(size_t i = 0; i < n; i++) {
+                m12.setValue(v0[i]); m34.setValue(v1[i]); cos12.setValue(v2[i]); cos34.setValue(v3[i]); phi.setValue(v4[i]);
+                eventNumber.setValue(d.getNumEvents());
+                d.addEvent();
+            }
+        }
+        put("kmatrix4.mc_events", dp->getMCevents());
+        dp->setData(&d);
+        dp->setDataSize(d.getNumEvents(), 6);
+        put("kmatrix4.nll", dp->calculateNLL());
+        put("kmatrix4.integral", 1.0 / dp->getNormalization());
+        {
+            std::vector<double> amps;
+            thrust::host_vector<fpcomplex> h = *(dp->cachedAMPs);
+            for(size_t i = 0; i < h.size(); i++) { amps.push_back(h[i].real()); amps.push_back(h[i].imag()); }
+            save_npy("kmatrix4.amps", amps.data(), d.getNumEvents(), 4);
+        }
+        K->beta_r[1].setChanged(true); K->s0_prod.setChanged(true);
+        dp->updateVariable(K->beta_r[1], 11.0); dp->updateVariable(K->s0_prod, -0.2); dp->updateParameters();
+        put("kmatrix4.nll_moved", dp->calculateNLL());
+        put("kmatrix4.integral_moved", 1.0 / dp->getNormalization());
+    }
+}
+
 static void case_dp4_fit() {
     DP4Model *M = make_dp4(60000, false);
     UnbinnedDataSet cand({M->m12, M->m34, M->cos12, M->cos34, M->phi, M->eventNumber});
@@ -1493,6 +1621,7 @@ int main(int argc, char **argv) {
             if(only == "all" || only == "dalitz") case_dalitz();
             if(only == "all" || only == "zoo3") case_zoo3();
             if(only == "all" || only == "zoo4") case_zoo4();
+            if(only == "all" || only == "kmatrix") case_kmatrix();
             if(only == "all" || only == "dalitzfit") case_dalitz_fit();
             if(only == "all" || only == "dp4") case_dp4();
             if(only == "all" || only == "dp4fit") case_dp4_fit();

@@ -448,3 +448,83 @@ class ZachFull:
 
     def dataset(self, dm_values):
         return dataset_from_columns([self.dm], [dm_values])
+
+
+def kmatrix_pars():
+    """Anisovich-Sarantsev pi pi S-wave K-matrix (the values of oracle/ref_driver.cpp KMatrixPars)"""
+    V = gf.Variable
+    br, bi = [8.5, 12.2, 29.2, 10.8, 3.1], [-4.2, 9.6, -2.1, -5.3, 7.7]
+    fr, fi = [-4.7, -23.2, -1.9, -14.7, 5.0], [6.4, -10.9, 15.3, 2.0, -3.3]
+    fs = [0.23399, 0.15044, -0.20545, 0.32825, 0.35412]
+    g = [[0.22889, -0.55377, 0.00000, -0.39899, -0.34639], [0.94128, 0.55095, 0.00000, 0.39065, 0.31503],
+         [0.36856, 0.23888, 0.55639, 0.18340, 0.18681], [0.33650, 0.40907, 0.85679, 0.19906, -0.00984],
+         [0.18171, -0.17558, -0.79658, -0.00355, 0.22358]]
+    pm = [0.65100, 1.20360, 1.55817, 1.21000, 1.82206]
+    K = dict(sA0=V("sA0", -0.15), sA=V("sA", 1.0), s0_prod=V("s0_prod", -0.07, 0.001, -5, 5), s0_scatt=V("s0_scatt", -3.92637))
+    K["beta_r"] = [V("beta_r%d" % i, br[i], 0.01, -100, 100) for i in range(5)]
+    K["beta_i"] = [V("beta_i%d" % i, bi[i], 0.01, -100, 100) for i in range(5)]
+    K["fprod_r"] = [V("fprod_r%d" % i, fr[i]) for i in range(5)]
+    K["fprod_i"] = [V("fprod_i%d" % i, fi[i]) for i in range(5)]
+    K["fscat"] = [V("fscat%d" % i, fs[i]) for i in range(5)]
+    K["poles"] = []
+    for i in range(5):
+        K["poles"] += [V("g%d%d" % (i, j), g[i][j]) for j in range(5)] + [V("pmass%d" % i, pm[i])]
+    return K
+
+
+class KMatrix3:
+    """D0 -> pi0 pi+ pi- with the pi+ pi- S-wave as a K-matrix and a rho+ (oracle/ref_driver.cpp case_kmatrix)"""
+
+    def __init__(self, grid=90):
+        k = self.keep = Keep()
+        V = gf.Variable
+        self.m12, self.m13 = gf.Observable("m12", 0, 3), gf.Observable("m13", 0, 3)
+        self.m12.numbins = self.m13.numbins = grid
+        self.evt = gf.EventNumber("eventNumber")
+        info = self.info = gf.DecayInfo3()
+        info.motherMass, info.daug1Mass, info.daug2Mass, info.daug3Mass = 1.86484, 0.1349766, 0.13957018, 0.13957018
+        info.meson_radius, info.mother_meson_radius = 1.5, 5.0
+        K = self.K = kmatrix_pars()
+        R = gf.Resonances
+        self.res = [k(R.kMatrix("kmat", V("km_r", 0.7), V("km_i", -0.4), K["sA0"], K["sA"], K["s0_prod"], K["s0_scatt"], K["beta_r"], K["beta_i"],
+                                K["fprod_r"], K["fprod_i"], K["fscat"], K["poles"], 0, 2)),
+                    k(R.RBW("rhop", V("rhop_r", 1.0), V("rhop_i", 0.0), V("rhop_m", 0.7758), V("rhop_w", 0.1503), 1, 0))]
+        info.resonances = self.res
+        self.eff = k(gf.PolynomialPdf("constantEff", [self.m12, self.m13], [V("one", 1)], [V("zero", 0)] * 2, 0))
+        self.signal = gf.Amp3Body("kmatrix3", self.m12, self.m13, self.evt, info, self.eff)
+
+    def dataset(self, m12, m13):
+        return dataset_from_columns([self.m12, self.m13, self.evt], [m12, m13, np.arange(len(m12), dtype=np.float64)])
+
+
+class KMatrix4:
+    """D0 -> K- pi+ pi+ pi-: a (pi pi)_S K-matrix x K*(892) amplitude and a rho x K* one (oracle/ref_driver.cpp case_kmatrix)"""
+
+    def __init__(self):
+        k = self.keep = Keep()
+        O, V = gf.Observable, gf.Variable
+        self.m12, self.m34 = O("m12", 0, 3), O("m34", 0, 3)
+        self.cos12, self.cos34, self.phi = O("cos12", -1, 1), O("cos34", -1, 1), O("phi", -3.5, 3.5)
+        self.evt = gf.EventNumber("eventNumber", 0, 2147483647)
+        mD0, piP, Km = 1.8645, 0.13957018, 0.493677
+        info = self.info = gf.DecayInfo4()
+        info.meson_radius = 1.5
+        info.particle_masses = [mD0, piP, piP, Km, piP]
+        K = self.K = kmatrix_pars()
+        L, P, S = gf.Lineshapes, gf.DP4Pair, gf.SF_4Body
+        ksM, ksW = V("Kstar_m", 0.89581), V("Kstar_w", 0.0474)
+        L1 = [k(L.kMatrix("kmat", V("km_r", 1), V("km_i", 0), K["sA0"], K["sA"], K["s0_prod"], K["s0_scatt"], K["beta_r"], K["beta_i"],
+                          K["fprod_r"], K["fprod_i"], K["fscat"], K["poles"], 0, int(P.M_12))),
+              k(L.RBW("Kstar", ksM, ksW, 1, int(P.M_34)))]
+        S1 = [k(gf.SpinFactor("SF", S.DtoVS_VtoP1P2_StoP3P4, mD0, 2, 3, 0, 1))]
+        L2 = [k(L.RBW("rho", V("rho_m", 0.77526), V("rho_w", 0.1478), 1, int(P.M_12))), k(L.RBW("Kstar", ksM, ksW, 1, int(P.M_34)))]
+        S2 = [k(gf.SpinFactor("SF", S.DtoV1V2_V1toP1P2_V2toP3P4_S, mD0, 0, 1, 2, 3))]
+        for a in (k(gf.Amplitude("KS", V("a1r", 0.02), V("a1i", 0.01), L1, S1, 1)), k(gf.Amplitude("RK", V("a2r", 1.0), V("a2i", 0.0), L2, S2, 1))):
+            info.add_amplitude(a)
+        self.observables = [self.m12, self.m34, self.cos12, self.cos34, self.phi, self.evt]
+        self.eff = k(gf.PolynomialPdf("constantEff", self.observables, [V("constantOne", 1)], [V("constantZero", 0)] * 2, 0))
+        self.dp = gf.Amp4Body("kmatrix4", self.observables, info, self.eff, 0)
+
+    def dataset(self, cols5):
+        n = len(cols5[0])
+        return dataset_from_columns(self.observables, list(cols5) + [np.arange(n, dtype=np.float64)])

@@ -295,6 +295,115 @@ def test_zoo3_resonance_shapes(golden):
     assert rel(1.0 / s.getNormalization(), golden["zoo3.integral_moved"]) < 1e-12
 
 
+def test_kmatrix_three_and_four_body(golden):
+    """The pi pi S-wave K-matrix (resonances/kMatrix.cu:19-121, lineshapes/kMatrix.cu:18-119, kMatrixUtils.cu): five channels, five
+    poles, LU inverse of 1 - i adler K rho. Same events and MC sample as the zoo3 / zoo4 cases."""
+    from models import KMatrix3, KMatrix4
+    M = KMatrix3()
+    d = M.dataset(golden.arr("zoo3.m12"), golden.arr("zoo3.m13"))
+    s = M.signal
+    s.setData(d)
+    s.setDataSize(len(d))
+    nll = s.calculateNLL()
+    w = np.asarray(s.getCachedWave(0))
+    ref = golden.arr("kmatrix3.wave")[0]
+    r = ref[0::2] + 1j * ref[1::2]
+    assert np.max(np.abs(w - r) / np.maximum(np.abs(r), 1e-300)) < 1e-10
+    assert rel(nll, golden["kmatrix3.nll"]) < RTOL_NLL
+    assert rel(1.0 / s.getNormalization(), golden["kmatrix3.integral"]) < 1e-11
+    K = M.K
+    K["beta_r"][1].changed = True
+    K["s0_prod"].changed = True
+    s.updateVariable(K["beta_r"][1], 11.0)
+    s.updateVariable(K["s0_prod"], -0.2)
+    s.updateParameters()
+    assert rel(s.calculateNLL(), golden["kmatrix3.nll_moved"]) < RTOL_NLL
+    assert rel(1.0 / s.getNormalization(), golden["kmatrix3.integral_moved"]) < 1e-11
+    for mode in ("Gram", "PerEvent"):
+        M = KMatrix4()
+        dp = M.dp
+        dp.setNormMode(getattr(gf.Amp4BodyBase.NormMode, mode))
+        names = ("m12", "m34", "cos12", "cos34", "phi")
+        mc = np.vstack([golden.arr("zoo4.mc_" + n) for n in names])
+        assert mc.shape[1] == int(golden["kmatrix4.mc_events"])
+        dp.setNormEvents(mc)
+        d = M.dataset([golden.arr("zoo4." + n) for n in names])
+        dp.setData(d)
+        dp.setDataSize(len(d), 6)
+        nll = dp.calculateNLL()
+        ref = golden.arr("kmatrix4.amps")
+        for a in range(2):
+            w = np.asarray(dp.getCachedAmp(a))
+            r = ref[:, 2 * a] + 1j * ref[:, 2 * a + 1]
+            assert np.max(np.abs(w - r) / np.maximum(np.abs(r), 1e-300)) < 1e-10, a
+        assert rel(nll, golden["kmatrix4.nll"]) < RTOL_NLL
+        assert rel(1.0 / dp.getNormalization(), golden["kmatrix4.integral"]) < 1e-11
+        K = M.K
+        K["beta_r"][1].changed = True
+        K["s0_prod"].changed = True
+        dp.updateVariable(K["beta_r"][1], 11.0)
+        dp.updateVariable(K["s0_prod"], -0.2)
+        dp.updateParameters()
+        assert rel(dp.calculateNLL(), golden["kmatrix4.nll_moved"]) < RTOL_NLL
+        assert rel(1.0 / dp.getNormalization(), golden["kmatrix4.integral_moved"]) < 1e-11
+
+
+def test_gspline_lineshape_self_consistent():
+    """Lineshapes::GSpline (lineshapes/GSpline.cu:31-161). Upstream's version cannot be pinned: make_spline_curvatures fills an
+    uninitialised Eigen matrix and getSpline reads past the constants it registered (see csrc/gf_amp4.cuh). The device function is
+    checked against a numpy restatement of the same formula on the same constants (parity with upstream: unpinned)."""
+    from models import Keep
+    k = Keep()
+    O, V = gf.Observable, gf.Variable
+    obs = [O("m12", 0, 3), O("m34", 0, 3), O("cos12", -1, 1), O("cos34", -1, 1), O("phi", -3.5, 3.5), gf.EventNumber("eventNumber", 0, 2147483647)]
+    mD0, piP, Km = 1.8645, 0.13957018, 0.493677
+    info = gf.DecayInfo4()
+    info.meson_radius = 1.5
+    info.particle_masses = [mD0, piP, piP, Km, piP]
+    knots = [V("k%d" % i, 0.3 + 0.2 * math.sin(0.7 * i) + 0.05 * i) for i in range(8)]
+    smin, smax, nb = 0.08, 1.6, 8
+    mass, width, radius = V("gs_m", 0.9), V("gs_w", 0.25), 1.5
+    L, P, S = gf.Lineshapes, gf.DP4Pair, gf.SF_4Body
+    ls = [k(L.GSpline("gspline", mass, width, 0, int(P.M_12), gf.FF.BL2, radius, knots, (smin, smax, nb))), k(L.One("one", mass, width, 0, int(P.M_34)))]
+    sf = [k(gf.SpinFactor("SF", S.ONE, mD0, 0, 1, 2, 3))]
+    info.add_amplitude(k(gf.Amplitude("A", V("ar", 1.0), V("ai", 0.0), ls, sf, 1)))
+    eff = k(gf.PolynomialPdf("constantEff", obs, [V("constantOne", 1)], [V("constantZero", 0)] * 2, 0))
+    dp = gf.Amp4Body("gs", obs, info, eff, 0)
+    n = 4000
+    cols, _ = gf.generatePhaseSpace5(info.particle_masses, n, 3)
+    dp.setNormEvents(np.asarray(cols)[:, :500])
+    dp.setData(dataset_from_columns(obs, list(np.asarray(cols)) + [np.arange(n, dtype=np.float64)]))
+    dp.setDataSize(n, 6)
+    dp.calculateNLL()
+    got = np.asarray(dp.getCachedAmp(0))
+    curv = np.asarray(L.GSpline.curvatures(knots, (smin, smax, nb)))
+    c = np.concatenate([curv, np.zeros(2 * nb + 2)])  # reads past the registered block yield zero
+
+    def spline(x, continued):
+        spacing = (smax - smin) / (nb - 1.0)
+        out = np.empty_like(x)
+        lo, hi = x <= smin, x >= smax
+        out[lo] = c[0] if continued else 0.0
+        out[hi] = c[nb - 1] if continued else 0.0
+        mid = ~(lo | hi)
+        dx = np.fmod(x[mid] - smin, spacing)
+        b = ((x[mid] - smin) / spacing).astype(int)
+        x0, x1, f0, f1 = c[b], c[b + 1], c[b + nb], c[b + nb + 1]
+        out[mid] = x0 + dx * ((x1 - x0) / spacing - (f1 + 2 * f0) * spacing / 6) + dx * dx * f0 + dx ** 3 * (f1 - f0) / (6 * spacing)
+        return out
+
+    m12 = np.asarray(cols)[0]
+    s_, m, w = m12 ** 2, mass.value, width.value
+    q2 = np.abs(s_ / 4.0 - (piP ** 2 + piP ** 2) / 2.0)
+    BF = np.exp(-q2 * radius ** 2 / 2)
+    ws, wn = w * spline(s_, True), w * spline(np.array([m * m]), False)[0]
+    gamma = m * math.sqrt(m * m + w * w)
+    kf = math.sqrt(2 * math.sqrt(2.0) * m * w * gamma / (math.pi * math.sqrt(m * m + gamma)))
+    rw = np.zeros_like(ws) if wn == 0 else w * ws / wn
+    want = kf * BF / ((m * m - s_) - 1j * m * rw)
+    np.testing.assert_allclose(got, want, rtol=1e-11)
+
+
 def test_dalitz_fit_matches_reference(golden):
     M = Dalitz(float_masses=False, grid=240)
     d = M.dataset(golden.arr("dalitzfit.m12"), golden.arr("dalitzfit.m13"))
