@@ -47,10 +47,15 @@ if len(sys.argv) > 3:
     t = {}
     if "k_eval_sum" in traffic:
         t["k_eval_sum_dram_bytes_per_launch"] = int(traffic["k_eval_sum"][0][0])  # first k_eval_sum = the Dalitz one
-    for k in ("k_amp3_waves", "k_amp4_cache", "k_amp4_sf"):
+    for k in ("k_amp3_waves", "k_amp4_cache", "k_amp4_sf", "k_amp4_update", "k_eval_fast_amp4", "k_eval_logleaf"):
         if k in traffic:
             t[k + "_fp64_flops_per_launch"] = traffic[k][0][1]
             t[k + "_dram_bytes_per_launch"] = int(traffic[k][0][0])
-    t["source"] = "ncu --set full --clock-control none, tools/profile_once.py at 10^7 events (profiles/r01_ncu_full_summary.csv)"
+    import subprocess
+    t["source"] = "ncu --set full --clock-control none, tools/profile_once.py at 10^7 events (profiles/r02_ncu_full_summary.csv)"
+    try:
+        t["git_head"] = subprocess.run(["git", "rev-parse", "--short", "HEAD"], capture_output=True, text=True).stdout.strip()
+    except Exception:
+        pass
     json.dump(t, open(sys.argv[3], "w"), indent=1)
 print("rows", len(out) - 1)

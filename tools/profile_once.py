@@ -1,6 +1,7 @@
 """tools/profile_once.py — launches every hot kernel a small, fixed number of times at BASELINE sizes so that one
 `ncu --set full -k regex:"k_amp|k_eval_sum"` capture holds all of them (Dalitz: k_amp3_waves/grid/gram + k_eval_sum;
-DP4 and TDDP4: k_amp4_sf, k_amp4_cache, k_amp4_amps, k_amp4_norm[_td], k_eval_sum). Not a benchmark."""
+DP4 and TDDP4: k_amp4_sf, k_amp4_update (first call and K*(892)-mass move), k_eval_fast_amp4; exp: k_eval_logleaf and the
+interpreter copy of k_eval_sum on 10^8 events). Not a benchmark."""
 import os
 import sys
 
@@ -13,7 +14,7 @@ import goofit_b200 as gf  # noqa: E402
 from models import DP4, TDDP4, Dalitz, dalitz_uniform_events  # noqa: E402
 
 N = int(sys.argv[1]) if len(sys.argv) > 1 else 10_000_000
-which = sys.argv[2] if len(sys.argv) > 2 else "dalitz,dp4,tddp4"
+which = sys.argv[2] if len(sys.argv) > 2 else "dalitz,dp4,tddp4,exp"
 if "dalitz" in which:
     M = Dalitz(float_masses=False, grid=240)
     m12, m13 = dalitz_uniform_events(N, 12345)
@@ -47,4 +48,15 @@ for kind in ("dp4", "tddp4"):
     M.signal.updateVariable(M.lsvars[2], 0.8975)
     M.signal.updateParameters()
     print(kind, M.signal.calculateNLL())
+if "exp" in which:
+    from models import dataset_from_columns
+    x = gf.Observable("x", 0, 10)
+    xs = np.random.default_rng(137).exponential(1.0, 10 * N)
+    xs = xs[xs < 10.0]
+    pdf = gf.ExpPdf("exppdf", x, gf.Variable("alpha", -2, 0.1, -10, 10))
+    pdf.setData(dataset_from_columns([x], [xs]))
+    print("exp", len(xs), pdf.calculateNLL(), gf.last_kernel_name())
+    gf.fast_enable(False)
+    print("exp (interpreter)", pdf.calculateNLL(), gf.last_kernel_name())
+    gf.fast_enable(True)
 print("launches", gf.launch_count())
