@@ -13,7 +13,9 @@ CAPI_PATH = _os.path.join(LIB_DIR, "libgoofit_b200.so")
 try:
     from ._goofit import *  # noqa: F401,F403
     from . import _goofit
-    from ._goofit import Resonances, Lineshapes  # noqa: F401
+    from ._goofit import Resonances, Lineshapes, minuit2  # noqa: F401
+    import sys as _sys
+    _sys.modules[__name__ + ".minuit2"] = minuit2  # `import goofit_b200.minuit2` / `from goofit_b200.minuit2 import MnMigrad` (upstream: goofit.minuit2)
 except ImportError as e:  # pragma: no cover - build missing
     raise ImportError(
         "goofit_b200: the native extension is not built (run `make` or `python -c 'import __graft_entry__ as g; g.build()'`): %s" % e

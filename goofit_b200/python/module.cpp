@@ -19,6 +19,7 @@ using namespace pybind11::literals;
 using namespace GooFit;
 
 void init_physics4(py::module &m);
+void init_minuit2(py::module &m);
 py::tuple generated_to_numpy(const GooFit::GeneratedSignal &G, int ncomp);
 
 
@@ -381,18 +382,8 @@ PYBIND11_MODULE(_goofit, m) {
     init_physics4(m);
 
     // ---- fitting ----
-    py::class_<Minuit2::FunctionMinimum>(m, "FunctionMinimum")
-        .def("Fval", &Minuit2::FunctionMinimum::Fval)
-        .def("Edm", &Minuit2::FunctionMinimum::Edm)
-        .def("NFcn", &Minuit2::FunctionMinimum::NFcn)
-        .def("IsValid", &Minuit2::FunctionMinimum::IsValid)
-        .def("HasCovariance", &Minuit2::FunctionMinimum::HasCovariance)
-        .def("HasValidCovariance", &Minuit2::FunctionMinimum::HasValidCovariance)
-        .def("HasAccurateCovar", &Minuit2::FunctionMinimum::HasAccurateCovar)
-        .def("HasReachedCallLimit", &Minuit2::FunctionMinimum::HasReachedCallLimit)
-        .def("IsAboveMaxEdm", &Minuit2::FunctionMinimum::IsAboveMaxEdm)
-        .def("values", [](const Minuit2::FunctionMinimum &f) { return f.UserState().Params(); })
-        .def("errors", [](const Minuit2::FunctionMinimum &f) { return f.UserState().Errors(); });
+    init_minuit2(m); // goofit_b200.minuit2: FCNBase, MnUserParameters, MnMigrad, FunctionMinimum, ... (python/Minuit2/*.cpp upstream)
+    m.attr("FunctionMinimum") = m.attr("minuit2").attr("FunctionMinimum");
     py::class_<Params>(m, "Params")
         .def(py::init<PdfBase &>(), "pdf"_a, py::keep_alive<1, 2>())
         .def("size", &Params::size)
@@ -401,7 +392,7 @@ PYBIND11_MODULE(_goofit, m) {
         .def("from_minuit_vector", &Params::from_minuit_vector, "values"_a, "force_changed"_a = false)
         .def("set_record", &Params::set_record, "do_record"_a = true)
         .def("get_recorded", &Params::get_recorded);
-    py::class_<FCN>(m, "FCN")
+    py::class_<FCN, Minuit2::FCNBase>(m, "FCN")
         .def(py::init<Params &>(), "params"_a, py::keep_alive<1, 2>())
         .def("__call__", (double (FCN::*)(const std::vector<double> &) const) & FCN::operator())
         .def("__call__", (double (FCN::*)() const) & FCN::operator())

@@ -352,3 +352,32 @@ def test_shard_needs_valid_rank_and_a_communicator():
         with pytest.raises(gf.GeneralError, match="rank"):
             gf.set_shard(*bad)
     gf.set_shard(0, 1)
+
+
+def test_minuit2_module_minimises_a_python_function():
+    """goofit.minuit2 (python/Minuit2/main.cpp + class files): FCNBase overridable from Python, MnUserParameters, MnMigrad,
+    FunctionMinimum / MnUserParameterState / MnUserCovariance accessors. Pure host code: runs without a device."""
+    import goofit_b200 as gf
+    import goofit_b200.minuit2 as m2
+    from goofit_b200.minuit2 import FCNBase, MnMigrad, MnUserParameters
+
+    class Paraboloid(FCNBase):
+        def __call__(self, v):
+            return (v[0] - 3.0) ** 2 + 2 * (v[1] + 1.0) ** 2 + 5
+
+        def Up(self):
+            return 1.0
+
+    p = MnUserParameters()
+    assert p.Add("a", 0.0, 0.1) and p.Add("b", 0.0, 0.1, -10, 10)
+    assert p.Parameter(1).HasLimits() and p.Parameter(0).GetName() == "a" and len(p.Parameters()) == 2
+    f = Paraboloid()
+    res = MnMigrad(f, p)()
+    assert res.IsValid() and res.HasCovariance() and not res.IsAboveMaxEdm() and not res.HasReachedCallLimit()
+    st = res.UserState()
+    assert abs(st.Value(0) - 3.0) < 1e-3 and abs(st.Value(1) + 1.0) < 1e-2 and abs(res.Fval() - 5.0) < 1e-4
+    cov = res.UserCovariance().to_matrix()
+    assert cov.shape == (2, 2) and abs(cov[0, 0] - 1.0) < 1e-2 and abs(cov[1, 1] - 0.5) < 1e-2
+    assert gf.FunctionMinimum is m2.FunctionMinimum and issubclass(gf.FCN, m2.FCNBase)
+    lvl = m2.MnPrint.GlobalLevel()
+    m2.MnPrint.SetGlobalLevel(lvl)
