@@ -93,7 +93,7 @@ def four_body(gf, lib, ctx, kind, n_data, n_mc, steps, peak_hbm):
     unique = 2_000_000
     masses = [1.8645, 0.13957018, 0.13957018, 0.493677, 0.13957018]
     t0 = time.perf_counter()
-    ph, _ = gf.generatePhaseSpace5(masses, unique, 4242)
+    ph, _ = gf.devicePhaseSpace5(masses, unique, 4242)  # GENBOD on the GPU (k_genbod)
     t_gen = time.perf_counter() - t0
     rng = np.random.default_rng(99)
     if kind == "dp4":

@@ -228,6 +228,19 @@ void init_physics4(py::module &m) {
         "mother_and_daughter_masses"_a, "nEvents"_a, "seed"_a = 0, "offset"_a = 0,
         "the stream of generatePhaseSpaceParticles generated on the GPU: (particles[nd, N, 4], weights[N], dim5[5, N] for four daughters)");
     m.def(
+        "devicePhaseSpace5",
+        [](std::vector<fptype> masses, size_t n, unsigned long seed, size_t offset) {
+            std::vector<fptype> w;
+            std::vector<std::vector<fptype>> v5;
+            devicePhaseSpace(masses, n, seed, offset, nullptr, w, &v5);
+            py::array_t<fptype> r({(size_t)5, n}), wa(n);
+            for(int k = 0; k < 5; k++) std::copy(v5[k].begin(), v5[k].end(), r.mutable_data(k, 0));
+            std::copy(w.begin(), w.end(), wa.mutable_data());
+            return py::make_tuple(r, wa);
+        },
+        "particle_masses"_a, "n"_a, "seed"_a = 0, "offset"_a = 0,
+        "generatePhaseSpace5's stream generated on the GPU: (m12, m34, cos12, cos34, phi) columns + weights");
+    m.def(
         "counterUniform",
         [](unsigned long seed, py::array_t<long long, py::array::c_style | py::array::forcecast> events, unsigned long stream) {
             py::array_t<fptype> out(events.size());

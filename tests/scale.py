@@ -123,7 +123,8 @@ def dalitz_model_events(gf, M, n, seed, chunk=8_000_000):
 
 
 def phase_space(gf, n, seed):
-    cols, w = gf.generatePhaseSpace5(MASSES4, n, seed)
+    """weighted four-body phase space in the five variables, generated on the GPU (k_genbod)"""
+    cols, w = gf.devicePhaseSpace5(MASSES4, n, seed)
     return np.asarray(cols), np.asarray(w)
 
 

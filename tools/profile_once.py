@@ -23,7 +23,7 @@ if "dalitz" in which:
     M.signal.setDataSize(len(d))
     print("dalitz", M.signal.calculateNLL(), M.signal.calculateNLL())
 masses = [1.8645, 0.13957018, 0.13957018, 0.493677, 0.13957018]
-ph, _ = gf.generatePhaseSpace5(masses, min(N, 2_000_000), 4242)
+ph, _ = gf.devicePhaseSpace5(masses, min(N, 2_000_000), 4242)
 reps = (N + ph.shape[1] - 1) // ph.shape[1]
 cols = np.ascontiguousarray(np.tile(ph, (1, reps))[:, :N])
 mc = np.ascontiguousarray(np.tile(ph[:, ::-1], (1, reps))[:, :N])
