@@ -397,8 +397,9 @@ __device__ __forceinline__ void gf_dmma(double &c0, double &c1, double a, double
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 constexpr int upd_tiles(int nb) { return nb == 1 ? 2 : (nb == 2 ? 6 : 0); } // 8x8 accumulator tiles: (C1, C2) per block pair (0,0) [, (0,1), (1,1)]
-// resident blocks per SM: the data-sample copy (no Gram accumulators) fits three at 80 registers
-constexpr int upd_blocks_per_sm(int nb) { return nb == 0 ? 3 : 2; }
+// measured (tools/ab_compare.sh, K*(892) move on 10^7 + 10^7 events): the MC copy at three resident blocks (80 registers, small
+// spills) against two (128): 1.80 -> 1.66 ms per call (DP4), 2.00 -> 1.77 ms (TDDP4); the 16-amplitude copy keeps two
+constexpr int upd_blocks_per_sm(int nb) { return nb == 2 ? 2 : 3; }
 inline size_t gf_upd_smem(size_t prog, int nLS, int nb) {
     return gf_align16(prog) + gf_align16(sizeof(gf_ls_slot) * (size_t)std::max(1, nLS)) + sizeof(double) * (GF_THREADS / 32) * 16 * nb * GF_UPD_TS;
 }
