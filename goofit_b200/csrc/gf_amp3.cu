@@ -8,6 +8,7 @@
 
 struct gf_amp3_state {
     int node = -1, n_res = 0, slot = -1;
+    int td = 0; // GF_OP_AMP3_TD: two cached planes per resonance (A_i at (m12, m13), B_i at (m13, m12)), six sums per ordered pair
     long ld = 0, n_events = 0;
     double2 *d_waves = nullptr;
     // normalisation grid cache
@@ -49,6 +50,9 @@ __device__ inline gf_decay3 gf_load_decay3(const double *c) {
 #ifndef GF_WAVES_BLOCKS
 #define GF_WAVES_BLOCKS 2 // measured: 2 blocks/SM at 128 registers beats 3 at 80 (spills)
 #endif
+// TD: the time-dependent amplitude caches every resonance twice, at the point and at the point with m12 and m13 exchanged
+// (the D0bar amplitude; SpecialWaveCalculator.cu:15-68); observables are dtime, sigma_t, m12, m13, event number, ...
+template <bool TD>
 __global__ void __launch_bounds__(GF_THREADS, GF_WAVES_BLOCKS)
     k_amp3_waves(const gf_dev_view V, int node, unsigned long long mask, double2 *waves, long ld) {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -59,7 +63,7 @@ __global__ void __launch_bounds__(GF_THREADS, GF_WAVES_BLOCKS)
     const int32_t *ob = P.ints + nd.obs_off;
     const int nres = in[1];
     const gf_decay3 D = gf_load_decay3(P.consts + nd.con_off);
-    const double *c12 = P.cols[ob[0]], *c13 = P.cols[ob[1]];
+    const double *c12 = P.cols[ob[TD ? 2 : 0]], *c13 = P.cols[ob[TD ? 3 : 1]];
     __shared__ gf_amp3_shared S;
     gf_amp3_prepare(S, P, in + 2, nres, mask, D);
     __syncthreads();
@@ -69,15 +73,22 @@ __global__ void __launch_bounds__(GF_THREADS, GF_WAVES_BLOCKS)
         bool inside = gf_in_dalitz(m12, m13, D.M, D.d1, D.d2, D.d3);
         double m23 = D.M * D.M + D.d1 * D.d1 + D.d2 * D.d2 + D.d3 * D.d3 - m12 - m13;
         // written once, next read by another kernel: streaming stores
-        gf_amp3_point(S, P, in + 2, D, inside, m12, m13, m23, [&](int i, double2 w) { __stcs(waves + (size_t)i * ld + e, w); });
+        if(!TD)
+            gf_amp3_point(S, P, in + 2, D, inside, m12, m13, m23, [&](int i, double2 w) { __stcs(waves + (size_t)i * ld + e, w); });
+        else {
+            gf_amp3_point(S, P, in + 2, D, inside, m12, m13, m23, [&](int i, double2 w) { __stcs(waves + (size_t)(2 * i) * ld + e, w); });
+            gf_amp3_point(S, P, in + 2, D, inside, m13, m12, m23, [&](int i, double2 w) { __stcs(waves + (size_t)(2 * i + 1) * ld + e, w); });
+        }
     }
 }
 
 // Bin centres as SpecialResonanceIntegrator.cu:60-77, including its use of the m12 bin count for the
 // m13 step (slot [2] read twice) — identical for square grids.
+// TD (SpecialDalitzIntegrator.cu:52-86): the m13 step uses the m13 bin count, and both A_i and B_i are kept per bin
+template <bool TD>
 __global__ void __launch_bounds__(GF_THREADS, 1) // <= 57 600 bins: latency-bound, registers are free
     k_amp3_grid(const gf_dev_view V, int node, int eff_first, int eff_root, unsigned long long mask, double lo12,
-                double hi12, int n12, double lo13, double hi13, long n_bins, double2 *gridB, double *gridEff) {
+                double hi12, int n12, double lo13, double hi13, int n13, long n_bins, double2 *gridB, double *gridEff) {
     extern __shared__ __align__(16) unsigned char smem[];
     gf_sprog P = gf_stage_program(V, smem);
     __syncthreads();
@@ -98,18 +109,23 @@ __global__ void __launch_bounds__(GF_THREADS, 1) // <= 57 600 bins: latency-boun
         m12 *= (b12 + 0.5);
         m12 += lo12;
         double m13 = hi13 - lo13;
-        m13 /= n12;
+        m13 /= TD ? n13 : n12;
         m13 *= (b13 + 0.5);
         m13 += lo13;
         bool inside = gf_in_dalitz(m12, m13, D.M, D.d1, D.d2, D.d3);
         double m23 = D.M * D.M + D.d1 * D.d1 + D.d2 * D.d2 + D.d3 * D.d3 - m12 - m13;
-        gf_amp3_point(S, P, in + 2, D, inside, m12, m13, m23, [&](int i, double2 w) { gridB[(size_t)i * n_bins + b] = w; });
+        if(!TD)
+            gf_amp3_point(S, P, in + 2, D, inside, m12, m13, m23, [&](int i, double2 w) { gridB[(size_t)i * n_bins + b] = w; });
+        else {
+            gf_amp3_point(S, P, in + 2, D, inside, m12, m13, m23, [&](int i, double2 w) { gridB[(size_t)(2 * i) * n_bins + b] = w; });
+            gf_amp3_point(S, P, in + 2, D, inside, m13, m12, m23, [&](int i, double2 w) { gridB[(size_t)(2 * i + 1) * n_bins + b] = w; });
+        }
         gf_evt_vals evt;
 #pragma unroll
         for(int k = 0; k < GF_MAX_OBS; k++) evt.v[k] = 0;
         evt.i = b;
-        evt.v[ob[0]] = m12;
-        evt.v[ob[1]] = m13;
+        evt.v[ob[TD ? 2 : 0]] = m12;
+        evt.v[ob[TD ? 3 : 1]] = m13;
         gridEff[b] = gf_eval_tree(P, V, eff_first, eff_root, evt);
     }
 }
@@ -166,20 +182,54 @@ __global__ void __launch_bounds__(GF_THREADS)
     }
 }
 
+// Amp3Body_TD: one block per ORDERED pair (i, j): sums over bins of eff x {A_i A_j*, A_i B_j*, B_i B_j*} in a fixed order
+// (SpecialDalitzIntegrator.cu:15-51; A_i B_j* is not Hermitian in (i, j), so all n^2 pairs are summed as upstream does)
+__global__ void __launch_bounds__(GF_THREADS)
+    k_amp3td_gram(const double2 *grid, const double *gridEff, long n_bins, int nres, const int *pairs, double *I) {
+    __shared__ double red[32];
+    const int i = pairs[2 * blockIdx.x], j = pairs[2 * blockIdx.x + 1];
+    const double2 *Ai = grid + (size_t)(2 * i) * n_bins, *Bi = grid + (size_t)(2 * i + 1) * n_bins;
+    const double2 *Aj = grid + (size_t)(2 * j) * n_bins, *Bj = grid + (size_t)(2 * j + 1) * n_bins;
+    double s[6] = {0, 0, 0, 0, 0, 0};
+    for(long b = threadIdx.x; b < n_bins; b += blockDim.x) {
+        const double2 ai = Ai[b], bi = Bi[b], aj = Aj[b], bj = Bj[b];
+        const double e = gridEff[b];
+        s[0] += (ai.x * aj.x + ai.y * aj.y) * e; // ai conj(aj)
+        s[1] += (ai.y * aj.x - ai.x * aj.y) * e;
+        s[2] += (ai.x * bj.x + ai.y * bj.y) * e; // ai conj(bj)
+        s[3] += (ai.y * bj.x - ai.x * bj.y) * e;
+        s[4] += (bi.x * bj.x + bi.y * bj.y) * e; // bi conj(bj)
+        s[5] += (bi.y * bj.x - bi.x * bj.y) * e;
+    }
+#pragma unroll
+    for(int k = 0; k < 6; ++k) {
+        const double r = gf_block_sum(s[k], red);
+        if(threadIdx.x == 0) I[6 * (i * nres + j) + k] = r;
+    }
+}
+
 static int amp3_check(gf_ctx *c, int node, gf_amp3_state **out, bool create) {
     if(!c) return gf_fail("null ctx");
-    if(node < 0 || node >= (int)c->h_nodes.size() || c->h_nodes[node].op != GF_OP_AMP3)
+    if(node < 0 || node >= (int)c->h_nodes.size() || (c->h_nodes[node].op != GF_OP_AMP3 && c->h_nodes[node].op != GF_OP_AMP3_TD))
         return gf_fail("gf_amp3: node is not an Amp3Body record");
     const gf_node &nd = c->h_nodes[node];
-    if(nd.nint < 2 || nd.ncon < 6 || nd.nobs < 3) return gf_fail("gf_amp3: malformed Amp3Body record");
+    const int td = nd.op == GF_OP_AMP3_TD ? 1 : 0;
+    if(nd.nint < 2 || nd.ncon < 6 || nd.nobs < (td ? 5 : 3)) return gf_fail("gf_amp3: malformed Amp3Body record");
     int nres = c->h_ints[nd.int_off + 1];
-    if(nres < 1 || nres > 64 || nd.nint < 2 + nres) return gf_fail("gf_amp3: 1..64 resonances");
+    if(nres < 1 || nres > 64 || nd.nint < 2 + nres + td) return gf_fail("gf_amp3: 1..64 resonances");
+    if(td) {
+        if(nd.npar < 5 + 2 * nres) return gf_fail("gf_amp3: Amp3Body_TD needs tau, x, y, deltax, deltay and one coefficient pair per resonance");
+        const int rn = c->h_ints[nd.int_off + 2 + nres];
+        if(rn < 0 || rn >= (int)c->h_nodes.size() || (c->h_nodes[rn].op != GF_OP_TRES_TRUTH && c->h_nodes[rn].op != GF_OP_TRES_3GAUSS))
+            return gf_fail("gf_amp3: not a decay-time resolution record");
+    }
     int slot = c->h_ints[nd.int_off];
     if(slot < 0 || slot >= GF_MAX_AUX) return gf_fail("gf_amp3: bad aux slot");
     gf_amp3_state *s = find_amp3(c, node, create);
     if(!s) return gf_fail("gf_amp3: gf_amp3_alloc not called for this node");
     s->n_res = nres;
     s->slot = slot;
+    s->td = td;
     *out = s;
     return 0;
 }
@@ -194,12 +244,16 @@ extern "C" int gf_amp3_alloc(gf_ctx *c, int node, size_t n_events) {
     s->n_events = (long)n_events;
     s->ld = (long)((n_events + 15) & ~size_t(15));
     if(s->ld == 0) s->ld = 16;
-    GF_CUDA(cudaMalloc(&s->d_waves, sizeof(double2) * (size_t)s->ld * s->n_res));
-    GF_CUDA(cudaMemsetAsync(s->d_waves, 0, sizeof(double2) * (size_t)s->ld * s->n_res, c->stream));
-    if(!s->d_I) GF_CUDA(cudaMalloc(&s->d_I, sizeof(double) * 2 * s->n_res * s->n_res));
+    const size_t planes = (size_t)s->n_res * (1 + s->td);
+    GF_CUDA(cudaMalloc(&s->d_waves, sizeof(double2) * (size_t)s->ld * planes));
+    GF_CUDA(cudaMemsetAsync(s->d_waves, 0, sizeof(double2) * (size_t)s->ld * planes, c->stream));
+    if(!s->d_I) {
+        GF_CUDA(cudaMalloc(&s->d_I, sizeof(double) * 6 * s->n_res * s->n_res));
+        GF_CUDA(cudaMemsetAsync(s->d_I, 0, sizeof(double) * 6 * s->n_res * s->n_res, c->stream));
+    }
     if(!s->d_pairs) {
-        GF_CUDA(cudaMalloc(&s->d_pairs, sizeof(int) * s->n_res * (s->n_res + 1)));
-        GF_CUDA(cudaMallocHost(&s->h_pairs, sizeof(int) * s->n_res * (s->n_res + 1)));
+        GF_CUDA(cudaMalloc(&s->d_pairs, sizeof(int) * 2 * s->n_res * s->n_res));
+        GF_CUDA(cudaMallocHost(&s->h_pairs, sizeof(int) * 2 * s->n_res * s->n_res));
     }
     c->view.aux[s->slot] = s->d_waves;
     c->view.aux_ld[s->slot] = s->ld;
@@ -221,9 +275,10 @@ extern "C" int gf_amp3_cache_waves(gf_ctx *c, int node, const uint8_t *redo_mask
     if(!mask || s->n_events == 0) return 0;
     cudaSetDevice(c->device);
     size_t sm = gf_prog_smem(c);
-    if(sm > 48 * 1024) cudaFuncSetAttribute(k_amp3_waves, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    auto kern = s->td ? k_amp3_waves<true> : k_amp3_waves<false>;
+    if(sm > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
     int blocks = gf_grid_blocks(c, s->n_events, GF_WAVES_BLOCKS);
-    k_amp3_waves<<<blocks, GF_THREADS, sm, c->stream>>>(c->view, node, mask, s->d_waves, s->ld);
+    kern<<<blocks, GF_THREADS, sm, c->stream>>>(c->view, node, mask, s->d_waves, s->ld);
     c->launches++;
     GF_CUDA(cudaGetLastError());
     return 0;
@@ -245,7 +300,7 @@ extern "C" int gf_amp3_integrals(gf_ctx *c, int node, const uint8_t *redo_mask, 
         GF_CUDA(cudaStreamSynchronize(c->stream));
         cudaFree(s->d_gridB); cudaFree(s->d_gridEff);
         s->d_gridB = nullptr; s->d_gridEff = nullptr;
-        GF_CUDA(cudaMalloc(&s->d_gridB, sizeof(double2) * (size_t)n_bins * s->n_res));
+        GF_CUDA(cudaMalloc(&s->d_gridB, sizeof(double2) * (size_t)n_bins * s->n_res * (1 + s->td)));
         GF_CUDA(cudaMalloc(&s->d_gridEff, sizeof(double) * (size_t)n_bins));
         s->n_bins = n_bins;
         for(int k = 0; k < 6; k++) s->spec[k] = lo_hi_n6[k];
@@ -253,33 +308,36 @@ extern "C" int gf_amp3_integrals(gf_ctx *c, int node, const uint8_t *redo_mask, 
         s->grid_valid = true;
     }
     size_t sm = gf_prog_smem(c);
-    if(sm > 48 * 1024) cudaFuncSetAttribute(k_amp3_grid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    auto gridk = s->td ? k_amp3_grid<true> : k_amp3_grid<false>;
+    if(sm > 48 * 1024) cudaFuncSetAttribute(gridk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
     int eff_first = eff_root - c->h_nodes[eff_root].size + 1;
     // As in the reference, integrals (and the efficiency they fold in) are refreshed only for flagged
     // resonances; with nothing flagged the cached I_ij are returned (Amp3Body.cu:266-275,313-316).
     if(mask) {
         int blocks = gf_grid_blocks(c, n_bins, 2);
-        k_amp3_grid<<<blocks, GF_THREADS, sm, c->stream>>>(c->view, node, eff_first, eff_root, mask, lo_hi_n6[0],
-                                                          lo_hi_n6[1], n12, lo_hi_n6[3], lo_hi_n6[4], n_bins,
-                                                          s->d_gridB, s->d_gridEff);
+        gridk<<<blocks, GF_THREADS, sm, c->stream>>>(c->view, node, eff_first, eff_root, mask, lo_hi_n6[0], lo_hi_n6[1], n12, lo_hi_n6[3],
+                                                     lo_hi_n6[4], n13, n_bins, s->d_gridB, s->d_gridEff);
         c->launches++;
         GF_CUDA(cudaGetLastError());
     }
     // pairs whose integral must be refreshed: either member flagged (Amp3Body.cu:313-316)
     std::vector<int> pairs;
     for(int i = 0; i < s->n_res; i++)
-        for(int j = i; j < s->n_res; j++)
+        for(int j = s->td ? 0 : i; j < s->n_res; j++)
             if(((mask >> i) & 1ull) || ((mask >> j) & 1ull)) { pairs.push_back(i); pairs.push_back(j); }
     if(!pairs.empty()) {
         // the pinned list is free again: every earlier call ended with the stream synchronisation below
         std::memcpy(s->h_pairs, pairs.data(), sizeof(int) * pairs.size());
         GF_CUDA(cudaMemcpyAsync(s->d_pairs, s->h_pairs, sizeof(int) * pairs.size(), cudaMemcpyHostToDevice, c->stream));
-        k_amp3_gram<<<(int)(pairs.size() / 2), GF_THREADS, 0, c->stream>>>(s->d_gridB, s->d_gridEff, n_bins, s->n_res,
-                                                                         s->d_pairs, s->d_I);
+        if(s->td)
+            k_amp3td_gram<<<(int)(pairs.size() / 2), GF_THREADS, 0, c->stream>>>(s->d_gridB, s->d_gridEff, n_bins, s->n_res, s->d_pairs, s->d_I);
+        else
+            k_amp3_gram<<<(int)(pairs.size() / 2), GF_THREADS, 0, c->stream>>>(s->d_gridB, s->d_gridEff, n_bins, s->n_res,
+                                                                             s->d_pairs, s->d_I);
         c->launches++;
         GF_CUDA(cudaGetLastError());
     }
-    GF_CUDA(cudaMemcpyAsync(I_re_im, s->d_I, sizeof(double) * 2 * s->n_res * s->n_res, cudaMemcpyDeviceToHost, c->stream));
+    GF_CUDA(cudaMemcpyAsync(I_re_im, s->d_I, sizeof(double) * (s->td ? 6 : 2) * s->n_res * s->n_res, cudaMemcpyDeviceToHost, c->stream));
     GF_CUDA(cudaStreamSynchronize(c->stream));
     return 0;
 }
@@ -287,7 +345,7 @@ extern "C" int gf_amp3_integrals(gf_ctx *c, int node, const uint8_t *redo_mask, 
 extern "C" int gf_amp3_get_wave(gf_ctx *c, int node, int res, double *out_re_im, size_t n_events) {
     gf_amp3_state *s;
     if(amp3_check(c, node, &s, false)) return 1;
-    if(res < 0 || res >= s->n_res) return gf_fail("gf_amp3_get_wave: bad resonance index");
+    if(res < 0 || res >= s->n_res * (1 + s->td)) return gf_fail("gf_amp3_get_wave: bad resonance index");
     if((long)n_events != s->n_events) return gf_fail("gf_amp3_get_wave: size mismatch");
     cudaSetDevice(c->device);
     GF_CUDA(cudaMemcpyAsync(out_re_im, s->d_waves + (size_t)res * s->ld, sizeof(double2) * n_events,
@@ -302,6 +360,7 @@ extern "C" int gf_amp3_wave_gram(gf_ctx *c, int node, double *W_re_im) {
     gf_amp3_state *s;
     if(amp3_check(c, node, &s, false)) return 1;
     if(!s->d_waves) return gf_fail("gf_amp3_wave_gram: no cached waves (gf_amp3_cache_waves)");
+    if(s->td) return gf_fail("gf_amp3_wave_gram: fit fractions are defined for the time-integrated Amp3Body");
     if(!W_re_im) return gf_fail("gf_amp3_wave_gram: null output");
     cudaSetDevice(c->device);
     const int n = s->n_res, npairs = n * (n + 1) / 2, nv = 2 * npairs * GF_WG_CHUNKS;

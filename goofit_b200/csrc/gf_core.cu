@@ -109,6 +109,7 @@ static int program_class(const gf_ctx *c, int first, int root) {
         case GF_OP_CONVOLVE: has |= GF_HAS_CONV; break;
         case GF_OP_AMP3: has |= GF_HAS_AMP3; break;
         case GF_OP_AMP4: has |= GF_HAS_AMP4; break;
+        case GF_OP_AMP3_TD: has |= GF_HAS_AMP3_TD | GF_HAS_3GAUSS; break;
         case GF_OP_AMP4_TD: {
             has |= GF_HAS_AMP4_TD;
             const int32_t *in = c->h_ints.data() + c->h_nodes[k].int_off; // ints[4] -> {resolution record, flags}
@@ -351,7 +352,7 @@ extern "C" int gf_validate_program(const gf_node *nodes, int n_nodes, int n_cons
                     return gf_fail("gf_set_program: combiner without child norm slots, node " + std::to_string(k));
                 if(nd.op == GF_OP_ADD && nd.npar < nd.nchild - 1) return gf_fail("gf_set_program: AddPdf weights, node " + std::to_string(k));
                 if(nd.op == GF_OP_ADD_EXT && nd.npar < nd.nchild) return gf_fail("gf_set_program: AddPdf weights, node " + std::to_string(k));
-                if(nd.op >= GF_OP_AMP3 && nd.op <= GF_OP_AMP4_TD) pops = 1; // the efficiency
+                if(nd.op >= GF_OP_AMP3 && nd.op <= GF_OP_AMP3_TD) pops = 1; // the efficiency
                 if(sp < pops) return gf_fail("gf_set_program: value-stack underflow at node " + std::to_string(k));
                 sp += 1 - pops;
                 if(sp > peak) peak = sp;

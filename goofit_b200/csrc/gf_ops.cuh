@@ -282,7 +282,7 @@ __device__ inline void gf_amp4td_AB(const double *p, const int32_t *flags, int n
 // the larger batches spill under the 64-register cap)
 #define GF_TD_CH 4
 // GF_HAS_3GAUSS: the Amp4Body_TD node may carry a ThreeGaussResolution (else TruthResolution only)
-enum : int { GF_HAS_CONV = 1, GF_HAS_AMP3 = 2, GF_HAS_AMP4 = 4, GF_HAS_AMP4_TD = 8, GF_HAS_3GAUSS = 16, GF_HAS_ALL = 31 };
+enum : int { GF_HAS_CONV = 1, GF_HAS_AMP3 = 2, GF_HAS_AMP4 = 4, GF_HAS_AMP4_TD = 8, GF_HAS_3GAUSS = 16, GF_HAS_AMP3_TD = 32, GF_HAS_ALL = 63 };
 
 // Post-order evaluation of nodes [first, last]; returns the root's raw value.
 template <int HAS = GF_HAS_ALL, class Evt>
@@ -410,6 +410,46 @@ __device__ inline double gf_eval_tree(const gf_sprog &P, const gf_dev_view &V, i
             double ret = gf_tres<(HAS & GF_HAS_3GAUSS) != 0>(rn.op, P.params + rn.par_off, nA + nB, nA - nB, t3re, t3im, p[0], dtime, p[1],
                                                              p[2], sigma);
             st[sp++] = ret * eff;
+        } break;
+        case GF_OP_AMP3_TD: if constexpr((HAS & GF_HAS_AMP3_TD) != 0) { // physics/Amp3Body_TD.cu:40-256
+            const double *c = P.consts + nd.con_off;
+            const int32_t *ob = P.ints + nd.obs_off;
+            double eff = st[--sp];
+            double m12 = evt(ob[2]), m13 = evt(ob[3]);
+            double ret = 0;
+            if(gf_in_dalitz(m12, m13, c[0], c[1], c[2], c[3])) {
+                long e = evt.event_number(ob[4]);
+                int nres = in[1];
+                const double2 *w = static_cast<const double2 *>(P.aux[in[0]]) + e;
+                long ld = P.aux_ld[in[0]];
+                double Ar = 0, Ai = 0, Br = 0, Bi = 0;
+#pragma unroll 2
+                for(int i = 0; i < nres; ++i) {
+                    double2 a = __ldg(w + (size_t)(2 * i) * ld), b = __ldg(w + (size_t)(2 * i + 1) * ld);
+                    double cr = p[5 + 2 * i], ci = p[6 + 2 * i];
+                    Ar += a.x * cr - a.y * ci; Ai += a.x * ci + a.y * cr; // ai * amp
+                    Br += b.x * cr - b.y * ci; Bi += b.x * ci + b.y * cr;
+                }
+                double tau = p[0], x = p[1], y = p[2];
+                int tag = nd.nobs > 6 ? (int)evt(ob[6]) : 0; // D0 / D0bar: x, y shifted by +- (deltax, deltay)
+                if(tag == 1) { x += p[3]; y += p[4]; }
+                else if(tag == -1) { x -= p[3]; y -= p[4]; }
+                double time = evt(ob[0]), sigma = evt(ob[1]);
+                double term1 = (Ar * Ar + Ai * Ai) + (Br * Br + Bi * Bi), term2 = (Ar * Ar + Ai * Ai) - (Br * Br + Bi * Bi);
+                double abr = Ar * Br + Ai * Bi, abi = Ai * Br - Ar * Bi; // A conj(B)
+                const gf_node &rn = P.nodes[in[2 + nres]];
+                const double *rp = P.params + rn.par_off;
+                ret = gf_tres<(HAS & GF_HAS_3GAUSS) != 0>(rn.op, rp, term1, term2, abr, abi, tau, time, x, y, sigma);
+                double mistag = nd.nobs > 5 ? evt(ob[5]) : 0.0;
+                if(mistag > 0) { // the wrongly tagged fraction: A <-> B at fixed world-average mixing (Amp3Body_TD.cu:226-245)
+                    const double xfix = 0.0039, yfix = 0.0065, taufix = 0.4101;
+                    ret *= (1 - 2 * mistag);
+                    ret += mistag * gf_tres<(HAS & GF_HAS_3GAUSS) != 0>(rn.op, rp, term1, -term2, abr, -abi, taufix, time, xfix, yfix, sigma);
+                    ret += mistag * gf_tres<(HAS & GF_HAS_3GAUSS) != 0>(rn.op, rp, term1, term2, abr, abi, taufix, time, xfix, yfix, sigma);
+                }
+                ret *= eff;
+            }
+            st[sp++] = ret;
         } break;
         default: st[sp++] = 0.0; break;
         }

@@ -19,6 +19,8 @@ class AmpComponent : public GooPdf {
 
 class ResonancePdf : public AmpComponent {
     friend class Amp3Body;
+    friend class Amp3Body_TD;
+    friend class Amp3Body_IS;
 
   public:
     Variable get_amp_real() const { return amp_real; }
@@ -161,6 +163,59 @@ class Amp3Body : public Amp3BodyBase { // Amp3Body.h:43-111
     int totalEventSize{3};
     int generation_offset{0};
     std::unique_ptr<UnbinnedDataSet> generated; // keeps the events of the last GenerateSig alive while they are the dataset
+};
+
+struct DecayInfo3t : public DecayInfo3 { // DalitzPlotHelpers.h:99-112
+    Variable _tau, _xmixing, _ymixing, _deltax, _deltay;
+    DecayInfo3t(Variable tau, Variable xmixing, Variable ymixing, Variable deltax, Variable deltay)
+        : _tau(tau)
+        , _xmixing(xmixing)
+        , _ymixing(ymixing)
+        , _deltax(deltax)
+        , _deltay(deltay) {}
+};
+class MixingTimeResolution;
+/// Time-dependent Dalitz amplitude with D0 mixing (Amp3Body_TD.h / Amp3Body_TD.cu:40-760): per event
+/// R(|A|^2 + |B|^2, |A|^2 - |B|^2, A conj(B); tau, t, x, y, sigma_t) x efficiency with A = sum c_i A_i(m12, m13), B = sum c_i
+/// A_i(m13, m12), x and y shifted by +-(deltax, deltay) according to the charm tag, and a mistagged fraction at fixed
+/// world-average mixing. Observables: dtime, sigma_t, m12, m13, event number, mistag, charm tag (both mandatory, as upstream
+/// dereferences them in its constructor).
+class Amp3Body_TD : public Amp3BodyBase {
+  public:
+    Amp3Body_TD(std::string n, Observable _dtime, Observable _sigmat, Observable m12, Observable m13, EventNumber eventNumber,
+                DecayInfo3t decay, MixingTimeResolution *r, GooPdf *eff, Observable *mistag = nullptr, Observable *charmtag = nullptr);
+    /// upstream's constructor for several resolution functions binned in the D0 mass: its device code never selects among them
+    /// ("Multiple resolution functions not supported yet!", Amp3Body_TD.cu:396), so the first one is used, as there
+    Amp3Body_TD(std::string n, Observable _dtime, Observable _sigmat, Observable m12, Observable m13, EventNumber eventNumber,
+                DecayInfo3t decay, std::vector<MixingTimeResolution *> &r, GooPdf *eff, Observable md0, Observable *mistag,
+                Observable *charmtag);
+    fptype normalize() override;
+    void setDataSize(unsigned int dataSize, unsigned int evtSize = 5, unsigned int offset = 0);
+    void setForceIntegrals(bool f = true) { forceRedoIntegrals = f; }
+    void setD0Fraction(fptype d0fraction);
+    fptype getD0Fraction() { return _D0Fraction; }
+    DecayInfo3t &getDecayInfo() { return decayInfo; }
+    static void resetCacheCounter() {}
+    /// (A_i, B_i) of resonance i at every event
+    std::vector<std::complex<fptype>> getCachedWaveA(size_t i) const;
+    std::vector<std::complex<fptype>> getCachedWaveB(size_t i) const;
+    void emitAux(detail::ProgramBuilder &B) override;
+    int emit(detail::ProgramBuilder &B) override;
+    void afterProgram() override;
+
+  protected:
+    void ensureCache();
+    void init(MixingTimeResolution *r, Observable *mistag, Observable *charmtag);
+    DecayInfo3t decayInfo;
+    Observable _m12, _m13;
+    std::unique_ptr<Observable> _mistag;
+    MixingTimeResolution *resolution;
+    GooPdf *efficiency;
+    std::vector<fptype> integrals; // six numbers per ordered pair (i, j)
+    fptype _D0Fraction{0.5};
+    bool forceRedoIntegrals{true};
+    bool cacheAllocated{false};
+    int totalEventSize{7};
 };
 
 /// Host helper that evaluates the PDF on the Dalitz grid and draws toy events from it

@@ -153,6 +153,25 @@ void init_physics4(py::module &m) {
                       Variable, Variable>(),
              "cf"_a, "tf"_a, "cb"_a, "cs"_a, "tb"_a, "ts"_a, "ob"_a, "os"_a, "sb"_a, "common_bias_offset"_a, "common_width_scale"_a,
              "common_bias_offset2"_a, "common_width_scale2"_a);
+    // time-dependent Dalitz amplitude (python/PDFs/physics/Amp3Body_TD.cpp, DalitzPlotHelpers.cpp upstream)
+    py::class_<DecayInfo3t, DecayInfo3>(m, "DecayInfo3t")
+        .def(py::init<Variable, Variable, Variable, Variable, Variable>(), "tau"_a, "xmixing"_a, "ymixing"_a, "deltax"_a, "deltay"_a)
+        .def_readonly("_tau", &DecayInfo3t::_tau)
+        .def_readonly("_xmixing", &DecayInfo3t::_xmixing)
+        .def_readonly("_ymixing", &DecayInfo3t::_ymixing)
+        .def_readonly("_deltax", &DecayInfo3t::_deltax)
+        .def_readonly("_deltay", &DecayInfo3t::_deltay);
+    py::class_<Amp3Body_TD, Amp3BodyBase>(m, "Amp3Body_TD")
+        .def(py::init<std::string, Observable, Observable, Observable, Observable, EventNumber, DecayInfo3t, MixingTimeResolution *, GooPdf *,
+                      Observable *, Observable *>(),
+             "n"_a, "dtime"_a, "sigmat"_a, "m12"_a, "m13"_a, "eventNumber"_a, "decay"_a, "r"_a, "eff"_a, "mistag"_a = nullptr,
+             "charmtag"_a = nullptr, py::keep_alive<1, 8>(), py::keep_alive<1, 9>(), py::keep_alive<1, 10>())
+        .def("setDataSize", &Amp3Body_TD::setDataSize, "dataSize"_a, "evtSize"_a = 5, "offset"_a = 0)
+        .def("setForceIntegrals", &Amp3Body_TD::setForceIntegrals, "f"_a = true)
+        .def("setD0Fraction", &Amp3Body_TD::setD0Fraction, "d0fraction"_a)
+        .def("getD0Fraction", &Amp3Body_TD::getD0Fraction)
+        .def("getCachedWaveA", [](const Amp3Body_TD &a, size_t i) { return py::array(py::cast(a.getCachedWaveA(i))); }, "i"_a)
+        .def("getCachedWaveB", [](const Amp3Body_TD &a, size_t i) { return py::array(py::cast(a.getCachedWaveB(i))); }, "i"_a);
     py::class_<DecayInfo4t, DecayInfo4>(m, "DecayInfo4t")
         .def(py::init<Variable, Variable, Variable, Variable>(), "tau"_a, "xmixing"_a, "ymixing"_a, "SqWStoRSrate"_a)
         .def_readonly("_tau", &DecayInfo4t::_tau)

@@ -72,6 +72,9 @@ enum gf_op {
     GF_OP_AMP3 = 48,        /* Amp3Body.cu:60  child: efficiency; ints: amp3 id */
     GF_OP_AMP4,             /* Amp4Body.cu:53 */
     GF_OP_AMP4_TD,          /* Amp4Body_TD.cu:167 */
+    GF_OP_AMP3_TD,          /* Amp3Body_TD.cu:40-256  child: efficiency; consts as GF_OP_AMP3; params tau, x, y, deltax, deltay, then (re, im) per
+                               resonance; obs dtime, sigma_t, m12, m13, event number [, mistag [, charm tag]]; ints {aux slot, n_res,
+                               res_node[n_res], resolution record}. Cached planes: A_i at (m12, m13) in plane 2i, B_i at (m13, m12) in 2i+1 */
     /* resonance / lineshape / spin-factor records (never on the per-event stack) */
     GF_OP_RES_RBW = 64,     /* resonances/RBW.cu:9 plainBW<1>; params mass,width; consts spin,cyc,norm */
     GF_OP_RES_RBW_SYM,      /* plainBW<2> */
@@ -143,6 +146,9 @@ int gf_amp3_alloc(gf_ctx *, int node, size_t n_events);
 int gf_amp3_cache_waves(gf_ctx *, int node, const uint8_t *redo_mask);
 int gf_amp3_integrals(gf_ctx *, int node, const uint8_t *redo_mask, const double *lo_hi_n6, int eff_root,
                       double *I_re_im /* n_res*n_res*2, row i col j */);
+/* For a GF_OP_AMP3_TD node (Amp3Body_TD.cu:592-760) the same three calls keep TWO planes per resonance (A_i, B_i: SpecialWaveCalculator.cu:15-68),
+ * gf_amp3_integrals returns SIX numbers per ordered pair, I[(i*n_res+j)*6 + ..] = sum_bins eff x {Re, Im of A_i A_j*, A_i B_j*, B_i B_j*}
+ * (SpecialDalitzIntegrator.cu:15-136), and gf_amp3_get_wave takes a plane index 0 .. 2 n_res - 1. */
 int gf_amp3_get_wave(gf_ctx *, int node, int res, double *out_re_im, size_t n_events);
 /* Hermitian matrix of the cached waves, W[(i*n_res+j)*2+{re,im}] = sum_e w_i(e) conj(w_j(e)), summed over ranks when a communicator
  * is attached: the device side of Amp3Body::fit_fractions (Amp3Body.cu:376-428, one transform_reduce of CoefSumFunctor per pair) */

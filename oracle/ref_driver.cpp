@@ -23,6 +23,7 @@
 #include <goofit/PDFs/combine/ConvolutionPdf.h>
 #include <goofit/PDFs/combine/ProdPdf.h>
 #include <goofit/PDFs/physics/Amp3Body.h>
+#include <goofit/PDFs/physics/Amp3Body_TD.h>
 #define private public // test infrastructure: read (and, for the at-scale cases, inject) the reference's private MC sample
 #define protected public
 #include <goofit/PDFs/physics/Amp4Body.h>
@@ -980,6 +981,106 @@ static void case_kmatrix() {
     }
 }
 
+// ---- Amp3Body_TD: time-dependent Dalitz amplitude with mixing (Amp3Body_TD.cu:40-760) -----------------------------------------
+// D0 -> pi0 pi+ pi- with the three rho(770) charge states, the f0(980) and a non-resonant term; Dalitz points of case_zoo3 (same
+// seed), decay time ~ exp(-t / tau), sigma_t uniform, charm tag +1 / -1 / 0 in turn, one mistag value for all events (upstream's
+// normalisation reads the Observable object's own value: Amp3Body_TD.cu:735-744).
+static void td3_one(const std::string &tag, int three_gauss, double mistag_value) {
+    Observable dtime{"dtime", 0, 10}, sigmat{"sigmat", -3, 3}, m12{"m12", 0, 3}, m13{"m13", 0, 3};
+    Observable mistag{"mistag", 0, 1}, charmtag{"charmtag", -2, 2};
+    EventNumber eventNumber{"eventNumber"};
+    m12.setNumBins(120);
+    m13.setNumBins(120);
+    Variable tau("tau", 0.4101, 0.001, 0.3, 0.5), xm("xmixing", 0.0049, 0.001, -0.1, 0.1), ym("ymixing", 0.0061, 0.001, -0.1, 0.1);
+    Variable dx("deltax", 0.0011, 0.001, -0.1, 0.1), dy("deltay", -0.0007, 0.001, -0.1, 0.1);
+    DecayInfo3t info{tau, xm, ym, dx, dy};
+    info.motherMass = _mD0; info.daug1Mass = piZeroMass; info.daug2Mass = piPlusMass; info.daug3Mass = piPlusMass;
+    info.meson_radius = 1.5; info.mother_meson_radius = 5.0;
+    Variable rhoM("rho_mass", 0.7758, 0.01, 0.7, 0.8), rhoW("rho_width", 0.1503, 0.01, 0.1, 0.2);
+    Variable f0M("f0_980_mass", 0.980, 0.01, 0.8, 1.2), f0W("f0_980_width", 0.044, 0.001, 0.001, 0.08);
+    Variable c4r("rhom_amp_real", 0.714, 0.001, 0, 0);
+    info.resonances = {
+        new Resonances::NonRes("nonr", Variable("nonr_amp_real", -0.5595), Variable("nonr_amp_imag", 0.108761)),
+        new Resonances::RBW("rhop", Variable("rhop_amp_real", 1.0), Variable("rhop_amp_imag", 0.0), rhoM, rhoW, 1, PAIR_12),
+        new Resonances::RBW("rho0", Variable("rho0_amp_real", 0.565), Variable("rho0_amp_imag", 0.164), rhoM, rhoW, 1, PAIR_23),
+        new Resonances::RBW("rhom", c4r, Variable("rhom_amp_imag", -0.025), rhoM, rhoW, 1, PAIR_13),
+        new Resonances::RBW("f0_980", Variable("f0_amp_real", 0.008 * (-_mD02)), Variable("f0_amp_imag", -0.013 * (-_mD02)), f0M, f0W, 0, PAIR_23),
+    };
+    MixingTimeResolution *res;
+    if(three_gauss) {
+        auto R = [&](const char *n, double v) { return Variable(n, v); };
+        res = new ThreeGaussResolution(R("coreFrac", 0.8), R("tailFrac", 0.15), R("coreBias", 0.05), R("coreScale", 1.0), R("tailBias", 0.1),
+                                       R("tailScale", 2.0), R("outlBias", -0.05), R("outlScale", 5.0), R("selBias", 0.02), R("cbo", 0.01),
+                                       R("cws", 1.1), R("cbo2", -0.02), R("cws2", 0.9));
+    } else
+        res = new TruthResolution();
+    Variable one("constantOne", 1), zero("constantZero", 0);
+    auto *eff = new PolynomialPdf("constantEff", std::vector<Observable>{m12, m13}, std::vector<Variable>{one}, std::vector<Variable>{zero, zero}, 0);
+    auto *dp  = new Amp3Body_TD("tddalitz", dtime, sigmat, m12, m13, eventNumber, info, res, eff, &mistag, &charmtag);
+    UnbinnedDataSet d({dtime, sigmat, m12, m13, eventNumber, mistag, charmtag});
+    std::mt19937_64 gen(77), gent(4711);
+    std::uniform_real_distribution<double> u(0, 3), u1(0, 1);
+    std::vector<double> T, S, C;
+    while(d.getNumEvents() < 500) {
+        double a = u(gen), b = u(gen);
+        if(!inDalitz(a, b, _mD0, piZeroMass, piPlusMass, piPlusMass)) continue;
+        double t;
+        do t = -0.4101 * std::log(1.0 - u1(gent)); while(t >= 10.0);
+        double sg = 0.02 + 0.06 * u1(gent);
+        int n = d.getNumEvents();
+        double ct = n % 3 == 0 ? 1.0 : (n % 3 == 1 ? -1.0 : 0.0);
+        m12.setValue(a); m13.setValue(b); eventNumber.setValue(n);
+        dtime.setValue(t); sigmat.setValue(sg); mistag.setValue(mistag_value); charmtag.setValue(ct);
+        T.push_back(t); S.push_back(sg); C.push_back(ct);
+        d.addEvent();
+    }
+    if(tag == "td3") { // one copy of the inputs (the Dalitz points are those of zoo3)
+        save_npy("td3.dtime", T); save_npy("td3.sigmat", S); save_npy("td3.charmtag", C);
+    }
+    dp->setData(&d);
+    dp->setDataSize(d.getNumEvents(), 7);
+    put(tag + ".nll", dp->calculateNLL());
+    put(tag + ".integral", 1.0 / dp->getNormalization());
+    {
+        std::vector<double> waves;
+        for(size_t i = 0; i < info.resonances.size(); i++) {
+            thrust::host_vector<WaveHolder_s> h = dp->getCachedWaveNoCopy(i);
+            for(size_t e = 0; e < h.size(); e++) {
+                waves.push_back(h[e].ai_real); waves.push_back(h[e].ai_imag); waves.push_back(h[e].bi_real); waves.push_back(h[e].bi_imag);
+            }
+        }
+        save_npy(tag + ".waves", waves.data(), info.resonances.size(), 4 * d.getNumEvents());
+    }
+    { // per-event probabilities through a ProdPdf wrapper, as for the time-integrated amplitude (DalitzPlotter.h:60-63)
+        ProdPdf wrap{"wrap", {dp}};
+        wrap.setData(&d);
+        dp->setDataSize(d.getNumEvents(), 7);
+        auto probs = wrap.getCompProbsAtDataPoints();
+        save_npy(tag + ".prob", probs[0]);
+    }
+    dp->setFitControl(std::make_shared<UnbinnedNllFit>());
+    dp->setData(&d);
+    dp->setDataSize(d.getNumEvents(), 7);
+    put(tag + ".nll_again", dp->calculateNLL());
+    // mixing parameters and one coefficient move: caches and integrals are reused
+    rhoM.setChanged(false); rhoW.setChanged(false); f0M.setChanged(false); f0W.setChanged(false);
+    dp->updateVariable(xm, 0.0123); dp->updateVariable(ym, -0.0071); dp->updateVariable(dx, 0.002); dp->updateVariable(tau, 0.4153);
+    dp->updateVariable(c4r, 0.75);
+    dp->updateParameters();
+    put(tag + ".nll_mix_moved", dp->calculateNLL());
+    put(tag + ".integral_mix_moved", 1.0 / dp->getNormalization());
+    // the rho mass moves: three of the five waves and their integrals are redone
+    rhoM.setChanged(true);
+    dp->updateVariable(rhoM, 0.77); dp->updateParameters();
+    put(tag + ".nll_mass_moved", dp->calculateNLL());
+    put(tag + ".integral_mass_moved", 1.0 / dp->getNormalization());
+}
+static void case_td3() {
+    td3_one("td3", 0, 0.0);
+    td3_one("td3mis", 0, 0.05);
+    td3_one("td3g3", 1, 0.05);
+}
+
 static void case_dp4_fit() {
     DP4Model *M = make_dp4(60000, false);
     UnbinnedDataSet cand({M->m12, M->m34, M->cos12, M->cos34, M->phi, M->eventNumber});
@@ -1622,6 +1723,7 @@ int main(int argc, char **argv) {
             if(only == "all" || only == "zoo3") case_zoo3();
             if(only == "all" || only == "zoo4") case_zoo4();
             if(only == "all" || only == "kmatrix") case_kmatrix();
+            if(only == "all" || only == "td3") case_td3();
             if(only == "all" || only == "dalitzfit") case_dalitz_fit();
             if(only == "all" || only == "dp4") case_dp4();
             if(only == "all" || only == "dp4fit") case_dp4_fit();

@@ -528,3 +528,46 @@ class KMatrix4:
     def dataset(self, cols5):
         n = len(cols5[0])
         return dataset_from_columns(self.observables, list(cols5) + [np.arange(n, dtype=np.float64)])
+
+
+class TD3:
+    """Amp3Body_TD on D0 -> pi0 pi+ pi- (oracle/ref_driver.cpp td3_one): non-resonant term, three rho(770) charge states, f0(980)"""
+
+    def __init__(self, three_gauss=False, grid=120):
+        k = self.keep = Keep()
+        O, V = gf.Observable, gf.Variable
+        self.dtime, self.sigmat = O("dtime", 0, 10), O("sigmat", -3, 3)
+        self.m12, self.m13 = O("m12", 0, 3), O("m13", 0, 3)
+        self.mistag, self.charmtag = O("mistag", 0, 1), O("charmtag", -2, 2)
+        self.evt = gf.EventNumber("eventNumber")
+        self.m12.numbins = self.m13.numbins = grid
+        self.tau, self.xm, self.ym = V("tau", 0.4101, 0.001, 0.3, 0.5), V("xmixing", 0.0049, 0.001, -0.1, 0.1), V("ymixing", 0.0061, 0.001, -0.1, 0.1)
+        self.dx, self.dy = V("deltax", 0.0011, 0.001, -0.1, 0.1), V("deltay", -0.0007, 0.001, -0.1, 0.1)
+        info = self.info = gf.DecayInfo3t(self.tau, self.xm, self.ym, self.dx, self.dy)
+        info.motherMass, info.daug1Mass, info.daug2Mass, info.daug3Mass = 1.86484, 0.1349766, 0.13957018, 0.13957018
+        info.meson_radius, info.mother_meson_radius = 1.5, 5.0
+        MD02 = 1.86484 ** 2
+        self.rhoM, self.rhoW = V("rho_mass", 0.7758, 0.01, 0.7, 0.8), V("rho_width", 0.1503, 0.01, 0.1, 0.2)
+        self.f0M, self.f0W = V("f0_980_mass", 0.980, 0.01, 0.8, 1.2), V("f0_980_width", 0.044, 0.001, 0.001, 0.08)
+        self.c4r = V("rhom_amp_real", 0.714, 0.001, 0, 0)
+        R = gf.Resonances
+        self.res = [k(R.NonRes("nonr", V("nonr_amp_real", -0.5595), V("nonr_amp_imag", 0.108761))),
+                    k(R.RBW("rhop", V("rhop_amp_real", 1.0), V("rhop_amp_imag", 0.0), self.rhoM, self.rhoW, 1, 0)),
+                    k(R.RBW("rho0", V("rho0_amp_real", 0.565), V("rho0_amp_imag", 0.164), self.rhoM, self.rhoW, 1, 2)),
+                    k(R.RBW("rhom", self.c4r, V("rhom_amp_imag", -0.025), self.rhoM, self.rhoW, 1, 1)),
+                    k(R.RBW("f0_980", V("f0_amp_real", 0.008 * (-MD02)), V("f0_amp_imag", -0.013 * (-MD02)), self.f0M, self.f0W, 0, 2))]
+        info.resonances = self.res
+        if three_gauss:
+            vals = [("coreFrac", 0.8), ("tailFrac", 0.15), ("coreBias", 0.05), ("coreScale", 1.0), ("tailBias", 0.1), ("tailScale", 2.0),
+                    ("outlBias", -0.05), ("outlScale", 5.0), ("selBias", 0.02), ("cbo", 0.01), ("cws", 1.1), ("cbo2", -0.02), ("cws2", 0.9)]
+            self.resol = k(gf.ThreeGaussResolution(*[V(n, v) for n, v in vals]))
+        else:
+            self.resol = k(gf.TruthResolution())
+        self.eff = k(gf.PolynomialPdf("constantEff", [self.m12, self.m13], [V("constantOne", 1)], [V("constantZero", 0)] * 2, 0))
+        self.dp = gf.Amp3Body_TD("tddalitz", self.dtime, self.sigmat, self.m12, self.m13, self.evt, info, self.resol, self.eff, self.mistag, self.charmtag)
+        self.observables = [self.dtime, self.sigmat, self.m12, self.m13, self.evt, self.mistag, self.charmtag]
+
+    def dataset(self, dtime, sigmat, m12, m13, mistag_value, charmtag):
+        n = len(m12)
+        self.mistag.value = mistag_value  # the normalisation reads the Observable's own value (Amp3Body_TD.cu:735-744)
+        return dataset_from_columns(self.observables, [dtime, sigmat, m12, m13, np.arange(n, dtype=np.float64), np.full(n, mistag_value), charmtag])

@@ -295,6 +295,54 @@ def test_zoo3_resonance_shapes(golden):
     assert rel(1.0 / s.getNormalization(), golden["zoo3.integral_moved"]) < 1e-12
 
 
+@pytest.mark.parametrize("tag,three_gauss,mistag", [("td3", False, 0.0), ("td3mis", False, 0.05), ("td3g3", True, 0.05)])
+def test_amp3body_td(golden, tag, three_gauss, mistag):
+    """Amp3Body_TD (Amp3Body_TD.cu:40-760, SpecialWaveCalculator.cu, SpecialDalitzIntegrator.cu): cached (A_i, B_i) planes, six grid
+    integrals per ordered pair, D0 / D0bar mixing shifts by charm tag, mistagged fraction, Truth and ThreeGauss resolution."""
+    from models import TD3
+    M = TD3(three_gauss=three_gauss)
+    d = M.dataset(golden.arr("td3.dtime"), golden.arr("td3.sigmat"), golden.arr("zoo3.m12"), golden.arr("zoo3.m13"), mistag, golden.arr("td3.charmtag"))
+    dp = M.dp
+    dp.setData(d)
+    dp.setDataSize(len(d), 7)
+    nll = dp.calculateNLL()
+    ref = golden.arr("td3.waves")  # [resonance, 4 * event] = (ai_re, ai_im, bi_re, bi_im)
+    for i in range(5):
+        a, b = np.asarray(dp.getCachedWaveA(i)), np.asarray(dp.getCachedWaveB(i))
+        ra, rb = ref[i][0::4] + 1j * ref[i][1::4], ref[i][2::4] + 1j * ref[i][3::4]
+        assert np.max(np.abs(a - ra) / np.maximum(np.abs(ra), 1e-300)) < 1e-11, i
+        assert np.max(np.abs(b - rb) / np.maximum(np.abs(rb), 1e-300)) < 1e-11, i
+    assert rel(1.0 / dp.getNormalization(), golden[tag + ".integral"]) < 1e-11
+    assert rel(nll, golden[tag + ".nll"]) < RTOL_NLL
+    wrap = gf.ProdPdf("wrap", [dp])
+    wrap.setData(d)
+    dp.setDataSize(len(d), 7)
+    probs = wrap.getCompProbsAtDataPoints()
+    want = golden.arr(tag + ".prob")
+    np.testing.assert_allclose(probs[0], want, rtol=1e-10, atol=1e-15 * float(np.median(want)) * 16)
+    dp.setFitControl(gf.UnbinnedNllFit())
+    dp.setData(d)
+    dp.setDataSize(len(d), 7)
+    assert dp.calculateNLL() == nll
+    for v in (M.rhoM, M.rhoW, M.f0M, M.f0W):
+        v.changed = False
+    dp.updateVariable(M.xm, 0.0123)
+    dp.updateVariable(M.ym, -0.0071)
+    dp.updateVariable(M.dx, 0.002)
+    dp.updateVariable(M.tau, 0.4153)
+    dp.updateVariable(M.c4r, 0.75)
+    dp.updateParameters()
+    before = gf.launch_count()
+    assert rel(dp.calculateNLL(), golden[tag + ".nll_mix_moved"]) < RTOL_NLL
+    assert gf.launch_count() - before == 1, "mixing parameters and coefficients move: the NLL kernel only"
+    assert rel(1.0 / dp.getNormalization(), golden[tag + ".integral_mix_moved"]) < 1e-11
+    M.rhoM.changed = True
+    dp.updateVariable(M.rhoM, 0.77)
+    dp.updateParameters()
+    assert rel(dp.calculateNLL(), golden[tag + ".nll_mass_moved"]) < RTOL_NLL
+    assert rel(1.0 / dp.getNormalization(), golden[tag + ".integral_mass_moved"]) < 1e-11
+
+
 def test_kmatrix_three_and_four_body(golden):
     """The pi pi S-wave K-matrix (resonances/kMatrix.cu:19-121, lineshapes/kMatrix.cu:18-119, kMatrixUtils.cu): five channels, five
     poles, LU inverse of 1 - i adler K rho. Same events and MC sample as the zoo3 / zoo4 cases."""
