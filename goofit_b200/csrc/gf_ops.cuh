@@ -190,6 +190,38 @@ __device__ inline void gf_tres_gauss(double &P1, double &P2, double &P3, double 
     P1 = NormG * 0.5 * (Ipy + Imy);
     P3 = NormG * 0.5 * (Ipy - Imy);
 }
+// sin, cos and e^b - 1 for the SMALL arguments of mixing fits (x t / tau, y t / tau with x, y ~ 1e-2): Taylor polynomials in
+// Horner form, exact to an ulp or two for |a| <= 0.25 (first neglected terms: a^16/16! < 2e-23 for cos, a^17/17! relative 1e-21
+// for sin, b^15/15! relative 3e-21 for expm1), instead of the libm routines with their range reduction (about 150 instructions
+// for the three). Larger arguments take the libm path.
+__device__ __forceinline__ void gf_sincos_small(double a, double &sn, double &cs) {
+    const double a2 = a * a;
+    cs = fma(a2, fma(a2, fma(a2, fma(a2, fma(a2, fma(a2, fma(a2, -1.0 / 87178291200.0, 1.0 / 479001600.0), -1.0 / 3628800.0), 1.0 / 40320.0), -1.0 / 720.0),
+                             1.0 / 24.0),
+                     -0.5),
+             1.0);
+    sn = a * fma(a2, fma(a2, fma(a2, fma(a2, fma(a2, fma(a2, fma(a2, -1.0 / 1307674368000.0, 1.0 / 6227020800.0), -1.0 / 39916800.0), 1.0 / 362880.0), -1.0 / 5040.0),
+                                 1.0 / 120.0),
+                         -1.0 / 6.0),
+                 1.0);
+}
+__device__ __forceinline__ double gf_expm1_small(double b) {
+    double p = 1.0 / 87178291200.0; // 1/14!
+    p = fma(p, b, 1.0 / 6227020800.0);
+    p = fma(p, b, 1.0 / 479001600.0);
+    p = fma(p, b, 1.0 / 39916800.0);
+    p = fma(p, b, 1.0 / 3628800.0);
+    p = fma(p, b, 1.0 / 362880.0);
+    p = fma(p, b, 1.0 / 40320.0);
+    p = fma(p, b, 1.0 / 5040.0);
+    p = fma(p, b, 1.0 / 720.0);
+    p = fma(p, b, 1.0 / 120.0);
+    p = fma(p, b, 1.0 / 24.0);
+    p = fma(p, b, 1.0 / 6.0);
+    p = fma(p, b, 0.5);
+    p = fma(p, b, 1.0);
+    return p * b;
+}
 // op = GF_OP_TRES_TRUTH (TruthResolution.cu:8-28) or GF_OP_TRES_3GAUSS (ThreeGaussResolution.cu:62-125; p = 13 parameters)
 template <bool WITH_3GAUSS = true>
 __device__ inline double gf_tres(int op, const double *p, double coshterm, double costerm, double sinhterm, double sinterm,
@@ -200,9 +232,16 @@ __device__ inline double gf_tres(int op, const double *p, double coshterm, doubl
         // accurate to an ulp or two for the small a = y t/tau of mixing fits (no e^a - e^-a cancellation)
         double ret = 0;
         dtime /= tau;
-        double sn, cs;
-        sincos(x * dtime, &sn, &cs);
-        const double u = expm1(y * dtime), ui = u / (u + 1.0);
+        double sn, cs, u;
+        const double ax = x * dtime, by = y * dtime;
+        if(fabs(ax) <= 0.25 && fabs(by) <= 0.25) {
+            gf_sincos_small(ax, sn, cs);
+            u = gf_expm1_small(by);
+        } else {
+            sincos(ax, &sn, &cs);
+            u = expm1(by);
+        }
+        const double ui = u / (u + 1.0);
         const double sh = 0.5 * (u + ui), ch = 1.0 + 0.5 * u * ui;
         ret += coshterm * ch;
         ret += costerm * cs;
