@@ -1626,6 +1626,8 @@ static int bench(const std::string &config, size_t N, int K, int W, const ScaleO
         after_setdata = [M, &d] { M->dp->setDataSize(d->getNumEvents(), 8); };
         movers = M->mix;
         report = movers;
+        if(opt.lsmove) // C5 as configured floats the rho / K* masses and widths too (TDDP4.cu:50-53): report them after a fit
+            for(auto &v : M->lsvars) report.push_back(v);
         if(opt.lsmove) ls_var = &M->lsvars[2];
         probs = [M] { return M->signal->getCompProbsAtDataPoints()[0]; };
     } else {

@@ -261,3 +261,38 @@ def test_dp4_fit_at_scale():
           % (res.NFcn(), rf["nfcn"], res.Fval(), rf["fval"], p.max(), fm.lastFitSeconds(), rf["wall_s"]))
     assert rf["valid"] and bool(fm)
     assert p.max() < 0.01, p
+
+
+def test_tddp4_fit_floating_lineshapes_at_scale():
+    """BASELINE configs[4] as configured: tau, x, y AND the rho / K*(892) masses and widths float (TDDP4.cu:50-53),
+    so most Minuit calls move a lineshape and go through the one-pass update (k_amp4_update, DMMA Gram). 3x10^5 model-drawn data
+    events + 3x10^5 MC normalisation events on both arms, seven free parameters."""
+    n = n_mc = 300_000
+    mc = scale.unweighted_phase_space(gf, n_mc, 199)
+    M = TDDP4(three_gauss=False, float_ls=True, float_mix=True)
+    ev = scale.tddp4_model_events(gf, M, n, 9, mc)
+    names = list(scale.NAMES5) + ["dtime", "sigmat"]
+    cols = {nm: ev[k] for k, nm in enumerate(names)}
+    cols.update({"mc_" + nm: mc[k] for k, nm in enumerate(scale.NAMES5)})
+    d = scale.write_columns(scale.scratch_dir("tddp4fit"), cols)
+    try:
+        ref = scale.run_reference("tddp4", 0, 1, 0, data=d, fit=True, lsmove=True)
+    finally:
+        shutil.rmtree(d, ignore_errors=True)
+    M = TDDP4(three_gauss=False, float_ls=True, float_mix=True)
+    M.dp.setNormEvents(mc)
+    data = M.dataset(list(ev))
+    M.signal.setData(data)
+    M.dp.setDataSize(len(data), 8)
+    assert scale.rel(M.signal.calculateNLL(), ref["first_nll"]) < TOL
+    l0 = gf.launch_count()
+    fm, res = scale.fit_with(gf, M.signal)
+    rf = ref["fit"]
+    assert rf["names"] == ["tau", "xmixing", "ymixing", "rho_mass", "rho_width", "KstarM", "KstarW"], rf["names"]
+    vals = [v.value for v in list(M.mix) + list(M.lsvars)]
+    p = scale.pulls(vals, rf["values"], rf["errors"])
+    print("tddp4 fit (7 free, lineshapes floating) 3e5+3e5: nfcn %d vs %d, fval %.6f vs %.6f, max pull %.2e, wall %.2f s vs reference %.1f s, %.1f launches/call"
+          % (res.NFcn(), rf["nfcn"], res.Fval(), rf["fval"], p.max(), fm.lastFitSeconds(), rf["wall_s"], (gf.launch_count() - l0) / max(res.NFcn(), 1)))
+    assert bool(fm) == rf["valid"]
+    assert p.max() < 0.01, p
+    assert scale.rel(res.Fval(), rf["fval"]) < 1e-9
