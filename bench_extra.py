@@ -385,6 +385,28 @@ def reference_side(gf, lib, ctx, n=1_000_000):
                                    "sample": "%d data + %d MC events x 3 FCN calls, unmodified reference (OMP backend, all host cores)" % (n, n)}
     except Exception as e:
         out.setdefault("dp4_fit", {"error": str(e)[:300]})
+    try:  # ---- TDDP4 as configured (C5): tau, x, y and the rho / K* masses and widths free; most calls move a lineshape
+        from models import TDDP4
+        m = n // 2
+        mc = scale.unweighted_phase_space(gf, m, 199)
+        M = TDDP4(three_gauss=False, float_ls=True, float_mix=True)
+        ev = scale.tddp4_model_events(gf, M, m, 9, mc)
+        names = list(scale.NAMES5) + ["dtime", "sigmat"]
+        cols = {nm: ev[k] for k, nm in enumerate(names)}
+        cols.update({"mc_" + nm: mc[k] for k, nm in enumerate(scale.NAMES5)})
+        M = TDDP4(three_gauss=False, float_ls=True, float_mix=True)
+        M.dp.setNormEvents(mc)
+        data = M.dataset(list(ev))
+        M.signal.setData(data)
+        M.dp.setDataSize(len(data), 8)
+        M.signal.calculateNLL()
+        n_keep, n = n, m
+        out["tddp4_fit"] = both("tddp4fit", "tddp4", cols, M.signal, list(M.mix) + list(M.lsvars), ref_kwargs={"lsmove": True})
+        n = n_keep
+        out["tddp4_fit"]["events"] = m
+        out["tddp4_fit"]["note"] = "%d data + %d MC events; 7 free parameters incl. lineshape masses and widths (TDDP4.cu:50-53)" % (m, m)
+    except Exception as e:
+        out["tddp4_fit"] = {"error": str(e)[:300]}
     try:  # ---- TDDP4 per-call cost of the reference
         rng = np.random.default_rng(5)
         mc = scale.unweighted_phase_space(gf, n, 7)

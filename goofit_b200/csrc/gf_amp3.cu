@@ -48,7 +48,7 @@ __device__ inline gf_decay3 gf_load_decay3(const double *c) {
 }
 
 #ifndef GF_WAVES_BLOCKS
-#define GF_WAVES_BLOCKS 2 // measured: 2 blocks/SM at 128 registers beats 3 at 80 (spills)
+#define GF_WAVES_BLOCKS 3 // measured (round 2, after the spills were removed): 3 blocks/SM at 80 registers 1.92 ms, 2 at 128 registers 2.07 ms
 #endif
 // TD: the time-dependent amplitude caches every resonance twice, at the point and at the point with m12 and m13 exchanged
 // (the D0bar amplitude; SpecialWaveCalculator.cu:15-68); observables are dtime, sigma_t, m12, m13, event number, ...

@@ -10,6 +10,41 @@ struct gf_decay3 { // Amp3Body node consts: Amp3Body.cu:144-149
 
 enum { GF_PAIR_12 = 0, GF_PAIR_13 = 1, GF_PAIR_23 = 2 }; // DalitzPlotHelpers.h:81
 
+// Branch-free reciprocal for the shared-work path (gf_pair_prepare / gf_rbw_term): the hardware seed (MUFU.RCP64H, ~2^-20) and one
+// cubic Newton step, e = 1 - x r, r <- r (1 + e + e^2): relative error ~e^3 + rounding, i.e. within an ulp or two of the
+// correctly rounded quotient, for finite non-zero normal x - which every denominator on that path is (s > 0 inside the Dalitz
+// boundary, 1 + z^2, A^2 + B^2). The IEEE division of `a / b` costs the same arithmetic plus a range check, a reconvergence
+// region and a slow-path call per division; with ~80 divisions per event those, not the FP64 pipe, bounded k_amp3_waves.
+#ifndef GF_FAST_RCP
+#define GF_FAST_RCP 1
+#endif
+__device__ __forceinline__ double gf_rcp(double x) {
+#if !GF_FAST_RCP
+    return 1.0 / x;
+#endif
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+    const double e = fma(-x, r, 1.0);
+    const double t = fma(e, e, e);
+    r = fma(r, t, r);
+    const double e2 = fma(-x, r, 1.0); // one linear step more: the seed is only guaranteed to ~2^-20
+    return fma(r, e2, r);
+}
+// gf_cm_mom / gf_cm_mom_mother with 1/s (and sqrt(s)) supplied by the caller, who shares them over everything a pair needs
+__device__ __forceinline__ double gf_cm_mom_s(double rs, double inv_s, double a, double b) {
+    double k1 = 1 - (a + b) * (a + b) * inv_s;
+    k1 = k1 >= 0 ? sqrt(k1) : 1;
+    double k2 = 1 - (a - b) * (a - b) * inv_s;
+    k2 = k2 >= 0 ? sqrt(k2) : 1;
+    return 0.5 * rs * k1 * k2;
+}
+__device__ __forceinline__ double gf_cm_mom_mother_s(double s, double inv_s, double dm, double inv_dm, double d3m) {
+    double k1 = 1 - (dm + d3m) * (dm + d3m) * inv_s;
+    k1 = k1 >= 0 ? sqrt(k1) : 1;
+    double k2 = 1 - (dm - d3m) * (dm - d3m) * inv_s;
+    k2 = k2 >= 0 ? sqrt(k2) : 1;
+    return 0.5 * s * k1 * k2 * inv_dm;
+}
 // Resonance.cu:50-63
 __device__ inline double gf_cm_mom(double s, double a, double b) {
     double k1 = 1 - (a + b) * (a + b) / s;
@@ -60,6 +95,29 @@ __device__ inline double gf_spin3(int spin, const gf_decay3 &D, double m12, doub
         double t2 = mA * mA - mB * mB;
         x *= ((sAB - (2 * mA * mA) - (2 * mB * mB)) + mf * (t2 * t2));
         x /= 3;
+        s -= x;
+    }
+    return s;
+}
+
+// the same with mf = 1 / sAB supplied (shared per pair)
+__device__ __forceinline__ double gf_spin3_mf(int spin, const gf_decay3 &D, double m12, double m13, double m23, int cyc, double mf) {
+    if(spin == 0) return 1;
+    double mA = cyc == GF_PAIR_12 ? D.d1 : (cyc == GF_PAIR_13 ? D.d3 : D.d2);
+    double mB = cyc == GF_PAIR_12 ? D.d2 : (cyc == GF_PAIR_13 ? D.d1 : D.d3);
+    double mC = cyc == GF_PAIR_12 ? D.d3 : (cyc == GF_PAIR_13 ? D.d2 : D.d1);
+    double sAC = cyc == GF_PAIR_12 ? m13 : (cyc == GF_PAIR_13 ? m23 : m12);
+    double sBC = cyc == GF_PAIR_12 ? m23 : (cyc == GF_PAIR_13 ? m12 : m13);
+    double sAB = cyc == GF_PAIR_12 ? m12 : (cyc == GF_PAIR_13 ? m13 : m23);
+    double s = -1;
+    s *= ((sBC - sAC) + (mf * (D.M * D.M - mC * mC) * (mA * mA - mB * mB)));
+    if(spin == 2) {
+        s *= s;
+        double t1 = D.M * D.M - mC * mC;
+        double x = ((sAB - (2 * D.M * D.M) - (2 * mC * mC)) + mf * (t1 * t1));
+        double t2 = mA * mA - mB * mB;
+        x *= ((sAB - (2 * mA * mA) - (2 * mB * mB)) + mf * (t2 * t2));
+        x *= (1.0 / 3.0);
         s -= x;
     }
     return s;
@@ -393,21 +451,23 @@ __device__ inline void gf_pair_prepare(gf_pair_inv &Q, const gf_pair_need &need,
     gf_pair_masses(cyc, D, da, db, bach);
     Q.s = cyc == GF_PAIR_12 ? m12 : (cyc == GF_PAIR_13 ? m13 : m23);
     Q.rs = sqrt(Q.s);
-    Q.q = gf_cm_mom(Q.s, da, db);
-    Q.qMn = need.norm ? gf_cm_mom_mother(Q.s, D.M, bach) : 0.0;
+    // 1/s once per pair: it serves the two-body momenta (four divisions upstream), the Zemach factors (two) and 1/sqrt(s)
+    const double inv_s = gf_rcp(Q.s);
+    Q.inv_rs = Q.rs * inv_s;
+    Q.q = gf_cm_mom_s(Q.rs, inv_s, da, db);
+    Q.qMn = need.norm ? gf_cm_mom_mother_s(Q.s, inv_s, D.M, 1.0 / D.M, bach) : 0.0;
     Q.qMp = need.plain ? gf_cm_mom(D.M * D.M, Q.rs, bach) : 0.0;
-    Q.inv_rs = 1.0 / Q.rs;
     Q.z1 = Q.z2 = 1.0;
     Q.bw1 = Q.bw2 = Q.bwM1 = Q.bwM2 = 1.0;
-    if(need.maxspin >= 1) Q.z1 = gf_spin3(1, D, m12, m13, m23, cyc);
-    if(need.maxspin >= 2) Q.z2 = gf_spin3(2, D, m12, m13, m23, cyc);
+    if(need.maxspin >= 1) Q.z1 = gf_spin3_mf(1, D, m12, m13, m23, cyc, inv_s);
+    if(need.maxspin >= 2) Q.z2 = gf_spin3_mf(2, D, m12, m13, m23, cyc, inv_s);
     if(need.norm && need.maxspin >= 1) {
-        Q.bw1 = 1.0 / gf_damp_sq_norm(Q.q, 1, D.rad);
-        Q.bwM1 = 1.0 / gf_damp_sq_norm(Q.qMn, 1, D.mrad);
+        Q.bw1 = gf_rcp(gf_damp_sq_norm(Q.q, 1, D.rad));
+        Q.bwM1 = gf_rcp(gf_damp_sq_norm(Q.qMn, 1, D.mrad));
     }
     if(need.norm && need.maxspin >= 2) {
-        Q.bw2 = 1.0 / gf_damp_sq_norm(Q.q, 2, D.rad);
-        Q.bwM2 = 1.0 / gf_damp_sq_norm(Q.qMn, 2, D.mrad);
+        Q.bw2 = gf_rcp(gf_damp_sq_norm(Q.q, 2, D.rad));
+        Q.bwM2 = gf_rcp(gf_damp_sq_norm(Q.qMn, 2, D.mrad));
     }
 }
 __device__ inline double gf_pow_odd(double r, int spin) { // r^(2 spin + 1)
@@ -433,10 +493,13 @@ __device__ inline double2 gf_rbw_term(const gf_res_inv &R, const gf_pair_inv &P,
     }
     double A = R.mass2 - P.s;
     double B = R.mw * gf_pow_odd(P.q * R.inv_q0, spin) * fr * P.inv_rs;
-    double C = 1.0 / (A * A + B * B);
+    double C = gf_rcp(A * A + B * B);
     double f = sqrt(fr * frM) * (spin == 0 ? 1.0 : (spin == 2 ? P.z2 : P.z1)) * C;
     return make_double2(A * f, B * f);
 }
+#ifndef GF_PAIR_UNROLL
+#define GF_PAIR_UNROLL 0 // measured: unrolling the three pairs keeps all of their state live (468 B of spills, 205 local loads per warp-event); 2.50 -> 2.07 ms without
+#endif
 #ifndef GF_RBW_ILP
 #define GF_RBW_ILP 1 // measured on 10^7 events x 16 resonances: 1: 2.35 ms, 2: 2.49 ms, 4: 2.37 ms (tools/ab_compare.sh): the chains already overlap across warps
 #endif
@@ -444,9 +507,12 @@ __device__ inline double2 gf_rbw_term(const gf_res_inv &R, const gf_pair_inv &P,
 struct gf_amp3_shared {
     gf_res_inv res[GF_MAX_RES];
     gf_pair_need need[3];
-    int n_pair[3], n_other;
+    int n_pair[3], n_other, n_flat;
     unsigned char by_pair[3][GF_MAX_RES]; // flagged plain RBWs grouped by resonant pair
-    unsigned char other[GF_MAX_RES];      // flagged GS / Gauss / NonRes / symmetrised RBW: evaluated unshared
+    unsigned char other[GF_MAX_RES];      // flagged GS / Gauss / symmetrised RBW / ...: evaluated unshared, out of line
+    unsigned char flat[GF_MAX_RES];       // flagged NonRes (NonRes.cu:8-11: the constant 1): no call, so that the ordinary Dalitz
+                                          // model makes no out-of-line call per event (the spills around it were ~160 local
+                                          // loads and stores per event in the round-2 profile)
 };
 // block-cooperative: fill S for the flagged resonances; call from all threads, then __syncthreads()
 __device__ inline void gf_amp3_prepare(gf_amp3_shared &S, const gf_sprog &P, const int32_t *res_nodes, int nres,
@@ -470,17 +536,25 @@ __device__ inline void gf_amp3_prepare(gf_amp3_shared &S, const gf_sprog &P, con
         S.need[c] = n;
         S.n_pair[c] = cnt;
     } else if(threadIdx.x == 3) {
-        int cnt = 0;
-        for(int i = 0; i < nres; ++i)
-            if(((mask >> i) & 1ull) && S.res[i].op != GF_OP_RES_RBW) S.other[cnt++] = (unsigned char)i;
+        int cnt = 0, nf = 0;
+        for(int i = 0; i < nres; ++i) {
+            if(!((mask >> i) & 1ull) || S.res[i].op == GF_OP_RES_RBW) continue;
+            if(S.res[i].op == GF_OP_RES_NONRES) S.flat[nf++] = (unsigned char)i;
+            else S.other[cnt++] = (unsigned char)i;
+        }
         S.n_other = cnt;
+        S.n_flat = nf;
     }
 }
 // every flagged resonance at one Dalitz point; out(i, value) receives each amplitude exactly once
 template <class Out>
 __device__ inline void gf_amp3_point(const gf_amp3_shared &S, const gf_sprog &P, const int32_t *res_nodes,
                                      const gf_decay3 &D, bool inside, double m12, double m13, double m23, const Out &out) {
+#if GF_PAIR_UNROLL
 #pragma unroll
+#else
+#pragma unroll 1
+#endif
     for(int c = 0; c < 3; ++c) {
         const int n = S.n_pair[c];
         if(n == 0) continue;
@@ -501,6 +575,7 @@ __device__ inline void gf_amp3_point(const gf_amp3_shared &S, const gf_sprog &P,
             out(i, inside ? gf_rbw_term(S.res[i], Q, D) : make_double2(0.0, 0.0));
         }
     }
+    for(int k = 0; k < S.n_flat; ++k) out(S.flat[k], inside ? make_double2(1.0, 0.0) : make_double2(0.0, 0.0));
     for(int k = 0; k < S.n_other; ++k) {
         const int i = S.other[k];
         out(i, inside ? gf_resonance_cold(&P.nodes[res_nodes[i]], P.params, P.consts, &D, m12, m13, m23) : make_double2(0.0, 0.0));
