@@ -6,6 +6,7 @@
 //   spin factors              src/PDFs/physics/SpinFactors.cu:83-568, detail/SpinHelper.h
 #pragma once
 #include "gf_kmatrix.cuh"
+#include "gf_math.cuh"
 
 enum gf_ls_kind { GF_LS_RBW = 0, GF_LS_SBW, GF_LS_LASS, GF_LS_BUGG, GF_LS_BUGG3, GF_LS_ONE, GF_LS_NONRES, GF_LS_FLATTE, GF_LS_GLASS, GF_LS_FOCUS, GF_LS_KMATRIX, GF_LS_GSPLINE };
 // same order as the reference's SF_4Body enum (SpinFactors.h:18-35)
@@ -181,7 +182,7 @@ __device__ __forceinline__ gf_bl_set gf_bl_prepare(double z2, int L) {
     gf_bl_set B;
     B.z2 = z2;
     B.L = L;
-    B.inv_d = L == 0 ? 1.0 : 1.0 / (L == 1 ? 1 + z2 : z2 * z2 + 3 * z2 + 9);
+    B.inv_d = L == 0 ? 1.0 : gf_rcp(L == 1 ? 1 + z2 : z2 * z2 + 3 * z2 + 9);
     return B;
 }
 __device__ __forceinline__ double gf_bl_prime_s(const gf_bl_set &B, double z02) {
@@ -199,13 +200,13 @@ __device__ __forceinline__ double gf_bl_s(const gf_bl_set &B) {
 __device__ __forceinline__ double gf_bl2_s(const gf_bl_set &B) { return B.L <= 2 ? (B.L == 0 ? 1.0 : B.inv_d) : 0; }
 // BW.cu:14-69. Against the reference's operation sequence the per-event part shares reciprocals: 1/Mpair serves num / (4 M^2)
 // and mass / Mpair, 1 / prSq is parameter-only, and the Blatt-Weisskopf ratios share the reciprocal of their common
-// denominator: three divisions and two square roots per event instead of six and two. Each substitution moves the result by
+// denominator: three reciprocals (branch-free, gf_math.cuh) and two square roots per event instead of six divisions and two. Each substitution moves the result by
 // an ulp or two (the amplitudes are compared with the reference at 1e-10, the NLL at 1e-12: tests/test_parity_gpu.py).
 __device__ inline gf_cplx gf_ls_bw_pt(double Mpair, double mass, double width, int orbital, int FF, double meson_radius, const gf_bw_inv &I) {
     const int to2Lplus1 = 2 * orbital + 1;
     double M2 = Mpair * Mpair;
     double num = (M2 - I.mpsq) * (M2 - I.mmsq);
-    double rM = 1.0 / Mpair;
+    double rM = gf_rcp(Mpair);
     double pABSq = num * (0.25 * (rM * rM));
     double pratio = sqrt(pABSq * I.inv_prSq);
     double pr2J1 = 1;
@@ -222,7 +223,7 @@ __device__ inline gf_cplx gf_ls_bw_pt(double Mpair, double mass, double width, i
     double GofM = width * pr2J1 * mratio * thisFR;
     gf_cplx bw = gf_c(mass * mass - M2, mass * GofM);
     double den = (mass * mass - M2) * (mass * mass - M2) + mass * GofM * mass * GofM;
-    return ((sqrt(I.k * frFactor)) / den) * bw;
+    return ((sqrt(I.k * frFactor)) * gf_rcp(den)) * bw;
 }
 __device__ inline gf_cplx gf_ls_bw(double Mpair, double m1, double m2, double mass, double width, int orbital, int FF,
                                    double meson_radius) {
@@ -234,7 +235,7 @@ __device__ inline gf_cplx gf_ls_sbw_pt(double Mpair, double mass, double width, 
     double frFactor = 1;
     if(0 != orbital && 0 != FF) {
         double num = (M2 - I.mpsq) * (M2 - I.mmsq);
-        double pABSq = num / (4 * M2);
+        double pABSq = num * (0.25 * gf_rcp(M2));
         double r2 = meson_radius * meson_radius;
         const gf_bl_set B = gf_bl_prepare(pABSq * r2, orbital);
         frFactor = (FF == 1 ? gf_bl_s(B) : gf_bl_prime_s(B, I.prSq2 * r2));
@@ -243,7 +244,7 @@ __device__ inline gf_cplx gf_ls_sbw_pt(double Mpair, double mass, double width, 
     double GofM = width;
     gf_cplx bw = gf_c(mass * mass - M2, mass * GofM);
     double den = (mass * mass - M2) * (mass * mass - M2) + mass * GofM * mass * GofM;
-    return ((sqrt(I.k * frFactor)) / den) * bw;
+    return ((sqrt(I.k * frFactor)) * gf_rcp(den)) * bw;
 }
 __device__ inline gf_cplx gf_ls_sbw(double Mpair, double m1, double m2, double mass, double width, int orbital, int FF,
                                     double meson_radius) {
