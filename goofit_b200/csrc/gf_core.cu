@@ -348,10 +348,14 @@ extern "C" int gf_validate_program(const gf_node *nodes, int n_nodes, int n_cons
                 const gf_node &nd = nodes[k];
                 if(!is_eval(nd.op)) return gf_fail("gf_set_program: non-evaluable record inside the subtree of node " + std::to_string(r));
                 int pops = nd.op < GF_OP_ADD ? 0 : (nd.op == GF_OP_CONVOLVE ? 0 : nd.nchild);
-                if(nd.op >= GF_OP_ADD && nd.op <= GF_OP_PROD && (nd.nint < nd.nchild || nd.nchild < 1))
+                const bool combiner = (nd.op >= GF_OP_ADD && nd.op <= GF_OP_PROD) || (nd.op >= GF_OP_EVTW_ADD && nd.op <= GF_OP_MAPPED);
+                if(combiner && (nd.nint < nd.nchild || nd.nchild < 1))
                     return gf_fail("gf_set_program: combiner without child norm slots, node " + std::to_string(k));
                 if(nd.op == GF_OP_ADD && nd.npar < nd.nchild - 1) return gf_fail("gf_set_program: AddPdf weights, node " + std::to_string(k));
                 if(nd.op == GF_OP_ADD_EXT && nd.npar < nd.nchild) return gf_fail("gf_set_program: AddPdf weights, node " + std::to_string(k));
+                if(nd.op == GF_OP_EVTW_ADD && nd.nobs < nd.nchild - 1) return gf_fail("gf_set_program: EventWeightedAddPdf weight columns, node " + std::to_string(k));
+                if(nd.op == GF_OP_EVTW_ADD_EXT && nd.nobs < nd.nchild) return gf_fail("gf_set_program: EventWeightedAddPdf weight columns, node " + std::to_string(k));
+                if(nd.op == GF_OP_MAPPED && nd.nchild < 2) return gf_fail("gf_set_program: MappedPdf needs a mapping function and a component, node " + std::to_string(k));
                 if(nd.op >= GF_OP_AMP3 && nd.op <= GF_OP_AMP3_TD) pops = 1; // the efficiency
                 if(sp < pops) return gf_fail("gf_set_program: value-stack underflow at node " + std::to_string(k));
                 sp += 1 - pops;

@@ -374,6 +374,43 @@ __device__ inline double gf_eval_tree(const gf_sprog &P, const gf_dev_view &V, i
             sp -= n;
             st[sp++] = ret;
         } break;
+        case GF_OP_EVTW_ADD: { // combine/EventWeightedAddPdf.cu:8-40: the weights are event columns, not parameters
+            int n = nd.nchild;
+            const int32_t *ob = P.ints + nd.obs_off;
+            double ret = 0, tw = 0;
+            const double *ch = st + (sp - n);
+            for(int i = 0; i < n - 1; ++i) {
+                double w = evt(ob[i]);
+                tw += w;
+                ret += w * ch[i] * P.norms[in[i]];
+            }
+            ret += (1 - tw) * ch[n - 1] * P.norms[in[n - 1]];
+            sp -= n;
+            st[sp++] = ret;
+        } break;
+        case GF_OP_EVTW_ADD_EXT: { // EventWeightedAddPdf.cu:42-73
+            int n = nd.nchild;
+            const int32_t *ob = P.ints + nd.obs_off;
+            double ret = 0, tw = 0;
+            const double *ch = st + (sp - n);
+            for(int i = 0; i < n; ++i) {
+                double w = evt(ob[i]);
+                ret += w * ch[i] * P.norms[in[i]];
+                tw += w;
+            }
+            ret /= tw;
+            sp -= n;
+            st[sp++] = ret;
+        } break;
+        case GF_OP_MAPPED: { // combine/MappedPdf.cu:7-55: child 0 picks which of the other children is the value
+            int n = nd.nchild;
+            const double *ch = st + (sp - n);
+            int target = (int)floor(0.5 + ch[0]);
+            target = target < 0 ? 0 : (target > n - 2 ? n - 2 : target); // upstream walks off its tables for an index out of range
+            double ret = ch[1 + target] * P.norms[in[1 + target]];
+            sp -= n;
+            st[sp++] = ret;
+        } break;
         case GF_OP_CONVOLVE: if constexpr((HAS & GF_HAS_CONV) != 0) { // combine/ConvolutionPdf.cu:27-75 via the per-offset table (gf_conv.cu)
             // ints = {aux slot, model root, resolution root}; consts = lo, hi, step
             const double *c = P.consts + nd.con_off;

@@ -82,6 +82,24 @@ class AddPdf : public CombinePdf { // combine/AddPdf.h
     bool extended;
 };
 
+/// combine/EventWeightedAddPdf.h: AddPdf whose weights are per-event observables (the first observables of the record)
+class EventWeightedAddPdf : public CombinePdf {
+  public:
+    EventWeightedAddPdf(std::string n, std::vector<Observable> weights, std::vector<PdfBase *> comps);
+    fptype normalize() override;
+    bool hasAnalyticIntegral() const override { return false; }
+
+  private:
+    bool extended;
+};
+/// combine/MappedPdf.h: the value of the mapping function m (rounded) selects which of the functions t is evaluated
+class MappedPdf : public CombinePdf {
+  public:
+    MappedPdf(std::string n, GooPdf *m, std::vector<GooPdf *> &t);
+    fptype normalize() override;
+    bool hasAnalyticIntegral() const override { return false; }
+};
+
 class ProdPdf : public CombinePdf { // combine/ProdPdf.h
   public:
     ProdPdf(std::string n, std::vector<PdfBase *> comps);

@@ -224,6 +224,47 @@ double AddPdf::calculateNLL() { // AddPdf.cu:187-204: extended term  N_exp - N l
     return ret;
 }
 
+// ---- EventWeightedAddPdf (combine/EventWeightedAddPdf.cu:85-150) ---------------------------------------------
+EventWeightedAddPdf::EventWeightedAddPdf(std::string n, std::vector<Observable> weights, std::vector<PdfBase *> comps)
+    : CombinePdf("EventWeightedAddPdf", n)
+    , extended(true) {
+    if(weights.size() != comps.size() && (weights.size() + 1) != comps.size())
+        throw GeneralError("Size of weights {} (+1) != comps {}", weights.size(), comps.size());
+    for(PdfBase *p : comps) {
+        if(p == nullptr) throw GeneralError("Invalid component");
+        components.push_back(p);
+    }
+    for(auto &w : weights) registerObservable(w); // before the components' observables: the device op reads the weights first
+    if(weights.size() < components.size()) extended = false;
+    observablesList = getObservables();
+    registerConstant(components.size());
+    registerFunction(extended ? "ptr_to_EventWeightedAddPdfsExt" : "ptr_to_EventWeightedAddPdfs", extended ? GF_OP_EVTW_ADD_EXT : GF_OP_EVTW_ADD);
+}
+fptype EventWeightedAddPdf::normalize() { // per-event weights: only the components can be normalised
+    for(PdfBase *comp : components) comp->normalize();
+    setNormalization(1.0);
+    return 1.0;
+}
+// ---- MappedPdf (combine/MappedPdf.cu:63-107) ---------------------------------------------------------------------
+MappedPdf::MappedPdf(std::string n, GooPdf *m, std::vector<GooPdf *> &t)
+    : CombinePdf("MappedPdf", n) {
+    if(!m || t.empty()) throw GeneralError("MappedPdf {} needs a mapping function and at least one component", n);
+    components.push_back(m);
+    for(GooPdf *f : t) {
+        if(!f) throw GeneralError("Invalid component");
+        components.push_back(f);
+    }
+    observablesList = getObservables();
+    registerConstant(components.size() - 1);
+    registerFunction("ptr_to_Mapped", GF_OP_MAPPED);
+}
+fptype MappedPdf::normalize() {
+    fptype ret = 0;
+    for(size_t i = 1; i < components.size(); ++i) ret += components[i]->normalize(); // the mapping function is not normalised
+    setNormalization(1.0);
+    return ret;
+}
+
 // ---- ProdPdf (combine/ProdPdf.cu:30-99) ---------------------------------------------------------------------
 ProdPdf::ProdPdf(std::string n, std::vector<PdfBase *> comps)
     : CombinePdf("ProdPdf", n) {

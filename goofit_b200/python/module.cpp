@@ -292,6 +292,11 @@ PYBIND11_MODULE(_goofit, m) {
         .def(py::init<std::string, Variable, PdfBase *, PdfBase *>(), "name"_a, "frac1"_a, "func1"_a, "func2"_a, py::keep_alive<1, 4>(), py::keep_alive<1, 5>());
     py::class_<ProdPdf, CombinePdf>(m, "ProdPdf")
         .def(py::init<std::string, std::vector<PdfBase *>>(), "name"_a, "comps"_a, py::keep_alive<1, 3>());
+    py::class_<EventWeightedAddPdf, CombinePdf>(m, "EventWeightedAddPdf")
+        .def(py::init<std::string, std::vector<Observable>, std::vector<PdfBase *>>(), "name"_a, "weights"_a, "comps"_a, py::keep_alive<1, 4>());
+    py::class_<MappedPdf, CombinePdf>(m, "MappedPdf")
+        .def(py::init([](std::string n, GooPdf *map, std::vector<GooPdf *> t) { return new MappedPdf(n, map, t); }), "name"_a, "m"_a, "t"_a,
+             py::keep_alive<1, 3>(), py::keep_alive<1, 4>());
     py::class_<ConvolutionPdf, CombinePdf>(m, "ConvolutionPdf")
         .def(py::init<std::string, Observable, GooPdf *, GooPdf *>(), "name"_a, "x"_a, "model"_a, "resolution"_a, py::keep_alive<1, 4>(), py::keep_alive<1, 5>())
         .def("setIntegrationConstants", &ConvolutionPdf::setIntegrationConstants, "lo"_a, "hi"_a, "step"_a);

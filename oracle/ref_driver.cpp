@@ -21,6 +21,8 @@
 #include <goofit/PDFs/basic/ScaledGaussianPdf.h>
 #include <goofit/PDFs/combine/AddPdf.h>
 #include <goofit/PDFs/combine/ConvolutionPdf.h>
+#include <goofit/PDFs/combine/EventWeightedAddPdf.h>
+#include <goofit/PDFs/combine/MappedPdf.h>
 #include <goofit/PDFs/combine/ProdPdf.h>
 #include <goofit/PDFs/physics/Amp3Body.h>
 #include <goofit/PDFs/physics/Amp3Body_TD.h>
@@ -1081,6 +1083,57 @@ static void case_td3() {
     td3_one("td3g3", 1, 0.05);
 }
 
+// ---- EventWeightedAddPdf (per-event weights, plain and extended) and MappedPdf (combine/*.cu) ---------------------------------
+static void case_combine2() {
+    Observable x{"x", -5, 5}, w1{"w1", 0, 1}, w2{"w2", 0, 5}, sel{"sel", 0, 2};
+    std::mt19937_64 gen(9001);
+    std::normal_distribution<double> g(0.3, 1.2);
+    std::uniform_real_distribution<double> u(0, 1);
+    std::vector<double> X, W1, W2, S;
+    while(X.size() < 700) {
+        double v = g(gen);
+        if(v <= -5 || v >= 5) continue;
+        X.push_back(v); W1.push_back(0.2 + 0.6 * u(gen)); W2.push_back(0.5 + 3.0 * u(gen)); S.push_back((double)(X.size() % 3));
+    }
+    save_npy("combine2.x", X); save_npy("combine2.w1", W1); save_npy("combine2.w2", W2); save_npy("combine2.sel", S);
+    Variable m1("m1", 0.2, 0.1, -3, 3), s1("s1", 1.1, 0.1, 0.3, 4), m2("m2", -0.8, 0.1, -3, 3), s2("s2", 2.0, 0.1, 0.3, 4), al("alpha", -0.3, 0.1, -2, 2);
+    { // plain: one weight column, last component takes 1 - w
+        GaussianPdf ga("ga", x, m1, s1);
+        ExpPdf ex("ex", x, al);
+        EventWeightedAddPdf ew("ew", {w1}, {&ga, &ex});
+        UnbinnedDataSet d({w1, x});
+        for(size_t i = 0; i < X.size(); i++) { x.setValue(X[i]); w1.setValue(W1[i]); d.addEvent(); }
+        ew.setData(&d);
+        put("combine2.ew_nll", ew.calculateNLL());
+        auto probs = ew.getCompProbsAtDataPoints();
+        save_npy("combine2.ew_prob", probs[0]);
+    }
+    { // extended: one weight column per component, divided by the total weight
+        GaussianPdf ga("ga", x, m1, s1), gb("gb", x, m2, s2);
+        EventWeightedAddPdf ew("ewx", {w1, w2}, {&ga, &gb});
+        UnbinnedDataSet d({w1, w2, x});
+        for(size_t i = 0; i < X.size(); i++) { x.setValue(X[i]); w1.setValue(W1[i]); w2.setValue(W2[i]); d.addEvent(); }
+        ew.setData(&d);
+        put("combine2.ewx_nll", ew.calculateNLL());
+        auto probs = ew.getCompProbsAtDataPoints();
+        save_npy("combine2.ewx_prob", probs[0]);
+    }
+    { // mapped: sel = 0, 1, 2 picks one of three shapes; the mapping function is the degree-1 polynomial 0 + 1 * sel
+        Variable zero("zero", 0), one("one", 1);
+        PolynomialPdf map("map", sel, std::vector<Variable>{zero, one});
+        GaussianPdf ga("ga", x, m1, s1), gb("gb", x, m2, s2);
+        ExpPdf ex("ex", x, al);
+        std::vector<GooPdf *> t = {&ga, &gb, &ex};
+        MappedPdf mp("mapped", &map, t);
+        UnbinnedDataSet d({sel, x});
+        for(size_t i = 0; i < X.size(); i++) { x.setValue(X[i]); sel.setValue(S[i]); d.addEvent(); }
+        mp.setData(&d);
+        put("combine2.map_nll", mp.calculateNLL());
+        auto probs = mp.getCompProbsAtDataPoints();
+        save_npy("combine2.map_prob", probs[0]);
+    }
+}
+
 static void case_dp4_fit() {
     DP4Model *M = make_dp4(60000, false);
     UnbinnedDataSet cand({M->m12, M->m34, M->cos12, M->cos34, M->phi, M->eventNumber});
@@ -1726,6 +1779,7 @@ int main(int argc, char **argv) {
             if(only == "all" || only == "zoo4") case_zoo4();
             if(only == "all" || only == "kmatrix") case_kmatrix();
             if(only == "all" || only == "td3") case_td3();
+            if(only == "all" || only == "combine2") case_combine2();
             if(only == "all" || only == "dalitzfit") case_dalitz_fit();
             if(only == "all" || only == "dp4") case_dp4();
             if(only == "all" || only == "dp4fit") case_dp4_fit();

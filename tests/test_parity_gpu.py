@@ -214,6 +214,51 @@ def test_add_prod(golden):
     check_pdf(golden, "prod", prod, d2)
 
 
+def test_event_weighted_add_and_mapped(golden):
+    """combine/EventWeightedAddPdf.cu (one weight column per component but the last; or one per component = extended, divided by
+    the total weight) and combine/MappedPdf.cu (the rounded value of the mapping function picks the shape) against the
+    reference on the same 700 events (oracle/ref_driver.cpp case_combine2)."""
+    V = gf.Variable
+    x = gf.Observable("x", -5, 5)
+    w1 = gf.Observable("w1", 0, 1)
+    w2 = gf.Observable("w2", 0, 5)
+    sel = gf.Observable("sel", 0, 2)
+    X, W1, W2, S = (golden.arr("combine2." + k) for k in ("x", "w1", "w2", "sel"))
+    m1, s1 = V("m1", 0.2, 0.1, -3, 3), V("s1", 1.1, 0.1, 0.3, 4)
+    m2, s2 = V("m2", -0.8, 0.1, -3, 3), V("s2", 2.0, 0.1, 0.3, 4)
+    al = V("alpha", -0.3, 0.1, -2, 2)
+
+    def check(pdf, data, tag):
+        pdf.setData(data)
+        nll = pdf.calculateNLL()
+        assert gf.last_kernel_name() == "k_eval_sum"  # no shape-specialised copy for these: the interpreter runs them
+        assert rel(nll, golden["combine2.%s_nll" % tag]) < RTOL_NLL, (tag, nll)
+        probs = np.asarray(pdf.getCompProbsAtDataPoints()[0])
+        np.testing.assert_allclose(probs, golden.arr("combine2.%s_prob" % tag), rtol=RTOL_EVT, atol=0)
+        assert rel(nll, math.fsum(-np.log(probs))) < RTOL_NLL
+        pdf.setFitControl(gf.UnbinnedNllFit())
+        pdf.setData(data)
+        assert pdf.calculateNLL() == nll
+
+    ga = gf.GaussianPdf("ga", x, m1, s1)
+    gb = gf.GaussianPdf("gb", x, m2, s2)
+    ex = gf.ExpPdf("ex", x, al)
+    check(gf.EventWeightedAddPdf("ew", [w1], [ga, ex]), dataset_from_columns([w1, x], [W1, X]), "ew")
+    check(gf.EventWeightedAddPdf("ewx", [w1, w2], [ga, gb]), dataset_from_columns([w1, w2, x], [W1, W2, X]), "ewx")
+    mapping = gf.PolynomialPdf("map", sel, [V("zero", 0), V("one", 1)])
+    mp = gf.MappedPdf("mapped", mapping, [ga, gb, ex])
+    check(mp, dataset_from_columns([sel, x], [S, X]), "map")
+    # a parameter of one of the mapped shapes moves: only that third of the events changes
+    before = np.asarray(mp.getCompProbsAtDataPoints()[0])
+    mp.updateVariable(m2, -0.5)
+    mp.updateParameters()
+    mp.setFitControl(gf.UnbinnedNllFit())
+    mp.calculateNLL()
+    after = np.asarray(mp.getCompProbsAtDataPoints()[0])
+    moved = before != after
+    assert moved[S == 1].all() and not moved[S != 1].any()
+
+
 def test_dalitz_values(golden):
     M = Dalitz(float_masses=True, grid=120)
     m12, m13 = golden.arr("dalitz.m12"), golden.arr("dalitz.m13")
