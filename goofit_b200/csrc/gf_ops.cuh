@@ -374,7 +374,7 @@ __device__ inline double gf_eval_tree(const gf_sprog &P, const gf_dev_view &V, i
             sp -= n;
             st[sp++] = ret;
         } break;
-        case GF_OP_EVTW_ADD: { // combine/EventWeightedAddPdf.cu:8-40: the weights are event columns, not parameters
+        case GF_OP_EVTW_ADD: { // combine/EventWeightedAddPdf.cu:8-44: the weights are event columns, not parameters
             int n = nd.nchild;
             const int32_t *ob = P.ints + nd.obs_off;
             double ret = 0, tw = 0;
@@ -388,7 +388,7 @@ __device__ inline double gf_eval_tree(const gf_sprog &P, const gf_dev_view &V, i
             sp -= n;
             st[sp++] = ret;
         } break;
-        case GF_OP_EVTW_ADD_EXT: { // EventWeightedAddPdf.cu:42-73
+        case GF_OP_EVTW_ADD_EXT: { // EventWeightedAddPdf.cu:46-91
             int n = nd.nchild;
             const int32_t *ob = P.ints + nd.obs_off;
             double ret = 0, tw = 0;
@@ -402,7 +402,7 @@ __device__ inline double gf_eval_tree(const gf_sprog &P, const gf_dev_view &V, i
             sp -= n;
             st[sp++] = ret;
         } break;
-        case GF_OP_MAPPED: { // combine/MappedPdf.cu:7-55: child 0 picks which of the other children is the value
+        case GF_OP_MAPPED: { // combine/MappedPdf.cu:6-38: child 0 picks which of the other children is the value
             int n = nd.nchild;
             const double *ch = st + (sp - n);
             int target = (int)floor(0.5 + ch[0]);

@@ -224,7 +224,7 @@ double AddPdf::calculateNLL() { // AddPdf.cu:187-204: extended term  N_exp - N l
     return ret;
 }
 
-// ---- EventWeightedAddPdf (combine/EventWeightedAddPdf.cu:85-150) ---------------------------------------------
+// ---- EventWeightedAddPdf (combine/EventWeightedAddPdf.cu:96-160) ---------------------------------------------
 EventWeightedAddPdf::EventWeightedAddPdf(std::string n, std::vector<Observable> weights, std::vector<PdfBase *> comps)
     : CombinePdf("EventWeightedAddPdf", n)
     , extended(true) {
@@ -245,7 +245,7 @@ fptype EventWeightedAddPdf::normalize() { // per-event weights: only the compone
     setNormalization(1.0);
     return 1.0;
 }
-// ---- MappedPdf (combine/MappedPdf.cu:63-107) ---------------------------------------------------------------------
+// ---- MappedPdf (combine/MappedPdf.cu:55-97) ---------------------------------------------------------------------
 MappedPdf::MappedPdf(std::string n, GooPdf *m, std::vector<GooPdf *> &t)
     : CombinePdf("MappedPdf", n) {
     if(!m || t.empty()) throw GeneralError("MappedPdf {} needs a mapping function and at least one component", n);

@@ -69,9 +69,9 @@ enum gf_op {
     GF_OP_ADD_EXT,          /* AddPdf.cu:53 */
     GF_OP_PROD,             /* ProdPdf.cu:9 */
     GF_OP_CONVOLVE,         /* ConvolutionPdf.cu:27  ints: conv id */
-    GF_OP_EVTW_ADD,         /* EventWeightedAddPdf.cu:8-40   weights = the first nchild-1 observable columns of the record */
-    GF_OP_EVTW_ADD_EXT,     /* EventWeightedAddPdf.cu:42-73  one weight column per component, sum divided by the total weight */
-    GF_OP_MAPPED,           /* MappedPdf.cu:8-47  child 0 = mapping function, value rounded to the index of the component to return */
+    GF_OP_EVTW_ADD,         /* EventWeightedAddPdf.cu:8-44   weights = the first nchild-1 observable columns of the record */
+    GF_OP_EVTW_ADD_EXT,     /* EventWeightedAddPdf.cu:46-91  one weight column per component, sum divided by the total weight */
+    GF_OP_MAPPED,           /* MappedPdf.cu:6-38  child 0 = mapping function, value rounded to the index of the component to return */
     GF_OP_AMP3 = 48,        /* Amp3Body.cu:60  child: efficiency; ints: amp3 id */
     GF_OP_AMP4,             /* Amp4Body.cu:53 */
     GF_OP_AMP4_TD,          /* Amp4Body_TD.cu:167 */
