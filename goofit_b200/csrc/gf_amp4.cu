@@ -232,6 +232,54 @@ __device__ __forceinline__ double2 gf_amp4_build(const int32_t *rec, const gf_am
     }
 }
 
+// The same amplitude from a per-block PLAN in shared memory (k_amp4_update): the plane base pointers are resolved once per block
+// instead of once per event (record look-up, 64-bit index * leading dimension), which was a third of the instructions the
+// update kernel issued (ncu source view: 450 of 1480 per event). Lineshape planes are read with ordinary loads: some were
+// written earlier in this very kernel by the same thread.
+#define GF_PLAN_MAXLS 6
+#define GF_PLAN_MAXSF 2
+struct gf_upd_plan {
+    const double2 *ls[GF_PLAN_MAXLS];
+    const double *sf[GF_PLAN_MAXSF];
+    double2 *out;
+    int toff;  // row offset of the amplitude's Re row in the warp's MMA tile, in doubles
+    int shape; // nPerm * 100 + LS_step * 10 + SF_step, or 0: not one of the compiled shapes, go through the record
+    int amp;
+    int pad;
+};
+template <int LS_STEP, int SF_STEP, int NPERM>
+__device__ __forceinline__ double2 gf_amp4_one_p(const gf_upd_plan &pl, long e) {
+    constexpr int NLS = LS_STEP * NPERM, NSF = SF_STEP * NPERM;
+    static_assert(NLS <= GF_PLAN_MAXLS && NSF <= GF_PLAN_MAXSF, "plan too small for this shape");
+    double2 L[NLS];
+    double S[NSF];
+#pragma unroll
+    for(int j = 0; j < NLS; ++j) L[j] = pl.ls[j][e];
+#pragma unroll
+    for(int j = 0; j < NSF; ++j) S[j] = __ldg(pl.sf[j] + e);
+    gf_cplx total = gf_c(0, 0);
+#pragma unroll
+    for(int p = 0; p < NPERM; ++p) {
+        gf_cplx ret = gf_c(1, 0);
+#pragma unroll
+        for(int j = 0; j < LS_STEP; ++j) ret = ret * gf_c(L[p * LS_STEP + j].x, L[p * LS_STEP + j].y);
+#pragma unroll
+        for(int j = 0; j < SF_STEP; ++j) ret = ret * gf_c(S[p * SF_STEP + j], 0.0);
+        total = total + ret;
+    }
+    total = total * (1 / sqrt((double)NPERM));
+    return make_double2(total.re, total.im);
+}
+__device__ __forceinline__ int gf_amp4_plan_shape(const int32_t *rec) {
+    const int numLS = rec[0], numSF = rec[1], nPerm = rec[2];
+    if(nPerm < 1 || nPerm > 2 || numLS % nPerm || numSF % nPerm) return 0;
+    const int shape = nPerm * 100 + (numLS / nPerm) * 10 + numSF / nPerm;
+    switch(shape) {
+    case 221: case 121: case 111: case 211: case 131: case 231: return shape;
+    default: return 0;
+    }
+}
+
 __global__ void __launch_bounds__(GF_THREADS, 3)
     k_amp4_amps(const gf_dev_view V, int node, gf_amp4_args A, unsigned long long amp_mask) {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -386,10 +434,15 @@ __global__ void __launch_bounds__(GF_THREADS, 2)
 // are three MMAs per four events whose 8x8 accumulators live distributed over the warp (4 registers per thread, instead of the
 // 72 a per-thread 8x8 complex accumulator would need - the reason k_amp4_gram tiles 4x4 and re-reads the planes per tile).
 // The rebuilt amplitudes never travel through HBM on their way to the sum, and the untouched ones are read once.
+#define GF_PF_K 4
+#ifndef GF_UPD_PF_L1
+#define GF_UPD_PF_L1 1
+#endif
 #define GF_UPD_TS 36 // tile row stride in doubles: 4 mod 16, so the MMA fragment reads (8 rows x 4 events) of a half-warp hit 16 different 8-byte banks
 struct gf_ls_slot { // per-lineshape record in shared memory, filled once per block for the flagged lineshapes
     gf_bw_inv inv;  // parameter-only part (valid when has_inv: constant daughters and a Breit-Wigner-type kind)
     const double *mcol, *dcol, *lp, *lc;
+    double2 *out;
     double d1c, d2;
     int kind, has_inv;
 };
@@ -417,6 +470,13 @@ __global__ void __launch_bounds__(GF_THREADS, upd_blocks_per_sm(NB))
     __shared__ const char *pf_base[160];
     __shared__ unsigned char pf_bytes[160];
     __shared__ int npf;
+    // resolved per block: where each rebuilt amplitude reads and writes, where each standing one is read, and which lines of the
+    // next group every lane requests (GF_PF_K planes per lane: plane (lane >> 2) + 8 k, line lane & 3 of its 32-event span)
+    __shared__ gf_upd_plan plans[16];
+    __shared__ const double2 *un_ptr[16];
+    __shared__ int un_off[16];
+    __shared__ const char *pf_lane[GF_PF_K][32];
+    __shared__ unsigned char pf_is16[GF_PF_K][32];
     gf_sprog P = gf_stage_program(V, smem);
     __syncthreads();
     const gf_node &nd = P.nodes[node];
@@ -442,6 +502,7 @@ __global__ void __launch_bounds__(GF_THREADS, upd_blocks_per_sm(NB))
             gf_pair_daughters(pair, L.d1c, L.d2, mc[1], mc[2], mc[3], mc[4]);
         L.mcol = pair < 2 ? A.cols[pair] : A.kin + (size_t)K.m[i] * A.ld;
         L.dcol = (pair >= 2 && K.d[i] >= 0) ? A.kin + (size_t)K.d[i] * A.ld : nullptr;
+        L.out = A.ls + (size_t)i * A.ld;
         L.has_inv = (L.dcol == nullptr && gf_ls_has_inv(L.kind)) ? 1 : 0;
         if(L.has_inv) L.inv = gf_bw_invariants(L.kind == GF_LS_SBW, L.d1c, L.d2, L.lp[0], L.lp[1]);
         slots[i] = L;
@@ -471,7 +532,45 @@ __global__ void __launch_bounds__(GF_THREADS, upd_blocks_per_sm(NB))
             if((sf_in >> k) & 1ull) { pf_base[np] = reinterpret_cast<const char *>(A.sf + (size_t)k * A.ld); pf_bytes[np++] = 8; }
         if(NB > 0)
             for(int u = 0; u < nu; ++u) { pf_base[np] = reinterpret_cast<const char *>(A.amps + (size_t)untouched[u] * A.ld); pf_bytes[np++] = 16; }
+        for(int f = 0; f < nf && np < 156; ++f) { // pair masses of the flagged lineshapes
+            const int i = flagged[f];
+            const gf_node &ln = P.nodes[in[5 + i]];
+            const int pair = (int)(P.consts + ln.con_off)[0];
+            const double *mcol = pair < 2 ? A.cols[pair] : A.kin + (size_t)K.m[i] * A.ld;
+            const double *dcol = (pair >= 2 && K.d[i] >= 0) ? A.kin + (size_t)K.d[i] * A.ld : nullptr;
+            bool seen = false;
+            for(int j = 0; j < np; ++j) seen = seen || pf_base[j] == reinterpret_cast<const char *>(mcol);
+            if(!seen) { pf_base[np] = reinterpret_cast<const char *>(mcol); pf_bytes[np++] = 8; }
+            if(dcol) { pf_base[np] = reinterpret_cast<const char *>(dcol); pf_bytes[np++] = 8; }
+        }
         npf = np;
+    }
+    __syncthreads();
+    if(threadIdx.x < 32 * GF_PF_K) {
+        const int k = threadIdx.x >> 5, l = threadIdx.x & 31;
+        const int j = (l >> 2) + 8 * k;
+        const bool on = j < npf && (l & 3) * 128 < 32 * pf_bytes[j];
+        pf_lane[k][l] = on ? pf_base[j] + (l & 3) * 128 : nullptr;
+        pf_is16[k][l] = on && pf_bytes[j] == 16;
+    }
+    if((int)threadIdx.x < nun) {
+        const int a = untouched[threadIdx.x];
+        un_ptr[threadIdx.x] = A.amps + (size_t)a * A.ld;
+        un_off[threadIdx.x] = ((a >> 3) * 16 + (a & 7)) * GF_UPD_TS;
+    }
+    if((int)threadIdx.x >= 32 && (int)threadIdx.x - 32 < nre) {
+        const int k = threadIdx.x - 32;
+        const int a = rebuilt[k];
+        const int32_t *rec = rec0 + start[a];
+        gf_upd_plan pl;
+        pl.shape = gf_amp4_plan_shape(rec);
+        pl.amp = a;
+        pl.pad = 0;
+        pl.out = A.amps + (size_t)a * A.ld;
+        pl.toff = ((a >> 3) * 16 + (a & 7)) * GF_UPD_TS;
+        for(int j = 0; j < GF_PLAN_MAXLS; ++j) pl.ls[j] = (pl.shape && j < rec[0]) ? A.ls + (size_t)rec[3 + j] * A.ld : nullptr;
+        for(int j = 0; j < GF_PLAN_MAXSF; ++j) pl.sf[j] = (pl.shape && j < rec[1]) ? A.sf + (size_t)rec[3 + rec[0] + j] * A.ld : nullptr;
+        plans[k] = pl;
     }
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     double *T = tiles + (size_t)wib * 16 * NB * GF_UPD_TS; // rows: block b -> [16 b, 16 b + 8) = Re, [16 b + 8, 16 b + 16) = Im
@@ -486,24 +585,20 @@ __global__ void __launch_bounds__(GF_THREADS, upd_blocks_per_sm(NB))
     for(long base = ((long)blockIdx.x * (GF_THREADS / 32) + wib) * 32; base < A.n; base += warp_stride) {
         const long e = base + lane;
         const bool live = e < A.n;
-        { // lane l requests line (l & 3) of planes l >> 2, l >> 2 + 8, ... of this warp's next 32 events
+        { // lane l requests line (l & 3) of planes l >> 2, l >> 2 + 8, ... of this warp's next 32 events into L2, and the same
+          // lines of the current 32 events (which the previous iteration brought into L2) into L1
             const long nb0 = base + warp_stride;
-            if(nb0 < A.n) {
-                for(int j = lane >> 2; j < npf; j += 8) {
-                    const int bytes = pf_bytes[j];
-                    if((lane & 3) * 128 < 32 * bytes) {
-                        const char *q = pf_base[j] + (size_t)nb0 * bytes + (lane & 3) * 128;
-                        asm volatile("prefetch.global.L2 [%0];" ::"l"(q));
-                    }
-                }
-                for(int f = lane; f < nflag; f += 32) { // pair masses of the flagged lineshapes (8 B per event: two lines)
-                    const gf_ls_slot &L = slots[flagged[f]];
-                    asm volatile("prefetch.global.L2 [%0];" ::"l"(L.mcol + nb0));
-                    asm volatile("prefetch.global.L2 [%0];" ::"l"(L.mcol + nb0 + 16));
-                    if(L.dcol) {
-                        asm volatile("prefetch.global.L2 [%0];" ::"l"(L.dcol + nb0));
-                        asm volatile("prefetch.global.L2 [%0];" ::"l"(L.dcol + nb0 + 16));
-                    }
+            const size_t off8 = (size_t)nb0 * 8, cur8 = (size_t)base * 8;
+            const bool more = nb0 < A.n;
+#pragma unroll
+            for(int k = 0; k < GF_PF_K; ++k) {
+                const char *q = pf_lane[k][lane];
+                if(q) {
+                    const bool wide = pf_is16[k][lane];
+#if GF_UPD_PF_L1
+                    asm volatile("prefetch.global.L1 [%0];" ::"l"(q + (wide ? 2 * cur8 : cur8)));
+#endif
+                    if(more) asm volatile("prefetch.global.L2 [%0];" ::"l"(q + (wide ? 2 * off8 : off8)));
                 }
             }
         }
@@ -513,13 +608,13 @@ __global__ void __launch_bounds__(GF_THREADS, upd_blocks_per_sm(NB))
                     double2 v[4];
 #pragma unroll
                     for(int j = 0; j < 4; ++j)
-                        if(g + j < nun) v[j] = __ldg(A.amps + (size_t)untouched[g + j] * A.ld + e);
+                        if(g + j < nun) v[j] = __ldg(un_ptr[g + j] + e);
 #pragma unroll
                     for(int j = 0; j < 4; ++j)
                         if(g + j < nun) {
-                            const int a = untouched[g + j];
-                            T[((a >> 3) * 16 + (a & 7)) * GF_UPD_TS + lane] = v[j].x;
-                            T[((a >> 3) * 16 + 8 + (a & 7)) * GF_UPD_TS + lane] = v[j].y;
+                            double *t = T + un_off[g + j] + lane;
+                            t[0] = v[j].x;
+                            t[8 * GF_UPD_TS] = v[j].y;
                         }
                 }
             }
@@ -532,15 +627,25 @@ __global__ void __launch_bounds__(GF_THREADS, upd_blocks_per_sm(NB))
                     r = gf_lineshape_inv(L.kind, L.lp, L.lc, mres, L.inv);
                 else
                     r = gf_lineshape(L.kind, L.lp, L.lc, mres, L.dcol ? __ldg(L.dcol + e) : L.d1c, L.d2);
-                A.ls[(size_t)i * A.ld + e] = make_double2(r.re, r.im);
+                L.out[e] = make_double2(r.re, r.im);
             }
             for(int k = 0; k < nre; ++k) {
-                const int a = rebuilt[k];
-                const double2 v = gf_amp4_build<true>(rec0 + start[a], A, e);
-                A.amps[(size_t)a * A.ld + e] = v;
+                const gf_upd_plan &pl = plans[k];
+                double2 v;
+                switch(pl.shape) { // uniform over the grid
+                case 221: v = gf_amp4_one_p<2, 1, 2>(pl, e); break; // Bose-symmetrised two-resonance chains (DP4, TDDP4)
+                case 121: v = gf_amp4_one_p<2, 1, 1>(pl, e); break;
+                case 111: v = gf_amp4_one_p<1, 1, 1>(pl, e); break;
+                case 211: v = gf_amp4_one_p<1, 1, 2>(pl, e); break;
+                case 131: v = gf_amp4_one_p<3, 1, 1>(pl, e); break;
+                case 231: v = gf_amp4_one_p<3, 1, 2>(pl, e); break;
+                default: v = gf_amp4_build<true>(rec0 + start[pl.amp], A, e);
+                }
+                pl.out[e] = v;
                 if(NB > 0) {
-                    T[((a >> 3) * 16 + (a & 7)) * GF_UPD_TS + lane] = v.x;
-                    T[((a >> 3) * 16 + 8 + (a & 7)) * GF_UPD_TS + lane] = v.y;
+                    double *t = T + pl.toff + lane;
+                    t[0] = v.x;
+                    t[8 * GF_UPD_TS] = v.y;
                 }
             }
         } else if(NB > 0) {
