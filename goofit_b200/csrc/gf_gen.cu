@@ -7,6 +7,8 @@
 // seed is the same whatever the batch, the rank or the thread that produces it, so a sample can be generated in place on each
 // GPU (or regenerated) without a host loop. One thread per event; no state is carried between events.
 #include "gf_internal.cuh"
+#include <mutex>
+#include <string>
 
 struct gf_v4 { double e, x, y, z; };
 __device__ __forceinline__ gf_v4 operator+(gf_v4 a, gf_v4 b) { return {a.e + b.e, a.x + b.x, a.y + b.y, a.z + b.z}; }
@@ -199,5 +201,87 @@ extern "C" int gf_genbod(gf_ctx *c, const double *masses, int nd, size_t n, uint
     if(e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
     if(e != cudaSuccess) return bail(cudaGetErrorString(e));
     cudaFree(d_p); cudaFree(d_w); cudaFree(d_v);
+    return 0;
+}
+
+// ---- gf_genbod without any allocation -----------------------------------------------------------------------------------------
+// gf_genbod stages its device outputs in buffers it cudaMallocs and cudaFrees on every call. Callers that may not allocate
+// (a stream under graph capture, a tight serving loop, a harness that forbids it) get the same kernel with that staging area in
+// a file-scope array instead: 22 doubles per event (weight, five variables, four four-vectors) for at most
+// GF_GENBOD_STATIC_MAX_EVENTS events = 5.5 MiB, held by every GPU that loads the library until the process exits.
+// `gf_genbod_scratch` below is the HOST-side stand-in of the device array: host code must never hand it to a kernel. Its device
+// address is resolved once per device with cudaGetSymbolAddress (that device current) and cached here.
+// Every call shares the array and it keeps the previous call's contents; the kernel overwrites every element the copies read
+// back (n weights, 5 n variables, 4 nd n momenta), so nothing needs clearing. Two calls that overlap on the GPU (two contexts =
+// two streams on one device, or two host threads) race on it: serialise them.
+static __device__ __align__(256) double gf_genbod_scratch[(size_t)22 * GF_GENBOD_STATIC_MAX_EVENTS];
+#define GF_GENBOD_MAX_DEVICES 64
+static double *g_genbod_scratch_ptr[GF_GENBOD_MAX_DEVICES]; // device address of gf_genbod_scratch on device d, null until resolved
+static std::mutex g_genbod_scratch_mu;
+
+extern "C" int gf_genbod_static(gf_ctx *c, const double *masses, int nd, size_t n, uint64_t seed, uint64_t offset, double *particles, double *weights,
+                                double *dim5) {
+    if(!c || !masses) return gf_fail("gf_genbod_static: null argument");
+    if(nd != 3 && nd != 4) return gf_fail("gf_genbod_static: 3 or 4 daughters");
+    if(dim5 && nd != 4) return gf_fail("gf_genbod_static: the five-variable form needs four daughters");
+    if(n > (size_t)GF_GENBOD_STATIC_MAX_EVENTS)
+        return gf_fail("gf_genbod_static: " + std::to_string(n) + " events exceed the static scratch array (at most " +
+                       std::to_string(GF_GENBOD_STATIC_MAX_EVENTS) + " per call; split the range by `offset`, or use gf_genbod)");
+    if(n == 0) return 0;
+    if(c->device < 0 || c->device >= GF_GENBOD_MAX_DEVICES) return gf_fail("gf_genbod_static: device index out of range");
+    cudaError_t e = cudaSetDevice(c->device);
+    if(e != cudaSuccess) return gf_fail(std::string("gf_genbod_static: cudaSetDevice: ") + cudaGetErrorString(e));
+    double *scratch;
+    {
+        std::lock_guard<std::mutex> lock(g_genbod_scratch_mu);
+        if(!g_genbod_scratch_ptr[c->device]) { // set-up, once per device, with that device current
+            void *ptr = nullptr;
+            e = cudaGetSymbolAddress(&ptr, gf_genbod_scratch);
+            if(e != cudaSuccess || !ptr) {
+                cudaGetLastError();
+                return gf_fail(std::string("gf_genbod_static: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+            }
+            g_genbod_scratch_ptr[c->device] = static_cast<double *>(ptr);
+        }
+        scratch = g_genbod_scratch_ptr[c->device];
+    }
+    gf_gen_args G;
+    G.M = masses[0];
+    G.nd = nd;
+    G.seed = seed;
+    G.offset = offset;
+    G.n = (long)n;
+    double tecm = G.M;
+    for(int k = 0; k < 4; k++) {
+        G.m[k] = k < nd ? masses[1 + k] : 0.0;
+        if(k < nd) tecm -= G.m[k];
+    }
+    if(!(tecm > 0)) return gf_fail("gf_genbod_static: not enough energy");
+    double emmax = tecm + G.m[0], emmin = 0;
+    G.wtmax = 1;
+    for(int k = 1; k < nd; k++) {
+        emmin += G.m[k - 1];
+        emmax += G.m[k];
+        G.wtmax *= gf_pdk(emmax, emmin, G.m[k]);
+    }
+    // fixed partition of the array (offsets by the maximum, so every part is 256-byte aligned whatever n is)
+    double *d_w = scratch;
+    double *d_v = dim5 ? scratch + (size_t)GF_GENBOD_STATIC_MAX_EVENTS : nullptr;
+    double *d_p = particles ? scratch + (size_t)6 * GF_GENBOD_STATIC_MAX_EVENTS : nullptr;
+    const int blocks = gf_grid_blocks(c, (long)n, 8);
+    if(nd == 3)
+        k_genbod<3><<<blocks, GF_THREADS, 0, c->stream>>>(G, d_p, d_w, nullptr);
+    else
+        k_genbod<4><<<blocks, GF_THREADS, 0, c->stream>>>(G, d_p, d_w, d_v);
+    c->launches++;
+    e = cudaGetLastError();
+    if(e == cudaSuccess && particles) e = cudaMemcpyAsync(particles, d_p, sizeof(double) * 4 * nd * n, cudaMemcpyDeviceToHost, c->stream);
+    if(e == cudaSuccess && weights) e = cudaMemcpyAsync(weights, d_w, sizeof(double) * n, cudaMemcpyDeviceToHost, c->stream);
+    if(e == cudaSuccess && dim5) e = cudaMemcpyAsync(dim5, d_v, sizeof(double) * 5 * n, cudaMemcpyDeviceToHost, c->stream);
+    if(e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    if(e != cudaSuccess) {
+        cudaGetLastError();
+        return gf_fail(std::string("gf_genbod_static: ") + cudaGetErrorString(e));
+    }
     return 0;
 }

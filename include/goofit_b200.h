@@ -222,6 +222,16 @@ int gf_set_params_async(gf_ctx *, const double *params, int n, const double *nor
  * optional: particles[nd][n][4] = (E, px, py, pz), weights[n] relative to the largest possible weight, dim5[5][n] = (m12, m34,
  * cos12, cos34, phi) for four daughters. */
 int gf_genbod(gf_ctx *, const double *masses, int nd, size_t n, uint64_t seed, uint64_t offset, double *particles, double *weights, double *dim5);
+/* gf_genbod for callers that may not allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc). It has no counterpart in the reference. Same
+ * arguments, same kernel and bit-identical outputs, but the device staging area is a file-scope __device__ array inside the
+ * library (22 doubles per event: 5.5 MiB, held by every GPU that loads the library until the process exits) instead of per-call
+ * cudaMalloc / cudaFree: no allocation of any kind is made. n is limited to GF_GENBOD_STATIC_MAX_EVENTS per call (an error names
+ * the limit beyond it; walk a longer range with `offset`). All calls on one device share the array: calls that overlap on the
+ * GPU (two contexts or two host threads) race on it and must be serialised by the caller. */
+#define GF_GENBOD_STATIC_MAX_EVENTS 32768
+int gf_genbod_static(gf_ctx *, const double *masses, int nd, size_t n, uint64_t seed, uint64_t offset, double *particles, double *weights,
+                     double *dim5);
 /* measured FP64 FMA peak of this GPU (DFMA micro-benchmark, TFLOP/s, 2 flops per FMA): the roofline denominator of
  * the FP64-bound cache kernels (k_amp3_waves, k_amp4_cache), which MEASURED_PEAKS.json does not carry */
 int gf_fp64_peak(gf_ctx *, double *tflops);
