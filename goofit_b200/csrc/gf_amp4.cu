@@ -435,6 +435,26 @@ __global__ void __launch_bounds__(GF_THREADS, 2)
 // 72 a per-thread 8x8 complex accumulator would need - the reason k_amp4_gram tiles 4x4 and re-reads the planes per tile).
 // The rebuilt amplitudes never travel through HBM on their way to the sum, and the untouched ones are read once.
 #define GF_PF_K 4
+// store policy of the planes the update writes (A/B switches; measured)
+#ifndef GF_UPD_ST
+#define GF_UPD_ST 1
+#endif
+#if GF_UPD_ST == 1 // amplitudes streamed (evict-first): they are not read again in this launch
+#define GF_UPD_STORE_LS(p, v) (*(p) = (v))
+#define GF_UPD_STORE_AMP(p, v) __stcs((p), (v))
+#elif GF_UPD_ST == 2
+#define GF_UPD_STORE_LS(p, v) __stcg((p), (v))
+#define GF_UPD_STORE_AMP(p, v) __stcs((p), (v))
+#else
+#define GF_UPD_STORE_LS(p, v) (*(p) = (v))
+#define GF_UPD_STORE_AMP(p, v) (*(p) = (v))
+#endif
+#ifndef GF_UPD_PF_L2
+#define GF_UPD_PF_L2 1
+#endif
+#ifndef GF_UPD_PF_POS
+#define GF_UPD_PF_POS 2
+#endif
 #ifndef GF_UPD_PF_L1
 #define GF_UPD_PF_L1 1
 #endif
@@ -452,7 +472,10 @@ __device__ __forceinline__ void gf_dmma(double &c0, double &c1, double a, double
 constexpr int upd_tiles(int nb) { return nb == 1 ? 2 : (nb == 2 ? 6 : 0); } // 8x8 accumulator tiles: (C1, C2) per block pair (0,0) [, (0,1), (1,1)]
 // measured (tools/ab_compare.sh, K*(892) move on 10^7 + 10^7 events): the MC copy at three resident blocks (80 registers, small
 // spills) against two (128): 1.80 -> 1.66 ms per call (DP4), 2.00 -> 1.77 ms (TDDP4); the 16-amplitude copy keeps two
-constexpr int upd_blocks_per_sm(int nb) { return nb == 2 ? 2 : 3; }
+#ifndef GF_UPD_BLOCKS
+#define GF_UPD_BLOCKS 3
+#endif
+constexpr int upd_blocks_per_sm(int nb) { return nb == 2 ? 2 : GF_UPD_BLOCKS; }
 inline size_t gf_upd_smem(size_t prog, int nLS, int nb) {
     return gf_align16(prog) + gf_align16(sizeof(gf_ls_slot) * (size_t)std::max(1, nLS)) + sizeof(double) * (GF_THREADS / 32) * 16 * nb * GF_UPD_TS;
 }
@@ -585,8 +608,11 @@ __global__ void __launch_bounds__(GF_THREADS, upd_blocks_per_sm(NB))
     for(long base = ((long)blockIdx.x * (GF_THREADS / 32) + wib) * 32; base < A.n; base += warp_stride) {
         const long e = base + lane;
         const bool live = e < A.n;
-        { // lane l requests line (l & 3) of planes l >> 2, l >> 2 + 8, ... of this warp's next 32 events into L2, and the same
-          // lines of the current 32 events (which the previous iteration brought into L2) into L1
+        // lane l requests line (l & 3) of planes l >> 2, l >> 2 + 8, ... : the current 32 events into L1 now, the warp's NEXT 32
+        // events into L2 at GF_UPD_PF_POS (0: now; 1: after the lineshapes; 2: after the amplitudes). Requested a whole iteration
+        // ahead, half of the lines were evicted again before their use (one pass of the grid moves 40-80 MB through L2; ncu:
+        // 3.20 GB of DRAM reads against 2.11 GB without prefetch), so the request is made late in the iteration.
+        auto request = [&](bool l1, bool l2) {
             const long nb0 = base + warp_stride;
             const size_t off8 = (size_t)nb0 * 8, cur8 = (size_t)base * 8;
             const bool more = nb0 < A.n;
@@ -595,13 +621,12 @@ __global__ void __launch_bounds__(GF_THREADS, upd_blocks_per_sm(NB))
                 const char *q = pf_lane[k][lane];
                 if(q) {
                     const bool wide = pf_is16[k][lane];
-#if GF_UPD_PF_L1
-                    asm volatile("prefetch.global.L1 [%0];" ::"l"(q + (wide ? 2 * cur8 : cur8)));
-#endif
-                    if(more) asm volatile("prefetch.global.L2 [%0];" ::"l"(q + (wide ? 2 * off8 : off8)));
+                    if(l1) asm volatile("prefetch.global.L1 [%0];" ::"l"(q + (wide ? 2 * cur8 : cur8)));
+                    if(l2 && more) asm volatile("prefetch.global.L2 [%0];" ::"l"(q + (wide ? 2 * off8 : off8)));
                 }
             }
-        }
+        };
+        request(GF_UPD_PF_L1 != 0, GF_UPD_PF_L2 != 0 && GF_UPD_PF_POS == 0);
         if(live) {
             if(NB > 0) { // amplitudes that stand: requested first, four at a time, so that their latency overlaps the lineshape arithmetic
                 for(int g = 0; g < nun; g += 4) {
@@ -627,8 +652,9 @@ __global__ void __launch_bounds__(GF_THREADS, upd_blocks_per_sm(NB))
                     r = gf_lineshape_inv(L.kind, L.lp, L.lc, mres, L.inv);
                 else
                     r = gf_lineshape(L.kind, L.lp, L.lc, mres, L.dcol ? __ldg(L.dcol + e) : L.d1c, L.d2);
-                L.out[e] = make_double2(r.re, r.im);
+                GF_UPD_STORE_LS(L.out + e, make_double2(r.re, r.im));
             }
+            if(GF_UPD_PF_L2 != 0 && GF_UPD_PF_POS == 1) request(false, true);
             for(int k = 0; k < nre; ++k) {
                 const gf_upd_plan &pl = plans[k];
                 double2 v;
@@ -641,13 +667,14 @@ __global__ void __launch_bounds__(GF_THREADS, upd_blocks_per_sm(NB))
                 case 231: v = gf_amp4_one_p<3, 1, 2>(pl, e); break;
                 default: v = gf_amp4_build<true>(rec0 + start[pl.amp], A, e);
                 }
-                pl.out[e] = v;
+                GF_UPD_STORE_AMP(pl.out + e, v);
                 if(NB > 0) {
                     double *t = T + pl.toff + lane;
                     t[0] = v.x;
                     t[8 * GF_UPD_TS] = v.y;
                 }
             }
+            if(GF_UPD_PF_L2 != 0 && GF_UPD_PF_POS == 2) request(false, true);
         } else if(NB > 0) {
             for(int a = 0; a < nAmp; ++a) {
                 T[((a >> 3) * 16 + (a & 7)) * GF_UPD_TS + lane] = 0.0;
