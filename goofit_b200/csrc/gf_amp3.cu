@@ -44,6 +44,7 @@ void gf_amp3_free(gf_ctx *c) {
 __device__ inline gf_decay3 gf_load_decay3(const double *c) {
     gf_decay3 D;
     D.M = c[0]; D.d1 = c[1]; D.d2 = c[2]; D.d3 = c[3]; D.rad = c[4]; D.mrad = c[5];
+    D.inv_M = 1.0 / D.M;
     return D;
 }
 

@@ -7,6 +7,7 @@
 
 struct gf_decay3 { // Amp3Body node consts: Amp3Body.cu:144-149
     double M, d1, d2, d3, rad, mrad;
+    double inv_M; // 1 / M (gf_load_decay3)
 };
 
 enum { GF_PAIR_12 = 0, GF_PAIR_13 = 1, GF_PAIR_23 = 2 }; // DalitzPlotHelpers.h:81
@@ -19,11 +20,15 @@ __device__ __forceinline__ double gf_cm_mom_s(double rs, double inv_s, double a,
     k2 = k2 >= 0 ? sqrt(k2) : 1;
     return 0.5 * rs * k1 * k2;
 }
+// For a pair mass inside the Dalitz plot both k1 and k2 are negative (s < (dm - d3m)^2 < (dm + d3m)^2), i.e. both factors are 1:
+// the square root is taken of the selected argument (sqrt(1) = 1), not selected after a square root of a negative number, which
+// sent every event through the out-of-line NaN path of sqrt (ncu: 6 of the 9 calls per event-warp of k_amp3_waves)
 __device__ __forceinline__ double gf_cm_mom_mother_s(double s, double inv_s, double dm, double inv_dm, double d3m) {
     double k1 = 1 - (dm + d3m) * (dm + d3m) * inv_s;
-    k1 = k1 >= 0 ? sqrt(k1) : 1;
     double k2 = 1 - (dm - d3m) * (dm - d3m) * inv_s;
-    k2 = k2 >= 0 ? sqrt(k2) : 1;
+    if(k1 < 0 && k2 < 0) return 0.5 * s * inv_dm;
+    k1 = sqrt(k1 >= 0 ? k1 : 1.0);
+    k2 = sqrt(k2 >= 0 ? k2 : 1.0);
     return 0.5 * s * k1 * k2 * inv_dm;
 }
 // Resonance.cu:50-63
@@ -387,11 +392,13 @@ struct gf_res_inv {
     double mass, width, mass2;
     double q0[2], qM0[2], frn[2], frMn[2]; // per symmetrisation term (cyc, cyc+1)
     double inv_q0, mw;                      // 1/q0 and mass^2 * width of the first term
+    double sfr;                             // sqrt(frn[0] * frMn[0]) (normalised form)
 };
 struct gf_pair_inv {
     double s, rs, inv_rs, q, qMn, qMp, z1, z2; // z1/z2: Zemach factor for spin 1 / 2
     // Blatt-Weisskopf pieces per spin 1, 2: normalised form -> 1/F(q), 1/F(qM); plain form -> F(q), F(qM)
     double bw1, bw2, bwM1, bwM2;
+    double sbw1, sbw2; // sqrt(bw1 * bwM1), sqrt(bw2 * bwM2) (normalised form)
 };
 struct gf_pair_need { // what the flagged resonances need of each pair (uniform over the grid)
     int used, norm, plain, maxspin;
@@ -409,6 +416,7 @@ __device__ inline void gf_res_prepare(gf_res_inv &R, const gf_node &nd, const do
     R.op = nd.op;
     R.spin = 0; R.cyc = 0; R.norm = 0; R.nterm = 1; R.pad = 0;
     R.mass = R.width = R.mass2 = 0;
+    R.sfr = 1;
     if(nd.op != GF_OP_RES_RBW && nd.op != GF_OP_RES_RBW_SYM) return; // only plain RBWs take the shared-work path
     R.mass = p[0]; R.width = p[1]; R.mass2 = p[0] * p[0];
     R.spin = (int)c[0]; R.cyc = (int)c[1]; R.norm = c[2] != 0.0;
@@ -425,6 +433,7 @@ __device__ inline void gf_res_prepare(gf_res_inv &R, const gf_node &nd, const do
     }
     R.inv_q0 = 1.0 / R.q0[0];
     R.mw = R.mass2 * R.width;
+    R.sfr = sqrt(R.frn[0] * R.frMn[0]);
 }
 __device__ inline void gf_pair_prepare(gf_pair_inv &Q, const gf_pair_need &need, int cyc, const gf_decay3 &D, double m12,
                                        double m13, double m23) {
@@ -436,19 +445,22 @@ __device__ inline void gf_pair_prepare(gf_pair_inv &Q, const gf_pair_need &need,
     const double inv_s = gf_rcp(Q.s);
     Q.inv_rs = Q.rs * inv_s;
     Q.q = gf_cm_mom_s(Q.rs, inv_s, da, db);
-    Q.qMn = need.norm ? gf_cm_mom_mother_s(Q.s, inv_s, D.M, 1.0 / D.M, bach) : 0.0;
+    Q.qMn = need.norm ? gf_cm_mom_mother_s(Q.s, inv_s, D.M, D.inv_M, bach) : 0.0;
     Q.qMp = need.plain ? gf_cm_mom(D.M * D.M, Q.rs, bach) : 0.0;
     Q.z1 = Q.z2 = 1.0;
     Q.bw1 = Q.bw2 = Q.bwM1 = Q.bwM2 = 1.0;
+    Q.sbw1 = Q.sbw2 = 1.0;
     if(need.maxspin >= 1) Q.z1 = gf_spin3_mf(1, D, m12, m13, m23, cyc, inv_s);
     if(need.maxspin >= 2) Q.z2 = gf_spin3_mf(2, D, m12, m13, m23, cyc, inv_s);
     if(need.norm && need.maxspin >= 1) {
         Q.bw1 = gf_rcp(gf_damp_sq_norm(Q.q, 1, D.rad));
         Q.bwM1 = gf_rcp(gf_damp_sq_norm(Q.qMn, 1, D.mrad));
+        Q.sbw1 = sqrt(Q.bw1 * Q.bwM1);
     }
     if(need.norm && need.maxspin >= 2) {
         Q.bw2 = gf_rcp(gf_damp_sq_norm(Q.q, 2, D.rad));
         Q.bwM2 = gf_rcp(gf_damp_sq_norm(Q.qMn, 2, D.mrad));
+        Q.sbw2 = sqrt(Q.bw2 * Q.bwM2);
     }
 }
 __device__ inline double gf_pow_odd(double r, int spin) { // r^(2 spin + 1)
@@ -475,7 +487,15 @@ __device__ inline double2 gf_rbw_term(const gf_res_inv &R, const gf_pair_inv &P,
     double A = R.mass2 - P.s;
     double B = R.mw * gf_pow_odd(P.q * R.inv_q0, spin) * fr * P.inv_rs;
     double C = gf_rcp(A * A + B * B);
-    double f = sqrt(fr * frM) * (spin == 0 ? 1.0 : (spin == 2 ? P.z2 : P.z1)) * C;
+    // sqrt(fr frM) z C: spin 0 has fr = frM = z = 1 (exactly C); in the normalised form the square root splits into a factor per
+    // resonance and one per pair and spin, both taken once (<= 2 ulp from the square root of the product)
+    double f;
+    if(spin == 0)
+        f = C;
+    else if(R.norm)
+        f = (R.sfr * (spin == 2 ? P.sbw2 : P.sbw1)) * (spin == 2 ? P.z2 : P.z1) * C;
+    else
+        f = sqrt(fr * frM) * (spin == 2 ? P.z2 : P.z1) * C;
     return make_double2(A * f, B * f);
 }
 #ifndef GF_PAIR_UNROLL
