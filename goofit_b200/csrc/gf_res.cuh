@@ -464,9 +464,13 @@ __device__ inline void gf_pair_prepare(gf_pair_inv &Q, const gf_pair_need &need,
     }
 }
 __device__ inline double gf_pow_odd(double r, int spin) { // r^(2 spin + 1)
-    double r2 = r * r, out = r;
-    for(int k = 0; k < spin; ++k) out *= r2;
-    return out;
+    const double r2 = r * r, o1 = r * r2, o2 = o1 * r2; // the same products in the same order as the loop, selected instead of branched on
+    if(spin > 2) {
+        double out = o2;
+        for(int k = 2; k < spin; ++k) out *= r2;
+        return out;
+    }
+    return spin == 0 ? r : (spin == 1 ? o1 : o2);
 }
 // one plain-RBW term from the shared pieces (RBW.cu:9-86 with the event/pair part hoisted into P). Against the
 // reference's operation sequence this trades four divisions and one square root per resonance for multiplications by
@@ -480,6 +484,9 @@ __device__ inline double2 gf_rbw_term(const gf_res_inv &R, const gf_pair_inv &P,
             fr = R.frn[0] * (spin == 2 ? P.bw2 : P.bw1); // as Resonance.cu:91-100: anything but spin 2 takes the spin-1 form
             frM = R.frMn[0] * (spin == 2 ? P.bwM2 : P.bwM1);
         } else {
+            // not to be evaluated speculatively: with no plain-form resonance on the pair qMp is 0, and the division inside
+            // gf_damp_sq then takes its out-of-line path (0 / x) on every event for a value that is thrown away
+            asm volatile("");
             fr = gf_damp_sq(P.q, spin, D.rad);
             frM = gf_damp_sq(P.qMp, spin, D.mrad);
         }
