@@ -476,8 +476,30 @@ __device__ inline double gf_pow_odd(double r, int spin) { // r^(2 spin + 1)
 // reference's operation sequence this trades four divisions and one square root per resonance for multiplications by
 // reciprocals that are shared per pair (1/sqrt(s), 1/F(q), 1/F(qM)) or per resonance (1/q0), and takes
 // sqrt(fr * frM) once instead of sqrt(fr) * sqrt(frM): each substitution moves the result by at most an ulp or two.
+// the normalised form (and spin 0) with the spin known at compile time: the same operations in the same order as the general
+// function below, without its selects and loops (the spin is uniform over the warp, so the dispatch is one branch)
+template <int SPIN>
+__device__ __forceinline__ double2 gf_rbw_term_n(const gf_res_inv &R, const gf_pair_inv &P) {
+    const double A = R.mass2 - P.s;
+    const double x = P.q * R.inv_q0;
+    double pw = x;
+    if(SPIN >= 1) {
+        const double x2 = x * x;
+        pw = x * x2;
+        if(SPIN == 2) pw = pw * x2;
+    }
+    double B = R.mw * pw;
+    if(SPIN != 0) B = B * (R.frn[0] * (SPIN == 2 ? P.bw2 : P.bw1));
+    B = B * P.inv_rs;
+    const double C = gf_rcp(A * A + B * B);
+    const double f = SPIN == 0 ? C : (R.sfr * (SPIN == 2 ? P.sbw2 : P.sbw1)) * (SPIN == 2 ? P.z2 : P.z1) * C;
+    return make_double2(A * f, B * f);
+}
 __device__ inline double2 gf_rbw_term(const gf_res_inv &R, const gf_pair_inv &P, const gf_decay3 &D) {
     const int spin = R.spin;
+    if(spin == 0) return gf_rbw_term_n<0>(R, P);
+    if(R.norm && spin == 1) return gf_rbw_term_n<1>(R, P);
+    if(R.norm && spin == 2) return gf_rbw_term_n<2>(R, P);
     double fr = 1, frM = 1;
     if(spin != 0) {
         if(R.norm) {
