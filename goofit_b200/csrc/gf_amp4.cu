@@ -464,7 +464,9 @@ struct gf_ls_slot { // per-lineshape record in shared memory, filled once per bl
     const double *mcol, *dcol, *lp, *lc;
     double2 *out;
     double d1c, d2;
-    int kind, has_inv;
+    double r2;       // meson radius squared (Breit-Wigner family)
+    int kind, has_inv; // has_inv: 0 no; 1 yes; 2 + L: yes, and a relativistic Breit-Wigner with orbital momentum L <= 2 (gf_ls_bw_pt_t<L>)
+    int FF, pad;
 };
 __device__ __forceinline__ void gf_dmma(double &c0, double &c1, double a, double b) {
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
@@ -527,7 +529,14 @@ __global__ void __launch_bounds__(GF_THREADS, upd_blocks_per_sm(NB))
         L.dcol = (pair >= 2 && K.d[i] >= 0) ? A.kin + (size_t)K.d[i] * A.ld : nullptr;
         L.out = A.ls + (size_t)i * A.ld;
         L.has_inv = (L.dcol == nullptr && gf_ls_has_inv(L.kind)) ? 1 : 0;
-        if(L.has_inv) L.inv = gf_bw_invariants(L.kind == GF_LS_SBW, L.d1c, L.d2, L.lp[0], L.lp[1]);
+        L.r2 = 0; L.FF = 0; L.pad = 0;
+        if(L.has_inv) {
+            L.inv = gf_bw_invariants(L.kind == GF_LS_SBW, L.d1c, L.d2, L.lp[0], L.lp[1]);
+            const int orbital = (int)L.lc[1];
+            L.FF = (int)L.lc[2];
+            L.r2 = L.lc[3] * L.lc[3];
+            if(L.kind == GF_LS_RBW && orbital >= 0 && orbital <= 2) L.has_inv = 2 + orbital;
+        }
         slots[i] = L;
     }
     if(threadIdx.x == 0) {
@@ -648,7 +657,13 @@ __global__ void __launch_bounds__(GF_THREADS, upd_blocks_per_sm(NB))
                 const gf_ls_slot &L = slots[i];
                 const double mres = __ldg(L.mcol + e);
                 gf_cplx r;
-                if(L.has_inv)
+                if(L.has_inv == 3)
+                    r = gf_ls_bw_pt_t<1>(mres, L.lp[0], L.lp[1], L.FF, L.r2, L.inv);
+                else if(L.has_inv == 2)
+                    r = gf_ls_bw_pt_t<0>(mres, L.lp[0], L.lp[1], L.FF, L.r2, L.inv);
+                else if(L.has_inv == 4)
+                    r = gf_ls_bw_pt_t<2>(mres, L.lp[0], L.lp[1], L.FF, L.r2, L.inv);
+                else if(L.has_inv)
                     r = gf_lineshape_inv(L.kind, L.lp, L.lc, mres, L.inv);
                 else
                     r = gf_lineshape(L.kind, L.lp, L.lc, mres, L.dcol ? __ldg(L.dcol + e) : L.d1c, L.d2);
