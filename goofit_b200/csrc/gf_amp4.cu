@@ -245,24 +245,34 @@ struct gf_upd_plan {
     int toff;  // row offset of the amplitude's Re row in the warp's MMA tile, in doubles
     int shape; // nPerm * 100 + LS_step * 10 + SF_step, or 0: not one of the compiled shapes, go through the record
     int amp;
-    int pad;
+    int same;  // the previous plan of the block has the same shape and the same lineshape planes: their products are reused
 };
+// prod[p] = the product of the lineshapes of permutation p, kept from the previous amplitude when this one has the very same
+// lineshape list (pl.same: the S, P and D waves of one decay chain differ in their spin factors only) - the same intermediate
+// value the reference's loop passes through, so nothing changes in the result; 8 of the 16 lineshape loads of a DP4 K* move go
 template <int LS_STEP, int SF_STEP, int NPERM>
-__device__ __forceinline__ double2 gf_amp4_one_p(const gf_upd_plan &pl, long e) {
+__device__ __forceinline__ double2 gf_amp4_one_p(const gf_upd_plan &pl, long e, gf_cplx (&prod)[2]) {
     constexpr int NLS = LS_STEP * NPERM, NSF = SF_STEP * NPERM;
-    static_assert(NLS <= GF_PLAN_MAXLS && NSF <= GF_PLAN_MAXSF, "plan too small for this shape");
-    double2 L[NLS];
+    static_assert(NLS <= GF_PLAN_MAXLS && NSF <= GF_PLAN_MAXSF && NPERM <= 2, "plan too small for this shape");
     double S[NSF];
 #pragma unroll
-    for(int j = 0; j < NLS; ++j) L[j] = pl.ls[j][e];
-#pragma unroll
     for(int j = 0; j < NSF; ++j) S[j] = __ldg(pl.sf[j] + e);
+    if(!pl.same) {
+        double2 L[NLS];
+#pragma unroll
+        for(int j = 0; j < NLS; ++j) L[j] = pl.ls[j][e];
+#pragma unroll
+        for(int p = 0; p < NPERM; ++p) {
+            gf_cplx ret = gf_c(1, 0);
+#pragma unroll
+            for(int j = 0; j < LS_STEP; ++j) ret = ret * gf_c(L[p * LS_STEP + j].x, L[p * LS_STEP + j].y);
+            prod[p] = ret;
+        }
+    }
     gf_cplx total = gf_c(0, 0);
 #pragma unroll
     for(int p = 0; p < NPERM; ++p) {
-        gf_cplx ret = gf_c(1, 0);
-#pragma unroll
-        for(int j = 0; j < LS_STEP; ++j) ret = ret * gf_c(L[p * LS_STEP + j].x, L[p * LS_STEP + j].y);
+        gf_cplx ret = prod[p];
 #pragma unroll
         for(int j = 0; j < SF_STEP; ++j) ret = ret * gf_c(S[p * SF_STEP + j], 0.0);
         total = total + ret;
@@ -456,7 +466,7 @@ __global__ void __launch_bounds__(GF_THREADS, 2)
 #define GF_UPD_PF_POS 2
 #endif
 #ifndef GF_UPD_PF_L1
-#define GF_UPD_PF_L1 1
+#define GF_UPD_PF_L1 0 // measured after the L2 request moved late: 1.392 ms with, 1.358 ms without (DP4 K* move)
 #endif
 #define GF_UPD_TS 36 // tile row stride in doubles: 4 mod 16, so the MMA fragment reads (8 rows x 4 events) of a half-warp hit 16 different 8-byte banks
 struct gf_ls_slot { // per-lineshape record in shared memory, filled once per block for the flagged lineshapes
@@ -494,7 +504,7 @@ __global__ void __launch_bounds__(GF_THREADS, upd_blocks_per_sm(NB))
     // into L2 while the current ones compute (measured on the DP4 K*(892) move: 1.96 -> 1.77 ms per likelihood call)
     __shared__ const char *pf_base[160];
     __shared__ unsigned char pf_bytes[160];
-    __shared__ int npf;
+    __shared__ int npf, npf_l1;
     // resolved per block: where each rebuilt amplitude reads and writes, where each standing one is read, and which lines of the
     // next group every lane requests (GF_PF_K planes per lane: plane (lane >> 2) + 8 k, line lane & 3 of its 32-event span)
     __shared__ gf_upd_plan plans[16];
@@ -562,6 +572,7 @@ __global__ void __launch_bounds__(GF_THREADS, upd_blocks_per_sm(NB))
             if((ls_in >> i) & 1ull) { pf_base[np] = reinterpret_cast<const char *>(A.ls + (size_t)i * A.ld); pf_bytes[np++] = 16; }
         for(int k = 0; k < nSF; ++k)
             if((sf_in >> k) & 1ull) { pf_base[np] = reinterpret_cast<const char *>(A.sf + (size_t)k * A.ld); pf_bytes[np++] = 8; }
+        npf_l1 = GF_UPD_PF_L1 == 2 ? np : 160; // L1 requests: 2 = only the planes read late in the iteration (by the amplitudes)
         if(NB > 0)
             for(int u = 0; u < nu; ++u) { pf_base[np] = reinterpret_cast<const char *>(A.amps + (size_t)untouched[u] * A.ld); pf_bytes[np++] = 16; }
         for(int f = 0; f < nf && np < 156; ++f) { // pair masses of the flagged lineshapes
@@ -583,7 +594,7 @@ __global__ void __launch_bounds__(GF_THREADS, upd_blocks_per_sm(NB))
         const int j = (l >> 2) + 8 * k;
         const bool on = j < npf && (l & 3) * 128 < 32 * pf_bytes[j];
         pf_lane[k][l] = on ? pf_base[j] + (l & 3) * 128 : nullptr;
-        pf_is16[k][l] = on && pf_bytes[j] == 16;
+        pf_is16[k][l] = (on && pf_bytes[j] == 16 ? 1 : 0) | (on && j < npf_l1 ? 2 : 0);
     }
     if((int)threadIdx.x < nun) {
         const int a = untouched[threadIdx.x];
@@ -597,7 +608,13 @@ __global__ void __launch_bounds__(GF_THREADS, upd_blocks_per_sm(NB))
         gf_upd_plan pl;
         pl.shape = gf_amp4_plan_shape(rec);
         pl.amp = a;
-        pl.pad = 0;
+        pl.same = 0;
+        if(k > 0 && pl.shape) {
+            const int32_t *prev = rec0 + start[rebuilt[k - 1]];
+            bool same = prev[0] == rec[0] && prev[1] == rec[1] && prev[2] == rec[2];
+            for(int j = 0; same && j < rec[0]; ++j) same = prev[3 + j] == rec[3 + j];
+            pl.same = same ? 1 : 0;
+        }
         pl.out = A.amps + (size_t)a * A.ld;
         pl.toff = ((a >> 3) * 16 + (a & 7)) * GF_UPD_TS;
         for(int j = 0; j < GF_PLAN_MAXLS; ++j) pl.ls[j] = (pl.shape && j < rec[0]) ? A.ls + (size_t)rec[3 + j] * A.ld : nullptr;
@@ -629,8 +646,9 @@ __global__ void __launch_bounds__(GF_THREADS, upd_blocks_per_sm(NB))
             for(int k = 0; k < GF_PF_K; ++k) {
                 const char *q = pf_lane[k][lane];
                 if(q) {
-                    const bool wide = pf_is16[k][lane];
-                    if(l1) asm volatile("prefetch.global.L1 [%0];" ::"l"(q + (wide ? 2 * cur8 : cur8)));
+                    const int fl = pf_is16[k][lane];
+                    const bool wide = fl & 1;
+                    if(l1 && (fl & 2)) asm volatile("prefetch.global.L1 [%0];" ::"l"(q + (wide ? 2 * cur8 : cur8)));
                     if(l2 && more) asm volatile("prefetch.global.L2 [%0];" ::"l"(q + (wide ? 2 * off8 : off8)));
                 }
             }
@@ -670,16 +688,17 @@ __global__ void __launch_bounds__(GF_THREADS, upd_blocks_per_sm(NB))
                 GF_UPD_STORE_LS(L.out + e, make_double2(r.re, r.im));
             }
             if(GF_UPD_PF_L2 != 0 && GF_UPD_PF_POS == 1) request(false, true);
+            gf_cplx prod[2] = {gf_c(0, 0), gf_c(0, 0)};
             for(int k = 0; k < nre; ++k) {
                 const gf_upd_plan &pl = plans[k];
                 double2 v;
                 switch(pl.shape) { // uniform over the grid
-                case 221: v = gf_amp4_one_p<2, 1, 2>(pl, e); break; // Bose-symmetrised two-resonance chains (DP4, TDDP4)
-                case 121: v = gf_amp4_one_p<2, 1, 1>(pl, e); break;
-                case 111: v = gf_amp4_one_p<1, 1, 1>(pl, e); break;
-                case 211: v = gf_amp4_one_p<1, 1, 2>(pl, e); break;
-                case 131: v = gf_amp4_one_p<3, 1, 1>(pl, e); break;
-                case 231: v = gf_amp4_one_p<3, 1, 2>(pl, e); break;
+                case 221: v = gf_amp4_one_p<2, 1, 2>(pl, e, prod); break; // Bose-symmetrised two-resonance chains (DP4, TDDP4)
+                case 121: v = gf_amp4_one_p<2, 1, 1>(pl, e, prod); break;
+                case 111: v = gf_amp4_one_p<1, 1, 1>(pl, e, prod); break;
+                case 211: v = gf_amp4_one_p<1, 1, 2>(pl, e, prod); break;
+                case 131: v = gf_amp4_one_p<3, 1, 1>(pl, e, prod); break;
+                case 231: v = gf_amp4_one_p<3, 1, 2>(pl, e, prod); break;
                 default: v = gf_amp4_build<true>(rec0 + start[pl.amp], A, e);
                 }
                 GF_UPD_STORE_AMP(pl.out + e, v);
