@@ -1,0 +1,6 @@
+// Source-compatibility header: the reference's <goofit/PDFs/physics/DP4Pdf.h> include path, served by the B200 host API.
+#pragma once
+#include <goofit/detail/Physics4.h>
+namespace GooFit {
+using DPPdf = Amp4Body;
+}

@@ -1,0 +1,6 @@
+// Source-compatibility header: the reference's <goofit/PDFs/physics/TddpPdf.h> include path, served by the B200 host API.
+#pragma once
+#include <goofit/detail/Physics3.h>
+namespace GooFit {
+using TddpPdf = Amp3Body_TD;
+}

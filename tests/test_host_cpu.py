@@ -381,3 +381,40 @@ def test_minuit2_module_minimises_a_python_function():
     assert gf.FunctionMinimum is m2.FunctionMinimum and issubclass(gf.FCN, m2.FCNBase)
     lvl = m2.MnPrint.GlobalLevel()
     m2.MnPrint.SetGlobalLevel(lvl)
+
+
+def test_reference_include_paths_compile(tmp_path):
+    """A user of the reference switches by changing the include directory: every <goofit/...> path of a class that is built here
+    must exist and compile, including the reference's own pre-2.2 alias headers (DalitzPlotPdf.h:8, Tddp4Pdf.h:8, ...)."""
+    import shutil
+    import subprocess
+    cxx = shutil.which("g++")
+    if cxx is None:
+        pytest.skip("no g++")
+    inc = os.path.join(ROOT, "goofit_b200", "host", "include")
+    headers = []
+    for base, _, files in os.walk(os.path.join(inc, "goofit")):
+        for f in sorted(files):
+            if f.endswith(".h"):
+                headers.append(os.path.relpath(os.path.join(base, f), inc))
+    assert len(headers) > 80
+    for must in ("goofit/PDFs/physics/Amp3Body_TD.h", "goofit/PDFs/physics/Lineshapes.h", "goofit/PDFs/physics/lineshapes/kMatrix.h",
+                 "goofit/PDFs/physics/resonances/kMatrix.h", "goofit/PDFs/physics/detail/NormEvents_4Body_Weighted.h",
+                 "goofit/PDFs/combine/EventWeightedAddPdf.h", "goofit/PDFs/combine/MappedPdf.h", "goofit/PDFs/physics/Tddp4Pdf.h"):
+        assert must in headers, must
+    src = tmp_path / "all_headers.cpp"
+    src.write_text("".join("#include <%s>\n" % h for h in sorted(headers)) + """
+#include <type_traits>
+using namespace GooFit;
+static_assert(std::is_same<DalitzPlotPdf, Amp3Body>::value && std::is_same<TDDP4, Amp4Body_TD>::value, "alias headers");
+static_assert(std::is_same<TddpPdf, Amp3Body_TD>::value && std::is_same<DPPdf, Amp4Body>::value, "alias headers");
+int main() { return 0; }
+""")
+    minuit = "/root/reference/extern/Minuit2/inc"
+    cmd = [cxx, "-std=c++17", "-fsyntax-only", "-I" + os.path.join(ROOT, "include"), "-I" + inc, "-DMATHCORE_STANDALONE", str(src)]
+    if os.path.isdir(minuit):
+        cmd.insert(2, "-I" + minuit)
+    else:
+        pytest.skip("Minuit2 headers (reference checkout) are not on this machine")
+    out = subprocess.run(cmd, capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr[-3000:]
