@@ -110,6 +110,8 @@ static int program_class(const gf_ctx *c, int first, int root) {
         case GF_OP_AMP3: has |= GF_HAS_AMP3; break;
         case GF_OP_AMP4: has |= GF_HAS_AMP4; break;
         case GF_OP_AMP3_TD: has |= GF_HAS_AMP3_TD | GF_HAS_3GAUSS; break;
+        case GF_OP_COMPOSITE_ARG:
+        case GF_OP_COMPOSITE: has |= GF_HAS_COMPOSITE; break;
         case GF_OP_AMP4_TD: {
             has |= GF_HAS_AMP4_TD;
             const int32_t *in = c->h_ints.data() + c->h_nodes[k].int_off; // ints[4] -> {resolution record, flags}
@@ -355,6 +357,9 @@ extern "C" int gf_validate_program(const gf_node *nodes, int n_nodes, int n_cons
                 if(nd.op == GF_OP_ADD_EXT && nd.npar < nd.nchild) return gf_fail("gf_set_program: AddPdf weights, node " + std::to_string(k));
                 if(nd.op == GF_OP_EVTW_ADD && nd.nobs < nd.nchild - 1) return gf_fail("gf_set_program: EventWeightedAddPdf weight columns, node " + std::to_string(k));
                 if(nd.op == GF_OP_EVTW_ADD_EXT && nd.nobs < nd.nchild) return gf_fail("gf_set_program: EventWeightedAddPdf weight columns, node " + std::to_string(k));
+                if(nd.op == GF_OP_COMPOSITE_ARG && (nd.nchild != 1 || nd.nobs < 1)) return gf_fail("gf_set_program: CompositePdf argument record, node " + std::to_string(k));
+                if(nd.op == GF_OP_COMPOSITE && (nd.nchild != 2 || k - 1 - nodes[k - 1].size < 0 || nodes[k - 1 - nodes[k - 1].size].op != GF_OP_COMPOSITE_ARG))
+                    return gf_fail("gf_set_program: CompositePdf record without its argument record, node " + std::to_string(k));
                 if(nd.op == GF_OP_MAPPED && nd.nchild < 2) return gf_fail("gf_set_program: MappedPdf needs a mapping function and a component, node " + std::to_string(k));
                 if(nd.op >= GF_OP_AMP3 && nd.op <= GF_OP_AMP3_TD) pops = 1; // the efficiency
                 if(sp < pops) return gf_fail("gf_set_program: value-stack underflow at node " + std::to_string(k));

@@ -321,13 +321,31 @@ __device__ inline void gf_amp4td_AB(const double *p, const int32_t *flags, int n
 // the larger batches spill under the 64-register cap)
 #define GF_TD_CH 4
 // GF_HAS_3GAUSS: the Amp4Body_TD node may carry a ThreeGaussResolution (else TruthResolution only)
-enum : int { GF_HAS_CONV = 1, GF_HAS_AMP3 = 2, GF_HAS_AMP4 = 4, GF_HAS_AMP4_TD = 8, GF_HAS_3GAUSS = 16, GF_HAS_AMP3_TD = 32, GF_HAS_ALL = 63 };
+enum : int { GF_HAS_CONV = 1, GF_HAS_AMP3 = 2, GF_HAS_AMP4 = 4, GF_HAS_AMP4_TD = 8, GF_HAS_3GAUSS = 16, GF_HAS_AMP3_TD = 32, GF_HAS_COMPOSITE = 64, GF_HAS_ALL = 127 };
+
+// the event as the interpreter reads it: the caller's accessor, with one column substituted while a CompositePdf's shell runs
+template <bool ON, class Evt>
+struct gf_evt_sub {
+    const Evt &in;
+    double val;
+    int obs;
+    __device__ inline double operator()(int ob) const {
+        if constexpr(ON) {
+            if(ob == obs) return val;
+        }
+        return in(ob);
+    }
+    __device__ inline long event_number(int col) const { return in.event_number(col); }
+};
 
 // Post-order evaluation of nodes [first, last]; returns the root's raw value.
 template <int HAS = GF_HAS_ALL, class Evt>
-__device__ inline double gf_eval_tree(const gf_sprog &P, const gf_dev_view &V, int first, int last, const Evt &evt) {
+__device__ inline double gf_eval_tree(const gf_sprog &P, const gf_dev_view &V, int first, int last, const Evt &evt_in) {
     double st[GF_MAX_STACK];
     int sp = 0;
+    // CompositePdf evaluates its shell on a copy of the event in which one observable holds the core function's value
+    // (CompositePdf.cu:24-31): between the GF_OP_COMPOSITE_ARG and GF_OP_COMPOSITE records reads of that column are substituted
+    gf_evt_sub<(HAS & GF_HAS_COMPOSITE) != 0, Evt> evt{evt_in, 0.0, -1};
     for(int k = first; k <= last; ++k) {
         const gf_node &nd = P.nodes[k];
         if(nd.op < GF_OP_ADD) {
@@ -410,6 +428,15 @@ __device__ inline double gf_eval_tree(const gf_sprog &P, const gf_dev_view &V, i
             double ret = ch[1 + target] * P.norms[in[1 + target]];
             sp -= n;
             st[sp++] = ret;
+        } break;
+        case GF_OP_COMPOSITE_ARG: if constexpr((HAS & GF_HAS_COMPOSITE) != 0) { // the core's value stays on the stack
+            evt.val = st[sp - 1];
+            evt.obs = nd.nobs > 0 ? P.ints[nd.obs_off] : -1;
+        } break;
+        case GF_OP_COMPOSITE: if constexpr((HAS & GF_HAS_COMPOSITE) != 0) { // [core value, shell value] -> shell value
+            evt.obs = -1;
+            st[sp - 2] = st[sp - 1];
+            sp -= 1;
         } break;
         case GF_OP_CONVOLVE: if constexpr((HAS & GF_HAS_CONV) != 0) { // combine/ConvolutionPdf.cu:27-75 via the per-offset table (gf_conv.cu)
             // ints = {aux slot, model root, resolution root}; consts = lo, hi, step

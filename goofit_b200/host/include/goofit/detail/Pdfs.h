@@ -100,6 +100,16 @@ class MappedPdf : public CombinePdf {
     bool hasAnalyticIntegral() const override { return false; }
 };
 
+/// combine/CompositePdf.h: f(x) = h(g(x)) for a core function g of any number of observables and a shell h of one. Neither is
+/// normalised inside the composite; the composite itself is, by the usual grid integral (CompositePdf.cu:38-75).
+class CompositePdf : public CombinePdf {
+  public:
+    CompositePdf(std::string n, PdfBase *core, PdfBase *shell);
+    fptype normalize() override;
+    bool hasAnalyticIntegral() const override { return false; }
+    int emit(detail::ProgramBuilder &B) override;
+};
+
 class ProdPdf : public CombinePdf { // combine/ProdPdf.h
   public:
     ProdPdf(std::string n, std::vector<PdfBase *> comps);

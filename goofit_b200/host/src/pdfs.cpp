@@ -265,6 +265,38 @@ fptype MappedPdf::normalize() {
     return ret;
 }
 
+// ---- CompositePdf (combine/CompositePdf.cu:38-75) -----------------------------------------------------------------
+CompositePdf::CompositePdf(std::string n, PdfBase *core, PdfBase *shell)
+    : CombinePdf("CompositePdf", n) {
+    if(!core || !shell) throw GeneralError("CompositePdf {} needs a core and a shell function", n);
+    // one substitution is live at a time on the device: a shell that is itself built on a composite would lose the outer one
+    std::vector<PdfBase *> todo{shell};
+    while(!todo.empty()) {
+        PdfBase *p = todo.back();
+        todo.pop_back();
+        if(dynamic_cast<CompositePdf *>(p)) throw GeneralError("CompositePdf {}: the shell may not contain another CompositePdf", n);
+        for(PdfBase *c : p->getComponents()) todo.push_back(c);
+    }
+    components.push_back(core);
+    components.push_back(shell);
+    observablesList = getObservables();
+    registerFunction("ptr_to_Composite", GF_OP_COMPOSITE);
+}
+// core nodes, the argument record (from here on the composite's observable 0 reads as the core's value), shell nodes, the record
+int CompositePdf::emit(detail::ProgramBuilder &B) {
+    const int first = (int)B.nodes.size();
+    const int coreSlot = B.nodes[components[0]->emit(B)].norm_slot;
+    emitRecord(B, GF_OP_COMPOSITE_ARG, 1, (int)B.nodes.size() - first + 1, {coreSlot});
+    const int shellSlot = B.nodes[components[1]->emit(B)].norm_slot;
+    return emitRecord(B, GF_OP_COMPOSITE, 2, (int)B.nodes.size() - first + 1, {coreSlot, shellSlot});
+}
+fptype CompositePdf::normalize() {
+    recursiveSetNormalization(1.0);
+    // the components may appear elsewhere in the full function and need their normalisation there (CompositePdf.cu:57-68)
+    for(PdfBase *c : components) c->normalize();
+    return GooPdf::normalize();
+}
+
 // ---- ProdPdf (combine/ProdPdf.cu:30-99) ---------------------------------------------------------------------
 ProdPdf::ProdPdf(std::string n, std::vector<PdfBase *> comps)
     : CombinePdf("ProdPdf", n) {

@@ -297,6 +297,8 @@ PYBIND11_MODULE(_goofit, m) {
     py::class_<MappedPdf, CombinePdf>(m, "MappedPdf")
         .def(py::init([](std::string n, GooPdf *map, std::vector<GooPdf *> t) { return new MappedPdf(n, map, t); }), "name"_a, "m"_a, "t"_a,
              py::keep_alive<1, 3>(), py::keep_alive<1, 4>());
+    py::class_<CompositePdf, CombinePdf>(m, "CompositePdf")
+        .def(py::init<std::string, PdfBase *, PdfBase *>(), "name"_a, "core"_a, "shell"_a, py::keep_alive<1, 3>(), py::keep_alive<1, 4>());
     py::class_<ConvolutionPdf, CombinePdf>(m, "ConvolutionPdf")
         .def(py::init<std::string, Observable, GooPdf *, GooPdf *>(), "name"_a, "x"_a, "model"_a, "resolution"_a, py::keep_alive<1, 4>(), py::keep_alive<1, 5>())
         .def("setIntegrationConstants", &ConvolutionPdf::setIntegrationConstants, "lo"_a, "hi"_a, "step"_a);

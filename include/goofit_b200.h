@@ -72,6 +72,9 @@ enum gf_op {
     GF_OP_EVTW_ADD,         /* EventWeightedAddPdf.cu:8-44   weights = the first nchild-1 observable columns of the record */
     GF_OP_EVTW_ADD_EXT,     /* EventWeightedAddPdf.cu:46-91  one weight column per component, sum divided by the total weight */
     GF_OP_MAPPED,           /* MappedPdf.cu:6-38  child 0 = mapping function, value rounded to the index of the component to return */
+    GF_OP_COMPOSITE_ARG,    /* CompositePdf.cu:6-24  child: the core function g; its value (left on the stack) becomes what the composite's
+                             * observable 0 reads as, until the GF_OP_COMPOSITE record that follows the shell */
+    GF_OP_COMPOSITE,        /* CompositePdf.cu:26-36 children: the GF_OP_COMPOSITE_ARG record and the shell h; value = h(g(event)), neither normalised */
     GF_OP_AMP3 = 48,        /* Amp3Body.cu:60  child: efficiency; ints: amp3 id */
     GF_OP_AMP4,             /* Amp4Body.cu:53 */
     GF_OP_AMP4_TD,          /* Amp4Body_TD.cu:167 */

@@ -22,6 +22,7 @@
 #include <goofit/PDFs/combine/AddPdf.h>
 #include <goofit/PDFs/combine/ConvolutionPdf.h>
 #include <goofit/PDFs/combine/EventWeightedAddPdf.h>
+#include <goofit/PDFs/combine/CompositePdf.h>
 #include <goofit/PDFs/combine/MappedPdf.h>
 #include <goofit/PDFs/combine/ProdPdf.h>
 #include <goofit/PDFs/physics/Amp3Body.h>
@@ -1134,6 +1135,50 @@ static void case_combine2() {
     }
 }
 
+// ---- CompositePdf: f(x) = h(g(x)), core g = 0.5 + 0.8 x, shell h = Gaussian; a second one with a two-observable core (combine/CompositePdf.cu)
+static void case_composite() {
+    Observable x{"x", -5, 5}, y{"y", -2, 2};
+    std::mt19937_64 gen(4711);
+    std::normal_distribution<double> g(-0.2, 1.4);
+    std::uniform_real_distribution<double> u(-2, 2);
+    std::vector<double> X, Y;
+    while(X.size() < 600) {
+        double v = g(gen);
+        if(v <= -5 || v >= 5) continue;
+        X.push_back(v); Y.push_back(u(gen));
+    }
+    save_npy("composite.x", X); save_npy("composite.y", Y);
+    Variable c0("c0", 0.5), c1("c1", 0.8), mean("cmean", 0.3, 0.1, -3, 3), sigma("csigma", 1.5, 0.1, 0.3, 4);
+    {
+        PolynomialPdf core("core", x, std::vector<Variable>{c0, c1});
+        GaussianPdf shell("shell", x, mean, sigma);
+        CompositePdf comp("comp", &core, &shell);
+        UnbinnedDataSet d({x});
+        for(size_t i = 0; i < X.size(); i++) { x.setValue(X[i]); d.addEvent(); }
+        comp.setData(&d);
+        put("composite.nll", comp.calculateNLL());
+        save_npy("composite.prob", comp.getCompProbsAtDataPoints()[0]);
+        // as a component of a sum, next to a plain shape of the same observable
+        Variable al("calpha", -0.2, 0.1, -2, 2), frac("cfrac", 0.6, 0.1, 0, 1);
+        ExpPdf ex("cex", x, al);
+        AddPdf sum("csum", frac, &comp, &ex);
+        sum.setData(&d);
+        put("composite.sum_nll", static_cast<GooPdf &>(sum).calculateNLL());
+        save_npy("composite.sum_prob", sum.getCompProbsAtDataPoints()[0]);
+    }
+    { // core of two observables (x first: its column is the one the shell reads the core value from)
+        Variable k0("k0", 0.25), zero("kzero", 0);
+        PolynomialPdf core("core2", std::vector<Observable>{x, y}, std::vector<Variable>{k0, c1, c1, k0}, std::vector<Variable>{zero, zero}, 1);
+        GaussianPdf shell("shell2", x, mean, sigma);
+        CompositePdf comp("comp2", &core, &shell);
+        UnbinnedDataSet d({x, y});
+        for(size_t i = 0; i < X.size(); i++) { x.setValue(X[i]); y.setValue(Y[i]); d.addEvent(); }
+        comp.setData(&d);
+        put("composite.two_nll", comp.calculateNLL());
+        save_npy("composite.two_prob", comp.getCompProbsAtDataPoints()[0]);
+    }
+}
+
 static void case_dp4_fit() {
     DP4Model *M = make_dp4(60000, false);
     UnbinnedDataSet cand({M->m12, M->m34, M->cos12, M->cos34, M->phi, M->eventNumber});
@@ -1780,6 +1825,7 @@ int main(int argc, char **argv) {
             if(only == "all" || only == "kmatrix") case_kmatrix();
             if(only == "all" || only == "td3") case_td3();
             if(only == "all" || only == "combine2") case_combine2();
+            if(only == "all" || only == "composite") case_composite();
             if(only == "all" || only == "dalitzfit") case_dalitz_fit();
             if(only == "all" || only == "dp4") case_dp4();
             if(only == "all" || only == "dp4fit") case_dp4_fit();

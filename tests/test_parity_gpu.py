@@ -259,6 +259,43 @@ def test_event_weighted_add_and_mapped(golden):
     assert moved[S == 1].all() and not moved[S != 1].any()
 
 
+def test_composite_pdf(golden):
+    """combine/CompositePdf.cu: f = h(g(event)); the shell h reads the core's value where the composite's first observable sits in
+    the event, neither is normalised inside, the composite is (grid integral). Alone, inside an AddPdf, and with a core of two
+    observables (oracle/ref_driver.cpp case_composite)."""
+    V = gf.Variable
+    x = gf.Observable("x", -5, 5)
+    y = gf.Observable("y", -2, 2)
+    X, Y = golden.arr("composite.x"), golden.arr("composite.y")
+    c0, c1 = V("c0", 0.5), V("c1", 0.8)
+    mean, sigma = V("cmean", 0.3, 0.1, -3, 3), V("csigma", 1.5, 0.1, 0.3, 4)
+
+    def check(pdf, data, tag):
+        pdf.setData(data)
+        nll = pdf.calculateNLL()
+        assert gf.last_kernel_name() == "k_eval_sum"
+        assert rel(nll, golden["composite.%snll" % tag]) < RTOL_NLL, (tag, nll, golden["composite.%snll" % tag])
+        probs = np.asarray(pdf.getCompProbsAtDataPoints()[0])
+        np.testing.assert_allclose(probs, golden.arr("composite.%sprob" % tag), rtol=RTOL_EVT, atol=0)
+        pdf.setFitControl(gf.UnbinnedNllFit())
+        pdf.setData(data)
+        assert pdf.calculateNLL() == nll
+
+    core = gf.PolynomialPdf("core", x, [c0, c1])
+    shell = gf.GaussianPdf("shell", x, mean, sigma)
+    comp = gf.CompositePdf("comp", core, shell)
+    d = dataset_from_columns([x], [X])
+    check(comp, d, "")
+    ex = gf.ExpPdf("cex", x, V("calpha", -0.2, 0.1, -2, 2))
+    check(gf.AddPdf("csum", V("cfrac", 0.6, 0.1, 0, 1), comp, ex), d, "sum_")
+    k0, zero = V("k0", 0.25), V("kzero", 0)
+    core2 = gf.PolynomialPdf("core2", [x, y], [k0, c1, c1, k0], [zero, zero], 1)
+    shell2 = gf.GaussianPdf("shell2", x, mean, sigma)
+    check(gf.CompositePdf("comp2", core2, shell2), dataset_from_columns([x, y], [X, Y]), "two_")
+    with pytest.raises(Exception):
+        gf.CompositePdf("nested", core, gf.CompositePdf("inner", core, shell))  # one substitution at a time: rejected on the host
+
+
 def test_dalitz_values(golden):
     M = Dalitz(float_masses=True, grid=120)
     m12, m13 = golden.arr("dalitz.m12"), golden.arr("dalitz.m13")
