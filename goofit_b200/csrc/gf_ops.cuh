@@ -23,6 +23,48 @@ __device__ inline double gf_klbw_momentum(double mass, double pimass, double d0m
 }
 __device__ inline double gf_klbw_factor(double momentum) { return 1 / sqrt(1.0 + 2.56 * momentum * momentum); }
 
+// Landau density by the CERNLIB G110 DENLAN rational approximations (Koelbig & Schorr, Comput. Phys. Commun. 31 (1984) 97), the
+// algorithm basic/LandauPdf.cu:8-86 evaluates: seven ranges of v = (x - mpv) / sigma, each a ratio of two quartic polynomials in v
+// or 1/v (Horner form, innermost coefficient first as upstream), with asymptotic forms below -5.5 and above 300.
+__device__ inline double gf_quartic(const double (&k)[5], double t) { return k[0] + (k[1] + (k[2] + (k[3] + k[4] * t) * t) * t) * t; }
+__device__ inline double gf_landau(double x, double mpv, double sigma) {
+    if(sigma <= 0) return 0;
+    // rows: -5.5 <= v < -1, -1 <= v < 1, 1 <= v < 5 (in v); 5 <= v < 12, 12 <= v < 50, 50 <= v < 300 (in 1/v)
+    const double num[6][5] = {{0.4259894875, -0.1249762550, 0.03984243700, -0.006298287635, 0.001511162253},
+                              {0.1788541609, 0.1173957403, 0.01488850518, -0.001394989411, 0.0001283617211},
+                              {0.1788544503, 0.09359161662, 0.006325387654, 0.00006611667319, -0.000002031049101},
+                              {0.9874054407, 118.6723273, 849.2794360, -743.7792444, 427.0262186},
+                              {1.003675074, 167.5702434, 4789.711289, 21217.86767, -22324.94910},
+                              {1.000827619, 664.9143136, 62972.92665, 475554.6998, -5743609.109}};
+    const double den[6][5] = {{1.0, -0.3388260629, 0.09594393323, -0.01608042283, 0.003778942063},
+                              {1.0, 0.7428795082, 0.3153932961, 0.06694219548, 0.008790609714},
+                              {1.0, 0.6097809921, 0.2560616665, 0.04746722384, 0.006957301675},
+                              {1.0, 106.8615961, 337.6496214, 2016.712389, 1597.063511},
+                              {1.0, 156.9424537, 3745.310488, 9834.698876, 66924.28357},
+                              {1.0, 651.4101098, 56974.73333, 165917.4725, -2815759.939}};
+    const double v = (x - mpv) / sigma;
+    double d;
+    if(v < -5.5) {
+        const double u = exp(v + 1.0);
+        if(u < 1e-10) return 0.0;
+        d = 0.3989422803 * (exp(-1 / u) / sqrt(u)) * (1 + (0.04166666667 + (-0.01996527778 + 0.02709538966 * u) * u) * u);
+    } else if(v < -1) {
+        const double u = exp(-v - 1);
+        d = exp(-u) * sqrt(u) * gf_quartic(num[0], v) / gf_quartic(den[0], v);
+    } else if(v < 5) {
+        const int r = v < 1 ? 1 : 2;
+        d = gf_quartic(num[r], v) / gf_quartic(den[r], v);
+    } else if(v < 300) {
+        const int r = v < 12 ? 3 : (v < 50 ? 4 : 5);
+        const double u = 1 / v;
+        d = u * u * gf_quartic(num[r], u) / gf_quartic(den[r], u);
+    } else {
+        const double u = 1 / (v - v * log(v) / (v + 1));
+        d = u * u * (1 + (-1.845568670 + -4.284640743 * u) * u);
+    }
+    return d / sigma;
+}
+
 template <class Evt>
 __device__ inline double gf_leaf(const gf_node &nd, const gf_sprog &P, const Evt &evt) {
     const double *p = P.params + nd.par_off;
@@ -128,6 +170,102 @@ __device__ inline double gf_leaf(const gf_node &nd, const gf_sprog &P, const Evt
         double g = p[2] + p[3] * log(px + sq);
         return p[3] / (p[1] * 2.506628 * sq) * exp(-0.5 * g * g);
     }
+    case GF_OP_BW: { // basic/BWPdf.cu:6-18 (its "rootPi" is -2 atan2(-1, 0) = pi)
+        double x = evt(ob[0]), mean = p[0], gamma = p[1];
+        double pi_ = -2. * atan2(-1.0, 0.0);
+        return (gamma / ((x - mean) * (x - mean) + gamma * gamma / 4)) / (2 * pi_);
+    }
+    case GF_OP_BIFURGAUSS: { // basic/BifurGaussPdf.cu:6-22
+        double x = evt(ob[0]), mean = p[0];
+        double sigma = x > mean ? p[2] : p[1];
+        return exp(-0.5 * (x - mean) * (x - mean) / (sigma * sigma));
+    }
+    case GF_OP_CRYSTALBALL: { // basic/CrystalBallPdf.cu:6-35
+        double x = evt(ob[0]), mean = p[0], sigma = p[1], alpha = p[2], power = p[3];
+        double rx = (sigma != 0) ? (x - mean) / sigma : 0;
+        if((alpha > 0 && rx <= alpha) || (alpha < 0 && rx >= alpha) || alpha == 0) return exp(-0.5 * rx * rx);
+        double n_over_alpha = power / alpha;
+        double a = exp(-0.5 * alpha * alpha);
+        double d = (n_over_alpha - alpha) + rx;
+        d = (d != 0) ? n_over_alpha / d : 0;
+        return a * pow(d, power);
+    }
+    case GF_OP_EXPGAUS: { // basic/ExpGausPdf.cu:6-23
+        double x = evt(ob[0]), mean = p[0], sigma = p[1], alpha = p[2];
+        double ret = 0.5 * alpha;
+        double exparg = ret * (2 * mean + alpha * sigma * sigma - 2 * x);
+        double erfarg = (mean + alpha * sigma * sigma - x) / (sigma * 1.4142135623);
+        ret *= exp(exparg);
+        ret *= erfc(erfarg);
+        return ret;
+    }
+    case GF_OP_NOVOSIBIRSK: { // basic/NovosibirskPdf.cu:6-38
+        double mean = p[0], sigma = p[1], tail = p[2], x = evt(ob[0]);
+        double qc;
+        if(fabs(tail) < 1.e-7) {
+            double t = (x - mean) / sigma;
+            qc = 0.5 * (t * t);
+        } else {
+            double qa = tail * sqrt(log(4.));
+            double qb = sinh(qa) / qa;
+            double qx = (x - mean) / sigma * qb;
+            double qy = 1. + tail * qx;
+            if(qy > 1.e-7) {
+                double l = log(qy) / tail;
+                qc = 0.5 * (l * l + tail * tail);
+            } else
+                qc = 15.0;
+        }
+        return exp(-qc);
+    }
+    case GF_OP_STEP: { // basic/StepPdf.cu:6-20
+        double x = evt(ob[0]);
+        bool above = x > p[0];
+        return ((int)c[0] == 1) == above ? 1.0 : 0.0;
+    }
+    case GF_OP_TRIGTHRESH_UPPER:
+    case GF_OP_TRIGTHRESH_LOWER:
+    case GF_OP_TRIGTHRESH2_UPPER:
+    case GF_OP_TRIGTHRESH2_LOWER: { // basic/TrigThresholdPdf.cu:6-75: 1 beyond half a period from the threshold, a sine edge before
+        const bool two = nd.op >= GF_OP_TRIGTHRESH2_UPPER, upper = nd.op == GF_OP_TRIGTHRESH_UPPER || nd.op == GF_OP_TRIGTHRESH2_UPPER;
+        double v = two ? p[3] - evt(ob[0]) - evt(ob[1]) : evt(ob[0]);
+        double distance = p[1] * (upper ? p[0] - v : v - p[0]);
+        double lin = p[2];
+        return distance > 0.5 ? 1.0 : (lin + (1 - lin) * sin(distance * 3.14159265));
+    }
+    case GF_OP_BERNSTEIN: { // basic/BernsteinPdf.cu:8-51: binomials by factorials as upstream (a / (b1 * b2) in doubles)
+        double x = evt(ob[0]), lowX = c[1], uppX = c[2];
+        int mindeg = (int)(unsigned int)c[3];
+        int maxDegree = (int)c[0] + mindeg;
+        double xn = (x - lowX) / (uppX - lowX), ret = 0;
+        auto fact = [](int n) { double f = 1; for(int k = 1; k <= n; ++k) f = k * f; return f; };
+        for(int i = 0; i < maxDegree - mindeg; i++) {
+            double val = p[i];
+            int n = maxDegree - 1;
+            double bin = i > n ? 0.0 : fact(n) / (fact(i) * fact(n - i));
+            val *= bin * pow(xn, (double)i) * pow(1 - xn, (double)(n - i));
+            val /= (uppX - lowX);
+            ret += val;
+        }
+        return ret;
+    }
+    case GF_OP_CORRGAUSS: { // basic/CorrGaussianPdf.cu:6-27: the y width grows with the x distance
+        double x = evt(ob[0]), y = evt(ob[1]);
+        double xd = (x - p[0]) / p[1];
+        double s2 = p[3] * (1.0 + p[4] * xd * xd);
+        double yd = (y - p[2]) * (s2 == 0.0 ? 0.0 : (1.0 / s2));
+        return exp(-0.5 * (xd * xd + yd * yd));
+    }
+    case GF_OP_BINTRANSFORM: { // basic/BinTransformPdf.cu:6-27: the global bin number of the event as a value
+        int ret = 0, previous = 1;
+        for(int i = 0; i < nd.nobs; ++i) {
+            int local = (int)floor((evt(ob[i]) - c[3 * i]) / c[3 * i + 1]);
+            ret += local * previous;
+            previous *= (int)c[3 * i + 2];
+        }
+        return (double)ret;
+    }
+    case GF_OP_LANDAU: return gf_landau(evt(ob[0]), p[0], p[1]);
     default: return 0.0;
     }
 }

@@ -65,6 +65,61 @@ class JohnsonSUPdf : public GooPdf { // basic/JohnsonSUPdf.h
     bool hasAnalyticIntegral() const override { return true; }
 };
 
+// ---- the remaining closed-form shapes of PDFs/basic ----
+class BWPdf : public GooPdf { // basic/BWPdf.h: non-relativistic Breit-Wigner
+  public:
+    BWPdf(std::string n, Observable _x, Variable m, Variable s);
+};
+class BifurGaussPdf : public GooPdf { // basic/BifurGaussPdf.h: Gaussian with different widths left and right of the mean
+  public:
+    BifurGaussPdf(std::string n, Observable _x, Variable m, Variable sL, Variable sR);
+    fptype integrate(fptype lo, fptype hi) const override; // upstream defines it and leaves hasAnalyticIntegral false
+};
+class CrystalBallPdf : public GooPdf { // basic/CrystalBallPdf.h: Gaussian core with a power-law tail
+  public:
+    CrystalBallPdf(std::string n, Observable _x, Variable m, Variable s, Variable a);
+    CrystalBallPdf(std::string n, Observable _x, Variable m, Variable s, Variable a, Variable power);
+    fptype integrate(fptype lo, fptype hi) const override;
+};
+class ExpGausPdf : public GooPdf { // basic/ExpGausPdf.h: exponential convolved with a Gaussian
+  public:
+    ExpGausPdf(std::string n, Observable _x, Variable m, Variable s, Variable t);
+};
+class NovosibirskPdf : public GooPdf { // basic/NovosibirskPdf.h
+  public:
+    NovosibirskPdf(std::string n, Observable _x, Variable m, Variable s, Variable t);
+};
+class StepPdf : public GooPdf { // basic/StepPdf.h: 0 / 1 around x0
+  public:
+    StepPdf(std::string n, Observable _x, Variable x0, int Up = 1);
+    fptype integrate(fptype lo, fptype hi) const override;
+    bool hasAnalyticIntegral() const override { return true; }
+};
+class TrigThresholdPdf : public GooPdf { // basic/TrigThresholdPdf.h: sine-shaped efficiency edge
+  public:
+    TrigThresholdPdf(std::string n, Observable _x, Variable thresh, Variable trigConst, Variable linConst, bool upper = true);
+    TrigThresholdPdf(std::string n, Observable _x, Observable _y, Variable thresh, Variable trigConst, Variable linConst, Variable massConstant,
+                     bool upper);
+};
+class BernsteinPdf : public GooPdf { // basic/BernsteinPdf.h: Bernstein polynomial on the observable's range
+  public:
+    BernsteinPdf(std::string n, Observable vars, std::vector<Variable> coeffs, unsigned int mindeg = 0);
+    bool hasAnalyticIntegral() const override { return false; }
+};
+class CorrGaussianPdf : public GooPdf { // basic/CorrGaussianPdf.h: 2-D Gaussian whose y width grows with the x distance
+  public:
+    CorrGaussianPdf(std::string n, Observable _x, Observable _y, Variable mean1, Variable sigma1, Variable mean2, Variable sigma2,
+                    Variable correlation);
+};
+class BinTransformPdf : public GooPdf { // basic/BinTransformPdf.h: N-D coordinates -> one global bin number
+  public:
+    BinTransformPdf(std::string n, std::vector<Observable> obses, std::vector<fptype> limits, std::vector<fptype> binSizes, std::vector<int> numBins);
+};
+class LandauPdf : public GooPdf { // basic/LandauPdf.h
+  public:
+    LandauPdf(std::string n, Observable _x, Variable mpv, Variable sigma);
+};
+
 class CombinePdf : public GooPdf { // PDFs/CombinePdf.h
   public:
     using GooPdf::GooPdf;

@@ -169,6 +169,107 @@ JohnsonSUPdf::JohnsonSUPdf(std::string n, Observable _x, Variable mean, Variable
     registerFunction("ptr_to_JohnsonSU", GF_OP_JOHNSONSU);
 }
 
+// ---- the remaining closed-form shapes of PDFs/basic ---------------------------------------------------------------
+BWPdf::BWPdf(std::string n, Observable _x, Variable mean, Variable width)
+    : GooPdf("BWPdf", n, _x, mean, width) { // BWPdf.cu:22-27
+    registerFunction("ptr_to_BW", GF_OP_BW);
+}
+BifurGaussPdf::BifurGaussPdf(std::string n, Observable _x, Variable mean, Variable sigmaL, Variable sigmaR)
+    : GooPdf("BifurGaussPdf", n, _x, mean, sigmaL, sigmaR) { // BifurGaussPdf.cu:26-31
+    registerFunction("ptr_to_BifurGauss", GF_OP_BIFURGAUSS);
+}
+fptype BifurGaussPdf::integrate(fptype, fptype) const { // BifurGaussPdf.cu:35-45: half of each side's Gaussian normalisation
+    fptype sL = par(1), sR = par(2);
+    return .5 * (1. / (sqrt(2 * M_PI) * sL)) + .5 * (1. / (sqrt(2 * M_PI) * sR));
+}
+CrystalBallPdf::CrystalBallPdf(std::string n, Observable _x, Variable mean, Variable sigma, Variable alpha)
+    : CrystalBallPdf(n, _x, mean, sigma, alpha, Variable(n + "_n", 2)) {} // CrystalBallPdf.cu:39-40
+CrystalBallPdf::CrystalBallPdf(std::string n, Observable _x, Variable mean, Variable sigma, Variable alpha, Variable power)
+    : GooPdf("CrystalBallPdf", n, _x, mean, sigma, alpha, power) {
+    registerFunction("ptr_to_CrystalBall", GF_OP_CRYSTALBALL);
+}
+// CrystalBallPdf.cu:50-110 (RooFit's analytic integral): the Gaussian part by erf, the tail by its power-law (or log) primitive
+fptype CrystalBallPdf::integrate(fptype lo, fptype hi) const {
+    const fptype sqrtPiOver2 = 1.2533141373, sqrt2 = 1.4142135624;
+    const fptype mean = par(0), sigma = par(1), alpha = par(2), power = par(3);
+    const bool useLog = fabs(power - 1.0) < 1.0e-05;
+    fptype tmin = (lo - mean) / sigma, tmax = (hi - mean) / sigma;
+    if(alpha < 0) {
+        const fptype t = tmin;
+        tmin = -tmax;
+        tmax = -t;
+    }
+    const fptype absAlpha = fabs(alpha);
+    auto gauss = [&](fptype from, fptype to) { return sigma * sqrtPiOver2 * (erf(to / sqrt2) - erf(from / sqrt2)); };
+    if(tmin >= -absAlpha) return gauss(tmin, tmax);
+    const fptype a = pow(power / absAlpha, power) * exp(-0.5 * absAlpha * absAlpha), b = power / absAlpha - absAlpha;
+    auto tail = [&](fptype to_arg) { // primitive between tmin and the point where (b - t) = to_arg
+        if(useLog) return a * sigma * (log(b - tmin) - log(to_arg));
+        return a * sigma / (1.0 - power) * (1.0 / (pow(b - tmin, power - 1.0)) - 1.0 / (pow(to_arg, power - 1.0)));
+    };
+    if(tmax <= -absAlpha) return tail(b - tmax);
+    return tail(power / absAlpha) + gauss(-absAlpha, tmax);
+}
+ExpGausPdf::ExpGausPdf(std::string n, Observable _x, Variable mean, Variable sigma, Variable tau)
+    : GooPdf("ExpGausPdf", n, _x, mean, sigma, tau) { // ExpGausPdf.cu:27-32
+    registerFunction("ptr_to_ExpGaus", GF_OP_EXPGAUS);
+}
+NovosibirskPdf::NovosibirskPdf(std::string n, Observable _x, Variable mean, Variable sigma, Variable tail)
+    : GooPdf("NovosibirskPdf", n, _x, mean, sigma, tail) { // NovosibirskPdf.cu:42-47
+    registerFunction("ptr_to_Novosibirsk", GF_OP_NOVOSIBIRSK);
+}
+StepPdf::StepPdf(std::string n, Observable _x, Variable x0, int Up)
+    : GooPdf("StepPdf", n, _x, x0) { // StepPdf.cu:25-36
+    registerConstant(Up);
+    registerFunction("ptr_to_Step", GF_OP_STEP);
+}
+fptype StepPdf::integrate(fptype lo, fptype hi) const { // StepPdf.cu:38-47
+    fptype x0 = par(0);
+    return (int)constantsList[0] == 1 ? hi - x0 : x0 - lo;
+}
+TrigThresholdPdf::TrigThresholdPdf(std::string n, Observable _x, Variable thresh, Variable trigConst, Variable linConst, bool upper)
+    : GooPdf("TrigThresholdPdf", n, _x, thresh, trigConst, linConst) { // TrigThresholdPdf.cu:84-94
+    registerFunction(upper ? "ptr_to_TrigThresholdUpper" : "ptr_to_TrigThresholdLower", upper ? GF_OP_TRIGTHRESH_UPPER : GF_OP_TRIGTHRESH_LOWER);
+}
+TrigThresholdPdf::TrigThresholdPdf(std::string n, Observable _x, Observable _y, Variable thresh, Variable trigConst, Variable linConst,
+                                   Variable massConstant, bool upper)
+    : GooPdf("TrigThresholdPdf", n, _x, _y, thresh, trigConst, linConst, massConstant) { // TrigThresholdPdf.cu:96-113
+    registerFunction(upper ? "ptr_to_VerySpecialEpisodeTrigThresholdUpper" : "ptr_to_VerySpecialEpisodeTrigThresholdLower",
+                     upper ? GF_OP_TRIGTHRESH2_UPPER : GF_OP_TRIGTHRESH2_LOWER);
+}
+BernsteinPdf::BernsteinPdf(std::string n, Observable obs, std::vector<Variable> coeffs, unsigned int mindeg)
+    : GooPdf("BernsteinPdf", n, obs) { // BernsteinPdf.cu:55-72
+    registerConstant(int(coeffs.size()));
+    registerConstant(obs.getLowerLimit());
+    registerConstant(obs.getUpperLimit());
+    registerConstant(mindeg);
+    for(auto &c : coeffs) registerParameter(c);
+    registerFunction("ptr_to_BernsteinPdf", GF_OP_BERNSTEIN);
+}
+CorrGaussianPdf::CorrGaussianPdf(std::string n, Observable _x, Observable _y, Variable mean1, Variable sigma1, Variable mean2, Variable sigma2,
+                                 Variable correlation)
+    : GooPdf("CorrGaussianPdf", n, _x, _y, mean1, sigma1, mean2, sigma2, correlation) { // CorrGaussianPdf.cu:31-44
+    registerFunction("ptr_to_CorrGaussian", GF_OP_CORRGAUSS);
+}
+BinTransformPdf::BinTransformPdf(std::string n, std::vector<Observable> obses, std::vector<fptype> limits, std::vector<fptype> binSizes,
+                                 std::vector<int> numBins)
+    : GooPdf("BinTransformPdf", n) { // BinTransformPdf.cu:31-51
+    if(limits.size() < obses.size() || binSizes.size() < obses.size() || numBins.size() < obses.size())
+        throw GeneralError("BinTransformPdf {}: one lower limit, bin size and bin count per observable", n);
+    for(const auto &o : obses) registerObservable(o);
+    observablesList = getObservables();
+    for(size_t i = 0; i < obses.size(); ++i) {
+        registerConstant(limits[i]);
+        registerConstant(binSizes[i]);
+        registerConstant(numBins[i]);
+    }
+    registerFunction("ptr_to_BinTransform", GF_OP_BINTRANSFORM);
+}
+LandauPdf::LandauPdf(std::string n, Observable _x, Variable mpv, Variable sigma)
+    : GooPdf("LandauPdf", n, _x, mpv, sigma) { // LandauPdf.cu:88-93
+    registerFunction("ptr_to_Landau", GF_OP_LANDAU);
+}
+
 // ---- AddPdf (combine/AddPdf.cu:85-204) --------------------------------------------------------------------
 AddPdf::AddPdf(std::string n, std::vector<Variable> weights, std::vector<PdfBase *> comps)
     : CombinePdf("AddPdf", n)

@@ -286,6 +286,31 @@ PYBIND11_MODULE(_goofit, m) {
         .def(py::init<std::string, Observable, Variable, Variable, Variable, Variable>(), "name"_a, "x"_a, "m"_a, "s"_a, "d"_a, "e"_a);
     py::class_<JohnsonSUPdf, GooPdf>(m, "JohnsonSUPdf")
         .def(py::init<std::string, Observable, Variable, Variable, Variable, Variable>(), "name"_a, "x"_a, "m"_a, "s"_a, "g"_a, "d"_a);
+    py::class_<BWPdf, GooPdf>(m, "BWPdf").def(py::init<std::string, Observable, Variable, Variable>(), "name"_a, "x"_a, "m"_a, "s"_a);
+    py::class_<BifurGaussPdf, GooPdf>(m, "BifurGaussPdf")
+        .def(py::init<std::string, Observable, Variable, Variable, Variable>(), "name"_a, "x"_a, "m"_a, "sL"_a, "sR"_a);
+    py::class_<CrystalBallPdf, GooPdf>(m, "CrystalBallPdf")
+        .def(py::init<std::string, Observable, Variable, Variable, Variable>(), "name"_a, "x"_a, "m"_a, "s"_a, "a"_a)
+        .def(py::init<std::string, Observable, Variable, Variable, Variable, Variable>(), "name"_a, "x"_a, "m"_a, "s"_a, "a"_a, "power"_a);
+    py::class_<ExpGausPdf, GooPdf>(m, "ExpGausPdf")
+        .def(py::init<std::string, Observable, Variable, Variable, Variable>(), "name"_a, "x"_a, "m"_a, "s"_a, "t"_a);
+    py::class_<NovosibirskPdf, GooPdf>(m, "NovosibirskPdf")
+        .def(py::init<std::string, Observable, Variable, Variable, Variable>(), "name"_a, "x"_a, "m"_a, "s"_a, "t"_a);
+    py::class_<StepPdf, GooPdf>(m, "StepPdf").def(py::init<std::string, Observable, Variable, int>(), "name"_a, "x"_a, "x0"_a, "Up"_a = 1);
+    py::class_<TrigThresholdPdf, GooPdf>(m, "TrigThresholdPdf")
+        .def(py::init<std::string, Observable, Variable, Variable, Variable, bool>(), "name"_a, "x"_a, "thresh"_a, "trigConst"_a, "linConst"_a,
+             "upper"_a = true)
+        .def(py::init<std::string, Observable, Observable, Variable, Variable, Variable, Variable, bool>(), "name"_a, "x"_a, "y"_a, "thresh"_a,
+             "trigConst"_a, "linConst"_a, "massConstant"_a, "upper"_a);
+    py::class_<BernsteinPdf, GooPdf>(m, "BernsteinPdf")
+        .def(py::init<std::string, Observable, std::vector<Variable>, unsigned int>(), "name"_a, "x"_a, "coeffs"_a, "mindeg"_a = 0);
+    py::class_<CorrGaussianPdf, GooPdf>(m, "CorrGaussianPdf")
+        .def(py::init<std::string, Observable, Observable, Variable, Variable, Variable, Variable, Variable>(), "name"_a, "x"_a, "y"_a, "mean1"_a,
+             "sigma1"_a, "mean2"_a, "sigma2"_a, "correlation"_a);
+    py::class_<BinTransformPdf, GooPdf>(m, "BinTransformPdf")
+        .def(py::init<std::string, std::vector<Observable>, std::vector<fptype>, std::vector<fptype>, std::vector<int>>(), "name"_a, "obses"_a,
+             "limits"_a, "binSizes"_a, "numBins"_a);
+    py::class_<LandauPdf, GooPdf>(m, "LandauPdf").def(py::init<std::string, Observable, Variable, Variable>(), "name"_a, "x"_a, "mpv"_a, "sigma"_a);
     py::class_<CombinePdf, GooPdf>(m, "CombinePdf");
     py::class_<AddPdf, CombinePdf>(m, "AddPdf")
         .def(py::init<std::string, std::vector<Variable>, std::vector<PdfBase *>>(), "name"_a, "weights"_a, "comps"_a, py::keep_alive<1, 4>())

@@ -65,6 +65,20 @@ enum gf_op {
     GF_OP_JOHNSONSU,        /* JohnsonSUPdf.cu:8 */
     GF_OP_CONSTANT,         /* a polynomial with only its x^0 term (PolynomialPdf.cu:8-25 with one weight and lowest degree 0,
                                :47-118 with maxDegree 0): the last parameter of the record; no observable is read */
+    GF_OP_BW,               /* BWPdf.cu:6         params: mean, gamma */
+    GF_OP_BIFURGAUSS,       /* BifurGaussPdf.cu:6 params: mean, sigmaLeft, sigmaRight */
+    GF_OP_CRYSTALBALL,      /* CrystalBallPdf.cu:6 params: mean, sigma, alpha, power */
+    GF_OP_EXPGAUS,          /* ExpGausPdf.cu:6    params: mean, sigma, alpha */
+    GF_OP_NOVOSIBIRSK,      /* NovosibirskPdf.cu:6 params: mean, sigma, tail */
+    GF_OP_STEP,             /* StepPdf.cu:6       params: x0; consts: Up */
+    GF_OP_TRIGTHRESH_UPPER, /* TrigThresholdPdf.cu:13 params: thresh, trigConst, linConst */
+    GF_OP_TRIGTHRESH_LOWER, /* TrigThresholdPdf.cu:28 */
+    GF_OP_TRIGTHRESH2_UPPER,/* TrigThresholdPdf.cu:43 two observables; params: thresh, trigConst, linConst, massConstant */
+    GF_OP_TRIGTHRESH2_LOWER,/* TrigThresholdPdf.cu:61 */
+    GF_OP_BERNSTEIN,        /* BernsteinPdf.cu:26 params: coefficients; consts: n, lowX, uppX, mindeg */
+    GF_OP_CORRGAUSS,        /* CorrGaussianPdf.cu:6 two observables; params: mean1, sigma1, mean2, sigma2, corr */
+    GF_OP_BINTRANSFORM,     /* BinTransformPdf.cu:6 consts per observable: lower limit, bin size, number of bins */
+    GF_OP_LANDAU,           /* LandauPdf.cu:25    params: mpv, sigma */
     GF_OP_ADD = 32,         /* AddPdf.cu:16  ints: child norm slots */
     GF_OP_ADD_EXT,          /* AddPdf.cu:53 */
     GF_OP_PROD,             /* ProdPdf.cu:9 */

@@ -23,6 +23,17 @@
 #include <goofit/PDFs/combine/ConvolutionPdf.h>
 #include <goofit/PDFs/combine/EventWeightedAddPdf.h>
 #include <goofit/PDFs/combine/CompositePdf.h>
+#include <goofit/PDFs/basic/BWPdf.h>
+#include <goofit/PDFs/basic/BifurGaussPdf.h>
+#include <goofit/PDFs/basic/CrystalBallPdf.h>
+#include <goofit/PDFs/basic/ExpGausPdf.h>
+#include <goofit/PDFs/basic/NovosibirskPdf.h>
+#include <goofit/PDFs/basic/StepPdf.h>
+#include <goofit/PDFs/basic/TrigThresholdPdf.h>
+#include <goofit/PDFs/basic/BernsteinPdf.h>
+#include <goofit/PDFs/basic/CorrGaussianPdf.h>
+#include <goofit/PDFs/basic/BinTransformPdf.h>
+#include <goofit/PDFs/basic/LandauPdf.h>
 #include <goofit/PDFs/combine/MappedPdf.h>
 #include <goofit/PDFs/combine/ProdPdf.h>
 #include <goofit/PDFs/physics/Amp3Body.h>
@@ -1135,6 +1146,79 @@ static void case_combine2() {
     }
 }
 
+// ---- the remaining closed-form shapes of PDFs/basic: BW, BifurGauss, CrystalBall (both tails), ExpGaus, Novosibirsk (with and
+// without tail), Step (both directions), TrigThreshold (four forms), Bernstein, CorrGaussian, Landau (every range), BinTransform
+static void case_basic2() {
+    Observable x{"x", -4, 6};
+    UnbinnedDataSet d{x};
+    fill_1d(d, x, 900, 21, 2);
+    save_npy("basic2.x", column(d, x));
+    Variable m{"b2m", 0.8, 0.1, -4, 6}, w{"b2w", 1.3, 0.1, 0.1, 5};
+    { BWPdf p{"bw", x, m, w}; dump_pdf("bw", p, d, true, &x); }
+    Variable sl{"b2sl", 0.9, 0.1, 0.1, 5}, sr{"b2sr", 1.7, 0.1, 0.1, 5};
+    { BifurGaussPdf p{"bifur", x, m, sl, sr}; dump_pdf("bifur", p, d, true, &x); }
+    Variable ap{"b2ap", 1.1, 0.1, 0.1, 5}, an{"b2an", -0.9, 0.1, -5, -0.1}, pw{"b2pw", 2.5, 0.1, 0.5, 10};
+    { CrystalBallPdf p{"cbpos", x, m, w, ap, pw}; dump_pdf("cbpos", p, d, true, &x); }
+    { CrystalBallPdf p{"cbneg", x, m, w, an}; dump_pdf("cbneg", p, d, true, &x); }
+    Variable tau{"b2tau", 0.7, 0.1, 0.05, 5};
+    { ExpGausPdf p{"expgaus", x, m, sl, tau}; dump_pdf("expgaus", p, d, true, &x); }
+    Variable tail{"b2tail", 0.35, 0.05, -2, 2}, notail{"b2notail", 0.0};
+    { NovosibirskPdf p{"novo", x, m, w, tail}; dump_pdf("novo", p, d, true, &x); }
+    { NovosibirskPdf p{"novo0", x, m, w, notail}; dump_pdf("novo0", p, d, true, &x); }
+    Variable x0{"b2x0", 0.4, 0.1, -4, 6};
+    { // a bare step is 0 for half of the events: as a factor of a product with a Gaussian, and summed with one
+        GaussianPdf g{"b2g", x, m, sr};
+        Variable f{"b2f", 0.3, 0.1, 0, 1};
+        StepPdf up{"stepup", x, x0, 1}, dn{"stepdn", x, x0, 0};
+        put("stepup.integral", up.integrate(-4, 6));
+        put("stepdn.integral", dn.integrate(-4, 6));
+        AddPdf a1{"stepup_add", f, &up, &g}, a2{"stepdn_add", f, &dn, &g};
+        dump_pdf("stepup_add", a1, d, true, &x);
+        dump_pdf("stepdn_add", a2, d, true, &x);
+    }
+    Variable th{"b2th", 1.0, 0.1, -4, 6}, tc{"b2tc", 0.12, 0.01, 0.01, 2}, lc{"b2lc", 0.6, 0.01, 0, 1};
+    { TrigThresholdPdf p{"trigup", x, th, tc, lc, true}; dump_pdf("trigup", p, d, true, &x); }
+    { TrigThresholdPdf p{"trigdn", x, th, tc, lc, false}; dump_pdf("trigdn", p, d, true, &x); }
+    std::vector<Variable> bc{Variable{"bc0", 1.0, 0.1, 0, 5}, Variable{"bc1", 0.3, 0.1, 0, 5}, Variable{"bc2", 1.6, 0.1, 0, 5}, Variable{"bc3", 0.7, 0.1, 0, 5}};
+    { BernsteinPdf p{"bern", x, bc}; dump_pdf("bern", p, d, true, &x); }
+    { BernsteinPdf p{"bern1", x, bc, 1}; dump_pdf("bern1", p, d, true, &x); }
+    { // Landau: narrow and wide, so that the events reach every range of (x - mpv) / sigma the approximation distinguishes
+        Variable mpv{"b2mpv", -0.5, 0.1, -4, 6}, s1{"b2ls1", 0.02, 0.01, 0.001, 5}, s2{"b2ls2", 0.6, 0.1, 0.001, 5};
+        LandauPdf p1{"landau_narrow", x, mpv, s1};
+        dump_pdf("landau_narrow", p1, d, true, &x);
+        LandauPdf p2{"landau_wide", x, mpv, s2};
+        dump_pdf("landau_wide", p2, d, true, &x);
+    }
+    { // two observables: CorrGaussian, the two-observable threshold forms, and the bin number as the mapping function of a MappedPdf
+        Observable y{"y", -3, 3};
+        y.setNumBins(60);
+        x.setNumBins(80);
+        UnbinnedDataSet d2({x, y});
+        std::mt19937_64 gen(77);
+        std::normal_distribution<double> gy(0.2, 1.1);
+        for(size_t i = 0; i < d.getNumEvents();) {
+            double v = gy(gen);
+            if(v <= -3 || v >= 3) continue;
+            x.setValue(d.getValue(x, i)); y.setValue(v); d2.addEvent(); ++i;
+        }
+        save_npy("basic2.y", column(d2, y));
+        Variable m2{"b2m2", 0.1, 0.1, -3, 3}, s2{"b2s2", 0.8, 0.1, 0.1, 5}, corr{"b2corr", 0.25, 0.05, -1, 1};
+        CorrGaussianPdf cg{"corrgauss", x, y, m, w, m2, s2, corr};
+        dump_pdf("corrgauss", cg, d2, false, nullptr);
+        Variable mc{"b2mc", 3.0, 0.1, 0, 10};
+        TrigThresholdPdf t2u{"trig2up", x, y, th, tc, lc, mc, true}, t2d{"trig2dn", x, y, th, tc, lc, mc, false};
+        dump_pdf("trig2up", t2u, d2, false, nullptr);
+        dump_pdf("trig2dn", t2d, d2, false, nullptr);
+        BinTransformPdf bt{"bintr", {x, y}, {-4, -3}, {5, 3}, {2, 2}}; // 2 x 2 bins -> 0..3
+        GaussianPdf g0{"bt0", x, m, sl}, g1{"bt1", x, m, sr}, g2{"bt2", y, m2, s2};
+        ExpPdf g3{"bt3", y, corr};
+        std::vector<GooPdf *> t{&g0, &g1, &g2, &g3};
+        MappedPdf mp{"bintr_mapped", &bt, t};
+        dump_pdf("bintr_mapped", mp, d2, false, nullptr);
+        x.setNumBins(100);
+    }
+}
+
 // ---- CompositePdf: f(x) = h(g(x)), core g = 0.5 + 0.8 x, shell h = Gaussian; a second one with a two-observable core (combine/CompositePdf.cu)
 static void case_composite() {
     Observable x{"x", -5, 5}, y{"y", -2, 2};
@@ -1826,6 +1910,7 @@ int main(int argc, char **argv) {
             if(only == "all" || only == "td3") case_td3();
             if(only == "all" || only == "combine2") case_combine2();
             if(only == "all" || only == "composite") case_composite();
+            if(only == "all" || only == "basic2") case_basic2();
             if(only == "all" || only == "dalitzfit") case_dalitz_fit();
             if(only == "all" || only == "dp4") case_dp4();
             if(only == "all" || only == "dp4fit") case_dp4_fit();

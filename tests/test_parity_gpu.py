@@ -259,6 +259,61 @@ def test_event_weighted_add_and_mapped(golden):
     assert moved[S == 1].all() and not moved[S != 1].any()
 
 
+def test_basic2_remaining_closed_form_shapes(golden):
+    """The closed-form shapes of PDFs/basic beyond the five configured fits: BW, BifurGauss, CrystalBall (both tails), ExpGaus,
+    Novosibirsk (with and without tail), Step (both directions, inside an AddPdf), TrigThreshold (all four forms), Bernstein,
+    CorrGaussian, Landau (narrow and wide: every range of the approximation), BinTransform as the mapping function of a MappedPdf
+    (oracle/ref_driver.cpp case_basic2)."""
+    V = gf.Variable
+    x = gf.Observable("x", -4, 6)
+    X = golden.arr("basic2.x")
+    d = dataset_from_columns([x], [X])
+    m, w = V("b2m", 0.8, 0.1, -4, 6), V("b2w", 1.3, 0.1, 0.1, 5)
+    sl, sr = V("b2sl", 0.9, 0.1, 0.1, 5), V("b2sr", 1.7, 0.1, 0.1, 5)
+    ap, an, pw = V("b2ap", 1.1, 0.1, 0.1, 5), V("b2an", -0.9, 0.1, -5, -0.1), V("b2pw", 2.5, 0.1, 0.5, 10)
+    tau = V("b2tau", 0.7, 0.1, 0.05, 5)
+    tail, notail = V("b2tail", 0.35, 0.05, -2, 2), V("b2notail", 0.0)
+    check_pdf(golden, "bw", gf.BWPdf("bw", x, m, w), d, x)
+    check_pdf(golden, "bifur", gf.BifurGaussPdf("bifur", x, m, sl, sr), d, x)
+    check_pdf(golden, "cbpos", gf.CrystalBallPdf("cbpos", x, m, w, ap, pw), d, x)
+    check_pdf(golden, "cbneg", gf.CrystalBallPdf("cbneg", x, m, w, an), d, x)
+    check_pdf(golden, "expgaus", gf.ExpGausPdf("expgaus", x, m, sl, tau), d, x)
+    check_pdf(golden, "novo", gf.NovosibirskPdf("novo", x, m, w, tail), d, x)
+    check_pdf(golden, "novo0", gf.NovosibirskPdf("novo0", x, m, w, notail), d, x)
+    x0 = V("b2x0", 0.4, 0.1, -4, 6)
+    g = gf.GaussianPdf("b2g", x, m, sr)
+    f = V("b2f", 0.3, 0.1, 0, 1)
+    up, dn = gf.StepPdf("stepup", x, x0, 1), gf.StepPdf("stepdn", x, x0, 0)
+    assert up.integrate(-4, 6) == golden["stepup.integral"] and dn.integrate(-4, 6) == golden["stepdn.integral"]
+    check_pdf(golden, "stepup_add", gf.AddPdf("stepup_add", f, up, g), d, x)
+    check_pdf(golden, "stepdn_add", gf.AddPdf("stepdn_add", f, dn, g), d, x)
+    th, tc, lc = V("b2th", 1.0, 0.1, -4, 6), V("b2tc", 0.12, 0.01, 0.01, 2), V("b2lc", 0.6, 0.01, 0, 1)
+    check_pdf(golden, "trigup", gf.TrigThresholdPdf("trigup", x, th, tc, lc, True), d, x)
+    check_pdf(golden, "trigdn", gf.TrigThresholdPdf("trigdn", x, th, tc, lc, False), d, x)
+    bc = [V("bc0", 1.0, 0.1, 0, 5), V("bc1", 0.3, 0.1, 0, 5), V("bc2", 1.6, 0.1, 0, 5), V("bc3", 0.7, 0.1, 0, 5)]
+    check_pdf(golden, "bern", gf.BernsteinPdf("bern", x, bc), d, x)
+    check_pdf(golden, "bern1", gf.BernsteinPdf("bern1", x, bc, 1), d, x)
+    mpv = V("b2mpv", -0.5, 0.1, -4, 6)
+    # the narrow Landau is 0 for the events far below its peak (as upstream): their terms are left out of the sum on both sides
+    # (far below the peak the density is exp(-1/u) with u = exp(v + 1): a relative error eps of u becomes eps / u of the value, so the
+    # values around 1e-298 carry 1e-12 where libm's exp differs by an ulp; the NLL is still held to 1e-12)
+    check_pdf(golden, "landau_narrow", gf.LandauPdf("landau_narrow", x, mpv, V("b2ls1", 0.02, 0.01, 0.001, 5)), d, x, rtol_evt=1e-10)
+    check_pdf(golden, "landau_wide", gf.LandauPdf("landau_wide", x, mpv, V("b2ls2", 0.6, 0.1, 0.001, 5)), d, x)
+    y = gf.Observable("y", -3, 3)
+    y.setNumBins(60)
+    x.setNumBins(80)
+    d2 = dataset_from_columns([x, y], [X, golden.arr("basic2.y")])
+    m2, s2, corr = V("b2m2", 0.1, 0.1, -3, 3), V("b2s2", 0.8, 0.1, 0.1, 5), V("b2corr", 0.25, 0.05, -1, 1)
+    check_pdf(golden, "corrgauss", gf.CorrGaussianPdf("corrgauss", x, y, m, w, m2, s2, corr), d2)
+    mc = V("b2mc", 3.0, 0.1, 0, 10)
+    check_pdf(golden, "trig2up", gf.TrigThresholdPdf("trig2up", x, y, th, tc, lc, mc, True), d2)
+    check_pdf(golden, "trig2dn", gf.TrigThresholdPdf("trig2dn", x, y, th, tc, lc, mc, False), d2)
+    bt = gf.BinTransformPdf("bintr", [x, y], [-4, -3], [5, 3], [2, 2])
+    comps = [gf.GaussianPdf("bt0", x, m, sl), gf.GaussianPdf("bt1", x, m, sr), gf.GaussianPdf("bt2", y, m2, s2), gf.ExpPdf("bt3", y, corr)]
+    check_pdf(golden, "bintr_mapped", gf.MappedPdf("bintr_mapped", bt, comps), d2)
+    x.setNumBins(100)
+
+
 def test_composite_pdf(golden):
     """combine/CompositePdf.cu: f = h(g(event)); the shell h reads the core's value where the composite's first observable sits in
     the event, neither is normalised inside, the composite is (grid integral). Alone, inside an AddPdf, and with a core of two
