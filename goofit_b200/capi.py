@@ -13,7 +13,7 @@ SYMBOLS = [
     "gf_eval_sum_async", "gf_partial_device_ptr", "gf_stream", "gf_sync", "gf_eval_events", "gf_integrate_grid",
     "gf_conv_setup", "gf_conv_fill", "gf_conv_sizes", "gf_conv_get_workspace", "gf_amp3_alloc", "gf_amp3_cache_waves",
     "gf_amp3_integrals", "gf_amp3_get_wave", "gf_amp3_wave_gram", "gf_amp4_alloc", "gf_amp4_set_mc", "gf_amp4_cache", "gf_amp4_norm",
-    "gf_amp4_norm_async", "gf_amp4_gram", "gf_amp4_get_amp", "gf_last_kernel_ms", "gf_last_kernel_name", "gf_set_option", "gf_amp4_cache_gram", "gf_amp4_cache_data", "gf_genbod", "gf_genbod_static", "gf_launch_count", "gf_comm_unique_id", "gf_comm_init",
+    "gf_amp4_norm_async", "gf_amp4_gram", "gf_amp4_get_amp", "gf_last_kernel_ms", "gf_last_kernel_name", "gf_set_option", "gf_amp4_cache_gram", "gf_amp4_cache_data", "gf_genbod", "gf_genbod_static", "gf_table_set", "gf_launch_count", "gf_comm_unique_id", "gf_comm_init",
     "gf_comm_destroy", "gf_allgather_events", "gf_comm_attached", "gf_comm_path", "gf_profile_begin", "gf_profile_end", "gf_timer_start", "gf_timer_stop", "gf_fp64_peak", "gf_set_params_async",
 ]
 

@@ -182,3 +182,29 @@ extern "C" int gf_conv_sizes(gf_ctx *c, int node, int *n_model, int *n_resol, in
     if(n_table) *n_table = s->nk;
     return 0;
 }
+
+// ---- plain tables (SmoothHistogramPdf) ----------------------------------------------------------------------------------------
+// One device array per GF_OP_HISTOGRAM record, reachable through the record's aux slot; kept in the same list as the convolution
+// workspaces so that gf_reset_aux / gf_destroy release it.
+extern "C" int gf_table_set(gf_ctx *c, int node, const double *values, size_t n) {
+    if(!c || !values || n == 0) return gf_fail("gf_table_set: null argument or empty table");
+    if(node < 0 || node >= (int)c->h_nodes.size() || c->h_nodes[node].op != GF_OP_HISTOGRAM) return gf_fail("gf_table_set: node is not a histogram record");
+    const gf_node &nd = c->h_nodes[node];
+    if(nd.nint < 1) return gf_fail("gf_table_set: malformed histogram record");
+    const int slot = c->h_ints[nd.int_off];
+    if(slot < 0 || slot >= GF_MAX_AUX) return gf_fail("gf_table_set: bad aux slot");
+    cudaSetDevice(c->device);
+    gf_conv_state *s = find_conv(c, node, true);
+    s->slot = slot;
+    GF_CUDA(cudaStreamSynchronize(c->stream));
+    if(!s->d_table || s->nk != (int)n) {
+        cudaFree(s->d_table);
+        s->d_table = nullptr;
+        GF_CUDA(cudaMalloc(&s->d_table, sizeof(double) * n));
+        s->nk = (int)n;
+    }
+    GF_CUDA(cudaMemcpy(s->d_table, values, sizeof(double) * n, cudaMemcpyHostToDevice));
+    c->view.aux[slot] = s->d_table;
+    c->view.aux_ld[slot] = (long)n;
+    return 0;
+}

@@ -266,6 +266,21 @@ __device__ inline double gf_leaf(const gf_node &nd, const gf_sprog &P, const Evt
         return (double)ret;
     }
     case GF_OP_LANDAU: return gf_landau(evt(ob[0]), p[0], p[1]);
+    case GF_OP_HISTOGRAM: { // basic/SmoothHistogramPdf.cu:13-46: the content of the event's bin in the table attached by gf_table_set
+        const int slot = P.ints[nd.int_off];
+        const double *table = static_cast<const double *>(P.aux[slot]);
+        const long n = P.aux_ld[slot];
+        if(!table || n <= 0) return 0.0;
+        const int nv = (int)c[0];
+        long global = 0, previous = 1;
+        for(int i = 0; i < nv; ++i) {
+            double v = (evt(ob[i]) - c[3 * i + 4]) / c[3 * i + 5];
+            global += previous * (long)floor(v);
+            previous *= (long)c[3 * (i + 1)];
+        }
+        global = global < 0 ? 0 : (global >= n ? n - 1 : global); // upstream reads outside its table for an event outside the histogram
+        return __ldg(table + global);
+    }
     default: return 0.0;
     }
 }

@@ -115,6 +115,25 @@ class BinTransformPdf : public GooPdf { // basic/BinTransformPdf.h: N-D coordina
   public:
     BinTransformPdf(std::string n, std::vector<Observable> obses, std::vector<fptype> limits, std::vector<fptype> binSizes, std::vector<int> numBins);
 };
+/// basic/SmoothHistogramPdf.h: the content of the event's bin in a histogram, each bin averaged with its neighbours:
+/// (own + s sum(neighbours)) / (1 + s n_neighbours) for the smoothing parameter s. The smoothed table lives on the device.
+class SmoothHistogramPdf : public GooPdf {
+  public:
+    SmoothHistogramPdf(std::string n, BinnedDataSet *x, Variable smoothing);
+    fptype normalize() override;
+    bool hasAnalyticIntegral() const override { return false; }
+    void extractHistogram(std::vector<fptype> &host_hist) const { host_hist = base; }
+    void copyHistogramToDevice(std::vector<fptype> &host_histogram);
+    int emit(detail::ProgramBuilder &B) override;
+    void afterProgram() override;
+
+  private:
+    std::vector<fptype> smoothedTable(fptype smoothing) const;
+    std::vector<fptype> base;
+    std::vector<int> nbins;
+    fptype totalEvents = 0, uploadedFor = 0;
+    bool uploaded = false;
+};
 class LandauPdf : public GooPdf { // basic/LandauPdf.h
   public:
     LandauPdf(std::string n, Observable _x, Variable mpv, Variable sigma);

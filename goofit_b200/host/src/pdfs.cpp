@@ -265,6 +265,91 @@ BinTransformPdf::BinTransformPdf(std::string n, std::vector<Observable> obses, s
     }
     registerFunction("ptr_to_BinTransform", GF_OP_BINTRANSFORM);
 }
+// ---- SmoothHistogramPdf (basic/SmoothHistogramPdf.cu:107-216) --------------------------------------------------------------
+SmoothHistogramPdf::SmoothHistogramPdf(std::string n, BinnedDataSet *hist, Variable smoothing)
+    : GooPdf("SmoothHistogramPdf", n, smoothing) {
+    if(!hist) throw GeneralError("SmoothHistogramPdf {} needs a histogram", n);
+    registerConstant(hist->getObservables().size());
+    registerConstant(0); // upstream's index into its table of histograms; the table hangs off the record here
+    registerConstant(hist->numVariables());
+    for(const Observable &var : hist->getObservables()) {
+        registerObservable(var);
+        registerConstant(var.getNumBins());
+        registerConstant(var.getLowerLimit());
+        registerConstant(var.getBinSize());
+        nbins.push_back((int)var.getNumBins());
+    }
+    std::vector<fptype> h(hist->getNumBins());
+    for(size_t i = 0; i < h.size(); ++i) {
+        h[i] = hist->getBinContent(i);
+        totalEvents += h[i];
+    }
+    if(totalEvents > 0) copyHistogramToDevice(h);
+    registerFunction("ptr_to_EvalHistogram", GF_OP_HISTOGRAM);
+}
+void SmoothHistogramPdf::copyHistogramToDevice(std::vector<fptype> &host_histogram) {
+    size_t expected = 1;
+    for(int b : nbins) expected *= (size_t)b;
+    if(expected != host_histogram.size())
+        throw GeneralError("SmoothHistogramPdf {}: histogram has {} bins, expected {}", getName(), host_histogram.size(), expected);
+    base     = host_histogram;
+    uploaded = false;
+}
+int SmoothHistogramPdf::emit(detail::ProgramBuilder &B) {
+    int slot = B.allocAux();
+    return emitRecord(B, GF_OP_HISTOGRAM, 0, 1, {slot});
+}
+void SmoothHistogramPdf::afterProgram() { uploaded = false; } // a new program: the aux slot is empty again
+// the Smoother functor (SmoothHistogramPdf.cu:48-103): every bin with the up to 3^d - 1 neighbours that exist
+std::vector<fptype> SmoothHistogramPdf::smoothedTable(fptype smoothing) const {
+    const int nv = (int)nbins.size();
+    int others = 1;
+    for(int v = 0; v < nv; ++v) others *= 3;
+    std::vector<fptype> out(base.size());
+    for(size_t g = 0; g < base.size(); ++g) {
+        fptype central = base[g], total = 0;
+        int surrounding = 0;
+        for(int i = 0; i < others; ++i) {
+            long curr = (long)g, prev = 1, track = (long)g;
+            bool off = false;
+            int code = i;
+            for(int v = 0; v < nv; ++v) {
+                const int offset = code % 3 - 1;
+                code /= 3;
+                curr += offset * prev;
+                prev *= nbins[v];
+                const long mine = track % nbins[v];
+                track /= nbins[v];
+                if(mine + offset < 0 || mine + offset >= nbins[v]) off = true;
+            }
+            if(curr == (long)g || off) continue;
+            surrounding++;
+            total += base[curr];
+        }
+        central += total * smoothing;
+        central /= (1 + surrounding * smoothing);
+        out[g] = central;
+    }
+    return out;
+}
+fptype SmoothHistogramPdf::normalize() { // SmoothHistogramPdf.cu:190-214
+    if(base.empty()) throw GeneralError("SmoothHistogramPdf {}: no histogram (copyHistogramToDevice)", getName());
+    if(nodeIdx < 0) throw GeneralError("SmoothHistogramPdf {}: call setData() on the top-level PDF first", getName());
+    const fptype smoothing = par(0);
+    std::vector<fptype> table = smoothedTable(smoothing);
+    if(!uploaded || uploadedFor != smoothing) {
+        Engine &E = Engine::get();
+        E.sync();
+        Engine::check(gf_table_set(E.ctx(), nodeIdx, table.data(), table.size()), "gf_table_set");
+        uploaded    = true;
+        uploadedFor = smoothing;
+    }
+    fptype ret = 0;
+    for(fptype v : table) ret += v; // upstream: thrust::reduce over the device vector
+    for(size_t v = 0; v < observablesList.size(); ++v) ret *= constantsList[3 + 3 * v + 2];
+    setNormalization(1.0 / ret);
+    return ret;
+}
 LandauPdf::LandauPdf(std::string n, Observable _x, Variable mpv, Variable sigma)
     : GooPdf("LandauPdf", n, _x, mpv, sigma) { // LandauPdf.cu:88-93
     registerFunction("ptr_to_Landau", GF_OP_LANDAU);

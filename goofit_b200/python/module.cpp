@@ -310,6 +310,8 @@ PYBIND11_MODULE(_goofit, m) {
     py::class_<BinTransformPdf, GooPdf>(m, "BinTransformPdf")
         .def(py::init<std::string, std::vector<Observable>, std::vector<fptype>, std::vector<fptype>, std::vector<int>>(), "name"_a, "obses"_a,
              "limits"_a, "binSizes"_a, "numBins"_a);
+    py::class_<SmoothHistogramPdf, GooPdf>(m, "SmoothHistogramPdf")
+        .def(py::init<std::string, BinnedDataSet *, Variable>(), "name"_a, "hist"_a, "smoothing"_a, py::keep_alive<1, 3>());
     py::class_<LandauPdf, GooPdf>(m, "LandauPdf").def(py::init<std::string, Observable, Variable, Variable>(), "name"_a, "x"_a, "mpv"_a, "sigma"_a);
     py::class_<CombinePdf, GooPdf>(m, "CombinePdf");
     py::class_<AddPdf, CombinePdf>(m, "AddPdf")

@@ -79,6 +79,8 @@ enum gf_op {
     GF_OP_CORRGAUSS,        /* CorrGaussianPdf.cu:6 two observables; params: mean1, sigma1, mean2, sigma2, corr */
     GF_OP_BINTRANSFORM,     /* BinTransformPdf.cu:6 consts per observable: lower limit, bin size, number of bins */
     GF_OP_LANDAU,           /* LandauPdf.cu:25    params: mpv, sigma */
+    GF_OP_HISTOGRAM,        /* SmoothHistogramPdf.cu:13-46 ints: aux slot of the (smoothed) bin table, see gf_table_set;
+                               consts: nObs, histogram index, nVars, then (bins, lower limit, bin size) per observable */
     GF_OP_ADD = 32,         /* AddPdf.cu:16  ints: child norm slots */
     GF_OP_ADD_EXT,          /* AddPdf.cu:53 */
     GF_OP_PROD,             /* ProdPdf.cu:9 */
@@ -249,6 +251,9 @@ int gf_genbod(gf_ctx *, const double *masses, int nd, size_t n, uint64_t seed, u
 #define GF_GENBOD_STATIC_MAX_EVENTS 32768
 int gf_genbod_static(gf_ctx *, const double *masses, int nd, size_t n, uint64_t seed, uint64_t offset, double *particles, double *weights,
                      double *dim5);
+/* a table of n doubles attached to a GF_OP_HISTOGRAM record (its ints[0] names the aux slot): replaces the device vectors behind
+ * dev_smoothed_histograms[] (SmoothHistogramPdf.cu:6-7,165-186). May be called again with new values (the smoothing moved). */
+int gf_table_set(gf_ctx *, int node, const double *values, size_t n);
 /* measured FP64 FMA peak of this GPU (DFMA micro-benchmark, TFLOP/s, 2 flops per FMA): the roofline denominator of
  * the FP64-bound cache kernels (k_amp3_waves, k_amp4_cache), which MEASURED_PEAKS.json does not carry */
 int gf_fp64_peak(gf_ctx *, double *tflops);

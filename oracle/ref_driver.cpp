@@ -34,6 +34,7 @@
 #include <goofit/PDFs/basic/CorrGaussianPdf.h>
 #include <goofit/PDFs/basic/BinTransformPdf.h>
 #include <goofit/PDFs/basic/LandauPdf.h>
+#include <goofit/PDFs/basic/SmoothHistogramPdf.h>
 #include <goofit/PDFs/combine/MappedPdf.h>
 #include <goofit/PDFs/combine/ProdPdf.h>
 #include <goofit/PDFs/physics/Amp3Body.h>
@@ -1219,6 +1220,43 @@ static void case_basic2() {
     }
 }
 
+// ---- SmoothHistogramPdf: a 1-D and a 2-D histogram, each bin averaged with its neighbours (basic/SmoothHistogramPdf.cu)
+static void case_smoothhist() {
+    Observable x{"x", -4, 6}, y{"y", -3, 3};
+    x.setNumBins(50);
+    y.setNumBins(12);
+    std::mt19937_64 gen(515);
+    std::normal_distribution<double> gx(0.9, 1.6), gy(-0.3, 1.2);
+    BinnedDataSet h1(x);
+    Observable x2{"x", -4, 6};
+    x2.setNumBins(20);
+    BinnedDataSet h2({x2, y});
+    std::vector<double> c1, c2;
+    for(int i = 0; i < 6000; i++) {
+        double vx = gx(gen), vy = gy(gen);
+        if(vx <= -4 || vx >= 6 || vy <= -3 || vy >= 3) continue;
+        x.setValue(vx); h1.addEvent();
+        x2.setValue(vx); y.setValue(vy); h2.addEvent();
+    }
+    for(size_t i = 0; i < h1.getNumBins(); i++) c1.push_back(h1.getBinContent(i));
+    for(size_t i = 0; i < h2.getNumBins(); i++) c2.push_back(h2.getBinContent(i));
+    save_npy("smoothhist.h1", c1); save_npy("smoothhist.h2", c2);
+    UnbinnedDataSet d{x}, d2({x2, y});
+    std::vector<double> X, Y;
+    while(X.size() < 700) {
+        double vx = gx(gen), vy = gy(gen);
+        if(vx <= -4 || vx >= 6 || vy <= -3 || vy >= 3) continue;
+        X.push_back(vx); Y.push_back(vy);
+        x.setValue(vx); d.addEvent();
+        x2.setValue(vx); y.setValue(vy); d2.addEvent();
+    }
+    save_npy("smoothhist.x", X); save_npy("smoothhist.y", Y);
+    Variable sm1{"sm1", 0.4, 0.05, 0, 2}, sm2{"sm2", 0.25, 0.05, 0, 2}, sm0{"sm0", 0.0};
+    { SmoothHistogramPdf p{"smooth1", &h1, sm1}; dump_pdf("smooth1", p, d, true, &x); put("smooth1.normalize", p.normalize()); }
+    { SmoothHistogramPdf p{"smooth0", &h1, sm0}; dump_pdf("smooth0", p, d, true, &x); }
+    { SmoothHistogramPdf p{"smooth2", &h2, sm2}; dump_pdf("smooth2", p, d2, false, nullptr); put("smooth2.normalize", p.normalize()); }
+}
+
 // ---- CompositePdf: f(x) = h(g(x)), core g = 0.5 + 0.8 x, shell h = Gaussian; a second one with a two-observable core (combine/CompositePdf.cu)
 static void case_composite() {
     Observable x{"x", -5, 5}, y{"y", -2, 2};
@@ -1911,6 +1949,7 @@ int main(int argc, char **argv) {
             if(only == "all" || only == "combine2") case_combine2();
             if(only == "all" || only == "composite") case_composite();
             if(only == "all" || only == "basic2") case_basic2();
+            if(only == "all" || only == "smoothhist") case_smoothhist();
             if(only == "all" || only == "dalitzfit") case_dalitz_fit();
             if(only == "all" || only == "dp4") case_dp4();
             if(only == "all" || only == "dp4fit") case_dp4_fit();

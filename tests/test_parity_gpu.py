@@ -314,6 +314,33 @@ def test_basic2_remaining_closed_form_shapes(golden):
     x.setNumBins(100)
 
 
+def test_smooth_histogram_pdf(golden):
+    """basic/SmoothHistogramPdf.cu: the bin content of a 1-D (50 bins) and a 2-D (20 x 12) histogram, each bin averaged with its
+    neighbours; the smoothed table is built by the host class and attached to the record with gf_table_set
+    (oracle/ref_driver.cpp case_smoothhist)."""
+    V = gf.Variable
+    x, y = gf.Observable("x", -4, 6), gf.Observable("y", -3, 3)
+    x.setNumBins(50)
+    y.setNumBins(12)
+    h1 = gf.BinnedDataSet(x)
+    for i, v in enumerate(golden.arr("smoothhist.h1")):
+        h1.setBinContent(i, v)
+    d = dataset_from_columns([x], [golden.arr("smoothhist.x")])
+    s1 = gf.SmoothHistogramPdf("smooth1", h1, V("sm1", 0.4, 0.05, 0, 2))
+    check_pdf(golden, "smooth1", s1, d, x)
+    assert rel(s1.normalize(), golden["smooth1.normalize"]) < RTOL_NLL
+    check_pdf(golden, "smooth0", gf.SmoothHistogramPdf("smooth0", h1, V("sm0", 0.0)), d, x)
+    x2 = gf.Observable("x", -4, 6)
+    x2.setNumBins(20)
+    h2 = gf.BinnedDataSet(x2, y)
+    for i, v in enumerate(golden.arr("smoothhist.h2")):
+        h2.setBinContent(i, v)
+    d2 = dataset_from_columns([x2, y], [golden.arr("smoothhist.x"), golden.arr("smoothhist.y")])
+    s2 = gf.SmoothHistogramPdf("smooth2", h2, V("sm2", 0.25, 0.05, 0, 2))
+    check_pdf(golden, "smooth2", s2, d2)
+    assert rel(s2.normalize(), golden["smooth2.normalize"]) < RTOL_NLL
+
+
 def test_composite_pdf(golden):
     """combine/CompositePdf.cu: f = h(g(event)); the shell h reads the core's value where the composite's first observable sits in
     the event, neither is normalised inside, the composite is (grid integral). Alone, inside an AddPdf, and with a core of two
