@@ -134,6 +134,10 @@ class SmoothHistogramPdf : public GooPdf {
     fptype totalEvents = 0, uploadedFor = 0;
     bool uploaded = false;
 };
+class VoigtianPdf : public GooPdf { // basic/VoigtianPdf.h: Breit-Wigner convolved with a Gaussian
+  public:
+    VoigtianPdf(std::string n, Observable _x, Variable m, Variable s, Variable w);
+};
 class LandauPdf : public GooPdf { // basic/LandauPdf.h
   public:
     LandauPdf(std::string n, Observable _x, Variable mpv, Variable sigma);

@@ -350,6 +350,10 @@ fptype SmoothHistogramPdf::normalize() { // SmoothHistogramPdf.cu:190-214
     setNormalization(1.0 / ret);
     return ret;
 }
+VoigtianPdf::VoigtianPdf(std::string n, Observable _x, Variable m, Variable s, Variable w)
+    : GooPdf("VoigtianPdf", n, _x, m, s, w) { // VoigtianPdf.cu:324-329
+    registerFunction("ptr_to_Voigtian", GF_OP_VOIGTIAN);
+}
 LandauPdf::LandauPdf(std::string n, Observable _x, Variable mpv, Variable sigma)
     : GooPdf("LandauPdf", n, _x, mpv, sigma) { // LandauPdf.cu:88-93
     registerFunction("ptr_to_Landau", GF_OP_LANDAU);

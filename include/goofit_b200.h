@@ -79,6 +79,8 @@ enum gf_op {
     GF_OP_CORRGAUSS,        /* CorrGaussianPdf.cu:6 two observables; params: mean1, sigma1, mean2, sigma2, corr */
     GF_OP_BINTRANSFORM,     /* BinTransformPdf.cu:6 consts per observable: lower limit, bin size, number of bins */
     GF_OP_LANDAU,           /* LandauPdf.cu:25    params: mpv, sigma */
+    GF_OP_VOIGTIAN,         /* VoigtianPdf.cu:285-320 params in constructor order (m, s, w); as upstream the device function takes the
+                               second as the Breit-Wigner width and the third as the Gaussian sigma */
     GF_OP_HISTOGRAM,        /* SmoothHistogramPdf.cu:13-46 ints: aux slot of the (smoothed) bin table, see gf_table_set;
                                consts: nObs, histogram index, nVars, then (bins, lower limit, bin size) per observable */
     GF_OP_ADD = 32,         /* AddPdf.cu:16  ints: child norm slots */

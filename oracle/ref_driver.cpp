@@ -34,6 +34,7 @@
 #include <goofit/PDFs/basic/CorrGaussianPdf.h>
 #include <goofit/PDFs/basic/BinTransformPdf.h>
 #include <goofit/PDFs/basic/LandauPdf.h>
+#include <goofit/PDFs/basic/VoigtianPdf.h>
 #include <goofit/PDFs/basic/SmoothHistogramPdf.h>
 #include <goofit/PDFs/combine/MappedPdf.h>
 #include <goofit/PDFs/combine/ProdPdf.h>
@@ -1257,6 +1258,27 @@ static void case_smoothhist() {
     { SmoothHistogramPdf p{"smooth2", &h2, sm2}; dump_pdf("smooth2", p, d2, false, nullptr); put("smooth2.normalize", p.normalize()); }
 }
 
+// ---- VoigtianPdf: wide, narrow (the h = 0.53 node grid near the real axis) and very narrow with events on the peak (the Pade form
+// for |z|^2 < 1e-7), and its two degenerate forms (basic/VoigtianPdf.cu). The constructor's (m, s, w) reach the device as (m, w, s).
+static void case_voigt() {
+    Observable x{"x", -4, 6};
+    UnbinnedDataSet d{x};
+    fill_1d(d, x, 800, 31, 2);
+    const double peak = 0.8;
+    for(double dx : {0.0, 1e-4, -1e-4, 2.5e-5}) { x.setValue(peak + dx); d.addEvent(); }
+    save_npy("voigt.x", column(d, x));
+    Variable m{"vm", peak, 0.1, -4, 6};
+    Variable a1{"va1", 0.9, 0.1, 0, 5}, b1{"vb1", 0.7, 0.1, 0, 5};
+    { VoigtianPdf p{"voigt_wide", x, m, a1, b1}; dump_pdf("voigt_wide", p, d, true, &x); }
+    Variable a2{"va2", 0.001, 0.0001, 0, 5}, b2{"vb2", 0.5, 0.1, 0, 5};
+    { VoigtianPdf p{"voigt_narrow", x, m, a2, b2}; dump_pdf("voigt_narrow", p, d, true, &x); }
+    Variable a3{"va3", 0.0002, 0.0001, 0, 5};
+    { VoigtianPdf p{"voigt_tiny", x, m, a3, b2}; dump_pdf("voigt_tiny", p, d, true, &x); }
+    Variable zero{"vzero", 0.0};
+    { VoigtianPdf p{"voigt_bw", x, m, a1, zero}; dump_pdf("voigt_bw", p, d, true, &x); }
+    { VoigtianPdf p{"voigt_gauss", x, m, zero, b1}; dump_pdf("voigt_gauss", p, d, true, &x); }
+}
+
 // ---- CompositePdf: f(x) = h(g(x)), core g = 0.5 + 0.8 x, shell h = Gaussian; a second one with a two-observable core (combine/CompositePdf.cu)
 static void case_composite() {
     Observable x{"x", -5, 5}, y{"y", -2, 2};
@@ -1950,6 +1972,7 @@ int main(int argc, char **argv) {
             if(only == "all" || only == "composite") case_composite();
             if(only == "all" || only == "basic2") case_basic2();
             if(only == "all" || only == "smoothhist") case_smoothhist();
+            if(only == "all" || only == "voigt") case_voigt();
             if(only == "all" || only == "dalitzfit") case_dalitz_fit();
             if(only == "all" || only == "dp4") case_dp4();
             if(only == "all" || only == "dp4fit") case_dp4_fit();

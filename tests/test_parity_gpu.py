@@ -341,6 +341,24 @@ def test_smooth_histogram_pdf(golden):
     assert rel(s2.normalize(), golden["smooth2.normalize"]) < RTOL_NLL
 
 
+def test_voigtian_pdf(golden):
+    """basic/VoigtianPdf.cu: Re w(z) by the Matta-Reichel series. Wide; narrow (events near the real axis, where the h = 0.53 node
+    grid takes over around half-integer Re z); very narrow with events on the peak (|z|^2 < 1e-7: the Pade form); and the two
+    degenerate forms. The constructor's (m, s, w) reach the device function as (m, width, sigma), as upstream
+    (oracle/ref_driver.cpp case_voigt)."""
+    V = gf.Variable
+    x = gf.Observable("x", -4, 6)
+    d = dataset_from_columns([x], [golden.arr("voigt.x")])
+    m = V("vm", 0.8, 0.1, -4, 6)
+    a1, b1 = V("va1", 0.9, 0.1, 0, 5), V("vb1", 0.7, 0.1, 0, 5)
+    a2, b2, a3, zero = V("va2", 0.001, 0.0001, 0, 5), V("vb2", 0.5, 0.1, 0, 5), V("va3", 0.0002, 0.0001, 0, 5), V("vzero", 0.0)
+    check_pdf(golden, "voigt_wide", gf.VoigtianPdf("voigt_wide", x, m, a1, b1), d, x)
+    check_pdf(golden, "voigt_narrow", gf.VoigtianPdf("voigt_narrow", x, m, a2, b2), d, x, rtol_evt=1e-11)
+    check_pdf(golden, "voigt_tiny", gf.VoigtianPdf("voigt_tiny", x, m, a3, b2), d, x, rtol_evt=1e-11)
+    check_pdf(golden, "voigt_bw", gf.VoigtianPdf("voigt_bw", x, m, a1, zero), d, x)
+    check_pdf(golden, "voigt_gauss", gf.VoigtianPdf("voigt_gauss", x, m, zero, b1), d, x)
+
+
 def test_composite_pdf(golden):
     """combine/CompositePdf.cu: f = h(g(event)); the shell h reads the core's value where the composite's first observable sits in
     the event, neither is normalised inside, the composite is (grid integral). Alone, inside an AddPdf, and with a core of two
