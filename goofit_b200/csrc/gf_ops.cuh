@@ -343,6 +343,15 @@ __device__ inline double gf_leaf(const gf_node &nd, const gf_sprog &P, const Evt
         cc /= s;
         return cc * 0.5641895835477563 * gf_faddeeva_re(cc * arg, 0.5 * cc * w);
     }
+    case GF_OP_VARBINTRANSFORM: { // utilities/VariableBinTransform1DPdf.cu:8-27: bin number of |x| among ascending limits
+        double v = fabs(evt(ob[0]));
+        int n = (int)c[0], ret = 0;
+        for(int i = 0; i < n; ++i) {
+            if(v < c[1 + i]) break;
+            ret++;
+        }
+        return (double)ret;
+    }
     case GF_OP_HISTOGRAM: { // basic/SmoothHistogramPdf.cu:13-46: the content of the event's bin in the table attached by gf_table_set
         const int slot = P.ints[nd.int_off];
         const double *table = static_cast<const double *>(P.aux[slot]);

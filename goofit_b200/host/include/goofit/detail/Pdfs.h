@@ -138,6 +138,11 @@ class VoigtianPdf : public GooPdf { // basic/VoigtianPdf.h: Breit-Wigner convolv
   public:
     VoigtianPdf(std::string n, Observable _x, Variable m, Variable s, Variable w);
 };
+/// utilities/VariableBinTransform1DPdf.h: the number of the variable-width bin |x| falls in (a mapping function for MappedPdf)
+class VariableBinTransform1DPdf : public GooPdf {
+  public:
+    VariableBinTransform1DPdf(std::string n, Observable _x, std::vector<fptype> binlimits);
+};
 class LandauPdf : public GooPdf { // basic/LandauPdf.h
   public:
     LandauPdf(std::string n, Observable _x, Variable mpv, Variable sigma);

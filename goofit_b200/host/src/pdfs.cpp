@@ -354,6 +354,12 @@ VoigtianPdf::VoigtianPdf(std::string n, Observable _x, Variable m, Variable s, V
     : GooPdf("VoigtianPdf", n, _x, m, s, w) { // VoigtianPdf.cu:324-329
     registerFunction("ptr_to_Voigtian", GF_OP_VOIGTIAN);
 }
+VariableBinTransform1DPdf::VariableBinTransform1DPdf(std::string n, Observable _x, std::vector<fptype> binlimits)
+    : GooPdf("VariableBinTransform1DPdf", n, _x) { // VariableBinTransform1DPdf.cu:31-43 (limits exclude the ends of the observable's range)
+    registerConstant((fptype)binlimits.size());
+    for(fptype l : binlimits) registerConstant(l);
+    registerFunction("ptr_to_VarBinTransform1D", GF_OP_VARBINTRANSFORM);
+}
 LandauPdf::LandauPdf(std::string n, Observable _x, Variable mpv, Variable sigma)
     : GooPdf("LandauPdf", n, _x, mpv, sigma) { // LandauPdf.cu:88-93
     registerFunction("ptr_to_Landau", GF_OP_LANDAU);

@@ -314,6 +314,8 @@ PYBIND11_MODULE(_goofit, m) {
         .def(py::init<std::string, BinnedDataSet *, Variable>(), "name"_a, "hist"_a, "smoothing"_a, py::keep_alive<1, 3>());
     py::class_<VoigtianPdf, GooPdf>(m, "VoigtianPdf")
         .def(py::init<std::string, Observable, Variable, Variable, Variable>(), "name"_a, "x"_a, "m"_a, "s"_a, "w"_a);
+    py::class_<VariableBinTransform1DPdf, GooPdf>(m, "VariableBinTransform1DPdf")
+        .def(py::init<std::string, Observable, std::vector<fptype>>(), "name"_a, "x"_a, "binlimits"_a);
     py::class_<LandauPdf, GooPdf>(m, "LandauPdf").def(py::init<std::string, Observable, Variable, Variable>(), "name"_a, "x"_a, "mpv"_a, "sigma"_a);
     py::class_<CombinePdf, GooPdf>(m, "CombinePdf");
     py::class_<AddPdf, CombinePdf>(m, "AddPdf")

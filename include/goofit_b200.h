@@ -83,6 +83,7 @@ enum gf_op {
                                second as the Breit-Wigner width and the third as the Gaussian sigma */
     GF_OP_HISTOGRAM,        /* SmoothHistogramPdf.cu:13-46 ints: aux slot of the (smoothed) bin table, see gf_table_set;
                                consts: nObs, histogram index, nVars, then (bins, lower limit, bin size) per observable */
+    GF_OP_VARBINTRANSFORM,  /* utilities/VariableBinTransform1DPdf.cu:8-27 consts: number of limits, the limits; value = how many of them |x| has reached */
     GF_OP_ADD = 32,         /* AddPdf.cu:16  ints: child norm slots */
     GF_OP_ADD_EXT,          /* AddPdf.cu:53 */
     GF_OP_PROD,             /* ProdPdf.cu:9 */

@@ -359,6 +359,39 @@ def test_voigtian_pdf(golden):
     check_pdf(golden, "voigt_gauss", gf.VoigtianPdf("voigt_gauss", x, m, zero, b1), d, x)
 
 
+def test_variable_bin_transform():
+    """utilities/VariableBinTransform1DPdf.cu: the number of ascending limits |x| has reached. Parity unpinned: upstream's class
+    cannot be run (its constructor never calls initialize() and its device function never advances the table cursor, :8-43; on
+    its own it segfaults in the reference build), so this is held to its documented meaning: on its own the values are
+    proportional to the bin number, and as the mapping function of a MappedPdf it picks the component of that bin."""
+    V = gf.Variable
+    x = gf.Observable("x", -4, 6)
+    X = np.random.default_rng(41).normal(0.5, 1.5, 4000)
+    X = X[(X > -4) & (X < 6)][:500]
+    d = dataset_from_columns([x], [X])
+    limits = [0.5, 1.25, 2.0, 3.5]
+    which = np.searchsorted(np.asarray(limits), np.abs(X), side="right")
+    vb = gf.VariableBinTransform1DPdf("varbin", x, limits)
+    vb.setData(d)
+    vb.calculateNLL()
+    p = np.asarray(vb.getCompProbsAtDataPoints()[0])
+    unit = p[which == 1][0]
+    np.testing.assert_allclose(p, which * unit, rtol=1e-14, atol=0)
+    m = V("vbm", 0.5, 0.1, -4, 6)
+    comps = [gf.GaussianPdf("vb%d" % k, x, m, V("vbs%d" % k, 0.6 + 0.4 * k, 0.1, 0.1, 5)) for k in range(5)]
+    mp = gf.MappedPdf("varbin_mapped", gf.VariableBinTransform1DPdf("varbin_map", x, limits), comps)
+    mp.setData(d)
+    mp.calculateNLL()
+    got = np.asarray(mp.getCompProbsAtDataPoints()[0])
+    for k, c in enumerate(comps):
+        c.setData(d)
+        c.calculateNLL()
+        want = np.asarray(c.getCompProbsAtDataPoints()[0])
+        sel = which == k
+        assert sel.any()
+        np.testing.assert_allclose(got[sel], want[sel], rtol=RTOL_EVT, atol=0)
+
+
 def test_composite_pdf(golden):
     """combine/CompositePdf.cu: f = h(g(event)); the shell h reads the core's value where the composite's first observable sits in
     the event, neither is normalised inside, the composite is (grid integral). Alone, inside an AddPdf, and with a core of two
