@@ -349,7 +349,7 @@ extern "C" int gf_validate_program(const gf_node *nodes, int n_nodes, int n_cons
             for(int k = first; k <= r; k++) {
                 const gf_node &nd = nodes[k];
                 if(!is_eval(nd.op)) return gf_fail("gf_set_program: non-evaluable record inside the subtree of node " + std::to_string(r));
-                int pops = nd.op < GF_OP_ADD ? 0 : (nd.op == GF_OP_CONVOLVE ? 0 : nd.nchild);
+                int pops = GF_IS_LEAF(nd.op) ? 0 : (nd.op == GF_OP_CONVOLVE ? 0 : nd.nchild);
                 const bool combiner = (nd.op >= GF_OP_ADD && nd.op <= GF_OP_PROD) || (nd.op >= GF_OP_EVTW_ADD && nd.op <= GF_OP_MAPPED);
                 if(combiner && (nd.nint < nd.nchild || nd.nchild < 1))
                     return gf_fail("gf_set_program: combiner without child norm slots, node " + std::to_string(k));

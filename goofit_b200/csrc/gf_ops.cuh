@@ -65,6 +65,8 @@ __device__ inline double gf_landau(double x, double mpv, double sigma) {
     return d / sigma;
 }
 
+__device__ inline bool gf_in_dalitz(double m12, double m13, double bigM, double dm1, double dm2, double dm3);
+
 // Re w(z), z = x + i y, of the complex error function by the Matta-Reichel series as RooFit's fast ComplexErrorFunc / CERNLIB WWERF
 // evaluate it and basic/VoigtianPdf.cu:41-104 restates it: twelve terms exp(-n_k) / ((d + n_k)^2 + f) on the grid n_k = (h k)^2,
 // h = 0.5 (0.53 when 2|x| is within 0.02 of an integer on the real axis, where the poles of the h = 0.5 correction term sit), a pole
@@ -352,6 +354,40 @@ __device__ inline double gf_leaf(const gf_node &nd, const gf_sprog &P, const Evt
         }
         return (double)ret;
     }
+    case GF_OP_DALITZ_VETO: { // physics/DalitzVetoPdf.cu:7-33: 1 inside the Dalitz plot and outside every veto band, else 0
+        double x = evt(ob[0]), y = evt(ob[1]);
+        double M = p[0], m1 = p[1], m2 = p[2], m3 = p[3];
+        double z = (M * M + m1 * m1 + m2 * m2 + m3 * m3) - x - y;
+        double ret = gf_in_dalitz(x, y, M, m1, m2, m3) ? 1.0 : 0.0;
+        const int nv = (int)(unsigned int)c[0];
+        for(int i = 0; i < nv; ++i) {
+            const int pair = (int)(unsigned int)c[1 + i];
+            const double lo = p[4 + 2 * i], hi = p[5 + 2 * i];
+            const double v = pair == 0 ? x : (pair == 1 ? y : z); // PAIR_12, PAIR_13, else PAIR_23
+            ret *= (v < hi && v > lo) ? 0.0 : 1.0;
+        }
+        return ret;
+    }
+    case GF_OP_SQDALITZ_EFF: { // physics/SquareDalitzEffPdf.cu:10-74: polynomial in m23 and theta' with D -> KS0 h h masses built in
+        const double x = evt(ob[0]), y = evt(ob[1]);
+        const double mD = 1.86483, mK = 0.497611, mh1 = 0.13957, mh2 = 0.13957;
+        if(!gf_in_dalitz(x, y, mD, mK, mh1, mh2)) return 0;
+        const double m23 = mD * mD + mK * mK + mh1 * mh1 + mh2 * mh2 - x - y;
+        double th;
+        if(m23 < 0)
+            th = 0;
+        else {
+            const double num = m23 * (x - y);
+            const double t1 = m23 - mh1 * mh1 + mh2 * mh2, t2 = mD * mD - mK * mK - m23;
+            const double l1 = t1 * t1 - 4 * m23 * mh2 * mh2, l2 = t2 * t2 - 4 * m23 * mK * mK;
+            const double den = sqrt(l1) * sqrt(l2);
+            th = (l1 < 0. || l2 < 0. || den == 0.) ? -99 : num / den;
+        }
+        if(th > 1. || th < -1.) return 0;
+        if(m23 < 0 || m23 > 2) return 0;
+        return p[0] * m23 * m23 + p[1] * m23 + p[2] * m23 * th * th + p[3] * th * th + p[4] * th + p[5] + p[6] * m23 * m23 * m23 * m23
+               + p[7] * m23 * m23 * m23;
+    }
     case GF_OP_HISTOGRAM: { // basic/SmoothHistogramPdf.cu:13-46: the content of the event's bin in the table attached by gf_table_set
         const int slot = P.ints[nd.int_off];
         const double *table = static_cast<const double *>(P.aux[slot]);
@@ -587,7 +623,7 @@ __device__ inline double gf_eval_tree(const gf_sprog &P, const gf_dev_view &V, i
     gf_evt_sub<(HAS & GF_HAS_COMPOSITE) != 0, Evt> evt{evt_in, 0.0, -1};
     for(int k = first; k <= last; ++k) {
         const gf_node &nd = P.nodes[k];
-        if(nd.op < GF_OP_ADD) {
+        if(GF_IS_LEAF(nd.op)) {
             st[sp++] = gf_leaf(nd, P, evt);
             continue;
         }

@@ -1,0 +1,3 @@
+// Source-compatibility header: the reference's <goofit/PDFs/physics/SquareDalitzEffPdf.h> include path, served by the B200 host API.
+#pragma once
+#include <goofit/detail/Physics3.h>

@@ -220,6 +220,28 @@ class Amp3Body_TD : public Amp3BodyBase {
 
 /// Host helper that evaluates the PDF on the Dalitz grid and draws toy events from it
 /// (DalitzPlotter.h:24-141; the ROOT histogram methods are out of scope).
+/// physics/DalitzVetoPdf.h: one band of a Dalitz variable to cut out
+struct VetoInfo {
+    Variable minimum;
+    Variable maximum;
+    DaughterPair cyclic_index;
+    VetoInfo(Variable minimum, Variable maximum, DaughterPair cyclic_index)
+        : minimum(minimum)
+        , maximum(maximum)
+        , cyclic_index(cyclic_index) {}
+};
+/// 1 inside the Dalitz plot and outside every veto band, 0 elsewhere: a factor of an efficiency function
+class DalitzVetoPdf : public GooPdf {
+  public:
+    DalitzVetoPdf(std::string n, Observable _x, Observable _y, Variable motherM, Variable d1m, Variable d2m, Variable d3m, std::vector<VetoInfo> vetos);
+};
+/// physics/SquareDalitzEffPdf.h: efficiency polynomial in m23 and theta' over the D -> KS0 h h Dalitz plot
+class SquareDalitzEffPdf : public GooPdf {
+  public:
+    SquareDalitzEffPdf(std::string n, Observable m12, Observable m13, Variable c0, Variable c1, Variable c2, Variable c3, Variable c4, Variable c5,
+                       Variable c6, Variable c7);
+};
+
 class DalitzPlotter {
   public:
     DalitzPlotter(GooPdf *overallSignal, Amp3Body *signalDalitz);

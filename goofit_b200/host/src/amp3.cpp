@@ -376,3 +376,23 @@ void DalitzPlotter::fillDataSetMC(UnbinnedDataSet &dataset, size_t nTotal, unsig
 }
 
 } // namespace GooFit
+
+// ---- efficiency helpers (physics/DalitzVetoPdf.cu:37-55, physics/SquareDalitzEffPdf.cu:78-95) --------------------------------
+namespace GooFit {
+DalitzVetoPdf::DalitzVetoPdf(std::string n, Observable _x, Observable _y, Variable motherM, Variable d1m, Variable d2m, Variable d3m,
+                             std::vector<VetoInfo> vetos)
+    : GooPdf("DalitzVetoPdf", n, _x, _y, motherM, d1m, d2m, d3m) {
+    registerConstant(vetos.size());
+    for(auto &veto : vetos) {
+        registerParameter(veto.minimum);
+        registerParameter(veto.maximum);
+        registerConstant(veto.cyclic_index);
+    }
+    registerFunction("ptr_to_DalitzVeto", GF_OP_DALITZ_VETO);
+}
+SquareDalitzEffPdf::SquareDalitzEffPdf(std::string n, Observable m12, Observable m13, Variable c0, Variable c1, Variable c2, Variable c3, Variable c4,
+                                       Variable c5, Variable c6, Variable c7)
+    : GooPdf("SquareDalitzEffPdf", n, m12, m13, c0, c1, c2, c3, c4, c5, c6, c7) {
+    registerFunction("ptr_to_SquareDalitzEff", GF_OP_SQDALITZ_EFF);
+}
+} // namespace GooFit

@@ -338,6 +338,17 @@ PYBIND11_MODULE(_goofit, m) {
     py::enum_<DaughterPair>(m, "DaughterPair")
         .value("PAIR_12", PAIR_12).value("PAIR_13", PAIR_13).value("PAIR_23", PAIR_23).export_values();
     m.def("inDalitz", &inDalitz, "m12"_a, "m13"_a, "bigM"_a, "dm1"_a, "dm2"_a, "dm3"_a);
+    py::class_<VetoInfo>(m, "VetoInfo")
+        .def(py::init<Variable, Variable, DaughterPair>(), "minimum"_a, "maximum"_a, "cyclic_index"_a)
+        .def_readwrite("minimum", &VetoInfo::minimum)
+        .def_readwrite("maximum", &VetoInfo::maximum)
+        .def_readwrite("cyclic_index", &VetoInfo::cyclic_index);
+    py::class_<DalitzVetoPdf, GooPdf>(m, "DalitzVetoPdf")
+        .def(py::init<std::string, Observable, Observable, Variable, Variable, Variable, Variable, std::vector<VetoInfo>>(), "name"_a, "x"_a, "y"_a,
+             "motherM"_a, "d1m"_a, "d2m"_a, "d3m"_a, "vetos"_a);
+    py::class_<SquareDalitzEffPdf, GooPdf>(m, "SquareDalitzEffPdf")
+        .def(py::init<std::string, Observable, Observable, Variable, Variable, Variable, Variable, Variable, Variable, Variable, Variable>(), "name"_a,
+             "m12"_a, "m13"_a, "c0"_a, "c1"_a, "c2"_a, "c3"_a, "c4"_a, "c5"_a, "c6"_a, "c7"_a);
     py::class_<AmpComponent, GooPdf>(m, "AmpComponent");
     py::class_<ResonancePdf, AmpComponent>(m, "ResonancePdf")
         .def("get_amp_real", &ResonancePdf::get_amp_real)

@@ -94,6 +94,9 @@ enum gf_op {
     GF_OP_COMPOSITE_ARG,    /* CompositePdf.cu:6-24  child: the core function g; its value (left on the stack) becomes what the composite's
                              * observable 0 reads as, until the GF_OP_COMPOSITE record that follows the shell */
     GF_OP_COMPOSITE,        /* CompositePdf.cu:26-36 children: the GF_OP_COMPOSITE_ARG record and the shell h; value = h(g(event)), neither normalised */
+    /* second range of leaf records (the first is below GF_OP_ADD): GF_IS_LEAF(op) */
+    GF_OP_DALITZ_VETO,      /* DalitzVetoPdf.cu:7-33 params: M, m1, m2, m3, then (min, max) per veto; consts: nVetos, pair index per veto */
+    GF_OP_SQDALITZ_EFF,     /* SquareDalitzEffPdf.cu:35-74 params: c0..c7 */
     GF_OP_AMP3 = 48,        /* Amp3Body.cu:60  child: efficiency; ints: amp3 id */
     GF_OP_AMP4,             /* Amp4Body.cu:53 */
     GF_OP_AMP4_TD,          /* Amp4Body_TD.cu:167 */
@@ -117,6 +120,8 @@ enum gf_op {
     GF_OP_TRES_TRUTH = 112, /* physics/TruthResolution.cu:8-28 ; no parameters */
     GF_OP_TRES_3GAUSS       /* physics/ThreeGaussResolution.cu:11-125 ; 13 parameters in constructor order */
 };
+/* records that push one value without popping any (closed-form shapes) */
+#define GF_IS_LEAF(op) ((op) < GF_OP_ADD || ((op) >= GF_OP_DALITZ_VETO && (op) < GF_OP_AMP3))
 
 enum gf_metric { /* MetricPointer.cu:8-58 */
     GF_METRIC_EVAL = 0, GF_METRIC_NLL = 1, GF_METRIC_PROB = 2,

@@ -34,6 +34,8 @@
 #include <goofit/PDFs/basic/CorrGaussianPdf.h>
 #include <goofit/PDFs/basic/BinTransformPdf.h>
 #include <goofit/PDFs/basic/LandauPdf.h>
+#include <goofit/PDFs/physics/DalitzVetoPdf.h>
+#include <goofit/PDFs/physics/SquareDalitzEffPdf.h>
 #include <goofit/PDFs/basic/VoigtianPdf.h>
 #include <goofit/PDFs/basic/SmoothHistogramPdf.h>
 #include <goofit/PDFs/combine/MappedPdf.h>
@@ -375,7 +377,7 @@ struct DalitzModel {
     std::vector<Variable> coefs; // (re, im) interleaved
 };
 
-static DalitzModel *make_dalitz(bool float_masses, int grid) {
+static DalitzModel *make_dalitz(bool float_masses, int grid, int eff_kind = 0) {
     auto *M = new DalitzModel();
     M->m12.setNumBins(grid);
     M->m13.setNumBins(grid);
@@ -418,6 +420,17 @@ static DalitzModel *make_dalitz(bool float_masses, int grid) {
     if(!float_masses)
         for(auto *res : d.resonances) res->setParameterConstantness(true);
     Variable one("constantOne", 1), zero("constantZero", 0);
+    if(eff_kind == 1) { // veto bands on two of the Dalitz variables
+        Variable vM("vetoM", _mD0), v1("veto1", piZeroMass), v2("veto2", piPlusMass), v3("veto3", piPlusMass);
+        Variable lo1("vetoLo1", 0.9), hi1("vetoHi1", 1.1), lo2("vetoLo2", 0.2), hi2("vetoHi2", 0.3);
+        std::vector<VetoInfo> vetos{VetoInfo(lo1, hi1, PAIR_12), VetoInfo(lo2, hi2, PAIR_23)};
+        auto *veto = new DalitzVetoPdf("veto", M->m12, M->m13, vM, v1, v2, v3, vetos);
+        M->eff = veto; // one record: upstream takes the LAST function of the table as the efficiency (Amp3Body.cu:196-203) and
+                       // skips exactly one record for it outside the Dalitz plot (:72-82), so a composed efficiency is not usable there
+    } else if(eff_kind == 2) { // the D -> KS0 h h efficiency polynomial (its own masses are built in)
+        Variable c0("sq0", 0.1), c1("sq1", -0.2), c2("sq2", 0.3), c3("sq3", 0.15), c4("sq4", 0.05), c5("sq5", 1.0), c6("sq6", 0.01), c7("sq7", -0.02);
+        M->eff = new SquareDalitzEffPdf("sqeff", M->m12, M->m13, c0, c1, c2, c3, c4, c5, c6, c7);
+    } else
     M->eff = new PolynomialPdf("constantEff", std::vector<Observable>{M->m12, M->m13}, std::vector<Variable>{one},
                                std::vector<Variable>{zero, zero}, 0);
     M->signal = new Amp3Body("signalPDF", M->m12, M->m13, M->eventNumber, d, M->eff);
@@ -1279,6 +1292,44 @@ static void case_voigt() {
     { VoigtianPdf p{"voigt_gauss", x, m, zero, b1}; dump_pdf("voigt_gauss", p, d, true, &x); }
 }
 
+// ---- DalitzVetoPdf and SquareDalitzEffPdf on their own, and a vetoed, sloped efficiency inside Amp3Body (physics/DalitzVetoPdf.cu,
+// physics/SquareDalitzEffPdf.cu, Amp3Body.cu:60-122)
+static void case_dalitzeff() {
+    DalitzModel *M = make_dalitz(false, 120, 1);
+    UnbinnedDataSet d({M->m12, M->m13, M->eventNumber});
+    fill_dalitz_uniform(*M, d, 500, 777);
+    for(double a : {0.05, 2.9}) { // outside the boundary
+        M->m12.setValue(a); M->m13.setValue(a > 2 ? 2.9 : 0.01); M->eventNumber.setValue(d.getNumEvents());
+        d.addEvent();
+    }
+    save_npy("dalitzeff.m12", column(d, M->m12));
+    save_npy("dalitzeff.m13", column(d, M->m13));
+    Amp3Body *sig = M->signal;
+    sig->setData(&d);
+    sig->setDataSize(d.getNumEvents());
+    put("dalitzeff.nll", sig->calculateNLL());
+    ProdPdf wrap{"wrap", {sig}};
+    wrap.setData(&d);
+    sig->setDataSize(d.getNumEvents());
+    save_npy("dalitzeff.prob", wrap.getCompProbsAtDataPoints()[0]);
+    // (on their own neither helper can be normalised: MetricTaker.cu:73-88 writes every dimension's bin centre into the first
+    // observable's slot, m13 stays 0 and no grid point lies inside the Dalitz plot - so both are pinned as the efficiency of an Amp3Body)
+    DalitzModel *M2 = make_dalitz(false, 120, 2);
+    UnbinnedDataSet e({M2->m12, M2->m13, M2->eventNumber});
+    for(size_t i = 0; i < d.getNumEvents(); i++) {
+        M2->m12.setValue(d.getValue(M->m12, i)); M2->m13.setValue(d.getValue(M->m13, i)); M2->eventNumber.setValue(i);
+        e.addEvent();
+    }
+    Amp3Body *sig2 = M2->signal;
+    sig2->setData(&e);
+    sig2->setDataSize(e.getNumEvents());
+    put("dalitzsq.nll", sig2->calculateNLL());
+    ProdPdf wrap2{"wrap2", {sig2}};
+    wrap2.setData(&e);
+    sig2->setDataSize(e.getNumEvents());
+    save_npy("dalitzsq.prob", wrap2.getCompProbsAtDataPoints()[0]);
+}
+
 // ---- CompositePdf: f(x) = h(g(x)), core g = 0.5 + 0.8 x, shell h = Gaussian; a second one with a two-observable core (combine/CompositePdf.cu)
 static void case_composite() {
     Observable x{"x", -5, 5}, y{"y", -2, 2};
@@ -1973,6 +2024,7 @@ int main(int argc, char **argv) {
             if(only == "all" || only == "basic2") case_basic2();
             if(only == "all" || only == "smoothhist") case_smoothhist();
             if(only == "all" || only == "voigt") case_voigt();
+            if(only == "all" || only == "dalitzeff") case_dalitzeff();
             if(only == "all" || only == "dalitzfit") case_dalitz_fit();
             if(only == "all" || only == "dp4") case_dp4();
             if(only == "all" || only == "dp4fit") case_dp4_fit();

@@ -33,7 +33,7 @@ def dataset_from_columns(observables, columns):
 class Dalitz:
     """D0 -> pi+ pi- pi0, 16 resonances (15 RBW + NonRes), constant efficiency."""
 
-    def __init__(self, float_masses=False, grid=240):
+    def __init__(self, float_masses=False, grid=240, eff_kind=0):
         k = self.keep = Keep()
         self.m12 = gf.Observable("m12", 0, 3)
         self.m13 = gf.Observable("m13", 0, 3)
@@ -82,7 +82,14 @@ class Dalitz:
         for r in self.resonances:
             d.add_resonance(r)
         one, zero = V("constantOne", 1), V("constantZero", 0)
-        self.eff = k(gf.PolynomialPdf("constantEff", [self.m12, self.m13], [one], [zero, zero], 0))
+        if eff_kind == 1:  # veto bands on two of the Dalitz variables (oracle make_dalitz eff_kind 1)
+            vetos = [gf.VetoInfo(V("vetoLo1", 0.9), V("vetoHi1", 1.1), gf.PAIR_12), gf.VetoInfo(V("vetoLo2", 0.2), V("vetoHi2", 0.3), gf.PAIR_23)]
+            self.eff = k(gf.DalitzVetoPdf("veto", self.m12, self.m13, V("vetoM", MD0), V("veto1", PI0), V("veto2", PIP), V("veto3", PIP), vetos))
+        elif eff_kind == 2:  # the D -> KS0 h h efficiency polynomial
+            c = [V("sq%d" % i, v) for i, v in enumerate((0.1, -0.2, 0.3, 0.15, 0.05, 1.0, 0.01, -0.02))]
+            self.eff = k(gf.SquareDalitzEffPdf("sqeff", self.m12, self.m13, *c))
+        else:
+            self.eff = k(gf.PolynomialPdf("constantEff", [self.m12, self.m13], [one], [zero, zero], 0))
         self.signal = gf.Amp3Body("signalPDF", self.m12, self.m13, self.evt, d, self.eff)
 
     def dataset(self, m12, m13):

@@ -392,6 +392,28 @@ def test_variable_bin_transform():
         np.testing.assert_allclose(got[sel], want[sel], rtol=RTOL_EVT, atol=0)
 
 
+@pytest.mark.parametrize("kind,tag", [(1, "dalitzeff"), (2, "dalitzsq")])
+def test_dalitz_efficiency_helpers(golden, kind, tag):
+    """physics/DalitzVetoPdf.cu (kind 1: two veto bands) and physics/SquareDalitzEffPdf.cu (kind 2) as the efficiency of the
+    16-resonance Amp3Body: NLL and per-event values against the reference, where neither helper can be normalised on its own: the grid integral
+    writes every dimension's bin centre into the first observable's slot (MetricTaker.cu:73-88, kept here), so m13 stays 0 and no
+    grid point is inside the Dalitz plot (oracle/ref_driver.cpp case_dalitzeff)."""
+    M = Dalitz(float_masses=False, grid=120, eff_kind=kind)
+    m12, m13 = golden.arr("dalitzeff.m12"), golden.arr("dalitzeff.m13")
+    d = M.dataset(m12, m13)
+    M.signal.setData(d)
+    M.signal.setDataSize(len(d))
+    nll = M.signal.calculateNLL()
+    assert rel(nll, golden[tag + ".nll"]) < RTOL_NLL, (nll, golden[tag + ".nll"])
+    wrap = gf.ProdPdf("wrap", [M.signal])
+    wrap.setData(d)
+    M.signal.setDataSize(len(d))
+    probs = np.asarray(wrap.getCompProbsAtDataPoints()[0])
+    want = golden.arr(tag + ".prob")
+    assert ((probs == 0) == (want == 0)).all() and (want == 0).sum() > 20
+    np.testing.assert_allclose(probs, want, rtol=1e-11, atol=0)
+
+
 def test_composite_pdf(golden):
     """combine/CompositePdf.cu: f = h(g(event)); the shell h reads the core's value where the composite's first observable sits in
     the event, neither is normalised inside, the composite is (grid integral). Alone, inside an AddPdf, and with a core of two
