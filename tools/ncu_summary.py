@@ -1,6 +1,7 @@
 """tools/ncu_summary.py <raw.csv> <out.csv> [traffic.json] — condense `ncu --page raw --csv` output to the columns the
 roofline discussion uses (one row per captured launch) and refresh profiles/traffic.json."""
 import csv
+import os
 import json
 import sys
 
@@ -53,9 +54,15 @@ if len(sys.argv) > 3:
             t[k + "_dram_bytes_per_launch"] = int(traffic[k][0][0])
     import subprocess
     t["source"] = "ncu --set full --clock-control none, tools/profile_once.py at 10^7 events (profiles/r02_ncu_full_summary.csv)"
+    head = ""
     try:
-        t["git_head"] = subprocess.run(["git", "rev-parse", "--short", "HEAD"], capture_output=True, text=True).stdout.strip()
+        head = subprocess.run(["git", "rev-parse", "--short", "HEAD"], capture_output=True, text=True).stdout.strip()
     except Exception:
         pass
+    if not head:  # the GPU box gets a snapshot without .git: tools/final_capture.sh is sent with the hash in .git_head
+        here = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+        if os.path.exists(os.path.join(here, ".git_head")):
+            head = open(os.path.join(here, ".git_head")).read().strip()
+    t["git_head"] = head
     json.dump(t, open(sys.argv[3], "w"), indent=1)
 print("rows", len(out) - 1)
