@@ -513,8 +513,12 @@ void PdfBase::setData(DataSet *data) {
                 owned.emplace_back(count);
                 std::iota(owned.back().begin(), owned.back().end(), 0.0);
                 cols.push_back(nullptr);
-            } else
-                cols.push_back(c.data() + first);
+            } else {
+                // a null pointer marks an owned column below: an empty dataset's vector may legitimately have none, so point at a
+                // dummy instead (no element of it is ever read: count is 0)
+                static const fptype none = 0;
+                cols.push_back(c.empty() ? &none : c.data() + first);
+            }
         }
     } else if(auto *bd = dynamic_cast<BinnedDataSet *>(data)) {
         numEvents  = 0;

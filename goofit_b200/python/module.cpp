@@ -142,6 +142,7 @@ PYBIND11_MODULE(_goofit, m) {
         size_t rows = a.shape(0), cols = a.shape(1), nobs = d.getObservables().size();
         if(rows != nobs && rows + 1 != nobs)
             throw GeneralError("The wrong number of rows, expected {}, but matrix had {}", nobs, rows);
+        if(cols == 0) return; // no events: nothing to append (and no element to take the address of)
         if(!filter) { // bulk path: columns are appended without touching the Observables
             std::vector<const fptype *> cp;
             std::vector<fptype> idx;

@@ -414,6 +414,27 @@ def test_dalitz_efficiency_helpers(golden, kind, tag):
     np.testing.assert_allclose(probs, want, rtol=1e-11, atol=0)
 
 
+def test_empty_and_single_event_datasets():
+    """Edge sizes: no event at all (uploading it must not crash; the empty sum is refused like upstream's), one event (a partial first block), and 33 events (one past a warp): the NLL equals -sum(log(prob))."""
+    V = gf.Variable
+    x = gf.Observable("x", -5, 5)
+    g = gf.GaussianPdf("edge_g", x, V("edge_m", 0.4, 0.1, -5, 5), V("edge_s", 1.3, 0.1, 0.1, 5))
+    for n in (0, 1, 33):
+        X = np.linspace(-2.0, 2.5, n) if n else np.empty(0)
+        d = dataset_from_columns([x], [X])
+        g.setData(d)
+        if n == 0:  # the empty sum is 0, which calculateNLL refuses as the reference does (GooPdf.cu:268-270 "zero NLL")
+            with pytest.raises(Exception, match="zero NLL"):
+                g.calculateNLL()
+            continue
+        nll = g.calculateNLL()
+        want = -np.log(np.exp(-0.5 * ((X - 0.4) / 1.3) ** 2) / (1.3 * math.sqrt(2 * math.pi)))
+        probs = np.asarray(g.getCompProbsAtDataPoints()[0])
+        assert len(probs) == n
+        np.testing.assert_allclose(-np.log(probs), want, rtol=1e-9, atol=0)  # analytic integral over all x vs the range: tails 1e-4
+        assert rel(nll, math.fsum(-np.log(probs))) < RTOL_NLL
+
+
 def test_composite_pdf(golden):
     """combine/CompositePdf.cu: f = h(g(event)); the shell h reads the core's value where the composite's first observable sits in
     the event, neither is normalised inside, the composite is (grid integral). Alone, inside an AddPdf, and with a core of two
