@@ -435,6 +435,37 @@ def test_empty_and_single_event_datasets():
         assert rel(nll, math.fsum(-np.log(probs))) < RTOL_NLL
 
 
+def test_misuse_raises_instead_of_crashing(golden):
+    """Calls out of order or with the wrong sizes end in an exception with a message, never in a crash or a silent wrong number."""
+    V = gf.Variable
+    x = gf.Observable("x", -5, 5)
+    g = gf.GaussianPdf("mis_g", x, V("mis_m", 0.4, 0.1, -5, 5), V("mis_s", 1.3, 0.1, 0.1, 5))
+    with pytest.raises(Exception):
+        g.calculateNLL()  # no data yet
+    # the amplitude caches follow the dataset: a larger, then a smaller dataset on the same model give what a fresh model gives
+    m12, m13 = golden.arr("dalitz.m12"), golden.arr("dalitz.m13")
+    M = Dalitz(float_masses=True, grid=120)
+    out = []
+    for n in (200, len(m12), 50):
+        d = M.dataset(m12[:n], m13[:n])
+        M.signal.setData(d)
+        M.signal.setDataSize(len(d))
+        out.append(M.signal.calculateNLL())
+    assert rel(out[1], golden["dalitz.nll"]) < RTOL_NLL
+    F = Dalitz(float_masses=True, grid=120)
+    d = F.dataset(m12[:50], m13[:50])
+    F.signal.setData(d)
+    F.signal.setDataSize(len(d))
+    assert F.signal.calculateNLL() == out[2]
+    # the cache is sized from the uploaded events, not from setDataSize's argument: a wrong argument cannot make it too small
+    d = M.dataset(m12[:300], m13[:300])
+    M.signal.setData(d)
+    M.signal.setDataSize(100)
+    wrong = M.signal.calculateNLL()
+    M.signal.setDataSize(len(d))
+    assert M.signal.calculateNLL() == wrong and math.isfinite(wrong)
+
+
 def test_composite_pdf(golden):
     """combine/CompositePdf.cu: f = h(g(event)); the shell h reads the core's value where the composite's first observable sits in
     the event, neither is normalised inside, the composite is (grid integral). Alone, inside an AddPdf, and with a core of two
