@@ -1,6 +1,7 @@
 // gf_ops.cuh — per-node device math and the post-order stack machine.
 // Each case cites the reference device function it reproduces (paths under /root/reference/src/PDFs).
 #pragma once
+#include "gf_math.cuh"
 
 // std::pow(double, int) of the reference promotes to pow(double, double). For k = 0, 1, 2 the results 1, x and the
 // correctly rounded x*x are what a correctly rounded pow returns, without ~200 instructions of generic pow; higher
@@ -506,7 +507,7 @@ __device__ inline double gf_tres(int op, const double *p, double coshterm, doubl
         // cosh/sinh share one expm1: with u = e^a - 1, sinh a = (u + u/(u+1))/2 and cosh a = 1 + u^2/(2(u+1)), both
         // accurate to an ulp or two for the small a = y t/tau of mixing fits (no e^a - e^-a cancellation)
         double ret = 0;
-        dtime /= tau;
+        dtime *= gf_rcp(tau); // 1 / tau is the same for every event of a call: one reciprocal per thread, not a division per event
         double sn, cs, u;
         const double ax = x * dtime, by = y * dtime;
         if(fabs(ax) <= 0.25 && fabs(by) <= 0.25) {
@@ -516,7 +517,7 @@ __device__ inline double gf_tres(int op, const double *p, double coshterm, doubl
             sincos(ax, &sn, &cs);
             u = expm1(by);
         }
-        const double ui = u / (u + 1.0);
+        const double ui = u * gf_rcp(u + 1.0);
         const double sh = 0.5 * (u + ui), ch = 1.0 + 0.5 * u * ui;
         ret += coshterm * ch;
         ret += costerm * cs;
