@@ -111,12 +111,11 @@ __device__ inline double gf_faddeeva_re(double x, double y) {
     }
     const double r = 0.31830988618379067154 * h; // h / pi
     const double d = (y - x) * (y + x), f = 4 * x * x * y * y;
-    double g = 0, q = 0;
+    double g = 0; // (the companion sum over (s - n) u feeds Im w only)
     for(int k = 1; k <= 12; k++) {
         const double n = (h * k) * (h * k);
         const double u = exp(-n) / ((d + n) * (d + n) + f);
         g += (s + n) * u;
-        q += (s - n) * u;
     }
     const double inv_s = 1 / s;
     double re = r * (y * (inv_s + 2.0 * g));
@@ -130,7 +129,6 @@ __device__ inline double gf_faddeeva_re(double x, double y) {
         sincos(2.0 * x * y, &s2, &c2);
         re += gg * (c2 * ff - s2 * sn);
     }
-    (void)q;
     return re;
 }
 
