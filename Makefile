@@ -28,6 +28,7 @@ LDSTD    := $(if $(SYSGCC),-L$(dir $(SYSGCC)),)
 PYEXT    := $(shell $(PYTHON) -c "import sysconfig; print(sysconfig.get_config_var('EXT_SUFFIX'))")
 PYINC    := $(shell $(PYTHON) -c "import sysconfig, pybind11; print('-I' + sysconfig.get_paths()['include'] + ' -I' + pybind11.get_include())")
 
+.SECONDEXPANSION:
 all: cuda host python examples
 cuda: $(LIBDIR)/libgoofit_b200.so
 host: $(LIBDIR)/libgoofit_host.so
@@ -65,7 +66,13 @@ PYOBJ := $(patsubst goofit_b200/python/%.cpp,build/py/%.o,$(PYSRC))
 goofit_b200/_goofit$(PYEXT): $(PYOBJ) $(LIBDIR)/libgoofit_host.so
 	$(CXX) -shared $(LDSTD) -o $@ $(PYOBJ) -L$(LIBDIR) -lgoofit_host -lgoofit_b200 -lMinuit2 -Wl,-rpath,'$$ORIGIN/lib'
 
-examples: examples/bin/exponential
+# The reference's OWN example sources, compiled unmodified where they lie against this repo's headers and libraries (the ones that
+# need no ROOT): what a user does who switches the include and library paths. Only where the reference checkout exists.
+REFEX    := $(if $(wildcard $(REF)/examples/exponential/exponential.cpp),examples/bin/ref_exponential examples/bin/ref_product,)
+examples: examples/bin/exponential $(REFEX)
+examples/bin/ref_%: $(REF)/examples/%/$$*.cpp $(LIBDIR)/libgoofit_host.so
+	@mkdir -p examples/bin
+	$(CXX) $(HFLAGS) -I$(REF)/extern/CLI11/include $< $(LDSTD) -L$(LIBDIR) -lgoofit_host -lgoofit_b200 -lMinuit2 -Wl,-rpath,'$$ORIGIN/../../goofit_b200/lib' -o $@
 examples/bin/%: examples/%.cpp $(LIBDIR)/libgoofit_host.so
 	@mkdir -p examples/bin
 	$(CXX) $(HFLAGS) $< $(LDSTD) -L$(LIBDIR) -lgoofit_host -lgoofit_b200 -lMinuit2 -Wl,-rpath,'$$ORIGIN/../../goofit_b200/lib' -o $@

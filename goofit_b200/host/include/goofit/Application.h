@@ -6,9 +6,11 @@
 #pragma once
 #include <cstdlib>
 #include <cstring>
+#include <fstream>
 #include <iostream>
 #include <string>
 
+#include <goofit/Color.h>
 #include <goofit/detail/Core.h>
 
 namespace GooFit {
@@ -42,6 +44,27 @@ class Application {
         return e.get_exit_code();
     }
     bool quiet() const { return quiet_; }
+    /// where an input file of an example lives (Application.cpp:295-333): the working directory, the directory of the
+    /// executable, then `base` under GOOFIT_SOURCE_DIR (an environment variable or compile-time macro here)
+    std::string get_filename(const std::string &input_str, std::string base = "") const {
+        auto exists = [](const std::string &p) {
+            std::ifstream f(p);
+            return f.good();
+        };
+        if(exists(input_str)) return input_str;
+        std::string prog = argc_ > 0 && argv_ && argv_[0] ? argv_[0] : "";
+        size_t loc = prog.rfind('/');
+        if(loc != std::string::npos && exists(prog.substr(0, loc) + "/" + input_str)) return prog.substr(0, loc) + "/" + input_str;
+        const char *env = std::getenv("GOOFIT_SOURCE_DIR");
+#ifdef GOOFIT_SOURCE_DIR
+        std::string src = env ? env : GOOFIT_SOURCE_DIR;
+#else
+        std::string src = env ? env : ".";
+#endif
+        if(!base.empty() && exists(src + "/" + base + "/" + input_str)) return src + "/" + base + "/" + input_str;
+        if(exists(src + "/../" + input_str)) return src + "/../" + input_str;
+        throw GeneralError("Could not find file: {}", input_str);
+    }
 
   private:
     std::string description_;
@@ -51,7 +74,7 @@ class Application {
     bool quiet_{false}, splash_{true};
 };
 } // namespace GooFit
-#define GOOFIT_PARSE(app)                                                                                              \
+#define GOOFIT_PARSE(app, ...)                                                                                             \
     try {                                                                                                              \
         app.run();                                                                                                     \
     } catch(const GooFit::GeneralError &e) {                                                                           \

@@ -5,6 +5,7 @@
 //  include/goofit/PDFs/GooPdf.h); everything below the API is new: the PDF tree is flattened to a
 // post-order node program (no function-pointer tables) and all evaluation goes to the CUDA library.
 #pragma once
+#include <climits>
 #include <algorithm>
 #include <cmath>
 #include <complex>
@@ -197,6 +198,8 @@ class Variable : public Indexable {
 };
 std::ostream &operator<<(std::ostream &o, const Variable &v);
 std::ostream &operator<<(std::ostream &o, const Observable &v);
+/// reads the next number of the stream into the observable's value (Variable.cpp:53)
+std::istream &operator>>(std::istream &i, Observable &v);
 
 class EventNumber : public Observable {
   public:

@@ -43,6 +43,12 @@ std::ostream &operator<<(std::ostream &o, const Observable &v) {
     return o;
 }
 
+std::istream &operator>>(std::istream &i, Observable &v) {
+    fptype x;
+    if(i >> x) v.setValue(x);
+    return i;
+}
+
 void abort(std::string file, int line, std::string reason, const PdfBase *pdf) {
     // same message shape as src/goofit/Abort.cpp:10-42 (parameter dump, then throw)
     std::ostringstream o;

@@ -418,3 +418,20 @@ int main() { return 0; }
         pytest.skip("Minuit2 headers (reference checkout) are not on this machine")
     out = subprocess.run(cmd, capture_output=True, text=True)
     assert out.returncode == 0, out.stderr[-3000:]
+
+
+def test_reference_examples_compile_unmodified():
+    """examples/DP4/DP4.cu, examples/exponential/exponential.cpp and examples/product/product.cpp of the reference checkout compile
+    as they are against this repo's <goofit/...> headers (the ROOT-free ones; the others stop at TCanvas.h)."""
+    import shutil
+    import subprocess
+    ref = "/root/reference/examples"
+    cxx = shutil.which("g++")
+    if cxx is None or not os.path.isdir(ref):
+        pytest.skip("needs g++ and the reference checkout")
+    inc = os.path.join(ROOT, "goofit_b200", "host", "include")
+    for src in ("DP4/DP4.cu", "exponential/exponential.cpp", "product/product.cpp"):
+        cmd = [cxx, "-std=c++17", "-fsyntax-only", "-x", "c++", "-I" + os.path.join(ROOT, "include"), "-I" + inc,
+               "-I/root/reference/extern/Minuit2/inc", "-I/root/reference/extern/CLI11/include", "-DMATHCORE_STANDALONE", os.path.join(ref, src)]
+        out = subprocess.run(cmd, capture_output=True, text=True)
+        assert out.returncode == 0, src + "\n" + out.stderr[-3000:]

@@ -1094,6 +1094,20 @@ def test_cpp_example_exponential():
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
 
 
+@pytest.mark.parametrize("name", ["ref_exponential", "ref_product"])
+def test_reference_example_sources_unmodified(name):
+    """The reference's own examples/exponential/exponential.cpp and examples/product/product.cpp, compiled UNMODIFIED (where they
+    lie in the reference checkout, `make examples`) against this repo's headers and linked to its libraries: the program's own exit
+    status is the check (exponential.cpp returns 1 unless the fitted alpha is within 1 % of -1, then the Minuit status)."""
+    import os
+    import subprocess
+    exe = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "examples", "bin", name)
+    if not os.path.exists(exe):
+        pytest.skip("examples/bin/%s not built (needs the reference checkout at build time)" % name)
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+
+
 def test_generate_sig_three_and_four_body():
     """Amp3Body::GenerateSig / Amp4Body::GenerateSig (Amp3Body.cu:430-547, Amp4Body.cu:560-677): the returned weight is the
     phase-space weight times the un-normalised PDF value at the generated point; checked against the cached waves /
