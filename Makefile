@@ -69,6 +69,24 @@ goofit_b200/_goofit$(PYEXT): $(PYOBJ) $(LIBDIR)/libgoofit_host.so
 # The reference's OWN example sources, compiled unmodified where they lie against this repo's headers and libraries (the ones that
 # need no ROOT): what a user does who switches the include and library paths. Only where the reference checkout exists.
 REFEX    := $(if $(wildcard $(REF)/examples/exponential/exponential.cpp),examples/bin/ref_exponential examples/bin/ref_product,)
+# The reference's OWN Catch2 test sources, compiled unmodified where they lie and linked against this repo's libraries: the tests its
+# tests/{convert,simple,PDFs}/CMakeLists.txt enable without ROOT, plus the ROOT-gated ones that never touch ROOT. Catch2 itself is an
+# empty submodule upstream; tests/ref_catch provides the part of its interface these sources use. {fmt} comes from the reference's extern/.
+RT_CONVERT := BifurGaussTest CompositeTest ConvolutionTest EventWeightedAddTest GaussianTest JohnsonSUTest KinLimitBWTest LandauTest \
+              NovosibirskTest PolynomialTest ProdTest ScaledGaussianTest SmoothHistogramTest StepTest VoigtianTest BWTest CorrGaussianTest
+RT_SIMPLE  := NormalizeTest AddNormTest SimpleTest BinningTest BlindTest MonteCarloTest
+RT_PDFS    := GenArgusTest GenGaussianTest
+RT_BIN     := $(RT_CONVERT:%=examples/bin/reftests/convert/%) $(RT_SIMPLE:%=examples/bin/reftests/simple/%) $(RT_PDFS:%=examples/bin/reftests/PDFs/%)
+RT_FLAGS   := $(HFLAGS) -Wno-unused-variable -Itests/ref_catch -I$(REF)/tests/include -I$(REF)/tests/convert -I$(REF)/tests/PDFs -I$(REF)/extern/fmt/include -DFMT_HEADER_ONLY
+build/reftests/%.o: $(REF)/tests/%.cpp tests/ref_catch/catch2/catch_all.hpp $(wildcard $(HOST)/include/goofit/detail/*.h)
+	@mkdir -p $(dir $@)
+	$(CXX) $(RT_FLAGS) -c $< -o $@
+# one executable per test file, as upstream's goofit_catch_test() builds them (each with tests/catch_main.cpp)
+examples/bin/reftests/%: build/reftests/%.o build/reftests/catch_main.o $(LIBDIR)/libgoofit_host.so
+	@mkdir -p $(dir $@)
+	$(CXX) $< build/reftests/catch_main.o $(LDSTD) -L$(LIBDIR) -lgoofit_host -lgoofit_b200 -lMinuit2 -Wl,-rpath,'$$ORIGIN/../../../../goofit_b200/lib' -o $@
+.PRECIOUS: build/reftests/%.o
+REFEX    += $(if $(wildcard $(REF)/tests/catch_main.cpp),$(RT_BIN),)
 examples: examples/bin/exponential $(REFEX)
 examples/bin/ref_%: $(REF)/examples/%/$$*.cpp $(LIBDIR)/libgoofit_host.so
 	@mkdir -p examples/bin

@@ -29,6 +29,14 @@
 #define __device__
 #endif
 
+// upstream's headers pull in {fmt} (goofit/Log.h); user code that calls fmt::print after including a goofit header keeps compiling where {fmt} is on
+// the include path (this library itself formats its messages without it)
+#if defined(__has_include)
+#if __has_include(<fmt/format.h>)
+#include <fmt/format.h>
+#endif
+#endif
+
 namespace GooFit {
 
 using fptype    = double;
