@@ -435,3 +435,13 @@ def test_reference_examples_compile_unmodified():
                "-I/root/reference/extern/Minuit2/inc", "-I/root/reference/extern/CLI11/include", "-DMATHCORE_STANDALONE", os.path.join(ref, src)]
         out = subprocess.run(cmd, capture_output=True, text=True)
         assert out.returncode == 0, src + "\n" + out.stderr[-3000:]
+
+
+def test_goofit_package_alias():
+    """`from goofit import *` / `import goofit.minuit2`: the reference's Python package name resolves to this implementation."""
+    import goofit
+    import goofit.minuit2  # noqa: F401
+    for name in ("Observable", "Variable", "UnbinnedDataSet", "BinnedDataSet", "ExpPdf", "GaussianPdf", "AddPdf", "ProdPdf", "ConvolutionPdf",
+                 "FitManager", "Amp3Body", "Amp4Body", "Amp4Body_TD", "DecayInfo3", "DecayInfo4", "Resonances", "Lineshapes"):
+        assert hasattr(goofit, name) and getattr(goofit, name) is getattr(gf, name), name
+    assert goofit.minuit2.MnMigrad is gf.minuit2.MnMigrad
