@@ -641,7 +641,7 @@ __global__ void __launch_bounds__(GF_THREADS, upd_blocks_per_sm(NB))
         auto request = [&](bool l1, bool l2) {
             const long nb0 = base + warp_stride;
             const size_t off8 = (size_t)nb0 * 8, cur8 = (size_t)base * 8;
-            const bool more = nb0 < A.n;
+            const bool more = nb0 + 32 <= A.n; // whole groups only: the lines of a partial last group may lie past the end of the last plane
 #pragma unroll
             for(int k = 0; k < GF_PF_K; ++k) {
                 const char *q = pf_lane[k][lane];
