@@ -59,4 +59,15 @@ if "exp" in which:
     gf.fast_enable(False)
     print("exp (interpreter)", pdf.calculateNLL(), gf.last_kernel_name())
     gf.fast_enable(True)
+if "zach" in which:
+    from models import ZachFull
+    rz = np.random.default_rng(12)
+    m = N
+    core = rz.normal(0.14543, 0.0004, m)
+    tail = 0.1395 + (0.1665 - 0.1395) * rz.beta(1.5, 4.0, m)
+    dm = np.where(rz.uniform(size=m) < 0.9, core, tail)
+    dm = dm[(dm > 0.1396) & (dm < 0.1664)]
+    Z = ZachFull()
+    Z.total.setData(Z.dataset(dm))
+    print("zach", len(dm), Z.total.calculateNLL(), Z.total.calculateNLL(), gf.last_kernel_name())
 print("launches", gf.launch_count())
