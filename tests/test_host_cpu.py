@@ -445,3 +445,24 @@ def test_goofit_package_alias():
                  "FitManager", "Amp3Body", "Amp4Body", "Amp4Body_TD", "DecayInfo3", "DecayInfo4", "Resonances", "Lineshapes"):
         assert hasattr(goofit, name) and getattr(goofit, name) is getattr(gf, name), name
     assert goofit.minuit2.MnMigrad is gf.minuit2.MnMigrad
+
+
+def test_functor_writer_round_trip(tmp_path):
+    """goofit/FunctorWriter.h: parameters of a PDF tree written to a text file and read back exactly; lists of numbers likewise
+    (tests/cpp/functor_writer.cpp; host-only, no device call)."""
+    import shutil
+    import subprocess
+    cxx = shutil.which("g++")
+    minuit = "/root/reference/extern/Minuit2/inc"
+    if cxx is None or not os.path.isdir(minuit):
+        pytest.skip("needs g++ and the Minuit2 headers of the reference checkout")
+    exe = tmp_path / "fw"
+    lib = os.path.join(ROOT, "goofit_b200", "lib")
+    gcc_lib = [p for p in ("/usr/lib/gcc/x86_64-linux-gnu/13",) if os.path.isdir(p)]
+    cmd = [cxx, "-std=c++17", "-I" + os.path.join(ROOT, "include"), "-I" + os.path.join(ROOT, "goofit_b200", "host", "include"), "-I" + minuit,
+           "-DMATHCORE_STANDALONE", os.path.join(ROOT, "tests", "cpp", "functor_writer.cpp")] + ["-L" + p for p in gcc_lib] + [
+           "-L" + lib, "-lgoofit_host", "-lgoofit_b200", "-lMinuit2", "-Wl,-rpath," + lib, "-o", str(exe)]
+    out = subprocess.run(cmd, capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr[-3000:]
+    run = subprocess.run([str(exe)], cwd=str(tmp_path), capture_output=True, text=True)
+    assert run.returncode == 0, (run.returncode, run.stdout, run.stderr)
