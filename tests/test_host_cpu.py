@@ -466,3 +466,9 @@ def test_functor_writer_round_trip(tmp_path):
     assert out.returncode == 0, out.stderr[-3000:]
     run = subprocess.run([str(exe)], cwd=str(tmp_path), capture_output=True, text=True)
     assert run.returncode == 0, (run.returncode, run.stdout, run.stderr)
+    # goofit/MathUtils.h: the compensated sum recovers 1 + 1e100 + 1 - 1e100 = 2 (header-only)
+    exe2 = tmp_path / "mu"
+    out = subprocess.run(cmd[:1] + ["-std=c++17"] + [c for c in cmd if c.startswith("-I") or c.startswith("-D")] + [os.path.join(ROOT, "tests", "cpp", "math_utils.cpp"), "-o", str(exe2)],
+                         capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr[-2000:]
+    assert subprocess.run([str(exe2)]).returncode == 0
