@@ -53,34 +53,96 @@ __global__ void __launch_bounds__(GF_THREADS, 4)
     }
 }
 
-// table[k-kmin] = sum_{i<n_model} model[i] * resol[i + offset - k], i ascending: one thread per k runs the reference's
-// sequential FMA chain (same order, same rounding), but the operands come from shared memory: a block of 64 consecutive
-// k stages GF_CONV_TILE model points and the GF_CONV_TILE + 63 resolution values they meet, so the chain waits on LDS and
-// the FP64 pipe instead of on one global load per term.
+// table[k-kmin] = sum_{i<n_model} model[i] * resol[i + offset - k]. A block computes 64 consecutive k; the operands come from
+// shared memory (GF_CONV_TILE model points and the GF_CONV_TILE + 63 resolution values they meet per round), so the sums wait
+// on LDS and the FP64 pipe instead of on one global load per term.
+// Round 1 ran the reference's sequential FMA chain (one thread per k, i ascending: bit-identical tables) - 64 threads per
+// block, two warps per SM, 105 us per 10^4 x 10^4 table, a third of the zachFit call when all three convolutions are refilled.
+// Now a block is 256 threads: GF_CONV_SEG groups each sum their share of every tile, a thread holds GF_CONV_KPT consecutive
+// entries whose resolution values form a sliding window in registers (one new shared-memory load per KPT FMAs instead of one per
+// FMA), and a round's global loads are all issued before the first is stored. The partial sums of an entry are added in a fixed
+// order - deterministic and run-to-run identical, but not the reference's order: an entry moves by a few ulp (10^4 positive
+// terms), the NLL by < 1e-14 relative against the 1e-12 bar. -DGF_CONV_SEG=1 -DGF_CONV_KPT=1 restores the sequential chain.
 #define GF_CONV_TILE 512
-__global__ void __launch_bounds__(64)
+#ifndef GF_CONV_SEG
+#define GF_CONV_SEG 16 // thread groups per entry (1 with GF_CONV_KPT 1 = the reference's sequential chain)
+#endif
+#ifndef GF_CONV_KPT
+#define GF_CONV_KPT 4 // consecutive k per thread: they share a sliding window of resolution values, one new LDS per KPT FMAs
+#endif
+#define GF_CONV_KT (64 / GF_CONV_KPT)              // threads along k
+#define GF_CONV_THREADS (GF_CONV_KT * GF_CONV_SEG) // 256
+// resolution values are stored swizzled (one 8-byte slot skipped every 16) so that the window loads of the GF_CONV_KT threads of a
+// group, GF_CONV_KPT doubles apart, fall into different banks
+__device__ __forceinline__ int gf_conv_sw(int q) { return q + (q >> 4); }
+__global__ void __launch_bounds__(GF_CONV_THREADS)
     k_conv_table(const double *__restrict__ model, const double *__restrict__ resol, int n_model, int n_resol,
                  int offset, int kmin, int nk, double *table) {
+    constexpr int NRES = GF_CONV_TILE + 64;
     __shared__ double sm_model[GF_CONV_TILE];
-    __shared__ double sm_res[GF_CONV_TILE + 64];
-    const int tl = threadIdx.x, t = blockIdx.x * 64 + tl;
+    __shared__ double sm_res[NRES + NRES / 16 + 1];
+    __shared__ double sm_part[GF_CONV_SEG][64];
+    const int kt = threadIdx.x % GF_CONV_KT, seg = threadIdx.x / GF_CONV_KT;
     const int k0 = kmin + blockIdx.x * 64;
-    double ret = 0;
+    constexpr int PER = GF_CONV_TILE / GF_CONV_SEG; // terms of a tile per group
+    static_assert(GF_CONV_TILE % GF_CONV_SEG == 0 && 64 % GF_CONV_KPT == 0, "tile must split evenly");
+    double acc[GF_CONV_KPT];
+#pragma unroll
+    for(int j = 0; j < GF_CONV_KPT; ++j) acc[j] = 0;
     for(int i0 = 0; i0 < n_model; i0 += GF_CONV_TILE) {
         const int n = min(GF_CONV_TILE, n_model - i0);
         const int jmin = i0 + offset - (k0 + 63); // resolution index met by (i0, the block's last k)
-        __syncthreads();
-        for(int q = tl; q < GF_CONV_TILE; q += 64) sm_model[q] = q < n ? __ldg(model + i0 + q) : 0.0;
-        for(int q = tl; q < GF_CONV_TILE + 64; q += 64) {
-            int jj = jmin + q;
-            sm_res[q] = (jj >= 0 && jj < n_resol) ? __ldg(resol + jj) : 0.0;
+        // this round's values into registers first (every load in flight at once), then into shared memory
+        constexpr int NM = (GF_CONV_TILE + GF_CONV_THREADS - 1) / GF_CONV_THREADS, NR = (NRES + GF_CONV_THREADS - 1) / GF_CONV_THREADS;
+        double vm[NM], vr[NR];
+#pragma unroll
+        for(int u = 0; u < NM; ++u) {
+            const int q = threadIdx.x + u * GF_CONV_THREADS;
+            vm[u] = q < n ? __ldg(model + i0 + q) : 0.0; // zero-padded: the terms past n add exact zeros
+        }
+#pragma unroll
+        for(int u = 0; u < NR; ++u) {
+            const int q = threadIdx.x + u * GF_CONV_THREADS, jj = jmin + q;
+            vr[u] = (q < NRES && jj >= 0 && jj < n_resol) ? __ldg(resol + jj) : 0.0;
         }
         __syncthreads();
-        const double *r = sm_res + (63 - tl);
+#pragma unroll
+        for(int u = 0; u < NM; ++u) {
+            const int q = threadIdx.x + u * GF_CONV_THREADS;
+            if(q < GF_CONV_TILE) sm_model[q] = vm[u];
+        }
+#pragma unroll
+        for(int u = 0; u < NR; ++u) {
+            const int q = threadIdx.x + u * GF_CONV_THREADS;
+            if(q < NRES) sm_res[gf_conv_sw(q)] = vr[u];
+        }
+        __syncthreads();
+        // entry k = k0 + KPT kt + j meets model[ii] with sm_res[(63 - KPT kt - j) + ii]: a window of KPT values that slides by one
+        // per term. w[j] holds sm_res[base - j + ii].
+        const double *m = sm_model + seg * PER;
+        const int base = 63 - GF_CONV_KPT * kt + seg * PER;
+        double w[GF_CONV_KPT];
+#pragma unroll
+        for(int j = 0; j < GF_CONV_KPT; ++j) w[j] = sm_res[gf_conv_sw(base - j)];
 #pragma unroll 8
-        for(int ii = 0; ii < n; ++ii) ret += sm_model[ii] * r[ii];
+        for(int ii = 0; ii < PER; ++ii) {
+            const double mv = m[ii];
+#pragma unroll
+            for(int j = 0; j < GF_CONV_KPT; ++j) acc[j] += mv * w[j];
+#pragma unroll
+            for(int j = GF_CONV_KPT - 1; j > 0; --j) w[j] = w[j - 1];
+            w[0] = sm_res[gf_conv_sw(base + ii + 1)];
+        }
     }
-    if(t < nk) table[t] = ret;
+#pragma unroll
+    for(int j = 0; j < GF_CONV_KPT; ++j) sm_part[seg][GF_CONV_KPT * kt + j] = acc[j];
+    __syncthreads();
+    if(threadIdx.x < 64 && blockIdx.x * 64 + (int)threadIdx.x < nk) {
+        double sum = sm_part[0][threadIdx.x];
+#pragma unroll
+        for(int g = 1; g < GF_CONV_SEG; ++g) sum += sm_part[g][threadIdx.x];
+        table[blockIdx.x * 64 + threadIdx.x] = sum;
+    }
 }
 
 static int conv_check(gf_ctx *c, int node, gf_conv_state **out, bool create) {
@@ -156,7 +218,7 @@ extern "C" int gf_conv_fill(gf_ctx *c, int node, int fill_model, int fill_resol)
             s->d_resol);
         c->launches++;
     }
-    k_conv_table<<<(s->nk + 63) / 64, 64, 0, c->stream>>>(s->d_model, s->d_resol, s->n_model, s->n_resol, s->offset,
+    k_conv_table<<<(s->nk + 63) / 64, GF_CONV_THREADS, 0, c->stream>>>(s->d_model, s->d_resol, s->n_model, s->n_resol, s->offset,
                                                          s->kmin, s->nk, s->d_table);
     c->launches++;
     GF_CUDA(cudaGetLastError());
