@@ -727,8 +727,13 @@ __device__ inline double gf_eval_tree(const gf_sprog &P, const gf_dev_view &V, i
             const int32_t *ob = P.ints + nd.obs_off;
             double x0 = evt(ob[0]);
             double lo = c[0], step = c[2];
-            double lbo = lo / step;
-            lbo -= floor(lbo);
+            double lbo;
+            if(nd.ncon >= 4)
+                lbo = c[3]; // the host class stores lo / step - floor(lo / step): the same two operations, once instead of per event
+            else {
+                lbo = lo / step;
+                lbo -= floor(lbo);
+            }
             int k = (int)floor(x0 / step - lbo);
             const double *tab = static_cast<const double *>(P.aux[in[0]]);
             long pk = P.aux_ld[in[0]];

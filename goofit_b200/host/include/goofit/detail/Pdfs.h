@@ -216,6 +216,7 @@ class ConvolutionPdf : public CombinePdf { // combine/ConvolutionPdf.h
   protected:
 
   private:
+    void setLowerBoundOffset();
     GooPdf *model;
     GooPdf *resolution;
     bool workspacesFilled{false};

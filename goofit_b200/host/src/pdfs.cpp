@@ -541,17 +541,25 @@ ConvolutionPdf::ConvolutionPdf(std::string n, Observable x, GooPdf *m, GooPdf *r
     registerConstant(-10);
     registerConstant(10);
     registerConstant(0.01);
+    registerConstant(0); // lower-bound offset in units of the step (set below): event-independent, kept out of the per-event path
+    setLowerBoundOffset();
     registerFunction("ptr_to_ConvolvePdfs", GF_OP_CONVOLVE);
 }
 void ConvolutionPdf::setIntegrationConstants(fptype lo, fptype hi, fptype step) {
     constantsList[0] = lo;
     constantsList[1] = hi;
     constantsList[2] = step;
+    setLowerBoundOffset();
     workspacesFilled = false;
     if(nodeIdx >= 0) { // already flattened: refresh the record and the device workspaces
         Engine &E = Engine::get();
         if(E.root) E.build(E.root);
     }
+}
+void ConvolutionPdf::setLowerBoundOffset() { // ConvolutionPdf.cu:44-46, the part that does not depend on the event
+    fptype lbo = constantsList[0] / constantsList[2];
+    lbo -= std::floor(lbo);
+    constantsList[3] = lbo;
 }
 void ConvolutionPdf::emitAux(detail::ProgramBuilder &B) {
     model->emitAux(B);
