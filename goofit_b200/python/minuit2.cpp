@@ -13,6 +13,7 @@
 #include <Minuit2/MinuitParameter.h>
 #include <Minuit2/MnApplication.h>
 #include <Minuit2/MnMigrad.h>
+#include <Minuit2/MinosError.h>
 #include <Minuit2/MnMinos.h>
 #include <Minuit2/MnPrint.h>
 #include <Minuit2/MnScan.h>
@@ -122,11 +123,28 @@ void init_minuit2(py::module &parent) {
     py::class_<MnScan, MnApplication>(m, "MnScan")
         .def(py::init([](const FCNBase &fcn, const MnUserParameters &par, unsigned int stra) { return new MnScan(fcn, par, MnStrategy(stra)); }), "fcn"_a,
              "par"_a, "stra"_a = 1, py::keep_alive<1, 2>());
+    py::class_<MinosError>(m, "MinosError") // python/Minuit2/MnMinos.cpp:17-35
+        .def_property_readonly("number", &MinosError::Parameter)
+        .def_property_readonly("lower", &MinosError::Lower)
+        .def_property_readonly("upper", &MinosError::Upper)
+        .def_property_readonly("is_valid", &MinosError::IsValid)
+        .def_property_readonly("lower_valid", &MinosError::LowerValid)
+        .def_property_readonly("upper_valid", &MinosError::UpperValid)
+        .def_property_readonly("at_lower_limit", &MinosError::AtLowerLimit)
+        .def_property_readonly("at_upper_limit", &MinosError::AtUpperLimit)
+        .def_property_readonly("at_lower_max_fcn", &MinosError::AtLowerMaxFcn)
+        .def_property_readonly("at_upper_max_fcn", &MinosError::AtUpperMaxFcn)
+        .def_property_readonly("lower_new_min", &MinosError::LowerNewMin)
+        .def_property_readonly("upper_new_min", &MinosError::UpperNewMin)
+        .def_property_readonly("nfcn", &MinosError::NFcn)
+        .def_property_readonly("min", &MinosError::Min);
     py::class_<MnMinos>(m, "MnMinos")
         .def(py::init([](const FCNBase &fcn, const FunctionMinimum &min, unsigned int stra) { return new MnMinos(fcn, min, MnStrategy(stra)); }), "fcn"_a,
              "min"_a, "stra"_a = 1, py::keep_alive<1, 2>(), py::keep_alive<1, 3>())
         .def("__call__", [](const MnMinos &self, unsigned int n, unsigned int maxcalls, double toler) { return self(n, maxcalls, toler); }, "n"_a,
-             "maxcalls"_a = 0, "toler"_a = 0.1, "the (lower, upper) MINOS errors of parameter n");
+             "maxcalls"_a = 0, "toler"_a = 0.1, "the (lower, upper) MINOS errors of parameter n")
+        .def("Minos", [](const MnMinos &self, unsigned int n, unsigned int maxcalls, double toler) { return self.Minos(n, maxcalls, toler); }, "n"_a,
+             "maxcalls"_a = 0, "toler"_a = 0.1, "the full MinosError of parameter n");
     py::class_<MnPrint> m_ls(m, "m_ls");
     m_ls.def_static("GlobalLevel", &MnPrint::GlobalLevel);
     m_ls.def_static("SetGlobalLevel", &MnPrint::SetGlobalLevel);

@@ -462,4 +462,5 @@ PYBIND11_MODULE(_goofit, m) {
         .def("lastFitCalls", &FitManagerMinuit2::lastFitCalls)
         .def("__int__", &FitManagerMinuit2::operator int)
         .def("__bool__", &FitManagerMinuit2::operator bool);
+    m.attr("FitManagerMinuit2") = m.attr("FitManager"); // the C++ class name; `FitManager` is what upstream's module exposes
 }

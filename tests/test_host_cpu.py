@@ -437,6 +437,31 @@ def test_reference_examples_compile_unmodified():
         assert out.returncode == 0, src + "\n" + out.stderr[-3000:]
 
 
+def test_minuit2_minos_error_binding():
+    """goofit.minuit2.MnMinos / MinosError (python/Minuit2/MnMinos.cpp of the reference) on a Python FCN: a parabola's MINOS errors
+    are its sigmas."""
+    m2 = gf.minuit2
+
+    class F(m2.FCNBase):
+        def Up(self):
+            return 0.5
+
+        def __call__(self, v):
+            return 0.5 * ((v[0] - 1.0) / 0.3) ** 2 + 0.5 * ((v[1] + 2) / 0.1) ** 2
+
+    f = F()
+    p = m2.MnUserParameters()
+    p.Add("a", 0.0, 0.1)
+    p.Add("b", 0.0, 0.1)
+    fmin = m2.MnMigrad(f, p)()
+    minos = m2.MnMinos(f, fmin)
+    lo, hi = minos(0)
+    assert abs(lo + 0.3) < 1e-6 and abs(hi - 0.3) < 1e-6
+    e = minos.Minos(1)
+    assert e.is_valid and e.number == 1 and abs(e.upper - 0.1) < 1e-6 and abs(e.lower + 0.1) < 1e-6
+    assert gf.FitManagerMinuit2 is gf.FitManager
+
+
 def test_goofit_package_alias():
     """`from goofit import *` / `import goofit.minuit2`: the reference's Python package name resolves to this implementation."""
     import goofit
