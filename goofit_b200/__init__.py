@@ -21,4 +21,25 @@ except ImportError as e:  # pragma: no cover - build missing
         "goofit_b200: the native extension is not built (run `make` or `python -c 'import __graft_entry__ as g; g.build()'`): %s" % e
     )
 
+
+
+def _help(cls):
+    """Upstream's PDFs carry a static help() that prints their documentation; here it prints the class's docstring and the
+    signatures of its constructors."""
+    text = (cls.__doc__ or cls.__name__).strip() + "\n" + (cls.__init__.__doc__ or "")
+    print(text)
+    return text
+
+
+for _name in dir(_goofit):
+    _cls = getattr(_goofit, _name)
+    if isinstance(_cls, type) and issubclass(_cls, _goofit.PdfBase) and "help" not in _cls.__dict__:
+        _cls.help = classmethod(_help)
+for _sub in (Resonances, Lineshapes):
+    for _name in dir(_sub):
+        _cls = getattr(_sub, _name)
+        if isinstance(_cls, type) and issubclass(_cls, _goofit.PdfBase) and "help" not in _cls.__dict__:
+            _cls.help = classmethod(_help)
+del _name, _cls, _sub
+
 from . import capi  # noqa: E402,F401

@@ -122,7 +122,8 @@ void init_minuit2(py::module &parent) {
              "par"_a, "stra"_a = 1, py::keep_alive<1, 2>());
     py::class_<MnScan, MnApplication>(m, "MnScan")
         .def(py::init([](const FCNBase &fcn, const MnUserParameters &par, unsigned int stra) { return new MnScan(fcn, par, MnStrategy(stra)); }), "fcn"_a,
-             "par"_a, "stra"_a = 1, py::keep_alive<1, 2>());
+             "par"_a, "stra"_a = 1, py::keep_alive<1, 2>())
+        .def("Scan", &MnScan::Scan, "Scan parameter.", "par"_a, "maxsteps"_a = 41, "low"_a = 0, "high"_a = 0);
     py::class_<MinosError>(m, "MinosError") // python/Minuit2/MnMinos.cpp:17-35
         .def_property_readonly("number", &MinosError::Parameter)
         .def_property_readonly("lower", &MinosError::Lower)

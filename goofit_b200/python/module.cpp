@@ -107,6 +107,8 @@ PYBIND11_MODULE(_goofit, m) {
         .def_property("error", &Variable::getError, &Variable::setError)
         .def_property("fixed", &Variable::IsFixed, &Variable::setFixed)
         .def_property("fitter_index", &Variable::getFitterIndex, &Variable::setFitterIndex)
+        .def_property_readonly("fitterIndex", &Variable::getFitterIndex)
+        .def_property("blind", nullptr, &Variable::setBlind)
         .def_property("changed", &Variable::getChanged, &Variable::setChanged)
         .def("getError", &Variable::getError)
         .def("setFixed", &Variable::setFixed)
@@ -193,7 +195,20 @@ PYBIND11_MODULE(_goofit, m) {
         .def("getBinSize", &BinnedDataSet::getBinSize, "ivar"_a)
         .def("getBinVolume", &BinnedDataSet::getBinVolume, "bin"_a)
         .def("getNumBins", &BinnedDataSet::getNumBins)
-        .def("getNumWeightedEvents", &BinnedDataSet::getNumWeightedEvents);
+        .def("getNumWeightedEvents", &BinnedDataSet::getNumWeightedEvents)
+        // python/goofit/BinnedDataSet.cpp:25-34
+        .def_property_readonly("bin_center", [](const BinnedDataSet &d) {
+            std::vector<std::vector<fptype>> c(d.numVariables());
+            for(size_t v = 0; v < c.size(); v++)
+                for(size_t b = 0; b < d.getNumBins(); b++) c[v].push_back(d.getBinCenter(v, b));
+            return c;
+        })
+        .def_property_readonly("bin_number", &BinnedDataSet::getBinNumber)
+        .def_property_readonly("bin_volume", [](const BinnedDataSet &d) { std::vector<fptype> v; for(size_t b = 0; b < d.getNumBins(); b++) v.push_back(d.getBinVolume(b)); return v; })
+        .def_property_readonly("bin_error", [](const BinnedDataSet &d) { std::vector<fptype> v; for(size_t b = 0; b < d.getNumBins(); b++) v.push_back(d.getBinError(b)); return v; })
+        .def_property_readonly("num_bins", &BinnedDataSet::getNumBins)
+        .def_property_readonly("num_events", &BinnedDataSet::getNumEvents)
+        .def_property_readonly("diminsions", &BinnedDataSet::getDiminsions);
 
     // ---- fit control ----
     py::enum_<EvalFunc>(m, "EvalFunc")
@@ -427,7 +442,21 @@ PYBIND11_MODULE(_goofit, m) {
         .def("getXval", &DalitzPlotter::getXval)
         .def("getYval", &DalitzPlotter::getYval)
         .def("getZval", &DalitzPlotter::getZval)
-        .def("getVal", &DalitzPlotter::getVal, "event"_a, "num"_a = 0);
+        .def("getVal", &DalitzPlotter::getVal, "event"_a, "num"_a = 0)
+        .def("getDataSet", &DalitzPlotter::getDataSet, py::return_value_policy::reference_internal)
+        .def("getM12", &DalitzPlotter::getM12)
+        .def("getM13", &DalitzPlotter::getM13)
+        .def("make2D", [](const DalitzPlotter &self) { // python/PDFs/physics/DalitzPlotter.cpp:31-49: bins without an evaluation stay 0
+                 const size_t n12 = self.getM12().getNumBins(), n13 = self.getM13().getNumBins();
+                 py::array_t<fptype> result({n12, n13});
+                 std::fill(result.mutable_data(), result.mutable_data() + n12 * n13, 0.0);
+                 for(size_t j = 0; j < self.getNumEvents(); ++j) result.mutable_at(self.getX(j), self.getY(j)) = self.getVal(j);
+                 return result;
+             }, "Make a 2D array for plotting")
+        .def("getExtent", [](const DalitzPlotter &self) {
+                 return std::vector<double>{self.getM12().getLowerLimit(), self.getM12().getUpperLimit(), self.getM13().getLowerLimit(),
+                                            self.getM13().getUpperLimit()};
+             }, "Get the extents for plotting");
 
     init_physics4(m);
 
@@ -441,7 +470,10 @@ PYBIND11_MODULE(_goofit, m) {
         .def("make_minuit_vector", &Params::make_minuit_vector)
         .def("from_minuit_vector", &Params::from_minuit_vector, "values"_a, "force_changed"_a = false)
         .def("set_record", &Params::set_record, "do_record"_a = true)
-        .def("get_recorded", &Params::get_recorded);
+        .def("get_recorded", &Params::get_recorded)
+        .def("SetGooFitParams", &Params::SetGooFitParams, "input"_a)
+        .def_property("record", nullptr, [](Params &p, bool on) { p.set_record(on); })
+        .def_property_readonly("recorded", &Params::get_recorded);
     py::class_<FCN, Minuit2::FCNBase>(m, "FCN")
         .def(py::init<Params &>(), "params"_a, py::keep_alive<1, 2>())
         .def("__call__", (double (FCN::*)(const std::vector<double> &) const) & FCN::operator())
@@ -461,6 +493,12 @@ PYBIND11_MODULE(_goofit, m) {
         .def("lastFitSeconds", &FitManagerMinuit2::lastFitSeconds)
         .def("lastFitCalls", &FitManagerMinuit2::lastFitCalls)
         .def("__int__", &FitManagerMinuit2::operator int)
-        .def("__bool__", &FitManagerMinuit2::operator bool);
+        .def("__bool__", &FitManagerMinuit2::operator bool)
+        .def("__nonzero__", &FitManagerMinuit2::operator bool)
+        .def("getMnScan", &FitManagerMinuit2::getMnScan)
+        .def_property("verbosity", &FitManagerMinuit2::getVerbosity, &FitManagerMinuit2::setVerbosity)
+        .def_property("max_calls", nullptr, &FitManagerMinuit2::setMaxCalls)
+        .def_property_readonly("params", &FitManagerMinuit2::getParams, py::return_value_policy::reference_internal)
+        .def_property_readonly("fcn", &FitManagerMinuit2::getFCN, py::return_value_policy::reference_internal);
     m.attr("FitManagerMinuit2") = m.attr("FitManager"); // the C++ class name; `FitManager` is what upstream's module exposes
 }

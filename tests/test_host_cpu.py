@@ -497,3 +497,38 @@ def test_functor_writer_round_trip(tmp_path):
                          capture_output=True, text=True)
     assert out.returncode == 0, out.stderr[-2000:]
     assert subprocess.run([str(exe2)]).returncode == 0
+
+
+def test_python_api_names_cover_the_reference_bindings():
+    """Every method, property and static the reference's pybind11 sources (python/goofit, python/PDFs, python/Minuit2) define on a
+    class that exists here is present on this module's class of the same name (parsed from the reference checkout; names only)."""
+    import glob
+    import re
+    ref = "/root/reference/python"
+    if not os.path.isdir(ref):
+        pytest.skip("needs the reference checkout")
+    defined = {}
+    for path in glob.glob(os.path.join(ref, "**", "*.cpp"), recursive=True):
+        txt = open(path).read()
+        for m in re.finditer(r'py::class_<([^>]+)>\s*\(\s*\w+\s*,\s*"(\w+)"', txt):
+            start = m.end()
+            nxt = re.search(r"py::class_<", txt[start:])
+            body = txt[start:start + (nxt.start() if nxt else len(txt))]
+            names = set(re.findall(r'\.def(?:_static|_property(?:_readonly)?|_readwrite|_readonly)?\(\s*"(\w+)"', body))
+            names |= set(re.findall(r"ADD_PROP(?:_RO|_WO)?\(\s*(\w+)", body))
+            defined.setdefault(m.group(2), set()).update(names)
+    assert len(defined) > 60
+    spaces = [gf, gf.Resonances, gf.Lineshapes, gf.minuit2]
+    checked, missing = 0, {}
+    for name, names in defined.items():
+        cls = next((getattr(s, name) for s in spaces if hasattr(s, name)), None)
+        if cls is None:
+            continue
+        checked += 1
+        lack = sorted(n for n in names if n != "__init__" and not hasattr(cls, n))
+        if lack:
+            missing[name] = lack
+    assert checked > 60 and not missing, missing
+    not_built = sorted(n for n in defined if not any(hasattr(s, n) for s in spaces))
+    # the classes this repo deliberately leaves out (DESIGN.md section 7) and two binding-only helpers
+    assert set(not_built) <= {"Amp3Body_IS", "AmpNBodyBase", "HelpPrinter", "InterHistPdf", "ThreeGaussResolutionExt", "ThreeGaussResolutionSplice"}, not_built
