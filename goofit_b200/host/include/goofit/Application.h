@@ -11,9 +11,23 @@
 #include <string>
 
 #include <goofit/Color.h>
+#include <goofit/Version.h>
 #include <goofit/detail/Core.h>
 
 namespace GooFit {
+/// Application.h:37-46 of the reference: what the start-up banner and `--info` print
+inline std::string goofit_info_version() { return std::string("GooFit (B200-native likelihood engine) ") + GOOFIT_VERSION; }
+inline std::string goofit_info_device(int gpuDev_) {
+    int sm = 0;
+    size_t free_b = 0, total_b = 0;
+    detail::Engine &E = detail::Engine::get();
+    if(gpuDev_ >= 0) E.setDevice(gpuDev_);
+    if(gf_device_info(E.ctx(), &sm, &free_b, &total_b) != 0) return "no CUDA device";
+    return "CUDA device " + std::to_string(gpuDev_ < 0 ? 0 : gpuDev_) + ": " + std::to_string(sm) + " SMs, " + std::to_string(total_b >> 30) + " GiB ("
+           + std::to_string(free_b >> 30) + " GiB free), sm_100a kernels";
+}
+inline void print_splash() { std::cout << goofit_info_version() << std::endl; }
+inline void print_goofit_info(int gpuDev_ = 0) { std::cout << goofit_info_version() << "\n" << goofit_info_device(gpuDev_) << std::endl; }
 class Application {
   public:
     Application(std::string description, int argc, char **argv)
@@ -44,6 +58,13 @@ class Application {
         return e.get_exit_code();
     }
     bool quiet() const { return quiet_; }
+    int get_device() const { return gpuDev_ < 0 ? 0 : gpuDev_; }
+    /// make the selected GPU current again (Application.cpp: cudaSetDevice; here the engine owns the context of its device)
+    void set_device() const {
+        if(gpuDev_ >= 0) detail::Engine::get().setDevice(gpuDev_);
+    }
+    /// upstream enables SIGFPE traps on the host; kept as a no-op: the device code reports through its status, never through signals
+    static void set_floating_exceptions() {}
     /// where an input file of an example lives (Application.cpp:295-333): the working directory, the directory of the
     /// executable, then `base` under GOOFIT_SOURCE_DIR (an environment variable or compile-time macro here)
     std::string get_filename(const std::string &input_str, std::string base = "") const {
