@@ -87,10 +87,18 @@ examples/bin/reftests/%: build/reftests/%.o build/reftests/catch_main.o $(LIBDIR
 	$(CXX) $< build/reftests/catch_main.o $(LDSTD) -L$(LIBDIR) -lgoofit_host -lgoofit_b200 -lMinuit2 -Wl,-rpath,'$$ORIGIN/../../../../goofit_b200/lib' -o $@
 .PRECIOUS: build/reftests/%.o
 REFEX    += $(if $(wildcard $(REF)/tests/catch_main.cpp),$(RT_BIN),)
+# The reference's ROOT-using examples, unmodified as well: GOOFIT_ROOT_FOUND=1 switches on the header-only ROOT conveniences of the
+# drop-in headers (plotToROOT, make2D, setROOTStyle) and tests/ref_root stands in for ROOT itself (histograms in memory, canvases that
+# draw nothing): neither machine has ROOT or a graphics stack. A user with ROOT passes its include path and libraries instead.
+REFEX_ROOT := $(if $(wildcard $(REF)/examples/dalitz/dalitz.cpp),examples/bin/ref_dalitz examples/bin/ref_addition examples/bin/ref_simpleFit \
+              examples/bin/ref_convolution examples/bin/ref_2d_plot examples/bin/ref_zachFit,)
+$(REFEX_ROOT): REFEX_EXTRA := -DGOOFIT_ROOT_FOUND=1 -Itests/ref_root -I$(REF)/extern/fmt/include -DFMT_HEADER_ONLY -Wno-sign-compare -Wno-unused-variable -Wno-unused-but-set-variable
+$(REFEX_ROOT): $(wildcard tests/ref_root/*.h)
+REFEX    += $(REFEX_ROOT)
 examples: examples/bin/exponential $(REFEX)
-examples/bin/ref_%: $(REF)/examples/%/$$*.cpp $(LIBDIR)/libgoofit_host.so
+examples/bin/ref_%: $(REF)/examples/%/$$*.cpp $(LIBDIR)/libgoofit_host.so $(HOST)/include/goofit/Application.h
 	@mkdir -p examples/bin
-	$(CXX) $(HFLAGS) -I$(REF)/extern/CLI11/include $< $(LDSTD) -L$(LIBDIR) -lgoofit_host -lgoofit_b200 -lMinuit2 -Wl,-rpath,'$$ORIGIN/../../goofit_b200/lib' -o $@
+	$(CXX) $(HFLAGS) $(REFEX_EXTRA) -I$(REF)/extern/CLI11/include $< $(LDSTD) -L$(LIBDIR) -lgoofit_host -lgoofit_b200 -lMinuit2 -Wl,-rpath,'$$ORIGIN/../../goofit_b200/lib' -o $@
 examples/bin/%: examples/%.cpp $(LIBDIR)/libgoofit_host.so
 	@mkdir -p examples/bin
 	$(CXX) $(HFLAGS) $< $(LDSTD) -L$(LIBDIR) -lgoofit_host -lgoofit_b200 -lMinuit2 -Wl,-rpath,'$$ORIGIN/../../goofit_b200/lib' -o $@

@@ -18,6 +18,17 @@
 #define GOOFIT_HOST "CPP"
 #define GOOFIT_ARCH_FLAGS "sm_100a"
 
+// ROOT is not part of this build; a user who has it compiles with -DGOOFIT_ROOT_FOUND=1 (upstream's configure-time switch, Version.h.in:18;
+// its CMake also defines ROOT_FOUND) and gets the header-only ROOT conveniences: GooPdf::plotToROOT, DalitzPlotter::make2D, setROOTStyle
+#ifndef GOOFIT_ROOT_FOUND
+#ifdef ROOT_FOUND
+#define GOOFIT_ROOT_FOUND 1
+#else
 #define GOOFIT_ROOT_FOUND 0
+#endif
+#endif
+#if GOOFIT_ROOT_FOUND && !defined(ROOT_FOUND)
+#define ROOT_FOUND 1
+#endif
 #define GOOFIT_SPLASH 1
 #define GOOFIT_KMATRIX 1

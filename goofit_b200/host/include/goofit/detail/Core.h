@@ -21,6 +21,10 @@
 #include <vector>
 
 #include "goofit_b200.h"
+#include <goofit/Version.h>
+#ifdef ROOT_FOUND
+#include <TH1D.h>
+#endif
 
 #ifndef __host__
 #define __host__
@@ -606,6 +610,19 @@ class GooPdf : public PdfBase {
     std::vector<fptype> evaluate_with_metric() const;
     /// sum over events of the metric (GooPdf.cu:45-78), all-reduced over shards
     double reduce_with_metric() const;
+#ifdef ROOT_FOUND
+    /// GooPdf.cpp:126-144 of the reference: the PDF over `var` as a ROOT histogram, normalised to normFactor (header-only here: the
+    /// library itself is built without ROOT). The caller owns the histogram.
+    TH1D *plotToROOT(Observable var, double normFactor = 1, std::string name = "") {
+        if(name.empty()) name = getName() + "_hist";
+        auto *ret = new TH1D(name.c_str(), "", (int)var.getNumBins(), var.getLowerLimit(), var.getUpperLimit());
+        std::vector<fptype> binValues = evaluateAtPoints(var);
+        double pdf_int = 0;
+        for(size_t i = 0; i < var.getNumBins(); ++i) pdf_int += binValues[i];
+        for(size_t i = 0; i < var.getNumBins(); ++i) ret->SetBinContent((int)i + 1, binValues[i] * normFactor / pdf_int / var.getBinSize());
+        return ret;
+    }
+#endif
 
   protected:
     int metric() const;

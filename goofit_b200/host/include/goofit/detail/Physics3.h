@@ -3,6 +3,9 @@
 //  include/goofit/PDFs/physics/resonances/{Resonance,RBW,GS,NonRes,Gauss}.h).
 #pragma once
 #include <goofit/detail/Pdfs.h>
+#if GOOFIT_ROOT_FOUND
+#include <TH2F.h>
+#endif
 
 namespace GooFit {
 
@@ -256,6 +259,15 @@ class DalitzPlotter {
     UnbinnedDataSet *getDataSet() { return &data; }
     const Observable &getM12() const { return m12; }
     const Observable &getM13() const { return m13; }
+#if GOOFIT_ROOT_FOUND
+    /// DalitzPlotter.h:116-137 of the reference: the evaluated grid as a TH2F (bins outside the Dalitz plot stay empty); the caller owns it
+    TH2F *make2D(std::string name = "dalitzplot", std::string title = "") {
+        auto *dalitzplot = new TH2F(name.c_str(), title.c_str(), (int)m12.getNumBins(), m12.getLowerLimit(), m12.getUpperLimit(),
+                                    (int)m13.getNumBins(), m13.getLowerLimit(), m13.getUpperLimit());
+        for(size_t j = 0; j < getNumEvents(); ++j) dalitzplot->SetBinContent(1 + (int)getX(j), 1 + (int)getY(j), getVal(j));
+        return dalitzplot;
+    }
+#endif
 
   private:
     std::vector<size_t> xbins, ybins;

@@ -1,0 +1,7 @@
+// tests/ref_root stand-in (see TH1.h)
+#pragma once
+#include "TH1.h"
+class TH1F : public TH1 {
+  public:
+    using TH1::TH1;
+};

@@ -30,3 +30,41 @@ def test_reference_catch_test(name):
     m = re.search(r"(\d+) test cases, (\d+) assertions, (\d+) failed", r.stderr)
     assert m, tail
     assert int(m.group(1)) >= 1 and int(m.group(2)) >= 1 and int(m.group(3)) == 0, tail
+
+
+# ---- the reference's ROOT-using examples, unmodified ------------------------------------------------------------------------------
+# examples/{dalitz,addition,simpleFit,convolution,2d_plot,zachFit} of the reference checkout, compiled where they lie with
+# GOOFIT_ROOT_FOUND=1 against this repo's headers (Application as a CLI::App, GooPdf::plotToROOT, DalitzPlotter::make2D, setROOTStyle)
+# and tests/ref_root, a headless stand-in for ROOT (`make examples`). Each program's own exit status is the check: they return the
+# Minuit status of their fit (FitManager converts to it), dalitz.cpp 7 on a run-time error.
+EXBIN = os.path.join(ROOT, "examples", "bin")
+ROOT_EXAMPLES = {
+    "ref_dalitz": ["--make-toy"],  # 10^6 events drawn from the 16-resonance model by DalitzPlotter::fillDataSetMC, then the 30-parameter fit
+    "ref_addition": [],
+    "ref_simpleFit": [],
+    "ref_convolution": [],
+    "ref_2d_plot": [],
+}
+
+
+@pytest.mark.parametrize("name", sorted(ROOT_EXAMPLES))
+def test_reference_root_example_unmodified(name, tmp_path):
+    exe = os.path.join(EXBIN, name)
+    if not os.path.exists(exe):
+        pytest.skip("examples/bin/%s not built (needs the reference checkout at build time)" % name)
+    r = subprocess.run([exe] + ROOT_EXAMPLES[name], capture_output=True, text=True, timeout=900, cwd=str(tmp_path))
+    assert r.returncode == 0, r.stdout[-2500:] + "\n" + r.stderr[-2500:]
+
+
+def test_reference_application_options(tmp_path):
+    """GooFit::Application as upstream's CLI::App (include/goofit/Application.h:48-93): --help lists the example's own options and the
+    GooFit group and exits 0; an unknown option is a parse error with CLI11's exit code; --info-only prints the device and exits 0."""
+    exe = os.path.join(EXBIN, "ref_dalitz")
+    if not os.path.exists(exe):
+        pytest.skip("examples/bin/ref_dalitz not built")
+    r = subprocess.run([exe, "--help"], capture_output=True, text=True, timeout=120, cwd=str(tmp_path))
+    assert r.returncode == 0 and "--make-toy" in r.stdout and "--gpu-dev" in r.stdout and "--config" in r.stdout, r.stdout + r.stderr
+    r = subprocess.run([exe, "--no-such-option"], capture_output=True, text=True, timeout=120, cwd=str(tmp_path))
+    assert r.returncode != 0, r.stdout + r.stderr
+    r = subprocess.run([exe, "--info-only"], capture_output=True, text=True, timeout=120, cwd=str(tmp_path))
+    assert r.returncode == 0 and "SMs" in r.stdout, r.stdout + r.stderr
