@@ -521,6 +521,13 @@ def test_functor_writer_round_trip(tmp_path):
                          capture_output=True, text=True)
     assert out.returncode == 0, out.stderr[-2000:]
     assert subprocess.run([str(exe2)]).returncode == 0
+    # goofit/utilities/Uncertain.h, goofit/detail/Complex.h (the _i literals), goofit/detail/Abort.h
+    exe3 = tmp_path / "sh"
+    cmd3 = [c if not c.endswith("functor_writer.cpp") else os.path.join(ROOT, "tests", "cpp", "small_headers.cpp") for c in cmd[:-1]] + [str(exe3)]
+    out = subprocess.run(cmd3, capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr[-2000:]
+    run = subprocess.run([str(exe3)], capture_output=True, text=True)
+    assert run.returncode == 0, (run.returncode, run.stderr)
 
 
 def test_python_api_names_cover_the_reference_bindings():
