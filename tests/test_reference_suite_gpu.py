@@ -56,6 +56,20 @@ def test_reference_root_example_unmodified(name, tmp_path):
     assert r.returncode == 0, r.stdout[-2500:] + "\n" + r.stderr[-2500:]
 
 
+def test_reference_zachfit_example_unmodified(tmp_path):
+    """examples/zachFit/zachFit.cpp in its default mode (unbinned; resolution-sample fit, then the data fit with the three
+    convolutions): upstream downloads the two BaBar text files at configure time, so tools/make_zachfit_toy.py writes synthetic ones of
+    the same format into dataFiles/ of the working directory (Application::get_filename finds them there)."""
+    import sys
+    exe = os.path.join(EXBIN, "ref_zachFit")
+    if not os.path.exists(exe):
+        pytest.skip("examples/bin/ref_zachFit not built (needs the reference checkout at build time)")
+    subprocess.run([sys.executable, os.path.join(ROOT, "tools", "make_zachfit_toy.py"), str(tmp_path), "100000"], check=True, timeout=120)
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=900, cwd=str(tmp_path))
+    assert r.returncode == 0, r.stdout[-2500:] + "\n" + r.stderr[-2500:]
+    assert "kpi_rd_width_bw" in r.stdout and "The minimization took" in r.stdout, r.stdout[-2500:]
+
+
 def test_reference_application_options(tmp_path):
     """GooFit::Application as upstream's CLI::App (include/goofit/Application.h:48-93): --help lists the example's own options and the
     GooFit group and exits 0; an unknown option is a parse error with CLI11's exit code; --info-only prints the device and exits 0."""
