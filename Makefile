@@ -91,9 +91,15 @@ REFEX    += $(if $(wildcard $(REF)/tests/catch_main.cpp),$(RT_BIN),)
 # drop-in headers (plotToROOT, make2D, setROOTStyle) and tests/ref_root stands in for ROOT itself (histograms in memory, canvases that
 # draw nothing): neither machine has ROOT or a graphics stack. A user with ROOT passes its include path and libraries instead.
 REFEX_ROOT := $(if $(wildcard $(REF)/examples/dalitz/dalitz.cpp),examples/bin/ref_dalitz examples/bin/ref_addition examples/bin/ref_simpleFit \
-              examples/bin/ref_convolution examples/bin/ref_2d_plot examples/bin/ref_zachFit,)
+              examples/bin/ref_convolution examples/bin/ref_2d_plot examples/bin/ref_zachFit examples/bin/ref_SigGen examples/bin/ref_TDDP4,)
 $(REFEX_ROOT): REFEX_EXTRA := -DGOOFIT_ROOT_FOUND=1 -Itests/ref_root -I$(REF)/extern/fmt/include -DFMT_HEADER_ONLY -Wno-sign-compare -Wno-unused-variable -Wno-unused-but-set-variable
+# SigGen.cpp and TDDP4.cu name MCBooster's host containers (goofit_b200/host/include/mcbooster: the subset GenerateSig returns) and call
+# thrust::count_if on them: Thrust's headers come with the CUDA toolkit, host backend
+examples/bin/ref_SigGen examples/bin/ref_TDDP4: REFEX_EXTRA += -isystem /usr/local/cuda/include -DTHRUST_DEVICE_SYSTEM=THRUST_DEVICE_SYSTEM_CPP
 $(REFEX_ROOT): $(wildcard tests/ref_root/*.h)
+examples/bin/ref_TDDP4: $(REF)/examples/TDDP4/TDDP4.cu $(LIBDIR)/libgoofit_host.so $(HOST)/include/goofit/Application.h
+	@mkdir -p examples/bin
+	$(CXX) $(HFLAGS) $(REFEX_EXTRA) -I$(REF)/extern/CLI11/include -x c++ $< -x none $(LDSTD) -L$(LIBDIR) -lgoofit_host -lgoofit_b200 -lMinuit2 -Wl,-rpath,'$$ORIGIN/../../goofit_b200/lib' -o $@
 REFEX    += $(REFEX_ROOT)
 examples: examples/bin/exponential $(REFEX)
 examples/bin/ref_%: $(REF)/examples/%/$$*.cpp $(LIBDIR)/libgoofit_host.so $(HOST)/include/goofit/Application.h

@@ -2,7 +2,10 @@
 // (reference: include/goofit/PDFs/physics/{Amp3Body.h,Amp3BodyBase.h,DalitzPlotHelpers.h,DalitzPlotter.h},
 //  include/goofit/PDFs/physics/resonances/{Resonance,RBW,GS,NonRes,Gauss}.h).
 #pragma once
+#include <tuple>
+
 #include <goofit/detail/Pdfs.h>
+#include <mcbooster/GContainers.h>
 #if GOOFIT_ROOT_FOUND
 #include <TH2F.h>
 #endif
@@ -90,15 +93,32 @@ class RhoOmegaMix : public ResonancePdf { // resonances/RhoOmegaMix.cu:139-167 (
 };
 } // namespace Resonances
 
-/// What GenerateSig returns (Amp3Body.cu:430-547, Amp4Body.cu:560-677 return the same four things as MCBooster
-/// containers): particles[d][4*event + {E, px, py, pz}], variables[v][event], the phase-space weight times the
-/// un-normalised PDF value, and the accept/reject flag of each event.
+/// The events of a GenerateSig call as flat columns (what the Python bindings turn into numpy arrays): particles[d][4*event + {E, px,
+/// py, pz}], variables[v][event], the phase-space weight times the un-normalised PDF value, and the accept/reject flag of each event.
 struct GeneratedSignal {
     std::vector<std::vector<fptype>> particles;
     std::vector<std::vector<fptype>> variables;
     std::vector<fptype> weights;
     std::vector<bool> flags;
 };
+/// The same four things as the MCBooster host containers upstream's GenerateSig returns (Amp3Body.h:55-56, Amp4Body.h:45-46,
+/// Amp4Body_TD.h:94-95): std::get<0..3> / std::tie on the result work as there, and as there the receiver owns the containers the two
+/// sets point to (the examples delete them). FLAGS is RealVector_h (0 or 1) for Amp3Body and Amp4Body, BoolVector_h for Amp4Body_TD.
+template <class FLAGS>
+using GeneratedSignalTuple = std::tuple<mcbooster::ParticlesSet_h, mcbooster::VariableSet_h, mcbooster::RealVector_h, FLAGS>;
+template <class FLAGS>
+inline GeneratedSignalTuple<FLAGS> toMCBoosterContainers(const GeneratedSignal &G) {
+    const size_t n = G.weights.size();
+    mcbooster::ParticlesSet_h particles;
+    for(const auto &col : G.particles) {
+        auto *p = new mcbooster::Particles_h(n);
+        for(size_t i = 0; i < n; i++) (*p)[i].set(col[4 * i], col[4 * i + 1], col[4 * i + 2], col[4 * i + 3]);
+        particles.push_back(p);
+    }
+    mcbooster::VariableSet_h variables;
+    for(const auto &col : G.variables) variables.push_back(new mcbooster::RealVector_h(col.begin(), col.end()));
+    return GeneratedSignalTuple<FLAGS>(std::move(particles), std::move(variables), G.weights, FLAGS(G.flags.begin(), G.flags.end()));
+}
 /// GENBOD phase-space events of mother -> 3 or 4 daughters from a counter-based generator: event i of a given seed is
 /// the same whatever the batch it is generated in (`offset` = index of the first event). Stand-in for
 /// mcbooster::PhaseSpace (not part of the reference checkout); weights are relative to the largest possible weight.
@@ -142,7 +162,11 @@ class Amp3Body : public Amp3BodyBase { // Amp3Body.h:43-111
     std::vector<std::vector<fptype>> fit_fractions();
     /// Amp3Body.cu:430-547: phase-space events, their (m12^2, m23^2, m13^2), weight x |sum c A|^2 x efficiency, and
     /// accept/reject flags. As upstream, the generated events REPLACE the PDF's dataset. seed 0 = seed 0 (upstream draws one).
-    GeneratedSignal GenerateSig(unsigned int numEvents, int seed = 0);
+    GeneratedSignal GenerateSigColumns(unsigned int numEvents, int seed = 0);
+    /// upstream's signature (Amp3Body.h:55-56): the same events as MCBooster host containers, owned by the receiver
+    GeneratedSignalTuple<mcbooster::RealVector_h> GenerateSig(unsigned int numEvents, int seed = 0) {
+        return toMCBoosterContainers<mcbooster::RealVector_h>(GenerateSigColumns(numEvents, seed));
+    }
     void setGenerationOffset(int off) { generation_offset = off; }
     int getGenerationOffset() const { return generation_offset; }
     /// normalisation integrals I_ij of the last normalize() (row i, column j)

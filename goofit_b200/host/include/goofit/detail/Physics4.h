@@ -215,7 +215,11 @@ class Amp4Body : public Amp4BodyBase { // Amp4Body.h:33-95
     int emit(detail::ProgramBuilder &B) override;
     /// Amp4Body.cu:560-677: phase-space events, their (m12, m34, cos12, cos34, phi), weight x |sum c A|^2 x efficiency,
     /// accept/reject flags. As upstream, the generated events REPLACE the PDF's dataset.
-    GeneratedSignal GenerateSig(unsigned int numEvents, int seed = 0);
+    GeneratedSignal GenerateSigColumns(unsigned int numEvents, int seed = 0);
+    /// upstream's signature (Amp4Body.h:45-46): the same events as MCBooster host containers, owned by the receiver
+    GeneratedSignalTuple<mcbooster::RealVector_h> GenerateSig(unsigned int numEvents, int seed = 0) {
+        return toMCBoosterContainers<mcbooster::RealVector_h>(GenerateSigColumns(numEvents, seed));
+    }
     void setGenerationOffset(int off) { generation_offset = off; }
     int getGenerationOffset() const { return generation_offset; }
 
@@ -323,7 +327,11 @@ class Amp4Body_TD final : public Amp4BodyBase { // Amp4Body_TD.h:34-137
     bool hasWeightedNormEvents() const { return weightedNorm; }
     /// Amp4Body_TD.cu:825-1018: unweighted phase space, decay times under an exponential envelope, accept/reject flags.
     /// As upstream, the generated events REPLACE the PDF's dataset.
-    GeneratedSignal GenerateSig(unsigned int numEvents, int seed = 0);
+    GeneratedSignal GenerateSigColumns(unsigned int numEvents, int seed = 0);
+    /// upstream's signature (Amp4Body_TD.h:94-95): the same events as MCBooster host containers, owned by the receiver
+    GeneratedSignalTuple<mcbooster::BoolVector_h> GenerateSig(unsigned int numEvents, int seed = 0) {
+        return toMCBoosterContainers<mcbooster::BoolVector_h>(GenerateSigColumns(numEvents, seed));
+    }
     void setGenerationOffset(int off) { generation_offset = off; }
     int getGenerationOffset() const { return generation_offset; }
     void setMaxWeight(fptype wmax) { maxWeight = wmax; }

@@ -271,7 +271,7 @@ fpcomplex Amp3Body::sumCachedWave(size_t i) const {
     auto w = getCachedWave(i);
     return std::accumulate(w.begin(), w.end(), fpcomplex(0, 0));
 }
-GeneratedSignal Amp3Body::GenerateSig(unsigned int numEvents, int seed) {
+GeneratedSignal Amp3Body::GenerateSigColumns(unsigned int numEvents, int seed) {
     GeneratedSignal G;
     devicePhaseSpace({decayInfo.motherMass, decayInfo.daug1Mass, decayInfo.daug2Mass, decayInfo.daug3Mass}, numEvents,
                      static_cast<unsigned long>(seed), generation_offset, &G.particles, G.weights);

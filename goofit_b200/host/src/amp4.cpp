@@ -431,7 +431,7 @@ std::vector<bool> unweightPhaseSpace(const std::vector<fptype> &w, unsigned long
     return flags;
 }
 
-GeneratedSignal Amp4Body::GenerateSig(unsigned int numEvents, int seed) {
+GeneratedSignal Amp4Body::GenerateSigColumns(unsigned int numEvents, int seed) {
     GeneratedSignal G;
     devicePhaseSpace(decayInfo.particle_masses, numEvents, static_cast<unsigned long>(seed), generation_offset, &G.particles, G.weights, &G.variables);
     std::vector<fptype> evt(numEvents);
@@ -958,7 +958,7 @@ fptype Amp4Body_TD::normalize() { // Amp4Body_TD.cu:744-799
 // u_i x wmax x exp(-gammamin t_i) < pdf_i. Returned: the accepted candidates' four-vectors, (m12, m34, cos12, cos34, phi, t), the
 // t = 0 values ("weights") and the flags. The uniform numbers come from this build's counter-based generator (MCBooster's
 // stream and thrust's minstd are not reproduced), keyed on (seed, generation_offset + index) like the phase space.
-GeneratedSignal Amp4Body_TD::GenerateSig(unsigned int numEvents, int seed) {
+GeneratedSignal Amp4Body_TD::GenerateSigColumns(unsigned int numEvents, int seed) {
     GeneratedSignal G;
     std::vector<std::vector<fptype>> P, V5;
     std::vector<fptype> w;

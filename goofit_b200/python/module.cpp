@@ -430,7 +430,7 @@ PYBIND11_MODULE(_goofit, m) {
         // upstream's binding exports three of the four components of each particle (python/PDFs/physics/Amp3Body.cpp:49-62)
         .def(
             "GenerateSig",
-            [](Amp3Body &self, size_t numEvents, int seed) { return generated_to_numpy(self.GenerateSig(numEvents, seed), 3); },
+            [](Amp3Body &self, size_t numEvents, int seed) { return generated_to_numpy(self.GenerateSigColumns(numEvents, seed), 3); },
             "numEvents"_a, "seed"_a = 0)
         .def("getDecayInfo", &Amp3Body::getDecayInfo, py::return_value_policy::reference_internal);
     py::class_<DalitzPlotter>(m, "DalitzPlotter")

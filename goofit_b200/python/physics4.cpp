@@ -142,7 +142,7 @@ void init_physics4(py::module &m) {
         .def("getGenerationOffset", &Amp4Body::getGenerationOffset)
         .def(
             "GenerateSig",
-            [](Amp4Body &self, size_t numEvents, int seed) { return generated_to_numpy(self.GenerateSig(numEvents, seed), 4); },
+            [](Amp4Body &self, size_t numEvents, int seed) { return generated_to_numpy(self.GenerateSigColumns(numEvents, seed), 4); },
             "numEvents"_a, "seed"_a = 0)
         .def("getMCevents", &Amp4Body::getMCevents);
     // time-dependent: python/PDFs/physics/{Amp4Body_TD.cu:18-38,TruthResolution.cpp,ThreeGaussResolution.cpp,DalitzPlotHelpers.cpp}
@@ -218,7 +218,7 @@ void init_physics4(py::module &m) {
         .def("getMaxWeight", &Amp4Body_TD::getMaxWeight)
         .def(
             "GenerateSig",
-            [](Amp4Body_TD &self, size_t numEvents, int seed) { return generated_to_numpy(self.GenerateSig(numEvents, seed), 4); },
+            [](Amp4Body_TD &self, size_t numEvents, int seed) { return generated_to_numpy(self.GenerateSigColumns(numEvents, seed), 4); },
             "numEvents"_a, "seed"_a = 0,
             "(particles[4, nAcc, 3 or 4], variables[6, nAcc] = m12, m34, cos12, cos34, phi, dtime, weights[nAcc] = PDF at t = 0, flags[nAcc])");
     m.def(

@@ -8,6 +8,7 @@
 #include <cmath>
 #include <string>
 #include <vector>
+#include "TString.h"
 
 enum EColorStandIn { kWhite = 0, kBlack = 1, kRed = 632, kGreen = 416, kBlue = 600, kYellow = 400, kMagenta = 616, kCyan = 432, kViridis = 112, kRainBow = 55 };
 

@@ -33,7 +33,7 @@ def test_reference_catch_test(name):
 
 
 # ---- the reference's ROOT-using examples, unmodified ------------------------------------------------------------------------------
-# examples/{dalitz,addition,simpleFit,convolution,2d_plot,zachFit} of the reference checkout, compiled where they lie with
+# examples/{dalitz,addition,simpleFit,convolution,2d_plot,zachFit,SigGen,TDDP4} of the reference checkout, compiled where they lie with
 # GOOFIT_ROOT_FOUND=1 against this repo's headers (Application as a CLI::App, GooPdf::plotToROOT, DalitzPlotter::make2D, setROOTStyle)
 # and tests/ref_root, a headless stand-in for ROOT (`make examples`). Each program's own exit status is the check: they return the
 # Minuit status of their fit (FitManager converts to it), dalitz.cpp 7 on a run-time error.
@@ -44,6 +44,9 @@ ROOT_EXAMPLES = {
     "ref_simpleFit": [],
     "ref_convolution": [],
     "ref_2d_plot": [],
+    # GenerateSig as upstream's tuple of MCBooster host containers (std::get / std::tie, thrust::count_if on the flags, the caller deletes the sets)
+    "ref_SigGen": [],  # Amp4Body: 4 x 10^6 events, accepted ones written to a TTree
+    "ref_TDDP4": ["-t", "2"],  # Amp4Body_TD with TruthResolution: 2 x 800 000 events (the default of 100 trials is a production run)
 }
 
 
