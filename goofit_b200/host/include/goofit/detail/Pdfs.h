@@ -206,6 +206,15 @@ class ProdPdf : public CombinePdf { // combine/ProdPdf.h
 class ConvolutionPdf : public CombinePdf { // combine/ConvolutionPdf.h
   public:
     ConvolutionPdf(std::string n, Observable _x, GooPdf *model, GooPdf *resolution);
+    /// ConvolutionPdf.cu:180-226 of the reference: the form for several convolutions that are evaluated side by side (the targets of a
+    /// MappedPdf), which upstream lets load their model workspaces into one shared-memory cache. Here every convolution reads its
+    /// own per-offset table (csrc/gf_conv.cu), so there is nothing to share: the values are those of the four-argument form. The
+    /// bookkeeping is kept: the PDF counts as not properly initialised until registerOthers has seen a list of numOthers + 1
+    /// convolutions that includes this one.
+    ConvolutionPdf(std::string n, Observable _x, GooPdf *model, GooPdf *resolution, unsigned int numOthers);
+    /// ConvolutionPdf.cu:284-311: same checks and messages as upstream; returns without effect when the list is wrong
+    void registerOthers(std::vector<ConvolutionPdf *> others);
+    bool isProperlyInitialised() const { return properlyInitialised; }
     fptype normalize() override;
     void setIntegrationConstants(fptype lo, fptype hi, fptype step);
 
@@ -220,6 +229,7 @@ class ConvolutionPdf : public CombinePdf { // combine/ConvolutionPdf.h
     GooPdf *model;
     GooPdf *resolution;
     bool workspacesFilled{false};
+    unsigned int numOthers{0};
 };
 
 } // namespace GooFit

@@ -545,6 +545,26 @@ ConvolutionPdf::ConvolutionPdf(std::string n, Observable x, GooPdf *m, GooPdf *r
     setLowerBoundOffset();
     registerFunction("ptr_to_ConvolvePdfs", GF_OP_CONVOLVE);
 }
+ConvolutionPdf::ConvolutionPdf(std::string n, Observable x, GooPdf *m, GooPdf *r, unsigned int others)
+    : ConvolutionPdf(std::move(n), x, m, r) {
+    // upstream's limit is the size of its shared-memory cache (CONVOLUTION_CACHE_SIZE 512, ConvolutionPdf.cu:218-220)
+    if(others > 512) throw GeneralError("numOthers {} must be not be more than the cache size {}", others, 512);
+    numOthers = others;
+    if(numOthers != 0) properlyInitialised = false;
+}
+void ConvolutionPdf::registerOthers(std::vector<ConvolutionPdf *> others) {
+    const unsigned int numExpectedOthers = numOthers + 1;
+    if(numExpectedOthers != others.size()) {
+        std::cout << "Problem: " << getName() << " initialized with " << others.size() << " other PDFs, expected " << numExpectedOthers
+                  << " (including itself). Returning without initialization.\n";
+        return;
+    }
+    if(std::find(others.begin(), others.end(), this) == others.end()) {
+        std::cout << "Problem: " << getName() << " initialized with list that did not include itself. Returning without initialisation.\n";
+        return;
+    }
+    properlyInitialised = true;
+}
 void ConvolutionPdf::setIntegrationConstants(fptype lo, fptype hi, fptype step) {
     constantsList[0] = lo;
     constantsList[1] = hi;

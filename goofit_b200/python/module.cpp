@@ -348,6 +348,9 @@ PYBIND11_MODULE(_goofit, m) {
         .def(py::init<std::string, PdfBase *, PdfBase *>(), "name"_a, "core"_a, "shell"_a, py::keep_alive<1, 3>(), py::keep_alive<1, 4>());
     py::class_<ConvolutionPdf, CombinePdf>(m, "ConvolutionPdf")
         .def(py::init<std::string, Observable, GooPdf *, GooPdf *>(), "name"_a, "x"_a, "model"_a, "resolution"_a, py::keep_alive<1, 4>(), py::keep_alive<1, 5>())
+        .def(py::init<std::string, Observable, GooPdf *, GooPdf *, unsigned int>(), "name"_a, "x"_a, "model"_a, "resolution"_a, "numOthers"_a,
+             py::keep_alive<1, 4>(), py::keep_alive<1, 5>())
+        .def("registerOthers", &ConvolutionPdf::registerOthers, "others"_a)
         .def("setIntegrationConstants", &ConvolutionPdf::setIntegrationConstants, "lo"_a, "hi"_a, "step"_a);
 
     // ---- three-body amplitude ----

@@ -565,3 +565,22 @@ def test_python_api_names_cover_the_reference_bindings():
     not_built = sorted(n for n in defined if not any(hasattr(s, n) for s in spaces))
     # the classes this repo deliberately leaves out and two binding-only helpers
     assert set(not_built) <= {"Amp3Body_IS", "AmpNBodyBase", "HelpPrinter", "InterHistPdf", "ThreeGaussResolutionExt", "ThreeGaussResolutionSplice"}, not_built
+
+
+def test_convolution_register_others_bookkeeping(capfd):
+    """ConvolutionPdf's five-argument form and registerOthers (ConvolutionPdf.cu:180-226,284-311): a list of the wrong length or one
+    that leaves the PDF itself out is reported with upstream's message and changes nothing (host-only, no device call)."""
+    x = gf.Observable("x", 0, 1)
+    g = gf.GaussianPdf("g", x, gf.Variable("m", 0.5), gf.Variable("s", 0.1))
+    r = gf.GaussianPdf("r", x, gf.Variable("m2", 0.0), gf.Variable("s2", 0.05))
+    c1 = gf.ConvolutionPdf("c1", x, g, r, 1)
+    c2 = gf.ConvolutionPdf("c2", x, g, r, 1)
+    c1.registerOthers([c1])
+    assert "c1 initialized with 1 other PDFs, expected 2" in capfd.readouterr().out
+    c1.registerOthers([c2, c2])
+    assert "did not include itself" in capfd.readouterr().out
+    c1.registerOthers([c1, c2])
+    c2.registerOthers([c1, c2])
+    assert capfd.readouterr().out == ""
+    with pytest.raises(Exception):
+        gf.ConvolutionPdf("c3", x, g, r, 513)
