@@ -14,6 +14,7 @@ try:
     from ._goofit import *  # noqa: F401,F403
     from . import _goofit
     from ._goofit import Resonances, Lineshapes, minuit2  # noqa: F401
+    from ._goofit import __version__, __main__  # noqa: F401  (the star import skips underscored names)
     import sys as _sys
     _sys.modules[__name__ + ".minuit2"] = minuit2  # `import goofit_b200.minuit2` / `from goofit_b200.minuit2 import MnMigrad` (upstream: goofit.minuit2)
 except ImportError as e:  # pragma: no cover - build missing
@@ -43,3 +44,4 @@ for _sub in (Resonances, Lineshapes):
 del _name, _cls, _sub
 
 from . import capi  # noqa: E402,F401
+from . import landau  # noqa: E402,F401  (upstream: goofit.landau, python/extras/landau.cpp)

@@ -11,6 +11,7 @@
 
 #include <Minuit2/FunctionMinimum.h>
 #include <Minuit2/MnUserParameterState.h>
+#include <goofit/Application.h>
 #include <goofit/detail/Fit.h>
 #include <goofit/detail/Physics3.h>
 
@@ -35,6 +36,30 @@ static DS *make_dataset(py::args args, py::kwargs kwargs) {
 PYBIND11_MODULE(_goofit, m) {
     m.doc() = "goofit_b200: B200-native GooFit likelihood engine (host API over hand-written sm_100a kernels)";
     py::register_exception<GeneralError>(m, "GeneralError");
+
+    // module-level functions and constants of python/goofit/Application.cpp and python/goofit/Version.cpp of the reference: every
+    // example there opens with `from goofit import *; print_goofit_info()`
+    m.def("print_splash", &print_splash, "Print a splash screen", py::call_guard<py::scoped_ostream_redirect>());
+    m.def(
+        "goofit_info", [](int gpuDev) { return goofit_info_version() + "\n" + goofit_info_device(gpuDev); }, "Get GooFit information", "gpuDevice"_a = 0);
+    m.def(
+        "print_goofit_info", [](int gpuDev) { py::print(goofit_info_version() + "\n" + goofit_info_device(gpuDev)); },
+        "Print GooFit information (same as goofit_info, kept for legacy code)", "gpuDevice"_a = 0);
+    m.def("set_floating_exceptions", &Application::set_floating_exceptions, "Enable floating point exceptions as Exceptions (no effect on a CUDA build, as upstream)");
+    m.def("__main__", []() { py::print(goofit_info_version() + "\n" + goofit_info_device(0)); });
+    m.attr("__version__") = py::make_tuple(GOOFIT_VERSION_MAJOR, GOOFIT_VERSION_MINOR, GOOFIT_VERSION_PATCH);
+    m.attr("GOOFIT_VERSION_TUPLE") = py::make_tuple(GOOFIT_VERSION_MAJOR, GOOFIT_VERSION_MINOR, GOOFIT_VERSION_PATCH);
+    m.attr("GOOFIT_VERSION") = GOOFIT_VERSION;
+    m.attr("GOOFIT_GIT_VERSION") = GOOFIT_VERSION;
+    m.attr("GOOFIT_TAG") = "";
+    m.attr("GOOFIT_SOURCE_DIR") = GOOFIT_SOURCE_DIR;
+    m.attr("CMAKE_CXX_FLAGS") = CMAKE_CXX_FLAGS;
+    m.attr("CMAKE_BUILD_TYPE") = CMAKE_BUILD_TYPE;
+    m.attr("GOOFIT_DEVICE") = GOOFIT_DEVICE;
+    m.attr("GOOFIT_HOST") = GOOFIT_HOST;
+    m.attr("ARCH_FLAGS") = GOOFIT_ARCH_FLAGS;
+    m.attr("ROOT_FOUND") = GOOFIT_ROOT_FOUND;
+    m.attr("INT_MAX") = INT_MAX;
 
     m.def("set_device", [](int dev) { detail::Engine::get().setDevice(dev); }, "device"_a);
     m.def("set_shard", [](int rank, int size) { detail::Engine::get().setShard(rank, size); }, "rank"_a, "size"_a);
@@ -462,6 +487,9 @@ PYBIND11_MODULE(_goofit, m) {
              }, "Get the extents for plotting");
 
     init_physics4(m);
+    // pre-2.2 class names the reference's bindings keep as module attributes (python/PDFs/physics/Amp3Body.cpp:79, Amp3Body_TD.cpp:129)
+    m.attr("DalitzPlotPdf") = m.attr("Amp3Body");
+    m.attr("TddpPdf") = m.attr("Amp3Body_TD");
 
     // ---- fitting ----
     init_minuit2(m); // goofit_b200.minuit2: FCNBase, MnUserParameters, MnMigrad, FunctionMinimum, ... (python/Minuit2/*.cpp upstream)

@@ -120,3 +120,20 @@ def test_minuit2_module_drives_a_goofit_likelihood():
     assert abs(a1 - alpha.value) < 1e-6 and abs(e1 - alpha.error) < 1e-6 * max(1.0, e1)
     assert abs(res.Fval() - r2.Fval()) < 1e-6 * abs(r2.Fval())
     assert "Minimum" in str(res) or "minimum" in str(res).lower()
+
+
+def test_module_level_info_functions(capsys):
+    """`from goofit import *; print_goofit_info()` — the first two lines of every script under the reference's python/examples
+    (python/goofit/Application.cpp, Version.cpp): the functions and constants exist at module level under both package names."""
+    import goofit
+    ns = {}
+    exec("from goofit import *", ns)
+    ns["print_goofit_info"]()
+    out = capsys.readouterr().out
+    assert "GooFit" in out and "SMs" in out, out
+    info = goofit.goofit_info(0)
+    assert "sm_100a" in info and goofit.GOOFIT_VERSION in info
+    assert goofit.__version__ == goofit.GOOFIT_VERSION_TUPLE == (2, 3, 0) and goofit.GOOFIT_DEVICE == "CUDA" and goofit.ROOT_FOUND == 0
+    assert ns["DalitzPlotPdf"] is gf.Amp3Body and ns["TddpPdf"] is gf.Amp3Body_TD
+    goofit.set_floating_exceptions()
+    goofit.print_splash()
