@@ -335,6 +335,11 @@ class BinnedDataSet : public DataSet {
 
 // ---- fit control (reference FitControl.h:11-76, PDFs/MetricPointer.h) ------------------------------
 enum class EvalFunc : size_t { Eval = 0, NLL, Prob, BinAvg, BinWithError, Chisq };
+/// FitControl.h:13-16 of the reference: the name upstream registers each metric's device function under
+inline const char *evalfunc_to_string(EvalFunc val) {
+    static const char *names[] = {"ptr_to_Eval", "ptr_to_NLL", "ptr_to_Prob", "ptr_to_BinAvg", "ptr_to_BinWithError", "ptr_to_Chisq"};
+    return names[static_cast<size_t>(val)];
+}
 
 class FitControl {
   public:
@@ -602,6 +607,8 @@ class GooPdf : public PdfBase {
     void scan(Observable var, std::vector<fptype> &values);
     void setFitControl(std::shared_ptr<FitControl> fc) override;
     void setParameterConstantness(bool constant = true);
+    /// GooPdf.cu:237-252 upstream switches printf debugging inside its device functions on; the kernels here carry none: accepted, no effect
+    void setDebugMask(int, bool = true) const {}
     int get_bin_grid_size() const;
     fptype get_bin_grid_volume() const;
     double reduce_with_bins() const;

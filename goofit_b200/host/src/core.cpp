@@ -245,8 +245,7 @@ size_t BinnedDataSet::getNumBins() const {
 fptype BinnedDataSet::getNumWeightedEvents() const { return std::accumulate(binvalues.begin(), binvalues.end(), 0.0); }
 
 std::string FitControl::getName() const {
-    static const char *names[] = {"ptr_to_Eval", "ptr_to_NLL", "ptr_to_Prob", "ptr_to_BinAvg", "ptr_to_BinWithError", "ptr_to_Chisq"};
-    return names[static_cast<size_t>(metricFunc)];
+    return evalfunc_to_string(metricFunc);
 }
 
 // ---- Engine -----------------------------------------------------------------------------------------
