@@ -183,6 +183,7 @@ class Amp4BodyBase : public GooPdf {
         std::vector<fptype> masses;
     } normSpec;
     void materialiseNormEvents();
+    bool normSampleEmpty{false}; // the generated sample had no accepted event: one candidate stands in, integrals are refused
     void setDataSizeCommon(unsigned int dataSize, unsigned int evtSize);
     /// (re)build the Gram matrix if the MC amplitudes changed; returns G[a * nAmps + b]
     const std::vector<std::complex<fptype>> &gram(bool mcAmpsChanged);

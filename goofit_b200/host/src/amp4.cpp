@@ -499,11 +499,14 @@ void Amp4BodyBase::materialiseNormEvents() {
     NormSpec spec = normSpec;
     normSpec.perBatch = 0;
     std::vector<std::vector<fptype>> all(5);
+    std::vector<fptype> firstCandidate;
     for(long seed : spec.seeds) {
         std::vector<fptype> w;
         std::vector<std::vector<fptype>> v5;
         devicePhaseSpace(spec.masses, spec.perBatch, static_cast<unsigned long>(seed), 0, nullptr, w, &v5);
         auto acc = unweightPhaseSpace(w, static_cast<unsigned long>(seed));
+        if(firstCandidate.empty() && !w.empty())
+            for(int k = 0; k < 5; k++) firstCandidate.push_back(v5[k][0]);
         if(spec.compact) {
             for(size_t i = 0; i < w.size(); i++)
                 if(acc[i])
@@ -514,11 +517,20 @@ void Amp4BodyBase::materialiseNormEvents() {
             for(int k = 0; k < 5; k++) all[k].insert(all[k].end(), v5[k].begin(), v5[k].begin() + nAcc);
         }
     }
-    if(all[0].empty()) throw GeneralError("{}: no normalisation event was accepted", getName());
+    // Nothing accepted (python/examples/generate_sig_example.py asks for ONE candidate because it only generates): upstream is left
+    // with an empty sample, which its GenerateSig never touches and whose integral would be 0 / 0. The caches here need a sample
+    // to be allocated against, so the first candidate stands in, and normalize() refuses to integrate over it.
+    const bool none = all[0].empty();
+    if(none) {
+        if(firstCandidate.empty()) throw GeneralError("{}: no normalisation event was generated", getName());
+        for(int k = 0; k < 5; k++) all[k].push_back(firstCandidate[k]);
+    }
     setNormEvents(all);
+    normSampleEmpty = none;
 }
 void Amp4BodyBase::setNormEvents(const std::vector<std::vector<fptype>> &cols5) {
     normSpec.perBatch = 0; // an explicit sample replaces a pending generated one
+    normSampleEmpty   = false;
     normWeights.clear();
     normDtime.clear();
     normSigma.clear();
@@ -903,6 +915,7 @@ fptype Amp4Body_TD::normalize() { // Amp4Body_TD.cu:744-799
         setNormalization(1.0);
         return 1.0;
     }
+    if(normSampleEmpty) throw GeneralError("{}: no normalisation event was accepted", getName());
     if(weightedNorm) { // NormEvents_4Body_Weighted::computeNorm_TD: sum_m w_m pdf(x_m, t_m, sigma_m) / sum of the initial weights
         if(any) Engine::check(gf_amp4_cache(E.ctx(), nodeIdx, spins, lsRedo.data(), ampRedo.data()), "gf_amp4_cache");
         double sum = 0;

@@ -1212,3 +1212,24 @@ def test_generate_sig_time_dependent():
     want = u * np.exp(-V[5] * gammamin) * 1.1 * w.max() < at_t
     assert (want != flags).sum() <= 2 and 0.003 < flags.mean() < 0.95
     assert M.dp.getMaxWeight() == 1.1 * w.max()
+
+
+def test_generate_sig_with_an_empty_normalisation_sample():
+    """python/examples/generate_sig_example.py of the reference builds Amp4Body_TD with ONE normalisation candidate because it only
+    generates: when the accept-reject step keeps none, GenerateSig still works (it never integrates: Amp4Body_TD.cu:946-950) and a
+    later normalize() says why it cannot."""
+    from models import TDDP4
+    M = None
+    for seed in range(1, 40):  # one candidate is accepted with its phase-space weight as probability: find a seed that rejects it
+        M = TDDP4(three_gauss=False, float_ls=False, float_mix=True, mc_to_gen=1, norm_seed=seed)
+        P, V, w, flags = M.dp.GenerateSig(20000, 5)
+        assert V.shape[0] == 6 and V.shape[1] == w.shape[0] > 100 and np.all(np.isfinite(w))
+        d = M.dataset([V[k] for k in range(5)] + [V[5], np.zeros(V.shape[1])])
+        M.signal.setData(d)
+        M.dp.setDataSize(V.shape[1], 8)
+        try:
+            M.dp.normalize()
+        except gf.GeneralError as e:
+            assert "no normalisation event was accepted" in str(e)
+            return
+    pytest.fail("every seed accepted its single normalisation candidate")
