@@ -6,7 +6,7 @@ set -u
 R=$(pwd)
 mkdir -p gpurun_out
 T=$(mktemp -d)
-for spec in "ref_dalitz --make-toy" "ref_addition" "ref_simpleFit" "ref_convolution" "ref_2d_plot"; do
+for spec in "ref_dalitz --make-toy" "ref_addition" "ref_simpleFit" "ref_convolution" "ref_2d_plot" "ref_SigGen" "ref_TDDP4 -t 2"; do
     set -- $spec
     name=$1; shift
     mkdir -p $T/$name
