@@ -317,7 +317,7 @@ class Amp4Body_TD final : public Amp4BodyBase { // Amp4Body_TD.h:34-137
     void setDataSize(unsigned int dataSize, unsigned int evtSize = 8) { setDataSizeCommon(dataSize, evtSize); }
     int getNumAccNormEvents() {
         materialiseNormEvents();
-        return static_cast<int>(MCevents);
+        return normSampleEmpty ? 0 : static_cast<int>(MCevents); // the stand-in candidate of an empty sample does not count
     }
     /// sum of the batches' initial weights: the number of accepted events for generated batches; for weighted batches the sum
     /// upstream forms with an INTEGER accumulator (thrust::reduce(..., 0), NormEvents_4Body_Weighted.cu:36), i.e. sum of floor(w)
