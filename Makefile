@@ -76,11 +76,20 @@ RT_CONVERT := BifurGaussTest CompositeTest ConvolutionTest EventWeightedAddTest 
               NovosibirskTest PolynomialTest ProdTest ScaledGaussianTest SmoothHistogramTest StepTest VoigtianTest BWTest CorrGaussianTest
 RT_SIMPLE  := NormalizeTest AddNormTest SimpleTest BinningTest BlindTest MonteCarloTest
 RT_PDFS    := GenArgusTest GenGaussianTest
+# the ROOT-gated ones that also fit through FitManagerMinuit1 (test_fitter_minuit1 of tests/convert/testhelpers.h) and Minuit1Test:
+# GOOFIT_ROOT_FOUND=1 with tests/ref_root, whose TMinuit stand-in is carried by Minuit2
+RT_ROOT_CONVERT := ArgusTest BinTransformTest CrystalBallTest ExpGaussTest ExpTest
+RT_ROOT_SIMPLE  := Minuit1Test
+RT_ROOT_OBJ := $(RT_ROOT_CONVERT:%=build/reftests/convert/%.o) $(RT_ROOT_SIMPLE:%=build/reftests/simple/%.o)
+$(RT_ROOT_OBJ): RT_EXTRA := -DGOOFIT_ROOT_FOUND=1 -Itests/ref_root
+$(RT_ROOT_OBJ): $(wildcard tests/ref_root/*.h) $(HOST)/include/goofit/fitting/FitManagerMinuit1.h
+RT_CONVERT += $(RT_ROOT_CONVERT)
+RT_SIMPLE  += $(RT_ROOT_SIMPLE)
 RT_BIN     := $(RT_CONVERT:%=examples/bin/reftests/convert/%) $(RT_SIMPLE:%=examples/bin/reftests/simple/%) $(RT_PDFS:%=examples/bin/reftests/PDFs/%)
 RT_FLAGS   := $(HFLAGS) -Wno-unused-variable -Itests/ref_catch -I$(REF)/tests/include -I$(REF)/tests/convert -I$(REF)/tests/PDFs -I$(REF)/extern/fmt/include -DFMT_HEADER_ONLY
 build/reftests/%.o: $(REF)/tests/%.cpp tests/ref_catch/catch2/catch_all.hpp $(wildcard $(HOST)/include/goofit/detail/*.h)
 	@mkdir -p $(dir $@)
-	$(CXX) $(RT_FLAGS) -c $< -o $@
+	$(CXX) $(RT_FLAGS) $(RT_EXTRA) -c $< -o $@
 # one executable per test file, as upstream's goofit_catch_test() builds them (each with tests/catch_main.cpp)
 examples/bin/reftests/%: build/reftests/%.o build/reftests/catch_main.o $(LIBDIR)/libgoofit_host.so
 	@mkdir -p $(dir $@)
@@ -91,12 +100,17 @@ REFEX    += $(if $(wildcard $(REF)/tests/catch_main.cpp),$(RT_BIN),)
 # drop-in headers (plotToROOT, make2D, setROOTStyle) and tests/ref_root stands in for ROOT itself (histograms in memory, canvases that
 # draw nothing): neither machine has ROOT or a graphics stack. A user with ROOT passes its include path and libraries instead.
 REFEX_ROOT := $(if $(wildcard $(REF)/examples/dalitz/dalitz.cpp),examples/bin/ref_dalitz examples/bin/ref_addition examples/bin/ref_simpleFit \
-              examples/bin/ref_convolution examples/bin/ref_2d_plot examples/bin/ref_zachFit examples/bin/ref_SigGen examples/bin/ref_TDDP4,)
+              examples/bin/ref_convolution examples/bin/ref_2d_plot examples/bin/ref_zachFit examples/bin/ref_SigGen examples/bin/ref_TDDP4 \
+              examples/bin/ref_chisquare examples/bin/ref_exponential1 examples/bin/ref_exponential2,)
 $(REFEX_ROOT): REFEX_EXTRA := -DGOOFIT_ROOT_FOUND=1 -Itests/ref_root -I$(REF)/extern/fmt/include -DFMT_HEADER_ONLY -Wno-sign-compare -Wno-unused-variable -Wno-unused-but-set-variable
 # SigGen.cpp and TDDP4.cu name MCBooster's host containers (goofit_b200/host/include/mcbooster: the subset GenerateSig returns) and call
 # thrust::count_if on them: Thrust's headers come with the CUDA toolkit, host backend
 examples/bin/ref_SigGen examples/bin/ref_TDDP4: REFEX_EXTRA += -isystem /usr/local/cuda/include -DTHRUST_DEVICE_SYSTEM=THRUST_DEVICE_SYSTEM_CPP
 $(REFEX_ROOT): $(wildcard tests/ref_root/*.h)
+# exponential1.cpp fits through FitManagerMinuit1, chisquare.cpp drives a TMinuit of its own beside GooFit's fit (tests/ref_root/TMinuit.h, carried by Minuit2)
+examples/bin/ref_exponential1 examples/bin/ref_exponential2: examples/bin/ref_exponential%: $(REF)/examples/exponential/exponential%.cpp $(LIBDIR)/libgoofit_host.so $(HOST)/include/goofit/fitting/FitManagerMinuit1.h
+	@mkdir -p examples/bin
+	$(CXX) $(HFLAGS) $(REFEX_EXTRA) -I$(REF)/extern/CLI11/include $< $(LDSTD) -L$(LIBDIR) -lgoofit_host -lgoofit_b200 -lMinuit2 -Wl,-rpath,'$$ORIGIN/../../goofit_b200/lib' -o $@
 examples/bin/ref_TDDP4: $(REF)/examples/TDDP4/TDDP4.cu $(LIBDIR)/libgoofit_host.so $(HOST)/include/goofit/Application.h
 	@mkdir -p examples/bin
 	$(CXX) $(HFLAGS) $(REFEX_EXTRA) -I$(REF)/extern/CLI11/include -x c++ $< -x none $(LDSTD) -L$(LIBDIR) -lgoofit_host -lgoofit_b200 -lMinuit2 -Wl,-rpath,'$$ORIGIN/../../goofit_b200/lib' -o $@

@@ -90,6 +90,7 @@ class PdfBase;
 
 // ---- Variable / Observable / EventNumber (reference Variable.h:22-263) ---------------------------
 class Params;
+class Minuit1;
 class Indexable {
   protected:
     struct State {
@@ -165,6 +166,7 @@ class Variable : public Indexable {
   public:
     class Key {
         friend Params;
+        friend Minuit1; // goofit/fitting/FitManagerMinuit1.h (builds with ROOT)
         Key() = default;
     };
     Variable(const Variable &) = default;

@@ -4,6 +4,7 @@
 class TLatex : public TObject {
   public:
     TLatex() = default;
+    TLatex(double, double, const char *) {}
     void DrawLatex(double, double, const char *) {}
     void SetTextSize(double) {}
     void SetNDC(bool = true) {}

@@ -403,7 +403,9 @@ def test_reference_include_paths_compile(tmp_path):
                  "goofit/PDFs/combine/EventWeightedAddPdf.h", "goofit/PDFs/combine/MappedPdf.h", "goofit/PDFs/physics/Tddp4Pdf.h"):
         assert must in headers, must
     src = tmp_path / "all_headers.cpp"
-    src.write_text("".join("#include <%s>\n" % h for h in sorted(headers)) + """
+    needs_root = "goofit/fitting/FitManagerMinuit1.h"  # TMinuit: as upstream, only for builds with ROOT (compiled below against the stand-in)
+    assert needs_root in headers
+    src.write_text("".join("#include <%s>\n" % h for h in sorted(headers) if h != needs_root) + """
 #include <type_traits>
 using namespace GooFit;
 static_assert(std::is_same<DalitzPlotPdf, Amp3Body>::value && std::is_same<TDDP4, Amp4Body_TD>::value, "alias headers");
@@ -418,6 +420,11 @@ int main() { return 0; }
         pytest.skip("Minuit2 headers (reference checkout) are not on this machine")
     out = subprocess.run(cmd, capture_output=True, text=True)
     assert out.returncode == 0, out.stderr[-3000:]
+    # with ROOT (here: the headless stand-in of tests/ref_root) every header compiles, FitManagerMinuit1.h and the ROOT conveniences included
+    src2 = tmp_path / "all_headers_root.cpp"
+    src2.write_text("".join("#include <%s>\n" % h for h in sorted(headers)) + "int main() { return 0; }\n")
+    out = subprocess.run(cmd[:-1] + ["-DGOOFIT_ROOT_FOUND=1", "-I" + os.path.join(ROOT, "tests", "ref_root"), str(src2)], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr[-3000:]
 
 
 def test_reference_examples_compile_unmodified():
@@ -426,8 +433,9 @@ def test_reference_examples_compile_unmodified():
     tests/ref_root, the ROOT-using ones (dalitz.cpp, zachFit.cpp, addition.cpp, simpleFit.cpp, convolution.cpp, 2d_plot.cpp), whose
     command lines need Application to be a real CLI::App, and SigGen.cpp / TDDP4.cu, which take GenerateSig's result apart as
     MCBooster host containers (goofit_b200/host/include/mcbooster) and call Thrust on them (the CUDA toolkit's headers, host backend).
-    What is left out needs Minuit1 (exponential1.cpp, chisquare.cpp), Boost and MCBooster's generator classes (TDDP4WeightedMC) or
-    5000 lines of ROOT I/O (pipipi0DPFit.cpp)."""
+    exponential1.cpp (FitManagerMinuit1) and chisquare.cpp (a TMinuit of its own) compile against the stand-in's TMinuit, which
+    Minuit2 carries. What is left out needs Boost and MCBooster's generator classes (TDDP4WeightedMC) or Amp3Body_IS and 5000 lines
+    of ROOT I/O (pipipi0DPFit.cpp)."""
     import shutil
     import subprocess
     ref = "/root/reference/examples"
@@ -441,7 +449,8 @@ def test_reference_examples_compile_unmodified():
     thrust = ["-isystem", "/usr/local/cuda/include", "-DTHRUST_DEVICE_SYSTEM=THRUST_DEVICE_SYSTEM_CPP"]  # user code calls thrust::count_if
     for src, extra in (("SigGen/SigGen.cpp", with_root + thrust), ("TDDP4/TDDP4.cu", with_root + thrust), ("DP4/DP4.cu", []), ("exponential/exponential.cpp", []), ("exponential/exponential2.cpp", []), ("product/product.cpp", []),
                        ("dalitz/dalitz.cpp", with_root), ("zachFit/zachFit.cpp", with_root), ("addition/addition.cpp", with_root),
-                       ("simpleFit/simpleFit.cpp", with_root), ("convolution/convolution.cpp", with_root), ("2d_plot/2d_plot.cpp", with_root)):
+                       ("simpleFit/simpleFit.cpp", with_root), ("convolution/convolution.cpp", with_root), ("2d_plot/2d_plot.cpp", with_root),
+                       ("exponential/exponential1.cpp", with_root), ("chisquare/chisquare.cpp", with_root)):
         out = subprocess.run(base + extra + [os.path.join(ref, src)], capture_output=True, text=True)
         assert out.returncode == 0, src + "\n" + out.stderr[-3000:]
 

@@ -47,6 +47,11 @@ ROOT_EXAMPLES = {
     # GenerateSig as upstream's tuple of MCBooster host containers (std::get / std::tie, thrust::count_if on the flags, the caller deletes the sets)
     "ref_SigGen": [],  # Amp4Body: 4 x 10^6 events, accepted ones written to a TTree
     "ref_TDDP4": ["-t", "2"],  # Amp4Body_TD with TruthResolution: 2 x 800 000 events (the default of 100 trials is a production run)
+    # TMinuit users: exponential1.cpp fits through goofit/fitting/FitManagerMinuit1.h, chisquare.cpp runs a TMinuit fit of its own beside
+    # GooFit's binned chi-square fits (tests/ref_root/TMinuit.h is carried by Minuit2); exponential2.cpp needs neither
+    "ref_exponential1": [],
+    "ref_exponential2": [],
+    "ref_chisquare": [],
 }
 
 
