@@ -2,10 +2,11 @@
 // Minuit2 (the C++ rewrite of the same algorithms, bundled with the reference) — there is no ROOT on either machine. TEST
 // INFRASTRUCTURE: it lets the reference's ROOT-gated tests and examples that fit through FitManagerMinuit1 compile unmodified and
 // run; a user with ROOT gets the real TMinuit. Parameters with lower == upper are unlimited, as in TMinuit; UP (the error
-// definition) is TMinuit's default 1; the status is 0 after a valid minimum and 4 otherwise, as TMinuit::Migrad returns it.
+// definition) is TMinuit's default 1; crossed limits are swapped as TMinuit does; the status is 0 after a valid minimum and 4 otherwise, as TMinuit::Migrad returns it.
 #pragma once
 #include <memory>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include <Minuit2/FCNBase.h>
@@ -35,7 +36,7 @@ class TMinuit {
 
     Int_t DefineParameter(Int_t parNo, const char *name, Double_t initVal, Double_t initErr, Double_t lowerLimit, Double_t upperLimit) {
         if(parNo != (Int_t)names_.size() || parNo >= maxpar_ || !(initErr >= 0)) return 4;
-        if(lowerLimit != upperLimit && !(lowerLimit < upperLimit)) return 4; // TMinuit rejects crossed limits
+        if(lowerLimit > upperLimit) std::swap(lowerLimit, upperLimit); // TMinuit: "PARAMETER LIMITS HAVE BEEN REVERSED" (GooFit's constants come with crossed limits)
         std::string n = name ? name : "";
         if(lowerLimit == upperLimit)
             upar_.Add(n, initVal, initErr);
