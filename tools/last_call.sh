@@ -1,12 +1,12 @@
 #!/bin/bash
-# tools/last_call.sh — one short gpurun call (1 GPU): the reference's ROOT-using examples (built unmodified against tests/ref_root), the
+# tools/last_call.sh — one short gpurun call (1 GPU): the reference's ROOT- and TMinuit-using examples (built unmodified against tests/ref_root), the
 # whole GPU test suite (no -x: every failure is listed), then the bench line and the reference arm. No ncu pass: no kernel changed
 # since tools/final_capture.sh last ran.
 set -u
 R=$(pwd)
 mkdir -p gpurun_out
 T=$(mktemp -d)
-for spec in "ref_dalitz --make-toy" "ref_addition" "ref_simpleFit" "ref_convolution" "ref_2d_plot" "ref_SigGen" "ref_TDDP4 -t 2"; do
+for spec in "ref_dalitz --make-toy" "ref_addition" "ref_simpleFit" "ref_convolution" "ref_2d_plot" "ref_SigGen" "ref_TDDP4 -t 2" "ref_exponential1" "ref_exponential2" "ref_chisquare"; do
     set -- $spec
     name=$1; shift
     mkdir -p $T/$name
