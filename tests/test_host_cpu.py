@@ -623,3 +623,23 @@ def test_landau_helpers_against_the_reference_header():
     import goofit_b200.landau as L2
     import goofit
     assert goofit.landau is L2
+
+
+def test_application_is_a_cli_app_help_and_parse_errors():
+    """GooFit::Application as upstream's CLI::App (Application.h:48-93), on the reference's own dalitz.cpp built unmodified: --help
+    lists the example's options and the GooFit group and exits 0; an unknown option and a missing file are CLI11 parse errors with
+    CLI11's exit codes. None of this needs a device: parsing ends before the first CUDA call."""
+    import subprocess
+    exe = os.path.join(ROOT, "examples", "bin", "ref_dalitz")
+    if not os.path.exists(exe):
+        pytest.skip("examples/bin/ref_dalitz not built (needs the reference checkout at build time)")
+    r = subprocess.run([exe, "--help"], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 0, r.stdout + r.stderr
+    for word in ("--make-toy", "--filename", "--gpu-dev", "--info-only", "--quiet", "--nosplash", "--config", "GooFit"):
+        assert word in r.stdout, (word, r.stdout)
+    r = subprocess.run([exe, "--no-such-option"], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 109 and "--no-such-option" in (r.stdout + r.stderr)  # CLI::ExitCodes::ExtrasError
+    r = subprocess.run([exe, "-f", "/no/such/file.txt"], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 105 and "file" in (r.stdout + r.stderr).lower()  # CLI::ExitCodes::ValidationError
+    r = subprocess.run([exe, "-q", "--nosplash"], capture_output=True, text=True, timeout=60)
+    assert r.returncode != 0 and "excludes" in (r.stdout + r.stderr).lower()  # the two GooFit flags exclude each other, as upstream
