@@ -2,6 +2,7 @@
 #include <goofit/Variable.h>
 #include <goofit/detail/Abort.h>
 #include <goofit/detail/Complex.h>
+#include <goofit/PDFs/physics/Amp3Body.h>
 #include <goofit/utilities/Uncertain.h>
 
 #include <cmath>
@@ -41,5 +42,25 @@ int main() {
         return 11;
     } catch(const GeneralError &) {
     }
+    // GenerateSig's return type: flat columns -> upstream's tuple of MCBooster host containers (the receiver owns the sets)
+    GeneratedSignal G;
+    G.particles = {{1, 2, 3, 4, 5, 6, 7, 8}, {9, 10, 11, 12, 13, 14, 15, 16}};
+    G.variables = {{0.1, 0.2}, {0.3, 0.4}, {0.5, 0.6}};
+    G.weights   = {0.7, 0.8};
+    G.flags     = {true, false};
+    mcbooster::ParticlesSet_h particles;
+    mcbooster::VariableSet_h variables;
+    mcbooster::RealVector_h weights;
+    mcbooster::BoolVector_h flags;
+    std::tie(particles, variables, weights, flags) = toMCBoosterContainers<mcbooster::BoolVector_h>(G);
+    if(particles.size() != 2 || variables.size() != 3 || weights.size() != 2 || flags.size() != 2) return 12;
+    if((*particles[1])[1].get(0) != 13 || (*particles[1])[1].get(3) != 16 || (*particles[0])[0].get(1) != 2) return 13;
+    if((*variables[2])[1] != 0.6 || weights[0] != 0.7 || !flags[0] || flags[1]) return 14;
+    for(auto *p : particles) delete p;
+    for(auto *v : variables) delete v;
+    auto asReal = toMCBoosterContainers<mcbooster::RealVector_h>(G); // Amp3Body / Amp4Body: the flags as 0 / 1 reals
+    if(std::get<3>(asReal)[0] != 1.0 || std::get<3>(asReal)[1] != 0.0) return 15;
+    for(auto *p : std::get<0>(asReal)) delete p;
+    for(auto *v : std::get<1>(asReal)) delete v;
     return 0;
 }
